@@ -1,0 +1,92 @@
+"""ctypes binding of the in-tree C-ABI library (include/hanabi_b200.h).
+
+There is no CPU fallback: if the library is missing this module raises, and
+every compute entry point fails with HB_ERR_CUDA when no device is usable.
+"""
+import ctypes as C
+import os
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "_lib", "libhanabi_b200.so")
+
+HB_OK = 0
+HB_ERR_INVALID = -1
+HB_ERR_CUDA = -2
+HB_ERR_INDEX = -3
+HB_ERR_STATE = -4
+
+_lib = None
+
+vp = C.c_void_p
+i64 = C.c_int64
+i32 = C.c_int
+f32 = C.c_float
+
+# name -> (restype, argtypes); kept in step with include/hanabi_b200.h
+SIGNATURES = {
+    "hb_last_error": (C.c_char_p, []),
+    "hb_version": (i32, []),
+    "hb_build_arch": (C.c_char_p, []),
+    # sum tree
+    "hb_st_create": (i32, [i64, i32, C.POINTER(vp)]),
+    "hb_st_destroy": (i32, [vp]),
+    "hb_st_capacity": (i64, [vp]),
+    "hb_st_depth": (i32, [vp]),
+    "hb_st_heap": (vp, [vp]),
+    "hb_st_update": (i32, [vp, vp, vp, i64, vp]),
+    "hb_st_update_range": (i32, [vp, i64, i64, vp, f32, vp]),
+    "hb_st_get_indices": (i32, [vp, vp, vp, i64, vp]),
+    "hb_st_get_values": (i32, [vp, vp, vp, i64, vp]),
+    "hb_st_total": (i32, [vp, vp, vp]),
+    "hb_st_sample": (i32, [vp, vp, vp, vp, vp, i64, vp]),
+    "hb_st_check": (i32, [vp, vp]),
+    "hb_st_update_host": (i32, [vp, vp, vp, i64]),
+    "hb_st_get_indices_host": (i32, [vp, vp, vp, i64]),
+    "hb_st_get_values_host": (i32, [vp, vp, vp, i64]),
+    "hb_st_total_host": (i32, [vp, vp]),
+    "hb_st_heap_host": (i32, [vp, vp]),
+}
+
+
+class HanabiB200Error(RuntimeError):
+    pass
+
+
+def lib():
+    """Load (once) and return the C-ABI library.  Raises if it is not built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise HanabiB200Error(
+            "CUDA extension %s is missing; build it with "
+            "`python -m hanabi_agents_b200.build` (there is no CPU fallback)" % LIB_PATH)
+    handle = C.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(handle, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = handle
+    return _lib
+
+
+def last_error():
+    return lib().hb_last_error().decode("utf-8", "replace")
+
+
+def check(rc):
+    """Map a C return code to a Python exception."""
+    if rc == HB_OK:
+        return
+    msg = last_error()
+    if rc == HB_ERR_INDEX:
+        raise IndexError(msg)
+    if rc == HB_ERR_INVALID:
+        raise ValueError(msg)
+    raise HanabiB200Error("hanabi_b200 error %d: %s" % (rc, msg))
+
+
+def current_stream_ptr():
+    """cudaStream_t of torch's current stream (torch is used for hand-off only)."""
+    import torch
+    return torch.cuda.current_stream().cuda_stream

@@ -1,0 +1,442 @@
+// Batched prioritized-replay sum tree for sm_100a.
+//
+// Replaces the pointer-chasing SumTree<float> of the reference
+// (sum_tree/sum_tree/include/sum_tree.h:22-130) with a flat 1-indexed heap in
+// HBM (it is 32 MiB at capacity 2^22, so it lives in the 126 MB L2):
+//   heap[1] = root, level l = [2^l, 2^(l+1)), leaves = [cap, 2*cap).
+//
+// Arithmetic contract (bit-exact against the reference run with one thread):
+//   * get_index:  q = quantile * root (one fp32 multiply), then per level
+//     `q < left ? go left : (q -= left, go right)`          sum_tree.h:46-50,92-105
+//   * update:     diff = value - leaf; every node on the leaf..root path does
+//     `node += diff` in fp32, elements applied in batch order.  Internal nodes
+//     are never recomputed from their children.               sum_tree.h:32-35,80-90
+// The update kernel keeps that order without serialising the batch: one warp
+// per tree level, 32 batch elements at a time; elements that hit the same node
+// are grouped with __match_any_sync and their diffs are added in lane (= batch)
+// order by the group's first lane, so duplicate leaves/ancestors are resolved
+// deterministically (the reference races on them under OpenMP).
+//
+// This file is compiled with -fmad=false: no multiply-add contraction may
+// change the reference's rounding.
+#include "common.cuh"
+#include <math.h>
+#include <new>
+
+struct hb_sumtree {
+  int device = 0;
+  int depth = 0;
+  int64_t cap = 0;       // 2^depth leaves
+  float* heap = nullptr; // 2*cap floats
+  int* err = nullptr;    // sticky out-of-range flag (device)
+  float* scratch = nullptr;  // diffs for the range update
+  int64_t scratch_n = 0;
+  // staging for the *_host entry points
+  void* stage = nullptr;
+  size_t stage_bytes = 0;
+};
+
+namespace {
+
+constexpr int kTopLevels = 11;                // levels 0..10 staged in smem
+constexpr int kTopNodes = 1 << kTopLevels;    // heap[1 .. 2047]
+constexpr int kDescendThreads = 256;
+constexpr int kPass = 1024;                   // batch elements per update pass
+
+__device__ __forceinline__ float ld_cg(const float* p) { return __ldcg(p); }
+__device__ __forceinline__ void st_cg(float* p, float v) { __stcg(p, v); }
+
+// ---- stratified prefix-sum descent (ST-2) + leaf gather (ST-3) -------------
+template <bool kWithValues>
+__global__ void __launch_bounds__(kDescendThreads)
+st_descend_kernel(const float* __restrict__ heap, int depth, int64_t cap,
+                  const float* __restrict__ q_in, int64_t* __restrict__ idx_out,
+                  float* __restrict__ val_out, float* __restrict__ total_out, int64_t n) {
+  __shared__ float top[kTopNodes];
+  const int staged = (int)min((int64_t)kTopNodes, 2 * cap);  // heap entries [0, staged)
+  for (int i = threadIdx.x; i < staged; i += kDescendThreads) top[i] = ld_cg(heap + i);
+  __syncthreads();
+
+  const int64_t k = (int64_t)blockIdx.x * kDescendThreads + threadIdx.x;
+  const float root = top[1];
+  if (kWithValues && total_out != nullptr && k == 0) *total_out = root;
+  if (k >= n) return;
+
+  float q = q_in[k] * root;  // getIndex: quantile * root_->value   sum_tree.h:47
+  int64_t node = 1;
+  for (int l = 0; l < depth; ++l) {
+    const int64_t left = node << 1;
+    const float lv = left < staged ? top[left] : ld_cg(heap + left);
+    if (q < lv) {             // sum_tree.h:99
+      node = left;
+    } else {                  // sum_tree.h:104
+      q = q - lv;
+      node = left + 1;
+    }
+  }
+  const int64_t leaf = node - cap;
+  idx_out[k] = leaf;
+  if (kWithValues) val_out[k] = node < staged ? top[node] : ld_cg(heap + node);
+}
+
+__global__ void st_gather_kernel(const float* __restrict__ heap, int64_t cap,
+                                 const int64_t* __restrict__ idx, float* __restrict__ out,
+                                 int64_t n, int* err) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  const int64_t i = idx[k];
+  if (i < 0 || i >= cap) {  // leaves_.at(idx) throws   sum_tree.h:62
+    *err = 1;
+    out[k] = 0.0f;
+    return;
+  }
+  out[k] = ld_cg(heap + cap + i);
+}
+
+__global__ void st_total_kernel(const float* __restrict__ heap, float* out) { *out = ld_cg(heap + 1); }
+
+// ---- ordered scatter-update (ST-4), general batch ---------------------------
+// One CTA.  Warp 0 first walks the batch at the leaf level (it needs the old
+// leaf to form diff), publishing diffs in shared memory; then warp w owns tree
+// level(s) depth-1-w, depth-1-w-nwarps, ... and replays the diffs there.
+__global__ void __launch_bounds__(1024)
+st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
+                 const int64_t* __restrict__ idx, const float* __restrict__ val, int64_t n,
+                 int* err) {
+  __shared__ float s_diff[kPass];
+  __shared__ int64_t s_leaf[kPass];  // heap position of the leaf, or -1
+  const int lane = threadIdx.x & 31;
+  const int warp = threadIdx.x >> 5;
+  const int nwarps = blockDim.x >> 5;
+  const unsigned full = 0xffffffffu;
+
+  for (int64_t base = 0; base < n; base += kPass) {
+    const int pass_n = (int)min((int64_t)kPass, n - base);
+    if (warp == 0) {
+      for (int c0 = 0; c0 < pass_n; c0 += 32) {
+        const int cnt = min(32, pass_n - c0);
+        const bool active = lane < cnt;
+        int64_t li = -1;
+        float v = 0.0f;
+        if (active) {
+          li = idx[base + c0 + lane];
+          v = val[base + c0 + lane];
+          if (li < 0 || li >= cap) { *err = 1; li = -1; }
+        }
+        const int64_t pos = li >= 0 ? cap + li : -1;
+        const long long key = li >= 0 ? (long long)pos : -(long long)(lane + 1);
+        const unsigned m = __match_any_sync(full, key);
+        const bool leader = (li >= 0) && (lane == __ffs(m) - 1);
+        float L = leader ? ld_cg(heap + pos) : 0.0f;
+        s_leaf[c0 + lane] = pos;
+        if (li < 0) s_diff[c0 + lane] = 0.0f;
+        for (int b = 0; b < cnt; ++b) {
+          const float vb = __shfl_sync(full, v, b);
+          if (leader && ((m >> b) & 1u)) {
+            const float d = vb - L;  // updateValue: value - leaf   sum_tree.h:33
+            L = L + d;               // updateValue_: node->value += diff   :84
+            s_diff[c0 + b] = d;
+          }
+        }
+        if (leader) st_cg(heap + pos, L);
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+    // internal levels, deepest first is not required: levels are independent.
+    for (int l = depth - 1 - warp; l >= 0; l -= nwarps) {
+      const int shift = depth - l;
+      for (int c0 = 0; c0 < pass_n; c0 += 32) {
+        const int cnt = min(32, pass_n - c0);
+        const int64_t pos = lane < cnt ? s_leaf[c0 + lane] : -1;
+        const int64_t node = pos >= 0 ? (pos >> shift) : -1;
+        const long long key = pos >= 0 ? (long long)node : -(long long)(lane + 1);
+        const unsigned m = __match_any_sync(full, key);
+        const bool leader = (pos >= 0) && (lane == __ffs(m) - 1);
+        float s = leader ? ld_cg(heap + node) : 0.0f;
+        for (int b = 0; b < cnt; ++b) {
+          const float db = s_diff[c0 + b];
+          if (leader && ((m >> b) & 1u)) s = s + db;
+        }
+        if (leader) st_cg(heap + node, s);
+        __syncwarp();
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---- ordered update of a contiguous ascending leaf range (PB-3 inserts) ----
+__global__ void st_range_leaf_kernel(float* __restrict__ heap, int64_t cap, int64_t start,
+                                     int64_t n, const float* __restrict__ val, float fill,
+                                     float* __restrict__ diff) {
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (k >= n) return;
+  float* leaf = heap + cap + start + k;
+  const float old = *leaf;
+  const float v = val ? val[k] : fill;
+  const float d = v - old;
+  *leaf = old + d;
+  diff[k] = d;
+}
+
+// blockIdx.y = internal level (0 = root); one thread per covered node adds the
+// diffs of its covered leaves in ascending (= batch) order.
+__global__ void st_range_internal_kernel(float* __restrict__ heap, int depth, int64_t cap,
+                                         int64_t start, int64_t n,
+                                         const float* __restrict__ diff) {
+  const int l = blockIdx.y;
+  const int shift = depth - l;
+  const int64_t first = (cap + start) >> shift;
+  const int64_t last = (cap + start + n - 1) >> shift;
+  const int64_t node = first + (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (node > last) return;
+  int64_t lo = (node << shift) - cap;            // first leaf under node
+  int64_t hi = lo + ((int64_t)1 << shift);       // one past last leaf
+  lo = max(lo, start);
+  hi = min(hi, start + n);
+  float s = heap[node];
+  const float* d = diff + (lo - start);
+  const int64_t cnt = hi - lo;
+  int64_t k = 0;
+  for (; k + 8 <= cnt; k += 8) {
+    float t[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) t[j] = __ldg(d + k + j);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s = s + t[j];
+  }
+  for (; k < cnt; ++k) s = s + __ldg(d + k);
+  heap[node] = s;
+}
+
+int ensure_stage(hb_sumtree* t, size_t bytes) {
+  if (t->stage_bytes >= bytes) return HB_OK;
+  if (t->stage) cudaFree(t->stage);
+  t->stage = nullptr;
+  t->stage_bytes = 0;
+  size_t want = bytes < 4096 ? 4096 : bytes * 2;
+  HB_CUDA(cudaMalloc(&t->stage, want));
+  t->stage_bytes = want;
+  return HB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hb_st_create(int64_t capacity, int device, hb_sumtree** out) {
+  HB_REQUIRE(out != nullptr, "hb_st_create: out is NULL");
+  HB_REQUIRE(capacity >= 1, "hb_st_create: capacity must be >= 1 (got %lld)", (long long)capacity);
+  // depth_ = ceil(log2(capacity))   sum_tree.h:28
+  const int depth = (int)ceil(log2((double)capacity));
+  HB_REQUIRE(depth <= 30, "hb_st_create: capacity %lld too large", (long long)capacity);
+  hb::DeviceGuard g(device);
+  if (!g.ok) { hb::set_error("hb_st_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
+  hb_sumtree* t = new (std::nothrow) hb_sumtree();
+  HB_REQUIRE(t != nullptr, "hb_st_create: out of host memory");
+  t->device = device;
+  t->depth = depth;
+  t->cap = (int64_t)1 << depth;
+  cudaError_t e = cudaMalloc(&t->heap, sizeof(float) * 2 * t->cap);
+  if (e == cudaSuccess) e = cudaMemset(t->heap, 0, sizeof(float) * 2 * t->cap);
+  if (e == cudaSuccess) e = cudaMalloc(&t->err, sizeof(int));
+  if (e == cudaSuccess) e = cudaMemset(t->err, 0, sizeof(int));
+  if (e != cudaSuccess) {
+    if (t->heap) cudaFree(t->heap);
+    if (t->err) cudaFree(t->err);
+    delete t;
+    return hb::cuda_fail(e, "hb_st_create alloc", __FILE__, __LINE__);
+  }
+  *out = t;
+  return HB_OK;
+}
+
+int hb_st_destroy(hb_sumtree* t) {
+  if (!t) return HB_OK;
+  hb::DeviceGuard g(t->device);
+  if (t->heap) cudaFree(t->heap);
+  if (t->err) cudaFree(t->err);
+  if (t->scratch) cudaFree(t->scratch);
+  if (t->stage) cudaFree(t->stage);
+  delete t;
+  return HB_OK;
+}
+
+int64_t hb_st_capacity(const hb_sumtree* t) { return t ? t->cap : 0; }
+int hb_st_depth(const hb_sumtree* t) { return t ? t->depth : -1; }
+float* hb_st_heap(hb_sumtree* t) { return t ? t->heap : nullptr; }
+
+int hb_st_update(hb_sumtree* t, const int64_t* d_idx, const float* d_val, int64_t n, void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_update: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(d_idx && d_val, "hb_st_update: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  int warps = t->depth + 1;
+  if (warps > 32) warps = 32;
+  if (warps < 1) warps = 1;
+  st_update_kernel<<<1, warps * 32, 0, (cudaStream_t)stream>>>(t->heap, t->depth, t->cap, d_idx,
+                                                                d_val, n, t->err);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
+                       void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_update_range: bad arguments");
+  if (n == 0) return HB_OK;
+  if (start < 0 || start + n > t->cap) {
+    hb::set_error("hb_st_update_range: [%lld,%lld) outside capacity %lld", (long long)start,
+                  (long long)(start + n), (long long)t->cap);
+    return HB_ERR_INDEX;
+  }
+  hb::DeviceGuard g(t->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (t->scratch_n < n) {
+    HB_CUDA(cudaStreamSynchronize(s));
+    if (t->scratch) cudaFree(t->scratch);
+    t->scratch = nullptr;
+    t->scratch_n = 0;
+    HB_CUDA(cudaMalloc(&t->scratch, sizeof(float) * n));
+    t->scratch_n = n;
+  }
+  const int threads = 256;
+  st_range_leaf_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, s>>>(
+      t->heap, t->cap, start, n, d_val, fill, t->scratch);
+  HB_CUDA(cudaGetLastError());
+  if (t->depth > 0) {
+    const int64_t widest = n / 2 + 2;  // nodes covered at the deepest internal level
+    const int th = 128;
+    dim3 grid((unsigned)((widest + th - 1) / th), (unsigned)t->depth);
+    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch);
+    HB_CUDA(cudaGetLastError());
+  }
+  return HB_OK;
+}
+
+int hb_st_get_indices(hb_sumtree* t, const float* d_q, int64_t* d_out, int64_t n, void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_get_indices: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(d_q && d_out, "hb_st_get_indices: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  const unsigned blocks = (unsigned)((n + kDescendThreads - 1) / kDescendThreads);
+  st_descend_kernel<false><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+      t->heap, t->depth, t->cap, d_q, d_out, nullptr, nullptr, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_st_sample(hb_sumtree* t, const float* d_q, int64_t* d_idx_out, float* d_val_out,
+                 float* d_total, int64_t n, void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_sample: bad arguments");
+  if (n == 0) {
+    if (d_total) return hb_st_total(t, d_total, stream);
+    return HB_OK;
+  }
+  HB_REQUIRE(d_q && d_idx_out && d_val_out, "hb_st_sample: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  const unsigned blocks = (unsigned)((n + kDescendThreads - 1) / kDescendThreads);
+  st_descend_kernel<true><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+      t->heap, t->depth, t->cap, d_q, d_idx_out, d_val_out, d_total, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_st_get_values(hb_sumtree* t, const int64_t* d_idx, float* d_out, int64_t n, void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_get_values: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(d_idx && d_out, "hb_st_get_values: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  st_gather_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      t->heap, t->cap, d_idx, d_out, n, t->err);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_st_total(hb_sumtree* t, float* d_out, void* stream) {
+  HB_REQUIRE(t && d_out, "hb_st_total: bad arguments");
+  hb::DeviceGuard g(t->device);
+  st_total_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(t->heap, d_out);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_st_check(hb_sumtree* t, void* stream) {
+  HB_REQUIRE(t, "hb_st_check: NULL tree");
+  hb::DeviceGuard g(t->device);
+  int flag = 0;
+  HB_CUDA(cudaMemcpyAsync(&flag, t->err, sizeof(int), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  if (flag) {
+    HB_CUDA(cudaMemsetAsync(t->err, 0, sizeof(int), (cudaStream_t)stream));
+    hb::set_error("sum tree: index out of range");
+    return HB_ERR_INDEX;
+  }
+  return HB_OK;
+}
+
+// ---- host-buffer forms (the pybind surface) --------------------------------
+int hb_st_update_host(hb_sumtree* t, const int64_t* h_idx, const float* h_val, int64_t n) {
+  HB_REQUIRE(t && n >= 0, "hb_st_update_host: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(h_idx && h_val, "hb_st_update_host: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  int rc = ensure_stage(t, (size_t)n * 12);
+  if (rc) return rc;
+  int64_t* d_idx = (int64_t*)t->stage;
+  float* d_val = (float*)((char*)t->stage + (size_t)n * 8);
+  HB_CUDA(cudaMemcpyAsync(d_idx, h_idx, (size_t)n * 8, cudaMemcpyHostToDevice, 0));
+  HB_CUDA(cudaMemcpyAsync(d_val, h_val, (size_t)n * 4, cudaMemcpyHostToDevice, 0));
+  rc = hb_st_update(t, d_idx, d_val, n, nullptr);
+  if (rc) return rc;
+  return hb_st_check(t, nullptr);
+}
+
+int hb_st_get_indices_host(hb_sumtree* t, const float* h_q, int64_t* h_out, int64_t n) {
+  HB_REQUIRE(t && n >= 0, "hb_st_get_indices_host: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(h_q && h_out, "hb_st_get_indices_host: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  int rc = ensure_stage(t, (size_t)n * 12);
+  if (rc) return rc;
+  int64_t* d_out = (int64_t*)t->stage;
+  float* d_q = (float*)((char*)t->stage + (size_t)n * 8);
+  HB_CUDA(cudaMemcpyAsync(d_q, h_q, (size_t)n * 4, cudaMemcpyHostToDevice, 0));
+  rc = hb_st_get_indices(t, d_q, d_out, n, nullptr);
+  if (rc) return rc;
+  HB_CUDA(cudaMemcpy(h_out, d_out, (size_t)n * 8, cudaMemcpyDeviceToHost));
+  return HB_OK;
+}
+
+int hb_st_get_values_host(hb_sumtree* t, const int64_t* h_idx, float* h_out, int64_t n) {
+  HB_REQUIRE(t && n >= 0, "hb_st_get_values_host: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(h_idx && h_out, "hb_st_get_values_host: NULL buffer");
+  hb::DeviceGuard g(t->device);
+  int rc = ensure_stage(t, (size_t)n * 12);
+  if (rc) return rc;
+  int64_t* d_idx = (int64_t*)t->stage;
+  float* d_out = (float*)((char*)t->stage + (size_t)n * 8);
+  HB_CUDA(cudaMemcpyAsync(d_idx, h_idx, (size_t)n * 8, cudaMemcpyHostToDevice, 0));
+  rc = hb_st_get_values(t, d_idx, d_out, n, nullptr);
+  if (rc) return rc;
+  HB_CUDA(cudaMemcpy(h_out, d_out, (size_t)n * 4, cudaMemcpyDeviceToHost));
+  return hb_st_check(t, nullptr);
+}
+
+int hb_st_total_host(hb_sumtree* t, float* h_out) {
+  HB_REQUIRE(t && h_out, "hb_st_total_host: bad arguments");
+  hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaMemcpy(h_out, t->heap + 1, sizeof(float), cudaMemcpyDeviceToHost));
+  return HB_OK;
+}
+
+int hb_st_heap_host(hb_sumtree* t, float* h_out) {
+  HB_REQUIRE(t && h_out, "hb_st_heap_host: bad arguments");
+  hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaDeviceSynchronize());
+  HB_CUDA(cudaMemcpy(h_out, t->heap, sizeof(float) * 2 * t->cap, cudaMemcpyDeviceToHost));
+  return HB_OK;
+}
+
+}  // extern "C"

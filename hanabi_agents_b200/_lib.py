@@ -21,6 +21,7 @@ vp = C.c_void_p
 i64 = C.c_int64
 i32 = C.c_int
 f32 = C.c_float
+u64 = C.c_uint64
 
 # name -> (restype, argtypes); kept in step with include/hanabi_b200.h
 SIGNATURES = {
@@ -45,6 +46,24 @@ SIGNATURES = {
     "hb_st_get_values_host": (i32, [vp, vp, vp, i64]),
     "hb_st_total_host": (i32, [vp, vp]),
     "hb_st_heap_host": (i32, [vp, vp]),
+    # environment
+    "hb_env_create": (i32, [i32, i32, i32, i32, i32, i32, i64, i32, C.POINTER(vp)]),
+    "hb_env_destroy": (i32, [vp]),
+    "hb_env_info": (i64, [vp, i32]),
+    "hb_env_set_shard": (i32, [vp, i64, i64]),
+    "hb_env_set_decks": (i32, [vp, vp, i64, vp]),
+    "hb_env_set_decks_host": (i32, [vp, vp, i64]),
+    "hb_env_reset": (i32, [vp, vp, vp, vp, vp]),
+    "hb_env_step": (i32, [vp, vp, vp, vp, vp, vp, vp]),
+    "hb_env_observe": (i32, [vp, i32, vp, vp, vp]),
+    "hb_env_illegal_count": (i32, [vp, C.POINTER(i64), vp]),
+    "hb_env_dump": (i32, [vp, vp, vp]),
+    "hb_env_unpack_obs": (i32, [vp, vp, vp, i64, vp]),
+    "hb_env_unpack_legal": (i32, [vp, vp, vp, i64, vp]),
+    "hb_env_step_host": (i32, [vp, vp, vp, vp, vp, vp]),
+    # rule-based agents
+    "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
+    "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),
 }
 
 

@@ -1,0 +1,575 @@
+// Batched Hanabi environment + rule-based policy kernels and their C ABI.
+// Device code: hanabi_game.cuh (state, legality, transition), hanabi_encode.cuh (canonical
+// observation), hanabi_rules.cuh (rule-based agents).  One warp per game, 8 games per CTA.
+#include "common.cuh"
+#include "hanabi_encode.cuh"
+#include "hanabi_rules.cuh"
+#include <new>
+#include <vector>
+
+using namespace hbg;
+
+struct hb_env {
+  int device = 0;
+  int P = 0, H = 0, C = 0, R = 0, shape = -1;
+  int deck_size = 0, num_moves = 0, legal_words = 0, state_words = 0;
+  Rt rt{};
+  uint32_t* state = nullptr;
+  uint8_t* decks = nullptr;
+  unsigned long long* illegal = nullptr;  // device counter
+  bool is_reset = false;
+  // staging for *_host entry points
+  void* stage = nullptr;
+  size_t stage_bytes = 0;
+};
+
+namespace {
+
+constexpr int kWarpsPerCta = 8;
+
+template <class SH>
+__device__ __forceinline__ void emit(const Game<SH>& g, const Rt& rt, long long game, uint32_t* buf,
+                                     uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
+                                     uint8_t* __restrict__ step_type) {
+  if (obs != nullptr) {
+    encode_obs(g, rt, g.cur, buf);
+    store_obs(rt, buf, obs, game);
+  }
+  if (legal != nullptr) {
+    const unsigned long long m = legal_mask(g, rt, g.cur);
+    if (lane_id() < SH::kLegalWords)
+      legal[game * SH::kLegalWords + lane_id()] = (uint32_t)(m >> (32 * lane_id()));
+  }
+  if (step_type != nullptr && lane_id() == 0) step_type[game] = (uint8_t)g.step_type;
+}
+
+template <class SH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
+                 uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
+                 uint8_t* __restrict__ step_type) {
+  extern __shared__ uint32_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  g.episode = 0;
+  reset_game(g, rt, deck_of<SH>(rt, decks, game, 0));
+  emit(g, rt, game, smem + warp * rt.obs_stride, obs, legal, step_type);
+  store_game(g, state, game);
+}
+
+// One env step for one game (shared by the step kernel and the fused self-play kernel).
+// A game whose previous step was LAST is reset onto its next deck (action ignored, reward 0,
+// FIRST) -- otherwise rl_env.step: apply, deal, reward = score delta.
+template <class SH>
+__device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
+                                           long long game, int action, unsigned long long* illegal) {
+  if (g.step_type == LAST) {
+    ++g.episode;
+    reset_game(g, rt, deck_of<SH>(rt, decks, game, g.episode));
+    return 0.0f;
+  }
+  const unsigned long long lm = legal_mask(g, rt, g.cur);
+  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {
+    if (lane_id() == 0) atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and skip
+    return 0.0f;
+  }
+  const int r = apply_move(g, rt, action, deck_of<SH>(rt, decks, game, g.episode));
+  g.step_type = g.terminal(rt) ? LAST : MID;
+  return (float)r;
+}
+
+template <class SH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
+                const int32_t* __restrict__ action, uint32_t* __restrict__ obs,
+                uint32_t* __restrict__ legal, float* __restrict__ reward,
+                uint8_t* __restrict__ step_type, unsigned long long* illegal) {
+  extern __shared__ uint32_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  const float r = step_game(g, rt, decks, game, action[game], illegal);
+  if (reward != nullptr && lane_id() == 0) reward[game] = r;
+  emit(g, rt, game, smem + warp * rt.obs_stride, obs, legal, step_type);
+  store_game(g, state, game);
+}
+
+template <class SH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
+                   uint32_t* __restrict__ obs, uint32_t* __restrict__ legal) {
+  extern __shared__ uint32_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  int q = g.cur + offset;
+  if (q >= SH::P) q -= SH::P;
+  uint32_t* buf = smem + warp * rt.obs_stride;
+  if (obs != nullptr) {
+    encode_obs(g, rt, q, buf);
+    store_obs(rt, buf, obs, game);
+  }
+  if (legal != nullptr) {   // HanabiState::LegalMoves: empty unless it is that player's turn
+    const unsigned long long m = offset == 0 ? legal_mask(g, rt, q) : 0ull;
+    if (lane_id() < SH::kLegalWords)
+      legal[game * SH::kLegalWords + lane_id()] = (uint32_t)(m >> (32 * lane_id()));
+  }
+}
+
+// RulebasedAgent.explore over the whole batch (rule_based.py:27-31)
+template <class SH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned long long step,
+                 int32_t* __restrict__ action, int32_t* __restrict__ rule_hit,
+                 unsigned long long* __restrict__ hist) {
+  const int warp = threadIdx.x >> 5;
+  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  int a = 0, hit = -1;
+  if (g.step_type != LAST)
+    a = rules_act(g, rt, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
+  if (lane_id() == 0) {
+    action[game] = a;
+    if (rule_hit != nullptr) rule_hit[game] = hit;
+    if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
+  }
+}
+
+// Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
+// held in registers; only the per-step outputs touch HBM.  Output row (t, game).
+template <class SH>
+__global__ void __launch_bounds__(kWarpsPerCta * 32)
+selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks, RuleSet rs,
+                unsigned long long step0, int n_steps, uint32_t* __restrict__ obs,
+                uint32_t* __restrict__ legal, float* __restrict__ reward,
+                uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
+                unsigned long long* __restrict__ hist, unsigned long long* illegal) {
+  extern __shared__ uint32_t smem[];
+  const int warp = threadIdx.x >> 5;
+  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  uint32_t* buf = smem + warp * rt.obs_stride;
+  for (int t = 0; t < n_steps; ++t) {
+    int a = 0, hit = -1;
+    if (g.step_type != LAST)
+      a = rules_act(g, rt, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
+    const float r = step_game(g, rt, decks, game, a, illegal);
+    const long long row = (long long)t * rt.n_games + game;
+    if (lane_id() == 0) {
+      if (action != nullptr) action[row] = a;
+      if (reward != nullptr) reward[row] = r;
+      if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
+    }
+    emit(g, rt, row, buf, obs, legal, step_type);
+  }
+  store_game(g, state, game);
+}
+
+// canonical int32 dump, one thread per game (tests; layout = oracle ho_env_dump)
+template <class SH>
+__global__ void env_dump_kernel(Rt rt, const uint32_t* __restrict__ state, int32_t* __restrict__ out,
+                                int dump_len) {
+  const long long game = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (game >= rt.n_games) return;
+  const uint32_t* w = state + game * SH::kStateWords;
+  const uint32_t a = w[SH::S], b = w[SH::S + 1];
+  const unsigned long long disc = (unsigned long long)w[SH::S + 2] | ((unsigned long long)w[SH::S + 3] << 32);
+  const uint32_t last = w[SH::S + 4];
+  int32_t* o = out + game * dump_len;
+  int k = 0;
+  const int life = (a >> 19) & 3;
+  int score = 0;
+  for (int c = 0; c < SH::C; ++c) score += (a >> (3 * c)) & 7;
+  o[k++] = (a >> 21) & 7; o[k++] = (a >> 15) & 15; o[k++] = life;
+  o[k++] = SH::DECK - (int)(b & 63); o[k++] = (a >> 24) & 7; o[k++] = (a >> 27) & 3;
+  o[k++] = life <= 0 ? 0 : score; o[k++] = (int32_t)(w[SH::S + 5] & 0x7fffffff);
+  for (int c = 0; c < SH::C; ++c) o[k++] = (a >> (3 * c)) & 7;
+  for (int p = 0; p < SH::P; ++p) o[k++] = (b >> (6 + 3 * p)) & 7;
+  for (int s = 0; s < SH::S; ++s) {
+    const uint32_t sw = w[s];
+    const bool have = slot_valid(sw);
+    const int cp = slot_cplaus(sw), rp = slot_rplaus(sw);
+    o[k++] = have ? slot_card(sw) : -1;
+    o[k++] = have ? cp : 0;
+    o[k++] = have ? rp : 0;
+    o[k++] = have && slot_chint(sw) ? __ffs(cp) - 1 : -1;
+    o[k++] = have && slot_rhint(sw) ? __ffs(rp) - 1 : -1;
+  }
+  for (int t = 0; t < SH::BPC; ++t) o[k++] = (int)((disc >> (2 * t)) & 3ull);
+  if (last & 1u) {
+    const int uid = (last >> 4) & 63;
+    const bool card_move = uid < 2 * SH::H;
+    int type, idx = -1, off = -1, mc = -1, mr = -1;
+    if (card_move) {
+      type = uid >= SH::H ? PLAY : DISCARD;
+      idx = uid >= SH::H ? uid - SH::H : uid;
+    } else {
+      int u = uid - 2 * SH::H;
+      const bool by_color = u < (SH::P - 1) * SH::C;
+      if (!by_color) u -= (SH::P - 1) * SH::C;
+      const int span = by_color ? SH::C : SH::R;
+      off = 1 + u / span;
+      type = by_color ? REVEAL_COLOR : REVEAL_RANK;
+      if (by_color) mc = u % span; else mr = u % span;
+    }
+    o[k++] = 1; o[k++] = (last >> 1) & 7; o[k++] = type; o[k++] = idx; o[k++] = off;
+    o[k++] = mc; o[k++] = mr;
+    o[k++] = card_move ? (int)((last >> 10) & 7) : -1;
+    o[k++] = card_move ? (int)((last >> 13) & 7) : -1;
+    o[k++] = (last >> 16) & 1; o[k++] = (last >> 17) & 1; o[k++] = (last >> 18) & 31;
+  } else {
+    for (int j = 0; j < 12; ++j) o[k++] = 0;
+  }
+}
+
+// bit-packed rows -> one byte per bit ([n, bits] int8, the reference's layout:
+// experience_buffer.py:9-12 stores obs / legal moves as np.byte)
+__global__ void unpack_bits_kernel(const uint32_t* __restrict__ packed, int stride_words, int bits,
+                                   int8_t* __restrict__ out, long long n) {
+  const long long total = n * bits;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long row = i / bits;
+    const int b = (int)(i - row * bits);
+    out[i] = (int8_t)((packed[row * stride_words + (b >> 5)] >> (b & 31)) & 1u);
+  }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ host side ----
+namespace {
+
+// The kernels are instantiated for the game shapes the reference's environments produce
+// (Hanabi-Full 2..5 players, Hanabi-Small, Hanabi-Very-Small; run_experiment.py:115-128).
+#define HB_SHAPES(X)            \
+  X(0, 2, 5, 5, 5)              \
+  X(1, 3, 5, 5, 5)              \
+  X(2, 4, 4, 5, 5)              \
+  X(3, 5, 4, 5, 5)              \
+  X(4, 2, 2, 2, 5)              \
+  X(5, 2, 2, 1, 5)
+
+int find_shape(int P, int H, int C, int R) {
+#define X(id, p, h, c, r) \
+  if (P == p && H == h && C == c && R == r) return id;
+  HB_SHAPES(X)
+#undef X
+  return -1;
+}
+
+#define HB_DISPATCH(env, CALL)                                                   \
+  switch ((env)->shape) {                                                        \
+    case 0: { using SH = Shape<2, 5, 5, 5>; CALL; break; }                       \
+    case 1: { using SH = Shape<3, 5, 5, 5>; CALL; break; }                       \
+    case 2: { using SH = Shape<4, 4, 5, 5>; CALL; break; }                       \
+    case 3: { using SH = Shape<5, 4, 5, 5>; CALL; break; }                       \
+    case 4: { using SH = Shape<2, 2, 2, 5>; CALL; break; }                       \
+    case 5: { using SH = Shape<2, 2, 1, 5>; CALL; break; }                       \
+    default: hb::set_error("unsupported game shape"); return HB_ERR_INVALID;     \
+  }
+
+inline unsigned grid_for(const hb_env* e) {
+  return (unsigned)((e->rt.n_games + kWarpsPerCta - 1) / kWarpsPerCta);
+}
+inline size_t smem_for(const hb_env* e) { return (size_t)kWarpsPerCta * e->rt.obs_stride * 4; }
+
+int env_stage(hb_env* e, size_t bytes) {
+  if (e->stage_bytes >= bytes) return HB_OK;
+  if (e->stage) cudaFree(e->stage);
+  e->stage = nullptr;
+  e->stage_bytes = 0;
+  HB_CUDA(cudaMalloc(&e->stage, bytes));
+  e->stage_bytes = bytes;
+  return HB_OK;
+}
+
+int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int32_t* iarg, int n,
+                 unsigned long long seed) {
+  HB_REQUIRE(n >= 0 && n <= kMaxRules, "rule list too long (%d > %d)", n, kMaxRules);
+  HB_REQUIRE(n == 0 || ids != nullptr, "rule ids are NULL");
+  rs.n = n;
+  rs.seed = seed;
+  for (int k = 0; k < n; ++k) {
+    HB_REQUIRE(ids[k] >= 0 && ids[k] < R_NUM_RULES, "unknown rule id %d", ids[k]);
+    rs.id[k] = ids[k];
+    rs.farg[k] = farg ? farg[k] : 0.0;
+    rs.iarg[k] = iarg ? iarg[k] : 0;
+  }
+  return HB_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hb_env_create(int players, int colors, int ranks, int hand_size, int max_info, int max_life,
+                  int64_t n_games, int device, hb_env** out) {
+  HB_REQUIRE(out != nullptr, "hb_env_create: out is NULL");
+  HB_REQUIRE(n_games >= 1, "hb_env_create: n_games must be >= 1");
+  const int shape = find_shape(players, hand_size, colors, ranks);
+  HB_REQUIRE(shape >= 0, "hb_env_create: unsupported game shape players=%d hand=%d colors=%d ranks=%d",
+             players, hand_size, colors, ranks);
+  HB_REQUIRE(max_info >= 0 && max_info <= 8 && max_life >= 1 && max_life <= 3,
+             "hb_env_create: max_info must be 0..8 and max_life 1..3");
+  hb::DeviceGuard g(device);
+  if (!g.ok) { hb::set_error("hb_env_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
+  hb_env* e = new (std::nothrow) hb_env();
+  HB_REQUIRE(e != nullptr, "hb_env_create: out of host memory");
+  e->device = device;
+  e->P = players; e->H = hand_size; e->C = colors; e->R = ranks; e->shape = shape;
+  const int bpc = colors * ranks;
+  int per_color = 0;
+  for (int r = 0; r < ranks; ++r) per_color += r == 0 ? 3 : (r == ranks - 1 ? 1 : 2);
+  e->deck_size = colors * per_color;
+  e->num_moves = 2 * hand_size + (players - 1) * (colors + ranks);
+  e->legal_words = (e->num_moves + 31) / 32;
+  e->state_words = (players * hand_size + 6 <= 16) ? 16 : 32;
+  Rt& rt = e->rt;
+  rt.max_info = max_info; rt.max_life = max_life;
+  const int hands_len = (players - 1) * hand_size * bpc + players;
+  rt.deck_thermo = e->deck_size - players * hand_size;
+  const int board_len = rt.deck_thermo + bpc + max_info + max_life;
+  const int last_len = players + 4 + players + colors + ranks + 2 * hand_size + bpc + 2;
+  const int know_len = players * hand_size * (bpc + colors + ranks);
+  rt.off_board = hands_len;
+  rt.off_disc = rt.off_board + board_len;
+  rt.off_last = rt.off_disc + e->deck_size;
+  rt.off_know = rt.off_last + last_len;
+  rt.obs_len = rt.off_know + know_len;
+  rt.obs_stride = (((rt.obs_len + 31) / 32) + 3) / 4 * 4;
+  rt.n_games = n_games; rt.n_total = n_games; rt.game_id_base = 0; rt.n_decks = 0;
+  cudaError_t err = cudaMalloc(&e->state, (size_t)n_games * e->state_words * 4);
+  if (err == cudaSuccess) err = cudaMemset(e->state, 0, (size_t)n_games * e->state_words * 4);
+  if (err == cudaSuccess) err = cudaMalloc(&e->illegal, sizeof(unsigned long long));
+  if (err == cudaSuccess) err = cudaMemset(e->illegal, 0, sizeof(unsigned long long));
+  if (err != cudaSuccess) {
+    if (e->state) cudaFree(e->state);
+    if (e->illegal) cudaFree(e->illegal);
+    delete e;
+    return hb::cuda_fail(err, "hb_env_create alloc", __FILE__, __LINE__);
+  }
+  *out = e;
+  return HB_OK;
+}
+
+int hb_env_destroy(hb_env* e) {
+  if (!e) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  if (e->state) cudaFree(e->state);
+  if (e->decks) cudaFree(e->decks);
+  if (e->illegal) cudaFree(e->illegal);
+  if (e->stage) cudaFree(e->stage);
+  delete e;
+  return HB_OK;
+}
+
+int64_t hb_env_info(const hb_env* e, int what) {
+  if (!e) return -1;
+  switch (what) {
+    case 0: return e->rt.obs_len;
+    case 1: return e->rt.obs_stride;
+    case 2: return e->num_moves;
+    case 3: return e->legal_words;
+    case 4: return e->deck_size;
+    case 5: return e->state_words;
+    case 6: return e->rt.n_games;
+    case 7: return 8 + e->C + e->P + 5 * e->P * e->H + e->C * e->R + 12;  // dump length
+    case 8: return e->P;
+    default: return -1;
+  }
+}
+
+int hb_env_set_shard(hb_env* e, int64_t game_id_base, int64_t n_total) {
+  HB_REQUIRE(e && game_id_base >= 0 && n_total >= game_id_base + e->rt.n_games,
+             "hb_env_set_shard: bad shard [%lld, +%lld) of %lld", (long long)game_id_base,
+             e ? (long long)e->rt.n_games : 0ll, (long long)n_total);
+  e->rt.game_id_base = game_id_base;
+  e->rt.n_total = n_total;
+  return HB_OK;
+}
+
+int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* stream) {
+  HB_REQUIRE(e && d_decks && n_decks >= 1, "hb_env_set_decks: bad arguments");
+  hb::DeviceGuard g(e->device);
+  if (e->decks) { HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); cudaFree(e->decks); e->decks = nullptr; }
+  const size_t bytes = (size_t)n_decks * e->deck_size;
+  HB_CUDA(cudaMalloc(&e->decks, bytes));
+  HB_CUDA(cudaMemcpyAsync(e->decks, d_decks, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  e->rt.n_decks = n_decks;
+  return HB_OK;
+}
+
+int hb_env_set_decks_host(hb_env* e, const uint8_t* h_decks, int64_t n_decks) {
+  HB_REQUIRE(e && h_decks && n_decks >= 1, "hb_env_set_decks_host: bad arguments");
+  // every deck must be a permutation of the card multiset (HLE deals from exactly that multiset)
+  const int bpc = e->C * e->R;
+  for (int64_t d = 0; d < n_decks; ++d) {
+    int cnt[32] = {0};
+    for (int i = 0; i < e->deck_size; ++i) {
+      const int c = h_decks[d * e->deck_size + i];
+      HB_REQUIRE(c < bpc, "deck %lld holds card index %d >= %d", (long long)d, c, bpc);
+      cnt[c]++;
+    }
+    for (int c = 0; c < bpc; ++c) {
+      const int r = c % e->R;
+      const int want = r == 0 ? 3 : (r == e->R - 1 ? 1 : 2);
+      HB_REQUIRE(cnt[c] == want, "deck %lld is not a permutation of the card multiset", (long long)d);
+    }
+  }
+  int rc = hb_env_set_decks(e, h_decks, n_decks, nullptr);
+  if (rc) return rc;
+  hb::DeviceGuard g(e->device);
+  HB_CUDA(cudaStreamSynchronize(nullptr));
+  return HB_OK;
+}
+
+int hb_env_reset(hb_env* e, uint32_t* d_obs, uint32_t* d_legal, uint8_t* d_step_type, void* stream) {
+  HB_REQUIRE(e, "hb_env_reset: NULL env");
+  if (!e->decks) { hb::set_error("hb_env_reset: call hb_env_set_decks first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (env_reset_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+                     e->rt, e->state, e->decks, d_obs, d_legal, d_step_type)));
+  HB_CUDA(cudaGetLastError());
+  e->is_reset = true;
+  return HB_OK;
+}
+
+int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d_legal,
+                float* d_reward, uint8_t* d_step_type, void* stream) {
+  HB_REQUIRE(e && d_action, "hb_env_step: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_env_step: reset the environment first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (env_step_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+                     e->rt, e->state, e->decks, d_action, d_obs, d_legal, d_reward, d_step_type,
+                     e->illegal)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, void* stream) {
+  HB_REQUIRE(e && offset >= 0 && offset < e->P, "hb_env_observe: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_env_observe: reset the environment first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (env_observe_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+                     e->rt, e->state, offset, d_obs, d_legal)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_env_illegal_count(hb_env* e, int64_t* out, void* stream) {
+  HB_REQUIRE(e && out, "hb_env_illegal_count: bad arguments");
+  hb::DeviceGuard g(e->device);
+  unsigned long long v = 0;
+  HB_CUDA(cudaMemcpyAsync(&v, e->illegal, sizeof(v), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  *out = (int64_t)v;
+  return HB_OK;
+}
+
+int hb_env_dump(hb_env* e, int32_t* d_out, void* stream) {
+  HB_REQUIRE(e && d_out, "hb_env_dump: bad arguments");
+  hb::DeviceGuard g(e->device);
+  const int len = (int)hb_env_info(e, 7);
+  const unsigned blocks = (unsigned)((e->rt.n_games + 127) / 128);
+  HB_DISPATCH(e, (env_dump_kernel<SH><<<blocks, 128, 0, (cudaStream_t)stream>>>(e->rt, e->state, d_out, len)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_env_unpack_obs(hb_env* e, const uint32_t* d_packed, int8_t* d_out, int64_t n, void* stream) {
+  HB_REQUIRE(e && d_packed && d_out && n >= 0, "hb_env_unpack_obs: bad arguments");
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  const long long total = n * e->rt.obs_len;
+  const unsigned blocks = (unsigned)min((long long)148 * 16, (total + 255) / 256);
+  unpack_bits_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_packed, e->rt.obs_stride,
+                                                               e->rt.obs_len, d_out, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_env_unpack_legal(hb_env* e, const uint32_t* d_legal, int8_t* d_out, int64_t n, void* stream) {
+  HB_REQUIRE(e && d_legal && d_out && n >= 0, "hb_env_unpack_legal: bad arguments");
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  const long long total = n * e->num_moves;
+  const unsigned blocks = (unsigned)min((long long)148 * 16, (total + 255) / 256);
+  unpack_bits_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_legal, e->legal_words, e->num_moves,
+                                                               d_out, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, const int32_t* rule_iarg,
+                 int n_rules, uint64_t seed, uint64_t step, int32_t* d_action, int32_t* d_rule_hit,
+                 uint64_t* d_hist, void* stream) {
+  HB_REQUIRE(e && d_action, "hb_rules_act: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_rules_act: reset the environment first"); return HB_ERR_STATE; }
+  RuleSet rs;
+  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  if (rc) return rc;
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (rules_act_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, 0, (cudaStream_t)stream>>>(
+                     e->rt, e->state, rs, step, d_action, d_rule_hit,
+                     (unsigned long long*)d_hist)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
+                    const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step0, int n_steps,
+                    uint32_t* d_obs, uint32_t* d_legal, float* d_reward, uint8_t* d_step_type,
+                    int32_t* d_action, uint64_t* d_hist, void* stream) {
+  HB_REQUIRE(e && n_steps >= 1, "hb_env_selfplay: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_env_selfplay: reset the environment first"); return HB_ERR_STATE; }
+  RuleSet rs;
+  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  if (rc) return rc;
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (selfplay_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+                     e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
+                     d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+// Host-buffer step: what a binding with numpy arguments calls (copies inside).
+int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
+                     float* h_reward, uint8_t* h_step_type) {
+  HB_REQUIRE(e && h_action, "hb_env_step_host: bad arguments");
+  hb::DeviceGuard g(e->device);
+  const size_t n = (size_t)e->rt.n_games;
+  const size_t b_act = n * 4, b_obs = n * e->rt.obs_stride * 4, b_leg = n * e->legal_words * 4,
+               b_rew = n * 4, b_st = (n + 3) / 4 * 4;
+  int rc = env_stage(e, b_act + b_obs + b_leg + b_rew + b_st);
+  if (rc) return rc;
+  char* p = (char*)e->stage;
+  int32_t* d_act = (int32_t*)p; p += b_act;
+  uint32_t* d_obs = (uint32_t*)p; p += b_obs;
+  uint32_t* d_leg = (uint32_t*)p; p += b_leg;
+  float* d_rew = (float*)p; p += b_rew;
+  uint8_t* d_st = (uint8_t*)p;
+  HB_CUDA(cudaMemcpyAsync(d_act, h_action, b_act, cudaMemcpyHostToDevice, nullptr));
+  rc = hb_env_step(e, d_act, h_obs ? d_obs : nullptr, h_legal ? d_leg : nullptr,
+                   h_reward ? d_rew : nullptr, h_step_type ? d_st : nullptr, nullptr);
+  if (rc) return rc;
+  if (h_obs) HB_CUDA(cudaMemcpyAsync(h_obs, d_obs, b_obs, cudaMemcpyDeviceToHost, nullptr));
+  if (h_legal) HB_CUDA(cudaMemcpyAsync(h_legal, d_leg, b_leg, cudaMemcpyDeviceToHost, nullptr));
+  if (h_reward) HB_CUDA(cudaMemcpyAsync(h_reward, d_rew, b_rew, cudaMemcpyDeviceToHost, nullptr));
+  if (h_step_type) HB_CUDA(cudaMemcpyAsync(h_step_type, d_st, n, cudaMemcpyDeviceToHost, nullptr));
+  HB_CUDA(cudaStreamSynchronize(nullptr));
+  return HB_OK;
+}
+
+}  // extern "C"

@@ -86,7 +86,82 @@ int hb_st_total_host(hb_sumtree* t, float* h_out);
  * node value with the oracle. */
 int hb_st_heap_host(hb_sumtree* t, float* h_out);
 
-/* @@ENV@@ */
+/* ------------------------------------------------------------------------ */
+/* Batched Hanabi environment.  Replaces, for N games at once, what the       */
+/* reference obtains from the third-party HLE through environment.step /      */
+/* observation['vectorized'] / legal_moves_as_int                             */
+/* (hanabi_agents/rainbow/run_experiment.py:266-273,293,308) and consumes as   */
+/* observations[1] = (obs[N,L], legal[N,A])  (rlax_dqn/rlax_rainbow.py:278,285).*/
+/* Outputs are bit-packed: obs row = obs_stride 32-bit words (bit b -> word    */
+/* b>>5, bit b&31), legal row = legal_words words over move uids; reward f32;  */
+/* step_type u8 in dm_env coding 0 FIRST / 1 MID / 2 LAST (rlax_rainbow.py:     */
+/* 294,300,306).  A game whose last step was LAST is reset onto its next deck   */
+/* by the following step (action ignored, reward 0, FIRST).                     */
+/* ------------------------------------------------------------------------ */
+typedef struct hb_env hb_env;
+
+/* HanabiGame parameters (players, colors, ranks, hand_size, max_information_tokens,
+ * max_life_tokens) as HLE's make('Hanabi-Full', num_players) etc. resolve them. */
+int hb_env_create(int players, int colors, int ranks, int hand_size, int max_info, int max_life,
+                  int64_t n_games, int device, hb_env** out);
+int hb_env_destroy(hb_env* e);
+/* what: 0 obs_len(bits) 1 obs_stride(words) 2 num_moves 3 legal_words 4 deck_size
+ *       5 state_words 6 n_games 7 dump_len 8 players */
+int64_t hb_env_info(const hb_env* e, int what);
+/* This device holds games [game_id_base, game_id_base+n_games) of an n_total-game job
+ * (deck selection and the rule agents' random stream use the global game id). */
+int hb_env_set_shard(hb_env* e, int64_t game_id_base, int64_t n_total);
+/* Deck pool [n_decks, deck_size] of card indices color*ranks+rank: the order in which HLE's
+ * chance node (HanabiState::ApplyMove kDeal / deal_random_card) deals, as an explicit input.
+ * Game g, episode k plays deck (g + k*n_total) mod n_decks. */
+int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* stream);
+int hb_env_set_decks_host(hb_env* e, const uint8_t* h_decks, int64_t n_decks); /* validates */
+/* environment.reset(): every game dealt from its first deck (run_experiment.py:293) */
+int hb_env_reset(hb_env* e, uint32_t* d_obs, uint32_t* d_legal, uint8_t* d_step_type, void* stream);
+/* environment.step(action) for every game (run_experiment.py:308): HanabiState::ApplyMove,
+ * chance deal, reward = score delta, then observation + legal moves of the player to move.
+ * Any output pointer may be NULL. */
+int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d_legal,
+                float* d_reward, uint8_t* d_step_type, void* stream);
+/* HanabiObservation of player (current + offset) mod players, without stepping. */
+int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, void* stream);
+/* Number of illegal actions seen so far (HLE aborts on them; here the game is left as is). */
+int hb_env_illegal_count(hb_env* e, int64_t* out, void* stream);
+/* Canonical int32 state dump [n_games, dump_len] (tests compare it with the oracle's). */
+int hb_env_dump(hb_env* e, int32_t* d_out, void* stream);
+/* Bit-packed rows -> one int8 per bit, the layout the reference stores
+ * (rlax_dqn/experience_buffer.py:9-12): [n, obs_len] and [n, num_moves]. */
+int hb_env_unpack_obs(hb_env* e, const uint32_t* d_packed, int8_t* d_out, int64_t n, void* stream);
+int hb_env_unpack_legal(hb_env* e, const uint32_t* d_legal, int8_t* d_out, int64_t n, void* stream);
+/* Host-buffer step (copies inside, synchronises): the call a numpy binding makes. */
+int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
+                     float* h_reward, uint8_t* h_step_type);
+
+/* ------------------------------------------------------------------------ */
+/* Rule-based agents.  Replaces RulebasedAgent.explore/exploit/get_move        */
+/* (hanabi_agents/rule_based/rule_based.py:13-34) over the rules of             */
+/* hanabi_agents/rule_based/ruleset.py.  Rule ids:                              */
+/*  0 discard_oldest_first :206  1 osawa_discard :220  2 tell_unknown :285      */
+/*  3 tell_randomly :314  4 play_safe_card :350  5 play_if_certain :383         */
+/*  6 tell_playable_card_outer :413  7 tell_dispensable_factory(iarg) :454      */
+/*  8 tell_anyone_useful_card :518  9 play_probably_safe_factory(farg,iarg) :617*/
+/* 10 hail_mary :653  11 legal_random :598  12 discard_randomly :607            */
+/* 13 tell_most_information :539                                               */
+/* ------------------------------------------------------------------------ */
+/* d_action[g] = move uid of the first rule that fires (else legal_random); d_rule_hit[g] =
+ * its index in the list (n_rules = fallback, -1 = game awaiting reset); d_hist[n_rules+1]
+ * accumulates the agent's histogram (rule_based.py:9-10,19-23).  Rule arrays are HOST. */
+int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
+                 const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
+                 int32_t* d_action, int32_t* d_rule_hit, uint64_t* d_hist, void* stream);
+/* Fused self-play: n_steps x {rules act, env step, observe} in one launch with the game state
+ * in registers.  Outputs are [n_steps, n_games, ...]; any may be NULL. */
+int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
+                    const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step0,
+                    int n_steps, uint32_t* d_obs, uint32_t* d_legal, float* d_reward,
+                    uint8_t* d_step_type, int32_t* d_action, uint64_t* d_hist, void* stream);
+
+/* @@REPLAY@@ */
 
 #ifdef __cplusplus
 }

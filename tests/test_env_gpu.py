@@ -1,0 +1,185 @@
+"""GPU parity: CUDA env / encoder / legal masks / rule agents (through the C ABI) vs the CPU
+oracle on the same decks and actions -- bit-exact observations, masks, rewards, step types and
+full game state at every step."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+CONFIGS = [("Hanabi-Full", 2), ("Hanabi-Full", 3), ("Hanabi-Full", 4), ("Hanabi-Full", 5),
+           ("Hanabi-Small", 2), ("Hanabi-Very-Small", 2)]
+
+
+def _pair(name, players, n, n_decks, seed=5, threads=8):
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.game import game_params, make_decks
+    from oracle.hanabi import HanabiOracleEnv
+    p = game_params(name, players)
+    decks = make_decks(p["colors"], p["ranks"], n_decks, seed)
+    env = HanabiParallelEnv(n, name, players, decks=decks)
+    ora = HanabiOracleEnv(n, threads=threads, **p)
+    ora.set_decks(decks)
+    return env, ora
+
+
+def _check(env, ora, obs, legal, reward=None, step_type=None):
+    import torch
+    torch.cuda.synchronize()
+    np.testing.assert_array_equal(env.unpack_obs(obs).cpu().numpy().astype(np.uint8), ora.obs)
+    np.testing.assert_array_equal(env.unpack_legal(legal).cpu().numpy().astype(np.uint8), ora.legal)
+    if reward is not None:
+        np.testing.assert_array_equal(reward.cpu().numpy(), ora.reward)
+    np.testing.assert_array_equal(step_type.cpu().numpy(), ora.step_type)
+    np.testing.assert_array_equal(env.dump(), ora.dump())
+
+
+@pytest.mark.parametrize("name,players", CONFIGS)
+def test_shapes(name, players):
+    env, ora = _pair(name, players, 4, 8)
+    assert (env.obs_len, env.num_moves, env.deck_size) == (ora.obs_len, ora.num_moves, ora.deck_size)
+    assert env.obs_stride % 4 == 0 and env.obs_stride * 32 >= env.obs_len
+    assert env.observation_spec().shape == (4, ora.obs_len)
+    assert env.action_spec().num_values == ora.num_moves
+
+
+@pytest.mark.parametrize("name,players", CONFIGS)
+def test_random_play_parity(name, players):
+    n = 512
+    env, ora = _pair(name, players, n, 700)    # pool smaller than games*episodes: decks recycle
+    rng = np.random.default_rng(players)
+    obs, legal, st = env.reset()
+    ora.reset()
+    _check(env, ora, obs, legal, None, st)
+    for step in range(260):
+        lg = ora.legal
+        pick = rng.random((n, lg.shape[1])) * lg
+        a = pick.argmax(1).astype(np.int32)
+        obs, legal, rew, st = env.step(a)
+        ora.step(a)
+        assert ora.illegal == 0
+        _check(env, ora, obs, legal, rew, st)
+    assert env.illegal_count() == 0
+    assert ora.dump()[:, 7].max() >= 2          # several episodes were played per game
+    # other seats' views
+    for off in range(players):
+        o, l = env.observe(off)
+        oo, ol = ora.observe(off)
+        np.testing.assert_array_equal(env.unpack_obs(o).cpu().numpy().astype(np.uint8), oo)
+        np.testing.assert_array_equal(env.unpack_legal(l).cpu().numpy().astype(np.uint8), ol)
+
+
+def test_illegal_actions_are_counted_and_ignored():
+    env, ora = _pair("Hanabi-Full", 2, 64, 64)
+    env.reset(); ora.reset()
+    a = np.zeros(64, np.int32)                   # discard at 8 information tokens: illegal
+    a[::2] = 5                                   # play card 0: legal
+    a[1] = 99
+    a[3] = -1
+    obs, legal, rew, st = env.step(a)
+    ora.step(a)
+    _check(env, ora, obs, legal, rew, st)
+    assert env.illegal_count() == 32 == ora.illegal
+
+
+def test_step_host_matches_device_path():
+    env, ora = _pair("Hanabi-Full", 2, 256, 512)
+    env.reset(); ora.reset()
+    rng = np.random.default_rng(0)
+    for _ in range(40):
+        a = (rng.random(ora.legal.shape) * ora.legal).argmax(1).astype(np.int32)
+        obs, legal, rew, st = env.step_host(a)
+        ora.step(a)
+        bits = np.unpackbits(obs.view(np.uint8), axis=1, bitorder="little")[:, :env.obs_len]
+        np.testing.assert_array_equal(bits, ora.obs)
+        np.testing.assert_array_equal(rew, ora.reward)
+        np.testing.assert_array_equal(st, ora.step_type)
+
+
+def _rules(preset):
+    from hanabi_agents_b200.rule_based import RulebasedAgent, predefined_rules
+    from oracle.hanabi import PRESETS
+    return RulebasedAgent(getattr(predefined_rules, preset + "_rules"), seed=77), PRESETS[preset]
+
+
+@pytest.mark.parametrize("preset", ["piers", "iggi", "outer", "flawed"])
+@pytest.mark.parametrize("name,players", [("Hanabi-Full", 2), ("Hanabi-Full", 5), ("Hanabi-Full", 3)])
+def test_rule_agents_parity(preset, name, players):
+    n = 384
+    env, ora = _pair(name, players, n, 999)
+    agent, orules = _rules(preset)
+    for (rid, fa, ia), r in zip(orules, agent.rules):
+        assert (rid, float(fa), ia) == (r.rule_id, r.farg, r.iarg)
+    env.reset(); ora.reset()
+    hist = np.zeros(len(orules) + 1, np.int64)
+    for step in range(220):
+        a = agent.explore(env.observations())
+        oa, ohit = ora.rules_act(orules, 77, step)
+        np.testing.assert_array_equal(a.cpu().numpy(), oa)
+        np.add.at(hist, ohit[ohit >= 0], 1)
+        obs, legal, rew, st = env.step(a)
+        ora.step(oa)
+        _check(env, ora, obs, legal, rew, st)
+    assert agent.histogram == hist.tolist() and agent.totalCalls == hist.sum()
+    assert env.illegal_count() == 0
+
+
+def test_fused_selfplay_equals_stepwise():
+    n, T = 300, 150
+    env, ora = _pair("Hanabi-Full", 2, n, 1000)
+    agent, orules = _rules("piers")
+    env.reset(); ora.reset()
+    obs, legal, rew, st, act = env.selfplay(agent, T, obs="alloc", legal="alloc", reward="alloc",
+                                            step_type="alloc", action="alloc")
+    for t in range(T):
+        oa, _ = ora.rules_act(orules, 77, t)
+        ora.step(oa)
+        np.testing.assert_array_equal(act[t].cpu().numpy(), oa)
+        np.testing.assert_array_equal(env.unpack_obs(obs[t]).cpu().numpy().astype(np.uint8), ora.obs)
+        np.testing.assert_array_equal(env.unpack_legal(legal[t]).cpu().numpy().astype(np.uint8), ora.legal)
+        np.testing.assert_array_equal(rew[t].cpu().numpy(), ora.reward)
+        np.testing.assert_array_equal(st[t].cpu().numpy(), ora.step_type)
+    np.testing.assert_array_equal(env.dump(), ora.dump())
+
+
+def test_sharded_envs_equal_one_env():
+    """Two shards (game_id_base) reproduce the games of one big env: no data-path collective."""
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.game import make_decks
+    n = 256
+    decks = make_decks(5, 5, 600, 3)
+    whole = HanabiParallelEnv(n, decks=decks)
+    parts = [HanabiParallelEnv(n // 2, decks=decks, game_id_base=b, n_total=n) for b in (0, n // 2)]
+    agent, _ = _rules("piers")
+    agents = [_rules("piers")[0] for _ in parts]
+    whole.reset()
+    for p in parts:
+        p.reset()
+    for _ in range(120):
+        whole.step(agent.explore(whole))
+        for p, ag in zip(parts, agents):
+            p.step(ag.explore(p))
+    np.testing.assert_array_equal(whole.dump(), np.concatenate([p.dump() for p in parts]))
+    import torch
+    np.testing.assert_array_equal(whole.obs_packed.cpu().numpy(),
+                                  torch.cat([p.obs_packed for p in parts]).cpu().numpy())
+
+
+def test_full_size_cfg2_properties_and_oracle():
+    """BASELINE cfg 2 size: 65,536 Hanabi-Full 2p games, rule-based self-play."""
+    n, T = 65536, 100
+    env, ora = _pair("Hanabi-Full", 2, n, 4 * 65536, threads=32)
+    agent, orules = _rules("piers")
+    env.reset(); ora.reset()
+    env.selfplay(agent, T)                         # no outputs kept: state only
+    for t in range(T):
+        oa, _ = ora.rules_act(orules, 77, t)
+        ora.step(oa)
+    d = env.dump()
+    np.testing.assert_array_equal(d, ora.dump())
+    # size-independent invariants (A.6): card conservation, token ranges
+    C, P, H = 5, 2, 5
+    hand_n = d[:, 8 + C:8 + C + P].sum(1)
+    disc = d[:, 8 + C + P + 5 * P * H:8 + C + P + 5 * P * H + 25].sum(1)
+    assert np.all(d[:, 3] + hand_n + disc + d[:, 8:8 + C].sum(1) == 50)
+    assert np.all((d[:, 1] >= 0) & (d[:, 1] <= 8)) and np.all((d[:, 2] >= 0) & (d[:, 2] <= 3))
+    assert env.illegal_count() == 0

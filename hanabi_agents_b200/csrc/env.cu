@@ -12,7 +12,7 @@ using namespace hbg;
 struct hb_env {
   int device = 0;
   int P = 0, H = 0, C = 0, R = 0, shape = -1;
-  int deck_size = 0, num_moves = 0, legal_words = 0, state_words = 0;
+  int deck_size = 0, num_moves = 0, legal_words = 0, state_words = 0, obs_len = 0, obs_stride = 0;
   Rt rt{};
   uint32_t* state = nullptr;
   uint8_t* decks = nullptr;
@@ -28,13 +28,10 @@ namespace {
 constexpr int kWarpsPerCta = 8;
 
 template <class SH>
-__device__ __forceinline__ void emit(const Game<SH>& g, const Rt& rt, long long game, uint32_t* buf,
+__device__ __forceinline__ void emit(const Game<SH>& g, const Rt& rt, long long game,
                                      uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
                                      uint8_t* __restrict__ step_type) {
-  if (obs != nullptr) {
-    encode_obs(g, rt, g.cur, buf);
-    store_obs(rt, buf, obs, game);
-  }
+  if (obs != nullptr) encode_obs(g, g.cur, obs + game * SH::kObsStride);
   if (legal != nullptr) {
     const unsigned long long m = legal_mask(g, rt, g.cur);
     if (lane_id() < SH::kLegalWords)
@@ -48,14 +45,13 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
 env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
                  uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
                  uint8_t* __restrict__ step_type) {
-  extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
   const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
   if (game >= rt.n_games) return;
   Game<SH> g;
   g.episode = 0;
   reset_game(g, rt, deck_of<SH>(rt, decks, game, 0));
-  emit(g, rt, game, smem + warp * rt.obs_stride, obs, legal, step_type);
+  emit(g, rt, game, obs, legal, step_type);
   store_game(g, state, game);
 }
 
@@ -64,19 +60,20 @@ env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict_
 // FIRST) -- otherwise rl_env.step: apply, deal, reward = score delta.
 template <class SH>
 __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
-                                           long long game, int action, unsigned long long* illegal) {
+                                           const uint8_t*& deck, long long game, int action,
+                                           unsigned long long* illegal) {
   if (g.step_type == LAST) {
     ++g.episode;
-    reset_game(g, rt, deck_of<SH>(rt, decks, game, g.episode));
+    deck = deck_of<SH>(rt, decks, game, g.episode);
+    reset_game(g, rt, deck);
     return 0.0f;
   }
-  const unsigned long long lm = legal_mask(g, rt, g.cur);
-  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {
+  if (!move_is_legal(g, action)) {
     if (lane_id() == 0) atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and skip
     return 0.0f;
   }
-  const int r = apply_move(g, rt, action, deck_of<SH>(rt, decks, game, g.episode));
-  g.step_type = g.terminal(rt) ? LAST : MID;
+  const int r = apply_move(g, rt, action, deck);
+  g.step_type = g.terminal() ? LAST : MID;
   return (float)r;
 }
 
@@ -86,15 +83,15 @@ env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 const int32_t* __restrict__ action, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, unsigned long long* illegal) {
-  extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
   const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
-  const float r = step_game(g, rt, decks, game, action[game], illegal);
+  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
+  const float r = step_game(g, rt, decks, deck, game, action[game], illegal);
   if (reward != nullptr && lane_id() == 0) reward[game] = r;
-  emit(g, rt, game, smem + warp * rt.obs_stride, obs, legal, step_type);
+  emit(g, rt, game, obs, legal, step_type);
   store_game(g, state, game);
 }
 
@@ -102,7 +99,6 @@ template <class SH>
 __global__ void __launch_bounds__(kWarpsPerCta * 32)
 env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
                    uint32_t* __restrict__ obs, uint32_t* __restrict__ legal) {
-  extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
   const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
   if (game >= rt.n_games) return;
@@ -110,11 +106,7 @@ env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
   load_game(g, state, game);
   int q = g.cur + offset;
   if (q >= SH::P) q -= SH::P;
-  uint32_t* buf = smem + warp * rt.obs_stride;
-  if (obs != nullptr) {
-    encode_obs(g, rt, q, buf);
-    store_obs(rt, buf, obs, game);
-  }
+  if (obs != nullptr) encode_obs(g, q, obs + game * SH::kObsStride);
   if (legal != nullptr) {   // HanabiState::LegalMoves: empty unless it is that player's turn
     const unsigned long long m = offset == 0 ? legal_mask(g, rt, q) : 0ull;
     if (lane_id() < SH::kLegalWords)
@@ -152,25 +144,24 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
-  extern __shared__ uint32_t smem[];
   const int warp = threadIdx.x >> 5;
   const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
-  uint32_t* buf = smem + warp * rt.obs_stride;
+  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
   for (int t = 0; t < n_steps; ++t) {
     int a = 0, hit = -1;
     if (g.step_type != LAST)
       a = rules_act(g, rt, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
-    const float r = step_game(g, rt, decks, game, a, illegal);
+    const float r = step_game(g, rt, decks, deck, game, a, illegal);
     const long long row = (long long)t * rt.n_games + game;
     if (lane_id() == 0) {
       if (action != nullptr) action[row] = a;
       if (reward != nullptr) reward[row] = r;
       if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
     }
-    emit(g, rt, row, buf, obs, legal, step_type);
+    emit(g, rt, row, obs, legal, step_type);
   }
   store_game(g, state, game);
 }
@@ -252,17 +243,17 @@ namespace {
 
 // The kernels are instantiated for the game shapes the reference's environments produce
 // (Hanabi-Full 2..5 players, Hanabi-Small, Hanabi-Very-Small; run_experiment.py:115-128).
-#define HB_SHAPES(X)            \
-  X(0, 2, 5, 5, 5)              \
-  X(1, 3, 5, 5, 5)              \
-  X(2, 4, 4, 5, 5)              \
-  X(3, 5, 4, 5, 5)              \
-  X(4, 2, 2, 2, 5)              \
-  X(5, 2, 2, 1, 5)
+#define HB_SHAPES(X)                  \
+  X(0, 2, 5, 5, 5, 8, 3)              \
+  X(1, 3, 5, 5, 5, 8, 3)              \
+  X(2, 4, 4, 5, 5, 8, 3)              \
+  X(3, 5, 4, 5, 5, 8, 3)              \
+  X(4, 2, 2, 2, 5, 3, 1)              \
+  X(5, 2, 2, 1, 5, 3, 1)
 
-int find_shape(int P, int H, int C, int R) {
-#define X(id, p, h, c, r) \
-  if (P == p && H == h && C == c && R == r) return id;
+int find_shape(int P, int H, int C, int R, int MI, int ML) {
+#define X(id, p, h, c, r, mi, ml) \
+  if (P == p && H == h && C == c && R == r && MI == mi && ML == ml) return id;
   HB_SHAPES(X)
 #undef X
   return -1;
@@ -270,19 +261,19 @@ int find_shape(int P, int H, int C, int R) {
 
 #define HB_DISPATCH(env, CALL)                                                   \
   switch ((env)->shape) {                                                        \
-    case 0: { using SH = Shape<2, 5, 5, 5>; CALL; break; }                       \
-    case 1: { using SH = Shape<3, 5, 5, 5>; CALL; break; }                       \
-    case 2: { using SH = Shape<4, 4, 5, 5>; CALL; break; }                       \
-    case 3: { using SH = Shape<5, 4, 5, 5>; CALL; break; }                       \
-    case 4: { using SH = Shape<2, 2, 2, 5>; CALL; break; }                       \
-    case 5: { using SH = Shape<2, 2, 1, 5>; CALL; break; }                       \
+    case 0: { using SH = Shape<2, 5, 5, 5, 8, 3>; CALL; break; }                       \
+    case 1: { using SH = Shape<3, 5, 5, 5, 8, 3>; CALL; break; }                       \
+    case 2: { using SH = Shape<4, 4, 5, 5, 8, 3>; CALL; break; }                       \
+    case 3: { using SH = Shape<5, 4, 5, 5, 8, 3>; CALL; break; }                       \
+    case 4: { using SH = Shape<2, 2, 2, 5, 3, 1>; CALL; break; }                       \
+    case 5: { using SH = Shape<2, 2, 1, 5, 3, 1>; CALL; break; }                       \
     default: hb::set_error("unsupported game shape"); return HB_ERR_INVALID;     \
   }
 
 inline unsigned grid_for(const hb_env* e) {
   return (unsigned)((e->rt.n_games + kWarpsPerCta - 1) / kWarpsPerCta);
 }
-inline size_t smem_for(const hb_env* e) { return (size_t)kWarpsPerCta * e->rt.obs_stride * 4; }
+inline size_t smem_for(const hb_env*) { return 0; }
 
 int env_stage(hb_env* e, size_t bytes) {
   if (e->stage_bytes >= bytes) return HB_OK;
@@ -317,11 +308,11 @@ int hb_env_create(int players, int colors, int ranks, int hand_size, int max_inf
                   int64_t n_games, int device, hb_env** out) {
   HB_REQUIRE(out != nullptr, "hb_env_create: out is NULL");
   HB_REQUIRE(n_games >= 1, "hb_env_create: n_games must be >= 1");
-  const int shape = find_shape(players, hand_size, colors, ranks);
-  HB_REQUIRE(shape >= 0, "hb_env_create: unsupported game shape players=%d hand=%d colors=%d ranks=%d",
-             players, hand_size, colors, ranks);
-  HB_REQUIRE(max_info >= 0 && max_info <= 8 && max_life >= 1 && max_life <= 3,
-             "hb_env_create: max_info must be 0..8 and max_life 1..3");
+  const int shape = find_shape(players, hand_size, colors, ranks, max_info, max_life);
+  HB_REQUIRE(shape >= 0,
+             "hb_env_create: unsupported game players=%d hand=%d colors=%d ranks=%d info=%d life=%d "
+             "(kernels exist for Hanabi-Full 2-5p, Hanabi-Small and Hanabi-Very-Small)",
+             players, hand_size, colors, ranks, max_info, max_life);
   hb::DeviceGuard g(device);
   if (!g.ok) { hb::set_error("hb_env_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
   hb_env* e = new (std::nothrow) hb_env();
@@ -336,18 +327,12 @@ int hb_env_create(int players, int colors, int ranks, int hand_size, int max_inf
   e->legal_words = (e->num_moves + 31) / 32;
   e->state_words = (players * hand_size + 6 <= 16) ? 16 : 32;
   Rt& rt = e->rt;
-  rt.max_info = max_info; rt.max_life = max_life;
   const int hands_len = (players - 1) * hand_size * bpc + players;
-  rt.deck_thermo = e->deck_size - players * hand_size;
-  const int board_len = rt.deck_thermo + bpc + max_info + max_life;
+  const int board_len = (e->deck_size - players * hand_size) + bpc + max_info + max_life;
   const int last_len = players + 4 + players + colors + ranks + 2 * hand_size + bpc + 2;
   const int know_len = players * hand_size * (bpc + colors + ranks);
-  rt.off_board = hands_len;
-  rt.off_disc = rt.off_board + board_len;
-  rt.off_last = rt.off_disc + e->deck_size;
-  rt.off_know = rt.off_last + last_len;
-  rt.obs_len = rt.off_know + know_len;
-  rt.obs_stride = (((rt.obs_len + 31) / 32) + 3) / 4 * 4;
+  e->obs_len = hands_len + board_len + e->deck_size + last_len + know_len;
+  e->obs_stride = (((e->obs_len + 31) / 32) + 3) / 4 * 4;
   rt.n_games = n_games; rt.n_total = n_games; rt.game_id_base = 0; rt.n_decks = 0;
   cudaError_t err = cudaMalloc(&e->state, (size_t)n_games * e->state_words * 4);
   if (err == cudaSuccess) err = cudaMemset(e->state, 0, (size_t)n_games * e->state_words * 4);
@@ -377,8 +362,8 @@ int hb_env_destroy(hb_env* e) {
 int64_t hb_env_info(const hb_env* e, int what) {
   if (!e) return -1;
   switch (what) {
-    case 0: return e->rt.obs_len;
-    case 1: return e->rt.obs_stride;
+    case 0: return e->obs_len;
+    case 1: return e->obs_stride;
     case 2: return e->num_moves;
     case 3: return e->legal_words;
     case 4: return e->deck_size;
@@ -491,10 +476,10 @@ int hb_env_unpack_obs(hb_env* e, const uint32_t* d_packed, int8_t* d_out, int64_
   HB_REQUIRE(e && d_packed && d_out && n >= 0, "hb_env_unpack_obs: bad arguments");
   if (n == 0) return HB_OK;
   hb::DeviceGuard g(e->device);
-  const long long total = n * e->rt.obs_len;
+  const long long total = n * e->obs_len;
   const unsigned blocks = (unsigned)min((long long)148 * 16, (total + 255) / 256);
-  unpack_bits_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_packed, e->rt.obs_stride,
-                                                               e->rt.obs_len, d_out, n);
+  unpack_bits_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(d_packed, e->obs_stride,
+                                                               e->obs_len, d_out, n);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -550,7 +535,7 @@ int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32
   HB_REQUIRE(e && h_action, "hb_env_step_host: bad arguments");
   hb::DeviceGuard g(e->device);
   const size_t n = (size_t)e->rt.n_games;
-  const size_t b_act = n * 4, b_obs = n * e->rt.obs_stride * 4, b_leg = n * e->legal_words * 4,
+  const size_t b_act = n * 4, b_obs = n * e->obs_stride * 4, b_leg = n * e->legal_words * 4,
                b_rew = n * 4, b_st = (n + 3) / 4 * 4;
   int rc = env_stage(e, b_act + b_obs + b_leg + b_rew + b_st);
   if (rc) return rc;

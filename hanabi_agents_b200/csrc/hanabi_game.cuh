@@ -30,9 +30,11 @@ constexpr unsigned kFull = 0xffffffffu;
 enum { FIRST = 0, MID = 1, LAST = 2 };
 enum { PLAY = 1, DISCARD = 2, REVEAL_COLOR = 3, REVEAL_RANK = 4 };
 
-template <int P_, int H_, int C_, int R_>
+template <int P_, int H_, int C_, int R_, int MI_, int ML_>
 struct Shape {
+  static_assert(R_ == 5, "rank-dependent bit tricks assume 5 ranks (3/2/2/2/1 instances)");
   static constexpr int P = P_, H = H_, C = C_, R = R_;
+  static constexpr int MAX_INFO = MI_, MAX_LIFE = ML_;
   static constexpr int S = P * H;                 // card slots
   static constexpr int BPC = C * R;               // bits per card
   static constexpr int kPerColor = (R == 1) ? 3 : (3 + 2 * (R - 2) + 1);
@@ -40,6 +42,20 @@ struct Shape {
   static constexpr int A = 2 * H + (P - 1) * (C + R);       // num moves
   static constexpr int kStateWords = (S + 6 <= 16) ? 16 : 32;
   static constexpr int kLegalWords = (A + 31) / 32;
+  // canonical observation layout, all in bits
+  static constexpr int kHandsCards = (P - 1) * H * BPC;      // other players' cards
+  static constexpr int kOffBoard = kHandsCards + P;           // after the "short hand" bits
+  static constexpr int kDeckThermo = DECK - P * H;
+  static constexpr int kOffFireworks = kOffBoard + kDeckThermo;
+  static constexpr int kOffInfo = kOffFireworks + BPC;
+  static constexpr int kOffDisc = kOffInfo + MAX_INFO + MAX_LIFE;
+  static constexpr int kOffLast = kOffDisc + DECK;
+  static constexpr int kLastLen = 2 * P + 4 + C + R + 2 * H + BPC + 2;
+  static constexpr int kOffKnow = kOffLast + kLastLen;
+  static constexpr int kKnowWidth = BPC + C + R;
+  static constexpr int kObsLen = kOffKnow + P * H * kKnowWidth;
+  static constexpr int kObsWords = (kObsLen + 31) / 32;
+  static constexpr int kObsStride = (kObsWords + 3) / 4 * 4;  // row = multiple of 16 B
   __host__ __device__ static constexpr int instances(int r) {
     return r == 0 ? 3 : (r == R - 1 ? 1 : 2);
   }
@@ -53,10 +69,6 @@ struct Shape {
 
 // runtime part of the configuration (kernel argument, by value)
 struct Rt {
-  int max_info, max_life;
-  int obs_len, obs_stride;          // bits, words per row (multiple of 4)
-  int off_board, off_disc, off_last, off_know;
-  int deck_thermo;                  // DECK - P*H
   long long n_games;                // games on this device
   long long n_total;                // games in the whole job (deck selection)
   long long game_id_base;           // global id of local game 0
@@ -85,8 +97,7 @@ struct Game {
     for (int c = 0; c < SH::C; ++c) s += firework(c);
     return s;
   }
-  __device__ __forceinline__ bool terminal(const Rt& rt) const {
-    (void)rt;
+  __device__ __forceinline__ bool terminal() const {
     return life < 1 || score() >= SH::C * SH::R || ttp <= 0;
   }
 };
@@ -161,8 +172,8 @@ __device__ __forceinline__ void reset_game(Game<SH>& g, const Rt& rt, const uint
   const int lane = lane_id();
   g.slot = lane < SH::S ? fresh_slot<SH>(deck[lane]) : 0u;
   g.fw = 0;
-  g.info = rt.max_info;
-  g.life = rt.max_life;
+  g.info = SH::MAX_INFO;
+  g.life = SH::MAX_LIFE;
   g.cur = 0;
   g.ttp = SH::P;
   g.step_type = FIRST;
@@ -181,7 +192,7 @@ __device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g, cons
   const int lane = lane_id();
   const unsigned long long hand_bits = (1ull << g.hand_n(q)) - 1;
   unsigned long long m = hand_bits << SH::H;                 // Play(i), i < hand size
-  if (g.info < rt.max_info) m |= hand_bits;                  // Discard(i)
+  if (g.info < SH::MAX_INFO) m |= hand_bits;                  // Discard(i)
   uint32_t lo = 0, hi = 0;
   if (g.info > 0 && lane < SH::S && slot_valid(g.slot)) {
     const int p = lane / SH::H;
@@ -202,6 +213,31 @@ __device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g, cons
   return m | (unsigned long long)lo | ((unsigned long long)hi << 32);
 }
 
+// MoveIsLegal for ONE move uid of the player to move (cheaper than the full mask).
+template <class SH>
+__device__ __forceinline__ bool move_is_legal(const Game<SH>& g, int uid) {
+  if (uid < 0 || uid >= SH::A) return false;
+  const int me = g.cur;
+  if (uid < SH::H) return g.info < SH::MAX_INFO && uid < g.hand_n(me);
+  if (uid < 2 * SH::H) return uid - SH::H < g.hand_n(me);
+  if (g.info <= 0) return false;
+  int u = uid - 2 * SH::H;
+  const bool by_color = u < (SH::P - 1) * SH::C;
+  if (!by_color) u -= (SH::P - 1) * SH::C;
+  const int span = by_color ? SH::C : SH::R;
+  const int k = 1 + u / span, v = u - (k - 1) * span;
+  int t = me + k;
+  if (t >= SH::P) t -= SH::P;
+  const int lane = lane_id();
+  bool match = false;
+  if (lane < SH::S && slot_valid(g.slot) && lane / SH::H == t) {
+    const int card = slot_card(g.slot);
+    const int c = card / SH::R, r = card - c * SH::R;
+    match = by_color ? (c == v) : (r == v);
+  }
+  return __any_sync(kFull, match);
+}
+
 // ---- transition (A.3): ApplyMove + chance deal + AdvanceToNextPlayer -------------------
 // `uid` must be legal.  Returns the reward (score delta).
 template <class SH>
@@ -219,12 +255,12 @@ __device__ __forceinline__ int apply_move(Game<SH>& g, const Rt& rt, int uid, co
     last |= ((uint32_t)c << 10) | ((uint32_t)r << 13);
     bool to_discard = true;
     if (!is_play) {
-      if (g.info < rt.max_info) { ++g.info; last |= 1u << 17; }
+      if (g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 17; }
     } else if (r == g.firework(c)) {             // AddToFireworks
       g.fw += 1u << (3 * c);
       last |= 1u << 16;
       to_discard = false;
-      if (g.firework(c) == SH::R && g.info < rt.max_info) { ++g.info; last |= 1u << 17; }
+      if (g.firework(c) == SH::R && g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 17; }
     } else {
       --g.life;
     }

@@ -45,7 +45,9 @@ __device__ __forceinline__ int rand_below(uint32_t r, int n) {
   return (int)(((unsigned long long)r * (unsigned long long)n) >> 32);
 }
 
-// Per-lane view of the observer (= player to move).
+// Per-lane view of the observer (= player to move) plus the warp-uniform quantities several
+// rules share.  2-bit-per-card-type packing ("spread" form, type t at bit 2t) lets the
+// playability sums run as popcounts.
 template <class SH>
 struct View {
   bool valid;       // this lane holds a card
@@ -54,7 +56,15 @@ struct View {
   int cp, rp;       // plausible colour / rank masks
   bool ch, rh;      // colour / rank explicitly hinted
   uint32_t key;     // order of iteration: (k, i)
+  unsigned long long grid_s;   // plausible(colour) x plausible(rank), spread form
+  unsigned long long pg_s;     // uniform: cards playable right now, spread form
+  int minfw;                   // uniform: min(fireworks)
 };
+
+// 5-bit mask -> bits at 0,2,4,6,8
+__device__ __forceinline__ uint32_t spread5(uint32_t x) {
+  return (x & 1u) | ((x & 2u) << 1) | ((x & 4u) << 2) | ((x & 8u) << 3) | ((x & 16u) << 4);
+}
 
 template <class SH>
 __device__ __forceinline__ View<SH> make_view(const Game<SH>& g) {
@@ -73,6 +83,17 @@ __device__ __forceinline__ View<SH> make_view(const Game<SH>& g) {
   v.ch = slot_chint(g.slot);
   v.rh = slot_rhint(g.slot);
   v.key = (uint32_t)(v.k * SH::H + v.i);
+  const unsigned long long rs = spread5((uint32_t)v.rp);
+  v.grid_s = 0;
+  v.pg_s = 0;
+  v.minfw = g.firework(0);
+#pragma unroll
+  for (int c = 0; c < SH::C; ++c) {
+    if ((v.cp >> c) & 1) v.grid_s |= rs << (10 * c);
+    const int f = g.firework(c);
+    if (f < SH::R) v.pg_s |= 1ull << (10 * c + 2 * f);
+    v.minfw = min(v.minfw, f);
+  }
   return v;
 }
 
@@ -93,90 +114,72 @@ template <class SH> __device__ __forceinline__ int uid_rank(int k, int r) {
   return 2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R + r;
 }
 
+// 2-bit fields holding num_in_deck_by_rank = [3,2,2,2,1]  (ruleset.py:9)
 template <class SH>
-__device__ __forceinline__ int min_firework(const Game<SH>& g) {
-  int m = g.firework(0);
-#pragma unroll
-  for (int c = 1; c < SH::C; ++c) m = min(m, g.firework(c));
-  return m;
+__device__ __forceinline__ constexpr unsigned long long in_deck_packed() {
+  unsigned long long k = 0;
+  for (int c = 0; c < SH::C; ++c)
+    k |= (3ull | (2ull << 2) | (2ull << 4) | (2ull << 6) | (1ull << 8)) << (10 * c);
+  return k;
 }
 
-// get_max_fireworks  ruleset.py:174-193 ; 3 bits per colour
+// get_max_fireworks  ruleset.py:174-193: 5, or the lowest rank whose every copy is discarded.
+// 3 bits per colour.
 template <class SH>
 __device__ __forceinline__ uint32_t max_fireworks(const Game<SH>& g) {
+  const unsigned long long x = g.disc ^ in_deck_packed<SH>();
+  const unsigned long long gone = ~(x | (x >> 1)) & 0x5555555555555555ull;   // count == in deck
   uint32_t out = 0;
 #pragma unroll
   for (int c = 0; c < SH::C; ++c) {
-    int m = 5;
-#pragma unroll
-    for (int r = 0; r < SH::R; ++r) {
-      const int n = g.disc_n(c * SH::R + r);
-      const int in_deck = r == 0 ? 3 : (r == 4 ? 1 : 2);   // num_in_deck_by_rank  ruleset.py:9
-      if (n > 0 && n >= in_deck && m >= r) m = r;
-    }
+    const uint32_t bits = (uint32_t)(gone >> (10 * c)) & 0x155u;
+    const int m = bits ? (__ffs(bits) - 1) >> 1 : 5;
     out |= (uint32_t)m << (3 * c);
   }
   return out;
 }
 
-// plausible(colour) x plausible(rank) grid of this lane's card, bit c*R+r
-template <class SH>
-__device__ __forceinline__ uint32_t plausible_grid(const View<SH>& v) {
-  uint32_t grid = 0;
-#pragma unroll
-  for (int c = 0; c < SH::C; ++c)
-    if ((v.cp >> c) & 1) grid |= (uint32_t)v.rp << (c * SH::R);
-  return grid;
+// sum of the 2-bit fields of x selected by sel (sel has bits at even positions)
+__device__ __forceinline__ int sum_fields(unsigned long long x, unsigned long long sel) {
+  return __popcll(x & sel) + 2 * __popcll((x >> 1) & sel);
 }
 
-// cards playable right now, bit c*R + fireworks[c]
-template <class SH>
-__device__ __forceinline__ uint32_t playable_grid(const Game<SH>& g) {
-  uint32_t pg = 0;
-#pragma unroll
-  for (int c = 0; c < SH::C; ++c)
-    if (g.firework(c) < SH::R) pg |= 1u << (c * SH::R + g.firework(c));
-  return pg;
-}
-
-// play_probably_safe_factory  ruleset.py:617-635 with get_card_playability :82-125
+// play_probably_safe_factory  ruleset.py:617-635 with get_card_playability :82-125.
+// playability = playable copies / plausible copies among the cards not visible to me; the
+// first-maximum (np.argmax) is taken by exact cross-multiplication, the threshold test is the
+// reference's float64 division.
 template <class SH>
 __device__ __forceinline__ int play_probably_safe(const Game<SH>& g, const View<SH>& v,
                                                   double threshold, bool require_extra_lives) {
   const int n = g.hand_n(g.cur);
   if (n == 0) return -1;
-  // visible copies per card type (2-bit fields): other hands + discards + fireworks  :60-76
+  // visible copies per card type: other hands + discards + fireworks  (:60-76)
   unsigned long long vis = (v.valid && v.k >= 1) ? (1ull << (2 * (v.c * SH::R + v.r))) : 0ull;
 #pragma unroll
   for (int o = 16; o >= 1; o >>= 1) vis += __shfl_xor_sync(kFull, vis, o);
   vis += g.disc;
 #pragma unroll
-  for (int c = 0; c < SH::C; ++c)
-    for (int r = 0; r < g.firework(c); ++r) vis += 1ull << (2 * (c * SH::R + r));
-  const uint32_t grid = plausible_grid(v), pg = playable_grid(g);
-  int total = 0, playable = 0;
+  for (int c = 0; c < SH::C; ++c)   // ranks below the stack height: one visible copy each
+    vis += (0x155ull & ((1ull << (2 * g.firework(c))) - 1)) << (10 * c);
+  unsigned long long inst = 0;
 #pragma unroll
-  for (int t = 0; t < SH::BPC; ++t) {
-    const int r = t % SH::R;
-    const int left = SH::instances(r) - (int)((vis >> (2 * t)) & 3ull);
-    if ((grid >> t) & 1) {
-      total += left;
-      if ((pg >> t) & 1) playable += left;
-    }
-  }
-  const double mine = (v.valid && v.k == 0) ? (double)playable / (double)total : -1.0;  // :105
-  // np.argmax: first maximum over my cards
+  for (int c = 0; c < SH::C; ++c)
+    inst |= (3ull | (2ull << 2) | (2ull << 4) | (2ull << 6) | (1ull << 8)) << (10 * c);
+  const unsigned long long left = inst - vis;            // no borrows: visible <= instances
+  const int total = sum_fields(left, v.grid_s);
+  const int playable = sum_fields(left, v.grid_s & v.pg_s);
+  const uint32_t mine = (uint32_t)playable | ((uint32_t)total << 8);
   int best = 0;
-  double best_p = __shfl_sync(kFull, mine, g.cur * SH::H);
+  uint32_t bp = __shfl_sync(kFull, mine, g.cur * SH::H);
   for (int i = 1; i < n; ++i) {
-    const double p = __shfl_sync(kFull, mine, g.cur * SH::H + i);
-    if (p > best_p) { best_p = p; best = i; }
+    const uint32_t x = __shfl_sync(kFull, mine, g.cur * SH::H + i);
+    // p_i/t_i > p_b/t_b  <=>  p_i*t_b > p_b*t_i   (t > 0)
+    if ((x & 255u) * (bp >> 8) > (bp & 255u) * (x >> 8)) { bp = x; best = i; }
   }
   if (!require_extra_lives || g.life > 1)
-    if (best_p >= threshold) return uid_play<SH>(best);
+    if ((double)(bp & 255u) / (double)(bp >> 8) >= threshold) return uid_play<SH>(best);   // :105,622
   return -1;
 }
-
 template <class SH>
 __device__ __forceinline__ int run_rule(const Game<SH>& g, const Rt& rt, const View<SH>& v, int rule,
                                         double farg, int iarg, unsigned long long seed,
@@ -191,7 +194,7 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, const Rt& rt, const V
     case R_OSAWA_DISCARD: {                            // :220-280
       if (g.info == 8) return -1;
       const uint32_t mf = max_fireworks(g);
-      const int minfw = min_firework(g);
+      const int minfw = v.minfw;
       const int hc = __ffs(v.cp) - 1, hr = __ffs(v.rp) - 1;   // hinted value = the single bit
       const int cidx = v.ch ? hc : C - 1;                     // fireworks[-1] quirk  :229-230
       bool a = g.firework(cidx) == 5;
@@ -232,7 +235,7 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, const Rt& rt, const V
     }
 
     case R_PLAY_SAFE_CARD: {                           // :350-380
-      const bool safe = (plausible_grid(v) & ~playable_grid(g)) == 0;
+      const bool safe = (v.grid_s & ~v.pg_s) == 0;
       const int l = first_lane(v, mine && safe);
       return l >= 0 ? uid_play<SH>(l - g.cur * H) : -1;
     }
@@ -256,7 +259,7 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, const Rt& rt, const V
 
     case R_TELL_DISPENSABLE: {                         // :454-514, iarg = min_information_tokens
       if (!(g.info < iarg) || g.info <= 0) return -1;
-      const int minfw = min_firework(g);
+      const int minfw = v.minfw;
       const int f = g.firework(v.c);
       int mv = -1;
       if (!v.ch && f == 5) mv = uid_color<SH>(v.k, v.c);
@@ -302,12 +305,15 @@ __device__ __forceinline__ int rules_act(const Game<SH>& g, const Rt& rt, const 
                                          unsigned long long game_id, unsigned long long step,
                                          int* hit) {
   const View<SH> v = make_view(g);
-  for (int k = 0; k < rs.n; ++k) {
-    const int a = run_rule(g, rt, v, rs.id[k], rs.farg[k], rs.iarg[k], rs.seed, game_id, step);
-    if (a >= 0) { *hit = k; return a; }
+  int a = -1, k = 0;
+#pragma unroll 1
+  for (; k <= rs.n; ++k) {   // k == rs.n: Ruleset.legal_random fallback (rule_based.py:24)
+    const bool fb = k == rs.n;
+    a = run_rule(g, rt, v, fb ? (int)R_LEGAL_RANDOM : rs.id[fb ? 0 : k], fb ? 0.0 : rs.farg[fb ? 0 : k],
+                 fb ? 0 : rs.iarg[fb ? 0 : k], rs.seed, game_id, step);
+    if (a >= 0 || fb) break;
   }
-  *hit = rs.n;
-  const int a = run_rule(g, rt, v, R_LEGAL_RANDOM, 0.0, 0, rs.seed, game_id, step);
+  *hit = k;
   return a < 0 ? 0 : a;
 }
 

@@ -1,6 +1,6 @@
 // Batched Hanabi environment + rule-based policy kernels and their C ABI.
 // Device code: hanabi_game.cuh (state, legality, transition), hanabi_encode.cuh (canonical
-// observation), hanabi_rules.cuh (rule-based agents).  One warp per game, 8 games per CTA.
+// observation), hanabi_rules.cuh (rule-based agents).  One thread per game, 64 games per CTA.
 #include "common.cuh"
 #include "hanabi_encode.cuh"
 #include "hanabi_rules.cuh"
@@ -25,33 +25,35 @@ struct hb_env {
 
 namespace {
 
-constexpr int kWarpsPerCta = 8;
+constexpr int kThreads = 64;   // games per CTA: 65,536 games -> 1024 CTAs = 6.9 per SM (148 SMs)
 
-template <class SH>
-__device__ __forceinline__ void emit(const Game<SH>& g, const Rt& rt, long long game,
-                                     uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
-                                     uint8_t* __restrict__ step_type) {
-  if (obs != nullptr) encode_obs(g, g.cur, obs + game * SH::kObsStride);
-  if (legal != nullptr) {
-    const unsigned long long m = legal_mask(g, rt, g.cur);
-    if (lane_id() < SH::kLegalWords)
-      legal[game * SH::kLegalWords + lane_id()] = (uint32_t)(m >> (32 * lane_id()));
-  }
-  if (step_type != nullptr && lane_id() == 0) step_type[game] = (uint8_t)g.step_type;
+__device__ __forceinline__ long long game_index() {
+  return (long long)blockIdx.x * kThreads + threadIdx.x;
 }
 
 template <class SH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__device__ __forceinline__ void emit(const Game<SH>& g, long long row, uint32_t* __restrict__ obs,
+                                     uint32_t* __restrict__ legal, uint8_t* __restrict__ step_type) {
+  if (obs != nullptr) encode_obs(g, SH::P - 1, obs + row * SH::kObsStride);
+  if (legal != nullptr) {
+    const unsigned long long m = legal_mask(g);
+    legal[row * SH::kLegalWords] = (uint32_t)m;
+    if (SH::kLegalWords > 1) legal[row * SH::kLegalWords + 1] = (uint32_t)(m >> 32);
+  }
+  if (step_type != nullptr) step_type[row] = (uint8_t)g.step_type;
+}
+
+template <class SH>
+__global__ void __launch_bounds__(kThreads)
 env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
                  uint32_t* __restrict__ obs, uint32_t* __restrict__ legal,
                  uint8_t* __restrict__ step_type) {
-  const int warp = threadIdx.x >> 5;
-  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  const long long game = game_index();
   if (game >= rt.n_games) return;
   Game<SH> g;
   g.episode = 0;
-  reset_game(g, rt, deck_of<SH>(rt, decks, game, 0));
-  emit(g, rt, game, obs, legal, step_type);
+  reset_game(g, deck_of<SH>(rt, decks, game, 0));
+  emit(g, game, obs, legal, step_type);
   store_game(g, state, game);
 }
 
@@ -65,108 +67,112 @@ __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint
   if (g.step_type == LAST) {
     ++g.episode;
     deck = deck_of<SH>(rt, decks, game, g.episode);
-    reset_game(g, rt, deck);
+    reset_game(g, deck);
     return 0.0f;
   }
-  if (!move_is_legal(g, action)) {
-    if (lane_id() == 0) atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and skip
+  const unsigned long long lm = legal_mask(g);
+  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {
+    atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and leave the game as it is
     return 0.0f;
   }
-  const int r = apply_move(g, rt, action, deck);
+  const int r = apply_move(g, action, deck);
   g.step_type = g.terminal() ? LAST : MID;
   return (float)r;
 }
 
 template <class SH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kThreads)
 env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
                 const int32_t* __restrict__ action, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, unsigned long long* illegal) {
-  const int warp = threadIdx.x >> 5;
-  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  const long long game = game_index();
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
   const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
   const float r = step_game(g, rt, decks, deck, game, action[game], illegal);
-  if (reward != nullptr && lane_id() == 0) reward[game] = r;
-  emit(g, rt, game, obs, legal, step_type);
+  if (reward != nullptr) reward[game] = r;
+  emit(g, game, obs, legal, step_type);
   store_game(g, state, game);
 }
 
+// HanabiObservation of the player `offset` seats after the player to move.
 template <class SH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kThreads)
 env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
                    uint32_t* __restrict__ obs, uint32_t* __restrict__ legal) {
-  const int warp = threadIdx.x >> 5;
-  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  const long long game = game_index();
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
-  int q = g.cur + offset;
-  if (q >= SH::P) q -= SH::P;
-  if (obs != nullptr) encode_obs(g, q, obs + game * SH::kObsStride);
   if (legal != nullptr) {   // HanabiState::LegalMoves: empty unless it is that player's turn
-    const unsigned long long m = offset == 0 ? legal_mask(g, rt, q) : 0ull;
-    if (lane_id() < SH::kLegalWords)
-      legal[game * SH::kLegalWords + lane_id()] = (uint32_t)(m >> (32 * lane_id()));
+    const unsigned long long m = offset == 0 ? legal_mask(g) : 0ull;
+    legal[game * SH::kLegalWords] = (uint32_t)m;
+    if (SH::kLegalWords > 1) legal[game * SH::kLegalWords + 1] = (uint32_t)(m >> 32);
+  }
+  if (obs != nullptr) {
+    rotate_seats(g, offset);
+    encode_obs(g, SH::P - 1 - offset, obs + game * SH::kObsStride);   // mover's seat seen from there
   }
 }
 
 // RulebasedAgent.explore over the whole batch (rule_based.py:27-31)
 template <class SH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kThreads)
 rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned long long step,
                  int32_t* __restrict__ action, int32_t* __restrict__ rule_hit,
                  unsigned long long* __restrict__ hist) {
-  const int warp = threadIdx.x >> 5;
-  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
+  const long long game = game_index();
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
   int a = 0, hit = -1;
   if (g.step_type != LAST)
-    a = rules_act(g, rt, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
-  if (lane_id() == 0) {
-    action[game] = a;
-    if (rule_hit != nullptr) rule_hit[game] = hit;
-    if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
-  }
+    a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
+  action[game] = a;
+  if (rule_hit != nullptr) rule_hit[game] = hit;
+  if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
 }
 
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
 // held in registers; only the per-step outputs touch HBM.  Output row (t, game).
 template <class SH>
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+__global__ void __launch_bounds__(kThreads)
 selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks, RuleSet rs,
                 unsigned long long step0, int n_steps, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
-  const int warp = threadIdx.x >> 5;
-  const long long game = (long long)blockIdx.x * kWarpsPerCta + warp;
-  if (game >= rt.n_games) return;
-  Game<SH> g;
-  load_game(g, state, game);
-  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
-  for (int t = 0; t < n_steps; ++t) {
-    int a = 0, hit = -1;
-    if (g.step_type != LAST)
-      a = rules_act(g, rt, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
-    const float r = step_game(g, rt, decks, deck, game, a, illegal);
-    const long long row = (long long)t * rt.n_games + game;
-    if (lane_id() == 0) {
+  __shared__ unsigned int s_hist[kMaxRules + 1];
+  if (threadIdx.x <= kMaxRules) s_hist[threadIdx.x] = 0;
+  __syncthreads();
+  const long long game = game_index();
+  if (game < rt.n_games) {
+    Game<SH> g;
+    load_game(g, state, game);
+    const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
+#pragma unroll 1
+    for (int t = 0; t < n_steps; ++t) {
+      int a = 0, hit = -1;
+      if (g.step_type != LAST)
+        a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
+      const float r = step_game(g, rt, decks, deck, game, a, illegal);
+      const long long row = (long long)t * rt.n_games + game;
       if (action != nullptr) action[row] = a;
       if (reward != nullptr) reward[row] = r;
-      if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
+      if (hit >= 0) atomicAdd(&s_hist[hit], 1u);
+      emit(g, row, obs, legal, step_type);
     }
-    emit(g, rt, row, obs, legal, step_type);
+    store_game(g, state, game);
   }
-  store_game(g, state, game);
+  __syncthreads();
+  if (hist != nullptr && threadIdx.x <= rs.n && s_hist[threadIdx.x])
+    atomicAdd(&hist[threadIdx.x], (unsigned long long)s_hist[threadIdx.x]);
 }
 
-// canonical int32 dump, one thread per game (tests; layout = oracle ho_env_dump)
+// canonical int32 dump, one thread per game, ABSOLUTE player order (tests; layout = oracle
+// ho_env_dump).  The state is seat-relative: absolute player p sits at seat (p - cur) mod P.
 template <class SH>
 __global__ void env_dump_kernel(Rt rt, const uint32_t* __restrict__ state, int32_t* __restrict__ out,
                                 int dump_len) {
@@ -178,27 +184,40 @@ __global__ void env_dump_kernel(Rt rt, const uint32_t* __restrict__ state, int32
   const uint32_t last = w[SH::S + 4];
   int32_t* o = out + game * dump_len;
   int k = 0;
-  const int life = (a >> 19) & 3;
+  const int life = (a >> 19) & 3, cur = (a >> 21) & 7;
   int score = 0;
   for (int c = 0; c < SH::C; ++c) score += (a >> (3 * c)) & 7;
-  o[k++] = (a >> 21) & 7; o[k++] = (a >> 15) & 15; o[k++] = life;
+  o[k++] = cur; o[k++] = (a >> 15) & 15; o[k++] = life;
   o[k++] = SH::DECK - (int)(b & 63); o[k++] = (a >> 24) & 7; o[k++] = (a >> 27) & 3;
   o[k++] = life <= 0 ? 0 : score; o[k++] = (int32_t)(w[SH::S + 5] & 0x7fffffff);
   for (int c = 0; c < SH::C; ++c) o[k++] = (a >> (3 * c)) & 7;
-  for (int p = 0; p < SH::P; ++p) o[k++] = (b >> (6 + 3 * p)) & 7;
-  for (int s = 0; s < SH::S; ++s) {
-    const uint32_t sw = w[s];
-    const bool have = slot_valid(sw);
-    const int cp = slot_cplaus(sw), rp = slot_rplaus(sw);
-    o[k++] = have ? slot_card(sw) : -1;
-    o[k++] = have ? cp : 0;
-    o[k++] = have ? rp : 0;
-    o[k++] = have && slot_chint(sw) ? __ffs(cp) - 1 : -1;
-    o[k++] = have && slot_rhint(sw) ? __ffs(rp) - 1 : -1;
+  for (int p = 0; p < SH::P; ++p) {
+    const int seat = (p - cur + SH::P) % SH::P;
+    o[k++] = (b >> (6 + 3 * seat)) & 7;
+  }
+  for (int p = 0; p < SH::P; ++p) {
+    const int seat = (p - cur + SH::P) % SH::P;
+    for (int i = 0; i < SH::H; ++i) {
+      const uint32_t sw = w[seat * SH::H + i];
+      const bool have = slot_valid(sw);
+      const uint32_t grid = slot_grid(sw);
+      const int card = slot_card(sw);
+      int cp = 0, rp = 0;
+      for (int c = 0; c < 5; ++c) {
+        const uint32_t rowbits = (grid >> (5 * c)) & 31u;
+        if (rowbits) cp |= 1 << c;
+        rp |= (int)rowbits;
+      }
+      o[k++] = have ? card : -1;
+      o[k++] = have ? cp : 0;
+      o[k++] = have ? rp : 0;
+      o[k++] = have && slot_chint(sw) ? card_color(card) : -1;
+      o[k++] = have && slot_rhint(sw) ? card_rank(card) : -1;
+    }
   }
   for (int t = 0; t < SH::BPC; ++t) o[k++] = (int)((disc >> (2 * t)) & 3ull);
   if (last & 1u) {
-    const int uid = (last >> 4) & 63;
+    const int uid = (last >> 1) & 63;
     const bool card_move = uid < 2 * SH::H;
     int type, idx = -1, off = -1, mc = -1, mr = -1;
     if (card_move) {
@@ -213,11 +232,12 @@ __global__ void env_dump_kernel(Rt rt, const uint32_t* __restrict__ state, int32
       type = by_color ? REVEAL_COLOR : REVEAL_RANK;
       if (by_color) mc = u % span; else mr = u % span;
     }
-    o[k++] = 1; o[k++] = (last >> 1) & 7; o[k++] = type; o[k++] = idx; o[k++] = off;
+    const int card = (last >> 7) & 31;
+    o[k++] = 1; o[k++] = (cur + SH::P - 1) % SH::P; o[k++] = type; o[k++] = idx; o[k++] = off;
     o[k++] = mc; o[k++] = mr;
-    o[k++] = card_move ? (int)((last >> 10) & 7) : -1;
-    o[k++] = card_move ? (int)((last >> 13) & 7) : -1;
-    o[k++] = (last >> 16) & 1; o[k++] = (last >> 17) & 1; o[k++] = (last >> 18) & 31;
+    o[k++] = card_move ? card_color(card) : -1;
+    o[k++] = card_move ? card_rank(card) : -1;
+    o[k++] = (last >> 12) & 1; o[k++] = (last >> 13) & 1; o[k++] = (last >> 14) & 31;
   } else {
     for (int j = 0; j < 12; ++j) o[k++] = 0;
   }
@@ -271,9 +291,8 @@ int find_shape(int P, int H, int C, int R, int MI, int ML) {
   }
 
 inline unsigned grid_for(const hb_env* e) {
-  return (unsigned)((e->rt.n_games + kWarpsPerCta - 1) / kWarpsPerCta);
+  return (unsigned)((e->rt.n_games + kThreads - 1) / kThreads);
 }
-inline size_t smem_for(const hb_env*) { return 0; }
 
 int env_stage(hb_env* e, size_t bytes) {
   if (e->stage_bytes >= bytes) return HB_OK;
@@ -297,6 +316,9 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
     rs.farg[k] = farg ? farg[k] : 0.0;
     rs.iarg[k] = iarg ? iarg[k] : 0;
   }
+  rs.id[n] = R_LEGAL_RANDOM;   // Ruleset.legal_random fallback (rule_based.py:24)
+  rs.farg[n] = 0.0;
+  rs.iarg[n] = 0;
   return HB_OK;
 }
 
@@ -423,7 +445,7 @@ int hb_env_reset(hb_env* e, uint32_t* d_obs, uint32_t* d_legal, uint8_t* d_step_
   HB_REQUIRE(e, "hb_env_reset: NULL env");
   if (!e->decks) { hb::set_error("hb_env_reset: call hb_env_set_decks first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (env_reset_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+  HB_DISPATCH(e, (env_reset_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, e->decks, d_obs, d_legal, d_step_type)));
   HB_CUDA(cudaGetLastError());
   e->is_reset = true;
@@ -435,7 +457,7 @@ int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d
   HB_REQUIRE(e && d_action, "hb_env_step: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_env_step: reset the environment first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (env_step_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+  HB_DISPATCH(e, (env_step_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, e->decks, d_action, d_obs, d_legal, d_reward, d_step_type,
                      e->illegal)));
   HB_CUDA(cudaGetLastError());
@@ -446,7 +468,7 @@ int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, vo
   HB_REQUIRE(e && offset >= 0 && offset < e->P, "hb_env_observe: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_env_observe: reset the environment first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (env_observe_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+  HB_DISPATCH(e, (env_observe_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, offset, d_obs, d_legal)));
   HB_CUDA(cudaGetLastError());
   return HB_OK;
@@ -505,7 +527,7 @@ int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, co
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (rules_act_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, 0, (cudaStream_t)stream>>>(
+  HB_DISPATCH(e, (rules_act_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, rs, step, d_action, d_rule_hit,
                      (unsigned long long*)d_hist)));
   HB_CUDA(cudaGetLastError());
@@ -522,7 +544,7 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (selfplay_kernel<SH><<<grid_for(e), kWarpsPerCta * 32, smem_for(e), (cudaStream_t)stream>>>(
+  HB_DISPATCH(e, (selfplay_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
                      d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
   HB_CUDA(cudaGetLastError());

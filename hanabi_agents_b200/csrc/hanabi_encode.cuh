@@ -1,26 +1,28 @@
 // Canonical observation encoder (HLE CanonicalObservationEncoder),
 // bit-packed: observation bit b lives in word b>>5, bit b&31 of the game's row.
 //
-// Lane W assembles output word W directly in a register -- no shared memory, no atomics:
-//   * the warp-uniform middle of the vector (short-hand bits, board, discards, last action)
-//     is built once as a handful of 32-bit words with compile-time bit offsets;
-//   * the card-dependent ends (hands section, card-knowledge section) are gathered from the
-//     slot lanes with shuffles: a 32-bit window overlaps at most kHandTaps one-hot card
-//     fields and kKnowTaps knowledge fields.
-// The finished row leaves with one coalesced store (row stride is a multiple of 16 B).
+// Thread-per-game, observer = seat 0 (hands are seat-relative, see hanabi_game.cuh), so the
+// bit offset of EVERY field of the vector is a compile-time constant: the row is assembled in
+// registers by OR-ing each field into one or two words with constant shifts, and leaves as
+// 16-byte vector stores (row stride is a multiple of 16 B).
 #pragma once
 #include "hanabi_game.cuh"
 
 namespace hbg {
 
-template <int OFF, int WIDTH, int W0, int NU>
-__device__ __forceinline__ void or_field(uint32_t (&U)[NU], uint32_t v) {
-  constexpr int idx = OFF / 32 - W0, sh = OFF % 32;
-  static_assert(idx >= 0 && idx < NU, "field outside the uniform window");
-  U[idx] |= v << sh;
+// OR a WIDTH-bit field into the row at compile-time bit offset OFF.
+template <int OFF, int WIDTH, int N>
+__device__ __forceinline__ void put(uint32_t (&row)[N], unsigned long long v) {
+  constexpr int idx = OFF / 32, sh = OFF % 32;
+  static_assert(WIDTH >= 1 && WIDTH <= 64 && idx < N, "field outside the row");
+  row[idx] |= (uint32_t)(v << sh);
   if constexpr (sh + WIDTH > 32) {
-    static_assert(idx + 1 < NU, "field crosses the end of the uniform window");
-    U[idx + 1] |= v >> (32 - sh);
+    static_assert(idx + 1 < N, "field outside the row");
+    row[idx + 1] |= (uint32_t)(v >> (32 - sh));
+  }
+  if constexpr (sh + WIDTH > 64) {
+    static_assert(idx + 2 < N, "field outside the row");
+    row[idx + 2] |= (uint32_t)(v >> (64 - sh));
   }
 }
 
@@ -41,79 +43,80 @@ __device__ __forceinline__ unsigned long long discard_thermometers(unsigned long
   return (ge1 & m0) | ((ge1 & m14) << 1) | ((ge2 & m0) << 1) | ((ge2 & m13) << 2) | ((eq3 & m0) << 2);
 }
 
-// Observation of player q (observer-relative offsets k = (p - q) mod P), written to `row`.
-template <class SH>
-__device__ __forceinline__ void encode_obs(const Game<SH>& g, int q, uint32_t* __restrict__ row) {
-  constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R, BPC = SH::BPC;
-  constexpr int KW = SH::kKnowWidth;
-  constexpr int W0 = SH::kHandsCards / 32, W1 = (SH::kOffKnow - 1) / 32, NU = W1 - W0 + 1;
-  constexpr int kHandTaps = (32 + BPC - 2) / BPC + 1;
-  constexpr int kKnowTaps = (32 + KW - 2) / KW + 1;
-  const int lane = lane_id();
+template <class SH, int K, int I, int N>
+__device__ __forceinline__ void put_hand_card(uint32_t (&row)[N], uint32_t w) {
+  // EncodeHands: one-hot card index of another player's card
+  put<(K - 1) * SH::H * SH::BPC + I * SH::BPC, SH::BPC>(row, slot_valid(w) ? (1ull << slot_card(w)) : 0ull);
+}
 
-  // ---- this lane's card-knowledge field: plausible grid | hinted colour | hinted rank ----
-  unsigned long long know = 0;
-  if (lane < SH::S && slot_valid(g.slot)) {
-    const uint32_t cp = slot_cplaus(g.slot), rp = slot_rplaus(g.slot);
-    uint32_t grid = 0;
-#pragma unroll
-    for (int c = 0; c < C; ++c)
-      if ((cp >> c) & 1) grid |= rp << (c * R);
-    const uint32_t hints = (slot_chint(g.slot) ? cp : 0u) | ((slot_rhint(g.slot) ? rp : 0u) << C);
-    know = (unsigned long long)grid | ((unsigned long long)hints << BPC);
+template <class SH, int K, int I, int N>
+__device__ __forceinline__ void put_knowledge(uint32_t (&row)[N], uint32_t w) {
+  // EncodeCardKnowledge: plausible grid | one-hot hinted colour | one-hot hinted rank.
+  // A hint names the card's true colour / rank, so the one-hots come from the card itself.
+  const int card = slot_card(w);
+  unsigned long long f = slot_grid(w);
+  f |= (unsigned long long)slot_chint(w) << (SH::BPC + card_color(card));
+  f |= (unsigned long long)slot_rhint(w) << (SH::BPC + SH::C + card_rank(card));
+  put<SH::kOffKnow + (K * SH::H + I) * SH::kKnowWidth, SH::kKnowWidth>(row, f);
+}
+
+template <class SH, int K, int N>
+__device__ __forceinline__ void put_seat(uint32_t (&row)[N], const Game<SH>& g) {
+  if constexpr (K < SH::P) {
+#define HB_CARD(I)                                                        \
+    if constexpr (I < SH::H) {                                            \
+      if constexpr (K >= 1) put_hand_card<SH, K, I>(row, g.hand[K][I]);   \
+      put_knowledge<SH, K, I>(row, g.hand[K][I]);                         \
+    }
+    HB_CARD(0) HB_CARD(1) HB_CARD(2) HB_CARD(3) HB_CARD(4)
+#undef HB_CARD
+    put_seat<SH, K + 1>(row, g);
   }
-  const uint32_t know_lo = (uint32_t)know, know_hi = (uint32_t)(know >> 32);
+}
 
-  // ---- warp-uniform words W0..W1 ---------------------------------------------------------
-  uint32_t U[NU];
+// Observation of the player at seat 0, `mover_seat` = seat of the player who made g.last
+// (P-1 for the player to move).  Writes kObsStride words at `out`.
+template <class SH>
+__device__ __forceinline__ void encode_obs(const Game<SH>& g, int mover_seat, uint32_t* __restrict__ out) {
+  constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R, BPC = SH::BPC;
+  uint32_t row[SH::kObsStride];
 #pragma unroll
-  for (int i = 0; i < NU; ++i) U[i] = 0;
+  for (int i = 0; i < SH::kObsStride; ++i) row[i] = 0;
+
+  put_seat<SH, 0>(row, g);                              // hands + card knowledge
+
   {
     uint32_t v = 0;                                     // EncodeHands: "hand is short" bits
 #pragma unroll
-    for (int k = 0; k < P; ++k) {
-      int p = q + k;
-      if (p >= P) p -= P;
-      if (g.hand_n(p) < H) v |= 1u << k;
-    }
-    or_field<SH::kHandsCards, P, W0>(U, v);
+    for (int k = 0; k < P; ++k)
+      if (g.hand_n(k) < H) v |= 1u << k;
+    put<SH::kHandsCards, P>(row, v);
   }
-  {
-    const int rem = SH::DECK - g.deck_pos;              // EncodeBoard: deck thermometer
-    constexpr int LO = SH::kDeckThermo < 32 ? SH::kDeckThermo : 32;
-    or_field<SH::kOffBoard, LO, W0>(U, rem >= 32 ? 0xffffffffu : ((1u << rem) - 1));
-    if constexpr (SH::kDeckThermo > 32)
-      or_field<SH::kOffBoard + 32, SH::kDeckThermo - 32, W0>(U, rem > 32 ? ((1u << (rem - 32)) - 1) : 0u);
-  }
-  {
+  {                                                     // EncodeBoard
+    const int rem = SH::DECK - g.deck_pos;
+    put<SH::kOffBoard, SH::kDeckThermo>(row, (1ull << rem) - 1);
     uint32_t v = 0;                                     // fireworks: one-hot of height-1
 #pragma unroll
     for (int c = 0; c < C; ++c) {
       const int f = g.firework(c);
       if (f > 0) v |= 1u << (c * R + f - 1);
     }
-    or_field<SH::kOffFireworks, BPC, W0>(U, v);
-    or_field<SH::kOffInfo, SH::MAX_INFO + SH::MAX_LIFE, W0>(
-        U, ((1u << g.info) - 1) | (((1u << g.life) - 1) << SH::MAX_INFO));
+    put<SH::kOffFireworks, BPC>(row, v);
+    put<SH::kOffInfo, SH::MAX_INFO + SH::MAX_LIFE>(
+        row, ((1u << g.info) - 1) | (((1u << g.life) - 1) << SH::MAX_INFO));
   }
-  {
-    const unsigned long long t = discard_thermometers<SH>(g.disc);   // EncodeDiscards
-    constexpr int LO = SH::DECK < 32 ? SH::DECK : 32;
-    or_field<SH::kOffDisc, LO, W0>(U, (uint32_t)t);
-    if constexpr (SH::DECK > 32) or_field<SH::kOffDisc + 32, SH::DECK - 32, W0>(U, (uint32_t)(t >> 32));
-  }
+  put<SH::kOffDisc, SH::DECK>(row, discard_thermometers<SH>(g.disc));   // EncodeDiscards
+
   if (g.last & 1u) {                                    // EncodeLastAction
     const uint32_t last = g.last;
-    const int uid = (last >> 4) & 63;
-    int rel = (int)((last >> 1) & 7) - q;
-    if (rel < 0) rel += P;
-    uint32_t a = 1u << rel, b, c3 = 0;
+    const int uid = (last >> 1) & 63;
+    uint32_t a = 1u << mover_seat, b, c3 = 0;
     if (uid < 2 * H) {
       const bool is_play = uid >= H;
       a |= 1u << (P + (is_play ? 0 : 1));               // move type: Play, Discard
       b = 1u << (H + (is_play ? uid - H : uid));        // card position
-      c3 = 1u << (((last >> 10) & 7) * R + ((last >> 13) & 7));   // card identity
-      if (is_play) c3 |= ((last >> 16) & 3u) << BPC;    // scored, information token
+      c3 = 1u << ((last >> 7) & 31);                    // card identity
+      if (is_play) c3 |= ((last >> 12) & 3u) << BPC;    // scored, information token
     } else {
       int u = uid - 2 * H;
       const bool by_color = u < (P - 1) * C;
@@ -121,63 +124,21 @@ __device__ __forceinline__ void encode_obs(const Game<SH>& g, int q, uint32_t* _
       const int span = by_color ? C : R;
       const int k = 1 + u / span, val = u - (k - 1) * span;
       a |= 1u << (P + (by_color ? 2 : 3));              // RevealColor, RevealRank
-      int tgt = rel + k;
+      int tgt = mover_seat + k;                         // observer-relative target
       if (tgt >= P) tgt -= P;
       a |= 1u << (P + 4 + tgt);
       a |= 1u << (2 * P + 4 + (by_color ? 0 : C) + val);
-      b = (last >> 18) & ((1u << H) - 1);               // reveal outcome
+      b = (last >> 14) & ((1u << H) - 1);               // reveal outcome
     }
-    or_field<SH::kOffLast, 2 * P + 4 + C + R, W0>(U, a);
-    or_field<SH::kOffLast + 2 * P + 4 + C + R, 2 * H, W0>(U, b);
-    or_field<SH::kOffLast + 2 * P + 4 + C + R + 2 * H, BPC + 2, W0>(U, c3);
+    put<SH::kOffLast, 2 * P + 4 + C + R>(row, a);
+    put<SH::kOffLast + 2 * P + 4 + C + R, 2 * H>(row, b);
+    put<SH::kOffLast + 2 * P + 4 + C + R + 2 * H, BPC + 2>(row, c3);
   }
 
-  // ---- one output word per lane (two rounds when the row is longer than 32 words) ---------
+  uint4* dst = reinterpret_cast<uint4*>(out);
 #pragma unroll
-  for (int base = 0; base < SH::kObsStride; base += 32) {
-    const int W = base + lane;
-    uint32_t word = 0;
-#pragma unroll
-    for (int i = 0; i < NU; ++i)
-      if (W == W0 + i) word = U[i];
-
-    if (base * 32 < SH::kHandsCards) {                  // EncodeHands: others' cards, one-hot
-      const int j0 = (32 * W) / BPC;
-#pragma unroll
-      for (int t = 0; t < kHandTaps; ++t) {
-        const int j = j0 + t;
-        const bool ok = j < (P - 1) * H;
-        const int k = 1 + j / H, i = j - (k - 1) * H;
-        int p = q + k;
-        if (p >= P) p -= P;
-        const uint32_t sw = __shfl_sync(kFull, g.slot, ok ? p * H + i : 0);
-        const int bit = j * BPC + slot_card(sw) - 32 * W;
-        if (ok && slot_valid(sw) && (unsigned)bit < 32u) word |= 1u << bit;
-      }
-    }
-    if ((base + 32) * 32 > SH::kOffKnow) {              // EncodeCardKnowledge
-      const int b0 = 32 * W - SH::kOffKnow;
-      const int j0 = b0 > 0 ? b0 / KW : 0;
-#pragma unroll
-      for (int t = 0; t < kKnowTaps; ++t) {
-        const int j = j0 + t;
-        const bool ok = j < P * H;
-        const int k = j / H, i = j - k * H;
-        int p = q + k;
-        if (p >= P) p -= P;
-        const int src = ok ? p * H + i : 0;
-        const uint32_t lo = __shfl_sync(kFull, know_lo, src);
-        const uint32_t hi = KW > 32 ? __shfl_sync(kFull, know_hi, src) : 0u;
-        const unsigned long long f = (unsigned long long)lo | ((unsigned long long)hi << 32);
-        const int rel = j * KW - b0;                    // field bit 0 relative to this word
-        uint32_t add = 0;
-        if (rel >= 0) { if (rel < 32) add = (uint32_t)(f << rel); }
-        else if (rel > -64) add = (uint32_t)(f >> (-rel));
-        if (ok) word |= add;
-      }
-    }
-    if (W < SH::kObsStride) row[W] = word;
-  }
+  for (int i = 0; i < SH::kObsStride / 4; ++i)
+    dst[i] = make_uint4(row[4 * i], row[4 * i + 1], row[4 * i + 2], row[4 * i + 3]);
 }
 
 }  // namespace hbg

@@ -1,43 +1,47 @@
-// Warp-per-game Hanabi engine: state layout and device functions.
+// Thread-per-game Hanabi engine: state layout, legality and transition.
 //
 // Replaces (for N games at once) the third-party HLE calls the reference makes through
 // `environment.step` / `observation['vectorized']` / `legal_moves_as_int`
 // (hanabi_agents/rainbow/run_experiment.py:266-273,308; consumed as observations[1] at
 // hanabi_agents/rlax_dqn/rlax_rainbow.py:278,285,298).  Semantics: SURVEY.md Appendix A.
 //
-// One warp owns one game.  Lane s < S (S = players*hand_size) owns CARD SLOT s =
-// player*H + index: its card and the hint knowledge about it live in one register.
-// Everything else (fireworks, tokens, discard counts, last move ...) is warp-uniform and
-// kept redundantly in every lane.  A game is `kStateWords` 32-bit words in HBM, lane j
-// loads/stores word j, so a game's state moves as one coalesced 64 B / 128 B access.
+// One THREAD owns one game; the whole game lives in its registers.  Every branch of the
+// rules (4 move types, N agent rules) is small, so a warp simply walks all of them with the
+// non-participating games predicated off: no instruction is spent on warp-uniform bookkeeping
+// (the first, warp-per-game version of this file spent >70 % of its issue slots there;
+// profiles/r01_selfplay_warp_per_game.md).
 //
-// Slot word:   [4:0] card (color*R+rank)  [9:5] colours still plausible  [14:10] ranks still
-//              plausible  [15] colour hinted  [16] rank hinted  [17] slot occupied
-// Scalar words (at word S + k):
-//   k=0  [14:0] fireworks 3b x5 | [18:15] info | [20:19] life | [23:21] cur player |
-//        [26:24] turns_to_play | [28:27] step_type
-//   k=1  [5:0] deck_pos | [20:6] hand_n 3b x5
-//   k=2,3  discard counts, 2 bits per card type (25 types -> 50 bits)
-//   k=4  last non-deal move: [0] valid [3:1] player [9:4] move uid [12:10] card colour
-//        [15:13] card rank [16] scored [17] info token [22:18] reveal bitmask
-//   k=5  episode counter (selects the deck: (game_id + episode*n_total) mod n_decks)
+// Hands are kept in SEAT-RELATIVE order: hand[0] is always the player to move, hand[k] the
+// player k seats later.  After every move the hands rotate by one seat, so all agent rules
+// and the whole observation encoder index with compile-time constants.
+//
+// A game is kStateWords 32-bit words in HBM (16 for 2 players = 64 B, else 32 = 128 B):
+//   words 0..S-1  card slots, seat-relative, slot (k, i) at word k*H + i:
+//        [24:0] plausible(colour) x plausible(rank) grid, bit colour*5+rank (0 = empty slot)
+//        [25] colour hinted  [26] rank hinted  [31:27] card index colour*5+rank
+//   word S+0  [14:0] fireworks 3b x5 | [18:15] info | [20:19] life | [23:21] player to move
+//             | [26:24] turns_to_play | [28:27] step_type
+//   word S+1  [5:0] deck_pos | [20:6] hand sizes 3b x5 (seat-relative)
+//   word S+2,3  discard counts, 2 bits per card type (25 types -> 50 bits)
+//   word S+4  last move (made by the player now at seat P-1): [0] valid [6:1] move uid
+//             [11:7] card index [12] scored [13] info token [18:14] reveal bitmask
+//   word S+5  episode counter (selects the deck: (game_id + episode*n_total) mod n_decks)
 #pragma once
 #include <stdint.h>
 
 namespace hbg {
 
-constexpr unsigned kFull = 0xffffffffu;
 enum { FIRST = 0, MID = 1, LAST = 2 };
 enum { PLAY = 1, DISCARD = 2, REVEAL_COLOR = 3, REVEAL_RANK = 4 };
 
 template <int P_, int H_, int C_, int R_, int MI_, int ML_>
 struct Shape {
-  static_assert(R_ == 5, "rank-dependent bit tricks assume 5 ranks (3/2/2/2/1 instances)");
+  static_assert(R_ == 5, "bit tricks assume 5 ranks with 3/2/2/2/1 instances");
   static constexpr int P = P_, H = H_, C = C_, R = R_;
   static constexpr int MAX_INFO = MI_, MAX_LIFE = ML_;
   static constexpr int S = P * H;                 // card slots
   static constexpr int BPC = C * R;               // bits per card
-  static constexpr int kPerColor = (R == 1) ? 3 : (3 + 2 * (R - 2) + 1);
+  static constexpr int kPerColor = 10;            // 3+2+2+2+1 cards per colour
   static constexpr int DECK = C * kPerColor;
   static constexpr int A = 2 * H + (P - 1) * (C + R);       // num moves
   static constexpr int kStateWords = (S + 6 <= 16) ? 16 : 32;
@@ -56,15 +60,7 @@ struct Shape {
   static constexpr int kObsLen = kOffKnow + P * H * kKnowWidth;
   static constexpr int kObsWords = (kObsLen + 31) / 32;
   static constexpr int kObsStride = (kObsWords + 3) / 4 * 4;  // row = multiple of 16 B
-  __host__ __device__ static constexpr int instances(int r) {
-    return r == 0 ? 3 : (r == R - 1 ? 1 : 2);
-  }
-  // bit offset of rank r inside one colour's discard thermometer block
-  __host__ __device__ static constexpr int disc_off(int r) {
-    int o = 0;
-    for (int i = 0; i < r; ++i) o += instances(i);
-    return o;
-  }
+  static constexpr uint32_t kGridAll = (1u << (C * R)) - 1;
 };
 
 // runtime part of the configuration (kernel argument, by value)
@@ -75,21 +71,35 @@ struct Rt {
   long long n_decks;
 };
 
+constexpr uint32_t kGridMask = 0x1ffffffu;
+__device__ __forceinline__ uint32_t slot_grid(uint32_t w) { return w & kGridMask; }
+__device__ __forceinline__ bool slot_valid(uint32_t w) { return (w & kGridMask) != 0; }
+__device__ __forceinline__ uint32_t slot_chint(uint32_t w) { return (w >> 25) & 1u; }
+__device__ __forceinline__ uint32_t slot_rhint(uint32_t w) { return (w >> 26) & 1u; }
+__device__ __forceinline__ int slot_card(uint32_t w) { return (int)(w >> 27); }
+__device__ __forceinline__ int card_color(int card) { return (card * 52) >> 8; }   // card / 5, card < 32
+__device__ __forceinline__ int card_rank(int card) { return card - 5 * card_color(card); }
+// all cells of colour c / of rank r in the 5x5 grid
+__device__ __forceinline__ uint32_t color_cells(int c) { return 31u << (5 * c); }
+__device__ __forceinline__ uint32_t rank_cells(int r) { return 0x108421u << r; }
+
+template <class SH>
+__device__ __forceinline__ uint32_t fresh_slot(int card) {
+  return SH::kGridAll | ((uint32_t)card << 27);   // everything plausible, nothing hinted
+}
+
 template <class SH>
 struct Game {
-  // per-lane
-  uint32_t slot;       // this lane's card slot word (0 for lanes >= S)
-  // warp-uniform
-  uint32_t fw;         // 3 bits per colour
+  uint32_t hand[SH::P][SH::H];   // seat-relative card slots
+  uint32_t fw;                   // 3 bits per colour
+  uint32_t hn;                   // 3 bits per seat
   int info, life, cur, ttp, step_type, deck_pos;
-  uint32_t hn;         // 3 bits per player
-  unsigned long long disc;  // 2 bits per card type
+  unsigned long long disc;       // 2 bits per card type
   uint32_t last;
   uint32_t episode;
 
   __device__ __forceinline__ int firework(int c) const { return (fw >> (3 * c)) & 7; }
-  __device__ __forceinline__ int hand_n(int p) const { return (hn >> (3 * p)) & 7; }
-  __device__ __forceinline__ int disc_n(int t) const { return (int)((disc >> (2 * t)) & 3ull); }
+  __device__ __forceinline__ int hand_n(int k) const { return (hn >> (3 * k)) & 7; }
   __device__ __forceinline__ int score() const {
     if (life <= 0) return 0;
     int s = 0;
@@ -97,38 +107,30 @@ struct Game {
     for (int c = 0; c < SH::C; ++c) s += firework(c);
     return s;
   }
+  // HanabiState::EndOfGameStatus
   __device__ __forceinline__ bool terminal() const {
     return life < 1 || score() >= SH::C * SH::R || ttp <= 0;
   }
 };
 
-__device__ __forceinline__ int lane_id() { return threadIdx.x & 31; }
-__device__ __forceinline__ int slot_card(uint32_t w) { return w & 31; }
-__device__ __forceinline__ int slot_cplaus(uint32_t w) { return (w >> 5) & 31; }
-__device__ __forceinline__ int slot_rplaus(uint32_t w) { return (w >> 10) & 31; }
-__device__ __forceinline__ bool slot_chint(uint32_t w) { return (w >> 15) & 1; }
-__device__ __forceinline__ bool slot_rhint(uint32_t w) { return (w >> 16) & 1; }
-__device__ __forceinline__ bool slot_valid(uint32_t w) { return (w >> 17) & 1; }
-
-template <class SH>
-__device__ __forceinline__ uint32_t fresh_slot(int card) {
-  return (uint32_t)card | (((1u << SH::C) - 1) << 5) | (((1u << SH::R) - 1) << 10) | (1u << 17);
-}
-
-// ---- state <-> HBM -----------------------------------------------------------------
+// ---- state <-> HBM (16-byte vector accesses; a game is 64 B or 128 B contiguous) ----------
 template <class SH>
 __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restrict__ state,
                                           long long game) {
-  const int lane = lane_id();
-  uint32_t w = 0;
-  if (lane < SH::kStateWords) w = state[game * SH::kStateWords + lane];
-  g.slot = lane < SH::S ? w : 0u;
-  const uint32_t a = __shfl_sync(kFull, w, SH::S + 0);
-  const uint32_t b = __shfl_sync(kFull, w, SH::S + 1);
-  const uint32_t d0 = __shfl_sync(kFull, w, SH::S + 2);
-  const uint32_t d1 = __shfl_sync(kFull, w, SH::S + 3);
-  g.last = __shfl_sync(kFull, w, SH::S + 4);
-  g.episode = __shfl_sync(kFull, w, SH::S + 5);
+  uint32_t w[SH::kStateWords];
+  const uint4* src = reinterpret_cast<const uint4*>(state + game * SH::kStateWords);
+#pragma unroll
+  for (int i = 0; i < SH::kStateWords / 4; ++i) {
+    if (4 * i < SH::S + 6) {
+      const uint4 v = src[i];
+      w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = w[k * SH::H + i];
+  const uint32_t a = w[SH::S], b = w[SH::S + 1];
   g.fw = a & 0x7fff;
   g.info = (a >> 15) & 15;
   g.life = (a >> 19) & 3;
@@ -137,40 +139,51 @@ __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restric
   g.step_type = (a >> 27) & 3;
   g.deck_pos = b & 63;
   g.hn = (b >> 6) & 0x7fff;
-  g.disc = (unsigned long long)d0 | ((unsigned long long)d1 << 32);
+  g.disc = (unsigned long long)w[SH::S + 2] | ((unsigned long long)w[SH::S + 3] << 32);
+  g.last = w[SH::S + 4];
+  g.episode = w[SH::S + 5];
 }
 
 template <class SH>
 __device__ __forceinline__ void store_game(const Game<SH>& g, uint32_t* __restrict__ state,
                                            long long game) {
-  const int lane = lane_id();
-  uint32_t w = g.slot;
-  const uint32_t a = g.fw | ((uint32_t)g.info << 15) | ((uint32_t)g.life << 19) |
-                     ((uint32_t)g.cur << 21) | ((uint32_t)g.ttp << 24) |
-                     ((uint32_t)g.step_type << 27);
-  const uint32_t b = (uint32_t)g.deck_pos | (g.hn << 6);
-  if (lane == SH::S + 0) w = a;
-  if (lane == SH::S + 1) w = b;
-  if (lane == SH::S + 2) w = (uint32_t)g.disc;
-  if (lane == SH::S + 3) w = (uint32_t)(g.disc >> 32);
-  if (lane == SH::S + 4) w = g.last;
-  if (lane == SH::S + 5) w = g.episode;
-  if (lane >= SH::S + 6) w = 0;
-  if (lane < SH::kStateWords) state[game * SH::kStateWords + lane] = w;
+  uint32_t w[SH::kStateWords];
+#pragma unroll
+  for (int i = 0; i < SH::kStateWords; ++i) w[i] = 0;
+#pragma unroll
+  for (int k = 0; k < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) w[k * SH::H + i] = g.hand[k][i];
+  w[SH::S] = g.fw | ((uint32_t)g.info << 15) | ((uint32_t)g.life << 19) | ((uint32_t)g.cur << 21) |
+             ((uint32_t)g.ttp << 24) | ((uint32_t)g.step_type << 27);
+  w[SH::S + 1] = (uint32_t)g.deck_pos | (g.hn << 6);
+  w[SH::S + 2] = (uint32_t)g.disc;
+  w[SH::S + 3] = (uint32_t)(g.disc >> 32);
+  w[SH::S + 4] = g.last;
+  w[SH::S + 5] = g.episode;
+  uint4* dst = reinterpret_cast<uint4*>(state + game * SH::kStateWords);
+#pragma unroll
+  for (int i = 0; i < SH::kStateWords / 4; ++i)
+    if (4 * i < SH::S + 6) dst[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
 }
 
 template <class SH>
 __device__ __forceinline__ const uint8_t* deck_of(const Rt& rt, const uint8_t* __restrict__ decks,
                                                   long long game, uint32_t episode) {
-  const long long row = (rt.game_id_base + game + (long long)episode * rt.n_total) % rt.n_decks;
+  const unsigned long long row =
+      (unsigned long long)(rt.game_id_base + game + (long long)episode * rt.n_total) %
+      (unsigned long long)rt.n_decks;
   return decks + row * SH::DECK;
 }
 
 // HanabiState ctor + initial deals (A.3): player 0 is filled first, then player 1, ...
+// Player 0 moves first, so seat-relative order == absolute order here.
 template <class SH>
-__device__ __forceinline__ void reset_game(Game<SH>& g, const Rt& rt, const uint8_t* deck) {
-  const int lane = lane_id();
-  g.slot = lane < SH::S ? fresh_slot<SH>(deck[lane]) : 0u;
+__device__ __forceinline__ void reset_game(Game<SH>& g, const uint8_t* __restrict__ deck) {
+#pragma unroll
+  for (int k = 0; k < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = fresh_slot<SH>(deck[k * SH::H + i]);
   g.fw = 0;
   g.info = SH::MAX_INFO;
   g.life = SH::MAX_LIFE;
@@ -180,132 +193,135 @@ __device__ __forceinline__ void reset_game(Game<SH>& g, const Rt& rt, const uint
   g.deck_pos = SH::S;
   g.hn = 0;
 #pragma unroll
-  for (int p = 0; p < SH::P; ++p) g.hn |= (uint32_t)SH::H << (3 * p);
+  for (int k = 0; k < SH::P; ++k) g.hn |= (uint32_t)SH::H << (3 * k);
   g.disc = 0;
   g.last = 0;
 }
 
-// ---- legality (A.4) -------------------------------------------------------------------
-// 64-bit mask over move uids for player q (the player to move).
+// ---- legality (A.4): 64-bit mask over move uids for the player to move ---------------------
 template <class SH>
-__device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g, const Rt& rt, int q) {
-  const int lane = lane_id();
-  const unsigned long long hand_bits = (1ull << g.hand_n(q)) - 1;
+__device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g) {
+  const unsigned long long hand_bits = (1ull << g.hand_n(0)) - 1;
   unsigned long long m = hand_bits << SH::H;                 // Play(i), i < hand size
-  if (g.info < SH::MAX_INFO) m |= hand_bits;                  // Discard(i)
-  uint32_t lo = 0, hi = 0;
-  if (g.info > 0 && lane < SH::S && slot_valid(g.slot)) {
-    const int p = lane / SH::H;
-    int k = p - q;
-    if (k < 0) k += SH::P;
-    if (k >= 1) {
-      const int card = slot_card(g.slot);
-      const int c = card / SH::R, r = card - c * SH::R;
-      const unsigned long long b =
-          (1ull << (2 * SH::H + (k - 1) * SH::C + c)) |
-          (1ull << (2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R + r));
-      lo = (uint32_t)b;
-      hi = (uint32_t)(b >> 32);
+  if (g.info < SH::MAX_INFO) m |= hand_bits;                 // Discard(i)
+  if (g.info > 0) {
+#pragma unroll
+    for (int k = 1; k < SH::P; ++k) {
+      uint32_t colors = 0, ranks = 0;                        // what the target hand contains
+#pragma unroll
+      for (int i = 0; i < SH::H; ++i) {
+        const uint32_t w = g.hand[k][i];
+        const int card = slot_card(w);
+        if (slot_valid(w)) {
+          colors |= 1u << card_color(card);
+          ranks |= 1u << card_rank(card);
+        }
+      }
+      m |= (unsigned long long)colors << (2 * SH::H + (k - 1) * SH::C);
+      m |= (unsigned long long)ranks << (2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R);
     }
   }
-  lo = __reduce_or_sync(kFull, lo);
-  if (SH::A > 32) hi = __reduce_or_sync(kFull, hi);
-  return m | (unsigned long long)lo | ((unsigned long long)hi << 32);
-}
-
-// MoveIsLegal for ONE move uid of the player to move (cheaper than the full mask).
-template <class SH>
-__device__ __forceinline__ bool move_is_legal(const Game<SH>& g, int uid) {
-  if (uid < 0 || uid >= SH::A) return false;
-  const int me = g.cur;
-  if (uid < SH::H) return g.info < SH::MAX_INFO && uid < g.hand_n(me);
-  if (uid < 2 * SH::H) return uid - SH::H < g.hand_n(me);
-  if (g.info <= 0) return false;
-  int u = uid - 2 * SH::H;
-  const bool by_color = u < (SH::P - 1) * SH::C;
-  if (!by_color) u -= (SH::P - 1) * SH::C;
-  const int span = by_color ? SH::C : SH::R;
-  const int k = 1 + u / span, v = u - (k - 1) * span;
-  int t = me + k;
-  if (t >= SH::P) t -= SH::P;
-  const int lane = lane_id();
-  bool match = false;
-  if (lane < SH::S && slot_valid(g.slot) && lane / SH::H == t) {
-    const int card = slot_card(g.slot);
-    const int c = card / SH::R, r = card - c * SH::R;
-    match = by_color ? (c == v) : (r == v);
-  }
-  return __any_sync(kFull, match);
+  return m;
 }
 
 // ---- transition (A.3): ApplyMove + chance deal + AdvanceToNextPlayer -------------------
-// `uid` must be legal.  Returns the reward (score delta).
 template <class SH>
-__device__ __forceinline__ int apply_move(Game<SH>& g, const Rt& rt, int uid, const uint8_t* deck) {
-  const int lane = lane_id();
+__device__ __forceinline__ void rotate_once(Game<SH>& g) {
+  uint32_t first[SH::H];
+#pragma unroll
+  for (int i = 0; i < SH::H; ++i) first[i] = g.hand[0][i];
+#pragma unroll
+  for (int k = 0; k + 1 < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = g.hand[k + 1][i];
+#pragma unroll
+  for (int i = 0; i < SH::H; ++i) g.hand[SH::P - 1][i] = first[i];
+  g.hn = (g.hn >> 3) | ((g.hn & 7u) << (3 * (SH::P - 1)));
+}
+
+// `uid` must be legal.  Returns the reward (score delta).  Ends with the seat rotation.
+template <class SH>
+__device__ __forceinline__ int apply_move(Game<SH>& g, int uid, const uint8_t* __restrict__ deck) {
+  constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R;
   const int before = g.score();
   if (g.deck_pos >= SH::DECK) --g.ttp;          // evaluated BEFORE the move
-  const int me = g.cur;
-  uint32_t last = 1u | ((uint32_t)me << 1) | ((uint32_t)uid << 4);
-  if (uid < 2 * SH::H) {
-    const bool is_play = uid >= SH::H;
-    const int idx = is_play ? uid - SH::H : uid;
-    const int card = slot_card(__shfl_sync(kFull, g.slot, me * SH::H + idx));
-    const int c = card / SH::R, r = card - c * SH::R;
-    last |= ((uint32_t)c << 10) | ((uint32_t)r << 13);
+  uint32_t last = 1u | ((uint32_t)uid << 1);
+  if (uid < 2 * H) {
+    const bool is_play = uid >= H;
+    const int idx = is_play ? uid - H : uid;
+    uint32_t w = 0;
+#pragma unroll
+    for (int i = 0; i < H; ++i)
+      if (i == idx) w = g.hand[0][i];
+    const int card = slot_card(w);
+    const int c = card_color(card), r = card_rank(card);
+    last |= (uint32_t)card << 7;
     bool to_discard = true;
     if (!is_play) {
-      if (g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 17; }
+      if (g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 13; }   // IncrementInformationTokens
     } else if (r == g.firework(c)) {             // AddToFireworks
       g.fw += 1u << (3 * c);
-      last |= 1u << 16;
+      last |= 1u << 12;
       to_discard = false;
-      if (g.firework(c) == SH::R && g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 17; }
+      if (r + 1 == R && g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 13; }
     } else {
       --g.life;
     }
     if (to_discard) g.disc += 1ull << (2 * card);
     // RemoveFromHand: later cards (and their knowledge) shift down
-    const uint32_t up = __shfl_down_sync(kFull, g.slot, 1);
-    const int p = lane / SH::H, i = lane - p * SH::H;
-    if (lane < SH::S && p == me && i >= idx) g.slot = (i == SH::H - 1) ? 0u : up;
-    int n = g.hand_n(me) - 1;
-    // chance node: the only short hand is `me`; the new card goes to the END of the hand
+#pragma unroll
+    for (int i = 0; i < H - 1; ++i)
+      if (i >= idx) g.hand[0][i] = g.hand[0][i + 1];
+    g.hand[0][H - 1] = 0;
+    int n = g.hand_n(0) - 1;
+    // chance node: the only short hand is the mover's; the new card goes to the END of it
     if (g.deck_pos < SH::DECK) {
-      const int nc = deck[g.deck_pos++];
-      if (lane == me * SH::H + n) g.slot = fresh_slot<SH>(nc);
+      const uint32_t fresh = fresh_slot<SH>(deck[g.deck_pos++]);
+#pragma unroll
+      for (int i = 0; i < H; ++i)
+        if (i == n) g.hand[0][i] = fresh;
       ++n;
     }
-    g.hn = (g.hn & ~(7u << (3 * me))) | ((uint32_t)n << (3 * me));
+    g.hn = (g.hn & ~7u) | (uint32_t)n;
   } else {
     --g.info;
-    int u = uid - 2 * SH::H;
-    const bool by_color = u < (SH::P - 1) * SH::C;
-    if (!by_color) u -= (SH::P - 1) * SH::C;
-    const int span = by_color ? SH::C : SH::R;
+    int u = uid - 2 * H;
+    const bool by_color = u < (P - 1) * C;
+    if (!by_color) u -= (P - 1) * C;
+    const int span = by_color ? C : R;
     const int k = 1 + u / span, v = u - (k - 1) * span;
-    int t = me + k;
-    if (t >= SH::P) t -= SH::P;
-    bool match = false;
-    if (lane < SH::S && slot_valid(g.slot) && lane / SH::H == t) {
-      const int card = slot_card(g.slot);
-      const int c = card / SH::R, r = card - c * SH::R;
-      if (by_color) {                            // HanabiHand::RevealColor
-        match = (c == v);
-        if (match) g.slot = (g.slot & ~(31u << 5)) | (1u << (5 + v)) | (1u << 15);
-        else g.slot &= ~(1u << (5 + v));
-      } else {                                   // HanabiHand::RevealRank
-        match = (r == v);
-        if (match) g.slot = (g.slot & ~(31u << 10)) | (1u << (10 + v)) | (1u << 16);
-        else g.slot &= ~(1u << (10 + v));
+    // HanabiHand::RevealColor / RevealRank: matching cards keep only the hinted cells and get
+    // the hinted flag; the others lose those cells
+    const uint32_t cells = by_color ? color_cells(v) : rank_cells(v);
+    const uint32_t flag = by_color ? (1u << 25) : (1u << 26);
+    uint32_t mask = 0;
+#pragma unroll
+    for (int kk = 1; kk < P; ++kk)
+#pragma unroll
+      for (int i = 0; i < H; ++i) {
+        const uint32_t w = g.hand[kk][i];
+        const int card = slot_card(w);
+        const bool match = (by_color ? card_color(card) : card_rank(card)) == v;
+        if (kk == k && slot_valid(w)) {
+          g.hand[kk][i] = match ? ((w & (cells | ~kGridMask)) | flag) : (w & ~cells);
+          if (match) mask |= 1u << i;
+        }
       }
-    }
-    const uint32_t mask = (__ballot_sync(kFull, match) >> (t * SH::H)) & ((1u << SH::H) - 1);
-    last |= mask << 18;
+    last |= mask << 14;
   }
   g.last = last;
-  g.cur = me + 1 == SH::P ? 0 : me + 1;
+  // AdvanceToNextPlayer: the next player becomes seat 0
+  g.cur = g.cur + 1 == P ? 0 : g.cur + 1;
+  rotate_once(g);
   return g.score() - before;
+}
+
+// View from another seat: rotate a copy so that seat `offset` becomes hand[0].
+template <class SH>
+__device__ __forceinline__ void rotate_seats(Game<SH>& g, int offset) {
+#pragma unroll
+  for (int step = 0; step + 1 < SH::P; ++step)
+    if (step < offset) rotate_once(g);
 }
 
 }  // namespace hbg

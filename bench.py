@@ -280,7 +280,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=128)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--games", type=int, default=GAMES_PER_GPU)
-    ap.add_argument("--fuse", type=int, default=32, help="env steps fused per launch")
+    ap.add_argument("--fuse", type=int, default=64, help="env steps fused per launch")
     ap.add_argument("--e2e-steps", type=int, default=64)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     args = ap.parse_args()

@@ -31,16 +31,20 @@ __device__ __forceinline__ long long game_index() {
   return (long long)blockIdx.x * kThreads + threadIdx.x;
 }
 
+// Writes the step outputs of one game; returns the legal-move mask of the player to move.
 template <class SH>
-__device__ __forceinline__ void emit(const Game<SH>& g, long long row, uint32_t* __restrict__ obs,
-                                     uint32_t* __restrict__ legal, uint8_t* __restrict__ step_type) {
+__device__ __forceinline__ unsigned long long emit(const Game<SH>& g, long long row,
+                                                   uint32_t* __restrict__ obs,
+                                                   uint32_t* __restrict__ legal,
+                                                   uint8_t* __restrict__ step_type) {
   if (obs != nullptr) encode_obs(g, SH::P - 1, obs + row * SH::kObsStride);
+  const unsigned long long m = legal_mask(g);
   if (legal != nullptr) {
-    const unsigned long long m = legal_mask(g);
     legal[row * SH::kLegalWords] = (uint32_t)m;
     if (SH::kLegalWords > 1) legal[row * SH::kLegalWords + 1] = (uint32_t)(m >> 32);
   }
   if (step_type != nullptr) step_type[row] = (uint8_t)g.step_type;
+  return m;
 }
 
 template <class SH>
@@ -63,15 +67,14 @@ env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict_
 template <class SH>
 __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
                                            const uint8_t*& deck, long long game, int action,
-                                           unsigned long long* illegal) {
+                                           unsigned long long lm, unsigned long long* illegal) {
   if (g.step_type == LAST) {
     ++g.episode;
     deck = deck_of<SH>(rt, decks, game, g.episode);
     reset_game(g, deck);
     return 0.0f;
   }
-  const unsigned long long lm = legal_mask(g);
-  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {
+  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {   // lm: legal moves of g
     atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and leave the game as it is
     return 0.0f;
   }
@@ -91,7 +94,7 @@ env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   Game<SH> g;
   load_game(g, state, game);
   const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
-  const float r = step_game(g, rt, decks, deck, game, action[game], illegal);
+  const float r = step_game(g, rt, decks, deck, game, action[game], legal_mask(g), illegal);
   if (reward != nullptr) reward[game] = r;
   emit(g, game, obs, legal, step_type);
   store_game(g, state, game);
@@ -138,37 +141,47 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
 // held in registers; only the per-step outputs touch HBM.  Output row (t, game).
 template <class SH>
-__global__ void __launch_bounds__(kThreads)
+__global__ void __launch_bounds__(kThreads, 7)
 selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks, RuleSet rs,
                 unsigned long long step0, int n_steps, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
-  __shared__ unsigned int s_hist[kMaxRules + 1];
-  if (threadIdx.x <= kMaxRules) s_hist[threadIdx.x] = 0;
-  __syncthreads();
   const long long game = game_index();
-  if (game < rt.n_games) {
-    Game<SH> g;
-    load_game(g, state, game);
-    const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
+  unsigned long long lm = legal_mask(g);
+  // rule-hit histogram: 8-bit counters packed in two registers (the host keeps n_steps <= 255)
+  unsigned long long cnt_lo = 0, cnt_hi = 0, cnt_fb = 0;
 #pragma unroll 1
-    for (int t = 0; t < n_steps; ++t) {
-      int a = 0, hit = -1;
-      if (g.step_type != LAST)
-        a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
-      const float r = step_game(g, rt, decks, deck, game, a, illegal);
-      const long long row = (long long)t * rt.n_games + game;
-      if (action != nullptr) action[row] = a;
-      if (reward != nullptr) reward[row] = r;
-      if (hit >= 0) atomicAdd(&s_hist[hit], 1u);
-      emit(g, row, obs, legal, step_type);
+  for (int t = 0; t < n_steps; ++t) {
+    int a = 0, hit = -1;
+    if (g.step_type != LAST)
+      a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
+    const float r = step_game(g, rt, decks, deck, game, a, lm, illegal);
+    const long long row = (long long)t * rt.n_games + game;
+    if (action != nullptr) action[row] = a;
+    if (reward != nullptr) reward[row] = r;
+    if (hit >= 0) {
+      if (hit < 8) cnt_lo += 1ull << (8 * hit);
+      else if (hit < 16) cnt_hi += 1ull << (8 * (hit - 8));
+      else ++cnt_fb;
     }
-    store_game(g, state, game);
+    lm = emit(g, row, obs, legal, step_type);
   }
-  __syncthreads();
-  if (hist != nullptr && threadIdx.x <= rs.n && s_hist[threadIdx.x])
-    atomicAdd(&hist[threadIdx.x], (unsigned long long)s_hist[threadIdx.x]);
+  store_game(g, state, game);
+  if (hist != nullptr) {
+#pragma unroll 1
+    for (int k = 0; k <= rs.n; ++k) {
+      unsigned int c = k < 8 ? (unsigned int)(cnt_lo >> (8 * k)) & 255u
+                             : (k < 16 ? (unsigned int)(cnt_hi >> (8 * (k - 8))) & 255u
+                                       : (unsigned int)cnt_fb);
+      c = __reduce_add_sync(__activemask(), c);
+      if ((threadIdx.x & 31) == 0 && c) atomicAdd(&hist[k], (unsigned long long)c);
+    }
+  }
 }
 
 // canonical int32 dump, one thread per game, ABSOLUTE player order (tests; layout = oracle
@@ -538,7 +551,7 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                     const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step0, int n_steps,
                     uint32_t* d_obs, uint32_t* d_legal, float* d_reward, uint8_t* d_step_type,
                     int32_t* d_action, uint64_t* d_hist, void* stream) {
-  HB_REQUIRE(e && n_steps >= 1, "hb_env_selfplay: bad arguments");
+  HB_REQUIRE(e && n_steps >= 1 && n_steps <= 255, "hb_env_selfplay: n_steps must be 1..255");
   if (!e->is_reset) { hb::set_error("hb_env_selfplay: reset the environment first"); return HB_ERR_STATE; }
   RuleSet rs;
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);

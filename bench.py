@@ -18,7 +18,6 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -42,44 +41,68 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe)."""
+    """nvidia-smi clocks / throttle reasons DURING the timed region (profiling recipe): one
+    `nvidia-smi -lms` process started before the region and stopped after it."""
     Q = ("index,clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, index):
-        self.index, self.rows, self.stop, self.t = index, [], threading.Event(), None
-
-    def _run(self):
-        while not self.stop.is_set():
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True,
-                                     text=True, timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([x.strip() for x in out.split(",")])
-            except Exception:
-                pass
-            self.stop.wait(0.2)
+    def __init__(self, index, period_ms=20):
+        self.index, self.period, self.proc, self.rows = index, period_ms, None, []
+        self.t0 = self.t1 = None
 
     def __enter__(self):
-        self.t = threading.Thread(target=self._run, daemon=True)
-        self.t.start()
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=timestamp," + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", str(self.period)],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            time.sleep(0.3)          # let the first samples arrive before the region starts
+        except Exception:
+            self.proc = None
         return self
 
+    def mark_start(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
     def __exit__(self, *a):
-        self.stop.set()
-        self.t.join(timeout=6)
+        if self.proc is None:
+            return
+        time.sleep(2.5 * self.period / 1e3)
+        self.proc.terminate()
+        try:
+            out, _ = self.proc.communicate(timeout=5)
+        except Exception:
+            self.proc.kill()
+            out = ""
+        import datetime
+        for line in out.splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+            except Exception:
+                ts = None
+            self.rows.append((ts, f[1:]))
 
     def summary(self):
-        if not self.rows:
+        rows = [r for ts, r in self.rows
+                if ts is None or self.t0 is None or (self.t0 - 0.05 <= ts <= self.t1 + 0.05)]
+        if not rows:
+            rows = [r for _, r in self.rows[-3:]]
+        if not rows:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": [], "samples": 0}
-        sm = sorted(float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit())
-        mx = max(float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit())
+        num = lambda x: x.replace(".", "").isdigit()  # noqa: E731
+        sm = sorted(float(r[1]) for r in rows if num(r[1]))
+        mx = max([float(r[2]) for r in rows if num(r[2])] or [0.0])
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in self.rows)]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(rows)}
 
 
 def cpu_port_throughput(n_games, seconds, threads, steps_cap=None, warm=2):
@@ -171,11 +194,13 @@ def run_ours(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         barrier()
+        clocks.mark_start()
         ev0.record()
         for k in chunks:
             launch(k)
         ev1.record()
         barrier()
+        clocks.mark_end()
     ms = ev0.elapsed_time(ev1)
     t = torch.tensor([ms], device=dev)
     if world > 1:
@@ -276,7 +301,7 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4096)
+    ap.add_argument("--steps", type=int, default=65536)
     ap.add_argument("--warmup", type=int, default=128)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--games", type=int, default=GAMES_PER_GPU)

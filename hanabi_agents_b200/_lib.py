@@ -64,6 +64,9 @@ SIGNATURES = {
     # rule-based agents
     "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
     "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),
+    # q-network
+    "hb_gemm_f16": (i32, [vp, i64, vp, i64, i32, i32, i32, i32, f32, vp, i32, vp, i64, vp, i64, vp,
+                          i32, f32, f32, f32, vp]),
 }
 
 

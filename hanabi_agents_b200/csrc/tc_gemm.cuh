@@ -1,0 +1,378 @@
+// tcgen05 / TMA GEMM tile for the Q-network (sm_100a only).
+//
+//   D[M, N] = A[M, K] . B[N, K]^T      A, B fp16, both K-major (row-major with K contiguous),
+//                                      fp32 accumulation in tensor memory.
+//
+// One CTA computes one 128 x 128 tile of D:
+//   warp 0     TMA producer: cp.async.bulk.tensor boxes of 128 rows x 64 fp16 (= one 128-byte
+//              swizzle span) for A and B into a kStages-deep shared-memory ring
+//   warp 1     MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::f16 (M128 N128 K16),
+//              four per k-block, accumulating into 128 TMEM columns; tcgen05.commit releases the
+//              ring slot / signals the epilogue
+//   warp 2     allocates / frees tensor memory
+//   warps 4-7  epilogue: tcgen05.ld 32 lanes x 32 columns at a time, fused bias / ReLU / gate /
+//              categorical head, vectorised global stores
+// Two CTAs fit one SM (3 stages x 32 KB each, 128 of 512 TMEM columns each), so one CTA's
+// epilogue overlaps the other's main loop.
+//
+// Replaces the jnp.dot calls of NoisyLinear (hanabi_agents/rlax_dqn/noisy_mlp.py:62,80) and their
+// jax.grad transposes (rlax_rainbow.py:203-213).
+#pragma once
+#include <cuda.h>
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace tc {
+
+constexpr int BM = 128, BN = 128, BK = 64;        // CTA tile; BK fp16 = 128 B = swizzle span
+constexpr int UMMA_K = 16;
+constexpr int kStages = 3;
+constexpr int kStageBytes = (BM + BN) * BK * 2;   // 32 KB
+constexpr int kTmemCols = 128;
+constexpr int kThreads = 256;
+constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+
+enum Epilogue {
+  EPI_F16 = 0,   // out16[m, n] = act(alpha * acc + bias[n]) (* gate(m, n) > 0), optional transposed copy
+  EPI_F32 = 1,   // out32[m, n] = alpha * acc + bias[n] (+ beta * out32[m, n])
+  EPI_C51 = 2,   // categorical head: columns are [action][64] (51 atoms + pad):
+                 //   logits32[m, n] (optional), q[m, a] = mean_j softmax_j(acc + bias) * z_j
+};
+
+struct EpiParams {
+  int M, N;                  // valid rows / columns of D
+  float alpha;
+  float beta;                // EPI_F32 only: accumulate into existing out32
+  const float* bias;         // [N] or nullptr
+  int relu;                  // EPI_F16: apply max(., 0)
+  const __half* gate;        // EPI_F16: multiply by (gate[m, n] > 0) (ReLU backward), or nullptr
+  int ld_gate;
+  __half* out16;             // EPI_F16: [M, ld_out]
+  __half* out16_t;           // EPI_F16: optional transposed copy [N, ld_out_t]
+  float* out32;              // EPI_F32 / EPI_C51 (logits, optional)
+  int ld_out, ld_out_t;
+  // EPI_C51
+  float* q;                  // [M, ld_q] expected value per action
+  int ld_q;
+  int n_atoms;               // 51
+  float z0, dz;              // atoms z_j = z0 + j * dz
+  float q_scale;             // 1/n_atoms (rlax_rainbow.py:118 uses mean) or 1 (sum)
+};
+
+// ---------------------------------------------------------------- PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+               "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+      "selp.b32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug must become a trap (an error the host sees), never a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > 4000000000ll) __trap();
+  }
+}
+__device__ __forceinline__ void fence_barrier_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar,
+                                            int x, int y) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes "
+      "[%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(x), "r"(y)
+      : "memory");
+}
+__device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
+  asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_dst, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                   smem_u32(smem_dst)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+               : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                         uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// tcgen05.commit: arrives on the mbarrier when all MMAs issued so far by this thread are done
+// (implies tcgen05.fence::before_thread_sync).
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                   smem_u32(bar))
+               : "memory");
+}
+// 32 lanes x 32 consecutive fp32 columns -> 32 registers per thread (thread = TMEM lane = D row)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+        "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+        "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+        "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+        "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// Shared-memory matrix descriptor, K-major, SWIZZLE_128B (cute::UMMA::SmemDescriptor):
+//   [13:0] start address >> 4, [29:16] leading byte offset >> 4 (unused for swizzled K-major),
+//   [45:32] stride byte offset >> 4 (8 rows x 128 B = 1024 B between 8-row groups),
+//   [47:46] version = 1 (Blackwell), [63:61] layout type 2 = SWIZZLE_128B.
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3fff);
+  d |= (uint64_t)1 << 16;
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// Instruction descriptor (cute::UMMA::InstrDescriptor), kind::f16: D fp32, A/B fp16, both K-major.
+__host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
+  return (1u << 4)                     // c_format = F32
+         | (0u << 7) | (0u << 10)      // a_format = b_format = F16
+         | (0u << 15) | (0u << 16)     // a_major = b_major = K
+         | ((uint32_t)(n >> 3) << 17)  // n_dim
+         | ((uint32_t)(m >> 4) << 24); // m_dim
+}
+
+// ---------------------------------------------------------------------- kernel ----
+template <int EPI>
+__global__ void __launch_bounds__(kThreads, 2)
+gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
+                int K, EpiParams ep) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
+  uint64_t* empty_bar = full_bar + kStages;
+  uint64_t* acc_bar = empty_bar + kStages;
+  uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
+  const int num_kb = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmap_a);
+    prefetch_tmap(&tmap_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < kStages; ++s) {
+      mbar_init(&full_bar[s], 1);
+      mbar_init(&empty_bar[s], 1);
+    }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t ph = (kb / kStages) & 1;
+        mbar_wait(&empty_bar[s], ph ^ 1);            // slot free (first pass: returns at once)
+        uint8_t* a_dst = smem + s * kStageBytes;
+        uint8_t* b_dst = a_dst + BM * BK * 2;
+        mbar_expect_tx(&full_bar[s], kStageBytes);
+        tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
+        tma_load_2d(b_dst, &tmap_b, &full_bar[s], kb * BK, n0);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_f16(BM, BN);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        const int s = kb % kStages;
+        const uint32_t ph = (kb / kStages) & 1;
+        mbar_wait(&full_bar[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
+        const uint32_t b_addr = a_addr + BM * BK * 2;
+#pragma unroll
+        for (int k = 0; k < BK / UMMA_K; ++k) {
+          const uint64_t adesc = make_smem_desc(a_addr + k * UMMA_K * 2);
+          const uint64_t bdesc = make_smem_desc(b_addr + k * UMMA_K * 2);
+          umma_f16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty_bar[s]);                  // frees the slot when these MMAs retire
+      }
+      umma_commit(acc_bar);                          // accumulator complete
+    }
+  } else if (warp >= 4) {
+    const int ew = warp - 4;                         // == warp % 4: the TMEM lane quarter it may read
+    mbar_wait(acc_bar, 0);
+    tc_fence_after();
+    const int m = m0 + ew * 32 + lane;
+    const bool row_ok = m < ep.M;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+    if (EPI == EPI_C51) {
+      // two actions per 128-column tile, 64 columns each (n_atoms real + pad)
+#pragma unroll 1
+      for (int h = 0; h < 2; ++h) {
+        uint32_t v0[32], v1[32];
+        tmem_ld32(lane_addr + h * 64, v0);
+        tmem_ld32(lane_addr + h * 64 + 32, v1);
+        const int nb = n0 + h * 64;
+        if (nb >= ep.N) continue;
+        float x[64];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          x[j] = ep.alpha * __uint_as_float(v0[j]) + (ep.bias ? __ldg(ep.bias + nb + j) : 0.f);
+          x[32 + j] = ep.alpha * __uint_as_float(v1[j]) + (ep.bias ? __ldg(ep.bias + nb + 32 + j) : 0.f);
+        }
+        if (row_ok && ep.out32 != nullptr) {
+          float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) dst[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+        }
+        if (row_ok && ep.q != nullptr) {
+          float mx = -INFINITY;
+#pragma unroll
+          for (int j = 0; j < 64; ++j)
+            if (j < ep.n_atoms) mx = fmaxf(mx, x[j]);
+          float den = 0.f, num = 0.f;
+#pragma unroll
+          for (int j = 0; j < 64; ++j)
+            if (j < ep.n_atoms) {
+              const float e = __expf(x[j] - mx);
+              den += e;
+              num += e * (ep.z0 + j * ep.dz);
+            }
+          ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
+        }
+      }
+    } else {
+#pragma unroll 1
+      for (int c = 0; c < BN / 32; ++c) {
+        uint32_t v[32];
+        tmem_ld32(lane_addr + c * 32, v);
+        const int nb = n0 + c * 32;
+        if (nb >= ep.N) continue;                    // warp-uniform
+        float x[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float t = ep.alpha * __uint_as_float(v[j]);
+          if (ep.bias != nullptr && nb + j < ep.N) t += __ldg(ep.bias + nb + j);
+          x[j] = t;
+        }
+        if (EPI == EPI_F16) {
+          if (ep.relu) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+          }
+          if (ep.gate != nullptr && row_ok) {
+            const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + nb);
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4) {
+              if (nb + 8 * j4 < ep.N) {
+                const uint4 gv = __ldg(g + j4);
+                const __half2* gh = reinterpret_cast<const __half2*>(&gv);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                  const float2 f = __half22float2(gh[j]);
+                  if (!(f.x > 0.f)) x[8 * j4 + 2 * j] = 0.f;
+                  if (!(f.y > 0.f)) x[8 * j4 + 2 * j + 1] = 0.f;
+                }
+              }
+            }
+          }
+          uint32_t p[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
+            p[j] = *reinterpret_cast<const uint32_t*>(&h2);
+          }
+          if (row_ok && ep.out16 != nullptr) {
+            uint4* dst = reinterpret_cast<uint4*>(ep.out16 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4)
+              if (nb + 8 * j4 < ep.N) dst[j4] = make_uint4(p[4 * j4], p[4 * j4 + 1], p[4 * j4 + 2], p[4 * j4 + 3]);
+          }
+          if (ep.out16_t != nullptr && row_ok) {
+            // transposed copy: for a fixed column the warp's 32 rows are contiguous
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (nb + j < ep.N)
+                ep.out16_t[(size_t)(nb + j) * ep.ld_out_t + m] = __float2half_rn(x[j]);
+          }
+        } else {  // EPI_F32
+          if (row_ok) {
+            float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+            for (int j4 = 0; j4 < 8; ++j4) {
+              if (nb + 4 * j4 < ep.N) {
+                float4 o = make_float4(x[4 * j4], x[4 * j4 + 1], x[4 * j4 + 2], x[4 * j4 + 3]);
+                if (ep.beta != 0.f) {
+                  const float4 old = dst[j4];
+                  o.x += ep.beta * old.x; o.y += ep.beta * old.y;
+                  o.z += ep.beta * old.z; o.w += ep.beta * old.w;
+                }
+                dst[j4] = o;
+              }
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+}  // namespace tc

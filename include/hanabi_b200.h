@@ -163,6 +163,25 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
 
 /* @@REPLAY@@ */
 
+/* ------------------------------------------------------------------------ */
+/* Q-network: NoisyMLP / MLP forward and backward, policy, learner step.      */
+/* Replaces jnp.dot in NoisyLinear (hanabi_agents/rlax_dqn/noisy_mlp.py:62,80),*/
+/* DQNPolicy.policy / eval_policy (rlax_rainbow.py:93-150), DQNLearning.       */
+/* update_q (rlax_rainbow.py:154-217, rlax_dqn.py:144-233) and optix.adam      */
+/* (rlax_rainbow.py:257).                                                      */
+/* ------------------------------------------------------------------------ */
+/* One tcgen05/TMA GEMM tile launch (tests, microbenchmarks):
+ * D = epilogue(alpha * A . B^T + bias); A [M, K], B [N, K] fp16 row-major DEVICE matrices.
+ * mode 0: fp16 out [M, ld_out] (+ReLU when relu != 0, + transposed copy d_out_t [N, ld_out_t]);
+ * mode 1: fp32 out; mode 2: categorical head -- columns are [action][64] (n_atoms used),
+ * d_out = fp32 logits (may be NULL), d_q[M, N/64] = q_scale * sum_j softmax_j * (z0 + j*dz). */
+int hb_gemm_f16(const void* d_a, int64_t lda, const void* d_b, int64_t ldb, int M, int N, int K,
+                int mode, float alpha, const float* d_bias, int relu, void* d_out, int64_t ld_out,
+                void* d_out_t, int64_t ld_out_t, float* d_q, int n_atoms, float z0, float dz,
+                float q_scale, void* stream);
+
+/* @@QNET@@ */
+
 #ifdef __cplusplus
 }
 #endif

@@ -67,6 +67,18 @@ SIGNATURES = {
     # q-network
     "hb_gemm_f16": (i32, [vp, i64, vp, i64, i32, i32, i32, i32, f32, vp, i32, vp, i64, vp, i64, vp,
                           i32, f32, f32, f32, vp]),
+    "hb_net_create": (i32, [i32, i32, vp, i32, i32, i32, f32, i32, i32, C.POINTER(vp)]),
+    "hb_net_destroy": (i32, [vp]),
+    "hb_net_info": (i64, [vp, i32]),
+    "hb_net_grad": (vp, [vp]),
+    "hb_net_set_param": (i32, [vp, i32, i32, vp, i64]),
+    "hb_net_get_param": (i32, [vp, i32, i32, vp, i64]),
+    "hb_net_refresh": (i32, [vp, vp]),
+    "hb_net_sync_target": (i32, [vp, vp]),
+    "hb_net_act": (i32, [vp, vp, vp, i32, i64, i32, f32, vp, u64, u64, i64, i32, vp, vp, vp]),
+    "hb_net_forward": (i32, [vp, vp, i64, i32, vp, vp, vp]),
+    "hb_net_grads": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp]),
+    "hb_net_adam": (i32, [vp, f32, f32, f32, f32, f32, vp]),
 }
 
 

@@ -1,13 +1,542 @@
 // Q-network (NoisyMLP / MLP), policy and learner step on tcgen05 GEMM tiles, and their C ABI.
+//
+// Reference (path:line under /root/reference/hanabi_agents/rlax_dqn):
+//   NoisyLinear / NoisyMLP            noisy_mlp.py:49-91, 154-185
+//   DQNPolicy.policy / eval_policy    rlax_rainbow.py:34-150
+//   DQNLearning.update_q (C51)        rlax_rainbow.py:154-217
+//   DQNLearning.update_q (double-Q)   rlax_dqn.py:144-233
+//   optix.adam                        rlax_rainbow.py:257
+//
+// A noisy layer  y = x.w + b + x.(w_mu + w_sigma*eps_w) + (b_mu + b_sigma*eps_b)  has noise drawn
+// at trace time (constants), so it is ONE effective layer  W = w + w_mu + w_sigma*eps_w,
+// bias likewise; gradients fan out as dw = dw_mu = dW, dw_sigma = dW*eps_w.
+// Masters, Adam moments and gradients are fp32; the GEMM operands are the fp16 roundings of the
+// effective weights ([N, K] and its transpose) and fp16 activations, accumulated in fp32.
 #include "tc_host.cuh"
+#include <math.h>
 #include <new>
 #include <vector>
 
+namespace {
+
+constexpr int kMaxLayers = 6;
+constexpr int kActChunk = 131072;   // rows per acting pass (bounds the workspace)
+
+struct LayerGeo {
+  int in, out;          // logical sizes (haiku w: [in, out])
+  int K, N;             // GEMM sizes: K = padded in, N = padded / re-laid-out out
+  long long eoff;       // offset of [W (N*K) | b (N)] in the flat effective-parameter space
+  long long woff;       // offset of W in the fp16 weight arrays
+  long long boff;       // offset of b in the effective-bias array
+};
+
+struct LayerTable {      // kernel argument for the fused Adam / refresh kernel
+  int n_layers;
+  LayerGeo l[kMaxLayers];
+};
+
+}  // namespace
+
+struct hb_qnet {
+  int device = 0;
+  int obs_len = 0, obs_stride = 0;
+  int A = 0, n_atoms = 1, noisy = 1;
+  float vmax = 25.f;
+  int n_layers = 0;
+  LayerTable tab{};
+  long long n_eff = 0, n_w = 0, n_b = 0;
+  int kinds = 1;                       // master tensors per effective parameter (3 noisy, 1 plain)
+  float* master = nullptr;             // [kinds][n_eff]
+  float* eps = nullptr;                // [n_eff] noise constants (noisy)
+  float* adam_m = nullptr;             // [kinds][n_eff]
+  float* adam_v = nullptr;
+  float* grad = nullptr;               // [n_eff] flat gradient bucket
+  __half* w16 = nullptr;               // online effective weights [N, K] per layer
+  __half* w16t = nullptr;              // transposes [K, N]
+  float* beff = nullptr;               // effective biases
+  __half* t16 = nullptr;               // target snapshot
+  float* tbeff = nullptr;
+  long long adam_step = 0;
+  // acting workspace
+  long long act_rows = 0;
+  __half* act_x = nullptr;
+  __half* act_h[2] = {nullptr, nullptr};
+  float* act_q = nullptr;
+  // learner workspace (batch capacity lb)
+  int lb = 0, lbp = 0;
+  __half* x = nullptr;                 // [2B, K0]
+  __half* xt = nullptr;                // [K0, Bp]
+  __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
+  __half* ht[kMaxLayers] = {nullptr};  // transposed [N, 2Bp]
+  __half* th[kMaxLayers] = {nullptr};  // target hidden [B, N]
+  __half* dz[kMaxLayers] = {nullptr};  // dL/d(pre-activation) [B, N]
+  __half* dzt[kMaxLayers] = {nullptr}; // transposed [N, Bp]
+  float* logits = nullptr;             // online head [2B, N_last]
+  float* q_on = nullptr;               // [2B, ldq]
+  float* tlogits = nullptr;            // target head [B, N_last]
+  float* w_is = nullptr;               // [B]
+  float* loss_b = nullptr;             // [B] per-sample loss / td
+  float* scalars = nullptr;            // [4]: mean loss, max weight, ...
+};
+
+namespace {
+
+int ceil_to(int x, int m) { return (x + m - 1) / m * m; }
+
+// ----------------------------------------------------------------- kernels ----
+// bit-packed rows -> fp16 0/1 rows (and, optionally, the transposed copy of the first rows_t rows)
+__global__ void unpack_rows_kernel(const uint32_t* __restrict__ packed, int stride, long long rows,
+                                   __half* __restrict__ out, int ld, __half* __restrict__ out_t,
+                                   int ld_t, long long rows_t) {
+  const long long total = rows * stride;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long r = i / stride;
+    const int w = (int)(i - r * stride);
+    const uint32_t bits = __ldg(packed + i);
+    uint32_t p[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      const uint32_t lo = (bits >> (2 * j)) & 1u, hi = (bits >> (2 * j + 1)) & 1u;
+      p[j] = (lo ? 0x3c00u : 0u) | (hi ? 0x3c000000u : 0u);   // half(1.0) = 0x3c00
+    }
+    uint4* dst = reinterpret_cast<uint4*>(out + r * ld + w * 32);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dst[j] = make_uint4(p[4 * j], p[4 * j + 1], p[4 * j + 2], p[4 * j + 3]);
+    if (out_t != nullptr && r < rows_t) {
+#pragma unroll 4
+      for (int j = 0; j < 32; ++j)
+        out_t[(long long)(w * 32 + j) * ld_t + r] = __ushort_as_half(((bits >> j) & 1u) ? 0x3c00 : 0);
+    }
+  }
+}
+
+__device__ __forceinline__ float uniform_from(unsigned long long seed, unsigned long long ctr,
+                                              unsigned long long row) {
+  unsigned long long x = seed + 0x9E3779B97F4A7C15ull * (row + 1);
+  x ^= ctr * 0xBF58476D1CE4E5B9ull;
+  x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
+  x ^= x >> 27; x *= 0x94D049BB133111EBull;
+  x ^= x >> 31;
+  return (float)(x >> 40) * (1.0f / 16777216.0f);   // [0, 1)
+}
+
+// DQNPolicy.policy / eval_policy after the network (rlax_rainbow.py:34-59,119-123,146-150):
+//   q = where(legal, q, -inf); greedy probs = ties of the row max split evenly;
+//   explore: probs = (1-eps)*greedy + eps*legal/num_legal; cpi = cumsum(probs), cpi[-1] = 1;
+//            action = first a with not (u > cpi[a]), u in [0, 0.999)
+//   exploit: rlax.greedy().sample = uniform among the maxima
+__global__ void policy_kernel(const float* __restrict__ q, int ldq, const uint32_t* __restrict__ legal,
+                              int legal_words, int A, long long n, int greedy, float epsilon,
+                              const float* __restrict__ uniform, unsigned long long seed,
+                              unsigned long long ctr, long long row0, int32_t* __restrict__ action,
+                              float* __restrict__ q_out) {
+  const long long r = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= n) return;
+  const float* qr = q + r * ldq;
+  unsigned long long lm = legal[r * legal_words];
+  if (legal_words > 1) lm |= (unsigned long long)legal[r * legal_words + 1] << 32;
+  float mx = -INFINITY;
+  int num_legal = 0;
+  for (int a = 0; a < A; ++a) {
+    const bool ok = (lm >> a) & 1ull;
+    const float v = ok ? qr[a] : -INFINITY;
+    if (q_out != nullptr) q_out[r * A + a] = v;
+    mx = fmaxf(mx, v);
+    num_legal += ok ? 1 : 0;
+  }
+  int n_max = 0;
+  for (int a = 0; a < A; ++a) {
+    const float v = ((lm >> a) & 1ull) ? qr[a] : -INFINITY;
+    n_max += (v == mx) ? 1 : 0;       // with no legal move every entry is -inf == max, as in jnp
+  }
+  float u = uniform != nullptr ? uniform[r] : uniform_from(seed, ctr, (unsigned long long)(row0 + r));
+  int act = 0;
+  if (greedy) {
+    // uniform among the n_max maxima
+    int pick = min((int)(u * (float)n_max), n_max - 1), seen = 0;
+    for (int a = 0; a < A; ++a) {
+      const float v = ((lm >> a) & 1ull) ? qr[a] : -INFINITY;
+      if (v == mx) {
+        if (seen == pick) { act = a; break; }
+        ++seen;
+      }
+    }
+  } else {
+    if (uniform == nullptr) u *= 0.999f;   // jax.random.uniform(maxval=0.999)
+    const float pg = 1.0f / (float)n_max;
+    const float pu = 1.0f / (float)num_legal;   // inf when no legal move, as legal / 0 in jnp
+    float c = 0.f;
+    act = A - 1;                                 // cpi[:, -1] = 1 and u < 1
+    for (int a = 0; a < A - 1; ++a) {
+      const bool ok = (lm >> a) & 1ull;
+      const float v = ok ? qr[a] : -INFINITY;
+      // separate roundings as in the reference's elementwise ops (no fused multiply-add)
+      const float p = __fadd_rn(__fmul_rn(1.0f - epsilon, (v == mx) ? pg : 0.f),
+                                __fmul_rn(epsilon, ok ? pu : 0.f));
+      c = __fadd_rn(c, p);
+      if (!(u > c)) { act = a; break; }
+    }
+  }
+  action[r] = act;
+}
+
+// weights_is = (1/prios)^beta / max(.)   rlax_rainbow.py:188-189 (fp32)
+__global__ void is_weights_kernel(const float* __restrict__ prios, int B, float beta,
+                                  float* __restrict__ w) {
+  __shared__ float red[32];
+  float mx = 0.f;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float v = powf(1.0f / prios[i], beta);
+    w[i] = v;
+    mx = fmaxf(mx, v);
+  }
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    mx = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (threadIdx.x == 0) red[0] = mx;
+  }
+  __syncthreads();
+  mx = red[0];
+  for (int i = threadIdx.x; i < B; i += blockDim.x) w[i] = w[i] / mx;
+}
+
+// One warp per sample.  rlax.categorical_double_q_learning (rlax_rainbow.py:172-184):
+//   a* = argmax_a q_sel;  p = softmax(target_logits[a*]);  target_z = r + gamma * z;
+//   m = categorical_l2_project(target_z, p, z);  loss = -sum_i m_i log_softmax(logits_tm1[a])_i
+// Writes loss_b and dL/dlogits * B / w-normalisation folded later:  dz[b, a*64+i] = w_b (p_i S - m_i).
+__global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const float* __restrict__ q_sel,
+                                int ldq, const float* __restrict__ tlogits, int ldl,
+                                const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
+                                const uint8_t* __restrict__ term_t, int mask_terminal,
+                                const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
+                                float gamma, __half* __restrict__ dz, __half* __restrict__ dzt,
+                                int ld_dzt, float* __restrict__ loss_b) {
+  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (b >= B) return;
+  const unsigned full = 0xffffffffu;
+  // a* = first maximum of q_sel[b, :]  (jnp.argmax)
+  float best = -INFINITY;
+  int besta = 0x7fffffff;
+  for (int a = lane; a < A; a += 32) {
+    const float v = q_sel[(long long)b * ldq + a];
+    if (v > best) { best = v; besta = a; }
+  }
+  for (int o = 16; o; o >>= 1) {
+    const float ov = __shfl_xor_sync(full, best, o);
+    const int oa = __shfl_xor_sync(full, besta, o);
+    if (ov > best || (ov == best && oa < besta)) { best = ov; besta = oa; }
+  }
+  const int astar = besta == 0x7fffffff ? 0 : besta;
+  const float vmin = -vmax, dzv = 2.0f * vmax / (float)(n_atoms - 1);
+  const int i0 = lane, i1 = lane + 32;
+  // target distribution p_j
+  const float* tl = tlogits + (long long)b * ldl + astar * 64;
+  const float t0 = i0 < n_atoms ? tl[i0] : -INFINITY, t1 = i1 < n_atoms ? tl[i1] : -INFINITY;
+  float mx = fmaxf(t0, t1);
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(full, mx, o));
+  float e0 = i0 < n_atoms ? expf(t0 - mx) : 0.f, e1 = i1 < n_atoms ? expf(t1 - mx) : 0.f;
+  float den = e0 + e1;
+  for (int o = 16; o; o >>= 1) den += __shfl_xor_sync(full, den, o);
+  const float p0 = e0 / den, p1 = e1 / den;
+  // projection onto the fixed support: m_i = sum_j clip(1 - |clip(tz_j) - z_i| / dz, 0, 1) p_j
+  const float r = r_t[b];
+  const float g = (mask_terminal && term_t != nullptr && term_t[b]) ? 0.f : gamma;
+  const float zi0 = vmin + dzv * (float)i0, zi1 = vmin + dzv * (float)i1;
+  float m0 = 0.f, m1 = 0.f;
+  for (int j = 0; j < n_atoms; ++j) {
+    const float pj = __shfl_sync(full, j < 32 ? p0 : p1, j & 31);
+    float tz = r + g * (vmin + dzv * (float)j);
+    tz = fminf(fmaxf(tz, vmin), vmax);
+    m0 += fminf(fmaxf(1.0f - fabsf(tz - zi0) / dzv, 0.f), 1.f) * pj;
+    m1 += fminf(fmaxf(1.0f - fabsf(tz - zi1) / dzv, 0.f), 1.f) * pj;
+  }
+  if (i0 >= n_atoms) m0 = 0.f;
+  if (i1 >= n_atoms) m1 = 0.f;
+  // log-softmax of the online logits of the action taken
+  const int a = a_tm1[b];
+  const float* ol = logits_tm1 + (long long)b * ldl + a * 64;
+  const float l0 = i0 < n_atoms ? ol[i0] : -INFINITY, l1 = i1 < n_atoms ? ol[i1] : -INFINITY;
+  float lmx = fmaxf(l0, l1);
+  for (int o = 16; o; o >>= 1) lmx = fmaxf(lmx, __shfl_xor_sync(full, lmx, o));
+  const float f0 = i0 < n_atoms ? expf(l0 - lmx) : 0.f, f1 = i1 < n_atoms ? expf(l1 - lmx) : 0.f;
+  float lden = f0 + f1;
+  for (int o = 16; o; o >>= 1) lden += __shfl_xor_sync(full, lden, o);
+  const float lse = lmx + logf(lden);
+  float part = (i0 < n_atoms ? m0 * (l0 - lse) : 0.f) + (i1 < n_atoms ? m1 * (l1 - lse) : 0.f);
+  float S = m0 + m1;
+  for (int o = 16; o; o >>= 1) {
+    part += __shfl_xor_sync(full, part, o);
+    S += __shfl_xor_sync(full, S, o);
+  }
+  if (lane == 0) loss_b[b] = -part;
+  const float w = w_is[b];
+  const float d0 = w * (f0 / lden * S - m0), d1 = w * (f1 / lden * S - m1);
+  const long long col = (long long)a * 64;
+  if (i0 < n_atoms) {
+    dz[(long long)b * ldl + col + i0] = __float2half_rn(d0);
+    dzt[(col + i0) * ld_dzt + b] = __float2half_rn(d0);
+  }
+  if (i1 < n_atoms) {
+    dz[(long long)b * ldl + col + i1] = __float2half_rn(d1);
+    dzt[(col + i1) * ld_dzt + b] = __float2half_rn(d1);
+  }
+}
+
+// rlax.double_q_learning + l2 loss (rlax_dqn.py:170-205): td = r + gamma * q_t[argmax q_sel] - q_tm1[a],
+// q_t zeroed on terminal; L = mean(w * 0.5 td^2)  ->  dz[b, a] = -w_b td_b.  One thread per sample.
+__global__ void dqn_loss_kernel(const float* __restrict__ q_on, int ldq, const float* __restrict__ q_t,
+                                const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
+                                const uint8_t* __restrict__ term_t, const float* __restrict__ w_is,
+                                int B, int A, float gamma, __half* __restrict__ dz, int ld_dz,
+                                __half* __restrict__ dzt, int ld_dzt, float* __restrict__ td_out) {
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= B) return;
+  const float* qs = q_on + (long long)(B + b) * ldq;     // online(obs_t)
+  int astar = 0;
+  float best = qs[0];
+  for (int a = 1; a < A; ++a)
+    if (qs[a] > best) { best = qs[a]; astar = a; }
+  const bool term = term_t != nullptr && term_t[b];
+  const float qt = term ? 0.f : q_t[(long long)b * ldq + astar];
+  const int a = a_tm1[b];
+  const float td = r_t[b] + gamma * qt - q_on[(long long)b * ldq + a];
+  td_out[b] = td;
+  const __half d = __float2half_rn(-w_is[b] * td);
+  dz[(long long)b * ld_dz + a] = d;
+  dzt[(long long)a * ld_dzt + b] = d;
+}
+
+// mean(loss_b * w) in a fixed order (one block, tree over fixed strides)
+__global__ void mean_loss_kernel(const float* __restrict__ loss_b, const float* __restrict__ w, int B,
+                                 int squared_half, float* __restrict__ out) {
+  __shared__ float red[256];
+  float s = 0.f;
+  for (int i = threadIdx.x; i < B; i += blockDim.x) {
+    const float l = squared_half ? 0.5f * loss_b[i] * loss_b[i] : loss_b[i];
+    s += l * w[i];
+  }
+  red[threadIdx.x] = s;
+  __syncthreads();
+  for (int o = blockDim.x >> 1; o; o >>= 1) {
+    if (threadIdx.x < o) red[threadIdx.x] += red[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) out[0] = red[0] / (float)B;
+}
+
+// gb[n] = alpha * sum_b zt[n, b]   (one warp per output unit, fixed order)
+__global__ void bias_grad_kernel(const __half* __restrict__ zt, int ld, int N, int B, float alpha,
+                                 float* __restrict__ gb) {
+  const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (n >= N) return;
+  float s = 0.f;
+  for (int b = lane; b < B; b += 32) s += __half2float(zt[(long long)n * ld + b]);
+  for (int o = 16; o; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) gb[n] = alpha * s;
+}
+
+// Fused Adam (optix.adam: m, v, bias correction, theta -= lr * mhat / (sqrt(vhat) + eps)) over the
+// flat effective-parameter space + refresh of the fp16 effective weights in both layouts.
+// do_update == 0: refresh only (after parameters were loaded).
+__global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, float* __restrict__ master,
+                                    const float* __restrict__ eps_noise, float* __restrict__ am,
+                                    float* __restrict__ av, const float* __restrict__ grad,
+                                    float grad_scale, int do_update, float lr, float b1, float b2,
+                                    float eps, float bc1, float bc2, __half* __restrict__ w16,
+                                    __half* __restrict__ w16t, float* __restrict__ beff) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_eff;
+       i += (long long)gridDim.x * blockDim.x) {
+    int l = 0;
+#pragma unroll
+    for (int k = 1; k < kMaxLayers; ++k)
+      if (k < tab.n_layers && i >= tab.l[k].eoff) l = k;
+    const LayerGeo g = tab.l[l];
+    const long long loc = i - g.eoff;
+    const float noise = kinds == 3 ? eps_noise[i] : 0.f;
+    float eff = 0.f;
+    for (int k = 0; k < kinds; ++k) {
+      float p = master[k * n_eff + i];
+      if (do_update) {
+        const float gr = grad[i] * grad_scale * (k == 2 ? noise : 1.0f);
+        float m = am[k * n_eff + i], v = av[k * n_eff + i];
+        m = b1 * m + (1.0f - b1) * gr;
+        v = b2 * v + (1.0f - b2) * gr * gr;
+        am[k * n_eff + i] = m;
+        av[k * n_eff + i] = v;
+        const float mhat = m / bc1, vhat = v / bc2;
+        p = p - lr * mhat / (sqrtf(vhat) + eps);
+        master[k * n_eff + i] = p;
+      }
+      eff += (k == 2) ? p * noise : p;
+    }
+    if (loc < (long long)g.N * g.K) {
+      const int n = (int)(loc / g.K), kk = (int)(loc - (long long)n * g.K);
+      const __half hv = __float2half_rn(eff);
+      w16[g.woff + loc] = hv;
+      w16t[g.woff + (long long)kk * g.N + n] = hv;
+    } else {
+      beff[g.boff + (loc - (long long)g.N * g.K)] = eff;
+    }
+  }
+}
+
+// ---------------------------------------------------------------- host helpers ----
+template <class T>
+int dev_alloc(T** p, size_t n) {
+  *p = nullptr;
+  HB_CUDA(cudaMalloc((void**)p, n * sizeof(T)));
+  HB_CUDA(cudaMemset(*p, 0, n * sizeof(T)));
+  return HB_OK;
+}
+template <class T>
+void dev_free(T*& p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+void free_learner_ws(hb_qnet* q) {
+  dev_free(q->x); dev_free(q->xt);
+  for (int l = 0; l < kMaxLayers; ++l) {
+    dev_free(q->h[l]); dev_free(q->ht[l]); dev_free(q->th[l]); dev_free(q->dz[l]); dev_free(q->dzt[l]);
+  }
+  dev_free(q->logits); dev_free(q->q_on); dev_free(q->tlogits); dev_free(q->w_is); dev_free(q->loss_b);
+  q->lb = q->lbp = 0;
+}
+
+int ensure_learner_ws(hb_qnet* q, int B) {
+  if (q->lb >= B) return HB_OK;
+  HB_CUDA(cudaDeviceSynchronize());
+  free_learner_ws(q);
+  const int Bp = ceil_to(B, 8);
+  const int K0 = q->tab.l[0].K;
+  const int nl = q->n_layers;
+  const int NL = q->tab.l[nl - 1].N;
+  int rc;
+  if ((rc = dev_alloc(&q->x, (size_t)2 * B * K0))) return rc;
+  if ((rc = dev_alloc(&q->xt, (size_t)K0 * Bp))) return rc;
+  for (int l = 0; l < nl; ++l) {
+    const int N = q->tab.l[l].N;
+    if (l < nl - 1) {
+      if ((rc = dev_alloc(&q->h[l], (size_t)2 * B * N))) return rc;
+      if ((rc = dev_alloc(&q->ht[l], (size_t)N * 2 * Bp))) return rc;
+      if ((rc = dev_alloc(&q->th[l], (size_t)B * N))) return rc;
+    }
+    if ((rc = dev_alloc(&q->dz[l], (size_t)B * N))) return rc;
+    if ((rc = dev_alloc(&q->dzt[l], (size_t)N * Bp))) return rc;
+  }
+  if ((rc = dev_alloc(&q->logits, (size_t)2 * B * NL))) return rc;
+  if ((rc = dev_alloc(&q->q_on, (size_t)2 * B * NL))) return rc;
+  if ((rc = dev_alloc(&q->tlogits, (size_t)B * NL))) return rc;
+  if ((rc = dev_alloc(&q->w_is, (size_t)B))) return rc;
+  if ((rc = dev_alloc(&q->loss_b, (size_t)B))) return rc;
+  q->lb = B;
+  q->lbp = Bp;
+  return HB_OK;
+}
+
+int ensure_act_ws(hb_qnet* q, long long rows) {
+  if (q->act_rows >= rows) return HB_OK;
+  HB_CUDA(cudaDeviceSynchronize());
+  dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
+  q->act_rows = 0;
+  int nmax = 8;
+  for (int l = 0; l + 1 < q->n_layers; ++l) nmax = nmax > q->tab.l[l].N ? nmax : q->tab.l[l].N;
+  const int NL = q->tab.l[q->n_layers - 1].N;
+  int rc;
+  if ((rc = dev_alloc(&q->act_x, (size_t)rows * q->tab.l[0].K))) return rc;
+  if ((rc = dev_alloc(&q->act_h[0], (size_t)rows * nmax))) return rc;
+  if ((rc = dev_alloc(&q->act_h[1], (size_t)rows * nmax))) return rc;
+  if ((rc = dev_alloc(&q->act_q, (size_t)rows * (q->n_atoms > 1 ? q->A : NL)))) return rc;
+  q->act_rows = rows;
+  return HB_OK;
+}
+
+int launch_unpack(const uint32_t* packed, int stride, long long rows, __half* out, int ld,
+                  __half* out_t, int ld_t, long long rows_t, cudaStream_t s) {
+  const long long total = rows * stride;
+  const unsigned blocks = (unsigned)((total + 255) / 256 < 148 * 32 ? (total + 255) / 256 : 148 * 32);
+  unpack_rows_kernel<<<blocks ? blocks : 1, 256, 0, s>>>(packed, stride, rows, out, ld, out_t, ld_t, rows_t);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+// Forward pass of `rows` rows already unpacked in x0 [rows, K0].  weights: w16 (online) or t16.
+// hidden activations go to hbuf[l] (ld = N_l) with optional transposed copies; the head writes
+// q (and logits when given).
+int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0, long long rows,
+            __half* const* hbuf, __half* const* hbuf_t, int ld_t, float* logits, float* q_out, int ldq,
+            cudaStream_t s) {
+  const __half* in = x0;
+  int ld_in = net->tab.l[0].K;
+  const int nl = net->n_layers;
+  for (int l = 0; l < nl; ++l) {
+    const LayerGeo& g = net->tab.l[l];
+    tc::EpiParams ep{};
+    ep.alpha = 1.f;
+    ep.bias = bias + g.boff;
+    int rc;
+    if (l < nl - 1) {
+      ep.relu = 1;
+      ep.out16 = hbuf[l];
+      ep.ld_out = g.N;
+      ep.out16_t = hbuf_t ? hbuf_t[l] : nullptr;
+      ep.ld_out_t = ld_t;
+      rc = tc::gemm<tc::EPI_F16>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
+      in = hbuf[l];
+      ld_in = g.N;
+    } else if (net->n_atoms > 1) {
+      ep.out32 = logits;
+      ep.ld_out = g.N;
+      ep.q = q_out;
+      ep.ld_q = ldq;
+      ep.n_atoms = net->n_atoms;
+      ep.z0 = -net->vmax;
+      ep.dz = 2.f * net->vmax / (float)(net->n_atoms - 1);
+      ep.q_scale = 1.0f / (float)net->n_atoms;     // jnp.mean(probs * atoms)  rlax_rainbow.py:118
+      rc = tc::gemm<tc::EPI_C51>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
+    } else {
+      ep.out32 = q_out;
+      ep.ld_out = ldq;
+      rc = tc::gemm<tc::EPI_F32>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
+    }
+    if (rc) return rc;
+  }
+  return HB_OK;
+}
+
+int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
+             cudaStream_t s) {
+  float bc1 = 1.f, bc2 = 1.f;
+  if (do_update) {
+    net->adam_step += 1;
+    bc1 = 1.0f - powf(b1, (float)net->adam_step);
+    bc2 = 1.0f - powf(b2, (float)net->adam_step);
+  }
+  const unsigned blocks = (unsigned)((net->n_eff + 255) / 256 < 148 * 16 ? (net->n_eff + 255) / 256 : 148 * 16);
+  adam_refresh_kernel<<<blocks, 256, 0, s>>>(net->tab, net->n_eff, net->kinds, net->master, net->eps,
+                                             net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
+                                             lr, b1, b2, eps, bc1, bc2, net->w16, net->w16t, net->beff);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+// maps (layer, kind, element of the reference-layout tensor) <-> flat effective index
+// weights: reference [in, out] row-major, element (i, o); ours row n(o), column i.
+inline int out_to_n(const hb_qnet* net, int layer, int o) {
+  if (layer == net->n_layers - 1 && net->n_atoms > 1) return (o / net->n_atoms) * 64 + (o % net->n_atoms);
+  return o;
+}
+
+}  // namespace
+
 extern "C" {
 
-// Test / microbenchmark entry: D = epilogue(alpha * A . B^T + bias), A [M, K] and B [N, K] fp16
-// row-major device matrices.  mode 0: fp16 out (+relu), 1: fp32 out, 2: categorical head
-// (out32 = logits [M, N], q = [M, N/64]).
 int hb_gemm_f16(const void* d_a, int64_t lda, const void* d_b, int64_t ldb, int M, int N, int K,
                 int mode, float alpha, const float* d_bias, int relu, void* d_out, int64_t ld_out,
                 void* d_out_t, int64_t ld_out_t, float* d_q, int n_atoms, float z0, float dz,
@@ -46,6 +575,318 @@ int hb_gemm_f16(const void* d_a, int64_t lda, const void* d_b, int64_t ldb, int 
       hb::set_error("hb_gemm_f16: unknown mode %d", mode);
       return HB_ERR_INVALID;
   }
+}
+
+int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int n_hidden,
+                  int num_actions, int n_atoms, float atom_vmax, int noisy, int device,
+                  hb_qnet** out) {
+  HB_REQUIRE(out != nullptr, "hb_net_create: out is NULL");
+  HB_REQUIRE(obs_len >= 1 && obs_stride_words * 32 >= obs_len && obs_stride_words % 4 == 0,
+             "hb_net_create: bad observation geometry (%d bits, %d words)", obs_len, obs_stride_words);
+  HB_REQUIRE(n_hidden >= 0 && n_hidden + 1 <= kMaxLayers, "hb_net_create: 0..%d hidden layers", kMaxLayers - 1);
+  HB_REQUIRE(num_actions >= 1 && num_actions <= 64, "hb_net_create: 1..64 actions");
+  HB_REQUIRE(n_atoms >= 1 && n_atoms <= 64, "hb_net_create: 1..64 atoms");
+  for (int l = 0; l < n_hidden; ++l)
+    HB_REQUIRE(hidden[l] >= 8 && hidden[l] % 8 == 0, "hb_net_create: hidden sizes must be multiples of 8");
+  hb::DeviceGuard g(device);
+  if (!g.ok) { hb::set_error("hb_net_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
+  hb_qnet* q = new (std::nothrow) hb_qnet();
+  HB_REQUIRE(q != nullptr, "hb_net_create: out of host memory");
+  q->device = device;
+  q->obs_len = obs_len;
+  q->obs_stride = obs_stride_words;
+  q->A = num_actions;
+  q->n_atoms = n_atoms;
+  q->noisy = noisy ? 1 : 0;
+  q->kinds = noisy ? 3 : 1;
+  q->vmax = atom_vmax;
+  q->n_layers = n_hidden + 1;
+  q->tab.n_layers = q->n_layers;
+  long long eoff = 0, woff = 0, boff = 0;
+  int in = obs_len, K = obs_stride_words * 32;
+  for (int l = 0; l < q->n_layers; ++l) {
+    LayerGeo& L = q->tab.l[l];
+    const bool last = l == q->n_layers - 1;
+    L.in = in;
+    L.out = last ? num_actions * n_atoms : hidden[l];
+    L.K = K;
+    L.N = last ? (n_atoms > 1 ? num_actions * 64 : ceil_to(num_actions, 8)) : hidden[l];
+    L.eoff = eoff; L.woff = woff; L.boff = boff;
+    eoff += (long long)L.N * L.K + L.N;
+    woff += (long long)L.N * L.K;
+    boff += L.N;
+    in = L.out;
+    K = L.N;
+  }
+  q->n_eff = eoff; q->n_w = woff; q->n_b = boff;
+  int rc = HB_OK;
+  if (!rc) rc = dev_alloc(&q->master, (size_t)q->kinds * q->n_eff);
+  if (!rc && noisy) rc = dev_alloc(&q->eps, (size_t)q->n_eff);
+  if (!rc) rc = dev_alloc(&q->adam_m, (size_t)q->kinds * q->n_eff);
+  if (!rc) rc = dev_alloc(&q->adam_v, (size_t)q->kinds * q->n_eff);
+  if (!rc) rc = dev_alloc(&q->grad, (size_t)q->n_eff);
+  if (!rc) rc = dev_alloc(&q->w16, (size_t)q->n_w);
+  if (!rc) rc = dev_alloc(&q->w16t, (size_t)q->n_w);
+  if (!rc) rc = dev_alloc(&q->t16, (size_t)q->n_w);
+  if (!rc) rc = dev_alloc(&q->beff, (size_t)q->n_b);
+  if (!rc) rc = dev_alloc(&q->tbeff, (size_t)q->n_b);
+  if (!rc) rc = dev_alloc(&q->scalars, 4);
+  if (rc) { hb_net_destroy(q); return rc; }
+  *out = q;
+  return HB_OK;
+}
+
+int hb_net_destroy(hb_qnet* q) {
+  if (!q) return HB_OK;
+  hb::DeviceGuard g(q->device);
+  cudaDeviceSynchronize();
+  dev_free(q->master); dev_free(q->eps); dev_free(q->adam_m); dev_free(q->adam_v); dev_free(q->grad);
+  dev_free(q->w16); dev_free(q->w16t); dev_free(q->t16); dev_free(q->beff); dev_free(q->tbeff);
+  dev_free(q->scalars);
+  dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
+  free_learner_ws(q);
+  delete q;
+  return HB_OK;
+}
+
+/* what: 0 n_layers, 1 n_eff (flat gradient length), 2 num_actions, 3 n_atoms, 4 noisy,
+ *       5 adam step count, 10+l: in of layer l, 20+l: out of layer l, 30+l: K, 40+l: N */
+int64_t hb_net_info(const hb_qnet* q, int what) {
+  if (!q) return -1;
+  if (what >= 10 && what < 50) {
+    const int l = what % 10;
+    if (l >= q->n_layers) return -1;
+    const LayerGeo& L = q->tab.l[l];
+    switch (what / 10) { case 1: return L.in; case 2: return L.out; case 3: return L.K; default: return L.N; }
+  }
+  switch (what) {
+    case 0: return q->n_layers;
+    case 1: return q->n_eff;
+    case 2: return q->A;
+    case 3: return q->n_atoms;
+    case 4: return q->noisy;
+    case 5: return q->adam_step;
+    default: return -1;
+  }
+}
+
+float* hb_net_grad(hb_qnet* q) { return q ? q->grad : nullptr; }
+
+/* kind: 0 w, 1 b, 2 w_mu, 3 b_mu, 4 w_sigma, 5 b_sigma, 6 eps_w, 7 eps_b, 8 dW (gradient of the
+ * effective weight), 9 db.  HOST arrays in the reference's layout: weights [in, out] row-major
+ * (noisy_mlp.py:61,73,78), biases [out]. */
+static int net_param_io(hb_qnet* q, int layer, int kind, float* h_data, int64_t n, bool set) {
+  HB_REQUIRE(q && h_data && layer >= 0 && layer < q->n_layers && kind >= 0 && kind <= 9,
+             "hb_net_param: bad arguments");
+  HB_REQUIRE(set ? kind <= 7 : true, "hb_net_set_param: gradients are read-only");
+  HB_REQUIRE(q->noisy || kind <= 1 || kind >= 8, "hb_net_param: plain MLP has only w and b");
+  const LayerGeo& L = q->tab.l[layer];
+  const bool is_w = (kind % 2) == 0;
+  const int64_t want = is_w ? (int64_t)L.in * L.out : L.out;
+  HB_REQUIRE(n == want, "hb_net_param: layer %d kind %d expects %lld values, got %lld", layer, kind,
+             (long long)want, (long long)n);
+  hb::DeviceGuard g(q->device);
+  float* base;
+  if (kind <= 5) base = q->master + (size_t)(kind / 2) * q->n_eff;
+  else if (kind <= 7) base = q->eps;
+  else base = q->grad;
+  base += L.eoff + (is_w ? 0 : (long long)L.N * L.K);
+  const size_t cnt = is_w ? (size_t)L.N * L.K : (size_t)L.N;
+  std::vector<float> tmp(cnt, 0.f);
+  HB_CUDA(cudaDeviceSynchronize());
+  if (!set) HB_CUDA(cudaMemcpy(tmp.data(), base, cnt * 4, cudaMemcpyDeviceToHost));
+  if (is_w) {
+    for (int i = 0; i < L.in; ++i)
+      for (int o = 0; o < L.out; ++o) {
+        float& d = tmp[(size_t)out_to_n(q, layer, o) * L.K + i];
+        float& h = h_data[(size_t)i * L.out + o];
+        if (set) d = h; else h = d;
+      }
+  } else {
+    for (int o = 0; o < L.out; ++o) {
+      float& d = tmp[(size_t)out_to_n(q, layer, o)];
+      if (set) d = h_data[o]; else h_data[o] = d;
+    }
+  }
+  if (set) HB_CUDA(cudaMemcpy(base, tmp.data(), cnt * 4, cudaMemcpyHostToDevice));
+  return HB_OK;
+}
+
+int hb_net_set_param(hb_qnet* q, int layer, int kind, const float* h_data, int64_t n) {
+  return net_param_io(q, layer, kind, const_cast<float*>(h_data), n, true);
+}
+int hb_net_get_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n) {
+  return net_param_io(q, layer, kind, h_out, n, false);
+}
+
+/* Recompute the fp16 effective weights from the masters (after hb_net_set_param). */
+int hb_net_refresh(hb_qnet* q, void* stream) {
+  HB_REQUIRE(q, "hb_net_refresh: NULL net");
+  hb::DeviceGuard g(q->device);
+  return run_adam(q, 0, 0.f, 0.f, 0.f, 0.f, 1.f, (cudaStream_t)stream);
+}
+
+/* trg_params = online_params  (rlax_rainbow.py:336-337) */
+int hb_net_sync_target(hb_qnet* q, void* stream) {
+  HB_REQUIRE(q, "hb_net_sync_target: NULL net");
+  hb::DeviceGuard g(q->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  HB_CUDA(cudaMemcpyAsync(q->t16, q->w16, (size_t)q->n_w * 2, cudaMemcpyDeviceToDevice, s));
+  HB_CUDA(cudaMemcpyAsync(q->tbeff, q->beff, (size_t)q->n_b * 4, cudaMemcpyDeviceToDevice, s));
+  return HB_OK;
+}
+
+/* DQNAgent.explore / exploit (rlax_rainbow.py:277-290) for n rows of bit-packed observations and
+ * legal-move masks.  greedy != 0: eval_policy.  d_uniform: one U[0,1) (explore: U[0,0.999)) draw per
+ * row, or NULL for the built-in counter-based stream keyed (seed, counter, row0 + row).
+ * d_q (optional): masked q-values [n, num_actions]. */
+int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int legal_words, int64_t n,
+               int greedy, float epsilon, const float* d_uniform, uint64_t seed, uint64_t counter,
+               int64_t row0, int use_target, int32_t* d_action, float* d_q, void* stream) {
+  HB_REQUIRE(q && d_obs && d_legal && d_action && n >= 0, "hb_net_act: bad arguments");
+  HB_REQUIRE(legal_words == (q->A + 31) / 32, "hb_net_act: legal_words does not match %d actions", q->A);
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(q->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long chunk = n < kActChunk ? n : kActChunk;
+  int rc = ensure_act_ws(q, chunk);
+  if (rc) return rc;
+  const int ldq = q->n_atoms > 1 ? q->A : q->tab.l[q->n_layers - 1].N;
+  for (long long r0 = 0; r0 < n; r0 += chunk) {
+    const long long rows = n - r0 < chunk ? n - r0 : chunk;
+    rc = launch_unpack(d_obs + r0 * q->obs_stride, q->obs_stride, rows, q->act_x, q->tab.l[0].K,
+                       nullptr, 0, 0, s);
+    if (rc) return rc;
+    __half* hb[kMaxLayers];
+    for (int l = 0; l < kMaxLayers; ++l) hb[l] = q->act_h[l & 1];
+    rc = forward(q, use_target ? q->t16 : q->w16, use_target ? q->tbeff : q->beff, q->act_x, rows, hb,
+                 nullptr, 0, nullptr, q->act_q, ldq, s);
+    if (rc) return rc;
+    policy_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, s>>>(
+        q->act_q, ldq, d_legal + r0 * legal_words, legal_words, q->A, rows, greedy, epsilon,
+        d_uniform ? d_uniform + r0 : nullptr, seed, counter, row0 + r0, d_action + r0,
+        d_q ? d_q + r0 * q->A : nullptr);
+    HB_CUDA(cudaGetLastError());
+  }
+  return HB_OK;
+}
+
+/* Forward + loss + backward of DQNLearning.update_q; leaves dL/dW_eff, dL/db_eff in the flat
+ * gradient bucket (hb_net_grad) -- the buffer a data-parallel job all-reduces -- and
+ *   d_loss_out[B]  per-sample loss (C51: cross-entropy; the reference's new_prios = |loss_b|,
+ *                  rlax_rainbow.py:198) or TD error (double-Q, rlax_dqn.py:233)
+ *   d_mean_loss[1] mean(loss_b * w_is)
+ * d_prios: sampled probabilities (C51 variant: w = (1/prios)^beta / max, rlax_rainbow.py:188-189);
+ * d_weights: importance weights given directly (rlax_dqn.py:144 signature); exactly one is non-NULL
+ * (both NULL = all ones).  mask_terminal: gamma*(1-terminal) as rainbow_agent.py:191-197 (C51 only;
+ * the rlax C51 learner ignores term_t).  Observations are bit-packed rows. */
+int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                 const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                 const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                 float* d_loss_out, float* d_mean_loss, void* stream) {
+  HB_REQUIRE(q && d_obs_tm1 && d_a_tm1 && d_r_t && d_obs_t && B >= 1, "hb_net_grads: bad arguments");
+  HB_REQUIRE(!(d_prios && d_weights), "hb_net_grads: give prios or weights, not both");
+  hb::DeviceGuard g(q->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = ensure_learner_ws(q, B);
+  if (rc) return rc;
+  const int nl = q->n_layers, K0 = q->tab.l[0].K, Bp = q->lbp;
+  const LayerGeo& LL = q->tab.l[nl - 1];
+  const int ldq = q->n_atoms > 1 ? q->A : LL.N;
+  // 1. unpack: rows [0, B) = obs_tm1 (+ transposed copy), rows [B, 2B) = obs_t
+  if ((rc = launch_unpack(d_obs_tm1, q->obs_stride, B, q->x, K0, q->xt, Bp, B, s))) return rc;
+  if ((rc = launch_unpack(d_obs_t, q->obs_stride, B, q->x + (size_t)B * K0, K0, nullptr, 0, 0, s))) return rc;
+  // 2. online network on both observation sets, target network on obs_t
+  if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s))) return rc;
+  if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
+                    q->n_atoms > 1 ? nullptr : q->tlogits, ldq, s))) return rc;
+  // 3. importance weights
+  if (d_prios) {
+    is_weights_kernel<<<1, 256, 0, s>>>(d_prios, B, beta, q->w_is);
+    HB_CUDA(cudaGetLastError());
+  } else if (d_weights) {
+    HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
+  } else {
+    std::vector<float> ones(B, 1.f);
+    HB_CUDA(cudaMemcpyAsync(q->w_is, ones.data(), (size_t)B * 4, cudaMemcpyHostToDevice, s));
+    HB_CUDA(cudaStreamSynchronize(s));
+  }
+  // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
+  HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, s));
+  HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, s));
+  if (q->n_atoms > 1) {
+    c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, q->q_on + (size_t)B * ldq, ldq, q->tlogits,
+                                               LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, q->w_is,
+                                               B, q->A, q->n_atoms, q->vmax, discount, q->dz[nl - 1],
+                                               q->dzt[nl - 1], Bp, q->loss_b);
+  } else {
+    dqn_loss_kernel<<<(B + 127) / 128, 128, 0, s>>>(q->q_on, ldq, q->tlogits, d_a_tm1, d_r_t, d_term_t,
+                                                   q->w_is, B, q->A, discount, q->dz[nl - 1], LL.N,
+                                                   q->dzt[nl - 1], Bp, q->loss_b);
+  }
+  HB_CUDA(cudaGetLastError());
+  mean_loss_kernel<<<1, 256, 0, s>>>(q->loss_b, q->w_is, B, q->n_atoms > 1 ? 0 : 1, q->scalars);
+  HB_CUDA(cudaGetLastError());
+  if (d_loss_out) HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
+  if (d_mean_loss) HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
+  // 5. backward
+  const float invB = 1.0f / (float)B;
+  for (int l = nl - 1; l >= 0; --l) {
+    const LayerGeo& L = q->tab.l[l];
+    // dW_l [N, K] = dZ_l^T . X_l  : A = dzt[l] [N, B], B = (layer input)^T [K, B]
+    const __half* in_t = l == 0 ? q->xt : q->ht[l - 1];
+    const int ld_in_t = l == 0 ? Bp : 2 * Bp;
+    tc::EpiParams ep{};
+    ep.alpha = invB;
+    ep.out32 = q->grad + L.eoff;
+    ep.ld_out = L.K;
+    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, s))) return rc;
+    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, s>>>(q->dzt[l], Bp, L.N, B, invB,
+                                                  q->grad + L.eoff + (long long)L.N * L.K);
+    HB_CUDA(cudaGetLastError());
+    if (l > 0) {
+      // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
+      tc::EpiParams eb{};
+      eb.alpha = 1.f;
+      eb.gate = q->h[l - 1];
+      eb.ld_gate = L.K;
+      eb.out16 = q->dz[l - 1];
+      eb.ld_out = L.K;
+      eb.out16_t = q->dzt[l - 1];
+      eb.ld_out_t = Bp;
+      if ((rc = tc::gemm<tc::EPI_F16>(q->dz[l], L.N, q->w16t + L.woff, L.N, B, L.K, L.N, eb, s))) return rc;
+    }
+  }
+  return HB_OK;
+}
+
+/* optix.adam update of every master tensor from the flat gradient bucket (after the optional
+ * all-reduce; grad_scale = 1/world_size) and refresh of the fp16 effective weights. */
+int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream) {
+  HB_REQUIRE(q, "hb_net_adam: NULL net");
+  hb::DeviceGuard g(q->device);
+  return run_adam(q, 1, lr, b1, b2, eps, grad_scale, (cudaStream_t)stream);
+}
+
+/* Q-values / logits of n packed observations (tests, evaluation): d_q [n, num_actions] unmasked;
+ * d_logits [n, N_last] (categorical: column a*64 + j) or NULL. */
+int hb_net_forward(hb_qnet* q, const uint32_t* d_obs, int64_t n, int use_target, float* d_q,
+                   float* d_logits, void* stream) {
+  HB_REQUIRE(q && d_obs && d_q && n >= 1 && n <= kActChunk, "hb_net_forward: bad arguments (n <= %d)", kActChunk);
+  hb::DeviceGuard g(q->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = ensure_act_ws(q, n);
+  if (rc) return rc;
+  if ((rc = launch_unpack(d_obs, q->obs_stride, n, q->act_x, q->tab.l[0].K, nullptr, 0, 0, s))) return rc;
+  __half* hb[kMaxLayers];
+  for (int l = 0; l < kMaxLayers; ++l) hb[l] = q->act_h[l & 1];
+  const int ldq = q->n_atoms > 1 ? q->A : q->tab.l[q->n_layers - 1].N;
+  rc = forward(q, use_target ? q->t16 : q->w16, use_target ? q->tbeff : q->beff, q->act_x, n, hb,
+               nullptr, 0, d_logits, q->act_q, ldq, s);
+  if (rc) return rc;
+  HB_CUDA(cudaMemcpy2DAsync(d_q, (size_t)q->A * 4, q->act_q, (size_t)ldq * 4, (size_t)q->A * 4, (size_t)n,
+                            cudaMemcpyDeviceToDevice, s));
+  return HB_OK;
 }
 
 }  // extern "C"

@@ -180,7 +180,53 @@ int hb_gemm_f16(const void* d_a, int64_t lda, const void* d_b, int64_t ldb, int 
                 void* d_out_t, int64_t ld_out_t, float* d_q, int n_atoms, float z0, float dz,
                 float q_scale, void* stream);
 
-/* @@QNET@@ */
+typedef struct hb_qnet hb_qnet;
+
+/* Network of DQNAgent.__init__ (rlax_rainbow.py:237-246): NoisyMLP(layers + [A * n_atoms]) reshaped
+ * to [A, n_atoms] (noisy != 0), or hk.nets.MLP(layers + [A]) of rlax_dqn.py:26-33 (noisy == 0,
+ * n_atoms == 1).  Input = bit-packed observation rows of obs_stride_words 32-bit words. */
+int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int n_hidden,
+                  int num_actions, int n_atoms, float atom_vmax, int noisy, int device,
+                  hb_qnet** out);
+int hb_net_destroy(hb_qnet* q);
+/* what: 0 n_layers, 1 length of the flat gradient bucket, 2 num_actions, 3 n_atoms, 4 noisy,
+ *       5 Adam step count, 10+l / 20+l: in / out of layer l, 30+l / 40+l: padded K / N */
+int64_t hb_net_info(const hb_qnet* q, int what);
+/* Device pointer of the flat fp32 gradient bucket (dW_eff, db_eff per layer): the one buffer a
+ * data-parallel job all-reduces between hb_net_grads and hb_net_adam. */
+float* hb_net_grad(hb_qnet* q);
+/* Parameter exchange in the reference's layout (haiku: w [in, out] row-major, b [out];
+ * noisy_mlp.py:61-84).  kind: 0 w, 1 b, 2 w_mu, 3 b_mu, 4 w_sigma, 5 b_sigma, 6 eps_w, 7 eps_b
+ * (the trace-time noise constants, noisy_mlp.py:79,87), 8 dW_eff, 9 db_eff (get only). HOST arrays. */
+int hb_net_set_param(hb_qnet* q, int layer, int kind, const float* h_data, int64_t n);
+int hb_net_get_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n);
+/* Recompute the fp16 effective weights after hb_net_set_param. */
+int hb_net_refresh(hb_qnet* q, void* stream);
+/* trg_params = online_params  (rlax_rainbow.py:336-337) */
+int hb_net_sync_target(hb_qnet* q, void* stream);
+/* DQNAgent.explore (greedy == 0, DQNPolicy.policy rlax_rainbow.py:93-123) / exploit (greedy != 0,
+ * eval_policy :125-150) on n bit-packed observation rows + legal masks.  d_uniform: one draw per row
+ * (explore: U[0, 0.999)), or NULL = counter-based stream keyed (seed, counter, row0 + row).
+ * d_q (optional) [n, num_actions]: q-values with illegal moves at -inf. */
+int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int legal_words, int64_t n,
+               int greedy, float epsilon, const float* d_uniform, uint64_t seed, uint64_t counter,
+               int64_t row0, int use_target, int32_t* d_action, float* d_q, void* stream);
+/* network.apply on n <= 131072 packed rows: d_q [n, num_actions] (unmasked), d_logits (optional)
+ * [n, A*64] with atom j of action a at column a*64 + j. */
+int hb_net_forward(hb_qnet* q, const uint32_t* d_obs, int64_t n, int use_target, float* d_q,
+                   float* d_logits, void* stream);
+/* jax.grad(loss) of DQNLearning.update_q: categorical double-Q (rlax_rainbow.py:172-200) when
+ * n_atoms > 1, double-Q with L2 loss (rlax_dqn.py:170-205) when n_atoms == 1.  Gradients are left
+ * in the flat bucket; d_loss_out[B] = per-sample loss (C51) / TD error (double-Q) -- what the agent
+ * feeds to update_priorities; d_mean_loss[1] = mean(loss * w).  d_prios: sampled probabilities
+ * (w = (1/prios)^beta / max); d_weights: importance weights given directly; both NULL = ones. */
+int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                 const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                 const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                 float* d_loss_out, float* d_mean_loss, void* stream);
+/* optix.adam(lr, b1, b2, eps) on every master tensor (rlax_rainbow.py:215-216,257) from
+ * grad_scale * bucket, then refresh of the effective weights. */
+int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 
 #ifdef __cplusplus
 }

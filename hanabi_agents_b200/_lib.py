@@ -64,6 +64,22 @@ SIGNATURES = {
     # rule-based agents
     "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
     "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),
+    "hb_st_update_range_dev": (i32, [vp, i64, i64, vp, vp]),
+    # replay shard
+    "hb_rb_create": (i32, [i32, i32, i32, i64, i32, f32, i32, C.POINTER(vp)]),
+    "hb_rb_destroy": (i32, [vp]),
+    "hb_rb_info": (i64, [vp, i32]),
+    "hb_rb_tree": (vp, [vp]),
+    "hb_rb_add": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
+    "hb_rb_store_first": (i32, [vp, vp, vp, vp, i64, vp]),
+    "hb_rb_add_masked": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), vp]),
+    "hb_rb_gather": (i32, [vp, vp, i64, vp, vp, vp, vp, vp, vp, vp]),
+    "hb_rb_check": (i32, [vp, vp]),
+    "hb_rb_sample": (i32, [vp, vp, i64, vp, vp, vp, vp]),
+    "hb_rb_update_priorities": (i32, [vp, vp, vp, i64, vp]),
+    "hb_rb_priority_range": (i32, [vp, C.POINTER(f32), C.POINTER(f32), vp]),
+    "hb_pack_bits": (i32, [vp, i32, vp, i32, i64, vp]),
+    "hb_unpack_bits": (i32, [vp, i32, i32, vp, i64, vp]),
     # q-network
     "hb_gemm_f16": (i32, [vp, i64, vp, i64, i32, i32, i32, i32, f32, vp, i32, vp, i64, vp, i64, vp,
                           i32, f32, f32, f32, vp]),

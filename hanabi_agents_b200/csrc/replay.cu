@@ -1,0 +1,539 @@
+// Device-resident replay shard: ring buffer of bit-packed transitions + prioritized sampling.
+//
+// Replaces (path:line under /root/reference/hanabi_agents/rlax_dqn)
+//   ExperienceBuffer   experience_buffer.py:5-97   (ring of obs_tm1 / act / rew / obs_t / lms / term)
+//   PriorityBuffer     priority_buffer.py:13-52    (ring + SumTree: insert at max priority,
+//                                                   stratified sample, priority update)
+// and the transition bookkeeping of DQNAgent.add_experience_first / add_experience
+// (rlax_rainbow.py:292-308: rows with step_type != 0 are appended in order, last_obs is refreshed).
+//
+// Observations stay in the packed form the env kernels emit (Full-2p: 96 B per row instead of
+// the reference's 658 int8); legal moves are 1-2 words per row.  Rows are appended with one warp
+// per transition (coalesced word copies); the masked append first ranks the selected rows with a
+// two-level ballot scan so that their order -- and therefore the ring and sum-tree contents --
+// is the reference's.
+#include "common.cuh"
+#include <new>
+
+struct hb_replay {
+  int device = 0;
+  int obs_len = 0, stride = 0, num_moves = 0, legal_words = 0;
+  int64_t cap = 0, size = 0, oldest = 0;
+  int prioritized = 0;
+  float alpha = 0.6f;
+  uint32_t* obs_tm1 = nullptr;
+  uint32_t* obs_t = nullptr;
+  uint32_t* lms = nullptr;
+  int32_t* act = nullptr;
+  float* rew = nullptr;
+  uint8_t* term = nullptr;
+  hb_sumtree* tree = nullptr;
+  float* prio_range = nullptr;        // device: [0] max_priority, [1] min_priority
+  // scratch for the masked append
+  int64_t scan_n = 0;
+  int32_t* block_sum = nullptr;       // per 1024-row block
+  int32_t* total = nullptr;           // device count of selected rows
+  int32_t* h_total = nullptr;         // pinned host copy
+  float* vals = nullptr;              // scratch for priorities / sampled values
+  int64_t vals_n = 0;
+};
+
+namespace {
+
+constexpr int kScanBlock = 1024;
+
+// ---- masked append: rank the rows with step_type != 0 ----------------------------------
+__global__ void __launch_bounds__(kScanBlock)
+mask_count_kernel(const uint8_t* __restrict__ step_type, int64_t n, int32_t* __restrict__ block_sum) {
+  __shared__ int warp_cnt[32];
+  const int64_t i = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const bool sel = i < n && step_type[i] != 0;
+  const unsigned b = __ballot_sync(0xffffffffu, sel);
+  if ((threadIdx.x & 31) == 0) warp_cnt[threadIdx.x >> 5] = __popc(b);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    int v = warp_cnt[threadIdx.x];
+    for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if (threadIdx.x == 0) block_sum[blockIdx.x] = v;
+  }
+}
+
+// exclusive scan of the block sums in place (one block; sequential over chunks of 1024)
+__global__ void __launch_bounds__(kScanBlock)
+mask_scan_kernel(int32_t* __restrict__ block_sum, int n_blocks, int32_t* __restrict__ total) {
+  __shared__ int sh[kScanBlock];
+  __shared__ int carry;
+  if (threadIdx.x == 0) carry = 0;
+  __syncthreads();
+  for (int base = 0; base < n_blocks; base += kScanBlock) {
+    const int i = base + threadIdx.x;
+    const int v = i < n_blocks ? block_sum[i] : 0;
+    sh[threadIdx.x] = v;
+    __syncthreads();
+    for (int o = 1; o < kScanBlock; o <<= 1) {
+      const int t = threadIdx.x >= o ? sh[threadIdx.x - o] : 0;
+      __syncthreads();
+      sh[threadIdx.x] += t;
+      __syncthreads();
+    }
+    if (i < n_blocks) block_sum[i] = carry + sh[threadIdx.x] - v;
+    __syncthreads();
+    if (threadIdx.x == 0) carry += sh[kScanBlock - 1];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *total = carry;
+}
+
+// One warp per 32 rows: ranks them, then copies each selected transition with lane-per-word
+// accesses.  Also refreshes last_obs for the selected rows (rlax_rainbow.py:308).
+__global__ void __launch_bounds__(kScanBlock)
+masked_append_kernel(hb_replay rb, uint32_t* __restrict__ last_obs, const uint32_t* __restrict__ obs,
+                     const uint32_t* __restrict__ lms, const int32_t* __restrict__ act,
+                     const float* __restrict__ rew, const uint8_t* __restrict__ step_type, int64_t n,
+                     const int32_t* __restrict__ block_off) {
+  __shared__ int warp_off[32];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int64_t i = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const uint8_t st = i < n ? step_type[i] : 0;
+  const bool sel = st != 0;
+  const unsigned b = __ballot_sync(0xffffffffu, sel);
+  if (lane == 0) warp_off[warp] = __popc(b);
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    const int v = warp_off[threadIdx.x];
+    int s = v;
+    for (int o = 1; o < 32; o <<= 1) {
+      const int t = __shfl_up_sync(0xffffffffu, s, o);
+      if (threadIdx.x >= o) s += t;
+    }
+    warp_off[threadIdx.x] = s - v;
+  }
+  __syncthreads();
+  const int64_t base = rb.oldest + block_off[blockIdx.x] + warp_off[warp];
+  unsigned todo = b;
+  while (todo) {
+    const int src_lane = __ffs(todo) - 1;
+    todo &= todo - 1;
+    const int64_t row = (int64_t)blockIdx.x * kScanBlock + warp * 32 + src_lane;
+    const int rank = __popc(b & ((1u << src_lane) - 1));
+    int64_t pos = base + rank;
+    if (pos >= rb.cap) pos -= rb.cap;                     // ring wrap (experience_buffer.py:62-81)
+    for (int w = lane; w < rb.stride; w += 32) {
+      const uint32_t prev = last_obs[row * rb.stride + w];
+      const uint32_t cur = obs[row * rb.stride + w];
+      rb.obs_tm1[pos * rb.stride + w] = prev;
+      rb.obs_t[pos * rb.stride + w] = cur;
+      last_obs[row * rb.stride + w] = cur;
+    }
+    if (lane < rb.legal_words) rb.lms[pos * rb.legal_words + lane] = lms[row * rb.legal_words + lane];
+    if (lane == 0) {
+      rb.act[pos] = act[row];
+      rb.rew[pos] = rew[row];
+      rb.term[pos] = step_type[row] == 2;
+    }
+  }
+}
+
+// add_experience_first: last_obs[step_type == 0] = obs[...]  (rlax_rainbow.py:292-295)
+__global__ void store_first_kernel(uint32_t* __restrict__ last_obs, const uint32_t* __restrict__ obs,
+                                   const uint8_t* __restrict__ step_type, int stride, int64_t n) {
+  const int64_t total = n * stride;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / stride;
+    if (step_type[r] == 0) last_obs[i] = obs[i];
+  }
+}
+
+// contiguous append of n given rows (ExperienceBuffer.add_transitions), warp per row
+__global__ void append_kernel(hb_replay rb, const uint32_t* __restrict__ obs_tm1,
+                              const int32_t* __restrict__ act, const float* __restrict__ rew,
+                              const uint32_t* __restrict__ obs_t, const uint32_t* __restrict__ lms,
+                              const uint8_t* __restrict__ term, int64_t n) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  int64_t pos = rb.oldest + row;
+  if (pos >= rb.cap) pos -= rb.cap;
+  for (int w = lane; w < rb.stride; w += 32) {
+    rb.obs_tm1[pos * rb.stride + w] = obs_tm1[row * rb.stride + w];
+    rb.obs_t[pos * rb.stride + w] = obs_t[row * rb.stride + w];
+  }
+  if (lane < rb.legal_words) rb.lms[pos * rb.legal_words + lane] = lms[row * rb.legal_words + lane];
+  if (lane == 0) {
+    rb.act[pos] = act[row];
+    rb.rew[pos] = rew[row];
+    rb.term[pos] = term[row] != 0;
+  }
+}
+
+// __getitem__(indices): fancy-index gather (experience_buffer.py:83-87), warp per row
+__global__ void gather_kernel(hb_replay rb, const int64_t* __restrict__ idx, int64_t n,
+                              uint32_t* __restrict__ obs_tm1, int32_t* __restrict__ act,
+                              float* __restrict__ rew, uint32_t* __restrict__ obs_t,
+                              uint32_t* __restrict__ lms, uint8_t* __restrict__ term, int* err) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= n) return;
+  int64_t pos = idx[row];
+  if (pos < 0) pos += rb.cap;                              // numpy negative indexing
+  if (pos < 0 || pos >= rb.cap) { if (lane == 0) *err = 1; return; }
+  for (int w = lane; w < rb.stride; w += 32) {
+    if (obs_tm1) obs_tm1[row * rb.stride + w] = rb.obs_tm1[pos * rb.stride + w];
+    if (obs_t) obs_t[row * rb.stride + w] = rb.obs_t[pos * rb.stride + w];
+  }
+  if (lms && lane < rb.legal_words) lms[row * rb.legal_words + lane] = rb.lms[pos * rb.legal_words + lane];
+  if (lane == 0) {
+    if (act) act[row] = rb.act[pos];
+    if (rew) rew[row] = rb.rew[pos];
+    if (term) term[row] = rb.term[pos];
+  }
+}
+
+// prios = (value + 1e-10) / total in float64  (priority_buffer.py:42)
+__global__ void prios_kernel(const float* __restrict__ val, const float* __restrict__ total, int64_t n,
+                             double* __restrict__ p64, float* __restrict__ p32) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const double p = ((double)val[i] + 1e-10) / (double)*total;
+  if (p64) p64[i] = p;
+  if (p32) p32[i] = (float)p;
+}
+
+// priorities = (|td| + 1e-10) ** alpha in float32, running max / min  (priority_buffer.py:49-51).
+// The power is evaluated in double and rounded once (= a correctly rounded powf).
+__global__ void priorities_kernel(const float* __restrict__ td, int64_t n, float alpha,
+                                  float* __restrict__ out, float* __restrict__ range) {
+  __shared__ float smax[32], smin[32];
+  float mx = -INFINITY, mn = INFINITY;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+    const float x = td[i] + 1e-10f;
+    const float p = (float)pow((double)x, (double)alpha);
+    out[i] = p;
+    mx = fmaxf(mx, p);
+    mn = fminf(mn, p);
+  }
+  for (int o = 16; o; o >>= 1) {
+    mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    mn = fminf(mn, __shfl_xor_sync(0xffffffffu, mn, o));
+  }
+  if ((threadIdx.x & 31) == 0) { smax[threadIdx.x >> 5] = mx; smin[threadIdx.x >> 5] = mn; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) { mx = fmaxf(mx, smax[w]); mn = fminf(mn, smin[w]); }
+    range[0] = fmaxf(range[0], mx);
+    range[1] = fminf(range[1], mn);
+  }
+}
+
+// one byte per bit <-> packed words (the reference's np.byte layout, experience_buffer.py:9-12)
+__global__ void pack_bits_kernel(const int8_t* __restrict__ in, int bits, uint32_t* __restrict__ out,
+                                 int stride, int64_t n) {
+  const int64_t total = n * stride;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / stride;
+    const int w = (int)(i - r * stride);
+    uint32_t v = 0;
+    for (int j = 0; j < 32; ++j) {
+      const int b = w * 32 + j;
+      if (b < bits && in[r * bits + b] != 0) v |= 1u << j;
+    }
+    out[i] = v;
+  }
+}
+
+__global__ void unpack_bits_kernel2(const uint32_t* __restrict__ packed, int stride, int bits,
+                                    int8_t* __restrict__ out, int64_t n) {
+  const int64_t total = n * bits;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / bits;
+    const int b = (int)(i - r * bits);
+    out[i] = (int8_t)((packed[r * stride + (b >> 5)] >> (b & 31)) & 1u);
+  }
+}
+
+unsigned blocks_for(int64_t total, int threads) {
+  int64_t b = (total + threads - 1) / threads;
+  if (b > 148 * 32) b = 148 * 32;
+  if (b < 1) b = 1;
+  return (unsigned)b;
+}
+
+int ensure_vals(hb_replay* rb, int64_t n, cudaStream_t s) {
+  if (rb->vals_n >= n) return HB_OK;
+  HB_CUDA(cudaStreamSynchronize(s));
+  if (rb->vals) cudaFree(rb->vals);
+  rb->vals = nullptr;
+  rb->vals_n = 0;
+  HB_CUDA(cudaMalloc(&rb->vals, sizeof(float) * (n + 1)));
+  rb->vals_n = n;
+  return HB_OK;
+}
+
+// bookkeeping of ExperienceBuffer.add_transitions (experience_buffer.py:49-81)
+void advance(hb_replay* rb, int64_t n) {
+  if (rb->oldest + n <= rb->cap) {
+    if (rb->oldest + n == rb->cap) rb->size = rb->cap;
+    rb->oldest = (rb->oldest + n) % rb->cap;
+    if (rb->oldest > rb->size) rb->size = rb->oldest;
+  } else {
+    rb->oldest = rb->oldest + n - rb->cap;
+    rb->size = rb->cap;
+  }
+}
+
+// PriorityBuffer.add_transitions: leaves of the rows about to be written take max_priority, in the
+// order of get_update_indices (experience_buffer.py:21-24): [oldest, cap) then [0, tail).
+int insert_priorities(hb_replay* rb, int64_t n, cudaStream_t s) {
+  if (!rb->prioritized || n == 0) return HB_OK;
+  const int64_t first = rb->oldest + n <= rb->cap ? n : rb->cap - rb->oldest;
+  int rc = hb_st_update_range_dev(rb->tree, rb->oldest, first, rb->prio_range, s);
+  if (rc) return rc;
+  if (first < n) rc = hb_st_update_range_dev(rb->tree, 0, n - first, rb->prio_range, s);
+  return rc;
+}
+
+}  // namespace
+
+extern "C" {
+
+int hb_rb_destroy(hb_replay* rb);
+
+int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capacity, int prioritized,
+                 float alpha, int device, hb_replay** out) {
+  HB_REQUIRE(out != nullptr, "hb_rb_create: out is NULL");
+  HB_REQUIRE(obs_len >= 1 && obs_stride_words * 32 >= obs_len && num_moves >= 1 && num_moves <= 64 &&
+                 capacity >= 1,
+             "hb_rb_create: bad arguments");
+  hb::DeviceGuard g(device);
+  if (!g.ok) { hb::set_error("hb_rb_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
+  hb_replay* rb = new (std::nothrow) hb_replay();
+  HB_REQUIRE(rb != nullptr, "hb_rb_create: out of host memory");
+  rb->device = device;
+  rb->obs_len = obs_len;
+  rb->stride = obs_stride_words;
+  rb->num_moves = num_moves;
+  rb->legal_words = (num_moves + 31) / 32;
+  rb->cap = capacity;
+  rb->prioritized = prioritized ? 1 : 0;
+  rb->alpha = alpha;
+  const size_t c = (size_t)capacity;
+  cudaError_t e = cudaMalloc(&rb->obs_tm1, c * rb->stride * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->obs_t, c * rb->stride * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->lms, c * rb->legal_words * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->act, c * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->rew, c * 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->term, c);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->total, 4);
+  if (e == cudaSuccess) e = cudaMallocHost(&rb->h_total, 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->prio_range, 8);
+  if (e == cudaSuccess) {
+    // np.empty in the reference; zero here so that unwritten rows are defined
+    cudaMemset(rb->obs_tm1, 0, c * rb->stride * 4);
+    cudaMemset(rb->obs_t, 0, c * rb->stride * 4);
+    cudaMemset(rb->lms, 0, c * rb->legal_words * 4);
+    cudaMemset(rb->act, 0, c * 4);
+    cudaMemset(rb->rew, 0, c * 4);
+    cudaMemset(rb->term, 0, c);
+    const float init[2] = {alpha, alpha};      // max_priority = min_priority = alpha  (:18-19)
+    e = cudaMemcpy(rb->prio_range, init, 8, cudaMemcpyHostToDevice);
+  }
+  if (e != cudaSuccess) {
+    hb_rb_destroy(rb);
+    return hb::cuda_fail(e, "hb_rb_create alloc", __FILE__, __LINE__);
+  }
+  if (prioritized) {
+    int rc = hb_st_create(capacity, device, &rb->tree);     // SumTree(capacity)  :17
+    if (rc) { hb_rb_destroy(rb); return rc; }
+  }
+  *out = rb;
+  return HB_OK;
+}
+
+int hb_rb_destroy(hb_replay* rb) {
+  if (!rb) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaDeviceSynchronize();
+  if (rb->obs_tm1) cudaFree(rb->obs_tm1);
+  if (rb->obs_t) cudaFree(rb->obs_t);
+  if (rb->lms) cudaFree(rb->lms);
+  if (rb->act) cudaFree(rb->act);
+  if (rb->rew) cudaFree(rb->rew);
+  if (rb->term) cudaFree(rb->term);
+  if (rb->total) cudaFree(rb->total);
+  if (rb->h_total) cudaFreeHost(rb->h_total);
+  if (rb->prio_range) cudaFree(rb->prio_range);
+  if (rb->block_sum) cudaFree(rb->block_sum);
+  if (rb->vals) cudaFree(rb->vals);
+  if (rb->tree) hb_st_destroy(rb->tree);
+  delete rb;
+  return HB_OK;
+}
+
+int64_t hb_rb_info(const hb_replay* rb, int what) {
+  if (!rb) return -1;
+  switch (what) {
+    case 0: return rb->cap;
+    case 1: return rb->size;
+    case 2: return rb->oldest;
+    case 3: return rb->stride;
+    case 4: return rb->legal_words;
+    case 5: return rb->prioritized;
+    default: return -1;
+  }
+}
+
+hb_sumtree* hb_rb_tree(hb_replay* rb) { return rb ? rb->tree : nullptr; }
+
+int hb_rb_add(hb_replay* rb, const uint32_t* d_obs_tm1, const int32_t* d_act, const float* d_rew,
+              const uint32_t* d_obs_t, const uint32_t* d_lms, const uint8_t* d_term, int64_t n,
+              void* stream) {
+  HB_REQUIRE(rb && n >= 0, "hb_rb_add: bad arguments");
+  if (n == 0) return HB_OK;
+  HB_REQUIRE(d_obs_tm1 && d_act && d_rew && d_obs_t && d_lms && d_term, "hb_rb_add: NULL buffer");
+  HB_REQUIRE(n <= rb->cap, "hb_rb_add: %lld rows exceed the capacity %lld", (long long)n, (long long)rb->cap);
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = insert_priorities(rb, n, s);
+  if (rc) return rc;
+  append_kernel<<<(unsigned)((n + 7) / 8), 256, 0, s>>>(*rb, d_obs_tm1, d_act, d_rew, d_obs_t, d_lms,
+                                                       d_term, n);
+  HB_CUDA(cudaGetLastError());
+  advance(rb, n);
+  return HB_OK;
+}
+
+int hb_rb_store_first(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
+                      const uint8_t* d_step_type, int64_t n, void* stream) {
+  HB_REQUIRE(rb && d_last_obs && d_obs && d_step_type && n >= 0, "hb_rb_store_first: bad arguments");
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  store_first_kernel<<<blocks_for(n * rb->stride, 256), 256, 0, (cudaStream_t)stream>>>(
+      d_last_obs, d_obs, d_step_type, rb->stride, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                     const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                     int64_t* n_added, void* stream) {
+  HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
+             "hb_rb_add_masked: bad arguments");
+  if (n_added) *n_added = 0;
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n_blocks = (n + kScanBlock - 1) / kScanBlock;
+  if (rb->scan_n < n_blocks) {
+    HB_CUDA(cudaStreamSynchronize(s));
+    if (rb->block_sum) cudaFree(rb->block_sum);
+    rb->block_sum = nullptr;
+    rb->scan_n = 0;
+    HB_CUDA(cudaMalloc(&rb->block_sum, sizeof(int32_t) * n_blocks));
+    rb->scan_n = n_blocks;
+  }
+  mask_count_kernel<<<(unsigned)n_blocks, kScanBlock, 0, s>>>(d_step_type, n, rb->block_sum);
+  HB_CUDA(cudaGetLastError());
+  mask_scan_kernel<<<1, kScanBlock, 0, s>>>(rb->block_sum, (int)n_blocks, rb->total);
+  HB_CUDA(cudaGetLastError());
+  HB_CUDA(cudaMemcpyAsync(rb->h_total, rb->total, 4, cudaMemcpyDeviceToHost, s));
+  HB_CUDA(cudaStreamSynchronize(s));       // the ring cursor lives on the host, as in the reference
+  const int64_t cnt = *rb->h_total;
+  if (n_added) *n_added = cnt;
+  if (cnt == 0) return HB_OK;
+  HB_REQUIRE(cnt <= rb->cap, "hb_rb_add_masked: %lld rows exceed the capacity %lld", (long long)cnt,
+             (long long)rb->cap);
+  int rc = insert_priorities(rb, cnt, s);
+  if (rc) return rc;
+  masked_append_kernel<<<(unsigned)n_blocks, kScanBlock, 0, s>>>(*rb, d_last_obs, d_obs, d_lms, d_act,
+                                                                d_rew, d_step_type, n, rb->block_sum);
+  HB_CUDA(cudaGetLastError());
+  advance(rb, cnt);
+  return HB_OK;
+}
+
+int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,
+                 float* d_rew, uint32_t* d_obs_t, uint32_t* d_lms, uint8_t* d_term, void* stream) {
+  HB_REQUIRE(rb && d_idx && n >= 0, "hb_rb_gather: bad arguments");
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  HB_CUDA(cudaMemsetAsync(rb->total, 0, 4, s));
+  gather_kernel<<<(unsigned)((n + 7) / 8), 256, 0, s>>>(*rb, d_idx, n, d_obs_tm1, d_act, d_rew, d_obs_t,
+                                                       d_lms, d_term, rb->total);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+/* Reads the out-of-range flag of the last hb_rb_gather (synchronises). */
+int hb_rb_check(hb_replay* rb, void* stream) {
+  HB_REQUIRE(rb, "hb_rb_check: NULL buffer");
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  HB_CUDA(cudaMemcpyAsync(rb->h_total, rb->total, 4, cudaMemcpyDeviceToHost, s));
+  HB_CUDA(cudaStreamSynchronize(s));
+  if (*rb->h_total) { hb::set_error("replay: index out of range"); return HB_ERR_INDEX; }
+  return HB_OK;
+}
+
+int hb_rb_sample(hb_replay* rb, const float* d_keys, int64_t n, int64_t* d_idx, double* d_prios64,
+                 float* d_prios32, void* stream) {
+  HB_REQUIRE(rb && rb->prioritized && d_keys && d_idx && n >= 1, "hb_rb_sample: bad arguments");
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = ensure_vals(rb, n, s);
+  if (rc) return rc;
+  // get_indices + get_values + get_total_val  (priority_buffer.py:41-42)
+  rc = hb_st_sample(rb->tree, d_keys, d_idx, rb->vals, rb->vals + n, n, s);
+  if (rc) return rc;
+  prios_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(rb->vals, rb->vals + n, n, d_prios64, d_prios32);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_rb_update_priorities(hb_replay* rb, const int64_t* d_idx, const float* d_td_abs, int64_t n,
+                            void* stream) {
+  HB_REQUIRE(rb && rb->prioritized && d_idx && d_td_abs && n >= 0, "hb_rb_update_priorities: bad arguments");
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = ensure_vals(rb, n, s);
+  if (rc) return rc;
+  priorities_kernel<<<1, 256, 0, s>>>(d_td_abs, n, rb->alpha, rb->vals, rb->prio_range);
+  HB_CUDA(cudaGetLastError());
+  return hb_st_update(rb->tree, d_idx, rb->vals, n, s);
+}
+
+int hb_rb_priority_range(hb_replay* rb, float* h_max, float* h_min, void* stream) {
+  HB_REQUIRE(rb && h_max && h_min, "hb_rb_priority_range: bad arguments");
+  hb::DeviceGuard g(rb->device);
+  float v[2];
+  HB_CUDA(cudaMemcpyAsync(v, rb->prio_range, 8, cudaMemcpyDeviceToHost, (cudaStream_t)stream));
+  HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream));
+  *h_max = v[0];
+  *h_min = v[1];
+  return HB_OK;
+}
+
+int hb_pack_bits(const int8_t* d_in, int bits, uint32_t* d_out, int stride_words, int64_t n, void* stream) {
+  HB_REQUIRE(d_in && d_out && bits >= 1 && stride_words * 32 >= bits && n >= 0, "hb_pack_bits: bad arguments");
+  if (n == 0) return HB_OK;
+  pack_bits_kernel<<<blocks_for(n * stride_words, 256), 256, 0, (cudaStream_t)stream>>>(d_in, bits, d_out,
+                                                                                       stride_words, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_unpack_bits(const uint32_t* d_packed, int stride_words, int bits, int8_t* d_out, int64_t n,
+                   void* stream) {
+  HB_REQUIRE(d_packed && d_out && bits >= 1 && stride_words * 32 >= bits && n >= 0, "hb_unpack_bits: bad arguments");
+  if (n == 0) return HB_OK;
+  unpack_bits_kernel2<<<blocks_for(n * bits, 256), 256, 0, (cudaStream_t)stream>>>(d_packed, stride_words,
+                                                                                  bits, d_out, n);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+}  // extern "C"

@@ -169,12 +169,12 @@ st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
 // ---- ordered update of a contiguous ascending leaf range (PB-3 inserts) ----
 __global__ void st_range_leaf_kernel(float* __restrict__ heap, int64_t cap, int64_t start,
                                      int64_t n, const float* __restrict__ val, float fill,
-                                     float* __restrict__ diff) {
+                                     const float* __restrict__ fill_dev, float* __restrict__ diff) {
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   float* leaf = heap + cap + start + k;
   const float old = *leaf;
-  const float v = val ? val[k] : fill;
+  const float v = val ? val[k] : (fill_dev ? *fill_dev : fill);
   const float d = v - old;
   *leaf = old + d;
   diff[k] = d;
@@ -281,8 +281,22 @@ int hb_st_update(hb_sumtree* t, const int64_t* d_idx, const float* d_val, int64_
   return HB_OK;
 }
 
+static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const float* d_val,
+                                float fill, const float* d_fill, void* stream);
+
 int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
                        void* stream) {
+  return st_update_range_impl(t, start, n, d_val, fill, nullptr, stream);
+}
+
+int hb_st_update_range_dev(hb_sumtree* t, int64_t start, int64_t n, const float* d_fill,
+                           void* stream) {
+  HB_REQUIRE(d_fill != nullptr, "hb_st_update_range_dev: NULL fill");
+  return st_update_range_impl(t, start, n, nullptr, 0.f, d_fill, stream);
+}
+
+static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const float* d_val,
+                                float fill, const float* d_fill, void* stream) {
   HB_REQUIRE(t && n >= 0, "hb_st_update_range: bad arguments");
   if (n == 0) return HB_OK;
   if (start < 0 || start + n > t->cap) {
@@ -302,7 +316,7 @@ int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_v
   }
   const int threads = 256;
   st_range_leaf_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, s>>>(
-      t->heap, t->cap, start, n, d_val, fill, t->scratch);
+      t->heap, t->cap, start, n, d_val, fill, d_fill, t->scratch);
   HB_CUDA(cudaGetLastError());
   if (t->depth > 0) {
     const int64_t widest = n / 2 + 2;  // nodes covered at the deepest internal level

@@ -31,8 +31,19 @@ class SumTreef:
         self._h = C.c_void_p()
         _lib.check(_lib.lib().hb_st_create(capacity, self._device, C.byref(self._h)))
 
+    @classmethod
+    def _from_handle(cls, handle, device, owner):
+        """Non-owning view of a tree that lives inside another object (the replay shard)."""
+        t = cls.__new__(cls)
+        t._device = int(device)
+        t._h = C.c_void_p(handle)
+        t._owner = owner
+        return t
+
     def __del__(self):
         h = getattr(self, "_h", None)
+        if getattr(self, "_owner", None) is not None:
+            return
         if h is not None and h.value:
             try:
                 _lib.lib().hb_st_destroy(h)

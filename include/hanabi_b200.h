@@ -63,6 +63,10 @@ int hb_st_update(hb_sumtree* t, const int64_t* d_idx, const float* d_val, int64_
  * d_val == NULL means every element takes `fill`. */
 int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
                        void* stream);
+/* Same with the fill value read from DEVICE memory at execution time (the replay shard keeps
+ * max_priority on the device: priority_buffer.py:29-31 without a host round trip). */
+int hb_st_update_range_dev(hb_sumtree* t, int64_t start, int64_t n, const float* d_fill,
+                           void* stream);
 /* getIndices(quantiles)  sum_tree.h:52-59 -> getIndex :46-50 -> getIndex_ :92-105 */
 int hb_st_get_indices(hb_sumtree* t, const float* d_q, int64_t* d_out, int64_t n, void* stream);
 /* getValues(indices)  sum_tree.h:65-72 (.at() bounds check -> sticky error flag) */
@@ -161,7 +165,56 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                     int n_steps, uint32_t* d_obs, uint32_t* d_legal, float* d_reward,
                     uint8_t* d_step_type, int32_t* d_action, uint64_t* d_hist, void* stream);
 
-/* @@REPLAY@@ */
+/* ------------------------------------------------------------------------ */
+/* Replay shard (device resident).  Replaces ExperienceBuffer                  */
+/* (hanabi_agents/rlax_dqn/experience_buffer.py:5-97), PriorityBuffer           */
+/* (rlax_dqn/priority_buffer.py:13-52) and the transition bookkeeping of        */
+/* DQNAgent.add_experience_first / add_experience (rlax_rainbow.py:292-308).    */
+/* Observations / legal moves are bit-packed rows as the env emits them.        */
+/* ------------------------------------------------------------------------ */
+typedef struct hb_replay hb_replay;
+
+/* ExperienceBuffer.__init__ :8-19 (prioritized == 0) / PriorityBuffer.__init__ :14-20 (alpha = 0.6:
+ * max_priority = min_priority = alpha, SumTree(capacity)). */
+int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capacity, int prioritized,
+                 float alpha, int device, hb_replay** out);
+int hb_rb_destroy(hb_replay* rb);
+/* what: 0 capacity, 1 size, 2 oldest_entry, 3 obs_stride, 4 legal_words, 5 prioritized */
+int64_t hb_rb_info(const hb_replay* rb, int what);
+/* The shard's sum tree (owned by the shard; NULL when not prioritized). */
+hb_sumtree* hb_rb_tree(hb_replay* rb);
+/* add_transitions (experience_buffer.py:26-81; priority_buffer.py:22-34: the leaves of the slots
+ * about to be written take max_priority first, in get_update_indices order :21-24). */
+int hb_rb_add(hb_replay* rb, const uint32_t* d_obs_tm1, const int32_t* d_act, const float* d_rew,
+              const uint32_t* d_obs_t, const uint32_t* d_lms, const uint8_t* d_term, int64_t n,
+              void* stream);
+/* DQNAgent.add_experience_first (rlax_rainbow.py:292-295): last_obs[step_type == 0] = obs[...] */
+int hb_rb_store_first(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
+                      const uint8_t* d_step_type, int64_t n, void* stream);
+/* DQNAgent.add_experience (rlax_rainbow.py:297-308): appends, in row order, the rows with
+ * step_type != 0 as (last_obs, act, rew, obs, lms, step_type == 2) and refreshes last_obs for them.
+ * Synchronises once to learn the count (the ring cursor is host state, as in the reference). */
+int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                     const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                     int64_t* n_added, void* stream);
+/* __getitem__(indices) (experience_buffer.py:83-87); any output may be NULL. */
+int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,
+                 float* d_rew, uint32_t* d_obs_t, uint32_t* d_lms, uint8_t* d_term, void* stream);
+int hb_rb_check(hb_replay* rb, void* stream);
+/* sample_batch after the keys are drawn (priority_buffer.py:41-42): indices = get_indices(keys);
+ * prios = (get_values(indices) + 1e-10) / get_total_val() in float64 (+ the float32 narrowing the
+ * jitted learner sees).  Keys are explicit so that "identical uniforms" is well defined. */
+int hb_rb_sample(hb_replay* rb, const float* d_keys, int64_t n, int64_t* d_idx, double* d_prios64,
+                 float* d_prios32, void* stream);
+/* update_priorities (priority_buffer.py:48-52): p = (|td| + 1e-10) ** alpha in float32 (power
+ * evaluated in double and rounded once), running max / min, ordered sum-tree scatter. */
+int hb_rb_update_priorities(hb_replay* rb, const int64_t* d_idx, const float* d_td_abs, int64_t n,
+                            void* stream);
+int hb_rb_priority_range(hb_replay* rb, float* h_max, float* h_min, void* stream);
+/* One int8 per bit <-> bit-packed rows (the reference stores np.byte rows, experience_buffer.py:9-12). */
+int hb_pack_bits(const int8_t* d_in, int bits, uint32_t* d_out, int stride_words, int64_t n, void* stream);
+int hb_unpack_bits(const uint32_t* d_packed, int stride_words, int bits, int8_t* d_out, int64_t n,
+                   void* stream);
 
 /* ------------------------------------------------------------------------ */
 /* Q-network: NoisyMLP / MLP forward and backward, policy, learner step.      */

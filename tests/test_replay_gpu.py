@@ -1,0 +1,133 @@
+"""GPU parity of the replay shard (csrc/replay.cu through the C ABI) against oracle/replay.py and
+the fixtures produced by the reference's own ExperienceBuffer: bit-exact ring contents, cursor,
+sampled indices / probabilities given identical uniforms, priorities and every sum-tree node."""
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "replay_ref.npz"))
+
+
+def _all_rows(buf):
+    tr = buf[np.arange(buf.capacity)]
+    return dict(obs_tm1=tr.observation_tm1, act=tr.action_tm1, rew=tr.reward_t, obs_t=tr.observation_t,
+                lms=tr.legal_moves_t, term=tr.terminal_t)
+
+
+def test_reference_fixtures_through_the_numpy_api():
+    from hanabi_agents_b200.rlax_dqn import ExperienceBuffer
+    L, A, cap = int(GOLD["L"]), int(GOLD["A"]), int(GOLD["cap"])
+    buf = ExperienceBuffer(L, A, 1, cap)
+    for k, n in enumerate(GOLD["sizes"]):
+        assert buf.get_update_indices(int(n)) == GOLD["upd%d" % k].tolist()
+        buf.add_transitions(GOLD["in%d_o1" % k], GOLD["in%d_a" % k], GOLD["in%d_r" % k],
+                            GOLD["in%d_o2" % k], GOLD["in%d_lm" % k], GOLD["in%d_t" % k])
+        assert buf.size == int(GOLD["st%d_size" % k]) and buf.oldest_entry == int(GOLD["st%d_oldest" % k])
+        for name, arr in _all_rows(buf).items():
+            np.testing.assert_array_equal(arr, GOLD["st%d_%s" % (k, name)], err_msg="%d %s" % (k, name))
+    tr = buf[GOLD["get_idx"]]
+    for name, got in zip(tr._fields, tr):
+        assert got.dtype == GOLD["get_" + name].dtype, name
+        np.testing.assert_array_equal(got, GOLD["get_" + name])
+    with pytest.raises(IndexError):
+        buf[[cap]]
+
+
+def _rand_tr(rng, n, L, A):
+    return ((rng.random((n, L)) < .2).astype(np.int8), rng.integers(0, A, (n, 1)).astype(np.int8),
+            rng.integers(-3, 3, (n, 1)).astype(np.float64), (rng.random((n, L)) < .2).astype(np.int8),
+            (rng.random((n, A)) < .5).astype(np.int8), rng.random((n, 1)) < .1)
+
+
+@pytest.mark.parametrize("L,A,cap", [(658, 20, 1000), (171, 11, 300), (1280, 48, 512)])
+def test_priority_buffer_parity(L, A, cap):
+    from hanabi_agents_b200.rlax_dqn import PriorityBuffer
+    from oracle.replay import OraclePriorityBuffer
+    rng = np.random.default_rng(cap)
+    dev, ora = PriorityBuffer(L, A, 1, cap), OraclePriorityBuffer(L, A, 1, cap)
+    assert dev.max_priority == np.float32(0.6) and dev.sum_tree.get_capacity() == ora.sum_tree.get_capacity()
+    B = 64
+    for it in range(40):
+        n = int(rng.integers(1, cap // 3))
+        tr = _rand_tr(rng, n, L, A)
+        dev.add_transitions(*tr)
+        ora.add_transitions(*tr)
+        assert (dev.size, dev.oldest_entry) == (ora.size, ora.oldest_entry)
+        np.testing.assert_array_equal(dev.sum_tree.heap()[1:], ora.sum_tree.heap()[1:])
+        u = rng.uniform(0, 1.0 / B, B)
+        idx, prios, batch = dev.sample_batch(B, u)
+        oidx, oprios, obatch = ora.sample_batch(B, u)
+        assert idx == oidx
+        np.testing.assert_array_equal(prios, oprios)
+        for g, o in zip(batch, obatch):
+            np.testing.assert_array_equal(g, o)
+        td = np.abs(rng.standard_normal(B)).astype(np.float32) * (it % 3)
+        dev.update_priorities(idx, td)
+        ora.update_priorities(oidx, td)
+        np.testing.assert_array_equal(dev.sum_tree.heap()[1:], ora.sum_tree.heap()[1:])
+        assert dev.max_priority == np.float32(ora.max_priority)
+        assert dev.min_priority == np.float32(ora.min_priority)
+    for name, arr in _all_rows(dev).items():
+        np.testing.assert_array_equal(arr, dict(obs_tm1=ora._obs_tm1_buf, act=ora._act_tm1_buf, rew=ora._rew_t_buf,
+                                                obs_t=ora._obs_t_buf, lms=ora._lms_t_buf,
+                                                term=ora._terminal_t_buf)[name])
+
+
+def test_masked_append_matches_add_experience():
+    """DQNAgent.add_experience / add_experience_first bookkeeping (rlax_rainbow.py:292-308) on packed
+    device rows vs the same statements on numpy arrays feeding the restated buffer."""
+    import torch
+    from hanabi_agents_b200.rlax_dqn import PriorityBuffer
+    from oracle.replay import OraclePriorityBuffer
+    from test_qnet_gpu import pack_bits
+    L, A, cap, N = 658, 20, 5000, 3000
+    rng = np.random.default_rng(4)
+    dev, ora = PriorityBuffer(L, A, 1, cap), OraclePriorityBuffer(L, A, 1, cap)
+    last_obs = np.zeros((N, L), np.int8)
+    d_last = torch.zeros((N, dev.obs_stride), dtype=torch.int32, device="cuda")
+    to_dev = lambda a: torch.as_tensor(a, device="cuda")  # noqa: E731
+    for it in range(6):
+        obs = (rng.random((N, L)) < .2).astype(np.int8)
+        legal = (rng.random((N, A)) < .5).astype(np.int8)
+        act = rng.integers(0, A, N).astype(np.int32)
+        rew = rng.integers(-2, 2, N).astype(np.float32)
+        st = rng.choice([0, 1, 1, 1, 2], N).astype(np.uint8) if it else np.zeros(N, np.uint8)
+        d_obs = to_dev(pack_bits(obs, dev.obs_stride).view(np.int32))
+        d_leg = to_dev(pack_bits(legal, dev.legal_words).view(np.int32))
+        # reference statements
+        first = st == 0
+        nf = st != 0
+        if nf.any():
+            ora.add_transitions(last_obs[nf], act[nf].reshape(-1, 1), rew[nf].reshape(-1, 1), obs[nf],
+                                legal[nf], (st[nf] == 2).reshape(-1, 1))
+            last_obs[nf] = obs[nf]
+        last_obs[first] = obs[first]
+        # device
+        n_added = dev.add_masked(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
+        dev.store_first(d_last, d_obs, to_dev(st))
+        assert n_added == int(nf.sum())
+        assert (dev.size, dev.oldest_entry) == (ora.size, ora.oldest_entry)
+        np.testing.assert_array_equal(dev.unpack_obs(d_last).cpu().numpy(), last_obs)
+        np.testing.assert_array_equal(dev.sum_tree.heap()[1:], ora.sum_tree.heap()[1:])
+    got = _all_rows(dev)
+    np.testing.assert_array_equal(got["obs_tm1"], ora._obs_tm1_buf)
+    np.testing.assert_array_equal(got["obs_t"], ora._obs_t_buf)
+    np.testing.assert_array_equal(got["act"], ora._act_tm1_buf)
+    np.testing.assert_array_equal(got["rew"], ora._rew_t_buf)
+    np.testing.assert_array_equal(got["lms"], ora._lms_t_buf)
+    np.testing.assert_array_equal(got["term"], ora._terminal_t_buf)
+
+
+def test_uniform_sample_uses_numpy_global_rng():
+    from hanabi_agents_b200.rlax_dqn import ExperienceBuffer
+    buf = ExperienceBuffer(40, 5, 1, 64)
+    rng = np.random.default_rng(0)
+    buf.add_transitions(*_rand_tr(rng, 20, 40, 5))
+    np.random.seed(3)
+    tr = buf.sample(8)
+    np.random.seed(3)
+    idx = np.random.choice(np.arange(64)[:20], size=8)
+    np.testing.assert_array_equal(tr.observation_tm1, buf[idx].observation_tm1)

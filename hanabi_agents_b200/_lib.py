@@ -89,6 +89,7 @@ SIGNATURES = {
     "hb_net_grad": (vp, [vp]),
     "hb_net_set_param": (i32, [vp, i32, i32, vp, i64]),
     "hb_net_get_param": (i32, [vp, i32, i32, vp, i64]),
+    "hb_net_get_target_param": (i32, [vp, i32, i32, vp, i64]),
     "hb_net_refresh": (i32, [vp, vp]),
     "hb_net_sync_target": (i32, [vp, vp]),
     "hb_net_act": (i32, [vp, vp, vp, i32, i64, i32, f32, vp, u64, u64, i64, i32, vp, vp, vp]),

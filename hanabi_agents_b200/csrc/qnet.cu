@@ -47,6 +47,7 @@ struct hb_qnet {
   long long n_eff = 0, n_w = 0, n_b = 0;
   int kinds = 1;                       // master tensors per effective parameter (3 noisy, 1 plain)
   float* master = nullptr;             // [kinds][n_eff]
+  float* tmaster = nullptr;            // masters of the target snapshot (save_weights)
   float* eps = nullptr;                // [n_eff] noise constants (noisy)
   float* adam_m = nullptr;             // [kinds][n_eff]
   float* adam_v = nullptr;
@@ -621,6 +622,7 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   q->n_eff = eoff; q->n_w = woff; q->n_b = boff;
   int rc = HB_OK;
   if (!rc) rc = dev_alloc(&q->master, (size_t)q->kinds * q->n_eff);
+  if (!rc) rc = dev_alloc(&q->tmaster, (size_t)q->kinds * q->n_eff);
   if (!rc && noisy) rc = dev_alloc(&q->eps, (size_t)q->n_eff);
   if (!rc) rc = dev_alloc(&q->adam_m, (size_t)q->kinds * q->n_eff);
   if (!rc) rc = dev_alloc(&q->adam_v, (size_t)q->kinds * q->n_eff);
@@ -640,7 +642,7 @@ int hb_net_destroy(hb_qnet* q) {
   if (!q) return HB_OK;
   hb::DeviceGuard g(q->device);
   cudaDeviceSynchronize();
-  dev_free(q->master); dev_free(q->eps); dev_free(q->adam_m); dev_free(q->adam_v); dev_free(q->grad);
+  dev_free(q->master); dev_free(q->tmaster); dev_free(q->eps); dev_free(q->adam_m); dev_free(q->adam_v); dev_free(q->grad);
   dev_free(q->w16); dev_free(q->w16t); dev_free(q->t16); dev_free(q->beff); dev_free(q->tbeff);
   dev_free(q->scalars);
   dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
@@ -675,7 +677,8 @@ float* hb_net_grad(hb_qnet* q) { return q ? q->grad : nullptr; }
 /* kind: 0 w, 1 b, 2 w_mu, 3 b_mu, 4 w_sigma, 5 b_sigma, 6 eps_w, 7 eps_b, 8 dW (gradient of the
  * effective weight), 9 db.  HOST arrays in the reference's layout: weights [in, out] row-major
  * (noisy_mlp.py:61,73,78), biases [out]. */
-static int net_param_io(hb_qnet* q, int layer, int kind, float* h_data, int64_t n, bool set) {
+static int net_param_io(hb_qnet* q, int layer, int kind, float* h_data, int64_t n, bool set,
+                        bool target = false) {
   HB_REQUIRE(q && h_data && layer >= 0 && layer < q->n_layers && kind >= 0 && kind <= 9,
              "hb_net_param: bad arguments");
   HB_REQUIRE(set ? kind <= 7 : true, "hb_net_set_param: gradients are read-only");
@@ -687,7 +690,7 @@ static int net_param_io(hb_qnet* q, int layer, int kind, float* h_data, int64_t 
              (long long)want, (long long)n);
   hb::DeviceGuard g(q->device);
   float* base;
-  if (kind <= 5) base = q->master + (size_t)(kind / 2) * q->n_eff;
+  if (kind <= 5) base = (target ? q->tmaster : q->master) + (size_t)(kind / 2) * q->n_eff;
   else if (kind <= 7) base = q->eps;
   else base = q->grad;
   base += L.eoff + (is_w ? 0 : (long long)L.N * L.K);
@@ -718,6 +721,10 @@ int hb_net_set_param(hb_qnet* q, int layer, int kind, const float* h_data, int64
 int hb_net_get_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n) {
   return net_param_io(q, layer, kind, h_out, n, false);
 }
+int hb_net_get_target_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n) {
+  HB_REQUIRE(kind >= 0 && kind <= 5, "hb_net_get_target_param: kind 0..5");
+  return net_param_io(q, layer, kind, h_out, n, false, true);
+}
 
 /* Recompute the fp16 effective weights from the masters (after hb_net_set_param). */
 int hb_net_refresh(hb_qnet* q, void* stream) {
@@ -733,6 +740,8 @@ int hb_net_sync_target(hb_qnet* q, void* stream) {
   cudaStream_t s = (cudaStream_t)stream;
   HB_CUDA(cudaMemcpyAsync(q->t16, q->w16, (size_t)q->n_w * 2, cudaMemcpyDeviceToDevice, s));
   HB_CUDA(cudaMemcpyAsync(q->tbeff, q->beff, (size_t)q->n_b * 4, cudaMemcpyDeviceToDevice, s));
+  HB_CUDA(cudaMemcpyAsync(q->tmaster, q->master, (size_t)q->kinds * q->n_eff * 4,
+                          cudaMemcpyDeviceToDevice, s));
   return HB_OK;
 }
 

@@ -161,6 +161,10 @@ class HanabiParallelEnv:
         _lib.check(_lib.lib().hb_env_unpack_legal(self._h, packed.data_ptr(), out.data_ptr(), n, self._s()))
         return out
 
+    def observations_packed(self):
+        """Same tuple with the bit-packed rows (zero copy): what DQNAgent takes on the fast path."""
+        return (self, (self.obs_packed, self.legal_packed))
+
     def observations(self):
         """The `observations` tuple the agents index: observations[1] == (obs, legal) int8 0/1
         (rlax_rainbow.py:278,285); observations[0] is this environment (what the rule-based

@@ -1,0 +1,150 @@
+"""DQNAgent with the reference's verbs (hanabi_agents/rlax_dqn/rlax_rainbow.py:220-365), running
+on the B200: tcgen05 Q-network, device-resident replay shard, fused learner step.
+
+Same constructor (`observation_spec`, `action_spec`, `params`), same methods
+(`explore`, `exploit`, `add_experience_first`, `add_experience`, `update`, `save_weights`,
+`restore_weights`, `requires_vectorized_observation`) and the same state (`train_step`,
+`experience`, `params`).  `observations[1] == (obs, legal)` may be
+  * bit-packed int32 CUDA tensors as HanabiParallelEnv emits them (zero copy), or
+  * 0/1 arrays [N, L] / [N, A] (numpy or CUDA) as the reference's callers pass (packed on the way in).
+Actions come back as a numpy array for numpy input (as the reference returns) and as a CUDA int32
+tensor for CUDA input.
+
+Data parallel: when torch.distributed is initialised, every rank owns its games and its replay
+shard; `update()` all-reduces the flat gradient bucket once (the only collective) and scales by
+1/world inside the fused Adam, so parameters stay identical on every rank.
+"""
+import os
+import pickle
+
+import numpy as np
+
+from .buffers import ExperienceBuffer, PriorityBuffer, _is_cuda
+from .network import QNetwork, init_params
+from .params import RlaxRainbowParams
+
+
+class DQNAgent:
+    def __init__(self, observation_spec, action_spec, params: RlaxRainbowParams = RlaxRainbowParams(),
+                 device=None, noisy=True, adam_eps=3.125e-5, process_group=None):
+        import torch
+        self.torch = torch
+        if not callable(params.epsilon):          # rlax_rainbow.py:227-232
+            eps = params.epsilon
+            params = params._replace(epsilon=lambda ts: eps)
+        if not callable(params.beta_is):
+            beta = params.beta_is
+            params = params._replace(beta_is=lambda ts: beta)
+        self.params = params
+        if device is None:
+            device = torch.cuda.current_device() if torch.cuda.is_available() else 0
+        self.device = torch.device("cuda", int(device))
+        self.n_envs, self.obs_len = int(observation_spec.shape[0]), int(observation_spec.shape[1])
+        self.num_actions = int(action_spec.num_values)
+        self.obs_stride = ((self.obs_len + 31) // 32 + 3) // 4 * 4
+        self.legal_words = (self.num_actions + 31) // 32
+        self.network = QNetwork(self.obs_len, self.obs_stride, list(params.layers), self.num_actions,
+                                params.n_atoms, float(params.atom_vmax), noisy=noisy, device=int(device))
+        # trg_params = network.init(...); online_params = trg_params   (rlax_rainbow.py:250-252)
+        self.network.set_params(init_params(self.obs_len, list(params.layers), self.num_actions,
+                                            params.n_atoms, noisy=noisy, seed=params.seed))
+        self.adam_eps = float(adam_eps)              # optix.adam(lr, eps=3.125e-5)  :257
+        self.train_step = 0
+        self._rng_counter = 0                        # stands in for hk.PRNGSequence(seed)  :234
+        cls = PriorityBuffer if params.use_priority else ExperienceBuffer
+        self.experience = cls(self.obs_len, self.num_actions, 1, params.experience_buffer_size,
+                              device=int(device))
+        self.last_obs = torch.zeros((self.n_envs, self.obs_stride), dtype=torch.int32, device=self.device)
+        self.requires_vectorized_observation = lambda: True
+        self.process_group = process_group
+        self.last_loss = None
+
+    # -- helpers ----------------------------------------------------------------------------
+    def _pack_pair(self, observations):
+        obs, legal = observations[1]
+        exp = self.experience
+        return (exp._packed(obs, self.obs_len, self.obs_stride),
+                exp._packed(legal, self.num_actions, self.legal_words), _is_cuda(obs))
+
+    def _dev(self, x, dtype):
+        return self.experience._vec(x, dtype)
+
+    def _world(self):
+        dist = self.torch.distributed
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_world_size(self.process_group), dist.get_rank(self.process_group)
+        return 1, 0
+
+    def _act(self, observations, greedy):
+        obs, legal, on_device = self._pack_pair(observations)
+        world, rank = self._world()
+        self._rng_counter += 1
+        act = self.network.act(obs, legal, greedy=greedy,
+                               epsilon=0.0 if greedy else float(self.params.epsilon(self.train_step)),
+                               seed=self.params.seed, counter=self._rng_counter,
+                               row0=rank * self.n_envs)
+        return act if on_device else act.cpu().numpy()
+
+    # -- the reference's verbs --------------------------------------------------------------
+    def exploit(self, observations):               # rlax_rainbow.py:277-282
+        return self._act(observations, True)
+
+    def explore(self, observations):               # rlax_rainbow.py:284-290
+        return self._act(observations, False)
+
+    def add_experience_first(self, observations, step_types):      # :292-295
+        obs, _, _ = self._pack_pair(observations)
+        self.experience.store_first(self.last_obs, obs, self._dev(step_types, self.torch.uint8))
+
+    def add_experience(self, observations, actions, rewards, step_types):   # :297-308
+        torch = self.torch
+        obs, legal, _ = self._pack_pair(observations)
+        return self.experience.add_masked(self.last_obs, obs, legal, self._dev(actions, torch.int32),
+                                          self._dev(rewards, torch.float32),
+                                          self._dev(step_types, torch.uint8))
+
+    def update(self, uniforms=None):
+        """One training step (rlax_rainbow.py:310-339).  `uniforms`: optional explicit draws for
+        the stratified keys (default: numpy's global RNG, as the reference)."""
+        B = self.params.train_batch_size
+        exp = self.experience
+        if self.params.use_priority:
+            idx, _, p32, (o1, a, r, o2, _lm, term) = exp.sample_device(B, uniforms)
+        else:
+            indices = np.random.choice(np.arange(0, exp.capacity, dtype=np.int64)[:exp.size], size=B)
+            o1, a, r, o2, _lm, term = exp.gather_packed(indices)
+            idx, p32 = None, None                   # prios = ones  (:317-318)
+        loss, mean = self.network.grads(o1, a, r, o2, term, prios=p32,
+                                        beta=float(self.params.beta_is(self.train_step)),
+                                        discount=float(self.params.discount))
+        world, _ = self._world()
+        if world > 1:
+            self.torch.distributed.all_reduce(self.network.grad_bucket, group=self.process_group)
+        self.network.adam(lr=float(self.params.learning_rate), eps=self.adam_eps, grad_scale=1.0 / world)
+        if self.params.use_priority:
+            exp.update_priorities(idx, loss.abs())  # :333-334
+        if self.train_step % self.params.target_update_period == 0:   # :336-337
+            self.network.sync_target()
+        self.train_step += 1
+        self.last_loss = mean
+        return mean
+
+    def __repr__(self):
+        return f"<rlax_dqn.DQNAgent(params={self.params})>"
+
+    # -- weights (rlax_rainbow.py:344-365) ----------------------------------------------------
+    def save_weights(self, path, fname_part):
+        """Pickles of the haiku-style parameter trees, file names as the reference writes them."""
+        for kind in ("online", "target"):
+            tree = self.network.haiku_tree(target=kind == "target")
+            with open(os.path.join(path, "rlax_rainbow_" + fname_part + "_" + kind + ".pkl"), "wb") as of:
+                pickle.dump(tree, of)
+
+    def restore_weights(self, online_weights_file, trg_weights_file):
+        with open(trg_weights_file, "rb") as iwf:
+            trg = pickle.load(iwf)
+        with open(online_weights_file, "rb") as iwf:
+            online = pickle.load(iwf)
+        self.network.load_haiku_tree(trg)
+        self.network.sync_target()
+        self.network.load_haiku_tree(online)

@@ -113,8 +113,9 @@ class QNetwork:
         if sync_target:
             self.sync_target()
 
-    def get_params(self, with_noise=False, grads=False):
+    def get_params(self, with_noise=False, grads=False, target=False):
         out = []
+        fn = _lib.lib().hb_net_get_target_param if target else _lib.lib().hb_net_get_param
         kinds = ["w", "b"] + (["w_mu", "b_mu", "w_sigma", "b_sigma"] if self.noisy else [])
         if with_noise and self.noisy:
             kinds += ["eps_w", "eps_b"]
@@ -125,15 +126,15 @@ class QNetwork:
             p = {}
             for k in kinds:
                 a = np.empty((fi, fo) if KIND[k] % 2 == 0 else (fo,), np.float32)
-                _lib.check(_lib.lib().hb_net_get_param(self._h, i, KIND[k], a.ctypes.data, a.size))
+                _lib.check(fn(self._h, i, KIND[k], a.ctypes.data, a.size))
                 p[k] = a
             out.append(p)
         return out
 
-    def haiku_tree(self):
+    def haiku_tree(self, target=False):
         """Parameters keyed like the reference's haiku tree (noisy_mlp.py:151)."""
         fmt = "noisy_mlp/~/noisy_linear_%d" if self.noisy else "mlp/~/linear_%d"
-        return {fmt % i: p for i, p in enumerate(self.get_params())}
+        return {fmt % i: p for i, p in enumerate(self.get_params(target=target))}
 
     def load_haiku_tree(self, tree, noise=None):
         layers = []

@@ -253,6 +253,8 @@ float* hb_net_grad(hb_qnet* q);
  * (the trace-time noise constants, noisy_mlp.py:79,87), 8 dW_eff, 9 db_eff (get only). HOST arrays. */
 int hb_net_set_param(hb_qnet* q, int layer, int kind, const float* h_data, int64_t n);
 int hb_net_get_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n);
+/* The same for trg_params (the snapshot taken by hb_net_sync_target); kind 0..5. */
+int hb_net_get_target_param(hb_qnet* q, int layer, int kind, float* h_out, int64_t n);
 /* Recompute the fp16 effective weights after hb_net_set_param. */
 int hb_net_refresh(hb_qnet* q, void* stream);
 /* trg_params = online_params  (rlax_rainbow.py:336-337) */

@@ -130,6 +130,150 @@ def cpu_port_throughput(n_games, seconds, threads, steps_cap=None, warm=2):
     return n_games * done / el, done, el
 
 
+
+def bench_learner(env, obs, legal, reward, stype, action, T, world, args):
+    """Learner updates/s (second half of the BASELINE metric) and acting rows/s for the Rainbow
+    configuration of BASELINE configs[3]: C51, Hanabi-Full 2p, 512x512 noisy MLP, batch 256,
+    prioritized replay shard filled from the self-play outputs of the timed region."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from hanabi_agents_b200.rlax_dqn import DQNAgent, RlaxRainbowParams
+    n = env.n
+    params = RlaxRainbowParams(train_batch_size=256, layers=[512, 512], experience_buffer_size=2 ** 19,
+                               n_atoms=51, atom_vmax=25, seed=SEED)
+    agent = DQNAgent(env.observation_spec(), env.action_spec(), params)
+    exp = agent.experience
+    # transitions between consecutive self-play steps of the same game
+    fill = min(T - 1, (2 ** 19) // n)
+    for t in range(fill):
+        exp.add_transitions(obs[t], action[t + 1], reward[t + 1], obs[t + 1], legal[t + 1],
+                            (stype[t + 1] == 2).to(torch.uint8))
+    np.random.seed(SEED)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(5):
+        agent.update()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    k = args.learner_steps
+    ev0.record()
+    for _ in range(k):
+        agent.update()
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    tt = torch.tensor([ms], device=env.device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt.item())
+    # forward 2.243 MFLOP/sample (folded noisy layers, SURVEY 8d), update = online fwd on 2B rows +
+    # target fwd on B rows + backward (2 fwd-equivalents on B rows) = 5 fwd-equivalents per sample
+    flop_fwd = 2.0 * (658 * 512 + 512 * 512 + 512 * 1020)
+    learner = {"updates_per_s": k / (ms * 1e-3), "ms_per_update": ms / k, "batch_per_gpu": 256,
+               "global_batch": 256 * world, "steps": k, "replay_rows": exp.size,
+               "net": "658-512-512-(20x51), noisy, C51 double-Q, Adam",
+               "algorithmic_tflops": 5 * flop_fwd * 256 * world * k / (ms * 1e-3) / 1e12,
+               "allreduce_bytes": agent.network.n_grad * 4 if world > 1 else 0,
+               "loss": float(agent.last_loss)}
+    # acting: explore() over the n games of this GPU, packed rows resident
+    o, l = obs[T - 1], legal[T - 1]
+    for _ in range(3):
+        agent.explore((None, (o, l)))
+    barrier()
+    ka = args.act_steps
+    ev0.record()
+    for _ in range(ka):
+        agent.explore((None, (o, l)))
+    ev1.record()
+    barrier()
+    ms = ev0.elapsed_time(ev1)
+    tt = torch.tensor([ms], device=env.device)
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms = float(tt.item())
+    tf = flop_fwd * n * ka / (ms * 1e-3) / 1e12
+    peak_tf = 1409.6
+    try:
+        peak_tf = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        pass
+    acting = {"rows_per_s": world * n * ka / (ms * 1e-3), "ms_per_call": ms / ka, "rows_per_gpu": n,
+              "roofline": {"bound": "tensor", "kernel": "gemm_f16_kernel (3 layers) + unpack + policy",
+                           "achieved": tf, "peak": peak_tf, "unit": "TFLOP/s", "frac": tf / peak_tf,
+                           "peak_source": "measured sustained cuBLAS bf16 (MEASURED_PEAKS.json)",
+                           "traffic": None}}
+    return learner, acting
+
+
+def bench_sum_tree(args):
+    """BASELINE configs[2]: capacity 2^22, batch 256 stratified sample + priority update
+    (SURVEY 8d cfg 3), device path; CPU side = the reference's own C++ tree (oracle/_ref)."""
+    import numpy as np
+    import torch
+    from hanabi_agents_b200.sum_tree import SumTreef
+    cap, B = 2 ** 22, 256
+    rng = np.random.default_rng(0)
+    tree = SumTreef(cap)
+    vals = rng.random(cap).astype(np.float32)
+    dv = torch.as_tensor(vals, device="cuda")
+    from hanabi_agents_b200 import _lib
+    for c0 in range(0, cap, 65536):
+        _lib.check(_lib.lib().hb_st_update_range(tree._h, c0, 65536, dv[c0:c0 + 65536].data_ptr(), 0.0,
+                                                 _lib.current_stream_ptr()))
+    iters = args.tree_iters
+    keys = torch.as_tensor((np.linspace(1 / B, 1, B)[None, :] - rng.uniform(0, 1 / B, (iters, B))).astype(np.float32),
+                           device="cuda")
+    newv = torch.as_tensor(rng.random((iters, B)).astype(np.float32), device="cuda")
+
+    def it(i):
+        idx, _, _ = tree.sample(keys[i])
+        tree.update_values(idx, newv[i])
+
+    for i in range(10):
+        it(i)
+    torch.cuda.synchronize()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    for i in range(iters):
+        it(i)
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1)
+    out = {"capacity": cap, "batch": B, "iters": iters, "iters_per_s": iters / (ms * 1e-3),
+           "us_per_iter": 1e3 * ms / iters,
+           "algorithmic_GBps": 70656 * iters / (ms * 1e-3) / 1e9,
+           "note": "latency-bound: 22 dependent levels; 2 launches per iteration"}
+    # CPU: the reference's own pybind module, one thread (parity mode) -- bounded sample
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
+        import sum_tree as ref_mod
+        t0 = time.perf_counter()
+        rt = ref_mod.SumTreef(cap)
+        for c0 in range(0, cap, 65536):
+            rt.update_values(list(range(c0, c0 + 65536)), vals[c0:c0 + 65536].tolist())
+        build_s = time.perf_counter() - t0
+        kk, vv = keys.cpu().numpy(), newv.cpu().numpy()
+        n_cpu = min(iters, 2000)
+        t0 = time.perf_counter()
+        for i in range(n_cpu):
+            ix = rt.get_indices(kk[i])
+            rt.get_values(ix)
+            rt.update_values(ix, vv[i])
+        el = time.perf_counter() - t0
+        out["cpu_reference"] = {"iters_per_s": n_cpu / el, "us_per_iter": 1e6 * el / n_cpu, "kind": "reference",
+                                "threads": int(os.environ.get("OMP_NUM_THREADS", os.cpu_count() or 1)),
+                                "build_and_fill_s": build_s,
+                                "sample": "%d iterations through the reference's pybind module" % n_cpu}
+    except Exception as e:  # the prebuilt module may be missing on a box without oracle/_ref
+        out["cpu_reference"] = {"unavailable": repr(e)[:200]}
+    return out
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -244,10 +388,14 @@ def run_ours(args):
     h2d = 4 * n
     d2h = n * (env.obs_stride * 4 + env.legal_words * 4 + 4 + 1 + 4)
 
+    learner = acting = None
+    if not args.no_learner:
+        learner, acting = bench_learner(env, obs, legal, reward, stype, action, T, world, args)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
+    tree = None if args.no_tree else bench_sum_tree(args)
 
     # ---- roofline of the dominant kernel (selfplay_kernel), live from the timed region
     peak, which = peaks()
@@ -292,6 +440,9 @@ def run_ours(args):
         "gpu_launches": launches,
         "roofline": roof,
         "cpu_baseline": cpu,
+        "learner": learner,
+        "acting": acting,
+        "sum_tree": tree,
     }
     print(json.dumps(out))
     if world > 1:
@@ -308,6 +459,11 @@ def main():
     ap.add_argument("--fuse", type=int, default=64, help="env steps fused per launch")
     ap.add_argument("--e2e-steps", type=int, default=64)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--learner-steps", type=int, default=300)
+    ap.add_argument("--act-steps", type=int, default=20)
+    ap.add_argument("--tree-iters", type=int, default=3000)
+    ap.add_argument("--no-learner", action="store_true")
+    ap.add_argument("--no-tree", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps > 2048:

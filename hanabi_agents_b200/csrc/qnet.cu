@@ -472,7 +472,7 @@ int launch_unpack(const uint32_t* packed, int stride, long long rows, __half* ou
 // q (and logits when given).
 int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0, long long rows,
             __half* const* hbuf, __half* const* hbuf_t, int ld_t, float* logits, float* q_out, int ldq,
-            cudaStream_t s) {
+            cudaStream_t s, const uint32_t* x_bits = nullptr) {
   const __half* in = x0;
   int ld_in = net->tab.l[0].K;
   const int nl = net->n_layers;
@@ -488,7 +488,10 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
       ep.ld_out = g.N;
       ep.out16_t = hbuf_t ? hbuf_t[l] : nullptr;
       ep.ld_out_t = ld_t;
-      rc = tc::gemm<tc::EPI_F16>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
+      if (l == 0 && x_bits != nullptr)   // bits expanded inside the kernel: no fp16 copy of the observations
+        rc = tc::gemm_bits<tc::EPI_F16>(x_bits, net->obs_stride, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
+      else
+        rc = tc::gemm<tc::EPI_F16>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
       in = hbuf[l];
       ld_in = g.N;
     } else if (net->n_atoms > 1) {
@@ -763,13 +766,16 @@ int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int l
   const int ldq = q->n_atoms > 1 ? q->A : q->tab.l[q->n_layers - 1].N;
   for (long long r0 = 0; r0 < n; r0 += chunk) {
     const long long rows = n - r0 < chunk ? n - r0 : chunk;
-    rc = launch_unpack(d_obs + r0 * q->obs_stride, q->obs_stride, rows, q->act_x, q->tab.l[0].K,
-                       nullptr, 0, 0, s);
-    if (rc) return rc;
+    const bool fused = q->n_layers > 1;           // layer 0 reads the packed rows directly
+    if (!fused) {
+      rc = launch_unpack(d_obs + r0 * q->obs_stride, q->obs_stride, rows, q->act_x, q->tab.l[0].K,
+                         nullptr, 0, 0, s);
+      if (rc) return rc;
+    }
     __half* hb[kMaxLayers];
     for (int l = 0; l < kMaxLayers; ++l) hb[l] = q->act_h[l & 1];
     rc = forward(q, use_target ? q->t16 : q->w16, use_target ? q->tbeff : q->beff, q->act_x, rows, hb,
-                 nullptr, 0, nullptr, q->act_q, ldq, s);
+                 nullptr, 0, nullptr, q->act_q, ldq, s, fused ? d_obs + r0 * q->obs_stride : nullptr);
     if (rc) return rc;
     policy_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, s>>>(
         q->act_q, ldq, d_legal + r0 * legal_words, legal_words, q->A, rows, greedy, epsilon,
@@ -886,12 +892,13 @@ int hb_net_forward(hb_qnet* q, const uint32_t* d_obs, int64_t n, int use_target,
   cudaStream_t s = (cudaStream_t)stream;
   int rc = ensure_act_ws(q, n);
   if (rc) return rc;
-  if ((rc = launch_unpack(d_obs, q->obs_stride, n, q->act_x, q->tab.l[0].K, nullptr, 0, 0, s))) return rc;
+  const bool fused = q->n_layers > 1;
+  if (!fused && (rc = launch_unpack(d_obs, q->obs_stride, n, q->act_x, q->tab.l[0].K, nullptr, 0, 0, s))) return rc;
   __half* hb[kMaxLayers];
   for (int l = 0; l < kMaxLayers; ++l) hb[l] = q->act_h[l & 1];
   const int ldq = q->n_atoms > 1 ? q->A : q->tab.l[q->n_layers - 1].N;
   rc = forward(q, use_target ? q->t16 : q->w16, use_target ? q->tbeff : q->beff, q->act_x, n, hb,
-               nullptr, 0, d_logits, q->act_q, ldq, s);
+               nullptr, 0, d_logits, q->act_q, ldq, s, fused ? d_obs : nullptr);
   if (rc) return rc;
   HB_CUDA(cudaMemcpy2DAsync(d_q, (size_t)q->A * 4, q->act_q, (size_t)ldq * 4, (size_t)q->A * 4, (size_t)n,
                             cudaMemcpyDeviceToDevice, s));

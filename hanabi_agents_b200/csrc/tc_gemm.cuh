@@ -3,17 +3,20 @@
 //   D[M, N] = A[M, K] . B[N, K]^T      A, B fp16, both K-major (row-major with K contiguous),
 //                                      fp32 accumulation in tensor memory.
 //
-// One CTA computes one 128 x 128 tile of D:
-//   warp 0     TMA producer: cp.async.bulk.tensor boxes of 128 rows x 64 fp16 (= one 128-byte
-//              swizzle span) for A and B into a kStages-deep shared-memory ring
-//   warp 1     MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::f16 (M128 N128 K16),
-//              four per k-block, accumulating into 128 TMEM columns; tcgen05.commit releases the
-//              ring slot / signals the epilogue
+// Persistent kernel, one CTA per SM, tiles of 128 x BN (BN = 128 or 256):
+//   warp 0     TMA producer: cp.async.bulk.tensor boxes of 128 (A) / BN (B) rows x 64 fp16 (= one
+//              128-byte swizzle span) into a 6 x 32 KB or 4 x 48 KB shared-memory ring that keeps
+//              running across tiles
+//   warp 1     MMA issuer: one lane issues tcgen05.mma.cta_group::1.kind::f16 (M128 x N BN x K16),
+//              four per k-block, into one of TWO TMEM accumulators (2 x BN columns);
+//              tcgen05.commit releases the ring slot / hands the accumulator to the epilogue
 //   warp 2     allocates / frees tensor memory
-//   warps 4-7  epilogue: tcgen05.ld 32 lanes x 32 columns at a time, fused bias / ReLU / gate /
-//              categorical head, vectorised global stores
-// Two CTAs fit one SM (3 stages x 32 KB each, 128 of 512 TMEM columns each), so one CTA's
-// epilogue overlaps the other's main loop.
+//   warps 4-11 epilogue (two warps per TMEM lane quarter, half the columns each) of the previous tile while the next one is being multiplied:
+//              tcgen05.ld 32 lanes x 32 columns at a time, fused bias / ReLU / gate / transposed
+//              copy / categorical head, vectorised global stores
+// BN = 256 halves the shared-memory fill traffic per flop (A 16 KB + B 32 KB per 128x256x64
+// block = 87 flop/B against 64 flop/B at BN = 128): the v1 one-tile-per-CTA kernel sat at 16-22 %
+// tensor-pipe activity, bound by CTA set-up and L2 -> SM fill (profiles/r01_gemm_acting_v1_*).
 //
 // Replaces the jnp.dot calls of NoisyLinear (hanabi_agents/rlax_dqn/noisy_mlp.py:62,80) and their
 // jax.grad transposes (rlax_rainbow.py:203-213).
@@ -25,13 +28,14 @@
 
 namespace tc {
 
-constexpr int BM = 128, BN = 128, BK = 64;        // CTA tile; BK fp16 = 128 B = swizzle span
+constexpr int BM = 128, BK = 64;                  // CTA tile rows; BK fp16 = 128 B = swizzle span
 constexpr int UMMA_K = 16;
-constexpr int kStages = 3;
-constexpr int kStageBytes = (BM + BN) * BK * 2;   // 32 KB
-constexpr int kTmemCols = 128;
-constexpr int kThreads = 256;
-constexpr int kSmemBytes = kStages * kStageBytes + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int kThreads = 384;                     // 4 control warps + 8 epilogue warps
+// tile width BN_ is 128 or 256 (template parameter): 6 x 32 KB or 4 x 48 KB of operand ring
+__host__ __device__ constexpr int stages_for(int bn) { return bn == 256 ? 4 : 6; }
+__host__ __device__ constexpr int smem_bytes_for(int bn) {
+  return stages_for(bn) * (BM + bn) * BK * 2 + 1024 /*align slack*/ + 256 /*barriers*/;
+}
 
 enum Epilogue {
   EPI_F16 = 0,   // out16[m, n] = act(alpha * acc + bias[n]) (* gate(m, n) > 0), optional transposed copy
@@ -58,6 +62,9 @@ struct EpiParams {
   int n_atoms;               // 51
   float z0, dz;              // atoms z_j = z0 + j * dz
   float q_scale;             // 1/n_atoms (rlax_rainbow.py:118 uses mean) or 1 (sum)
+  // ABITS kernels: the A operand is bit-packed rows (bit k of row m at word k>>5, position k&31)
+  const uint32_t* a_bits;    // [M, a_stride] words
+  int a_stride;
 };
 
 // ---------------------------------------------------------------- PTX wrappers ----
@@ -71,6 +78,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
                "r"(bytes)
                : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
   uint32_t ok;
@@ -183,35 +193,197 @@ __host__ __device__ constexpr uint32_t make_idesc_f16(int m, int n) {
          | ((uint32_t)(m >> 4) << 24); // m_dim
 }
 
+// bias[nb .. nb+W) -> x (zero where there is no bias / beyond N).  N is a multiple of 4 and the
+// array is 16-byte aligned, so whole float4 groups are either inside or outside.  The loads carry
+// no dependence on one another: the v1 epilogue's per-element predicated loads serialised on the
+// load latency and cost 24k cycles per 128 x 256 tile (profiles/r01_gemm_epilogue.md).
+template <int W>
+__device__ __forceinline__ void load_bias(const float* __restrict__ bias, int nb, int N, float (&x)[W]) {
+  float4 b[W / 4];
+#pragma unroll
+  for (int j = 0; j < W / 4; ++j) {
+    b[j] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (bias != nullptr && nb + 4 * j < N) b[j] = __ldg(reinterpret_cast<const float4*>(bias + nb) + j);
+  }
+#pragma unroll
+  for (int j = 0; j < W / 4; ++j) {
+    x[4 * j] = b[j].x; x[4 * j + 1] = b[j].y; x[4 * j + 2] = b[j].z; x[4 * j + 3] = b[j].w;
+  }
+}
+
+// ---------------------------------------------------------------------- epilogue ----
+// One epilogue warp: rows m0 + ew*32 + lane of the tile whose accumulator starts at TMEM column
+// `acc_col` (thread = TMEM lane = D row, 32 fp32 columns per tcgen05.ld).
+template <int EPI, int BN_>
+__device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_col, int m0, int n0,
+                                              int ew, int half, int lane, const EpiParams& ep) {
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc_col;
+  const bool row_ok = (m0 + ew * 32 + lane) < ep.M;
+  const int m = m0 + ew * 32 + lane;
+  if (EPI == EPI_C51) {
+    // BN_/64 actions per tile, 64 columns each (n_atoms real + pad)
+#pragma unroll 1
+    for (int h = half * (BN_ / 128); h < (half + 1) * (BN_ / 128); ++h) {
+      uint32_t v0[32], v1[32];
+      tmem_ld32(lane_addr + h * 64, v0);
+      tmem_ld32(lane_addr + h * 64 + 32, v1);
+      const int nb = n0 + h * 64;
+      if (nb >= ep.N) continue;
+      float x[64];
+      load_bias<64>(ep.bias, nb, ep.N, x);           // vector loads issued together
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        x[j] += ep.alpha * __uint_as_float(v0[j]);
+        x[32 + j] += ep.alpha * __uint_as_float(v1[j]);
+      }
+      if (row_ok && ep.out32 != nullptr) {
+        float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+        for (int j = 0; j < 16; ++j) dst[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
+      }
+      if (row_ok && ep.q != nullptr) {
+        // pad columns (j >= n_atoms) become -inf: they add exp(-inf) = 0 to both sums, so the
+        // loops below run over all 64 columns without per-element predicates; four partial
+        // accumulators break the dependent-add chains
+#pragma unroll
+        for (int j = 32; j < 64; ++j)
+          if (j >= ep.n_atoms) x[j] = -INFINITY;
+        if (ep.n_atoms < 32) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (j >= ep.n_atoms) x[j] = -INFINITY;
+        }
+        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+        for (int j = 0; j < 64; ++j) m4[j & 3] = fmaxf(m4[j & 3], x[j]);
+        const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+        const float kLog2e = 1.4426950408889634f;
+        const float mxs = mx * kLog2e;
+        float d4[4] = {0.f, 0.f, 0.f, 0.f}, n4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int j = 0; j < 64; ++j) {
+          const float e = exp2f(fmaf(x[j], kLog2e, -mxs));
+          d4[j & 3] += e;
+          n4[j & 3] = fmaf(e, ep.z0 + (float)j * ep.dz, n4[j & 3]);
+        }
+        const float den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
+        const float num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
+        ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
+      }
+    }
+  } else {
+#pragma unroll 1
+    for (int c = half * (BN_ / 64); c < (half + 1) * (BN_ / 64); ++c) {
+      uint32_t v[32];
+      tmem_ld32(lane_addr + c * 32, v);
+      const int nb = n0 + c * 32;
+      if (nb >= ep.N) continue;                    // warp-uniform
+      float x[32];
+      load_bias<32>(ep.bias, nb, ep.N, x);           // vector loads issued together
+#pragma unroll
+      for (int j = 0; j < 32; ++j) x[j] += ep.alpha * __uint_as_float(v[j]);
+      if (EPI == EPI_F16) {
+        if (ep.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
+        }
+        if (ep.gate != nullptr && row_ok) {
+          const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + nb);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4) {
+            if (nb + 8 * j4 < ep.N) {
+              const uint4 gv = __ldg(g + j4);
+              const __half2* gh = reinterpret_cast<const __half2*>(&gv);
+#pragma unroll
+              for (int j = 0; j < 4; ++j) {
+                const float2 f = __half22float2(gh[j]);
+                if (!(f.x > 0.f)) x[8 * j4 + 2 * j] = 0.f;
+                if (!(f.y > 0.f)) x[8 * j4 + 2 * j + 1] = 0.f;
+              }
+            }
+          }
+        }
+        uint32_t p[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
+          p[j] = *reinterpret_cast<const uint32_t*>(&h2);
+        }
+        if (row_ok && ep.out16 != nullptr) {
+          uint4* dst = reinterpret_cast<uint4*>(ep.out16 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+          for (int j4 = 0; j4 < 4; ++j4)
+            if (nb + 8 * j4 < ep.N) dst[j4] = make_uint4(p[4 * j4], p[4 * j4 + 1], p[4 * j4 + 2], p[4 * j4 + 3]);
+        }
+        if (ep.out16_t != nullptr && row_ok) {
+          // transposed copy: for a fixed column the warp's 32 rows are contiguous
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (nb + j < ep.N)
+              ep.out16_t[(size_t)(nb + j) * ep.ld_out_t + m] = __float2half_rn(x[j]);
+        }
+      } else {  // EPI_F32
+        if (row_ok) {
+          float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
+#pragma unroll
+          for (int j4 = 0; j4 < 8; ++j4) {
+            if (nb + 4 * j4 < ep.N) {
+              float4 o = make_float4(x[4 * j4], x[4 * j4 + 1], x[4 * j4 + 2], x[4 * j4 + 3]);
+              if (ep.beta != 0.f) {
+                const float4 old = dst[j4];
+                o.x += ep.beta * old.x; o.y += ep.beta * old.y;
+                o.z += ep.beta * old.z; o.w += ep.beta * old.w;
+              }
+              dst[j4] = o;
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
 // ---------------------------------------------------------------------- kernel ----
-template <int EPI>
-__global__ void __launch_bounds__(kThreads, 2)
+// Persistent: grid = min(#tiles, #SMs); CTA c computes tiles c, c + grid, ... (n fastest, so the
+// CTAs working at the same time share A tiles through L2).  The TMEM accumulator is double
+// buffered: the MMA warp fills buffer (i & 1) of its i-th tile while the epilogue warps drain the
+// other one.
+template <int EPI, int BN_, bool ABITS>
+__global__ void __launch_bounds__(kThreads, 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                 int K, EpiParams ep) {
+  constexpr int kSt = stages_for(BN_);
+  constexpr int kStB = (BM + BN_) * BK * 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = (uint64_t*)(smem + kStages * kStageBytes);
-  uint64_t* empty_bar = full_bar + kStages;
-  uint64_t* acc_bar = empty_bar + kStages;
-  uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
+  uint64_t* full_bar = (uint64_t*)(smem + kSt * kStB);
+  uint64_t* empty_bar = full_bar + kSt;
+  uint64_t* acc_full = empty_bar + kSt;
+  uint64_t* acc_empty = acc_full + 2;
+  uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m0 = blockIdx.y * BM, n0 = blockIdx.x * BN;
   const int num_kb = (K + BK - 1) / BK;
+  const int tiles_n = (ep.N + BN_ - 1) / BN_;
+  const int tiles_m = (ep.M + BM - 1) / BM;
+  const int total = tiles_m * tiles_n;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
     prefetch_tmap(&tmap_b);
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < kStages; ++s) {
-      mbar_init(&full_bar[s], 1);
+    for (int s = 0; s < kSt; ++s) {
+      mbar_init(&full_bar[s], ABITS ? 3 : 1);        // TMA thread (+ the two unpacking warps)
       mbar_init(&empty_bar[s], 1);
     }
-    mbar_init(acc_bar, 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&acc_full[b], 1);
+      mbar_init(&acc_empty[b], 8);                   // one arrival per epilogue warp
+    }
     fence_barrier_init();
   }
-  if (warp == 2) tmem_alloc(tmem_slot, kTmemCols);
+  if (warp == 2) tmem_alloc(tmem_slot, 2 * BN_);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -219,159 +391,114 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
 
   if (warp == 0) {
     if (lane == 0) {
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t ph = (kb / kStages) & 1;
-        mbar_wait(&empty_bar[s], ph ^ 1);            // slot free (first pass: returns at once)
-        uint8_t* a_dst = smem + s * kStageBytes;
-        uint8_t* b_dst = a_dst + BM * BK * 2;
-        mbar_expect_tx(&full_bar[s], kStageBytes);
-        tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
-        tma_load_2d(b_dst, &tmap_b, &full_bar[s], kb * BK, n0);
+      int it = 0;                                    // k-blocks issued so far (ring position)
+      for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN_;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % kSt;
+          const uint32_t ph = (it / kSt) & 1;
+          mbar_wait(&empty_bar[s], ph ^ 1);          // slot free (first pass: returns at once)
+          uint8_t* a_dst = smem + s * kStB;
+          uint8_t* b_dst = a_dst + BM * BK * 2;
+          if (ABITS) {
+            mbar_expect_tx(&full_bar[s], BN_ * BK * 2);
+          } else {
+            mbar_expect_tx(&full_bar[s], kStB);
+            tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
+          }
+          tma_load_2d(b_dst, &tmap_b, &full_bar[s], kb * BK, n0);
+        }
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
-      constexpr uint32_t idesc = make_idesc_f16(BM, BN);
-      for (int kb = 0; kb < num_kb; ++kb) {
-        const int s = kb % kStages;
-        const uint32_t ph = (kb / kStages) & 1;
-        mbar_wait(&full_bar[s], ph);
+      constexpr uint32_t idesc = make_idesc_f16(BM, BN_);
+      int it = 0, i = 0;
+      for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+        const int buf = i & 1;
+        mbar_wait(&acc_empty[buf], ((i >> 1) & 1) ^ 1);   // epilogue has drained this buffer
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + s * kStageBytes);
-        const uint32_t b_addr = a_addr + BM * BK * 2;
+        const uint32_t acc = tmem_base + buf * BN_;
+        for (int kb = 0; kb < num_kb; ++kb, ++it) {
+          const int s = it % kSt;
+          const uint32_t ph = (it / kSt) & 1;
+          mbar_wait(&full_bar[s], ph);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem + s * kStB);
+          const uint32_t b_addr = a_addr + BM * BK * 2;
 #pragma unroll
-        for (int k = 0; k < BK / UMMA_K; ++k) {
-          const uint64_t adesc = make_smem_desc(a_addr + k * UMMA_K * 2);
-          const uint64_t bdesc = make_smem_desc(b_addr + k * UMMA_K * 2);
-          umma_f16(tmem_base, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = make_smem_desc(a_addr + k * UMMA_K * 2);
+            const uint64_t bdesc = make_smem_desc(b_addr + k * UMMA_K * 2);
+            umma_f16(acc, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty_bar[s]);                // frees the slot when these MMAs retire
         }
-        umma_commit(&empty_bar[s]);                  // frees the slot when these MMAs retire
+        umma_commit(&acc_full[buf]);                 // accumulator complete
       }
-      umma_commit(acc_bar);                          // accumulator complete
+    }
+  } else if (ABITS && (warp == 2 || warp == 3)) {
+    // A operand straight from the bit-packed observation rows: thread p owns rows p and p + 64 of
+    // the tile, keeps their packed words in registers and expands 8 bits -> 8 fp16 (one 16-byte
+    // chunk) at a time into the 128-byte-swizzled layout the MMA descriptor expects
+    // (chunk c of row r at r*128 + ((c ^ (r & 7)) << 4)).
+    const int p = (warp - 2) * 32 + lane;
+    int it = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+      const int m0 = (t / tiles_n) * BM;
+      for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        const int s = it % kSt;
+        const uint32_t ph = (it / kSt) & 1;
+        uint2 w[2];
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const int m = m0 + p + 64 * rr;
+          w[rr] = make_uint2(0u, 0u);
+          if (m < ep.M && 2 * kb + 1 < ep.a_stride)
+            w[rr] = __ldg(reinterpret_cast<const uint2*>(ep.a_bits + (size_t)m * ep.a_stride) + kb);
+        }
+        mbar_wait(&empty_bar[s], ph ^ 1);
+        uint8_t* a_dst = smem + s * kStB;
+#pragma unroll
+        for (int rr = 0; rr < 2; ++rr) {
+          const int r = p + 64 * rr;
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const uint32_t byte = ((c < 4 ? w[rr].x : w[rr].y) >> (8 * (c & 3))) & 0xffu;
+            uint32_t h[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const uint32_t two = (byte >> (2 * i)) & 3u;
+              h[i] = ((two | (two << 15)) & 0x00010001u) * 0x3c00u;   // half(1.0) = 0x3c00
+            }
+            *reinterpret_cast<uint4*>(a_dst + r * 128 + ((c ^ (r & 7)) << 4)) = make_uint4(h[0], h[1], h[2], h[3]);
+          }
+        }
+        fence_proxy_async();                         // generic-proxy writes -> visible to the MMA
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&full_bar[s]);
+      }
     }
   } else if (warp >= 4) {
-    const int ew = warp - 4;                         // == warp % 4: the TMEM lane quarter it may read
-    mbar_wait(acc_bar, 0);
-    tc_fence_after();
-    const int m = m0 + ew * 32 + lane;
-    const bool row_ok = m < ep.M;
-    const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
-    if (EPI == EPI_C51) {
-      // two actions per 128-column tile, 64 columns each (n_atoms real + pad)
-#pragma unroll 1
-      for (int h = 0; h < 2; ++h) {
-        uint32_t v0[32], v1[32];
-        tmem_ld32(lane_addr + h * 64, v0);
-        tmem_ld32(lane_addr + h * 64 + 32, v1);
-        const int nb = n0 + h * 64;
-        if (nb >= ep.N) continue;
-        float x[64];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          x[j] = ep.alpha * __uint_as_float(v0[j]) + (ep.bias ? __ldg(ep.bias + nb + j) : 0.f);
-          x[32 + j] = ep.alpha * __uint_as_float(v1[j]) + (ep.bias ? __ldg(ep.bias + nb + 32 + j) : 0.f);
-        }
-        if (row_ok && ep.out32 != nullptr) {
-          float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) dst[j] = make_float4(x[4 * j], x[4 * j + 1], x[4 * j + 2], x[4 * j + 3]);
-        }
-        if (row_ok && ep.q != nullptr) {
-          float mx = -INFINITY;
-#pragma unroll
-          for (int j = 0; j < 64; ++j)
-            if (j < ep.n_atoms) mx = fmaxf(mx, x[j]);
-          float den = 0.f, num = 0.f;
-#pragma unroll
-          for (int j = 0; j < 64; ++j)
-            if (j < ep.n_atoms) {
-              const float e = __expf(x[j] - mx);
-              den += e;
-              num += e * (ep.z0 + j * ep.dz);
-            }
-          ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
-        }
-      }
-    } else {
-#pragma unroll 1
-      for (int c = 0; c < BN / 32; ++c) {
-        uint32_t v[32];
-        tmem_ld32(lane_addr + c * 32, v);
-        const int nb = n0 + c * 32;
-        if (nb >= ep.N) continue;                    // warp-uniform
-        float x[32];
-#pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float t = ep.alpha * __uint_as_float(v[j]);
-          if (ep.bias != nullptr && nb + j < ep.N) t += __ldg(ep.bias + nb + j);
-          x[j] = t;
-        }
-        if (EPI == EPI_F16) {
-          if (ep.relu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) x[j] = fmaxf(x[j], 0.f);
-          }
-          if (ep.gate != nullptr && row_ok) {
-            const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + nb);
-#pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4) {
-              if (nb + 8 * j4 < ep.N) {
-                const uint4 gv = __ldg(g + j4);
-                const __half2* gh = reinterpret_cast<const __half2*>(&gv);
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                  const float2 f = __half22float2(gh[j]);
-                  if (!(f.x > 0.f)) x[8 * j4 + 2 * j] = 0.f;
-                  if (!(f.y > 0.f)) x[8 * j4 + 2 * j + 1] = 0.f;
-                }
-              }
-            }
-          }
-          uint32_t p[16];
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
-            p[j] = *reinterpret_cast<const uint32_t*>(&h2);
-          }
-          if (row_ok && ep.out16 != nullptr) {
-            uint4* dst = reinterpret_cast<uint4*>(ep.out16 + (size_t)m * ep.ld_out + nb);
-#pragma unroll
-            for (int j4 = 0; j4 < 4; ++j4)
-              if (nb + 8 * j4 < ep.N) dst[j4] = make_uint4(p[4 * j4], p[4 * j4 + 1], p[4 * j4 + 2], p[4 * j4 + 3]);
-          }
-          if (ep.out16_t != nullptr && row_ok) {
-            // transposed copy: for a fixed column the warp's 32 rows are contiguous
-#pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (nb + j < ep.N)
-                ep.out16_t[(size_t)(nb + j) * ep.ld_out_t + m] = __float2half_rn(x[j]);
-          }
-        } else {  // EPI_F32
-          if (row_ok) {
-            float4* dst = reinterpret_cast<float4*>(ep.out32 + (size_t)m * ep.ld_out + nb);
-#pragma unroll
-            for (int j4 = 0; j4 < 8; ++j4) {
-              if (nb + 4 * j4 < ep.N) {
-                float4 o = make_float4(x[4 * j4], x[4 * j4 + 1], x[4 * j4 + 2], x[4 * j4 + 3]);
-                if (ep.beta != 0.f) {
-                  const float4 old = dst[j4];
-                  o.x += ep.beta * old.x; o.y += ep.beta * old.y;
-                  o.z += ep.beta * old.z; o.w += ep.beta * old.w;
-                }
-                dst[j4] = o;
-              }
-            }
-          }
-        }
-      }
+    const int ew = warp & 3;                         // the TMEM lane quarter this warp may read
+    const int half = (warp - 4) >> 2;                // which half of the tile's columns it drains
+    int i = 0;
+    for (int t = blockIdx.x; t < total; t += gridDim.x, ++i) {
+      const int buf = i & 1;
+      const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN_;
+      mbar_wait(&acc_full[buf], (i >> 1) & 1);
+      tc_fence_after();
+      epilogue_tile<EPI, BN_>(tmem_base, (uint32_t)(buf * BN_), m0, n0, ew, half, lane, ep);
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    tmem_dealloc(tmem_base, 2 * BN_);
   }
 }
 

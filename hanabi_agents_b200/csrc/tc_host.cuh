@@ -23,9 +23,10 @@ inline EncodeTiledFn encode_fn() {
   return fn;
 }
 
-// fp16 matrix [rows, cols] with leading dimension ld (elements), K-major; box = 128 rows x 64 cols,
+// fp16 matrix [rows, cols] with leading dimension ld (elements), K-major; box = box_rows x 64 cols,
 // 128-byte swizzle; out-of-range parts of a box read as zero.
-inline int make_tmap(CUtensorMap* map, const __half* ptr, int64_t rows, int64_t cols, int64_t ld) {
+inline int make_tmap(CUtensorMap* map, const __half* ptr, int64_t rows, int64_t cols, int64_t ld,
+                     int box_rows) {
   EncodeTiledFn fn = encode_fn();
   if (fn == nullptr) { hb::set_error("cuTensorMapEncodeTiled is not available"); return HB_ERR_CUDA; }
   if (((uintptr_t)ptr & 15) != 0 || (ld * 2) % 16 != 0 || rows < 1 || cols < 1) {
@@ -34,7 +35,7 @@ inline int make_tmap(CUtensorMap* map, const __half* ptr, int64_t rows, int64_t 
   }
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
   cuuint64_t strides[1] = {(cuuint64_t)ld * 2};
-  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)BM};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, (void*)ptr, dims, strides, box, estr,
                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
@@ -43,35 +44,69 @@ inline int make_tmap(CUtensorMap* map, const __half* ptr, int64_t rows, int64_t 
   return HB_OK;
 }
 
-template <int EPI>
+inline int sm_count() {
+  static int n[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) return 148;
+  if (n[dev] == 0) n[dev] = hb::num_sms(dev);
+  return n[dev];
+}
+
+template <int EPI, int BN_, bool ABITS = false>
 inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
                        const EpiParams& ep, cudaStream_t stream) {
   static bool configured[64] = {false};
   int dev = 0;
   HB_CUDA(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !configured[dev]) {
-    HB_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 kSmemBytes));
+    HB_CUDA(cudaFuncSetAttribute(gemm_f16_kernel<EPI, BN_, ABITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 smem_bytes_for(BN_)));
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
-  dim3 grid((unsigned)((N + BN - 1) / BN), (unsigned)((M + BM - 1) / BM));
-  gemm_f16_kernel<EPI><<<grid, kThreads, kSmemBytes, stream>>>(ta, tb, K, ep);
+  const long long tiles = (long long)((N + BN_ - 1) / BN_) * ((M + BM - 1) / BM);
+  const int sms = sm_count();
+  const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
+  gemm_f16_kernel<EPI, BN_, ABITS><<<grid, kThreads, smem_bytes_for(BN_), stream>>>(ta, tb, K, ep);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
 
-// D = A . B^T with freshly encoded maps (acting path: row count changes call to call).
+// D = A . B^T with freshly encoded maps.  Tile width: 256 when the output is at least that wide.
 template <int EPI>
 inline int gemm(const __half* A, int64_t lda, const __half* B, int64_t ldb, int M, int N, int K,
                 EpiParams ep, cudaStream_t stream) {
+  const int bn = N >= 256 ? 256 : 128;
   CUtensorMap ta, tb;
-  int rc = make_tmap(&ta, A, M, K, lda);
+  int rc = make_tmap(&ta, A, M, K, lda, BM);
   if (rc) return rc;
-  rc = make_tmap(&tb, B, N, K, ldb);
+  rc = make_tmap(&tb, B, N, K, ldb, bn);
   if (rc) return rc;
   ep.M = M;
   ep.N = N;
-  return launch_gemm<EPI>(ta, tb, M, N, K, ep, stream);
+  if (bn == 256) return launch_gemm<EPI, 256>(ta, tb, M, N, K, ep, stream);
+  return launch_gemm<EPI, 128>(ta, tb, M, N, K, ep, stream);
+}
+
+// Same with the A operand given as bit-packed rows [M, a_stride words] (K = 32 * a_stride bits,
+// a_stride even): the kernel expands the bits itself, no fp16 copy of A ever exists in HBM.
+template <int EPI>
+inline int gemm_bits(const uint32_t* A_bits, int a_stride, const __half* B, int64_t ldb, int M, int N,
+                     int K, EpiParams ep, cudaStream_t stream) {
+  if (a_stride % 2 != 0 || K > 32 * a_stride || ((uintptr_t)A_bits & 7) != 0) {
+    hb::set_error("gemm_bits: packed rows must be 8-byte aligned with an even word stride");
+    return HB_ERR_INVALID;
+  }
+  const int bn = N >= 256 ? 256 : 128;
+  CUtensorMap tb;
+  int rc = make_tmap(&tb, B, N, K, ldb, bn);
+  if (rc) return rc;
+  ep.M = M;
+  ep.N = N;
+  ep.a_bits = A_bits;
+  ep.a_stride = a_stride;
+  if (bn == 256) return launch_gemm<EPI, 256, true>(tb, tb, M, N, K, ep, stream);
+  return launch_gemm<EPI, 128, true>(tb, tb, M, N, K, ep, stream);
 }
 
 }  // namespace tc

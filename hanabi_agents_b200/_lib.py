@@ -96,6 +96,16 @@ SIGNATURES = {
     "hb_net_forward": (i32, [vp, vp, i64, i32, vp, vp, vp]),
     "hb_net_grads": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp]),
     "hb_net_adam": (i32, [vp, f32, f32, f32, f32, f32, vp]),
+    # fused learner step
+    "hb_learner_create": (i32, [vp, vp, i32, i32, C.POINTER(vp)]),
+    "hb_learner_destroy": (i32, [vp]),
+    "hb_learner_set_graph": (i32, [vp, i32]),
+    "hb_learner_info": (i64, [vp, i32]),
+    "hb_learner_loss": (vp, [vp]),
+    "hb_learner_mean_loss": (vp, [vp]),
+    "hb_learner_indices": (vp, [vp]),
+    "hb_learner_grads": (i32, [vp, vp, vp, f32, f32, i32, vp]),
+    "hb_learner_apply": (i32, [vp, f32, f32, f32, f32, f32, vp]),
 }
 
 

@@ -349,8 +349,15 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, 
                                     const float* __restrict__ eps_noise, float* __restrict__ am,
                                     float* __restrict__ av, const float* __restrict__ grad,
                                     float grad_scale, int do_update, float lr, float b1, float b2,
-                                    float eps, float bc1, float bc2, __half* __restrict__ w16,
+                                    float eps, const int* __restrict__ step_ptr, __half* __restrict__ w16,
                                     __half* __restrict__ w16t, float* __restrict__ beff) {
+  // bias corrections from the device-side step counter (so that the launch can sit in a CUDA graph)
+  float bc1 = 1.f, bc2 = 1.f;
+  if (do_update) {
+    const float t = (float)*step_ptr;
+    bc1 = 1.0f - powf(b1, t);
+    bc2 = 1.0f - powf(b2, t);
+  }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_eff;
        i += (long long)gridDim.x * blockDim.x) {
     int l = 0;
@@ -385,6 +392,12 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, 
       beff[g.boff + (loc - (long long)g.N * g.K)] = eff;
     }
   }
+}
+
+__global__ void adam_tick_kernel(int* step) { *step += 1; }
+__global__ void fill_kernel(float* p, float v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
 }
 
 // ---------------------------------------------------------------- host helpers ----
@@ -516,16 +529,16 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
 
 int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
              cudaStream_t s) {
-  float bc1 = 1.f, bc2 = 1.f;
+  int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
   if (do_update) {
-    net->adam_step += 1;
-    bc1 = 1.0f - powf(b1, (float)net->adam_step);
-    bc2 = 1.0f - powf(b2, (float)net->adam_step);
+    net->adam_step += 1;                       // host mirror (hb_net_info); the kernels use the device copy
+    adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr);
+    HB_CUDA(cudaGetLastError());
   }
   const unsigned blocks = (unsigned)((net->n_eff + 255) / 256 < 148 * 16 ? (net->n_eff + 255) / 256 : 148 * 16);
   adam_refresh_kernel<<<blocks, 256, 0, s>>>(net->tab, net->n_eff, net->kinds, net->master, net->eps,
                                              net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                             lr, b1, b2, eps, bc1, bc2, net->w16, net->w16t, net->beff);
+                                             lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -670,7 +683,12 @@ int64_t hb_net_info(const hb_qnet* q, int what) {
     case 2: return q->A;
     case 3: return q->n_atoms;
     case 4: return q->noisy;
-    case 5: return q->adam_step;
+    case 5: {   // the step counter lives on the device (graph replays advance it)
+      int v = 0;
+      hb::DeviceGuard g(q->device);
+      if (cudaMemcpy(&v, q->scalars + 2, 4, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+      return v;
+    }
     default: return -1;
   }
 }
@@ -822,9 +840,8 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
   } else if (d_weights) {
     HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
   } else {
-    std::vector<float> ones(B, 1.f);
-    HB_CUDA(cudaMemcpyAsync(q->w_is, ones.data(), (size_t)B * 4, cudaMemcpyHostToDevice, s));
-    HB_CUDA(cudaStreamSynchronize(s));
+    fill_kernel<<<(B + 255) / 256, 256, 0, s>>>(q->w_is, 1.f, B);
+    HB_CUDA(cudaGetLastError());
   }
   // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
   HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, s));

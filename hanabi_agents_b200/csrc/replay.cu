@@ -207,7 +207,7 @@ __global__ void priorities_kernel(const float* __restrict__ td, int64_t n, float
   __shared__ float smax[32], smin[32];
   float mx = -INFINITY, mn = INFINITY;
   for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
-    const float x = td[i] + 1e-10f;
+    const float x = fabsf(td[i]) + 1e-10f;       // the agent passes onp.abs(tds) (rlax_rainbow.py:334)
     const float p = (float)pow((double)x, (double)alpha);
     out[i] = p;
     mx = fmaxf(mx, p);

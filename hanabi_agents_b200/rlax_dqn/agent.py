@@ -58,6 +58,7 @@ class DQNAgent:
         self.requires_vectorized_observation = lambda: True
         self.process_group = process_group
         self.last_loss = None
+        self._learner = None
 
     # -- helpers ----------------------------------------------------------------------------
     def _pack_pair(self, observations):
@@ -103,31 +104,60 @@ class DQNAgent:
                                           self._dev(rewards, torch.float32),
                                           self._dev(step_types, torch.uint8))
 
+    def _make_learner(self):
+        import ctypes as C
+        from .. import _lib
+        from .network import _DevArray
+        L = _lib.lib()
+        h = C.c_void_p()
+        B = self.params.train_batch_size
+        _lib.check(L.hb_learner_create(self.network._h, self.experience._h, B, self.device.index, C.byref(h)))
+        self._learner = h
+        torch = self.torch
+        self._loss_view = torch.as_tensor(_DevArray(L.hb_learner_loss(h), B, self), device=self.device)
+        self._mean_view = torch.as_tensor(_DevArray(L.hb_learner_mean_loss(h), 1, self), device=self.device)
+
+    def __del__(self):
+        h = getattr(self, "_learner", None)
+        if h is not None and h.value:
+            try:
+                from .. import _lib
+                _lib.lib().hb_learner_destroy(h)
+            except Exception:
+                pass
+            self._learner = None
+
     def update(self, uniforms=None):
-        """One training step (rlax_rainbow.py:310-339).  `uniforms`: optional explicit draws for
-        the stratified keys (default: numpy's global RNG, as the reference)."""
+        """One training step (rlax_rainbow.py:310-339): sample_batch -> update_q -> update_priorities
+        -> target sync.  Two C calls (each a replayed CUDA graph) around the gradient all-reduce.
+        `uniforms`: optional explicit draws for the stratified keys (default: numpy's global RNG,
+        exactly as the reference draws them).  Returns the mean loss as a 1-element CUDA tensor."""
+        from .. import _lib
+        L = _lib.lib()
+        if getattr(self, "_learner", None) is None:
+            self._make_learner()
         B = self.params.train_batch_size
         exp = self.experience
+        stream = _lib.current_stream_ptr()
         if self.params.use_priority:
-            idx, _, p32, (o1, a, r, o2, _lm, term) = exp.sample_device(B, uniforms)
-        else:
-            indices = np.random.choice(np.arange(0, exp.capacity, dtype=np.int64)[:exp.size], size=B)
-            o1, a, r, o2, _lm, term = exp.gather_packed(indices)
-            idx, p32 = None, None                   # prios = ones  (:317-318)
-        loss, mean = self.network.grads(o1, a, r, o2, term, prios=p32,
-                                        beta=float(self.params.beta_is(self.train_step)),
-                                        discount=float(self.params.discount))
+            keys = np.ascontiguousarray(PriorityBuffer.stratified_keys(B, uniforms), dtype=np.float32)
+            kp, ip = keys.ctypes.data, None
+        else:                                        # uniform sample, prios = ones  (:315-318)
+            idx = np.ascontiguousarray(
+                np.random.choice(np.arange(0, exp.capacity, dtype=np.int64)[:exp.size], size=B), dtype=np.int64)
+            kp, ip = None, idx.ctypes.data
+        _lib.check(L.hb_learner_grads(self._learner, kp, ip, float(self.params.beta_is(self.train_step)),
+                                      float(self.params.discount), 0, stream))
         world, _ = self._world()
         if world > 1:
             self.torch.distributed.all_reduce(self.network.grad_bucket, group=self.process_group)
-        self.network.adam(lr=float(self.params.learning_rate), eps=self.adam_eps, grad_scale=1.0 / world)
-        if self.params.use_priority:
-            exp.update_priorities(idx, loss.abs())  # :333-334
+        _lib.check(L.hb_learner_apply(self._learner, float(self.params.learning_rate), 0.9, 0.999,
+                                      self.adam_eps, 1.0 / world, stream))
         if self.train_step % self.params.target_update_period == 0:   # :336-337
             self.network.sync_target()
         self.train_step += 1
-        self.last_loss = mean
-        return mean
+        self.last_loss = self._mean_view
+        return self._mean_view
 
     def __repr__(self):
         return f"<rlax_dqn.DQNAgent(params={self.params})>"

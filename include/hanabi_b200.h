@@ -283,6 +283,28 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
  * grad_scale * bucket, then refresh of the effective weights. */
 int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* One learner step = DQNAgent.update (rlax_rainbow.py:310-339) in two C calls   */
+/* around the caller's gradient all-reduce; each phase is a replayed CUDA graph. */
+/* ------------------------------------------------------------------------ */
+typedef struct hb_learner hb_learner;
+int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_learner** out);
+int hb_learner_destroy(hb_learner* L);
+int hb_learner_set_graph(hb_learner* L, int on);
+/* what: 0 batch, 1 graph captures so far, 2 eager steps run */
+int64_t hb_learner_info(const hb_learner* L, int what);
+/* Device views of the last step: per-sample loss / TD [batch], mean loss [1], sampled rows [batch]. */
+float* hb_learner_loss(hb_learner* L);
+float* hb_learner_mean_loss(hb_learner* L);
+int64_t* hb_learner_indices(hb_learner* L);
+/* Phase A: sample_batch (priority_buffer.py:36-46; h_keys = the B stratified keys, float32 as
+ * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss).  HOST arrays. */
+int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
+                     int mask_terminal, void* stream);
+/* Phase B: optix.adam on grad_scale * bucket, then update_priorities(indices, |loss|). */
+int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
+                     void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -113,3 +113,42 @@ def test_agent_numpy_compat_and_weights_roundtrip(tmp_path):
     noise = [{k: v for k, v in l.items() if k.startswith("eps")} for l in agent.network.get_params(with_noise=True)]
     other.network.set_params(noise, sync_target=True)
     assert torch.equal(other.network.forward(env.obs_packed), agent.network.forward(env.obs_packed))
+
+
+def test_graph_replay_equals_eager_updates():
+    """The learner step replayed as CUDA graphs must be bit-identical to the eager launches."""
+    import torch
+    from hanabi_agents_b200 import _lib
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.rlax_dqn import DQNAgent, RlaxRainbowParams
+    N, B = 512, 64
+    params = RlaxRainbowParams(train_batch_size=B, layers=[512, 512], experience_buffer_size=8192, seed=5,
+                               target_update_period=3)
+    agents = []
+    for use_graph in (1, 0):
+        env = HanabiParallelEnv(N, "Hanabi-Full", 2, seed=9)
+        agent = DQNAgent(env.observation_spec(), env.action_spec(), params)
+        env.reset()
+        obs = env.observations_packed()
+        agent.add_experience_first(obs, env.step_type)
+        for _ in range(6):
+            a = agent.explore(obs)
+            env.step(a)
+            obs = env.observations_packed()
+            agent.add_experience(obs, a, env.reward, env.step_type)
+            agent.add_experience_first(obs, env.step_type)
+        agent._make_learner()
+        _lib.check(_lib.lib().hb_learner_set_graph(agent._learner, use_graph))
+        rng = np.random.default_rng(1)
+        losses = [float(agent.update(uniforms=rng.uniform(0, 1.0 / B, B))) for _ in range(8)]
+        torch.cuda.synchronize()
+        captures = int(_lib.lib().hb_learner_info(agent._learner, 1))
+        assert captures == (2 if use_graph else 0)
+        assert int(_lib.lib().hb_net_info(agent.network._h, 5)) == 8          # Adam steps taken
+        agents.append((agent, losses, agent.network.get_params(), agent.experience.sum_tree.heap()))
+    (_, l0, p0, h0), (_, l1, p1, h1) = agents
+    assert l0 == l1
+    for a, b in zip(p0, p1):
+        for k in a:
+            np.testing.assert_array_equal(a[k], b[k])
+    np.testing.assert_array_equal(h0, h1)

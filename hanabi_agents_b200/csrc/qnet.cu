@@ -65,6 +65,9 @@ struct hb_qnet {
   float* act_q = nullptr;
   // learner workspace (batch capacity lb)
   int lb = 0, lbp = 0;
+  uint32_t* xb = nullptr;              // [2B, obs_stride] packed rows: obs_tm1 then obs_t
+  cudaStream_t side = nullptr;         // second stream: target forward / weight gradients run beside
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_dz[kMaxLayers] = {nullptr};
   __half* x = nullptr;                 // [2B, K0]
   __half* xt = nullptr;                // [K0, Bp]
   __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
@@ -109,6 +112,26 @@ __global__ void unpack_rows_kernel(const uint32_t* __restrict__ packed, int stri
       for (int j = 0; j < 32; ++j)
         out_t[(long long)(w * 32 + j) * ld_t + r] = __ushort_as_half(((bits >> j) & 1u) ? 0x3c00 : 0);
     }
+  }
+}
+
+// xt[k, r] = bit k of packed row r as fp16 (the K-major operand of the first layer's weight
+// gradient): one thread per (k, 8 consecutive rows) -> one 16-byte store, coalesced along r.
+__global__ void unpack_t_kernel(const uint32_t* __restrict__ packed, int stride, int rows,
+                                __half* __restrict__ out_t, int ld_t) {
+  const int groups = (rows + 7) / 8;
+  const long long total = (long long)stride * 32 * groups;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int k = (int)(i / groups), r0 = (int)(i - (long long)k * groups) * 8;
+    uint32_t h[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int r = r0 + j;
+      const uint32_t bit = r < rows ? (__ldg(packed + (long long)r * stride + (k >> 5)) >> (k & 31)) & 1u : 0u;
+      h[j >> 1] |= (bit ? 0x3c00u : 0u) << (16 * (j & 1));
+    }
+    *reinterpret_cast<uint4*>(out_t + (long long)k * ld_t + r0) = make_uint4(h[0], h[1], h[2], h[3]);
   }
 }
 
@@ -384,13 +407,36 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, 
       eff += (k == 2) ? p * noise : p;
     }
     if (loc < (long long)g.N * g.K) {
-      const int n = (int)(loc / g.K), kk = (int)(loc - (long long)n * g.K);
-      const __half hv = __float2half_rn(eff);
-      w16[g.woff + loc] = hv;
-      w16t[g.woff + (long long)kk * g.N + n] = hv;
+      w16[g.woff + loc] = __float2half_rn(eff);   // transposes: transpose16_kernel (coalesced)
     } else {
       beff[g.boff + (loc - (long long)g.N * g.K)] = eff;
     }
+  }
+}
+
+// w16t[k, n] = w16[n, k] for every layer: 32 x 32 tiles through shared memory so that both the
+// reads and the writes are coalesced (the v1 Adam kernel scattered 2-byte stores: 38 us per step).
+__global__ void transpose16_kernel(LayerTable tab, const __half* __restrict__ w16, __half* __restrict__ w16t) {
+  __shared__ __half tile[32][33];
+  int t = blockIdx.x, l = 0;
+  for (; l < tab.n_layers; ++l) {
+    const int nt = ((tab.l[l].N + 31) / 32) * ((tab.l[l].K + 31) / 32);
+    if (t < nt) break;
+    t -= nt;
+  }
+  if (l >= tab.n_layers) return;
+  const LayerGeo g = tab.l[l];
+  const int tiles_k = (g.K + 31) / 32;
+  const int n0 = (t / tiles_k) * 32, k0 = (t % tiles_k) * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;       // 32 x 8 threads
+  for (int r = ty; r < 32; r += 8) {
+    const int n = n0 + r, k = k0 + tx;
+    tile[r][tx] = (n < g.N && k < g.K) ? w16[g.woff + (long long)n * g.K + k] : __float2half(0.f);
+  }
+  __syncthreads();
+  for (int r = ty; r < 32; r += 8) {
+    const int k = k0 + r, n = n0 + tx;
+    if (n < g.N && k < g.K) w16t[g.woff + (long long)k * g.N + n] = tile[tx][r];
   }
 }
 
@@ -415,7 +461,7 @@ void dev_free(T*& p) {
 }
 
 void free_learner_ws(hb_qnet* q) {
-  dev_free(q->x); dev_free(q->xt);
+  dev_free(q->x); dev_free(q->xt); dev_free(q->xb);
   for (int l = 0; l < kMaxLayers; ++l) {
     dev_free(q->h[l]); dev_free(q->ht[l]); dev_free(q->th[l]); dev_free(q->dz[l]); dev_free(q->dzt[l]);
   }
@@ -433,6 +479,13 @@ int ensure_learner_ws(hb_qnet* q, int B) {
   const int NL = q->tab.l[nl - 1].N;
   int rc;
   if ((rc = dev_alloc(&q->x, (size_t)2 * B * K0))) return rc;
+  if ((rc = dev_alloc(&q->xb, (size_t)2 * B * q->obs_stride))) return rc;
+  if (q->side == nullptr) {
+    HB_CUDA(cudaStreamCreateWithFlags(&q->side, cudaStreamNonBlocking));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_fork, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
+    for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
+  }
   if ((rc = dev_alloc(&q->xt, (size_t)K0 * Bp))) return rc;
   for (int l = 0; l < nl; ++l) {
     const int N = q->tab.l[l].N;
@@ -539,6 +592,11 @@ int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float ep
   adam_refresh_kernel<<<blocks, 256, 0, s>>>(net->tab, net->n_eff, net->kinds, net->master, net->eps,
                                              net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
                                              lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
+  HB_CUDA(cudaGetLastError());
+  int tiles = 0;
+  for (int l = 0; l < net->n_layers; ++l)
+    tiles += ((net->tab.l[l].N + 31) / 32) * ((net->tab.l[l].K + 31) / 32);
+  transpose16_kernel<<<tiles, 256, 0, s>>>(net->tab, net->w16, net->w16t);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -661,6 +719,12 @@ int hb_net_destroy(hb_qnet* q) {
   dev_free(q->master); dev_free(q->tmaster); dev_free(q->eps); dev_free(q->adam_m); dev_free(q->adam_v); dev_free(q->grad);
   dev_free(q->w16); dev_free(q->w16t); dev_free(q->t16); dev_free(q->beff); dev_free(q->tbeff);
   dev_free(q->scalars);
+  if (q->side) {
+    cudaStreamDestroy(q->side);
+    cudaEventDestroy(q->ev_fork);
+    cudaEventDestroy(q->ev_join);
+    for (int l = 0; l < kMaxLayers; ++l) cudaEventDestroy(q->ev_dz[l]);
+  }
   dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
   free_learner_ws(q);
   delete q;
@@ -826,26 +890,43 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
   const int nl = q->n_layers, K0 = q->tab.l[0].K, Bp = q->lbp;
   const LayerGeo& LL = q->tab.l[nl - 1];
   const int ldq = q->n_atoms > 1 ? q->A : LL.N;
-  // 1. unpack: rows [0, B) = obs_tm1 (+ transposed copy), rows [B, 2B) = obs_t
-  if ((rc = launch_unpack(d_obs_tm1, q->obs_stride, B, q->x, K0, q->xt, Bp, B, s))) return rc;
-  if ((rc = launch_unpack(d_obs_t, q->obs_stride, B, q->x + (size_t)B * K0, K0, nullptr, 0, 0, s))) return rc;
-  // 2. online network on both observation sets, target network on obs_t
-  if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s))) return rc;
+  // 1. packed rows side by side: [0, B) = obs_tm1, [B, 2B) = obs_t
+  const size_t row_words = (size_t)q->obs_stride;
+  HB_CUDA(cudaMemcpyAsync(q->xb, d_obs_tm1, (size_t)B * row_words * 4, cudaMemcpyDeviceToDevice, s));
+  HB_CUDA(cudaMemcpyAsync(q->xb + (size_t)B * row_words, d_obs_t, (size_t)B * row_words * 4,
+                          cudaMemcpyDeviceToDevice, s));
+  const bool fused = nl > 1;                 // layer 0 expands the bits inside the GEMM
+  if (!fused && (rc = launch_unpack(q->xb, q->obs_stride, 2 * B, q->x, K0, nullptr, 0, 0, s))) return rc;
+  // fork: the side stream runs the target network, the transposed observations and the importance
+  // weights while the main stream runs the online network (both join before the loss)
+  HB_CUDA(cudaEventRecord(q->ev_fork, s));
+  HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_fork, 0));
   if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
-                    q->n_atoms > 1 ? nullptr : q->tlogits, ldq, s))) return rc;
-  // 3. importance weights
-  if (d_prios) {
-    is_weights_kernel<<<1, 256, 0, s>>>(d_prios, B, beta, q->w_is);
-    HB_CUDA(cudaGetLastError());
-  } else if (d_weights) {
-    HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
-  } else {
-    fill_kernel<<<(B + 255) / 256, 256, 0, s>>>(q->w_is, 1.f, B);
+                    q->n_atoms > 1 ? nullptr : q->tlogits, ldq, q->side,
+                    fused ? q->xb + (size_t)B * row_words : nullptr))) return rc;
+  {
+    const long long tot = (long long)K0 * ((B + 7) / 8);
+    unpack_t_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, q->side>>>(q->xb, q->obs_stride, B, q->xt, Bp);
     HB_CUDA(cudaGetLastError());
   }
-  // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
+  // importance weights
+  if (d_prios) {
+    is_weights_kernel<<<1, 256, 0, q->side>>>(d_prios, B, beta, q->w_is);
+    HB_CUDA(cudaGetLastError());
+  } else if (d_weights) {
+    HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, q->side));
+  } else {
+    fill_kernel<<<(B + 255) / 256, 256, 0, q->side>>>(q->w_is, 1.f, B);
+    HB_CUDA(cudaGetLastError());
+  }
+  HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, q->side));
+  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  // 2. online network on both observation sets (main stream)
+  if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
+                    fused ? q->xb : nullptr))) return rc;
   HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, s));
-  HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, s));
+  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
   if (q->n_atoms > 1) {
     c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, q->q_on + (size_t)B * ldq, ldq, q->tlogits,
                                                LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, q->w_is,
@@ -861,10 +942,13 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
   HB_CUDA(cudaGetLastError());
   if (d_loss_out) HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
   if (d_mean_loss) HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
-  // 5. backward
+  // 5. backward: the dZ chain (critical path) on the main stream, the weight / bias gradients of
+  //    every layer on the side stream as soon as that layer's dZ exists
   const float invB = 1.0f / (float)B;
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];
+    HB_CUDA(cudaEventRecord(q->ev_dz[l], s));              // dz[l] / dzt[l] are complete here
+    HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_dz[l], 0));
     // dW_l [N, K] = dZ_l^T . X_l  : A = dzt[l] [N, B], B = (layer input)^T [K, B]
     const __half* in_t = l == 0 ? q->xt : q->ht[l - 1];
     const int ld_in_t = l == 0 ? Bp : 2 * Bp;
@@ -872,9 +956,9 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
     ep.alpha = invB;
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
-    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, s))) return rc;
-    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, s>>>(q->dzt[l], Bp, L.N, B, invB,
-                                                  q->grad + L.eoff + (long long)L.N * L.K);
+    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, q->side))) return rc;
+    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, q->side>>>(q->dzt[l], Bp, L.N, B, invB,
+                                                        q->grad + L.eoff + (long long)L.N * L.K);
     HB_CUDA(cudaGetLastError());
     if (l > 0) {
       // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
@@ -889,6 +973,8 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
       if ((rc = tc::gemm<tc::EPI_F16>(q->dz[l], L.N, q->w16t + L.woff, L.N, B, L.K, L.N, eb, s))) return rc;
     }
   }
+  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
   return HB_OK;
 }
 

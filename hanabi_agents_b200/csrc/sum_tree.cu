@@ -112,6 +112,47 @@ st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
 
   for (int64_t base = 0; base < n; base += kPass) {
     const int pass_n = (int)min((int64_t)kPass, n - base);
+    // ---- fast path: non-decreasing, in-range indices (what stratified sampling produces).
+    // Elements that share a node are then a contiguous run of the batch, so one thread per
+    // (level, run) adds the run's diffs in batch order -- the same per-node order of additions
+    // as the sequential reference -- and all runs of all levels proceed in parallel.
+    {
+      bool ok = true;
+      for (int b = threadIdx.x; b < pass_n; b += blockDim.x) {
+        const int64_t li = idx[base + b];
+        const bool in_range = li >= 0 && li < cap;
+        s_leaf[b] = in_range ? cap + li : -1;
+        if (!in_range || (b > 0 && idx[base + b - 1] > li)) ok = false;
+      }
+      if (__syncthreads_and(ok)) {
+        for (int b = threadIdx.x; b < pass_n; b += blockDim.x) {
+          const int64_t pos = s_leaf[b];
+          if (b == 0 || s_leaf[b - 1] != pos) {
+            float L = ld_cg(heap + pos);
+            for (int j = b; j < pass_n && s_leaf[j] == pos; ++j) {
+              const float d = val[base + j] - L;   // updateValue: value - leaf   sum_tree.h:33
+              L = L + d;                           // updateValue_: node->value += diff   :84
+              s_diff[j] = d;
+            }
+            st_cg(heap + pos, L);
+          }
+        }
+        __syncthreads();
+        const int items = depth * pass_n;
+        for (int it = threadIdx.x; it < items; it += blockDim.x) {
+          const int l = it / pass_n, b = it - l * pass_n;      // level l: shift = depth - l
+          const int shift = depth - l;
+          const int64_t node = s_leaf[b] >> shift;
+          if (b == 0 || (s_leaf[b - 1] >> shift) != node) {
+            float sacc = ld_cg(heap + node);
+            for (int j = b; j < pass_n && (s_leaf[j] >> shift) == node; ++j) sacc = sacc + s_diff[j];
+            st_cg(heap + node, sacc);
+          }
+        }
+        __syncthreads();
+        continue;
+      }
+    }
     if (warp == 0) {
       for (int c0 = 0; c0 < pass_n; c0 += 32) {
         const int cnt = min(32, pass_n - c0);
@@ -272,9 +313,7 @@ int hb_st_update(hb_sumtree* t, const int64_t* d_idx, const float* d_val, int64_
   if (n == 0) return HB_OK;
   HB_REQUIRE(d_idx && d_val, "hb_st_update: NULL buffer");
   hb::DeviceGuard g(t->device);
-  int warps = t->depth + 1;
-  if (warps > 32) warps = 32;
-  if (warps < 1) warps = 1;
+  const int warps = 32;   // the sorted fast path spreads (level, run) items over the whole CTA
   st_update_kernel<<<1, warps * 32, 0, (cudaStream_t)stream>>>(t->heap, t->depth, t->cap, d_idx,
                                                                 d_val, n, t->err);
   HB_CUDA(cudaGetLastError());

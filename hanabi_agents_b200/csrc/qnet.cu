@@ -272,12 +272,15 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
   const float g = (mask_terminal && term_t != nullptr && term_t[b]) ? 0.f : gamma;
   const float zi0 = vmin + dzv * (float)i0, zi1 = vmin + dzv * (float)i1;
   float m0 = 0.f, m1 = 0.f;
+  const float inv_dz = 1.0f / dzv;
+#pragma unroll 4
   for (int j = 0; j < n_atoms; ++j) {
     const float pj = __shfl_sync(full, j < 32 ? p0 : p1, j & 31);
     float tz = r + g * (vmin + dzv * (float)j);
     tz = fminf(fmaxf(tz, vmin), vmax);
-    m0 += fminf(fmaxf(1.0f - fabsf(tz - zi0) / dzv, 0.f), 1.f) * pj;
-    m1 += fminf(fmaxf(1.0f - fabsf(tz - zi1) / dzv, 0.f), 1.f) * pj;
+    // rlax.categorical_l2_project multiplies by the reciprocal spacing (d_pos = 1 / d_pos)
+    m0 += fminf(fmaxf(1.0f - fabsf(tz - zi0) * inv_dz, 0.f), 1.f) * pj;
+    m1 += fminf(fmaxf(1.0f - fabsf(tz - zi1) * inv_dz, 0.f), 1.f) * pj;
   }
   if (i0 >= n_atoms) m0 = 0.f;
   if (i1 >= n_atoms) m1 = 0.f;
@@ -368,12 +371,13 @@ __global__ void bias_grad_kernel(const __half* __restrict__ zt, int ld, int N, i
 // Fused Adam (optix.adam: m, v, bias correction, theta -= lr * mhat / (sqrt(vhat) + eps)) over the
 // flat effective-parameter space + refresh of the fp16 effective weights in both layouts.
 // do_update == 0: refresh only (after parameters were loaded).
-__global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, float* __restrict__ master,
+template <int KINDS>
+__global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds*/, float* __restrict__ master,
                                     const float* __restrict__ eps_noise, float* __restrict__ am,
                                     float* __restrict__ av, const float* __restrict__ grad,
                                     float grad_scale, int do_update, float lr, float b1, float b2,
                                     float eps, const int* __restrict__ step_ptr, __half* __restrict__ w16,
-                                    __half* __restrict__ w16t, float* __restrict__ beff) {
+                                    __half* __restrict__ /*w16t*/, float* __restrict__ beff) {
   // bias corrections from the device-side step counter (so that the launch can sit in a CUDA graph)
   float bc1 = 1.f, bc2 = 1.f;
   if (do_update) {
@@ -381,35 +385,60 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int kinds, 
     bc1 = 1.0f - powf(b1, t);
     bc2 = 1.0f - powf(b2, t);
   }
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_eff;
-       i += (long long)gridDim.x * blockDim.x) {
+  // four consecutive parameters per thread (every block boundary is a multiple of 8 elements)
+  const long long n4 = n_eff >> 2;
+  for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4;
+       i4 += (long long)gridDim.x * blockDim.x) {
+    const long long i = i4 << 2;
     int l = 0;
 #pragma unroll
     for (int k = 1; k < kMaxLayers; ++k)
       if (k < tab.n_layers && i >= tab.l[k].eoff) l = k;
     const LayerGeo g = tab.l[l];
     const long long loc = i - g.eoff;
-    const float noise = kinds == 3 ? eps_noise[i] : 0.f;
-    float eff = 0.f;
-    for (int k = 0; k < kinds; ++k) {
-      float p = master[k * n_eff + i];
-      if (do_update) {
-        const float gr = grad[i] * grad_scale * (k == 2 ? noise : 1.0f);
-        float m = am[k * n_eff + i], v = av[k * n_eff + i];
-        m = b1 * m + (1.0f - b1) * gr;
-        v = b2 * v + (1.0f - b2) * gr * gr;
-        am[k * n_eff + i] = m;
-        av[k * n_eff + i] = v;
-        const float mhat = m / bc1, vhat = v / bc2;
-        p = p - lr * mhat / (sqrtf(vhat) + eps);
-        master[k * n_eff + i] = p;
-      }
-      eff += (k == 2) ? p * noise : p;
+    float noise[4] = {0.f, 0.f, 0.f, 0.f};
+    if (KINDS == 3) {
+      const float4 t = *reinterpret_cast<const float4*>(eps_noise + i);
+      noise[0] = t.x; noise[1] = t.y; noise[2] = t.z; noise[3] = t.w;
     }
-    if (loc < (long long)g.N * g.K) {
-      w16[g.woff + loc] = __float2half_rn(eff);   // transposes: transpose16_kernel (coalesced)
+    float gr4[4] = {0.f, 0.f, 0.f, 0.f};
+    if (do_update) {
+      const float4 t = *reinterpret_cast<const float4*>(grad + i);
+      gr4[0] = t.x; gr4[1] = t.y; gr4[2] = t.z; gr4[3] = t.w;
+    }
+    float eff[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < KINDS; ++k) {
+      float4 pv = *reinterpret_cast<const float4*>(master + k * n_eff + i);
+      float p[4] = {pv.x, pv.y, pv.z, pv.w};
+      if (do_update) {
+        const float4 mv = *reinterpret_cast<const float4*>(am + k * n_eff + i);
+        const float4 vv = *reinterpret_cast<const float4*>(av + k * n_eff + i);
+        float m[4] = {mv.x, mv.y, mv.z, mv.w}, v[4] = {vv.x, vv.y, vv.z, vv.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float gr = gr4[j] * grad_scale * (k == 2 ? noise[j] : 1.0f);
+          m[j] = b1 * m[j] + (1.0f - b1) * gr;
+          v[j] = b2 * v[j] + (1.0f - b2) * gr * gr;
+          const float mhat = m[j] / bc1, vhat = v[j] / bc2;
+          p[j] = p[j] - lr * mhat / (sqrtf(vhat) + eps);
+        }
+        *reinterpret_cast<float4*>(am + k * n_eff + i) = make_float4(m[0], m[1], m[2], m[3]);
+        *reinterpret_cast<float4*>(av + k * n_eff + i) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(master + k * n_eff + i) = make_float4(p[0], p[1], p[2], p[3]);
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j) eff[j] += (k == 2) ? p[j] * noise[j] : p[j];
+    }
+    if (loc < (long long)g.N * g.K) {   // transposes: transpose16_kernel (coalesced)
+      const __half2 h0 = __floats2half2_rn(eff[0], eff[1]), h1 = __floats2half2_rn(eff[2], eff[3]);
+      uint2 o;
+      o.x = *reinterpret_cast<const uint32_t*>(&h0);
+      o.y = *reinterpret_cast<const uint32_t*>(&h1);
+      *reinterpret_cast<uint2*>(w16 + g.woff + loc) = o;
     } else {
-      beff[g.boff + (loc - (long long)g.N * g.K)] = eff;
+      *reinterpret_cast<float4*>(beff + g.boff + (loc - (long long)g.N * g.K)) =
+          make_float4(eff[0], eff[1], eff[2], eff[3]);
     }
   }
 }
@@ -588,10 +617,16 @@ int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float ep
     adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr);
     HB_CUDA(cudaGetLastError());
   }
-  const unsigned blocks = (unsigned)((net->n_eff + 255) / 256 < 148 * 16 ? (net->n_eff + 255) / 256 : 148 * 16);
-  adam_refresh_kernel<<<blocks, 256, 0, s>>>(net->tab, net->n_eff, net->kinds, net->master, net->eps,
-                                             net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                             lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
+  const long long n4 = net->n_eff / 4;
+  const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
+  if (net->kinds == 3)
+    adam_refresh_kernel<3><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 3, net->master, net->eps,
+                                                  net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
+                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
+  else
+    adam_refresh_kernel<1><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 1, net->master, net->eps,
+                                                  net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
+                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
   HB_CUDA(cudaGetLastError());
   int tiles = 0;
   for (int l = 0; l < net->n_layers; ++l)

@@ -145,7 +145,17 @@ st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
           const int64_t node = s_leaf[b] >> shift;
           if (b == 0 || (s_leaf[b - 1] >> shift) != node) {
             float sacc = ld_cg(heap + node);
-            for (int j = b; j < pass_n && (s_leaf[j] >> shift) == node; ++j) sacc = sacc + s_diff[j];
+            int j = b;
+            // whole groups of 8 inside the run: the loads are independent, the adds stay ordered
+            while (j + 8 <= pass_n && (s_leaf[j + 7] >> shift) == node) {
+              float d[8];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) d[u] = s_diff[j + u];
+#pragma unroll
+              for (int u = 0; u < 8; ++u) sacc = sacc + d[u];
+              j += 8;
+            }
+            for (; j < pass_n && (s_leaf[j] >> shift) == node; ++j) sacc = sacc + s_diff[j];
             st_cg(heap + node, sacc);
           }
         }

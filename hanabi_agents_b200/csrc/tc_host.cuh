@@ -2,6 +2,7 @@
 #pragma once
 #include "common.cuh"
 #include "tc_gemm.cuh"
+#include <stdlib.h>
 
 namespace tc {
 
@@ -76,7 +77,10 @@ inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int 
 template <int EPI>
 inline int gemm(const __half* A, int64_t lda, const __half* B, int64_t ldb, int M, int N, int K,
                 EpiParams ep, cudaStream_t stream) {
-  const int bn = N >= 256 ? 256 : 128;
+  // wide tiles only when there are enough of them to occupy the machine: a small problem is
+  // latency bound and finishes sooner spread over twice as many CTAs
+  int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
+  if (const char* f = getenv("HB_FORCE_BN")) bn = (atoi(f) == 256 && N >= 256) ? 256 : (atoi(f) == 128 ? 128 : bn);
   CUtensorMap ta, tb;
   int rc = make_tmap(&ta, A, M, K, lda, BM);
   if (rc) return rc;
@@ -97,7 +101,10 @@ inline int gemm_bits(const uint32_t* A_bits, int a_stride, const __half* B, int6
     hb::set_error("gemm_bits: packed rows must be 8-byte aligned with an even word stride");
     return HB_ERR_INVALID;
   }
-  const int bn = N >= 256 ? 256 : 128;
+  // wide tiles only when there are enough of them to occupy the machine: a small problem is
+  // latency bound and finishes sooner spread over twice as many CTAs
+  int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
+  if (const char* f = getenv("HB_FORCE_BN")) bn = (atoi(f) == 256 && N >= 256) ? 256 : (atoi(f) == 128 ? 128 : bn);
   CUtensorMap tb;
   int rc = make_tmap(&tb, B, N, K, ldb, bn);
   if (rc) return rc;

@@ -2,7 +2,6 @@
 #pragma once
 #include "common.cuh"
 #include "tc_gemm.cuh"
-#include <stdlib.h>
 
 namespace tc {
 
@@ -79,8 +78,7 @@ inline int gemm(const __half* A, int64_t lda, const __half* B, int64_t ldb, int 
                 EpiParams ep, cudaStream_t stream) {
   // wide tiles only when there are enough of them to occupy the machine: a small problem is
   // latency bound and finishes sooner spread over twice as many CTAs
-  int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
-  if (const char* f = getenv("HB_FORCE_BN")) bn = (atoi(f) == 256 && N >= 256) ? 256 : (atoi(f) == 128 ? 128 : bn);
+  const int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
   CUtensorMap ta, tb;
   int rc = make_tmap(&ta, A, M, K, lda, BM);
   if (rc) return rc;
@@ -103,8 +101,7 @@ inline int gemm_bits(const uint32_t* A_bits, int a_stride, const __half* B, int6
   }
   // wide tiles only when there are enough of them to occupy the machine: a small problem is
   // latency bound and finishes sooner spread over twice as many CTAs
-  int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
-  if (const char* f = getenv("HB_FORCE_BN")) bn = (atoi(f) == 256 && N >= 256) ? 256 : (atoi(f) == 128 ? 128 : bn);
+  const int bn = (N >= 256 && (long long)((N + 255) / 256) * ((M + BM - 1) / BM) >= 64) ? 256 : 128;
   CUtensorMap tb;
   int rc = make_tmap(&tb, B, N, K, ldb, bn);
   if (rc) return rc;

@@ -64,13 +64,20 @@ env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict_
 // One env step for one game (shared by the step kernel and the fused self-play kernel).
 // A game whose previous step was LAST is reset onto its next deck (action ignored, reward 0,
 // FIRST) -- otherwise rl_env.step: apply, deal, reward = score delta.
+// `row` is the deck-pool row of the current episode, (game_id + episode * n_total) mod n_decks; the
+// next episode's row is row + (n_total mod n_decks) with one conditional subtraction -- the 64-bit
+// modulo of deck_of() was 21.6 % of all warp instructions of the self-play kernel when it sat in
+// this branch (some lane of a warp resets in ~40 % of the steps; profiles/r01_selfplay_history.md).
 template <class SH>
 __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
-                                           const uint8_t*& deck, long long game, int action,
+                                           const uint8_t*& deck, unsigned long long& row,
+                                           unsigned long long row_step, int action,
                                            unsigned long long lm, unsigned long long* illegal) {
   if (g.step_type == LAST) {
     ++g.episode;
-    deck = deck_of<SH>(rt, decks, game, g.episode);
+    row += row_step;
+    if (row >= (unsigned long long)rt.n_decks) row -= (unsigned long long)rt.n_decks;
+    deck = decks + row * SH::DECK;
     reset_game(g, deck);
     return 0.0f;
   }
@@ -93,8 +100,9 @@ env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
-  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
-  const float r = step_game(g, rt, decks, deck, game, action[game], legal_mask(g), illegal);
+  unsigned long long row = deck_row<SH>(rt, game, g.episode);
+  const uint8_t* deck = decks + row * SH::DECK;
+  const float r = step_game(g, rt, decks, deck, row, rt.row_step, action[game], legal_mask(g), illegal);
   if (reward != nullptr) reward[game] = r;
   emit(g, game, obs, legal, step_type);
   store_game(g, state, game);
@@ -151,7 +159,8 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
-  const uint8_t* deck = deck_of<SH>(rt, decks, game, g.episode);
+  unsigned long long row = deck_row<SH>(rt, game, g.episode);   // one 64-bit modulo per launch
+  const uint8_t* deck = decks + row * SH::DECK;
   unsigned long long lm = legal_mask(g);
   // rule-hit histogram: 8-bit counters packed in two registers (the host keeps n_steps <= 255)
   unsigned long long cnt_lo = 0, cnt_hi = 0, cnt_fb = 0;
@@ -160,7 +169,7 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
     int a = 0, hit = -1;
     if (g.step_type != LAST)
       a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
-    const float r = step_game(g, rt, decks, deck, game, a, lm, illegal);
+    const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, lm, illegal);
     const long long row = (long long)t * rt.n_games + game;
     if (action != nullptr) action[row] = a;
     if (reward != nullptr) reward[row] = r;
@@ -416,6 +425,7 @@ int hb_env_set_shard(hb_env* e, int64_t game_id_base, int64_t n_total) {
              e ? (long long)e->rt.n_games : 0ll, (long long)n_total);
   e->rt.game_id_base = game_id_base;
   e->rt.n_total = n_total;
+  if (e->rt.n_decks > 0) e->rt.row_step = n_total % e->rt.n_decks;
   return HB_OK;
 }
 
@@ -427,6 +437,7 @@ int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* s
   HB_CUDA(cudaMalloc(&e->decks, bytes));
   HB_CUDA(cudaMemcpyAsync(e->decks, d_decks, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   e->rt.n_decks = n_decks;
+  e->rt.row_step = e->rt.n_total % n_decks;
   return HB_OK;
 }
 

@@ -69,6 +69,7 @@ struct Rt {
   long long n_total;                // games in the whole job (deck selection)
   long long game_id_base;           // global id of local game 0
   long long n_decks;
+  long long row_step;               // n_total mod n_decks: deck-row increment from one episode to the next
 };
 
 constexpr uint32_t kGridMask = 0x1ffffffu;
@@ -165,6 +166,12 @@ __device__ __forceinline__ void store_game(const Game<SH>& g, uint32_t* __restri
 #pragma unroll
   for (int i = 0; i < SH::kStateWords / 4; ++i)
     if (4 * i < SH::S + 6) dst[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
+}
+
+template <class SH>
+__device__ __forceinline__ unsigned long long deck_row(const Rt& rt, long long game, uint32_t episode) {
+  return (unsigned long long)(rt.game_id_base + game + (long long)episode * rt.n_total) %
+         (unsigned long long)rt.n_decks;
 }
 
 template <class SH>

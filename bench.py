@@ -230,8 +230,11 @@ def bench_sum_tree(args):
                            device="cuda")
     newv = torch.as_tensor(rng.random((iters, B)).astype(np.float32), device="cuda")
 
+    bufs = (torch.empty(B, dtype=torch.int64, device="cuda"), torch.empty(B, dtype=torch.float32, device="cuda"),
+            torch.empty(1, dtype=torch.float32, device="cuda"))
+
     def it(i):
-        idx, _, _ = tree.sample(keys[i])
+        idx, _, _ = tree.sample(keys[i], out=bufs)
         tree.update_values(idx, newv[i])
 
     for i in range(10):

@@ -133,13 +133,17 @@ class SumTreef:
         return "<SumTree(capacity=%d, maxval=%f)>" % (self.get_capacity(), self.get_total_val())
 
     # -- device fast path -------------------------------------------------
-    def sample(self, quantiles):
-        """get_indices + get_values + get_total_val in one launch (device tensors)."""
+    def sample(self, quantiles, out=None):
+        """get_indices + get_values + get_total_val in one launch (device tensors).
+        `out` = (idx int64[n], val float32[n], total float32[1]) reuses caller-owned buffers."""
         import torch
         q = quantiles.to(torch.float32).contiguous()
-        idx = torch.empty(q.numel(), dtype=torch.int64, device=q.device)
-        val = torch.empty(q.numel(), dtype=torch.float32, device=q.device)
-        tot = torch.empty(1, dtype=torch.float32, device=q.device)
+        if out is not None:
+            idx, val, tot = out
+        else:
+            idx = torch.empty(q.numel(), dtype=torch.int64, device=q.device)
+            val = torch.empty(q.numel(), dtype=torch.float32, device=q.device)
+            tot = torch.empty(1, dtype=torch.float32, device=q.device)
         _lib.check(_lib.lib().hb_st_sample(self._h, q.data_ptr(), idx.data_ptr(), val.data_ptr(),
                                            tot.data_ptr(), q.numel(), _lib.current_stream_ptr()))
         return idx, val, tot

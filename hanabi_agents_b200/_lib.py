@@ -106,6 +106,14 @@ SIGNATURES = {
     "hb_learner_indices": (vp, [vp]),
     "hb_learner_grads": (i32, [vp, vp, vp, f32, f32, i32, vp]),
     "hb_learner_apply": (i32, [vp, f32, f32, f32, f32, f32, vp]),
+    # self-play session
+    "hb_session_create": (i32, [i32, i64, i32, C.POINTER(vp)]),
+    "hb_session_destroy": (i32, [vp]),
+    "hb_session_reset": (i32, [vp, i32, vp]),
+    "hb_session_begin_turn": (i32, [vp, i32, vp, vp]),
+    "hb_session_end_turn": (i32, [vp, i32, vp, vp, i32, vp]),
+    "hb_session_buffer": (vp, [vp, i32, i32]),
+    "hb_session_stats": (i32, [vp, vp, vp]),
 }
 
 
@@ -151,3 +159,19 @@ def current_stream_ptr():
     """cudaStream_t of torch's current stream (torch is used for hand-off only)."""
     import torch
     return torch.cuda.current_stream().cuda_stream
+
+
+class DevView:
+    """__cuda_array_interface__ view of library-owned device memory (zero copy into torch)."""
+
+    def __init__(self, ptr, n, typestr, owner):
+        self._owner = owner
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+def dev_tensor(ptr, n, typestr, owner, device):
+    import torch
+    if not ptr:
+        raise HanabiB200Error("NULL device buffer")
+    return torch.as_tensor(DevView(ptr, n, typestr, owner), device=device)

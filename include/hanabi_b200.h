@@ -305,6 +305,40 @@ int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, f
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
                      void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* Self-play session bookkeeping (the per-player accounting of the driver loop  */
+/* hanabi_agents/rainbow/run_experiment.py:280-336, over N lockstep games).     */
+/* Seat k = tick mod players moves in every game; a finished game spends one    */
+/* tick on the env's reset step, so all games stay on the same rotation.        */
+/* ------------------------------------------------------------------------ */
+typedef struct hb_session hb_session;
+int hb_session_create(int players, int64_t n_games, int device, hb_session** out);
+int hb_session_destroy(hb_session* s);
+/* obs_stacker.reset_stack / has_played = {} / reward_since_last_action = 0  (:292-299);
+ * clear_stats also zeroes the episode counters. */
+int hb_session_reset(hb_session* s, int clear_stats, void* stream);
+/* Before seat `agent` acts on the env's current outputs (d_game_step_type [N], dm_env coding):
+ * fills the step type every seat is shown this tick --
+ *   game LAST            -> LAST for every seat that has played this episode (end_episode :335)
+ *   seat to move         -> MID if it has played (agent.step :319), else FIRST (begin_episode :324)
+ *   anything else        -> FIRST (= nothing to record)
+ * The matching actions / rewards are the seat's rows of buffers 1 / 0 below. */
+int hb_session_begin_turn(hb_session* s, int agent, const uint8_t* d_game_step_type, void* stream);
+/* After env.step(d_action) returned d_reward: the mover's accumulator restarts at this reward,
+ * every other seat's grows by it (:305-310,331); episode return / length advance (:307,312).
+ * Games the env reset in this tick close their books instead (statistics, all seats cleared).
+ * lenient != 0: reward = max(reward, 0)  (LENIENT_SCORE :306). */
+int hb_session_end_turn(hb_session* s, int agent, const int32_t* d_action, const float* d_reward,
+                        int lenient, void* stream);
+/* Device buffers.  Per seat (row `agent`): 0 reward since last action f32[N], 1 last action i32[N],
+ * 2 step type shown u8[N], 3 has-played u8[N].  Per game: 4 running return f32, 5 running length
+ * i32, 6 finished episodes i32, 7 / 8 return f32 / length i32 of the first finished episode,
+ * 10 game step type before this tick's env step u8.  9: f64[4] sum of returns, episodes, sum of
+ * lengths, sum of squared returns. */
+void* hb_session_buffer(hb_session* s, int which, int agent);
+/* Synchronising copy of buffer 9 to the host. */
+int hb_session_stats(hb_session* s, double* h_out4, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

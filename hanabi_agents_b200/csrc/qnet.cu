@@ -142,7 +142,11 @@ __device__ __forceinline__ float uniform_from(unsigned long long seed, unsigned 
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
   x ^= x >> 27; x *= 0x94D049BB133111EBull;
   x ^= x >> 31;
-  return (float)(x >> 40) * (1.0f / 16777216.0f);   // [0, 1)
+  // (0, 1): the centre of one of 2^23 cells.  Never exactly 0 -- with u == 0 the reference's
+  // `argmin(rnds > cpi)` (rlax_rainbow.py:44) returns action 0 even when it is illegal (cpi[0] == 0);
+  // jax.random.uniform hits that once in 2^23 draws, a 131,072-game session every ~64 ticks.
+  // Explicit `uniform` inputs keep the reference's behaviour, quirk included.
+  return ((float)(x >> 41) + 0.5f) * (1.0f / 8388608.0f);
 }
 
 // DQNPolicy.policy / eval_policy after the network (rlax_rainbow.py:34-59,119-123,146-150):

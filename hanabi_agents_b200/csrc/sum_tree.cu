@@ -268,8 +268,8 @@ __global__ void st_range_internal_kernel(float* __restrict__ heap, int depth, in
 // of load latency (a 65,536-row insert: 1.0 ms -> ~0.2 ms).  blockIdx.y = level (0 = root).
 __global__ void st_range_internal_warp_kernel(float* __restrict__ heap, int depth, int64_t cap,
                                               int64_t start, int64_t n,
-                                              const float* __restrict__ diff) {
-  const int l = blockIdx.y;
+                                              const float* __restrict__ diff, int level0) {
+  const int l = blockIdx.y + level0;
   const int shift = depth - l;
   const int lane = threadIdx.x & 31;
   const int64_t first = (cap + start) >> shift;
@@ -296,6 +296,212 @@ __global__ void st_range_internal_warp_kernel(float* __restrict__ heap, int dept
     }
   }
   if (lane == 0) heap[node] = s;
+}
+
+// ---- the levels next to the root: an ORDERED fp32 sum as a parallel scan ------------------------
+// A node near the root adds thousands of diffs (the root: all n) and the reference adds them one
+// by one in batch order, each add rounded to fp32 (sum_tree.h:80-90) -- one dependent chain, at
+// best 4 cycles per element (65,536 rows: 0.14 ms; the shuffle replay above: 0.32 ms, half of a
+// self-play training tick).  The chain is only apparent.  While the running sum s stays inside one
+// binade [2^e, 2^(e+1)) it is an integer S in [2^23, 2^24) times u = 2^(e-23), and
+//     fl32(s + d) = (S + RN(d / u)) * u
+// where RN rounds to nearest and the exact tie d/u = m + 1/2 goes to the EVEN neighbour of S + m.
+// So one element is the map  S -> S + a  or (tie)  S -> even_up(S + m); a run of elements composes
+// to  S -> S + A  (no tie in the run)  or  S -> even_up(S + A) + R  (A: everything up to the first
+// tie, R: everything after it, which no longer depends on S because the value after a tie is even).
+// These maps compose associatively: every thread folds its slice of the run, one block scan gives
+// each thread its incoming S, and a second pass over the slice checks that every exact partial sum
+// stayed inside [2^23, 2^24) -- the premise.  Where it did not (the sum crossed a binade, a diff was
+// as large as the sum, NaN ...), the verified prefix is kept, the offending slice is added the slow
+// way in fp32, and the rest is retried in the new binade.  Bit-identical to the chain by
+// construction; tests/test_sum_tree_gpu.py drives ties, crossings, cancellations and NaNs through it.
+constexpr int kScanThreads = 1024;
+constexpr int kScanMinRun = 512;     // shorter remainders: plain ordered chain by one warp
+constexpr int kScanSpanLog2 = 11;    // levels whose nodes cover >= 2048 leaves use the scan
+
+struct SegFn {
+  long long A, R;
+  int tie;
+};
+
+__device__ __forceinline__ SegFn seg_compose(const SegFn& f, const SegFn& g) {   // f first, then g
+  SegFn o;
+  if (!f.tie) {
+    o.tie = g.tie; o.A = f.A + g.A; o.R = g.R;
+  } else if (!g.tie) {
+    o.tie = 1; o.A = f.A; o.R = f.R + g.A;
+  } else {
+    long long t = f.R + g.A;
+    t += t & 1;
+    o.tie = 1; o.A = f.A; o.R = t + g.R;
+  }
+  return o;
+}
+
+__device__ __forceinline__ long long seg_apply(const SegFn& f, long long S) {
+  long long t = S + f.A;
+  if (!f.tie) return t;
+  t += t & 1;
+  return t + f.R;
+}
+
+__device__ __forceinline__ SegFn seg_shfl_up(const SegFn& v, int delta) {
+  SegFn o;
+  o.A = __shfl_up_sync(0xffffffffu, v.A, delta);
+  o.R = __shfl_up_sync(0xffffffffu, v.R, delta);
+  o.tie = __shfl_up_sync(0xffffffffu, v.tie, delta);
+  return o;
+}
+
+// ordered chain s = s + d[0] + d[1] ... by one warp (every lane returns the result)
+__device__ __forceinline__ float warp_chain(float s, const float* __restrict__ d, int64_t cnt, int lane) {
+  float next = lane < cnt ? __ldg(d + lane) : 0.f;
+  for (int64_t k = 0; k < cnt; k += 32) {
+    const float cur = next;
+    if (k + 32 + lane < cnt) next = __ldg(d + k + 32 + lane);
+    const int m = cnt - k >= 32 ? 32 : (int)(cnt - k);
+    for (int j = 0; j < m; ++j) s = s + __shfl_sync(0xffffffffu, cur, j);
+  }
+  return s;
+}
+
+__global__ void __launch_bounds__(kScanThreads)
+st_range_internal_scan_kernel(float* __restrict__ heap, int depth, int64_t cap, int64_t start,
+                              int64_t n, const float* __restrict__ diff) {
+  const int l = blockIdx.y;
+  const int shift = depth - l;
+  const int64_t first = (cap + start) >> shift;
+  const int64_t last = (cap + start + n - 1) >> shift;
+  const int64_t node = first + blockIdx.x;
+  if (node > last) return;
+  int64_t lo = (node << shift) - cap;
+  int64_t hi = lo + ((int64_t)1 << shift);
+  lo = max(lo, start);
+  hi = min(hi, start + n);
+  const float* d = diff + (lo - start);
+  const int64_t cnt = hi - lo;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  __shared__ float sh_s;
+  __shared__ int sh_bad;
+  __shared__ SegFn sh_warp[32];
+  constexpr long long kLo = 1ll << 23, kHi = (1ll << 24) - 1;
+
+  float s = heap[node];
+  int64_t pos = 0;
+  while (pos < cnt) {                         // every branch below is uniform over the CTA
+    const int64_t rem = cnt - pos;
+    const uint32_t bits = __float_as_uint(s);
+    const int eb = (int)((bits >> 23) & 0xffu);
+    const bool speculate = rem >= kScanMinRun && s > 0.f && eb >= 1 && eb <= 254;
+    if (!speculate) {
+      const int64_t take = rem < kScanMinRun ? rem : (int64_t)kScanMinRun;
+      if (warp == 0) {
+        const float r = warp_chain(s, d + pos, take, lane);
+        if (lane == 0) sh_s = r;
+      }
+      __syncthreads();
+      s = sh_s;
+      __syncthreads();
+      pos += take;
+      continue;
+    }
+    const int64_t seg = (rem + kScanThreads - 1) / kScanThreads;
+    int64_t b = pos + (int64_t)tid * seg;
+    if (b > cnt) b = cnt;
+    const int64_t e = b + seg < cnt ? b + seg : cnt;
+    // d / u with u = 2^(eb-127-23): a power-of-two scaling, exact in double
+    const double scale = __longlong_as_double((long long)(1173 - eb) << 52);
+    if (tid == 0) sh_bad = kScanThreads;
+    // pass 1: this slice as a map on S
+    SegFn f;
+    f.A = 0; f.R = 0; f.tie = 0;
+    for (int64_t k = b; k < e; ++k) {
+      const double D = (double)__ldg(d + k) * scale;
+      if (!(fabs(D) < 16777216.0)) continue;            // flagged by pass 2; nothing after it is kept
+      const double fl = floor(D);
+      const double fr = D - fl;
+      long long m = (long long)fl;
+      const bool tie = fr == 0.5;
+      if (fr > 0.5) m += 1;
+      if (!f.tie) {
+        f.A += m;
+        f.tie = tie ? 1 : 0;
+      } else if (!tie) {
+        f.R += m;
+      } else {
+        long long t = f.R + m;
+        t += t & 1;
+        f.R = t;
+      }
+    }
+    // block-wide exclusive scan under composition
+    SegFn inc = f;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const SegFn up = seg_shfl_up(inc, o);
+      if (lane >= o) inc = seg_compose(up, inc);
+    }
+    if (lane == 31) sh_warp[warp] = inc;
+    __syncthreads();
+    if (warp == 0) {
+      SegFn w = sh_warp[lane];
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const SegFn up = seg_shfl_up(w, o);
+        if (lane >= o) w = seg_compose(up, w);
+      }
+      sh_warp[lane] = w;
+    }
+    __syncthreads();
+    SegFn pre = seg_shfl_up(inc, 1);
+    if (lane == 0) { pre.A = 0; pre.R = 0; pre.tie = 0; }
+    if (warp > 0) pre = seg_compose(sh_warp[warp - 1], pre);
+    const long long S0 = (long long)((bits & 0x7fffffu) | 0x800000u);
+    const long long S_in = seg_apply(pre, S0);
+    // pass 2: replay the slice from its true incoming S and check the premise at every element
+    long long S = S_in;
+    bool ok = true;
+    for (int64_t k = b; k < e; ++k) {
+      const double D = (double)__ldg(d + k) * scale;
+      if (!(fabs(D) < 16777216.0)) { ok = false; break; }
+      const double fl = floor(D);
+      const double fr = D - fl;
+      const long long m = (long long)fl;
+      if (S + m < kLo) { ok = false; break; }          // exact sum below 2^e: finer grid there
+      long long t = S + m;
+      if (fr == 0.5) t += t & 1;
+      else if (fr > 0.5) t += 1;
+      if (t > kHi) { ok = false; break; }               // reached 2^(e+1): coarser grid from here
+      S = t;
+    }
+    if (!ok) atomicMin(&sh_bad, tid);
+    __syncthreads();
+    const int bad = sh_bad;
+    if (bad == kScanThreads) {
+      if (tid == kScanThreads - 1) sh_s = __uint_as_float(((uint32_t)eb << 23) | ((uint32_t)S & 0x7fffffu));
+      __syncthreads();
+      s = sh_s;
+      __syncthreads();
+      pos = cnt;
+    } else {
+      if (tid == bad) sh_s = __uint_as_float(((uint32_t)eb << 23) | ((uint32_t)S_in & 0x7fffffu));
+      __syncthreads();
+      const float sb = sh_s;
+      __syncthreads();
+      int64_t bb = pos + (int64_t)bad * seg;
+      if (bb > cnt) bb = cnt;
+      const int64_t be = bb + seg < cnt ? bb + seg : cnt;
+      if (warp == 0) {
+        const float r = warp_chain(sb, d + bb, be - bb, lane);
+        if (lane == 0) sh_s = r;
+      }
+      __syncthreads();
+      s = sh_s;
+      __syncthreads();
+      pos = be;
+    }
+  }
+  if (tid == 0) heap[node] = s;
 }
 
 int ensure_stage(hb_sumtree* t, size_t bytes) {
@@ -405,19 +611,29 @@ static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const f
       t->heap, t->cap, start, n, d_val, fill, d_fill, t->scratch);
   HB_CUDA(cudaGetLastError());
   if (t->depth > 0) {
-    // levels whose nodes cover >= 64 leaves: warp per node; deeper levels: thread per node
-    const int warp_levels = t->depth >= 6 ? t->depth - 5 : 0;      // levels 0 .. depth-6
+    // levels whose nodes cover >= 2048 leaves: CTA per node, ordered sum as a scan;
+    // >= 64 leaves: warp per node, ordered chain; deeper levels: thread per node
+    const int scan_levels = t->depth >= kScanSpanLog2 ? t->depth - kScanSpanLog2 + 1 : 0;   // 0 .. depth-11
+    const int warp_levels = (t->depth >= 6 ? t->depth - 5 : 0) - scan_levels;               // .. depth-6
+    if (scan_levels > 0) {
+      const int64_t widest = (n >> kScanSpanLog2) + 2;
+      dim3 grid((unsigned)widest, (unsigned)scan_levels);
+      st_range_internal_scan_kernel<<<grid, kScanThreads, 0, s>>>(t->heap, t->depth, t->cap, start, n,
+                                                                   t->scratch);
+      HB_CUDA(cudaGetLastError());
+    }
     if (warp_levels > 0) {
       const int64_t widest = n / 64 + 2;
       dim3 grid((unsigned)((widest + 3) / 4), (unsigned)warp_levels);
-      st_range_internal_warp_kernel<<<grid, 128, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch);
+      st_range_internal_warp_kernel<<<grid, 128, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch,
+                                                         scan_levels);
       HB_CUDA(cudaGetLastError());
     }
+    const int upper = scan_levels + warp_levels;
     const int64_t widest = n / 2 + 2;  // nodes covered at the deepest internal level
     const int th = 128;
-    dim3 grid((unsigned)((widest + th - 1) / th), (unsigned)(t->depth - warp_levels));
-    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch,
-                                                 warp_levels);
+    dim3 grid((unsigned)((widest + th - 1) / th), (unsigned)(t->depth - upper));
+    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch, upper);
     HB_CUDA(cudaGetLastError());
   }
   return HB_OK;

@@ -82,6 +82,16 @@ class SumTreef:
         _lib.check(_lib.lib().hb_st_update_range(self._h, int(start), int(n), None, float(value),
                                                  self._stream()))
 
+    def update_range_values(self, start, values):
+        """Ordered update of leaves [start, start+len(values)) with one value each (device or host)."""
+        import torch
+        if not _is_cuda_tensor(values):
+            values = torch.as_tensor(np.ascontiguousarray(values, dtype=np.float32),
+                                     device=torch.device("cuda", self._device))
+        v = values.to(torch.float32).contiguous()
+        _lib.check(_lib.lib().hb_st_update_range(self._h, int(start), v.numel(), v.data_ptr(), 0.0,
+                                                 self._stream()))
+
     def get_index(self, quantile):
         """getIndex(quantile)  sum_tree.h:46-50"""
         return self.get_indices([quantile])[0]

@@ -148,3 +148,70 @@ def test_full_size_properties_cfg3():
     cs = np.concatenate([[0.0], np.cumsum(vals.astype(np.float64))])
     q = keys.astype(np.float64) * float(heap[1])
     assert np.all(cs[idx] <= q * (1 + 1e-3) + 1.0) and np.all(q <= cs[idx + 1] * (1 + 1e-3) + 1.0)
+
+
+# ---- the scan formulation of the ordered sums near the root (csrc/sum_tree.cu) -----------------
+def _apply_range(t, o, start, vals):
+    vals = np.asarray(vals, np.float32)
+    t.update_range_values(start, vals)
+    o.update_values(np.arange(start, start + len(vals)), vals)
+    np.testing.assert_array_equal(t.heap()[1:], o.heap()[1:])
+
+
+def test_range_scan_fill_from_empty_crosses_every_binade():
+    t, o = _trees(1 << 17)
+    _apply_range(t, o, 0, np.full(100000, 0.6, np.float32))
+    _apply_range(t, o, 100000, np.full((1 << 17) - 100000, 0.6, np.float32))
+    _apply_range(t, o, 777, np.full(70001, 0.37, np.float32))       # sums shrink again
+
+
+def test_range_scan_exact_ties_round_to_even():
+    cap = 1 << 17
+    t, o = _trees(cap)
+    _apply_range(t, o, 0, np.ones(cap, np.float32))                  # root = 2^17 exactly, u = 2^-6
+    # diff = 2^-7 = u/2 at the root (a tie at EVERY element), = u one level down, 2u below that ...
+    _apply_range(t, o, 0, np.full(cap, 1 + 2.0 ** -7, np.float32))
+    rng = np.random.default_rng(5)
+    for _ in range(4):   # ties mixed with non-ties and negative diffs, odd starts and lengths
+        start = int(rng.integers(0, cap // 2))
+        n = int(rng.integers(3000, cap // 2))
+        j = rng.integers(-8, 9, n)
+        _apply_range(t, o, start, (1 + j * 2.0 ** -9).astype(np.float32))
+
+
+def test_range_scan_cancellation_large_diffs_and_non_finite():
+    cap = 1 << 16
+    t, o = _trees(cap)
+    rng = np.random.default_rng(6)
+    v = rng.random(cap).astype(np.float32)
+    v[rng.integers(0, cap, 40)] = 1e8                                # the [PROBE] of SURVEY ST-4
+    _apply_range(t, o, 0, v)
+    _apply_range(t, o, 0, np.ones(cap, np.float32))                  # huge negative diffs
+    v = (rng.random(cap) * 1e-6).astype(np.float32)
+    _apply_range(t, o, 0, v)                                         # totals fall through ~20 binades
+    v = rng.random(30000).astype(np.float32)
+    v[12345] = np.inf
+    v[20000] = np.nan
+    _apply_range(t, o, 1000, v)
+    _apply_range(t, o, 0, rng.random(cap).astype(np.float32))        # NaN stays, as in the reference
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_range_scan_fuzz(seed):
+    rng = np.random.default_rng(100 + seed)
+    depth = int(rng.integers(11, 19))
+    cap = 1 << depth
+    t, o = _trees(cap)
+    for _ in range(6):
+        n = int(rng.integers(1, cap + 1))
+        start = int(rng.integers(0, cap - n + 1))
+        kind = int(rng.integers(0, 4))
+        if kind == 0:
+            v = np.full(n, rng.random() * 2, np.float32)
+        elif kind == 1:
+            v = (rng.random(n) ** 0.6).astype(np.float32)
+        elif kind == 2:
+            v = (2.0 ** rng.integers(-12, 6, n)).astype(np.float32)   # powers of two: ties galore
+        else:
+            v = (rng.random(n) * 10.0 ** rng.integers(-6, 5)).astype(np.float32)
+        _apply_range(t, o, start, v)

@@ -84,16 +84,21 @@ mask_scan_kernel(int32_t* __restrict__ block_sum, int n_blocks, int32_t* __restr
   if (threadIdx.x == 0) *total = carry;
 }
 
-// One warp per 32 rows: ranks them, then copies each selected transition with lane-per-word
-// accesses.  Also refreshes last_obs for the selected rows (rlax_rainbow.py:308).
+// Ranks the selected rows of a 1024-row block (ballot + block offsets from the scan), then copies
+// the selected transitions with 16-byte accesses, one (row, 16-byte chunk) item per thread and
+// pass: every load is independent of the others (the first version walked a warp's rows one after
+// the other, 24 of 32 lanes busy, one row's latency at a time: 33 us for 60,000 rows; this: ~6 us).
+// Also refreshes last_obs for the selected rows (rlax_rainbow.py:308).
 __global__ void __launch_bounds__(kScanBlock)
 masked_append_kernel(hb_replay rb, uint32_t* __restrict__ last_obs, const uint32_t* __restrict__ obs,
                      const uint32_t* __restrict__ lms, const int32_t* __restrict__ act,
                      const float* __restrict__ rew, const uint8_t* __restrict__ step_type, int64_t n,
                      const int32_t* __restrict__ block_off) {
   __shared__ int warp_off[32];
+  __shared__ int64_t dst_row[kScanBlock];          // ring position of each selected row, -1 otherwise
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const int64_t i = (int64_t)blockIdx.x * kScanBlock + threadIdx.x;
+  const int64_t row0 = (int64_t)blockIdx.x * kScanBlock;
+  const int64_t i = row0 + threadIdx.x;
   const uint8_t st = i < n ? step_type[i] : 0;
   const bool sel = st != 0;
   const unsigned b = __ballot_sync(0xffffffffu, sel);
@@ -109,39 +114,47 @@ masked_append_kernel(hb_replay rb, uint32_t* __restrict__ last_obs, const uint32
     warp_off[threadIdx.x] = s - v;
   }
   __syncthreads();
-  const int64_t base = rb.oldest + block_off[blockIdx.x] + warp_off[warp];
-  unsigned todo = b;
-  while (todo) {
-    const int src_lane = __ffs(todo) - 1;
-    todo &= todo - 1;
-    const int64_t row = (int64_t)blockIdx.x * kScanBlock + warp * 32 + src_lane;
-    const int rank = __popc(b & ((1u << src_lane) - 1));
-    int64_t pos = base + rank;
-    if (pos >= rb.cap) pos -= rb.cap;                     // ring wrap (experience_buffer.py:62-81)
-    for (int w = lane; w < rb.stride; w += 32) {
-      const uint32_t prev = last_obs[row * rb.stride + w];
-      const uint32_t cur = obs[row * rb.stride + w];
-      rb.obs_tm1[pos * rb.stride + w] = prev;
-      rb.obs_t[pos * rb.stride + w] = cur;
-      last_obs[row * rb.stride + w] = cur;
-    }
-    if (lane < rb.legal_words) rb.lms[pos * rb.legal_words + lane] = lms[row * rb.legal_words + lane];
-    if (lane == 0) {
-      rb.act[pos] = act[row];
-      rb.rew[pos] = rew[row];
-      rb.term[pos] = step_type[row] == 2;
-    }
+  int64_t pos = -1;
+  if (sel) {
+    pos = rb.oldest + block_off[blockIdx.x] + warp_off[warp] + __popc(b & ((1u << lane) - 1));
+    if (pos >= rb.cap) pos -= rb.cap;                       // ring wrap (experience_buffer.py:62-81)
+    for (int w = 0; w < rb.legal_words; ++w) rb.lms[pos * rb.legal_words + w] = lms[i * rb.legal_words + w];
+    rb.act[pos] = act[i];
+    rb.rew[pos] = rew[i];
+    rb.term[pos] = st == 2;
+  }
+  dst_row[threadIdx.x] = pos;
+  __syncthreads();
+  const int q = rb.stride >> 2;                             // 16-byte chunks per row (stride % 4 == 0)
+  const uint4* src_prev = reinterpret_cast<const uint4*>(last_obs) + row0 * q;
+  const uint4* src_cur = reinterpret_cast<const uint4*>(obs) + row0 * q;
+  uint4* upd = reinterpret_cast<uint4*>(last_obs) + row0 * q;
+  uint4* o1 = reinterpret_cast<uint4*>(rb.obs_tm1);
+  uint4* o2 = reinterpret_cast<uint4*>(rb.obs_t);
+  const int items = kScanBlock * q;
+  for (int item = threadIdx.x; item < items; item += kScanBlock) {
+    const int r = item / q, c = item - r * q;
+    const int64_t d = dst_row[r];
+    if (d < 0) continue;
+    const uint4 prev = src_prev[item];
+    const uint4 cur = src_cur[item];
+    o1[d * q + c] = prev;
+    o2[d * q + c] = cur;
+    upd[item] = cur;
   }
 }
 
-// add_experience_first: last_obs[step_type == 0] = obs[...]  (rlax_rainbow.py:292-295)
+// add_experience_first: last_obs[step_type == FIRST] = obs  (rlax_rainbow.py:292-295), 16-byte items
 __global__ void store_first_kernel(uint32_t* __restrict__ last_obs, const uint32_t* __restrict__ obs,
                                    const uint8_t* __restrict__ step_type, int stride, int64_t n) {
-  const int64_t total = n * stride;
+  const int q = stride >> 2;
+  const int64_t total = n * q;
+  const uint4* src = reinterpret_cast<const uint4*>(obs);
+  uint4* dst = reinterpret_cast<uint4*>(last_obs);
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t r = i / stride;
-    if (step_type[r] == 0) last_obs[i] = obs[i];
+    const int64_t r = i / q;
+    if (step_type[r] == 0) dst[i] = src[i];
   }
 }
 
@@ -307,6 +320,8 @@ int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capac
   HB_REQUIRE(obs_len >= 1 && obs_stride_words * 32 >= obs_len && num_moves >= 1 && num_moves <= 64 &&
                  capacity >= 1,
              "hb_rb_create: bad arguments");
+  HB_REQUIRE(obs_stride_words % 4 == 0, "hb_rb_create: rows must be a multiple of 16 bytes (stride %d words)",
+             obs_stride_words);
   hb::DeviceGuard g(device);
   if (!g.ok) { hb::set_error("hb_rb_create: cannot select CUDA device %d", device); return HB_ERR_CUDA; }
   hb_replay* rb = new (std::nothrow) hb_replay();
@@ -408,9 +423,10 @@ int hb_rb_add(hb_replay* rb, const uint32_t* d_obs_tm1, const int32_t* d_act, co
 int hb_rb_store_first(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
                       const uint8_t* d_step_type, int64_t n, void* stream) {
   HB_REQUIRE(rb && d_last_obs && d_obs && d_step_type && n >= 0, "hb_rb_store_first: bad arguments");
+  HB_REQUIRE((((uintptr_t)d_last_obs | (uintptr_t)d_obs) & 15) == 0, "hb_rb_store_first: rows must be 16-byte aligned");
   if (n == 0) return HB_OK;
   hb::DeviceGuard g(rb->device);
-  store_first_kernel<<<blocks_for(n * rb->stride, 256), 256, 0, (cudaStream_t)stream>>>(
+  store_first_kernel<<<blocks_for(n * (rb->stride / 4), 256), 256, 0, (cudaStream_t)stream>>>(
       d_last_obs, d_obs, d_step_type, rb->stride, n);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
@@ -421,6 +437,7 @@ int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
                      int64_t* n_added, void* stream) {
   HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
              "hb_rb_add_masked: bad arguments");
+  HB_REQUIRE((((uintptr_t)d_last_obs | (uintptr_t)d_obs) & 15) == 0, "hb_rb_add_masked: rows must be 16-byte aligned");
   if (n_added) *n_added = 0;
   if (n == 0) return HB_OK;
   hb::DeviceGuard g(rb->device);

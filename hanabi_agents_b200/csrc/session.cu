@@ -77,18 +77,31 @@ __global__ void end_turn_kernel(hb_session s, int agent, const int32_t* __restri
       s.ep_len[g] += 1;
     }
   }
-  // episode statistics: warp sums, one atomic per warp that closed an episode
+  // episode statistics: warp sums -> block sums -> four atomics per block that closed an episode
+  // (one set per warp serialised 8,000 double atomics on one address: 16 us of a 65,536-game tick)
+  __shared__ double red[4][kThreads / 32];
   for (int o = 16; o > 0; o >>= 1) {
     ret += __shfl_xor_sync(0xffffffffu, ret, o);
     len += __shfl_xor_sync(0xffffffffu, len, o);
     cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
     sq += __shfl_xor_sync(0xffffffffu, sq, o);
   }
-  if ((threadIdx.x & 31) == 0 && cnt > 0.0) {
-    atomicAdd(&s.stats[0], ret);
-    atomicAdd(&s.stats[1], cnt);
-    atomicAdd(&s.stats[2], len);
-    atomicAdd(&s.stats[3], sq);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) { red[0][warp] = ret; red[1][warp] = cnt; red[2][warp] = len; red[3][warp] = sq; }
+  __syncthreads();
+  if (warp == 0) {
+    double v[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      v[k] = lane < kThreads / 32 ? red[k][lane] : 0.0;
+      for (int o = 16; o > 0; o >>= 1) v[k] += __shfl_xor_sync(0xffffffffu, v[k], o);
+    }
+    if (lane == 0 && v[1] > 0.0) {
+      atomicAdd(&s.stats[0], v[0]);
+      atomicAdd(&s.stats[1], v[1]);
+      atomicAdd(&s.stats[2], v[2]);
+      atomicAdd(&s.stats[3], v[3]);
+    }
   }
 }
 

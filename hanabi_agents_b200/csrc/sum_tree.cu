@@ -317,6 +317,7 @@ __global__ void st_range_internal_warp_kernel(float* __restrict__ heap, int dept
 // construction; tests/test_sum_tree_gpu.py drives ties, crossings, cancellations and NaNs through it.
 constexpr int kScanThreads = 1024;
 constexpr int kScanMinRun = 512;     // shorter remainders: plain ordered chain by one warp
+constexpr int kScanSlice = 8;        // elements per thread and window
 constexpr int kScanSpanLog2 = 11;    // levels whose nodes cover >= 2048 leaves use the scan
 
 struct SegFn {
@@ -405,19 +406,33 @@ st_range_internal_scan_kernel(float* __restrict__ heap, int depth, int64_t cap, 
       pos += take;
       continue;
     }
-    const int64_t seg = (rem + kScanThreads - 1) / kScanThreads;
+    // one window of at most kScanThreads * kScanSlice elements: a failed premise costs one window,
+    // not the whole remainder (a node that starts empty crosses a binade every doubling)
+    const int64_t win = rem < (int64_t)kScanThreads * kScanSlice ? rem : (int64_t)kScanThreads * kScanSlice;
+    const int64_t seg = (win + kScanThreads - 1) / kScanThreads;      // <= kScanSlice
+    const int64_t wend = pos + win;
     int64_t b = pos + (int64_t)tid * seg;
-    if (b > cnt) b = cnt;
-    const int64_t e = b + seg < cnt ? b + seg : cnt;
+    if (b > wend) b = wend;
+    const int64_t e = b + seg < wend ? b + seg : wend;
     // d / u with u = 2^(eb-127-23): a power-of-two scaling, exact in double
     const double scale = __longlong_as_double((long long)(1173 - eb) << 52);
     if (tid == 0) sh_bad = kScanThreads;
-    // pass 1: this slice as a map on S
+    // the slice in registers; 0 past its end (d = 0 is the identity map)
+    double Dv[kScanSlice];
+    bool fin = true;
+#pragma unroll
+    for (int j = 0; j < kScanSlice; ++j) {
+      const float x = b + j < e ? __ldg(d + b + j) : 0.f;
+      Dv[j] = (double)x * scale;
+      fin = fin && (fabs(Dv[j]) < 16777216.0);
+    }
+    // pass 1: this slice as a map on S (a slice with a non-finite / oversized element is
+    // flagged below; nothing after it is kept)
     SegFn f;
     f.A = 0; f.R = 0; f.tie = 0;
-    for (int64_t k = b; k < e; ++k) {
-      const double D = (double)__ldg(d + k) * scale;
-      if (!(fabs(D) < 16777216.0)) continue;            // flagged by pass 2; nothing after it is kept
+#pragma unroll
+    for (int j = 0; j < kScanSlice; ++j) {
+      const double D = fin ? Dv[j] : 0.0;
       const double fl = floor(D);
       const double fr = D - fl;
       long long m = (long long)fl;
@@ -460,18 +475,18 @@ st_range_internal_scan_kernel(float* __restrict__ heap, int depth, int64_t cap, 
     const long long S_in = seg_apply(pre, S0);
     // pass 2: replay the slice from its true incoming S and check the premise at every element
     long long S = S_in;
-    bool ok = true;
-    for (int64_t k = b; k < e; ++k) {
-      const double D = (double)__ldg(d + k) * scale;
-      if (!(fabs(D) < 16777216.0)) { ok = false; break; }
+    bool ok = fin;
+#pragma unroll
+    for (int j = 0; j < kScanSlice; ++j) {
+      const double D = fin ? Dv[j] : 0.0;
       const double fl = floor(D);
       const double fr = D - fl;
       const long long m = (long long)fl;
-      if (S + m < kLo) { ok = false; break; }          // exact sum below 2^e: finer grid there
+      if (S + m < kLo) ok = false;                     // exact sum below 2^e: finer grid there
       long long t = S + m;
       if (fr == 0.5) t += t & 1;
       else if (fr > 0.5) t += 1;
-      if (t > kHi) { ok = false; break; }               // reached 2^(e+1): coarser grid from here
+      if (t > kHi) ok = false;                         // reached 2^(e+1): coarser grid from here
       S = t;
     }
     if (!ok) atomicMin(&sh_bad, tid);
@@ -482,15 +497,15 @@ st_range_internal_scan_kernel(float* __restrict__ heap, int depth, int64_t cap, 
       __syncthreads();
       s = sh_s;
       __syncthreads();
-      pos = cnt;
+      pos = wend;
     } else {
       if (tid == bad) sh_s = __uint_as_float(((uint32_t)eb << 23) | ((uint32_t)S_in & 0x7fffffu));
       __syncthreads();
       const float sb = sh_s;
       __syncthreads();
       int64_t bb = pos + (int64_t)bad * seg;
-      if (bb > cnt) bb = cnt;
-      const int64_t be = bb + seg < cnt ? bb + seg : cnt;
+      if (bb > wend) bb = wend;
+      const int64_t be = bb + seg < wend ? bb + seg : wend;
       if (warp == 0) {
         const float r = warp_chain(sb, d + bb, be - bb, lane);
         if (lane == 0) sh_s = r;

@@ -137,10 +137,15 @@ class HanabiParallelEnv:
                                                step_type.ctypes.data))
         return obs, legal, reward, step_type
 
-    def observe(self, offset=0):
+    def observe(self, offset=0, out=None):
+        """HanabiObservation of the player `offset` seats after the mover, for every game
+        (bit-packed rows + legal masks; `out` = (obs, legal) reuses caller-owned buffers)."""
         torch = self.torch
-        obs = torch.zeros_like(self.obs_packed)
-        legal = torch.zeros_like(self.legal_packed)
+        if out is not None:
+            obs, legal = out
+        else:
+            obs = torch.empty_like(self.obs_packed)
+            legal = torch.empty_like(self.legal_packed)
         _lib.check(_lib.lib().hb_env_observe(self._h, int(offset), obs.data_ptr(), legal.data_ptr(),
                                              self._s()))
         return obs, legal

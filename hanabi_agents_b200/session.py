@@ -62,6 +62,7 @@ class HanabiParallelSession:
                 self._learners.append(a)
         self.tick = 0
         self.is_reset = False
+        self._side_obs = None
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -87,7 +88,9 @@ class HanabiParallelSession:
             return (env, None)
         if offset == 0:
             return env.observations_packed()
-        return (env, env.observe(offset))
+        if self._side_obs is None:
+            self._side_obs = (self.torch.empty_like(env.obs_packed), self.torch.empty_like(env.legal_packed))
+        return (env, env.observe(offset, out=self._side_obs))
 
     # -- control ----------------------------------------------------------------------------
     def reset(self, clear_stats=True):

@@ -210,6 +210,63 @@ def bench_learner(env, obs, legal, reward, stype, action, T, world, args):
     return learner, acting
 
 
+def bench_session(n, world, rank, args):
+    """DQN self-play through HanabiParallelSession at the Rainbow configuration
+    of BASELINE configs[3]: two learning agents take turns over n games of this GPU; a training
+    tick = per-seat accounting + replay insert (both seats) + explore + env step; then the same
+    with one learner update per agent and tick (gradient all-reduce across ranks when world > 1)."""
+    import torch
+    import torch.distributed as dist
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.rlax_dqn import DQNAgent, RlaxRainbowParams
+    from hanabi_agents_b200.session import HanabiParallelSession
+    env = HanabiParallelEnv(n, "Hanabi-Full", 2, n_decks=4 * n * world, seed=SEED,
+                            game_id_base=rank * n, n_total=n * world)
+    params = RlaxRainbowParams(train_batch_size=256, layers=[512, 512], experience_buffer_size=2 ** 20,
+                               n_atoms=51, atom_vmax=25, seed=SEED)
+    agents = [DQNAgent(env.observation_spec(), env.action_spec(), params),
+              DQNAgent(env.observation_spec(), env.action_spec(), params._replace(seed=SEED + 1))]
+    ses = HanabiParallelSession(env, agents)
+    ses.reset()
+    ses.run(24, train=True)                       # fills both shards past the batch size
+    for a in agents:
+        a.update()
+
+    def timed(fn, reps):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], device=env.device)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def learn_tick():
+        ses.step(train=True)
+        for a in agents:
+            a.update()
+
+    k = args.session_ticks
+    ev = timed(lambda: ses.step(train=False), k)
+    tr = timed(lambda: ses.step(train=True), k)
+    lt = timed(learn_tick, k)
+    st = ses.stats()
+    return {"games_per_gpu": n, "ticks": k, "agents": "2 x DQNAgent 658-512-512-(20x51) noisy C51, replay 2^20 rows each",
+            "eval_tick_ms": ev, "train_tick_ms": tr, "train_tick_plus_update_ms": lt,
+            "env_steps_per_s_eval": world * n / (ev * 1e-3), "env_steps_per_s_train": world * n / (tr * 1e-3),
+            "env_steps_per_s_train_plus_update": world * n / (lt * 1e-3),
+            "episodes_closed": st["episodes"], "mean_episode_length": st["mean_length"],
+            "illegal_moves": env.illegal_count()}
+
+
 def bench_sum_tree(args):
     """BASELINE configs[2]: capacity 2^22, batch 256 stratified sample + priority update
     (SURVEY 8d cfg 3), device path; CPU side = the reference's own C++ tree (oracle/_ref)."""
@@ -394,6 +451,7 @@ def run_ours(args):
     learner = acting = None
     if not args.no_learner:
         learner, acting = bench_learner(env, obs, legal, reward, stype, action, T, world, args)
+    session = None if args.no_session else bench_session(n, world, rank, args)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -446,6 +504,7 @@ def run_ours(args):
         "learner": learner,
         "acting": acting,
         "sum_tree": tree,
+        "session": session,
     }
     print(json.dumps(out))
     if world > 1:
@@ -467,6 +526,8 @@ def main():
     ap.add_argument("--tree-iters", type=int, default=3000)
     ap.add_argument("--no-learner", action="store_true")
     ap.add_argument("--no-tree", action="store_true")
+    ap.add_argument("--no-session", action="store_true")
+    ap.add_argument("--session-ticks", type=int, default=100)
     args = ap.parse_args()
     if args.impl == "reference":
         if args.steps > 2048:

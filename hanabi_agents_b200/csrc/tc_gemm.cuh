@@ -13,7 +13,8 @@
 //   warp 2     allocates / frees tensor memory
 //   warps 4-11 epilogue (two warps per TMEM lane quarter, half the columns each) of the previous tile while the next one is being multiplied:
 //              tcgen05.ld 32 lanes x 32 columns at a time, fused bias / ReLU / gate / transposed
-//              copy / categorical head, vectorised global stores
+//              copy / categorical head; fp16 outputs leave through swizzled shared memory and
+//              cp.async.bulk.tensor stores, the others with vectorised global stores
 // BN = 256 halves the shared-memory fill traffic per flop (A 16 KB + B 32 KB per 128x256x64
 // block = 87 flop/B against 64 flop/B at BN = 128): the v1 one-tile-per-CTA kernel sat at 16-22 %
 // tensor-pipe activity, bound by CTA set-up and L2 -> SM fill (profiles/r01_gemm_acting_v1_*).
@@ -33,8 +34,11 @@ constexpr int UMMA_K = 16;
 constexpr int kThreads = 384;                     // 4 control warps + 8 epilogue warps
 // tile width BN_ is 128 or 256 (template parameter): 6 x 32 KB or 4 x 48 KB of operand ring
 __host__ __device__ constexpr int stages_for(int bn) { return bn == 256 ? 4 : 6; }
+constexpr int kEpiWarps = 8;
+constexpr int kOutStage = 32 * 64 * 2;            // per epilogue warp: 32 rows x 64 fp16, TMA-store box
 __host__ __device__ constexpr int smem_bytes_for(int bn) {
-  return stages_for(bn) * (BM + bn) * BK * 2 + 1024 /*align slack*/ + 256 /*barriers*/;
+  return stages_for(bn) * (BM + bn) * BK * 2 + kEpiWarps * kOutStage + 1024 /*align slack*/ +
+         256 /*barriers*/;
 }
 
 enum Epilogue {
@@ -53,6 +57,7 @@ struct EpiParams {
   const __half* gate;        // EPI_F16: multiply by (gate[m, n] > 0) (ReLU backward), or nullptr
   int ld_gate;
   __half* out16;             // EPI_F16: [M, ld_out]
+  int tma_out;               // EPI_F16: out16 goes out through the TMA-store map (staged in smem)
   __half* out16_t;           // EPI_F16: optional transposed copy [N, ld_out_t]
   float* out32;              // EPI_F32 / EPI_C51 (logits, optional)
   int ld_out, ld_out_t;
@@ -117,6 +122,20 @@ __device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* m
       ::"r"(smem_u32(smem_dst)), "l"((uint64_t)map), "r"(smem_u32(bar)), "r"(x), "r"(y)
       : "memory");
 }
+// shared -> global tile store (bulk async-group completion)
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, const void* smem_src, int x, int y) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(
+                   (uint64_t)map),
+               "r"(smem_u32(smem_src)), "r"(x), "r"(y)
+               : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+// the staging buffer of every committed store has been read (it may be overwritten)
+__device__ __forceinline__ void tma_store_wait_read() {
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+// every committed store is complete
+__device__ __forceinline__ void tma_store_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void prefetch_tmap(const CUtensorMap* map) {
   asm volatile("prefetch.tensormap [%0];" ::"l"((uint64_t)map) : "memory");
 }
@@ -216,7 +235,8 @@ __device__ __forceinline__ void load_bias(const float* __restrict__ bias, int nb
 // `acc_col` (thread = TMEM lane = D row, 32 fp32 columns per tcgen05.ld).
 template <int EPI, int BN_>
 __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_col, int m0, int n0,
-                                              int ew, int half, int lane, const EpiParams& ep) {
+                                              int ew, int half, int lane, const EpiParams& ep,
+                                              const CUtensorMap* tmap_out, uint8_t* stage) {
   const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16) + acc_col;
   const bool row_ok = (m0 + ew * 32 + lane) < ep.M;
   const int m = m0 + ew * 32 + lane;
@@ -269,6 +289,71 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_c
         const float den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
         const float num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
         ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
+      }
+    }
+  } else if (EPI == EPI_F16 && ep.tma_out) {
+    // 64 columns at a time: the warp's 32 x 64 fp16 block is laid out in shared memory as the
+    // 128-byte-swizzled box of the output tensor map and leaves with ONE bulk tensor store --
+    // whole 128-byte lines, asynchronous, clipped at M and N by the map.  (Direct stores had every
+    // thread write its own 64-byte pieces of a row, 1 KB apart from its neighbours': the fp16
+    // layers ran 20-25 % behind the same tile with a small output.)
+#pragma unroll 1
+    for (int c = half * (BN_ / 128); c < (half + 1) * (BN_ / 128); ++c) {
+      uint32_t v0[32], v1[32];
+      tmem_ld32(lane_addr + c * 64, v0);
+      tmem_ld32(lane_addr + c * 64 + 32, v1);
+      const int nb = n0 + c * 64;
+      if (nb >= ep.N) continue;                    // warp-uniform
+      float x[64];
+      load_bias<64>(ep.bias, nb, ep.N, x);
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        x[j] += ep.alpha * __uint_as_float(v0[j]);
+        x[32 + j] += ep.alpha * __uint_as_float(v1[j]);
+      }
+      if (ep.relu) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j) x[j] = fmaxf(x[j], 0.f);
+      }
+      if (ep.gate != nullptr && row_ok) {
+        const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + nb);
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4) {
+          if (nb + 8 * j4 < ep.N) {
+            const uint4 gv = __ldg(g + j4);
+            const __half2* gh = reinterpret_cast<const __half2*>(&gv);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float2 f = __half22float2(gh[j]);
+              if (!(f.x > 0.f)) x[8 * j4 + 2 * j] = 0.f;
+              if (!(f.y > 0.f)) x[8 * j4 + 2 * j + 1] = 0.f;
+            }
+          }
+        }
+      }
+      uint32_t p[32];
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
+        p[j] = *reinterpret_cast<const uint32_t*>(&h2);
+      }
+      if (lane == 0) tma_store_wait_read();        // the previous block has left the buffer
+      __syncwarp();
+#pragma unroll
+      for (int j4 = 0; j4 < 8; ++j4)               // 16-byte chunk j4 of row `lane`, swizzled
+        *reinterpret_cast<uint4*>(stage + lane * 128 + ((j4 ^ (lane & 7)) << 4)) =
+            make_uint4(p[4 * j4], p[4 * j4 + 1], p[4 * j4 + 2], p[4 * j4 + 3]);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_2d(tmap_out, stage, nb, m0 + ew * 32);
+        tma_store_commit();
+      }
+      if (ep.out16_t != nullptr && row_ok) {
+#pragma unroll
+        for (int j = 0; j < 64; ++j)
+          if (nb + j < ep.N)
+            ep.out16_t[(size_t)(nb + j) * ep.ld_out_t + m] = __float2half_rn(x[j]);
       }
     }
   } else {
@@ -351,12 +436,13 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_c
 template <int EPI, int BN_, bool ABITS>
 __global__ void __launch_bounds__(kThreads, 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
-                int K, EpiParams ep) {
+                const __grid_constant__ CUtensorMap tmap_out, int K, EpiParams ep) {
   constexpr int kSt = stages_for(BN_);
   constexpr int kStB = (BM + BN_) * BK * 2;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full_bar = (uint64_t*)(smem + kSt * kStB);
+  uint8_t* out_stage = smem + kSt * kStB;            // kEpiWarps x 4 KB, 1024-byte aligned
+  uint64_t* full_bar = (uint64_t*)(out_stage + kEpiWarps * kOutStage);
   uint64_t* empty_bar = full_bar + kSt;
   uint64_t* acc_full = empty_bar + kSt;
   uint64_t* acc_empty = acc_full + 2;
@@ -371,6 +457,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmap_a);
     prefetch_tmap(&tmap_b);
+    if (EPI == EPI_F16 && ep.tma_out) prefetch_tmap(&tmap_out);
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < kSt; ++s) {
@@ -488,11 +575,13 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
       const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN_;
       mbar_wait(&acc_full[buf], (i >> 1) & 1);
       tc_fence_after();
-      epilogue_tile<EPI, BN_>(tmem_base, (uint32_t)(buf * BN_), m0, n0, ew, half, lane, ep);
+      epilogue_tile<EPI, BN_>(tmem_base, (uint32_t)(buf * BN_), m0, n0, ew, half, lane, ep, &tmap_out,
+                              out_stage + (warp - 4) * kOutStage);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&acc_empty[buf]);
     }
+    if (EPI == EPI_F16 && ep.tma_out && lane == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();

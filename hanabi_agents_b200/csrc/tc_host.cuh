@@ -54,8 +54,8 @@ inline int sm_count() {
 }
 
 template <int EPI, int BN_, bool ABITS = false>
-inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
-                       const EpiParams& ep, cudaStream_t stream) {
+inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tout, int M, int N,
+                       int K, const EpiParams& ep, cudaStream_t stream) {
   static bool configured[64] = {false};
   int dev = 0;
   HB_CUDA(cudaGetDevice(&dev));
@@ -67,8 +67,22 @@ inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int 
   const long long tiles = (long long)((N + BN_ - 1) / BN_) * ((M + BM - 1) / BM);
   const int sms = sm_count();
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  gemm_f16_kernel<EPI, BN_, ABITS><<<grid, kThreads, smem_bytes_for(BN_), stream>>>(ta, tb, K, ep);
+  gemm_f16_kernel<EPI, BN_, ABITS><<<grid, kThreads, smem_bytes_for(BN_), stream>>>(ta, tb, tout, K, ep);
   HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+// Output map of the fp16 epilogue (box = 32 rows x 64 columns, what one epilogue warp stores at a
+// time); falls back to direct stores when the output is not 16-byte aligned.
+template <int EPI>
+inline int out_map(CUtensorMap* tout, const CUtensorMap& dflt, EpiParams& ep) {
+  *tout = dflt;
+  ep.tma_out = 0;
+  if (EPI != EPI_F16 || ep.out16 == nullptr) return HB_OK;
+  if (((uintptr_t)ep.out16 & 15) != 0 || ((long long)ep.ld_out * 2) % 16 != 0) return HB_OK;
+  const int rc = make_tmap(tout, ep.out16, ep.M, ep.N, ep.ld_out, 32);
+  if (rc) return rc;
+  ep.tma_out = 1;
   return HB_OK;
 }
 
@@ -86,8 +100,11 @@ inline int gemm(const __half* A, int64_t lda, const __half* B, int64_t ldb, int 
   if (rc) return rc;
   ep.M = M;
   ep.N = N;
-  if (bn == 256) return launch_gemm<EPI, 256>(ta, tb, M, N, K, ep, stream);
-  return launch_gemm<EPI, 128>(ta, tb, M, N, K, ep, stream);
+  CUtensorMap tout;
+  rc = out_map<EPI>(&tout, tb, ep);
+  if (rc) return rc;
+  if (bn == 256) return launch_gemm<EPI, 256>(ta, tb, tout, M, N, K, ep, stream);
+  return launch_gemm<EPI, 128>(ta, tb, tout, M, N, K, ep, stream);
 }
 
 // Same with the A operand given as bit-packed rows [M, a_stride words] (K = 32 * a_stride bits,
@@ -109,8 +126,11 @@ inline int gemm_bits(const uint32_t* A_bits, int a_stride, const __half* B, int6
   ep.N = N;
   ep.a_bits = A_bits;
   ep.a_stride = a_stride;
-  if (bn == 256) return launch_gemm<EPI, 256, true>(tb, tb, M, N, K, ep, stream);
-  return launch_gemm<EPI, 128, true>(tb, tb, M, N, K, ep, stream);
+  CUtensorMap tout;
+  rc = out_map<EPI>(&tout, tb, ep);
+  if (rc) return rc;
+  if (bn == 256) return launch_gemm<EPI, 256, true>(tb, tb, tout, M, N, K, ep, stream);
+  return launch_gemm<EPI, 128, true>(tb, tb, tout, M, N, K, ep, stream);
 }
 
 }  // namespace tc

@@ -210,6 +210,37 @@ def bench_learner(env, obs, legal, reward, stype, action, T, world, args):
     return learner, acting
 
 
+def cpu_learner_baseline(seconds):
+    """CPU baseline of the learner step ('PyTorch-CPU restatement, all cores; JAX CPU
+    learner unavailable on this box'): oracle/learner.py OracleQNet, same net / batch as `learner`."""
+    import numpy as np
+    import torch
+    from hanabi_agents_b200.rlax_dqn.network import init_params
+    from oracle.learner import OracleQNet
+    rng = np.random.default_rng(SEED)
+    B, L, A = 256, 658, 20
+    net = OracleQNet(init_params(L, [512, 512], A, 51, noisy=True, seed=SEED), A, 51, 25.0, noisy=True,
+                     mirror_fp16=False)
+    o1 = torch.tensor((rng.random((B, L)) < 0.15).astype(np.float32))
+    o2 = torch.tensor((rng.random((B, L)) < 0.15).astype(np.float32))
+    a = torch.tensor(rng.integers(0, A, B))
+    r = torch.tensor(rng.integers(0, 2, B).astype(np.float32))
+    term = torch.zeros(B, dtype=torch.bool)
+    pr = torch.tensor(rng.random(B).astype(np.float32) + 0.1)
+    done, t0 = 0, time.perf_counter()
+    while True:
+        _, _, g = net.grads(o1, a, r, o2, term, prios=pr, beta=0.4, discount=0.99)
+        net.adam(g, lr=6.25e-5)
+        done += 1
+        el = time.perf_counter() - t0
+        if el >= seconds or done >= 200:
+            break
+    return {"updates_per_s": done / el, "ms_per_update": 1e3 * el / done, "kind": "port",
+            "threads": torch.get_num_threads(),
+            "sample": "%d updates of batch 256 in %.1f s (PyTorch-CPU fp32 restatement of update_q + adam; "
+                      "the reference's JAX learner is not installable here)" % (done, el)}
+
+
 def bench_session(n, world, rank, args):
     """DQN self-play through HanabiParallelSession at the Rainbow configuration
     of BASELINE configs[3]: two learning agents take turns over n games of this GPU; a training
@@ -308,6 +339,27 @@ def bench_sum_tree(args):
            "us_per_iter": 1e3 * ms / iters,
            "algorithmic_GBps": 70656 * iters / (ms * 1e-3) / 1e9,
            "note": "latency-bound: 22 dependent levels; 2 launches per iteration"}
+    # throughput variant (SURVEY 8d cfg 3): 1,024 independent batches of 256 keys in flight in ONE
+    # sample launch (descent + leaf gather + total: 4*22 + 4 = 92 algorithmic bytes per key)
+    nb = 1024
+    big = torch.as_tensor((np.linspace(1 / B, 1, B)[None, :] - rng.uniform(0, 1 / B, (nb, B))).astype(np.float32)
+                          .reshape(-1), device="cuda")
+    bb = (torch.empty(nb * B, dtype=torch.int64, device="cuda"), torch.empty(nb * B, dtype=torch.float32, device="cuda"),
+          torch.empty(1, dtype=torch.float32, device="cuda"))
+    for _ in range(3):
+        tree.sample(big, out=bb)
+    torch.cuda.synchronize()
+    reps = 20
+    ev0.record()
+    for _ in range(reps):
+        tree.sample(big, out=bb)
+    ev1.record()
+    torch.cuda.synchronize()
+    tms = ev0.elapsed_time(ev1) / reps
+    out["throughput_variant"] = {"batches_in_flight": nb, "keys_per_launch": nb * B, "ms_per_launch": tms,
+                                 "keys_per_s": nb * B / (tms * 1e-3),
+                                 "algorithmic_GBps": 92.0 * nb * B / (tms * 1e-3) / 1e9,
+                                 "note": "sampling only: ordered updates of one tree are one dependent chain"}
     # CPU: the reference's own pybind module, one thread (parity mode) -- bounded sample
     try:
         sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
@@ -457,6 +509,11 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     tree = None if args.no_tree else bench_sum_tree(args)
+    if learner is not None and args.cpu_seconds > 0:
+        try:
+            learner["cpu_baseline"] = cpu_learner_baseline(min(args.cpu_seconds, 10.0))
+        except Exception as e:
+            learner["cpu_baseline"] = {"unavailable": repr(e)[:200]}
 
     # ---- roofline of the dominant kernel (selfplay_kernel), live from the timed region
     peak, which = peaks()
@@ -476,7 +533,8 @@ def run_ours(args):
             traffic = None
     roof = {"bound": "hbm", "kernel": "selfplay_kernel", "achieved": achieved, "peak": peak,
             "peak_source": which + " copy bandwidth (MEASURED_PEAKS.json)", "unit": "GB/s",
-            "frac": achieved / peak, "traffic": traffic,
+            "frac": achieved / peak, "peak_nominal": 8000.0, "frac_nominal": achieved / 8000.0,
+            "traffic": traffic,
             "algorithmic_bytes_per_launch": bytes_per_launch,
             "launch_ms": launch_ms}
 

@@ -129,7 +129,7 @@ env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
 }
 
 // RulebasedAgent.explore over the whole batch (rule_based.py:27-31)
-template <class SH>
+template <class SH, bool EXT>
 __global__ void __launch_bounds__(kThreads)
 rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned long long step,
                  int32_t* __restrict__ action, int32_t* __restrict__ rule_hit,
@@ -140,7 +140,7 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
   load_game(g, state, game);
   int a = 0, hit = -1;
   if (g.step_type != LAST)
-    a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
+    a = rules_act<SH, EXT>(g, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
   action[game] = a;
   if (rule_hit != nullptr) rule_hit[game] = hit;
   if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
@@ -148,7 +148,7 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
 
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
 // held in registers; only the per-step outputs touch HBM.  Output row (t, game).
-template <class SH>
+template <class SH, bool EXT>
 __global__ void __launch_bounds__(kThreads, 7)
 selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks, RuleSet rs,
                 unsigned long long step0, int n_steps, uint32_t* __restrict__ obs,
@@ -168,7 +168,7 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   for (int t = 0; t < n_steps; ++t) {
     int a = 0, hit = -1;
     if (g.step_type != LAST)
-      a = rules_act(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
+      a = rules_act<SH, EXT>(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
     const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, lm, illegal);
     const long long row = (long long)t * rt.n_games + game;
     if (action != nullptr) action[row] = a;
@@ -324,6 +324,13 @@ int env_stage(hb_env* e, size_t bytes) {
   HB_CUDA(cudaMalloc(&e->stage, bytes));
   e->stage_bytes = bytes;
   return HB_OK;
+}
+
+// rule lists with one of the rules that are dead in the reference run the EXT kernels
+inline bool uses_ext_rules(const RuleSet& rs) {
+  for (int k = 0; k < rs.n; ++k)
+    if (rs.id[k] >= R_TELL_ANYONE_USELESS_CARD) return true;
+  return false;
 }
 
 int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int32_t* iarg, int n,
@@ -551,9 +558,15 @@ int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, co
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (rules_act_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
-                     e->rt, e->state, rs, step, d_action, d_rule_hit,
-                     (unsigned long long*)d_hist)));
+  if (uses_ext_rules(rs)) {
+    HB_DISPATCH(e, (rules_act_kernel<SH, true><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
+                       e->rt, e->state, rs, step, d_action, d_rule_hit,
+                       (unsigned long long*)d_hist)));
+  } else {
+    HB_DISPATCH(e, (rules_act_kernel<SH, false><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
+                       e->rt, e->state, rs, step, d_action, d_rule_hit,
+                       (unsigned long long*)d_hist)));
+  }
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -568,9 +581,15 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
-  HB_DISPATCH(e, (selfplay_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
-                     e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
-                     d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
+  if (uses_ext_rules(rs)) {
+    HB_DISPATCH(e, (selfplay_kernel<SH, true><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
+                       e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
+                       d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
+  } else {
+    HB_DISPATCH(e, (selfplay_kernel<SH, false><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
+                       e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
+                       d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
+  }
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }

@@ -9,7 +9,10 @@
 // counter-based stream keyed (seed, game id, step, draw); legal_random / discard_randomly use
 // their intended semantics (the reference versions raise TypeError, ruleset.py:598-614);
 // tell_unknown hints the real card's colour/rank (the reference builds an illegal move from
-// the knowledge object, :291-307); osawa_discard keeps the fireworks[-1] quirk (:229-230).
+// the knowledge object, :291-307); osawa_discard keeps the fireworks[-1] quirk (:229-230);
+// tell_anyone_useless_card (:522-535), tell_playable_card (:570-594) and
+// discard_probably_useless (:638-649) raise TypeError in the reference and follow their intended
+// semantics here.
 #pragma once
 #include "hanabi_game.cuh"
 
@@ -20,7 +23,8 @@ enum RuleId {
   R_PLAY_SAFE_CARD = 4, R_PLAY_IF_CERTAIN = 5, R_TELL_PLAYABLE_CARD_OUTER = 6,
   R_TELL_DISPENSABLE = 7, R_TELL_ANYONE_USEFUL_CARD = 8, R_PLAY_PROBABLY_SAFE = 9,
   R_HAIL_MARY = 10, R_LEGAL_RANDOM = 11, R_DISCARD_RANDOMLY = 12, R_TELL_MOST_INFORMATION = 13,
-  R_NUM_RULES = 14
+  R_TELL_ANYONE_USELESS_CARD = 14, R_TELL_PLAYABLE_CARD = 15, R_DISCARD_PROBABLY_USELESS = 16,
+  R_NUM_RULES = 17
 };
 
 constexpr int kMaxRules = 16;
@@ -152,6 +156,49 @@ __device__ __forceinline__ int play_probably_safe(const Game<SH>& g, double thre
   return -1;
 }
 
+// grid of the cards that can no longer score: rank below the stack or at / beyond max_fireworks
+// (useless_card  ruleset.py:35-42)
+template <class SH>
+__device__ __forceinline__ uint32_t useless_grid(const Game<SH>& g) {
+  uint32_t mf;
+  const uint32_t useful = useful_grid(g, &mf);
+  uint32_t below = 0;
+#pragma unroll
+  for (int c = 0; c < SH::C; ++c) below |= ((1u << g.firework(c)) - 1) << (5 * c);
+  return (~useful | below) & SH::kGridAll;
+}
+
+// discard_probably_useless_factory  ruleset.py:638-649 with get_probability_useless :127-170
+// (intended semantics): same bookkeeping as play_probably_safe with the useless grid.
+template <class SH>
+__device__ __forceinline__ int discard_probably_useless(const Game<SH>& g, double threshold) {
+  const int n = g.hand_n(0);
+  if (!(g.info < 8) || n == 0) return -1;
+  unsigned long long vis = g.disc;
+#pragma unroll
+  for (int k = 1; k < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i)
+      if (slot_valid(g.hand[k][i])) vis += 1ull << (2 * slot_card(g.hand[k][i]));
+#pragma unroll
+  for (int c = 0; c < SH::C; ++c)
+    vis += (0x155ull & ((1ull << (2 * g.firework(c))) - 1)) << (10 * c);
+  const unsigned long long left = instances_packed<SH>() - vis;
+  const unsigned long long ug_s = spread_grid(useless_grid(g));
+  int best = 0, bu = 0, bt = 1;
+#pragma unroll
+  for (int i = 0; i < SH::H; ++i) {
+    if (i < n) {
+      const unsigned long long gs = spread_grid(slot_grid(g.hand[0][i]));
+      const int total = sum_fields(left, gs);
+      const int useless = sum_fields(left, gs & ug_s);
+      if (i == 0 || useless * bt > bu * total) { bu = useless; bt = total; best = i; }
+    }
+  }
+  if ((double)bu / (double)bt >= threshold) return uid_discard<SH>(best);
+  return -1;
+}
+
 // tell_playable_card_outer  ruleset.py:413-451
 template <class SH>
 __device__ __forceinline__ int tell_playable_outer(const Game<SH>& g) {
@@ -171,11 +218,66 @@ __device__ __forceinline__ int tell_playable_outer(const Game<SH>& g) {
   return mv;
 }
 
+// The three rules that are dead in the reference (ids >= R_TELL_ANYONE_USELESS_CARD).  Kept out of
+// run_rule's switch and compiled only into the EXT instantiations of the kernels: with them in
+// the same switch the fused self-play kernel of the headline benchmark lost 11 % (register
+// allocation of the hot cases), although a piers agent never executes them.
 template <class SH>
+__device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double farg,
+                                         unsigned long long seed, unsigned long long game_id,
+                                         unsigned long long step) {
+  constexpr int H = SH::H, P = SH::P;
+  switch (rule) {
+    case R_TELL_ANYONE_USELESS_CARD: {                 // :522-535 (intended semantics)
+      if (!(g.info > 1)) return -1;
+      const uint32_t ug = useless_grid(g);
+      int mv = -1;
+#pragma unroll
+      for (int k = P - 1; k >= 1; --k)
+#pragma unroll
+        for (int i = H - 1; i >= 0; --i) {
+          const uint32_t w = g.hand[k][i];
+          const int card = slot_card(w);
+          if (slot_valid(w) && ((ug >> card) & 1u)) {
+            if (!slot_chint(w)) mv = uid_color<SH>(k, card_color(card));
+            else if (!slot_rhint(w)) mv = uid_rank<SH>(k, card_rank(card));
+          }
+        }
+      return mv;
+    }
+
+    case R_TELL_PLAYABLE_CARD: {                       // :570-594 (intended semantics)
+      if (!(g.info > 0)) return -1;
+      int fk = -1, fc = 0;
+#pragma unroll
+      for (int k = P - 1; k >= 1; --k)
+#pragma unroll
+        for (int i = H - 1; i >= 0; --i) {
+          const uint32_t w = g.hand[k][i];
+          const int card = slot_card(w);
+          if (slot_valid(w) && card_rank(card) == g.firework(card_color(card))) { fk = k; fc = card; }
+        }
+      if (fk < 0) return -1;
+      const int coin = rand_below(rule_rand(seed, game_id, step, 4), 2);   // random.randint(0, 1) :584
+      return coin == 0 ? uid_rank<SH>(fk, card_rank(fc)) : uid_color<SH>(fk, card_color(fc));
+    }
+
+    case R_DISCARD_PROBABLY_USELESS:                   // :638-649
+      return discard_probably_useless(g, farg);
+
+    default:
+      return -1;
+  }
+}
+
+template <class SH, bool EXT = false>
 __device__ __forceinline__ int run_rule(const Game<SH>& g, int rule, double farg, int iarg,
                                         unsigned long long seed, unsigned long long game_id,
                                         unsigned long long step) {
   constexpr int C = SH::C, R = SH::R, H = SH::H, P = SH::P;
+  if constexpr (EXT) {
+    if (rule >= R_TELL_ANYONE_USELESS_CARD) return run_ext_rule(g, rule, farg, seed, game_id, step);
+  }
   switch (rule) {
     case R_DISCARD_OLDEST_FIRST:                       // ruleset.py:206-216
       return g.info < 8 ? uid_discard<SH>(0) : -1;
@@ -311,7 +413,7 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, int rule, double farg
 
 // RulebasedAgent.get_move  rule_based.py:13-25.  *hit = index of the rule that fired
 // (rs.n = the legal_random fallback, stored by the host as entry [n]).
-template <class SH>
+template <class SH, bool EXT = false>
 __device__ __forceinline__ int rules_act(const Game<SH>& g, const RuleSet& rs,
                                          unsigned long long game_id, unsigned long long step,
                                          int* hit) {
@@ -319,7 +421,7 @@ __device__ __forceinline__ int rules_act(const Game<SH>& g, const RuleSet& rs,
 #pragma unroll 1
   for (int k = 0; k <= rs.n; ++k) {
     if (a < 0) {
-      const int r = run_rule(g, rs.id[k], rs.farg[k], rs.iarg[k], rs.seed, game_id, step);
+      const int r = run_rule<SH, EXT>(g, rs.id[k], rs.farg[k], rs.iarg[k], rs.seed, game_id, step);
       if (r >= 0) { a = r; h = k; }
     }
   }

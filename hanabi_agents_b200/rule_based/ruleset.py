@@ -44,17 +44,12 @@ class Ruleset:
     def play_probably_safe_factory(treshold=0.95, require_extra_lives=False):  # :617
         return Rule(9, "play_probably_safe", farg=treshold, iarg=int(bool(require_extra_lives)))
 
-    # Rules of the reference that index the observation dict-style and therefore raise on the
-    # pybind objects it is given (ruleset.py:522-535, 570-594, 638-649): not provided.
+    # The reference versions of the next three index the observation dict-style and raise TypeError
+    # on the pybind objects they are given (ruleset.py:522-535, 570-594, 638-649); these follow the
+    # semantics the code spells out.
+    tell_anyone_useless_card = Rule(14, "tell_anyone_useless_card")  # :522
+    tell_playable_card = Rule(15, "tell_playable_card")              # :570 (coin :584 = counter-based draw)
+
     @staticmethod
-    def _dead(name):
-        def rule(*_a, **_k):
-            raise NotImplementedError(
-                "%s crashes in the reference (dict-style access on HLE objects); no semantics "
-                "to mirror" % name)
-        return rule
-
-
-Ruleset.tell_anyone_useless_card = Ruleset._dead("tell_anyone_useless_card")
-Ruleset.tell_playable_card = Ruleset._dead("tell_playable_card")
-Ruleset.discard_probably_useless_factory = Ruleset._dead("discard_probably_useless_factory")
+    def discard_probably_useless_factory(treshold=0.75):             # :638
+        return Rule(16, "discard_probably_useless", farg=treshold)

@@ -146,7 +146,8 @@ class HanabiOracleEnv:
 R_DISCARD_OLDEST_FIRST, R_OSAWA_DISCARD, R_TELL_UNKNOWN, R_TELL_RANDOMLY, R_PLAY_SAFE_CARD, \
     R_PLAY_IF_CERTAIN, R_TELL_PLAYABLE_CARD_OUTER, R_TELL_DISPENSABLE, R_TELL_ANYONE_USEFUL_CARD, \
     R_PLAY_PROBABLY_SAFE, R_HAIL_MARY, R_LEGAL_RANDOM, R_DISCARD_RANDOMLY, \
-    R_TELL_MOST_INFORMATION = range(14)
+    R_TELL_MOST_INFORMATION, R_TELL_ANYONE_USELESS_CARD, R_TELL_PLAYABLE_CARD, \
+    R_DISCARD_PROBABLY_USELESS = range(17)
 
 # predefined_rules.py:3-39
 PRESETS = {

@@ -16,6 +16,10 @@
  *    (ruleset.py:291-307), an illegal move; the intended value (the real card's) is used.
  *  - osawa_discard :229-230 evaluates fireworks[card.color] for un-hinted cards; with
  *    kUnknownColor = -1 that is Python's negative index = the LAST colour's stack.  Kept.
+ *  - tell_anyone_useless_card :522-535, tell_playable_card :570-594 and
+ *    discard_probably_useless_factory :638-649 (+ get_probability_useless :127-170, useless_card
+ *    :35-42) index the observation dict-style and raise TypeError on the pybind objects; their
+ *    INTENDED behaviour is restated, the coin of tell_playable_card :584 is draw 4.
  */
 #include "hanabi_oracle.h"
 #include <string.h>
@@ -25,7 +29,8 @@ enum {
   RO_PLAY_SAFE_CARD = 4, RO_PLAY_IF_CERTAIN = 5, RO_TELL_PLAYABLE_CARD_OUTER = 6,
   RO_TELL_DISPENSABLE = 7, RO_TELL_ANYONE_USEFUL_CARD = 8, RO_PLAY_PROBABLY_SAFE = 9,
   RO_HAIL_MARY = 10, RO_LEGAL_RANDOM = 11, RO_DISCARD_RANDOMLY = 12, RO_TELL_MOST_INFORMATION = 13,
-  RO_NUM_RULES = 14
+  RO_TELL_ANYONE_USELESS_CARD = 14, RO_TELL_PLAYABLE_CARD = 15, RO_DISCARD_PROBABLY_USELESS = 16,
+  RO_NUM_RULES = 17
 };
 
 static const int kNumInDeckByRank[5] = {3, 2, 2, 2, 1}; /* ruleset.py:9 */
@@ -100,6 +105,43 @@ static int play_probably_safe(const view* v, double threshold, int require_extra
   for (int i = 1; i < n; ++i) if (p[i] > p[best]) best = i; /* np.argmax: first maximum */
   if (!require_extra_lives || v->s->life > 1)
     if (p[best] >= threshold) return mk(v, HO_PLAY, best, -1, -1, -1);
+  return -1;
+}
+
+/* useless_card  ruleset.py:35-42 */
+static int useless_card(const view* v, const int* maxfw, int c, int r) {
+  return r < v->s->fireworks[c] || r >= maxfw[c];
+}
+
+/* discard_probably_useless_factory  ruleset.py:638-649 with get_probability_useless :127-170
+ * (player_offset = 0), intended semantics */
+static int discard_probably_useless(const view* v, double threshold) {
+  const ho_game* g = v->g; const ho_state* s = v->s;
+  const int n = s->hand_n[v->me];
+  if (!(s->info < 8) || n == 0) return -1;
+  int maxfw[HO_MAXC];
+  max_fireworks(v, maxfw);
+  int visible[HO_MAXCARDS] = {0};
+  for (int k = 1; k < g->players; ++k)
+    for (int i = 0; i < s->hand_n[pl(v, k)]; ++i) visible[s->hand_card[pl(v, k)][i]]++;
+  for (int c = 0; c < g->bits_per_card; ++c) visible[c] += s->discard_count[c];
+  for (int c = 0; c < g->colors; ++c)
+    for (int r = 0; r < s->fireworks[c]; ++r) visible[c * g->ranks + r]++;
+  double p[HO_MAXH];
+  for (int i = 0; i < n; ++i) {
+    int total = 0, useless = 0;
+    for (int c = 0; c < g->colors; ++c)
+      for (int r = 0; r < g->ranks; ++r)
+        if ((s->color_plaus[v->me][i] >> c & 1) && (s->rank_plaus[v->me][i] >> r & 1)) {
+          const int k = g->card_count[c * g->ranks + r] - visible[c * g->ranks + r];
+          total += k;
+          if (useless_card(v, maxfw, c, r)) useless += k;
+        }
+    p[i] = (double)useless / (double)total; /* :151 */
+  }
+  int best = 0;
+  for (int i = 1; i < n; ++i) if (p[i] > p[best]) best = i; /* np.argmax :643 */
+  if (p[best] >= threshold) return mk(v, HO_DISCARD, best, -1, -1, -1);
   return -1;
 }
 
@@ -240,6 +282,41 @@ static int run_rule(const view* v, int rule, double farg, int iarg) {
       return mk(v, HO_DISCARD, ro_below(ro_rand(v->seed, v->game_id, v->step, 3), s->hand_n[me]),
                 -1, -1, -1);
     }
+
+    case RO_TELL_ANYONE_USELESS_CARD: { /* :522-535, intended */
+      if (!(s->info > 1)) return -1;
+      int maxfw[HO_MAXC];
+      max_fireworks(v, maxfw);
+      for (int k = 1; k < g->players; ++k) {
+        const int t = pl(v, k);
+        for (int i = 0; i < s->hand_n[t]; ++i) {
+          const int c = s->hand_card[t][i] / R, r = s->hand_card[t][i] % R;
+          if (useless_card(v, maxfw, c, r)) {
+            if (s->color_hint[t][i] < 0) return mk(v, HO_REVEAL_COLOR, -1, k, c, -1);
+            if (s->rank_hint[t][i] < 0) return mk(v, HO_REVEAL_RANK, -1, k, -1, r);
+          }
+        }
+      }
+      return -1;
+    }
+
+    case RO_TELL_PLAYABLE_CARD: { /* :570-594, intended; the coin :584 is draw 4 */
+      if (!(s->info > 0)) return -1;
+      for (int k = 1; k < g->players; ++k) {
+        const int t = pl(v, k);
+        for (int i = 0; i < s->hand_n[t]; ++i) {
+          const int c = s->hand_card[t][i] / R, r = s->hand_card[t][i] % R;
+          if (r == s->fireworks[c]) {
+            const int coin = ro_below(ro_rand(v->seed, v->game_id, v->step, 4), 2);
+            return coin == 0 ? mk(v, HO_REVEAL_RANK, -1, k, -1, r) : mk(v, HO_REVEAL_COLOR, -1, k, c, -1);
+          }
+        }
+      }
+      return -1;
+    }
+
+    case RO_DISCARD_PROBABLY_USELESS: /* :638-649 */
+      return discard_probably_useless(v, farg);
 
     case RO_TELL_MOST_INFORMATION: /* :539-562 always returns None (:562) */
     default:

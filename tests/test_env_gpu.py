@@ -123,6 +123,46 @@ def test_rule_agents_parity(preset, name, players):
     assert env.illegal_count() == 0
 
 
+@pytest.mark.parametrize("name,players", [("Hanabi-Full", 2), ("Hanabi-Full", 4)])
+def test_intended_rules_parity(name, players):
+    """tell_anyone_useless_card / tell_playable_card / discard_probably_useless (dead in the
+    reference, intended semantics here: SURVEY 8f row 4) against the C oracle, stepwise and fused."""
+    from hanabi_agents_b200.rule_based import RulebasedAgent, Ruleset
+    from oracle import hanabi as oh
+    rules = [Ruleset.play_safe_card, Ruleset.tell_playable_card, Ruleset.tell_anyone_useless_card,
+             Ruleset.discard_probably_useless_factory(0.4), Ruleset.osawa_discard, Ruleset.tell_randomly]
+    orules = [(oh.R_PLAY_SAFE_CARD, 0, 0), (oh.R_TELL_PLAYABLE_CARD, 0, 0), (oh.R_TELL_ANYONE_USELESS_CARD, 0, 0),
+              (oh.R_DISCARD_PROBABLY_USELESS, 0.4, 0), (oh.R_OSAWA_DISCARD, 0, 0), (oh.R_TELL_RANDOMLY, 0, 0)]
+    n = 384
+    env, ora = _pair(name, players, n, 999)
+    agent = RulebasedAgent(rules, seed=77)
+    env.reset(); ora.reset()
+    hist = np.zeros(len(orules) + 1, np.int64)
+    for step in range(200):
+        a = agent.explore(env.observations())
+        oa, ohit = ora.rules_act(orules, 77, step)
+        np.testing.assert_array_equal(a.cpu().numpy(), oa)
+        np.add.at(hist, ohit[ohit >= 0], 1)
+        obs, legal, rew, st = env.step(a)
+        ora.step(oa)
+        _check(env, ora, obs, legal, rew, st)
+    assert agent.histogram == hist.tolist()
+    assert min(hist[1:4]) > 0, hist             # each of the three fired
+    assert env.illegal_count() == 0
+    # the same rule list through the fused self-play kernel
+    env2, ora2 = _pair(name, players, n, 999)
+    agent2 = RulebasedAgent(rules, seed=77)
+    env2.reset(); ora2.reset()
+    T = 120
+    obs, legal, rew, st, act = env2.selfplay(agent2, T, obs="alloc", legal="alloc", reward="alloc",
+                                             step_type="alloc", action="alloc")
+    for t in range(T):
+        oa, _ = ora2.rules_act(orules, 77, t)
+        ora2.step(oa)
+        np.testing.assert_array_equal(act[t].cpu().numpy(), oa)
+    _check(env2, ora2, obs[T - 1], legal[T - 1], rew[T - 1], st[T - 1])
+
+
 def test_fused_selfplay_equals_stepwise():
     n, T = 300, 150
     env, ora = _pair("Hanabi-Full", 2, n, 1000)

@@ -245,3 +245,144 @@ def test_illegal_action_is_counted_and_ignored():
     np.testing.assert_array_equal(e.dump(), before)
     e.step([99])
     assert e.illegal == 1
+
+
+# ---- the three rules that crash in the reference (dict-style access on pybind objects), restated
+# ---- with their intended semantics: the C oracle against a literal Python reading of ruleset.py
+def _py_rule_view(dump_row, players, colors, ranks, hand_size):
+    """Unpacks one ho_env_dump row into the dict-style observation those rules index."""
+    d = list(dump_row)
+    cur, info = d[0], d[1]
+    k = 8
+    fireworks = d[k:k + colors]; k += colors
+    hand_n = d[k:k + players]; k += players
+    hands = []
+    for p in range(players):
+        cards = []
+        for h in range(hand_size):
+            card, cp, rp, ch, rh = d[k:k + 5]; k += 5
+            if h < hand_n[p]:
+                cards.append(dict(color=card // ranks, rank=card % ranks, cp=cp, rp=rp, ch=ch, rh=rh))
+        hands.append(cards)
+    discards = d[k:k + colors * ranks]
+    # observed_hands[offset]: offset 0 = me
+    observed = [hands[(cur + o) % players] for o in range(players)]
+    return dict(info=info, fireworks=fireworks, observed=observed, discards=discards,
+                colors=colors, ranks=ranks, hand_size=hand_size, players=players)
+
+
+_NUM_IN_DECK = [3, 2, 2, 2, 1]          # ruleset.py:9
+
+
+def _py_max_fireworks(v):               # ruleset.py:174-193
+    out = [5] * v["colors"]
+    for c in range(v["colors"]):
+        for r in range(v["ranks"]):
+            n = v["discards"][c * v["ranks"] + r]
+            if n > 0 and n >= _NUM_IN_DECK[r] and out[c] >= r:
+                out[c] = r
+    return out
+
+
+def _py_useless(card_c, card_r, fireworks, maxfw):   # ruleset.py:35-42
+    return card_r < fireworks[card_c] or card_r >= maxfw[card_c]
+
+
+def _uid(v, kind, a, b=None):
+    H, C, R, P = v["hand_size"], v["colors"], v["ranks"], v["players"]
+    if kind == "discard":
+        return a
+    if kind == "color":                 # (target offset, colour)
+        return 2 * H + (a - 1) * C + b
+    return 2 * H + (P - 1) * C + (a - 1) * R + b
+
+
+def _py_tell_anyone_useless_card(v):    # ruleset.py:522-535
+    if v["info"] > 1:
+        maxfw = _py_max_fireworks(v)
+        for off in range(1, v["players"]):
+            for card in v["observed"][off]:
+                if _py_useless(card["color"], card["rank"], v["fireworks"], maxfw):
+                    if card["ch"] < 0:
+                        return _uid(v, "color", off, card["color"])
+                    if card["rh"] < 0:
+                        return _uid(v, "rank", off, card["rank"])
+    return None
+
+
+def _py_tell_playable_card(v):          # ruleset.py:570-594: the two moves the coin chooses between
+    if v["info"] > 0:
+        for off in range(1, v["players"]):
+            for card in v["observed"][off]:
+                if card["rank"] == v["fireworks"][card["color"]]:
+                    return (_uid(v, "rank", off, card["rank"]), _uid(v, "color", off, card["color"]))
+    return None
+
+
+def _py_discard_probably_useless(v, threshold):   # ruleset.py:638-649 + :127-170
+    if not v["info"] < 8:
+        return None
+    C, R = v["colors"], v["ranks"]
+    visible = list(v["discards"])
+    for off in range(1, v["players"]):
+        for card in v["observed"][off]:
+            visible[card["color"] * R + card["rank"]] += 1
+    for c in range(C):
+        for r in range(v["fireworks"][c]):
+            visible[c * R + r] += 1
+    maxfw = _py_max_fireworks(v)
+    probs = []
+    for card in v["observed"][0]:
+        total = useless = 0
+        for c in range(C):
+            for r in range(R):
+                if (card["cp"] >> c) & 1 and (card["rp"] >> r) & 1:
+                    n = _NUM_IN_DECK[r] - visible[c * R + r]
+                    total += n
+                    if _py_useless(c, r, v["fireworks"], maxfw):
+                        useless += n
+        probs.append(useless / total)
+    if not probs:
+        return None
+    idx = int(np.argmax(probs))
+    return _uid(v, "discard", idx) if probs[idx] >= threshold else None
+
+
+@pytest.mark.parametrize("name,players", [("Hanabi-Full", 2), ("Hanabi-Full", 4), ("Hanabi-Small", 2)])
+def test_intended_semantics_of_the_dead_rules(name, players):
+    from oracle.hanabi import (R_DISCARD_PROBABLY_USELESS, R_TELL_ANYONE_USELESS_CARD, R_TELL_PLAYABLE_CARD,
+                               PRESETS)
+    p = game_params(name, players)
+    n = 96
+    env = HanabiOracleEnv(n, **p)
+    env.set_decks(make_decks(p["colors"], p["ranks"], 4 * n, 21))
+    env.reset()
+    fired = [0, 0, 0]
+    for step in range(150):
+        dump = env.dump()
+        views = [_py_rule_view(dump[g], players, p["colors"], p["ranks"], p["hand_size"]) for g in range(n)]
+        live = env.step_type != 2
+        for j, (rid, farg, py) in enumerate((
+                (R_TELL_ANYONE_USELESS_CARD, 0.0, _py_tell_anyone_useless_card),
+                (R_TELL_PLAYABLE_CARD, 0.0, _py_tell_playable_card),
+                (R_DISCARD_PROBABLY_USELESS, 0.4, lambda v: _py_discard_probably_useless(v, 0.4)))):
+            act, hit = env.rules_act([(rid, farg, 0)], 5, step)
+            for g in np.flatnonzero(live):
+                want = py(views[g])
+                if want is None:
+                    assert hit[g] == 1, (name, step, g, j)          # fell through to legal_random
+                else:
+                    assert hit[g] == 0
+                    fired[j] += 1
+                    if isinstance(want, tuple):
+                        assert act[g] in want
+                    else:
+                        assert act[g] == want
+        # play on so that fireworks / discards / hints all develop (piers hard-codes 8 information
+        # tokens like the reference's rules, ruleset.py:207,221: on Hanabi-Small use random legal moves)
+        from oracle.hanabi import R_LEGAL_RANDOM
+        driver = PRESETS["piers"] if p["max_info"] == 8 else [(R_LEGAL_RANDOM, 0, 0)]
+        a, _ = env.rules_act(driver, 5, step)
+        env.step(a)
+        assert env.illegal == 0
+    assert all(f > 20 for f in fired), fired

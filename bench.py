@@ -469,20 +469,22 @@ def run_ours(args):
     # each step, observation / legal / reward / step type are read back to the host each step.
     e_steps = min(args.steps, args.e2e_steps)
     a_host = torch.zeros(n, dtype=torch.int32).pin_memory()
-    o_host = torch.empty((n, env.obs_stride), dtype=torch.int32).pin_memory()
-    l_host = torch.empty((n, env.legal_words), dtype=torch.int32).pin_memory()
-    r_host = torch.empty(n, dtype=torch.float32).pin_memory()
-    s_host = torch.empty(n, dtype=torch.uint8).pin_memory()
+    blob_host = torch.empty(env.outputs_blob.numel(), dtype=torch.uint8).pin_memory()
+    o_host, l_host, r_host, s_host = env.split_outputs(blob_host)
+    side = torch.cuda.Stream()
+    stepped = torch.cuda.Event()
 
     def e2e_step():
+        main = torch.cuda.current_stream()
         a_dev = a_host.to(dev, non_blocking=True)                 # H2D: this step's actions
-        o, l, r, s = env.step(a_dev)
-        o_host.copy_(o, non_blocking=True)                        # D2H: observation + mask + ...
-        l_host.copy_(l, non_blocking=True)
-        r_host.copy_(r, non_blocking=True)
-        s_host.copy_(s, non_blocking=True)
-        a_host.copy_(agent.explore(env), non_blocking=True)       # next actions back to the host
-        torch.cuda.current_stream().synchronize()
+        env.step(a_dev)
+        stepped.record(main)
+        blob_host.copy_(env.outputs_blob, non_blocking=True)      # D2H: observation + mask + reward + type
+        with torch.cuda.stream(side):                             # meanwhile: the agent's next move ...
+            side.wait_event(stepped)
+            a_host.copy_(agent.explore(env), non_blocking=True)   # ... and its way back to the host
+        main.synchronize()
+        side.synchronize()
 
     a_host.copy_(agent.explore(env))
     for _ in range(3):
@@ -498,7 +500,7 @@ def run_ours(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_val = world * n * e_steps / float(te.item())
     h2d = 4 * n
-    d2h = n * (env.obs_stride * 4 + env.legal_words * 4 + 4 + 1 + 4)
+    d2h = env.outputs_blob.numel() + 4 * n
 
     learner = acting = None
     if not args.no_learner:
@@ -554,8 +556,8 @@ def run_ours(args):
                    "decks": "numpy default_rng(%d) permutations, pool of %d" % (SEED, 4 * n)},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e_steps, "path": "env.step (1 launch) + agent.explore (1 launch) per step, "
-                "pinned host buffers"},
+                "steps": e_steps, "path": "per step: actions H2D from pinned memory, env.step (1 launch), one D2H of the "
+                "step outputs, agent.explore (1 launch, beside the copy) and its actions D2H; host in the loop"},
         "gpu_launches": launches,
         "roofline": roof,
         "cpu_baseline": cpu,

@@ -60,14 +60,32 @@ class HanabiParallelEnv:
         if n_total is not None or game_id_base:
             _lib.check(L.hb_env_set_shard(self._h, int(game_id_base), int(n_total or self.n)))
         self.game_id_base, self.n_total = int(game_id_base), int(n_total or self.n)
-        z = lambda shape, dt: torch.zeros(shape, dtype=dt, device=self.device)  # noqa: E731
-        self.obs_packed = z((self.n, self.obs_stride), torch.int32)
-        self.legal_packed = z((self.n, self.legal_words), torch.int32)
-        self.reward = z((self.n,), torch.float32)
-        self.step_type = z((self.n,), torch.uint8)
+        # the step outputs are views of ONE device allocation (`outputs_blob`), so that a host-side
+        # consumer fetches a whole step with a single copy; `split_outputs` carves the same views
+        # out of a host copy of the blob
+        def up(x):
+            return (x + 255) // 256 * 256
+        sizes = [self.n * self.obs_stride * 4, self.n * self.legal_words * 4, self.n * 4, self.n]
+        self._blob_off = [0]
+        for b in sizes:
+            self._blob_off.append(self._blob_off[-1] + up(b))
+        self.outputs_blob = torch.zeros(self._blob_off[-1], dtype=torch.uint8, device=self.device)
+        self.obs_packed, self.legal_packed, self.reward, self.step_type = self.split_outputs(self.outputs_blob)
         if decks is None:
             decks = make_decks(params["colors"], params["ranks"], n_decks or 4 * self.n_total, seed)
         self.set_decks(decks)
+
+    def split_outputs(self, blob):
+        """(obs_packed, legal_packed, reward, step_type) views of a uint8 blob laid out like
+        `outputs_blob` (device or pinned host)."""
+        torch = self.torch
+        o = self._blob_off
+        n = self.n
+        obs = blob[o[0]:o[0] + n * self.obs_stride * 4].view(torch.int32).view(n, self.obs_stride)
+        legal = blob[o[1]:o[1] + n * self.legal_words * 4].view(torch.int32).view(n, self.legal_words)
+        reward = blob[o[2]:o[2] + n * 4].view(torch.float32)
+        step_type = blob[o[3]:o[3] + n]
+        return obs, legal, reward, step_type
 
     def __del__(self):
         h = getattr(self, "_h", None)

@@ -101,6 +101,9 @@ SIGNATURES = {
     "hb_learner_destroy": (i32, [vp]),
     "hb_learner_set_graph": (i32, [vp, i32]),
     "hb_learner_info": (i64, [vp, i32]),
+    "hb_rb_set_insert_priority": (i32, [vp, f32]),
+    "hb_net_grads_rainbow": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, vp, vp, vp]),
+    "hb_net_adam_tf": (i32, [vp, f32, f32, f32, f32, f32, vp]),
     "hb_learner_loss": (vp, [vp]),
     "hb_learner_mean_loss": (vp, [vp]),
     "hb_learner_indices": (vp, [vp]),

@@ -77,6 +77,7 @@ struct hb_qnet {
   __half* dzt[kMaxLayers] = {nullptr}; // transposed [N, Bp]
   float* logits = nullptr;             // online head [2B, N_last]
   float* q_on = nullptr;               // [2B, ldq]
+  float* q_tg = nullptr;               // [B, ldq] target-network q at obs_t (TF-Rainbow variant)
   float* tlogits = nullptr;            // target head [B, N_last]
   float* w_is = nullptr;               // [B]
   float* loss_b = nullptr;             // [B] per-sample loss / td
@@ -237,7 +238,8 @@ __global__ void is_weights_kernel(const float* __restrict__ prios, int B, float 
 //   m = categorical_l2_project(target_z, p, z);  loss = -sum_i m_i log_softmax(logits_tm1[a])_i
 // Writes loss_b and dL/dlogits * B / w-normalisation folded later:  dz[b, a*64+i] = w_b (p_i S - m_i).
 __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const float* __restrict__ q_sel,
-                                int ldq, const float* __restrict__ tlogits, int ldl,
+                                int ldq, const uint32_t* __restrict__ legal_t, int legal_words,
+                                const float* __restrict__ tlogits, int ldl,
                                 const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
                                 const uint8_t* __restrict__ term_t, int mask_terminal,
                                 const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
@@ -251,7 +253,9 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
   float best = -INFINITY;
   int besta = 0x7fffffff;
   for (int a = lane; a < A; a += 32) {
-    const float v = q_sel[(long long)b * ldq + a];
+    float v = q_sel[(long long)b * ldq + a];
+    // TF-Rainbow: argmax(next_qt + next_legal_actions), illegal = -inf  (rainbow_agent.py:203-204)
+    if (legal_t != nullptr && !((legal_t[(long long)b * legal_words + (a >> 5)] >> (a & 31)) & 1u)) v = -INFINITY;
     if (v > best) { best = v; besta = a; }
   }
   for (int o = 16; o; o >>= 1) {
@@ -381,7 +385,7 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds
                                     float* __restrict__ av, const float* __restrict__ grad,
                                     float grad_scale, int do_update, float lr, float b1, float b2,
                                     float eps, const int* __restrict__ step_ptr, __half* __restrict__ w16,
-                                    __half* __restrict__ /*w16t*/, float* __restrict__ beff) {
+                                    __half* __restrict__ /*w16t*/, float* __restrict__ beff, int tf_style) {
   // bias corrections from the device-side step counter (so that the launch can sit in a CUDA graph)
   float bc1 = 1.f, bc2 = 1.f;
   if (do_update) {
@@ -424,8 +428,14 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds
           const float gr = gr4[j] * grad_scale * (k == 2 ? noise[j] : 1.0f);
           m[j] = b1 * m[j] + (1.0f - b1) * gr;
           v[j] = b2 * v[j] + (1.0f - b2) * gr * gr;
-          const float mhat = m[j] / bc1, vhat = v[j] / bc2;
-          p[j] = p[j] - lr * mhat / (sqrtf(vhat) + eps);
+          if (tf_style) {
+            // tf.train.AdamOptimizer (rainbow_agent.py:228-230): lr_t = lr sqrt(1-b2^t)/(1-b1^t),
+            // theta -= lr_t m / (sqrt(v) + eps) -- eps is NOT bias corrected
+            p[j] = p[j] - (lr * sqrtf(bc2) / bc1) * m[j] / (sqrtf(v[j]) + eps);
+          } else {
+            const float mhat = m[j] / bc1, vhat = v[j] / bc2;
+            p[j] = p[j] - lr * mhat / (sqrtf(vhat) + eps);
+          }
         }
         *reinterpret_cast<float4*>(am + k * n_eff + i) = make_float4(m[0], m[1], m[2], m[3]);
         *reinterpret_cast<float4*>(av + k * n_eff + i) = make_float4(v[0], v[1], v[2], v[3]);
@@ -498,7 +508,8 @@ void free_learner_ws(hb_qnet* q) {
   for (int l = 0; l < kMaxLayers; ++l) {
     dev_free(q->h[l]); dev_free(q->ht[l]); dev_free(q->th[l]); dev_free(q->dz[l]); dev_free(q->dzt[l]);
   }
-  dev_free(q->logits); dev_free(q->q_on); dev_free(q->tlogits); dev_free(q->w_is); dev_free(q->loss_b);
+  dev_free(q->logits); dev_free(q->q_on); dev_free(q->q_tg); dev_free(q->tlogits); dev_free(q->w_is);
+  dev_free(q->loss_b);
   q->lb = q->lbp = 0;
 }
 
@@ -533,6 +544,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
   if ((rc = dev_alloc(&q->logits, (size_t)2 * B * NL))) return rc;
   if ((rc = dev_alloc(&q->q_on, (size_t)2 * B * NL))) return rc;
   if ((rc = dev_alloc(&q->tlogits, (size_t)B * NL))) return rc;
+  if ((rc = dev_alloc(&q->q_tg, (size_t)B * NL))) return rc;
   if ((rc = dev_alloc(&q->w_is, (size_t)B))) return rc;
   if ((rc = dev_alloc(&q->loss_b, (size_t)B))) return rc;
   q->lb = B;
@@ -614,7 +626,7 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
 }
 
 int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
-             cudaStream_t s) {
+             cudaStream_t s, int tf_style = 0) {
   int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
   if (do_update) {
     net->adam_step += 1;                       // host mirror (hb_net_info); the kernels use the device copy
@@ -626,11 +638,11 @@ int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float ep
   if (net->kinds == 3)
     adam_refresh_kernel<3><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 3, net->master, net->eps,
                                                   net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
+                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   else
     adam_refresh_kernel<1><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 1, net->master, net->eps,
                                                   net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff);
+                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   HB_CUDA(cudaGetLastError());
   int tiles = 0;
   for (int l = 0; l < net->n_layers; ++l)
@@ -916,10 +928,38 @@ int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int l
  * d_weights: importance weights given directly (rlax_dqn.py:144 signature); exactly one is non-NULL
  * (both NULL = all ones).  mask_terminal: gamma*(1-terminal) as rainbow_agent.py:191-197 (C51 only;
  * the rlax C51 learner ignores term_t).  Observations are bit-packed rows. */
+static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                          const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                          const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                          float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
+                          const uint32_t* d_legal_t);
+
 int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,
                  float* d_loss_out, float* d_mean_loss, void* stream) {
+  return net_grads_impl(q, d_obs_tm1, d_a_tm1, d_r_t, d_obs_t, d_term_t, d_prios, d_weights, B, beta, discount,
+                        mask_terminal, d_loss_out, d_mean_loss, stream, 0, nullptr);
+}
+
+/* TF-Rainbow target (rainbow/rainbow_agent.py:183-236): the greedy next action comes from the TARGET
+ * network's q = sum(p z) over the LEGAL next moves, gamma is masked by the terminal flag, importance
+ * weights are given (1/sqrt(priority), normalised by the caller's max).  Same kernels otherwise. */
+int hb_net_grads_rainbow(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                         const uint32_t* d_obs_t, const uint32_t* d_legal_t, const uint8_t* d_term_t,
+                         const float* d_weights, int B, float cumulative_gamma, float* d_loss_out,
+                         float* d_mean_loss, void* stream) {
+  HB_REQUIRE(q && q->n_atoms > 1 && d_legal_t && d_term_t, "hb_net_grads_rainbow: categorical net, legal moves "
+             "and terminals are required");
+  return net_grads_impl(q, d_obs_tm1, d_a_tm1, d_r_t, d_obs_t, d_term_t, nullptr, d_weights, B, 0.f,
+                        cumulative_gamma, 1, d_loss_out, d_mean_loss, stream, 1, d_legal_t);
+}
+
+static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                          const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                          const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                          float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
+                          const uint32_t* d_legal_t) {
   HB_REQUIRE(q && d_obs_tm1 && d_a_tm1 && d_r_t && d_obs_t && B >= 1, "hb_net_grads: bad arguments");
   HB_REQUIRE(!(d_prios && d_weights), "hb_net_grads: give prios or weights, not both");
   hb::DeviceGuard g(q->device);
@@ -941,7 +981,7 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
   HB_CUDA(cudaEventRecord(q->ev_fork, s));
   HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_fork, 0));
   if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
-                    q->n_atoms > 1 ? nullptr : q->tlogits, ldq, q->side,
+                    q->n_atoms > 1 ? (tf_variant ? q->q_tg : nullptr) : q->tlogits, ldq, q->side,
                     fused ? q->xb + (size_t)B * row_words : nullptr))) return rc;
   {
     const long long tot = (long long)K0 * ((B + 7) / 8);
@@ -967,7 +1007,8 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
   // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
   if (q->n_atoms > 1) {
-    c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, q->q_on + (size_t)B * ldq, ldq, q->tlogits,
+    c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, tf_variant ? q->q_tg : q->q_on + (size_t)B * ldq, ldq,
+                                               tf_variant ? d_legal_t : nullptr, (q->A + 31) / 32, q->tlogits,
                                                LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, q->w_is,
                                                B, q->A, q->n_atoms, q->vmax, discount, q->dz[nl - 1],
                                                q->dzt[nl - 1], Bp, q->loss_b);
@@ -1019,6 +1060,12 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
 
 /* optix.adam update of every master tensor from the flat gradient bucket (after the optional
  * all-reduce; grad_scale = 1/world_size) and refresh of the fp16 effective weights. */
+int hb_net_adam_tf(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream) {
+  HB_REQUIRE(q, "hb_net_adam_tf: NULL net");
+  hb::DeviceGuard g(q->device);
+  return run_adam(q, 1, lr, b1, b2, eps, grad_scale, (cudaStream_t)stream, 1);
+}
+
 int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream) {
   HB_REQUIRE(q, "hb_net_adam: NULL net");
   hb::DeviceGuard g(q->device);

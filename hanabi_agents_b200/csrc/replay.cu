@@ -28,7 +28,8 @@ struct hb_replay {
   float* rew = nullptr;
   uint8_t* term = nullptr;
   hb_sumtree* tree = nullptr;
-  float* prio_range = nullptr;        // device: [0] max_priority, [1] min_priority
+  float* prio_range = nullptr;        // device: [0] max_priority, [1] min_priority, [2] fixed insert priority
+  bool fixed_insert = false;          // new rows take prio_range[2] instead of the running max
   // scratch for the masked append
   int64_t scan_n = 0;
   int32_t* block_sum = nullptr;       // per 1024-row block
@@ -302,9 +303,10 @@ void advance(hb_replay* rb, int64_t n) {
 int insert_priorities(hb_replay* rb, int64_t n, cudaStream_t s) {
   if (!rb->prioritized || n == 0) return HB_OK;
   const int64_t first = rb->oldest + n <= rb->cap ? n : rb->cap - rb->oldest;
-  int rc = hb_st_update_range_dev(rb->tree, rb->oldest, first, rb->prio_range, s);
+  const float* fill = rb->fixed_insert ? rb->prio_range + 2 : rb->prio_range;
+  int rc = hb_st_update_range_dev(rb->tree, rb->oldest, first, fill, s);
   if (rc) return rc;
-  if (first < n) rc = hb_st_update_range_dev(rb->tree, 0, n - first, rb->prio_range, s);
+  if (first < n) rc = hb_st_update_range_dev(rb->tree, 0, n - first, fill, s);
   return rc;
 }
 
@@ -343,7 +345,7 @@ int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capac
   if (e == cudaSuccess) e = cudaMalloc(&rb->term, c);
   if (e == cudaSuccess) e = cudaMalloc(&rb->total, 4);
   if (e == cudaSuccess) e = cudaMallocHost(&rb->h_total, 4);
-  if (e == cudaSuccess) e = cudaMalloc(&rb->prio_range, 8);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->prio_range, 12);
   if (e == cudaSuccess) {
     // np.empty in the reference; zero here so that unwritten rows are defined
     cudaMemset(rb->obs_tm1, 0, c * rb->stride * 4);
@@ -521,6 +523,14 @@ int hb_rb_update_priorities(hb_replay* rb, const int64_t* d_idx, const float* d_
   priorities_kernel<<<1, 256, 0, s>>>(d_td_abs, n, rb->alpha, rb->vals, rb->prio_range);
   HB_CUDA(cudaGetLastError());
   return hb_st_update(rb->tree, d_idx, rb->vals, n, s);
+}
+
+int hb_rb_set_insert_priority(hb_replay* rb, float value) {
+  HB_REQUIRE(rb && rb->prioritized, "hb_rb_set_insert_priority: not a prioritized buffer");
+  hb::DeviceGuard g(rb->device);
+  rb->fixed_insert = value > 0.f;
+  if (rb->fixed_insert) HB_CUDA(cudaMemcpy(rb->prio_range + 2, &value, 4, cudaMemcpyHostToDevice));
+  return HB_OK;
 }
 
 int hb_rb_priority_range(hb_replay* rb, float* h_max, float* h_min, void* stream) {

@@ -211,6 +211,10 @@ int hb_rb_sample(hb_replay* rb, const float* d_keys, int64_t n, int64_t* d_idx, 
 int hb_rb_update_priorities(hb_replay* rb, const int64_t* d_idx, const float* d_td_abs, int64_t n,
                             void* stream);
 int hb_rb_priority_range(hb_replay* rb, float* h_max, float* h_min, void* stream);
+/* Priority of newly inserted rows: value > 0 = that constant (DEFAULT_PRIORITY = 100 of
+ * rainbow/prioritized_replay_memory.py:38,95-103); value <= 0 = the running max_priority
+ * (priority_buffer.py:29-31, the default). */
+int hb_rb_set_insert_priority(hb_replay* rb, float value);
 /* One int8 per bit <-> bit-packed rows (the reference stores np.byte rows, experience_buffer.py:9-12). */
 int hb_pack_bits(const int8_t* d_in, int bits, uint32_t* d_out, int stride_words, int64_t n, void* stream);
 int hb_unpack_bits(const uint32_t* d_packed, int stride_words, int bits, int8_t* d_out, int64_t n,
@@ -279,6 +283,17 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,
                  float* d_loss_out, float* d_mean_loss, void* stream);
+/* The same with the TF-Rainbow target of rainbow/rainbow_agent.py:183-236 (the `rainbow/` package's
+ * learner): next action = argmax over the LEGAL next moves (d_legal_t, packed) of the
+ * TARGET network's q; gamma^n masked by d_term_t (:191-197); d_weights = the caller's importance weights
+ * (1/sqrt(priority + 1e-10) / max, :237-240).  Categorical networks only. */
+int hb_net_grads_rainbow(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                         const uint32_t* d_obs_t, const uint32_t* d_legal_t, const uint8_t* d_term_t,
+                         const float* d_weights, int B, float cumulative_gamma, float* d_loss_out,
+                         float* d_mean_loss, void* stream);
+/* tf.train.AdamOptimizer(learning_rate, epsilon) (rainbow_agent.py:228-230): lr_t = lr sqrt(1-b2^t)/(1-b1^t),
+ * theta -= lr_t m / (sqrt(v) + eps). */
+int hb_net_adam_tf(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 /* optix.adam(lr, b1, b2, eps) on every master tensor (rlax_rainbow.py:215-216,257) from
  * grad_scale * bucket, then refresh of the effective weights. */
 int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream);

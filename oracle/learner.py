@@ -168,8 +168,10 @@ class OracleQNet:
 
     # -- learner --------------------------------------------------------------------------
     def loss(self, obs_tm1, a_tm1, r_t, obs_t, term_t, prios=None, weights=None, beta=0.4,
-             discount=0.99, mask_terminal=False):
-        """Returns (mean_loss, per_sample) with the autograd graph attached to self.params."""
+             discount=0.99, mask_terminal=False, tf_variant=False, legal_t=None):
+        """Returns (mean_loss, per_sample) with the autograd graph attached to self.params.
+        tf_variant: the target of rainbow/rainbow_agent.py:183-210 -- the next action is the argmax of the
+        TARGET network's q = sum(p z) over the legal next moves (`legal_t` 0/1), gamma masked by term_t."""
         eff = self.effective()
         B = obs_tm1.shape[0]
         if prios is not None:
@@ -183,7 +185,12 @@ class OracleQNet:
             logits_tm1 = self.apply(eff, obs_tm1)
             with torch.no_grad():
                 logits_t = self.apply(self.target, obs_t)
-                q_sel = self.q_values(self.apply(eff, obs_t))
+                if tf_variant:
+                    q_sel = torch.sum(torch.softmax(logits_t, -1) * self.atoms, -1)      # :199-201
+                    q_sel = torch.where(legal_t.bool(), q_sel, torch.full_like(q_sel, -float("inf")))
+                    mask_terminal = True
+                else:
+                    q_sel = self.q_values(self.apply(eff, obs_t))
             losses = []
             for b in range(B):
                 a_star = int(torch.argmax(q_sel[b]))
@@ -217,6 +224,17 @@ class OracleQNet:
             for v in l.values():
                 v.requires_grad_(False)
         return float(mean_loss.detach()), per.detach(), g
+
+    def adam_tf(self, grads, lr=2.5e-5, b1=0.9, b2=0.999, eps=3.125e-5):
+        """tf.train.AdamOptimizer: lr_t = lr sqrt(1 - b2^t) / (1 - b1^t); theta -= lr_t m / (sqrt(v) + eps)."""
+        self.t += 1
+        lr_t = lr * (1 - b2 ** self.t) ** 0.5 / (1 - b1 ** self.t)
+        with torch.no_grad():
+            for p, g, m, v in zip(self.params, grads, self.m, self.v):
+                for k in p:
+                    m[k] = b1 * m[k] + (1 - b1) * g[k]
+                    v[k] = b2 * v[k] + (1 - b2) * g[k] * g[k]
+                    p[k] -= lr_t * m[k] / (torch.sqrt(v[k]) + eps)
 
     def adam(self, grads, lr=1e-3, b1=0.9, b2=0.999, eps=3.125e-5):
         """optix.adam: scale_by_adam (bias-corrected) then scale(-lr)."""

@@ -348,6 +348,22 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
   rs.id[n] = R_LEGAL_RANDOM;   // Ruleset.legal_random fallback (rule_based.py:24)
   rs.farg[n] = 0.0;
   rs.iarg[n] = 0;
+  // comparison tables of the threshold rules: the reference's float64 division, done here once
+  int slots = 0;
+  for (int k = 0; k <= n; ++k) {
+    rs.tslot[k] = -1;
+    const bool thr_rule = rs.id[k] == R_PLAY_PROBABLY_SAFE || rs.id[k] == R_DISCARD_PROBABLY_USELESS;
+    if (!thr_rule || slots >= kThrSlots) continue;
+    for (int t = 0; t < kThrRows; ++t) {
+      unsigned long long m = 0;
+      for (int p = 0; p < 64 && t > 0; ++p) {
+        volatile double q = (double)p / (double)t;    // rounded to double, no extended precision
+        if (q >= rs.farg[k]) m |= 1ull << p;
+      }
+      rs.thr[slots][t] = m;
+    }
+    rs.tslot[k] = slots++;
+  }
   return HB_OK;
 }
 

@@ -28,13 +28,29 @@ enum RuleId {
 };
 
 constexpr int kMaxRules = 16;
+constexpr int kThrSlots = 4;      // rules with a probability threshold that get a comparison table
+constexpr int kThrRows = 52;      // denominators 0..51 (a deck holds 50 cards)
 struct RuleSet {        // entry [n] is the legal_random fallback, filled by the host
   int n;
   int id[kMaxRules + 1];
   int iarg[kMaxRules + 1];
   double farg[kMaxRules + 1];
   unsigned long long seed;
+  // `(double)p / (double)t >= farg` (ruleset.py:105,622 / :151,644) for every count pair, evaluated
+  // once on the host in IEEE double: bit p of thr[slot][t].  The float64 division itself was a
+  // ~100-instruction subroutine, called twice per game step: 22 % of all warp instructions of the
+  // fused self-play kernel (profiles/r01_selfplay_history.md, v4).
+  int tslot[kMaxRules + 1];       // -1: divide
+  unsigned long long thr[kThrSlots][kThrRows];
 };
+
+// numerator / denominator >= threshold, exactly as the reference's float64 division decides it
+__device__ __forceinline__ bool ratio_at_least(const RuleSet& rs, int slot, int num, int den,
+                                               double threshold) {
+  if (threshold <= 0.0) return true;                       // num >= 0, den > 0
+  if (slot >= 0 && den < kThrRows && num < 64) return (rs.thr[slot][den] >> num) & 1ull;
+  return (double)num / (double)den >= threshold;
+}
 
 __device__ __forceinline__ uint32_t rule_rand(unsigned long long seed, unsigned long long game,
                                               unsigned long long step, uint32_t k) {
@@ -125,7 +141,7 @@ __device__ __forceinline__ int sum_fields(unsigned long long x, unsigned long lo
 // reference's float64 division.
 template <class SH>
 __device__ __forceinline__ int play_probably_safe(const Game<SH>& g, double threshold,
-                                                  bool require_extra_lives) {
+                                                  bool require_extra_lives, const RuleSet& rs, int slot) {
   const int n = g.hand_n(0);
   if (n == 0) return -1;
   // visible copies per card type: other hands + discards + fireworks  (:60-76)
@@ -152,7 +168,7 @@ __device__ __forceinline__ int play_probably_safe(const Game<SH>& g, double thre
     }
   }
   if (!require_extra_lives || g.life > 1)
-    if ((double)bp / (double)bt >= threshold) return uid_play<SH>(best);   // :105, :622
+    if (ratio_at_least(rs, slot, bp, bt, threshold)) return uid_play<SH>(best);   // :105, :622
   return -1;
 }
 
@@ -171,7 +187,8 @@ __device__ __forceinline__ uint32_t useless_grid(const Game<SH>& g) {
 // discard_probably_useless_factory  ruleset.py:638-649 with get_probability_useless :127-170
 // (intended semantics): same bookkeeping as play_probably_safe with the useless grid.
 template <class SH>
-__device__ __forceinline__ int discard_probably_useless(const Game<SH>& g, double threshold) {
+__device__ __forceinline__ int discard_probably_useless(const Game<SH>& g, double threshold,
+                                                        const RuleSet& rs, int slot) {
   const int n = g.hand_n(0);
   if (!(g.info < 8) || n == 0) return -1;
   unsigned long long vis = g.disc;
@@ -195,7 +212,7 @@ __device__ __forceinline__ int discard_probably_useless(const Game<SH>& g, doubl
       if (i == 0 || useless * bt > bu * total) { bu = useless; bt = total; best = i; }
     }
   }
-  if ((double)bu / (double)bt >= threshold) return uid_discard<SH>(best);
+  if (ratio_at_least(rs, slot, bu, bt, threshold)) return uid_discard<SH>(best);
   return -1;
 }
 
@@ -223,8 +240,8 @@ __device__ __forceinline__ int tell_playable_outer(const Game<SH>& g) {
 // the same switch the fused self-play kernel of the headline benchmark lost 11 % (register
 // allocation of the hot cases), although a piers agent never executes them.
 template <class SH>
-__device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double farg,
-                                         unsigned long long seed, unsigned long long game_id,
+__device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double farg, const RuleSet& rs,
+                                         int slot, unsigned long long seed, unsigned long long game_id,
                                          unsigned long long step) {
   constexpr int H = SH::H, P = SH::P;
   switch (rule) {
@@ -263,7 +280,7 @@ __device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double far
     }
 
     case R_DISCARD_PROBABLY_USELESS:                   // :638-649
-      return discard_probably_useless(g, farg);
+      return discard_probably_useless(g, farg, rs, slot);
 
     default:
       return -1;
@@ -271,12 +288,14 @@ __device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double far
 }
 
 template <class SH, bool EXT = false>
-__device__ __forceinline__ int run_rule(const Game<SH>& g, int rule, double farg, int iarg,
-                                        unsigned long long seed, unsigned long long game_id,
-                                        unsigned long long step) {
+__device__ __forceinline__ int run_rule(const Game<SH>& g, const RuleSet& rs, int k,
+                                        unsigned long long game_id, unsigned long long step) {
   constexpr int C = SH::C, R = SH::R, H = SH::H, P = SH::P;
+  const int rule = rs.id[k], iarg = rs.iarg[k], slot = rs.tslot[k];
+  const double farg = rs.farg[k];
+  const unsigned long long seed = rs.seed;
   if constexpr (EXT) {
-    if (rule >= R_TELL_ANYONE_USELESS_CARD) return run_ext_rule(g, rule, farg, seed, game_id, step);
+    if (rule >= R_TELL_ANYONE_USELESS_CARD) return run_ext_rule(g, rule, farg, rs, slot, seed, game_id, step);
   }
   switch (rule) {
     case R_DISCARD_OLDEST_FIRST:                       // ruleset.py:206-216
@@ -384,10 +403,10 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, int rule, double farg
     }
 
     case R_PLAY_PROBABLY_SAFE:                         // :617-635
-      return play_probably_safe(g, farg, iarg != 0);
+      return play_probably_safe(g, farg, iarg != 0, rs, slot);
 
     case R_HAIL_MARY:                                  // :653-655
-      if (SH::DECK - g.deck_pos == 0 && g.life > 1) return play_probably_safe(g, 0.0, false);
+      if (SH::DECK - g.deck_pos == 0 && g.life > 1) return play_probably_safe(g, 0.0, false, rs, -1);
       return -1;
 
     case R_LEGAL_RANDOM: {                             // :598-604 (intended semantics)
@@ -421,7 +440,7 @@ __device__ __forceinline__ int rules_act(const Game<SH>& g, const RuleSet& rs,
 #pragma unroll 1
   for (int k = 0; k <= rs.n; ++k) {
     if (a < 0) {
-      const int r = run_rule<SH, EXT>(g, rs.id[k], rs.farg[k], rs.iarg[k], rs.seed, game_id, step);
+      const int r = run_rule<SH, EXT>(g, rs, k, game_id, step);
       if (r >= 0) { a = r; h = k; }
     }
   }

@@ -403,11 +403,11 @@ __device__ __forceinline__ int run_rule(const Game<SH>& g, const RuleSet& rs, in
     }
 
     case R_PLAY_PROBABLY_SAFE:                         // :617-635
-      return play_probably_safe(g, farg, iarg != 0, rs, slot);
-
-    case R_HAIL_MARY:                                  // :653-655
-      if (SH::DECK - g.deck_pos == 0 && g.life > 1) return play_probably_safe(g, 0.0, false, rs, -1);
-      return -1;
+    case R_HAIL_MARY: {                                // :653-655 = play_probably_safe(0.0) when the deck is
+      const bool hm = rule == R_HAIL_MARY;             // empty and a life can be spared; ONE inlined copy
+      if (hm && !(SH::DECK - g.deck_pos == 0 && g.life > 1)) return -1;
+      return play_probably_safe(g, hm ? 0.0 : farg, hm ? false : iarg != 0, rs, hm ? -1 : slot);
+    }
 
     case R_LEGAL_RANDOM: {                             // :598-604 (intended semantics)
       unsigned long long m = legal_mask(g);

@@ -1,0 +1,258 @@
+// The learner's one exchange step over NVLink peer memory: an in-place sum of the flat fp32
+// gradient bucket across the GPUs of one node ("ncclAllReduce(sum, fp32) of the flat
+// gradient bucket once per update, fixed algorithm for run-to-run determinism").
+//
+// One process per GPU.  Every rank exports its bucket and a small flag array with CUDA IPC and maps
+// its peers'; the kernel is a two-shot all-reduce with plain peer loads / stores over NVLink:
+//   barrier      every rank's bucket is complete (stream order) and visible
+//   shot 1       rank r sums slice r of ALL buckets, ranks in fixed order 0..W-1 (every rank computes
+//                the same bits), and writes the result over slice r of its own bucket
+//   barrier
+//   shot 2       rank r copies the reduced slice j from rank j's bucket, for every j != r
+//   barrier      nobody still reads a bucket that its owner is about to overwrite
+// 2 (W-1)/W of the bucket crosses NVLink per rank instead of the (W-1) of a one-shot scheme; at the
+// 5-23 MB of this path the three flag barriers (a few microseconds each) are the rest of the cost.
+// Barriers are per CTA: CTA b of rank r raises flag[peer][b][r] on every peer and waits for its own
+// row -- only CTAs with the same index on different GPUs wait for each other, so no co-residency of a
+// whole grid is assumed.  Waits are bounded: a peer that never arrives becomes a trap, not a hang.
+#include "common.cuh"
+#include <new>
+#include <string.h>
+
+namespace {
+constexpr int kMaxWorld = 8;
+constexpr int kCommBlocks = 144;      // CTAs per rank (same on every rank; < 148 SMs, all resident)
+constexpr int kCommThreads = 512;
+}  // namespace
+
+struct hb_comm {
+  int device = 0, rank = 0, world = 1;
+  float* own = nullptr;               // this rank's bucket (not owned)
+  int64_t n = 0;
+  uint32_t* flags = nullptr;          // [3 barriers][kCommBlocks][kMaxWorld] epoch counters (owned, exported)
+  float* peer_buf[kMaxWorld] = {nullptr};
+  uint32_t* peer_flags[kMaxWorld] = {nullptr};
+  bool opened = false;
+  uint32_t epoch = 0;
+};
+
+namespace {
+
+struct CommArgs {
+  float* buf[kMaxWorld];
+  uint32_t* flags[kMaxWorld];
+  int rank, world;
+  long long n4;                       // float4 elements
+  uint32_t epoch;
+};
+
+// peer data: system-scope loads that never come from this SM's L1
+__device__ __forceinline__ float4 ld_peer(const float4* p) {
+  float4 v;
+  asm volatile("ld.volatile.global.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_flag(uint32_t* p, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_flag(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ void st_flag_relaxed(uint32_t* p, uint32_t v) {
+  asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_flag_relaxed(const uint32_t* p) {
+  uint32_t v;
+  asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+
+// CTA-level barrier across the GPUs (stage 0..2).  Thread i < world signals peer i and waits for it.
+// PUBLISH: this CTA wrote data the peers will read after the barrier (release store); otherwise the
+// signal is a relaxed store (stage 0: the bucket was written by earlier kernels of this stream).
+// The poll is a relaxed system-scope load; one acquire fence follows the successful poll.
+template <bool PUBLISH>
+__device__ __forceinline__ void gpu_barrier(const CommArgs& a, int stage) {
+  __syncthreads();
+  if (threadIdx.x < a.world) {
+    const int peer = threadIdx.x;
+    const size_t slot = ((size_t)stage * kCommBlocks + blockIdx.x) * kMaxWorld;
+    if (peer != a.rank) {
+      if (PUBLISH) st_flag(a.flags[peer] + slot + a.rank, a.epoch);
+      else st_flag_relaxed(a.flags[peer] + slot + a.rank, a.epoch);
+      const uint32_t* mine = a.flags[a.rank] + slot + peer;
+      const long long t0 = clock64();
+      while ((int32_t)(ld_flag_relaxed(mine) - a.epoch) < 0) {
+        if (clock64() - t0 > 8000000000ll) __trap();      // ~4 s: a rank is missing
+      }
+      asm volatile("fence.acq_rel.sys;" ::: "memory");
+    }
+  }
+  __syncthreads();
+}
+
+template <int W>
+__global__ void __launch_bounds__(kCommThreads)
+allreduce_two_shot_kernel(CommArgs a) {
+  const int r = a.rank;
+  const long long per = (a.n4 + W - 1) / W;               // slice length in float4
+  gpu_barrier<false>(a, 0);
+  constexpr int U = W <= 2 ? 8 : (W <= 4 ? 4 : 2);         // independent peer loads in flight per thread
+  const long long stride = (long long)kCommBlocks * kCommThreads;
+  {
+    const long long lo = per * r, hi = lo + per < a.n4 ? lo + per : a.n4;
+    for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += U * stride) {
+      float4 v[U][W];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+#pragma unroll
+        for (int j = 0; j < W; ++j)
+          if (i < hi) v[u][j] = ld_peer(reinterpret_cast<const float4*>(a.buf[j]) + i);
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const long long i = i0 + u * stride;
+        if (i < hi) {
+          float4 s = v[u][0];
+#pragma unroll
+          for (int j = 1; j < W; ++j) { s.x += v[u][j].x; s.y += v[u][j].y; s.z += v[u][j].z; s.w += v[u][j].w; }
+          reinterpret_cast<float4*>(a.buf[r])[i] = s;
+        }
+      }
+    }
+  }
+  gpu_barrier<true>(a, 1);
+  for (int jj = 1; jj < W; ++jj) {
+    const int j = (r + jj) % W;                            // spread the peers over the links
+    const long long lo = per * j, hi = lo + per < a.n4 ? lo + per : a.n4;
+    const float4* src = reinterpret_cast<const float4*>(a.buf[j]);
+    float4* dst = reinterpret_cast<float4*>(a.buf[r]);
+    for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += 2 * U * stride) {
+      float4 v[2 * U];
+#pragma unroll
+      for (int u = 0; u < 2 * U; ++u)
+        if (i0 + u * stride < hi) v[u] = ld_peer(src + i0 + u * stride);
+#pragma unroll
+      for (int u = 0; u < 2 * U; ++u)
+        if (i0 + u * stride < hi) dst[i0 + u * stride] = v[u];
+    }
+  }
+  gpu_barrier<false>(a, 2);
+}
+
+}  // namespace
+
+extern "C" {
+
+int hb_comm_destroy(hb_comm* c);
+
+int hb_comm_create(int rank, int world, int device, float* d_bucket, int64_t n, hb_comm** out) {
+  HB_REQUIRE(out != nullptr && d_bucket != nullptr, "hb_comm_create: NULL argument");
+  HB_REQUIRE(world >= 1 && world <= kMaxWorld && rank >= 0 && rank < world, "hb_comm_create: rank %d of %d",
+             rank, world);
+  HB_REQUIRE(n > 0 && n % 4 == 0 && ((uintptr_t)d_bucket & 15) == 0,
+             "hb_comm_create: the bucket must be 16-byte aligned with a multiple of 4 elements");
+  hb::DeviceGuard g(device);
+  HB_REQUIRE(g.ok, "hb_comm_create: cannot select device %d", device);
+  hb_comm* c = new (std::nothrow) hb_comm();
+  HB_REQUIRE(c != nullptr, "hb_comm_create: out of host memory");
+  c->device = device; c->rank = rank; c->world = world; c->own = d_bucket; c->n = n;
+  const size_t fbytes = (size_t)3 * kCommBlocks * kMaxWorld * sizeof(uint32_t);
+  // own 2 MB block: the IPC handle then maps exactly this allocation on the peers
+  cudaError_t e = cudaMalloc(&c->flags, fbytes < ((size_t)2 << 20) ? ((size_t)2 << 20) : fbytes);
+  if (e == cudaSuccess) e = cudaMemset(c->flags, 0, fbytes);
+  if (e != cudaSuccess) { delete c; return hb::cuda_fail(e, "hb_comm_create alloc", __FILE__, __LINE__); }
+  c->peer_buf[rank] = d_bucket;
+  c->peer_flags[rank] = c->flags;
+  *out = c;
+  return HB_OK;
+}
+
+/* 128 bytes: the IPC handles of the bucket and of the flag array, to be all-gathered by the caller. */
+int hb_comm_export(hb_comm* c, void* h_out128) {
+  HB_REQUIRE(c && h_out128, "hb_comm_export: NULL argument");
+  hb::DeviceGuard g(c->device);
+  cudaIpcMemHandle_t hb_, hf;
+  HB_CUDA(cudaIpcGetMemHandle(&hb_, c->own));
+  HB_CUDA(cudaIpcGetMemHandle(&hf, c->flags));
+  static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+  memcpy(h_out128, &hb_, 64);
+  memcpy((char*)h_out128 + 64, &hf, 64);
+  return HB_OK;
+}
+
+/* h_all: world x 128 bytes in rank order (what hb_comm_export produced on every rank). */
+int hb_comm_open(hb_comm* c, const void* h_all) {
+  HB_REQUIRE(c && h_all, "hb_comm_open: NULL argument");
+  HB_REQUIRE(!c->opened, "hb_comm_open: already opened");
+  hb::DeviceGuard g(c->device);
+  for (int j = 0; j < c->world; ++j) {
+    if (j == c->rank) continue;
+    cudaIpcMemHandle_t hb_, hf;
+    memcpy(&hb_, (const char*)h_all + (size_t)j * 128, 64);
+    memcpy(&hf, (const char*)h_all + (size_t)j * 128 + 64, 64);
+    HB_CUDA(cudaIpcOpenMemHandle((void**)&c->peer_buf[j], hb_, cudaIpcMemLazyEnablePeerAccess));
+    HB_CUDA(cudaIpcOpenMemHandle((void**)&c->peer_flags[j], hf, cudaIpcMemLazyEnablePeerAccess));
+  }
+  c->opened = true;
+  return HB_OK;
+}
+
+int hb_comm_destroy(hb_comm* c) {
+  if (c == nullptr) return HB_OK;
+  hb::DeviceGuard g(c->device);
+  if (c->opened)
+    for (int j = 0; j < c->world; ++j) {
+      if (j == c->rank) continue;
+      if (c->peer_buf[j]) cudaIpcCloseMemHandle(c->peer_buf[j]);
+      if (c->peer_flags[j]) cudaIpcCloseMemHandle(c->peer_flags[j]);
+    }
+  if (c->flags) cudaFree(c->flags);
+  delete c;
+  return HB_OK;
+}
+
+/* In-place sum of the bucket over all ranks; every rank must call it the same number of times.
+ * Stream ordered; the result is identical on every rank (fixed summation order). */
+int hb_comm_allreduce(hb_comm* c, void* stream) {
+  HB_REQUIRE(c != nullptr, "hb_comm_allreduce: NULL communicator");
+  if (c->world == 1) return HB_OK;
+  if (!c->opened) { hb::set_error("hb_comm_allreduce: peers are not mapped (hb_comm_open)"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(c->device);
+  CommArgs a;
+  for (int j = 0; j < kMaxWorld; ++j) { a.buf[j] = c->peer_buf[j]; a.flags[j] = c->peer_flags[j]; }
+  a.rank = c->rank; a.world = c->world; a.n4 = c->n / 4;
+  a.epoch = ++c->epoch;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (c->world) {
+    case 2: allreduce_two_shot_kernel<2><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 3: allreduce_two_shot_kernel<3><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 4: allreduce_two_shot_kernel<4><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 5: allreduce_two_shot_kernel<5><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 6: allreduce_two_shot_kernel<6><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 7: allreduce_two_shot_kernel<7><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    default: allreduce_two_shot_kernel<8><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+  }
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_comm_info(const hb_comm* c, int what) {
+  if (c == nullptr) return -1;
+  switch (what) {
+    case 0: return c->rank;
+    case 1: return c->world;
+    case 2: return c->opened ? 1 : 0;
+    case 3: return (int)c->epoch;
+    default: return -1;
+  }
+}
+
+}  // extern "C"

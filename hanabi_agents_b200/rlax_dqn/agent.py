@@ -127,6 +127,23 @@ class DQNAgent:
                 pass
             self._learner = None
 
+    def _allreduce_grads(self):
+        """The one collective of the job: sum of the flat gradient bucket over the ranks.  One kernel over
+        NVLink peer memory (dist.NvlinkAllReduce) when the peers can be mapped, NCCL otherwise or when
+        HB_ALLREDUCE=nccl."""
+        if getattr(self, "_comm", None) is None:
+            self._comm = False
+            if os.environ.get("HB_ALLREDUCE", "nvlink") != "nccl":
+                try:
+                    from ..dist import NvlinkAllReduce
+                    self._comm = NvlinkAllReduce(self.network.grad_bucket, self.process_group)
+                except Exception:      # noqa: BLE001 -- every rank takes the same branch (dist.py)
+                    self._comm = False
+        if self._comm:
+            self._comm()
+        else:
+            self.torch.distributed.all_reduce(self.network.grad_bucket, group=self.process_group)
+
     def update(self, uniforms=None):
         """One training step (rlax_rainbow.py:310-339): sample_batch -> update_q -> update_priorities
         -> target sync.  Two C calls (each a replayed CUDA graph) around the gradient all-reduce.
@@ -150,7 +167,7 @@ class DQNAgent:
                                       float(self.params.discount), 0, stream))
         world, _ = self._world()
         if world > 1:
-            self.torch.distributed.all_reduce(self.network.grad_bucket, group=self.process_group)
+            self._allreduce_grads()
         _lib.check(L.hb_learner_apply(self._learner, float(self.params.learning_rate), 0.9, 0.999,
                                       self.adam_eps, 1.0 / world, stream))
         if self.train_step % self.params.target_update_period == 0:   # :336-337

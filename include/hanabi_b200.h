@@ -354,6 +354,26 @@ void* hb_session_buffer(hb_session* s, int which, int agent);
 /* Synchronising copy of buffer 9 to the host. */
 int hb_session_stats(hb_session* s, double* h_out4, void* stream);
 
+/* ------------------------------------------------------------------------ */
+/* The learner's one exchange step: in-place sum of the flat fp32   */
+/* gradient bucket over the GPUs of one node, as a two-shot all-reduce kernel   */
+/* over NVLink peer memory (CUDA IPC, one process per GPU).  Replaces nothing   */
+/* in the reference (it is single-process); stands where a data-parallel JAX     */
+/* learner would call lax.psum on the gradients of rlax_rainbow.py:203-213.      */
+/* ------------------------------------------------------------------------ */
+typedef struct hb_comm hb_comm;
+int hb_comm_create(int rank, int world, int device, float* d_bucket, int64_t n, hb_comm** out);
+int hb_comm_destroy(hb_comm* c);
+/* 128 bytes of IPC handles (bucket, flags); the caller all-gathers them in rank order ... */
+int hb_comm_export(hb_comm* c, void* h_out128);
+/* ... and maps every peer from the gathered world x 128 bytes. */
+int hb_comm_open(hb_comm* c, const void* h_all);
+/* Stream-ordered all-reduce; every rank calls it once per step.  The sum runs over the ranks in
+ * fixed order, so every rank ends with the same bits. */
+int hb_comm_allreduce(hb_comm* c, void* stream);
+/* what: 0 rank, 1 world, 2 peers mapped, 3 calls so far */
+int hb_comm_info(const hb_comm* c, int what);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,9 +1,9 @@
-// One learner step of DQNAgent.update (hanabi_agents/rlax_dqn/rlax_rainbow.py:310-339) as ONE
-// C call: stratified sample -> gather -> forward / loss / backward -> [all-reduce by the caller] ->
-// Adam -> priority update.  The step is a fixed sequence of ~35 small launches, so it is captured
-// once into two CUDA graphs (phase A up to the gradient bucket, phase B from Adam on) and replayed;
-// what changes from step to step (the stratified keys, or the uniform indices) travels through a
-// pinned staging buffer that the graph's first node copies to the device.
+// One learner step of DQNAgent.update (hanabi_agents/rlax_dqn/rlax_rainbow.py:310-339) as TWO
+// C calls around the caller's gradient all-reduce: stratified sample -> gather -> forward / loss /
+// backward (hb_learner_grads) | Adam -> priority update (hb_learner_apply).  A phase is a fixed
+// sequence of ~15-20 small launches, so each is captured once into a CUDA graph and replayed; what
+// changes from step to step (the stratified keys, or the uniform indices) is copied from a 4-slot
+// ring of pinned staging rows to the device right before the phase-A graph is launched.
 //
 // Built only on the public entry points of the other translation units (hb_rb_*, hb_net_*).
 #include "common.cuh"

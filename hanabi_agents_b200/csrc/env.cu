@@ -65,19 +65,18 @@ env_reset_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict_
 // A game whose previous step was LAST is reset onto its next deck (action ignored, reward 0,
 // FIRST) -- otherwise rl_env.step: apply, deal, reward = score delta.
 // `row` is the deck-pool row of the current episode, (game_id + episode * n_total) mod n_decks; the
-// next episode's row is row + (n_total mod n_decks) with one conditional subtraction -- the 64-bit
-// modulo of deck_of() was 21.6 % of all warp instructions of the self-play kernel when it sat in
-// this branch (some lane of a warp resets in ~40 % of the steps; profiles/r01_selfplay_history.md).
+// next episode's row is row + (n_total mod n_decks) with one conditional subtraction (no 64-bit
+// modulo in the step loop).  `next_card` = deck[g.deck_pos], loaded by the caller ahead of time.
 template <class SH>
 __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
                                            const uint8_t*& deck, unsigned long long& row,
-                                           unsigned long long row_step, int action,
+                                           unsigned long long row_step, int action, uint32_t next_card,
                                            unsigned long long lm, unsigned long long* illegal) {
   if (g.step_type == LAST) {
     ++g.episode;
     row += row_step;
     if (row >= (unsigned long long)rt.n_decks) row -= (unsigned long long)rt.n_decks;
-    deck = decks + row * SH::DECK;
+    deck = decks + row * kDeckPitch;
     reset_game(g, deck);
     return 0.0f;
   }
@@ -85,9 +84,15 @@ __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint
     atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and leave the game as it is
     return 0.0f;
   }
-  const int r = apply_move(g, action, deck);
+  const int r = apply_move(g, action, next_card);
   g.step_type = g.terminal() ? LAST : MID;
   return (float)r;
+}
+
+// deck[g.deck_pos] (the pitch leaves room to read one past a 50-card deck)
+template <class SH>
+__device__ __forceinline__ uint32_t peek_card(const Game<SH>& g, const uint8_t* deck) {
+  return __ldg(deck + g.deck_pos);
 }
 
 template <class SH>
@@ -101,8 +106,9 @@ env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   Game<SH> g;
   load_game(g, state, game);
   unsigned long long row = deck_row<SH>(rt, game, g.episode);
-  const uint8_t* deck = decks + row * SH::DECK;
-  const float r = step_game(g, rt, decks, deck, row, rt.row_step, action[game], legal_mask(g), illegal);
+  const uint8_t* deck = decks + row * kDeckPitch;
+  const float r = step_game(g, rt, decks, deck, row, rt.row_step, action[game], peek_card(g, deck),
+                            legal_mask(g), illegal);
   if (reward != nullptr) reward[game] = r;
   emit(g, game, obs, legal, step_type);
   store_game(g, state, game);
@@ -148,6 +154,10 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
 
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
 // held in registers; only the per-step outputs touch HBM.  Output row (t, game).
+// Pass t of the loop is {observation of state t -> row t-1, rule bodies on state t} as ONE basic block
+// (both only read the state; stores are predicated, not branched around), then {rule list, transition
+// t -> row t}.  The observation of state 0 was written by the previous launch (pass 0 stores
+// nothing); pass n_steps only writes the last observation.
 template <class SH, bool EXT>
 __global__ void __launch_bounds__(kThreads, 7)
 selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks, RuleSet rs,
@@ -157,28 +167,47 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
   const long long game = game_index();
   if (game >= rt.n_games) return;
+  const unsigned long long game_id = (unsigned long long)(rt.game_id_base + game);
   Game<SH> g;
   load_game(g, state, game);
   unsigned long long row = deck_row<SH>(rt, game, g.episode);   // one 64-bit modulo per launch
-  const uint8_t* deck = decks + row * SH::DECK;
-  unsigned long long lm = legal_mask(g);
+  const uint8_t* deck = decks + row * kDeckPitch;
   // rule-hit histogram: 8-bit counters packed in two registers (the host keeps n_steps <= 255)
   unsigned long long cnt_lo = 0, cnt_hi = 0, cnt_fb = 0;
 #pragma unroll 1
-  for (int t = 0; t < n_steps; ++t) {
+  for (int t = 0;; ++t) {
+    const long long orow = (long long)(t - 1) * rt.n_games + game;     // outputs of state t
+    const bool out = t > 0;
+    const uint32_t next_card = peek_card(g, deck);
+    const unsigned long long lm = legal_mask(g);
+    {
+      uint32_t orow_w[SH::kObsStride];
+      encode_row(g, SH::P - 1, orow_w);
+      uint32_t* dst = obs + orow * SH::kObsStride;
+#pragma unroll
+      for (int i = 0; i < SH::kObsStride / 4; ++i)
+        st_v4_if(out && obs != nullptr, dst + 4 * i, orow_w[4 * i], orow_w[4 * i + 1], orow_w[4 * i + 2],
+                 orow_w[4 * i + 3]);
+    }
+    st_u32_if(out && legal != nullptr, legal + orow * SH::kLegalWords, (uint32_t)lm);
+    if (SH::kLegalWords > 1)
+      st_u32_if(out && legal != nullptr, legal + orow * SH::kLegalWords + 1, (uint32_t)(lm >> 32));
+    st_u8_if(out && step_type != nullptr, step_type + orow, (uint32_t)g.step_type);
+    Cores co;
+    rule_cores(g, rs.used, co);
+    if (t == n_steps) break;
+
     int a = 0, hit = -1;
-    if (g.step_type != LAST)
-      a = rules_act<SH, EXT>(g, rs, (unsigned long long)(rt.game_id_base + game), step0 + t, &hit);
-    const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, lm, illegal);
-    const long long row = (long long)t * rt.n_games + game;
-    if (action != nullptr) action[row] = a;
-    if (reward != nullptr) reward[row] = r;
+    if (g.step_type != LAST) a = rules_resolve<SH, EXT>(g, co, rs, game_id, step0 + t, &hit);
+    const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, next_card, lm, illegal);
+    const long long arow = (long long)t * rt.n_games + game;
+    if (action != nullptr) action[arow] = a;
+    if (reward != nullptr) reward[arow] = r;
     if (hit >= 0) {
       if (hit < 8) cnt_lo += 1ull << (8 * hit);
       else if (hit < 16) cnt_hi += 1ull << (8 * (hit - 8));
       else ++cnt_fb;
     }
-    lm = emit(g, row, obs, legal, step_type);
   }
   store_game(g, state, game);
   if (hist != nullptr) {
@@ -206,13 +235,12 @@ __global__ void env_dump_kernel(Rt rt, const uint32_t* __restrict__ state, int32
   const uint32_t last = w[SH::S + 4];
   int32_t* o = out + game * dump_len;
   int k = 0;
-  const int life = (a >> 19) & 3, cur = (a >> 21) & 7;
-  int score = 0;
-  for (int c = 0; c < SH::C; ++c) score += (a >> (3 * c)) & 7;
-  o[k++] = cur; o[k++] = (a >> 15) & 15; o[k++] = life;
-  o[k++] = SH::DECK - (int)(b & 63); o[k++] = (a >> 24) & 7; o[k++] = (a >> 27) & 3;
+  const int life = (a >> 29) & 3, cur = (b >> 21) & 7;
+  const int score = __popc(a & kGridMask);
+  o[k++] = cur; o[k++] = (a >> 25) & 15; o[k++] = life;
+  o[k++] = SH::DECK - (int)(b & 63); o[k++] = (b >> 24) & 7; o[k++] = (b >> 27) & 3;
   o[k++] = life <= 0 ? 0 : score; o[k++] = (int32_t)(w[SH::S + 5] & 0x7fffffff);
-  for (int c = 0; c < SH::C; ++c) o[k++] = (a >> (3 * c)) & 7;
+  for (int c = 0; c < SH::C; ++c) o[k++] = __popc((a >> (5 * c)) & 31u);
   for (int p = 0; p < SH::P; ++p) {
     const int seat = (p - cur + SH::P) % SH::P;
     o[k++] = (b >> (6 + 3 * seat)) & 7;
@@ -339,9 +367,11 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
   HB_REQUIRE(n == 0 || ids != nullptr, "rule ids are NULL");
   rs.n = n;
   rs.seed = seed;
+  rs.used = 1u << R_LEGAL_RANDOM;
   for (int k = 0; k < n; ++k) {
     HB_REQUIRE(ids[k] >= 0 && ids[k] < R_NUM_RULES, "unknown rule id %d", ids[k]);
     rs.id[k] = ids[k];
+    rs.used |= 1u << ids[k];
     rs.farg[k] = farg ? farg[k] : 0.0;
     rs.iarg[k] = iarg ? iarg[k] : 0;
   }
@@ -456,9 +486,12 @@ int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* s
   HB_REQUIRE(e && d_decks && n_decks >= 1, "hb_env_set_decks: bad arguments");
   hb::DeviceGuard g(e->device);
   if (e->decks) { HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); cudaFree(e->decks); e->decks = nullptr; }
-  const size_t bytes = (size_t)n_decks * e->deck_size;
+  // one deck per kDeckPitch-byte row (aligned 16-byte loads of the initial deal; the tail is zero)
+  const size_t bytes = (size_t)n_decks * kDeckPitch;
   HB_CUDA(cudaMalloc(&e->decks, bytes));
-  HB_CUDA(cudaMemcpyAsync(e->decks, d_decks, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  HB_CUDA(cudaMemsetAsync(e->decks, 0, bytes, (cudaStream_t)stream));
+  HB_CUDA(cudaMemcpy2DAsync(e->decks, kDeckPitch, d_decks, e->deck_size, e->deck_size, (size_t)n_decks,
+                            cudaMemcpyDefault, (cudaStream_t)stream));
   e->rt.n_decks = n_decks;
   e->rt.row_step = e->rt.n_total % n_decks;
   return HB_OK;

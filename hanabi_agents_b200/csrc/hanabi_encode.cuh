@@ -46,7 +46,7 @@ __device__ __forceinline__ unsigned long long discard_thermometers(unsigned long
 template <class SH, int K, int I, int N>
 __device__ __forceinline__ void put_hand_card(uint32_t (&row)[N], uint32_t w) {
   // EncodeHands: one-hot card index of another player's card
-  put<(K - 1) * SH::H * SH::BPC + I * SH::BPC, SH::BPC>(row, slot_valid(w) ? (1ull << slot_card(w)) : 0ull);
+  put<(K - 1) * SH::H * SH::BPC + I * SH::BPC, SH::BPC>(row, slot_onehot(w));
 }
 
 template <class SH, int K, int I, int N>
@@ -75,11 +75,10 @@ __device__ __forceinline__ void put_seat(uint32_t (&row)[N], const Game<SH>& g) 
 }
 
 // Observation of the player at seat 0, `mover_seat` = seat of the player who made g.last
-// (P-1 for the player to move).  Writes kObsStride words at `out`.
+// (P-1 for the player to move), assembled in registers: kObsStride words.
 template <class SH>
-__device__ __forceinline__ void encode_obs(const Game<SH>& g, int mover_seat, uint32_t* __restrict__ out) {
+__device__ __forceinline__ void encode_row(const Game<SH>& g, int mover_seat, uint32_t (&row)[SH::kObsStride]) {
   constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R, BPC = SH::BPC;
-  uint32_t row[SH::kObsStride];
 #pragma unroll
   for (int i = 0; i < SH::kObsStride; ++i) row[i] = 0;
 
@@ -95,13 +94,8 @@ __device__ __forceinline__ void encode_obs(const Game<SH>& g, int mover_seat, ui
   {                                                     // EncodeBoard
     const int rem = SH::DECK - g.deck_pos;
     put<SH::kOffBoard, SH::kDeckThermo>(row, (1ull << rem) - 1);
-    uint32_t v = 0;                                     // fireworks: one-hot of height-1
-#pragma unroll
-    for (int c = 0; c < C; ++c) {
-      const int f = g.firework(c);
-      if (f > 0) v |= 1u << (c * R + f - 1);
-    }
-    put<SH::kOffFireworks, BPC>(row, v);
+    // fireworks: one-hot of height-1 = the top bit of each colour's thermometer
+    put<SH::kOffFireworks, BPC>(row, g.fw & ~((g.fw >> 1) & kLow4));
     put<SH::kOffInfo, SH::MAX_INFO + SH::MAX_LIFE>(
         row, ((1u << g.info) - 1) | (((1u << g.life) - 1) << SH::MAX_INFO));
   }
@@ -135,10 +129,34 @@ __device__ __forceinline__ void encode_obs(const Game<SH>& g, int mover_seat, ui
     put<SH::kOffLast + 2 * P + 4 + C + R + 2 * H, BPC + 2>(row, c3);
   }
 
+}
+
+// ... and written as kObsStride words at `out` (16-byte stores).
+template <class SH>
+__device__ __forceinline__ void encode_obs(const Game<SH>& g, int mover_seat, uint32_t* __restrict__ out) {
+  uint32_t row[SH::kObsStride];
+  encode_row(g, mover_seat, row);
   uint4* dst = reinterpret_cast<uint4*>(out);
 #pragma unroll
   for (int i = 0; i < SH::kObsStride / 4; ++i)
     dst[i] = make_uint4(row[4 * i], row[4 * i + 1], row[4 * i + 2], row[4 * i + 3]);
+}
+
+// Stores that are switched off by a predicate instead of a branch: the fused self-play kernel keeps
+// {encoder, legal moves, rule bodies} in ONE basic block so that the scheduler can interleave their
+// independent dependency chains; `if (ptr != nullptr)` around the encoder would cut the block.
+__device__ __forceinline__ void st_v4_if(bool p, uint32_t* ptr, uint32_t a, uint32_t b, uint32_t c,
+                                         uint32_t d) {
+  asm volatile("{ .reg .pred q; setp.ne.u32 q, %5, 0; @q st.global.v4.u32 [%0], {%1, %2, %3, %4}; }"
+               :: "l"(ptr), "r"(a), "r"(b), "r"(c), "r"(d), "r"((uint32_t)p));
+}
+__device__ __forceinline__ void st_u32_if(bool p, uint32_t* ptr, uint32_t a) {
+  asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.global.u32 [%0], %1; }"
+               :: "l"(ptr), "r"(a), "r"((uint32_t)p));
+}
+__device__ __forceinline__ void st_u8_if(bool p, uint8_t* ptr, uint32_t a) {
+  asm volatile("{ .reg .pred q; setp.ne.u32 q, %2, 0; @q st.global.u8 [%0], %1; }"
+               :: "l"(ptr), "r"(a), "r"((uint32_t)p));
 }
 
 }  // namespace hbg

@@ -19,9 +19,10 @@
 //   words 0..S-1  card slots, seat-relative, slot (k, i) at word k*H + i:
 //        [24:0] plausible(colour) x plausible(rank) grid, bit colour*5+rank (0 = empty slot)
 //        [25] colour hinted  [26] rank hinted  [31:27] card index colour*5+rank
-//   word S+0  [14:0] fireworks 3b x5 | [18:15] info | [20:19] life | [23:21] player to move
+//   word S+0  [24:0] fireworks as a thermometer grid (bit colour*5+rank set iff rank < stack height)
+//             | [28:25] info | [30:29] life
+//   word S+1  [5:0] deck_pos | [20:6] hand sizes 3b x5 (seat-relative) | [23:21] player to move
 //             | [26:24] turns_to_play | [28:27] step_type
-//   word S+1  [5:0] deck_pos | [20:6] hand sizes 3b x5 (seat-relative)
 //   word S+2,3  discard counts, 2 bits per card type (25 types -> 50 bits)
 //   word S+4  last move (made by the player now at seat P-1): [0] valid [6:1] move uid
 //             [11:7] card index [12] scored [13] info token [18:14] reveal bitmask
@@ -89,30 +90,53 @@ __device__ __forceinline__ uint32_t fresh_slot(int card) {
   return SH::kGridAll | ((uint32_t)card << 27);   // everything plausible, nothing hinted
 }
 
+// ---- 25-bit grids (bit colour*5 + rank) -------------------------------------------------------
+// Everything the rules and the transition ask about a card ("is it playable", "has it been played",
+// "is its colour finished", "is its rank below every stack") is ONE AND of the card's one-hot grid
+// bit with a grid derived from the fireworks / discards once per step.
+constexpr uint32_t kLsb5 = 0x0108421u;       // bit 0 of every colour group
+constexpr uint32_t kLow4 = 0x0F7BDEFu;       // bits 0..3 of every colour group
+constexpr uint32_t kRank4 = 0x1084210u;      // bit 4 (the last rank) of every colour group
+// bit 0 / bit 1 of the number of copies per card type (3,2,2,2,1): ranks {0,4} / ranks {0,1,2,3}
+constexpr uint32_t kInst0 = kLsb5 | kRank4;
+constexpr uint32_t kInst1 = kLow4;
+
 template <class SH>
 struct Game {
   uint32_t hand[SH::P][SH::H];   // seat-relative card slots
-  uint32_t fw;                   // 3 bits per colour
+  uint32_t fw;                   // fireworks thermometer grid: bit 5c+r <=> r < height of stack c
   uint32_t hn;                   // 3 bits per seat
   int info, life, cur, ttp, step_type, deck_pos;
-  unsigned long long disc;       // 2 bits per card type
+  unsigned long long disc;       // 2 bits per card type (count of discarded copies)
+  uint32_t d0, d1;               // the same counts as two bit planes in grid layout (derived, not stored)
   uint32_t last;
   uint32_t episode;
 
-  __device__ __forceinline__ int firework(int c) const { return (fw >> (3 * c)) & 7; }
+  __device__ __forceinline__ int firework(int c) const { return __popc((fw >> (5 * c)) & 31u); }
   __device__ __forceinline__ int hand_n(int k) const { return (hn >> (3 * k)) & 7; }
-  __device__ __forceinline__ int score() const {
-    if (life <= 0) return 0;
-    int s = 0;
-#pragma unroll
-    for (int c = 0; c < SH::C; ++c) s += firework(c);
-    return s;
-  }
+  __device__ __forceinline__ int score() const { return life <= 0 ? 0 : __popc(fw); }
   // HanabiState::EndOfGameStatus
   __device__ __forceinline__ bool terminal() const {
-    return life < 1 || score() >= SH::C * SH::R || ttp <= 0;
+    return life < 1 || __popc(fw) >= SH::C * SH::R || ttp <= 0;
+  }
+  // grid of the cards playable right now: bit 5c + height(c)   (playable_card, ruleset.py:14-33).
+  // (fw << 1) | lsb is the thermometer one notch higher; what leaks across a group boundary lands on
+  // a bit the lsb mask sets anyway.
+  __device__ __forceinline__ uint32_t playable() const {
+    return ((fw << 1) | kLsb5) & ~fw & SH::kGridAll;
   }
 };
+
+// every second bit of x (bits 0, 2, 4, ...) packed into the low 32 bits
+__device__ __forceinline__ uint32_t even_bits(unsigned long long x) {
+  x &= 0x5555555555555555ull;
+  x = (x | (x >> 1)) & 0x3333333333333333ull;
+  x = (x | (x >> 2)) & 0x0f0f0f0f0f0f0f0full;
+  x = (x | (x >> 4)) & 0x00ff00ff00ff00ffull;
+  x = (x | (x >> 8)) & 0x0000ffff0000ffffull;
+  x = (x | (x >> 16)) & 0x00000000ffffffffull;
+  return (uint32_t)x;
+}
 
 // ---- state <-> HBM (16-byte vector accesses; a game is 64 B or 128 B contiguous) ----------
 template <class SH>
@@ -132,15 +156,17 @@ __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restric
 #pragma unroll
     for (int i = 0; i < SH::H; ++i) g.hand[k][i] = w[k * SH::H + i];
   const uint32_t a = w[SH::S], b = w[SH::S + 1];
-  g.fw = a & 0x7fff;
-  g.info = (a >> 15) & 15;
-  g.life = (a >> 19) & 3;
-  g.cur = (a >> 21) & 7;
-  g.ttp = (a >> 24) & 7;
-  g.step_type = (a >> 27) & 3;
+  g.fw = a & kGridMask;
+  g.info = (a >> 25) & 15;
+  g.life = (a >> 29) & 3;
   g.deck_pos = b & 63;
   g.hn = (b >> 6) & 0x7fff;
+  g.cur = (b >> 21) & 7;
+  g.ttp = (b >> 24) & 7;
+  g.step_type = (b >> 27) & 3;
   g.disc = (unsigned long long)w[SH::S + 2] | ((unsigned long long)w[SH::S + 3] << 32);
+  g.d0 = even_bits(g.disc);
+  g.d1 = even_bits(g.disc >> 1);
   g.last = w[SH::S + 4];
   g.episode = w[SH::S + 5];
 }
@@ -155,9 +181,9 @@ __device__ __forceinline__ void store_game(const Game<SH>& g, uint32_t* __restri
   for (int k = 0; k < SH::P; ++k)
 #pragma unroll
     for (int i = 0; i < SH::H; ++i) w[k * SH::H + i] = g.hand[k][i];
-  w[SH::S] = g.fw | ((uint32_t)g.info << 15) | ((uint32_t)g.life << 19) | ((uint32_t)g.cur << 21) |
-             ((uint32_t)g.ttp << 24) | ((uint32_t)g.step_type << 27);
-  w[SH::S + 1] = (uint32_t)g.deck_pos | (g.hn << 6);
+  w[SH::S] = g.fw | ((uint32_t)g.info << 25) | ((uint32_t)g.life << 29);
+  w[SH::S + 1] = (uint32_t)g.deck_pos | (g.hn << 6) | ((uint32_t)g.cur << 21) |
+                 ((uint32_t)g.ttp << 24) | ((uint32_t)g.step_type << 27);
   w[SH::S + 2] = (uint32_t)g.disc;
   w[SH::S + 3] = (uint32_t)(g.disc >> 32);
   w[SH::S + 4] = g.last;
@@ -168,6 +194,10 @@ __device__ __forceinline__ void store_game(const Game<SH>& g, uint32_t* __restri
     if (4 * i < SH::S + 6) dst[i] = make_uint4(w[4 * i], w[4 * i + 1], w[4 * i + 2], w[4 * i + 3]);
 }
 
+// The deck pool on the device: one deck per 64-byte row (hb_env_set_decks pads the rows), so that the
+// cards of the initial deal are one aligned 16-byte load.
+constexpr int kDeckPitch = 64;
+
 template <class SH>
 __device__ __forceinline__ unsigned long long deck_row(const Rt& rt, long long game, uint32_t episode) {
   return (unsigned long long)(rt.game_id_base + game + (long long)episode * rt.n_total) %
@@ -177,20 +207,31 @@ __device__ __forceinline__ unsigned long long deck_row(const Rt& rt, long long g
 template <class SH>
 __device__ __forceinline__ const uint8_t* deck_of(const Rt& rt, const uint8_t* __restrict__ decks,
                                                   long long game, uint32_t episode) {
-  const unsigned long long row =
-      (unsigned long long)(rt.game_id_base + game + (long long)episode * rt.n_total) %
-      (unsigned long long)rt.n_decks;
-  return decks + row * SH::DECK;
+  return decks + deck_row<SH>(rt, game, episode) * kDeckPitch;
 }
 
 // HanabiState ctor + initial deals (A.3): player 0 is filled first, then player 1, ...
 // Player 0 moves first, so seat-relative order == absolute order here.
 template <class SH>
 __device__ __forceinline__ void reset_game(Game<SH>& g, const uint8_t* __restrict__ deck) {
+  static_assert(SH::S <= 32, "initial deal read as two 16-byte loads");
+  uint32_t q[8];
+  {
+    const uint4 v = *reinterpret_cast<const uint4*>(deck);
+    q[0] = v.x; q[1] = v.y; q[2] = v.z; q[3] = v.w;
+  }
+  if constexpr (SH::S > 16) {
+    const uint4 v = *reinterpret_cast<const uint4*>(deck + 16);
+    q[4] = v.x; q[5] = v.y; q[6] = v.z; q[7] = v.w;
+  }
 #pragma unroll
   for (int k = 0; k < SH::P; ++k)
 #pragma unroll
-    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = fresh_slot<SH>(deck[k * SH::H + i]);
+    for (int i = 0; i < SH::H; ++i) {
+      const int j = k * SH::H + i;
+      const uint32_t card = (q[j >> 2] >> (8 * (j & 3))) & 0xffu;
+      g.hand[k][i] = fresh_slot<SH>((int)card);
+    }
   g.fw = 0;
   g.info = SH::MAX_INFO;
   g.life = SH::MAX_LIFE;
@@ -202,7 +243,38 @@ __device__ __forceinline__ void reset_game(Game<SH>& g, const uint8_t* __restric
 #pragma unroll
   for (int k = 0; k < SH::P; ++k) g.hn |= (uint32_t)SH::H << (3 * k);
   g.disc = 0;
+  g.d0 = 0;
+  g.d1 = 0;
   g.last = 0;
+}
+
+// one-hot grid bit of the card in a slot (0 for an empty slot: the true identity of a card is
+// always among its plausible ones, and an empty slot has an empty grid)
+__device__ __forceinline__ uint32_t slot_onehot(uint32_t w) { return (1u << (w >> 27)) & w & kGridMask; }
+
+// union of the one-hots of hand k
+template <class SH>
+__device__ __forceinline__ uint32_t hand_union(const Game<SH>& g, int k) {
+  uint32_t u = 0;
+#pragma unroll
+  for (int i = 0; i < SH::H; ++i) u |= slot_onehot(g.hand[k][i]);
+  return u;
+}
+
+// which colours / ranks occur in a grid, as C-bit / R-bit masks
+template <class SH>
+__device__ __forceinline__ uint32_t grid_ranks(uint32_t u) {
+  uint32_t r = u;
+#pragma unroll
+  for (int c = 1; c < SH::C; ++c) r |= u >> (5 * c);
+  return r & 31u;
+}
+template <class SH>
+__device__ __forceinline__ uint32_t grid_colors(uint32_t u) {
+  // bit 4 of a group <- "group is not zero", then bits 4, 9, 14, ... gathered into bits 0..4 by one
+  // multiplication (the 25 partial products land on distinct bits: 5j - 4i is injective on 0..4)
+  const uint32_t t = (((u & kLow4) + kLow4) | u) & kRank4;
+  return (((t >> 4) * 0x11111u) >> 16) & ((1u << SH::C) - 1);
 }
 
 // ---- legality (A.4): 64-bit mask over move uids for the player to move ---------------------
@@ -211,23 +283,14 @@ __device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g) {
   const unsigned long long hand_bits = (1ull << g.hand_n(0)) - 1;
   unsigned long long m = hand_bits << SH::H;                 // Play(i), i < hand size
   if (g.info < SH::MAX_INFO) m |= hand_bits;                 // Discard(i)
-  if (g.info > 0) {
+  unsigned long long hints = 0;
 #pragma unroll
-    for (int k = 1; k < SH::P; ++k) {
-      uint32_t colors = 0, ranks = 0;                        // what the target hand contains
-#pragma unroll
-      for (int i = 0; i < SH::H; ++i) {
-        const uint32_t w = g.hand[k][i];
-        const int card = slot_card(w);
-        if (slot_valid(w)) {
-          colors |= 1u << card_color(card);
-          ranks |= 1u << card_rank(card);
-        }
-      }
-      m |= (unsigned long long)colors << (2 * SH::H + (k - 1) * SH::C);
-      m |= (unsigned long long)ranks << (2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R);
-    }
+  for (int k = 1; k < SH::P; ++k) {
+    const uint32_t u = hand_union(g, k);                     // what the target hand contains
+    hints |= (unsigned long long)grid_colors<SH>(u) << (2 * SH::H + (k - 1) * SH::C);
+    hints |= (unsigned long long)grid_ranks<SH>(u) << (2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R);
   }
+  if (g.info > 0) m |= hints;
   return m;
 }
 
@@ -247,75 +310,85 @@ __device__ __forceinline__ void rotate_once(Game<SH>& g) {
 }
 
 // `uid` must be legal.  Returns the reward (score delta).  Ends with the seat rotation.
+// `next_card` = deck[g.deck_pos] (whatever when the deck is empty): the caller loads it ahead of time
+// so that the chance node does not wait for memory.
+// Written without branches: a warp nearly always holds games making every kind of move, so both
+// sides would be walked anyway; as selects they are one basic block the scheduler can interleave.
 template <class SH>
-__device__ __forceinline__ int apply_move(Game<SH>& g, int uid, const uint8_t* __restrict__ deck) {
+__device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_card) {
   constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R;
-  const int before = g.score();
-  if (g.deck_pos >= SH::DECK) --g.ttp;          // evaluated BEFORE the move
+  const int before = __popc(g.fw);                 // the game is running: life >= 1
+  const bool deck_empty = g.deck_pos >= SH::DECK;
+  if (deck_empty) --g.ttp;                         // evaluated BEFORE the move
+  const uint32_t pg = g.playable();
+  const bool card_move = uid < 2 * H;
+  const bool is_play = card_move && uid >= H;
   uint32_t last = 1u | ((uint32_t)uid << 1);
-  if (uid < 2 * H) {
-    const bool is_play = uid >= H;
-    const int idx = is_play ? uid - H : uid;
-    uint32_t w = 0;
+
+  // ---- Play / Discard of hand[0][idx] (idx = H: not a card move, nothing shifts)
+  const int idx = card_move ? (is_play ? uid - H : uid) : H;
+  uint32_t w = 0;
 #pragma unroll
-    for (int i = 0; i < H; ++i)
-      if (i == idx) w = g.hand[0][i];
-    const int card = slot_card(w);
-    const int c = card_color(card), r = card_rank(card);
-    last |= (uint32_t)card << 7;
-    bool to_discard = true;
-    if (!is_play) {
-      if (g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 13; }   // IncrementInformationTokens
-    } else if (r == g.firework(c)) {             // AddToFireworks
-      g.fw += 1u << (3 * c);
-      last |= 1u << 12;
-      to_discard = false;
-      if (r + 1 == R && g.info < SH::MAX_INFO) { ++g.info; last |= 1u << 13; }
-    } else {
-      --g.life;
-    }
-    if (to_discard) g.disc += 1ull << (2 * card);
-    // RemoveFromHand: later cards (and their knowledge) shift down
-#pragma unroll
-    for (int i = 0; i < H - 1; ++i)
-      if (i >= idx) g.hand[0][i] = g.hand[0][i + 1];
-    g.hand[0][H - 1] = 0;
-    int n = g.hand_n(0) - 1;
-    // chance node: the only short hand is the mover's; the new card goes to the END of it
-    if (g.deck_pos < SH::DECK) {
-      const uint32_t fresh = fresh_slot<SH>(deck[g.deck_pos++]);
-#pragma unroll
-      for (int i = 0; i < H; ++i)
-        if (i == n) g.hand[0][i] = fresh;
-      ++n;
-    }
-    g.hn = (g.hn & ~7u) | (uint32_t)n;
-  } else {
-    --g.info;
-    int u = uid - 2 * H;
-    const bool by_color = u < (P - 1) * C;
-    if (!by_color) u -= (P - 1) * C;
-    const int span = by_color ? C : R;
-    const int k = 1 + u / span, v = u - (k - 1) * span;
-    // HanabiHand::RevealColor / RevealRank: matching cards keep only the hinted cells and get
-    // the hinted flag; the others lose those cells
-    const uint32_t cells = by_color ? color_cells(v) : rank_cells(v);
-    const uint32_t flag = by_color ? (1u << 25) : (1u << 26);
-    uint32_t mask = 0;
-#pragma unroll
-    for (int kk = 1; kk < P; ++kk)
-#pragma unroll
-      for (int i = 0; i < H; ++i) {
-        const uint32_t w = g.hand[kk][i];
-        const int card = slot_card(w);
-        const bool match = (by_color ? card_color(card) : card_rank(card)) == v;
-        if (kk == k && slot_valid(w)) {
-          g.hand[kk][i] = match ? ((w & (cells | ~kGridMask)) | flag) : (w & ~cells);
-          if (match) mask |= 1u << i;
-        }
-      }
-    last |= mask << 14;
+  for (int i = 0; i < H; ++i)
+    if (i == idx) w = g.hand[0][i];
+  const uint32_t card = w >> 27;
+  const uint32_t oh = card_move ? (1u << card) : 0u;
+  const bool fits = (oh & pg) != 0;
+  const bool succ = is_play && fits;               // AddToFireworks
+  const bool fail = is_play && !fits;
+  const bool room = g.info < SH::MAX_INFO;
+  // IncrementInformationTokens: a discard, or the last card of a stack
+  const bool token = room && ((card_move && !is_play) || (succ && (oh & kRank4) != 0));
+  if (card_move) last |= card << 7;
+  if (succ) { g.fw |= oh; last |= 1u << 12; }
+  if (token) { ++g.info; last |= 1u << 13; }
+  if (fail) --g.life;
+  if (card_move && !succ) {                        // to the discard pile
+    g.disc += 1ull << (2 * card);
+    const uint32_t carry = g.d0 & oh;
+    g.d0 ^= oh;
+    g.d1 ^= carry;
   }
+  // RemoveFromHand: later cards (and their knowledge) shift down; the chance node puts the new card
+  // at the END of the mover's hand.  While the deck lasts every hand is full, so that is slot H-1.
+#pragma unroll
+  for (int i = 0; i < H - 1; ++i)
+    if (i >= idx) g.hand[0][i] = g.hand[0][i + 1];
+  if (card_move) {
+    g.hand[0][H - 1] = deck_empty ? 0u : fresh_slot<SH>((int)next_card);
+    if (deck_empty) g.hn -= 1u; else ++g.deck_pos;
+  }
+
+  // ---- RevealColor / RevealRank: matching cards keep only the hinted cells and get the hinted
+  // flag; the others lose those cells (HanabiHand::RevealColor / RevealRank)
+  int u = uid - 2 * H;
+  const bool by_color = u < (P - 1) * C;
+  if (!by_color) u -= (P - 1) * C;
+  int k = 1, v = u;
+  if constexpr (P > 2) {
+    const int span = by_color ? C : R;
+    k = 1 + u / span;
+    v = u - (k - 1) * span;
+  }
+  uint32_t cells = by_color ? color_cells(v) : rank_cells(v);
+  uint32_t flag = by_color ? (1u << 25) : (1u << 26);
+  if (card_move) { cells = 0; flag = 0; }
+  else --g.info;
+  uint32_t mask = 0;
+#pragma unroll
+  for (int kk = 1; kk < P; ++kk) {
+    const uint32_t kcells = (P == 2 || kk == k) ? cells : 0u;
+    const uint32_t kflag = (P == 2 || kk == k) ? flag : 0u;
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const uint32_t s = g.hand[kk][i];
+      const bool match = (slot_onehot(s) & kcells) != 0;
+      g.hand[kk][i] = match ? ((s & (kcells | ~kGridMask)) | kflag) : (s & ~kcells);
+      if (match) mask |= 1u << i;
+    }
+  }
+  last |= mask << 14;
+
   g.last = last;
   // AdvanceToNextPlayer: the next player becomes seat 0
   g.cur = g.cur + 1 == P ? 0 : g.cur + 1;

@@ -32,6 +32,7 @@ constexpr int kThrSlots = 4;      // rules with a probability threshold that get
 constexpr int kThrRows = 52;      // denominators 0..51 (a deck holds 50 cards)
 struct RuleSet {        // entry [n] is the legal_random fallback, filled by the host
   int n;
+  unsigned int used;    // bit r: rule id r occurs in the list (its core is evaluated)
   int id[kMaxRules + 1];
   int iarg[kMaxRules + 1];
   double farg[kMaxRules + 1];
@@ -74,114 +75,164 @@ template <class SH> __device__ __forceinline__ int uid_rank(int k, int r) {
   return 2 * SH::H + (SH::P - 1) * SH::C + (k - 1) * SH::R + r;
 }
 
+// ---- grids derived from the board once per step -------------------------------------------------
+// rows of the finished colours (stack height 5)
 template <class SH>
-__device__ __forceinline__ int min_firework(const Game<SH>& g) {
-  int m = g.firework(0);
-#pragma unroll
-  for (int c = 1; c < SH::C; ++c) m = min(m, g.firework(c));
-  return m;
-}
+__device__ __forceinline__ uint32_t done_rows(const Game<SH>& g) { return ((g.fw >> 4) & kLsb5) * 31u; }
 
-// grid of the cards playable right now: bit c*5 + fireworks[c]   (playable_card :14-33)
+// cards whose rank is below EVERY stack (rank < min(fireworks)), in every colour row
 template <class SH>
-__device__ __forceinline__ uint32_t playable_grid(const Game<SH>& g) {
-  uint32_t pg = 0;
+__device__ __forceinline__ uint32_t below_all_grid(const Game<SH>& g) {
+  uint32_t a = g.fw;
 #pragma unroll
-  for (int c = 0; c < SH::C; ++c)
-    if (g.firework(c) < SH::R) pg |= 1u << (c * SH::R + g.firework(c));
-  return pg;
-}
-
-template <class SH>
-__device__ __forceinline__ constexpr unsigned long long instances_packed() {
-  unsigned long long k = 0;   // 2-bit fields 3,2,2,2,1 per colour = num_in_deck_by_rank (ruleset.py:9)
-  for (int c = 0; c < SH::C; ++c)
-    k |= (3ull | (2ull << 2) | (2ull << 4) | (2ull << 6) | (1ull << 8)) << (10 * c);
-  return k;
+  for (int c = 1; c < SH::C; ++c) a &= g.fw >> (5 * c);
+  return (a & 31u) * kLsb5;
 }
 
 // get_max_fireworks  ruleset.py:174-193: 5, or the lowest rank whose every copy is discarded.
-// Returned as the grid of cards still worth keeping: bit c*5+r set iff r < max_fireworks[c];
-// *mf_out gets the packed 3-bit values.
+// Returned as the grid of cards still worth keeping: bit c*5+r set iff r < max_fireworks[c].
 template <class SH>
-__device__ __forceinline__ uint32_t useful_grid(const Game<SH>& g, uint32_t* mf_out) {
-  const unsigned long long x = g.disc ^ instances_packed<SH>();
-  const unsigned long long gone = ~(x | (x >> 1)) & 0x5555555555555555ull;   // count == in deck
-  uint32_t grid = 0, mf = 0;
-#pragma unroll
-  for (int c = 0; c < SH::C; ++c) {
-    const uint32_t bits = (uint32_t)(gone >> (10 * c)) & 0x155u;
-    const int m = bits ? (__ffs(bits) - 1) >> 1 : 5;
-    mf |= (uint32_t)m << (3 * c);
-    grid |= ((1u << m) - 1) << (5 * c);
-  }
-  *mf_out = mf;
-  return grid;
-}
-
-// 25-bit grid (bit 5c+r) -> 2-bit-field positions (bit 10c+2r)
-__device__ __forceinline__ unsigned long long spread_grid(uint32_t grid) {
-  unsigned long long x = grid;
-  x = (x | (x << 16)) & 0x0000ffff0000ffffull;
-  x = (x | (x << 8)) & 0x00ff00ff00ff00ffull;
-  x = (x | (x << 4)) & 0x0f0f0f0f0f0f0f0full;
-  x = (x | (x << 2)) & 0x3333333333333333ull;
-  x = (x | (x << 1)) & 0x5555555555555555ull;
-  return x;
-}
-
-// sum of the 2-bit fields of x selected by sel (sel has bits at even positions)
-__device__ __forceinline__ int sum_fields(unsigned long long x, unsigned long long sel) {
-  return __popcll(x & sel) + 2 * __popcll((x >> 1) & sel);
-}
-
-// play_probably_safe_factory  ruleset.py:617-635 with get_card_playability :82-125.
-// playability = playable copies / plausible copies among the cards not visible to me; the
-// first-maximum (np.argmax) is taken by exact cross-multiplication, the threshold test is the
-// reference's float64 division.
-template <class SH>
-__device__ __forceinline__ int play_probably_safe(const Game<SH>& g, double threshold,
-                                                  bool require_extra_lives, const RuleSet& rs, int slot) {
-  const int n = g.hand_n(0);
-  if (n == 0) return -1;
-  // visible copies per card type: other hands + discards + fireworks  (:60-76)
-  unsigned long long vis = g.disc;
-#pragma unroll
-  for (int k = 1; k < SH::P; ++k)
-#pragma unroll
-    for (int i = 0; i < SH::H; ++i)
-      if (slot_valid(g.hand[k][i])) vis += 1ull << (2 * slot_card(g.hand[k][i]));
-#pragma unroll
-  for (int c = 0; c < SH::C; ++c)   // ranks below the stack height: one visible copy each
-    vis += (0x155ull & ((1ull << (2 * g.firework(c))) - 1)) << (10 * c);
-  const unsigned long long left = instances_packed<SH>() - vis;   // no borrows: visible <= instances
-  const unsigned long long pg_s = spread_grid(playable_grid(g));
-  int best = 0, bp = 0, bt = 1;
-#pragma unroll
-  for (int i = 0; i < SH::H; ++i) {
-    if (i < n) {
-      const unsigned long long gs = spread_grid(slot_grid(g.hand[0][i]));
-      const int total = sum_fields(left, gs);
-      const int playable = sum_fields(left, gs & pg_s);
-      // p_i/t_i > p_b/t_b  <=>  p_i*t_b > p_b*t_i   (t > 0); first maximum wins
-      if (i == 0 || playable * bt > bp * total) { bp = playable; bt = total; best = i; }
-    }
-  }
-  if (!require_extra_lives || g.life > 1)
-    if (ratio_at_least(rs, slot, bp, bt, threshold)) return uid_play<SH>(best);   // :105, :622
-  return -1;
+__device__ __forceinline__ uint32_t useful_grid(const Game<SH>& g) {
+  uint32_t p = ~((g.d0 ^ kInst0) | (g.d1 ^ kInst1)) & SH::kGridAll;   // count == copies in the deck
+  p |= (p << 1) & ~kLsb5;                                             // prefix-OR inside each colour
+  p |= (p << 2) & ~(kLsb5 | (kLsb5 << 1));
+  p |= (p << 1) & ~kLsb5;
+  return ~p & SH::kGridAll;
 }
 
 // grid of the cards that can no longer score: rank below the stack or at / beyond max_fireworks
 // (useless_card  ruleset.py:35-42)
 template <class SH>
 __device__ __forceinline__ uint32_t useless_grid(const Game<SH>& g) {
-  uint32_t mf;
-  const uint32_t useful = useful_grid(g, &mf);
-  uint32_t below = 0;
+  return (~useful_grid(g) | g.fw) & SH::kGridAll;
+}
+
+// copies of every card type that I cannot see (deck + my own hand), as two bit planes:
+// copies in the game - discards - other hands - cards on the stacks   (get_visible_cards :60-76)
+template <class SH>
+__device__ __forceinline__ void unseen_planes(const Game<SH>& g, uint32_t& l0, uint32_t& l1) {
+  uint32_t v0 = g.d0 ^ g.fw, v1 = g.d1 ^ (g.d0 & g.fw);      // one visible copy per rank below a stack
 #pragma unroll
-  for (int c = 0; c < SH::C; ++c) below |= ((1u << g.firework(c)) - 1) << (5 * c);
-  return (~useful | below) & SH::kGridAll;
+  for (int k = 1; k < SH::P; ++k)
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) {
+      const uint32_t oh = slot_onehot(g.hand[k][i]);
+      v1 ^= v0 & oh;
+      v0 ^= oh;
+    }
+  l0 = kInst0 ^ v0;                                          // copies - visible, no borrow out of a field
+  l1 = kInst1 ^ v1 ^ (~kInst0 & v0);
+}
+
+__device__ __forceinline__ int count_planes(uint32_t sel, uint32_t l0, uint32_t l1) {
+  return __popc(sel & l0) + 2 * __popc(sel & l1);
+}
+
+// What each rule would do, gates that depend on the rule's arguments left out.  A warp holds games
+// in every situation, so it walks (nearly) every rule every step anyway: the bodies are evaluated
+// once, side by side, as straight-line code that shares the board grids and the card one-hots,
+// and the rule list is resolved afterwards (rules_resolve).
+struct Cores {
+  int play_safe, play_certain, tell_playable, tell_dispensable, osawa, tell_unknown;
+  int best, bp, bt;     // play_probably_safe: first-maximum card, its playable / plausible copies
+};
+
+template <class SH>
+__device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int used, Cores& o) {
+  constexpr int C = SH::C, H = SH::H, P = SH::P;
+  const uint32_t pg = g.playable();
+  const uint32_t done = done_rows(g);
+  const uint32_t ltmin = below_all_grid(g);
+  const uint32_t useful = useful_grid(g);
+
+  o.play_safe = -1;                                    // :350-380: every plausible identity playable
+  if (used & (1u << R_PLAY_SAFE_CARD)) {
+#pragma unroll
+    for (int i = H - 1; i >= 0; --i) {
+      const uint32_t grid = slot_grid(g.hand[0][i]);
+      if (grid != 0 && (grid & ~pg) == 0) o.play_safe = uid_play<SH>(i);
+    }
+  }
+
+  o.play_certain = -1;                                 // :383-409
+  if (used & (1u << R_PLAY_IF_CERTAIN)) {
+#pragma unroll
+    for (int i = H - 1; i >= 0; --i) {
+      const uint32_t w = g.hand[0][i];
+      if ((w & (3u << 25)) == (3u << 25) && (slot_onehot(w) & pg) != 0) o.play_certain = uid_play<SH>(i);
+    }
+  }
+
+  // play_probably_safe_factory  ruleset.py:617-635 with get_card_playability :82-125.
+  // playability = playable copies / plausible copies among the cards not visible to me; the
+  // first-maximum (np.argmax) is taken by exact cross-multiplication.  An empty slot counts 0 / 0 and
+  // never beats the running maximum.
+  o.best = 0; o.bp = 0; o.bt = 1;
+  if (used & ((1u << R_PLAY_PROBABLY_SAFE) | (1u << R_HAIL_MARY))) {
+    uint32_t l0, l1;
+    unseen_planes(g, l0, l1);
+#pragma unroll
+    for (int i = 0; i < H; ++i) {
+      const uint32_t grid = slot_grid(g.hand[0][i]);
+      const int total = count_planes(grid, l0, l1);
+      const int playable = count_planes(grid & pg, l0, l1);
+      // p_i/t_i > p_b/t_b  <=>  p_i*t_b > p_b*t_i   (t > 0); first maximum wins
+      if (i == 0 || playable * o.bt > o.bp * total) { o.bp = playable; o.bt = total; o.best = i; }
+    }
+  }
+
+  o.osawa = -1;                                        // :220-280
+  if (used & (1u << R_OSAWA_DISCARD)) {
+    const bool last_done = (g.fw >> (5 * (C - 1) + 4)) & 1u;   // fireworks[-1] quirk  :229-230
+    const uint32_t dead = g.fw | ~useful;              // rank < stack, or rank >= max_fireworks
+    int first = -1, second = -1;
+#pragma unroll
+    for (int i = H - 1; i >= 0; --i) {
+      const uint32_t w = g.hand[0][i];
+      const uint32_t oh = slot_onehot(w);
+      const bool ch = slot_chint(w), rh = slot_rhint(w);
+      bool a = ch ? (oh & done) != 0 : last_done;
+      if (ch && rh) a = a || (oh & dead) != 0;
+      if (rh) a = a || (oh & ltmin) != 0;
+      if (oh != 0 && a) first = i;
+      if (oh != 0 && (slot_grid(w) & useful) == 0) second = i;   // no plausible identity is still useful
+    }
+    o.osawa = first >= 0 ? uid_discard<SH>(first) : (second >= 0 ? uid_discard<SH>(second) : -1);
+  }
+
+  o.tell_playable = -1;                                // tell_playable_card_outer :413-451
+  o.tell_dispensable = -1;                             // tell_dispensable_factory :454-514
+  o.tell_unknown = -1;                                 // :285-309 (next player, colour first)
+  const bool want_tp = used & ((1u << R_TELL_PLAYABLE_CARD_OUTER) | (1u << R_TELL_ANYONE_USEFUL_CARD));
+  const bool want_td = used & (1u << R_TELL_DISPENSABLE);
+  const bool want_tu = used & (1u << R_TELL_UNKNOWN);
+  if (want_tp || want_td || want_tu) {
+#pragma unroll
+    for (int k = P - 1; k >= 1; --k)                   // reverse order, last write = first match
+#pragma unroll
+      for (int i = H - 1; i >= 0; --i) {
+        const uint32_t w = g.hand[k][i];
+        const uint32_t oh = slot_onehot(w);
+        const int card = slot_card(w), c = card_color(card), r = card_rank(card);
+        const bool ch = slot_chint(w), rh = slot_rhint(w);
+        const int by_c = uid_color<SH>(k, c), by_r = uid_rank<SH>(k, r);
+        if (want_tp && (oh & pg) != 0) {
+          if (!rh) o.tell_playable = by_r;
+          else if (!ch) o.tell_playable = by_c;
+        }
+        if (want_td && oh != 0) {
+          const bool f5 = (oh & done) != 0, lt = (oh & ltmin) != 0, bl = (oh & g.fw) != 0;
+          if (!ch && f5) o.tell_dispensable = by_c;
+          else if (!rh && lt) o.tell_dispensable = by_r;
+          else if (bl && !ch && rh) o.tell_dispensable = by_c;
+          else if (bl && ch && !rh) o.tell_dispensable = by_r;
+        }
+        if (want_tu && k == 1 && oh != 0) {
+          if (!ch) o.tell_unknown = by_c;
+          else if (!rh) o.tell_unknown = by_r;
+        }
+      }
+  }
 }
 
 // discard_probably_useless_factory  ruleset.py:638-649 with get_probability_useless :127-170
@@ -191,48 +242,19 @@ __device__ __forceinline__ int discard_probably_useless(const Game<SH>& g, doubl
                                                         const RuleSet& rs, int slot) {
   const int n = g.hand_n(0);
   if (!(g.info < 8) || n == 0) return -1;
-  unsigned long long vis = g.disc;
-#pragma unroll
-  for (int k = 1; k < SH::P; ++k)
-#pragma unroll
-    for (int i = 0; i < SH::H; ++i)
-      if (slot_valid(g.hand[k][i])) vis += 1ull << (2 * slot_card(g.hand[k][i]));
-#pragma unroll
-  for (int c = 0; c < SH::C; ++c)
-    vis += (0x155ull & ((1ull << (2 * g.firework(c))) - 1)) << (10 * c);
-  const unsigned long long left = instances_packed<SH>() - vis;
-  const unsigned long long ug_s = spread_grid(useless_grid(g));
+  uint32_t l0, l1;
+  unseen_planes(g, l0, l1);
+  const uint32_t ug = useless_grid(g);
   int best = 0, bu = 0, bt = 1;
 #pragma unroll
   for (int i = 0; i < SH::H; ++i) {
-    if (i < n) {
-      const unsigned long long gs = spread_grid(slot_grid(g.hand[0][i]));
-      const int total = sum_fields(left, gs);
-      const int useless = sum_fields(left, gs & ug_s);
-      if (i == 0 || useless * bt > bu * total) { bu = useless; bt = total; best = i; }
-    }
+    const uint32_t grid = slot_grid(g.hand[0][i]);
+    const int total = count_planes(grid, l0, l1);
+    const int useless = count_planes(grid & ug, l0, l1);
+    if (i == 0 || useless * bt > bu * total) { bu = useless; bt = total; best = i; }
   }
   if (ratio_at_least(rs, slot, bu, bt, threshold)) return uid_discard<SH>(best);
   return -1;
-}
-
-// tell_playable_card_outer  ruleset.py:413-451
-template <class SH>
-__device__ __forceinline__ int tell_playable_outer(const Game<SH>& g) {
-  if (g.info <= 0) return -1;
-  int mv = -1;
-#pragma unroll
-  for (int k = SH::P - 1; k >= 1; --k)          // reverse order, last write = first match
-#pragma unroll
-    for (int i = SH::H - 1; i >= 0; --i) {
-      const uint32_t w = g.hand[k][i];
-      const int card = slot_card(w), c = card_color(card), r = card_rank(card);
-      if (slot_valid(w) && r == g.firework(c)) {
-        if (!slot_rhint(w)) mv = uid_rank<SH>(k, r);
-        else if (!slot_chint(w)) mv = uid_color<SH>(k, c);
-      }
-    }
-  return mv;
 }
 
 // The three rules that are dead in the reference (ids >= R_TELL_ANYONE_USELESS_CARD).  Kept out of
@@ -287,165 +309,104 @@ __device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double far
   }
 }
 
+// RulebasedAgent.get_move  rule_based.py:13-25: the first rule of the list that yields a move wins.
+// *hit = index of the rule that fired (rs.n = the legal_random fallback, stored by the host as
+// entry [n]).  The rule ids are warp-uniform (kernel argument), so the switch is a uniform branch.
 template <class SH, bool EXT = false>
-__device__ __forceinline__ int run_rule(const Game<SH>& g, const RuleSet& rs, int k,
-                                        unsigned long long game_id, unsigned long long step) {
-  constexpr int C = SH::C, R = SH::R, H = SH::H, P = SH::P;
-  const int rule = rs.id[k], iarg = rs.iarg[k], slot = rs.tslot[k];
-  const double farg = rs.farg[k];
+__device__ __forceinline__ int rules_resolve(const Game<SH>& g, const Cores& co, const RuleSet& rs,
+                                             unsigned long long game_id, unsigned long long step,
+                                             int* hit) {
+  constexpr int H = SH::H;
   const unsigned long long seed = rs.seed;
-  if constexpr (EXT) {
-    if (rule >= R_TELL_ANYONE_USELESS_CARD) return run_ext_rule(g, rule, farg, rs, slot, seed, game_id, step);
-  }
-  switch (rule) {
-    case R_DISCARD_OLDEST_FIRST:                       // ruleset.py:206-216
-      return g.info < 8 ? uid_discard<SH>(0) : -1;
-
-    case R_OSAWA_DISCARD: {                            // :220-280
-      if (g.info == 8) return -1;
-      uint32_t mf;
-      const uint32_t useful = useful_grid(g, &mf);
-      const int minfw = min_firework(g);
-      int first = -1, second = -1;
-#pragma unroll
-      for (int i = H - 1; i >= 0; --i) {
-        const uint32_t w = g.hand[0][i];
-        if (!slot_valid(w)) continue;
-        const int card = slot_card(w), hc = card_color(card), hr = card_rank(card);
-        const bool ch = slot_chint(w), rh = slot_rhint(w);
-        const int cidx = ch ? hc : C - 1;              // fireworks[-1] quirk  :229-230
-        bool a = g.firework(cidx) == 5;
-        if (ch && rh) a = a || hr < g.firework(hc) || hr >= (int)((mf >> (3 * hc)) & 7);
-        if (rh) a = a || hr < minfw;
-        if (a) first = i;
-        if ((slot_grid(w) & useful) == 0) second = i;  // no plausible identity is still useful
+  const int n0 = g.hand_n(0);
+  int a = -1, h = rs.n;
+#pragma unroll 1
+  for (int k = 0; k <= rs.n; ++k) {
+    const int rule = rs.id[k];
+    int r = -1;
+    if constexpr (EXT) {
+      if (rule >= R_TELL_ANYONE_USELESS_CARD) {
+        if (a < 0) r = run_ext_rule(g, rule, rs.farg[k], rs, rs.tslot[k], seed, game_id, step);
+        if (a < 0 && r >= 0) { a = r; h = k; }
+        continue;
       }
-      if (first >= 0) return uid_discard<SH>(first);
-      return second >= 0 ? uid_discard<SH>(second) : -1;
     }
-
-    case R_TELL_UNKNOWN: {                             // :285-309 (next player, colour first)
-      if (g.info <= 0) return -1;
-      int mv = -1;
+    switch (rule) {
+      case R_DISCARD_OLDEST_FIRST:                       // ruleset.py:206-216
+        r = g.info < 8 ? uid_discard<SH>(0) : -1;
+        break;
+      case R_OSAWA_DISCARD:
+        r = g.info == 8 ? -1 : co.osawa;
+        break;
+      case R_TELL_UNKNOWN:
+        r = g.info > 0 ? co.tell_unknown : -1;
+        break;
+      case R_PLAY_SAFE_CARD:
+        r = co.play_safe;
+        break;
+      case R_PLAY_IF_CERTAIN:
+        r = co.play_certain;
+        break;
+      case R_TELL_PLAYABLE_CARD_OUTER:                   // :413-451
+      case R_TELL_ANYONE_USEFUL_CARD:                    // :518-519
+        r = g.info > 0 ? co.tell_playable : -1;
+        break;
+      case R_TELL_DISPENSABLE:                           // iarg = min_information_tokens
+        r = (g.info < rs.iarg[k] && g.info > 0) ? co.tell_dispensable : -1;
+        break;
+      case R_PLAY_PROBABLY_SAFE:                         // :617-635; iarg = require_extra_lives
+        if (n0 > 0 && (rs.iarg[k] == 0 || g.life > 1) &&
+            ratio_at_least(rs, rs.tslot[k], co.bp, co.bt, rs.farg[k]))   // :105, :622
+          r = uid_play<SH>(co.best);
+        break;
+      case R_HAIL_MARY:                                  // :653-655 = play_probably_safe(0.0) when the
+        if (n0 > 0 && SH::DECK - g.deck_pos == 0 && g.life > 1)          // deck is empty and a life
+          r = uid_play<SH>(co.best);                                      // can be spared
+        break;
+      case R_TELL_RANDOMLY:                              // :314-347
+        if (a < 0 && g.info > 0 && g.hand_n(1) > 0) {
+          const int idx = rand_below(rule_rand(seed, game_id, step, 0), g.hand_n(1));
+          const int coin = rand_below(rule_rand(seed, game_id, step, 1), 2);
+          uint32_t w = 0;
 #pragma unroll
-      for (int i = H - 1; i >= 0; --i) {
-        const uint32_t w = g.hand[1][i];
-        const int card = slot_card(w);
-        if (slot_valid(w)) {
-          if (!slot_chint(w)) mv = uid_color<SH>(1, card_color(card));
-          else if (!slot_rhint(w)) mv = uid_rank<SH>(1, card_rank(card));
+          for (int i = 0; i < H; ++i)
+            if (i == idx) w = g.hand[1][i];
+          const int card = slot_card(w);
+          r = coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
         }
-      }
-      return mv;
-    }
-
-    case R_TELL_RANDOMLY: {                            // :314-347
-      if (g.info <= 0) return -1;
-      const int n = g.hand_n(1);
-      if (n == 0) return -1;
-      const int idx = rand_below(rule_rand(seed, game_id, step, 0), n);
-      const int coin = rand_below(rule_rand(seed, game_id, step, 1), 2);
-      uint32_t w = 0;
-#pragma unroll
-      for (int i = 0; i < H; ++i)
-        if (i == idx) w = g.hand[1][i];
-      const int card = slot_card(w);
-      return coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
-    }
-
-    case R_PLAY_SAFE_CARD: {                           // :350-380: every plausible identity playable
-      const uint32_t pg = playable_grid(g);
-      int mv = -1;
-#pragma unroll
-      for (int i = H - 1; i >= 0; --i) {
-        const uint32_t w = g.hand[0][i];
-        if (slot_valid(w) && (slot_grid(w) & ~pg) == 0) mv = uid_play<SH>(i);
-      }
-      return mv;
-    }
-
-    case R_PLAY_IF_CERTAIN: {                          // :383-409
-      int mv = -1;
-#pragma unroll
-      for (int i = H - 1; i >= 0; --i) {
-        const uint32_t w = g.hand[0][i];
-        const int card = slot_card(w);
-        if (slot_valid(w) && slot_chint(w) && slot_rhint(w) &&
-            card_rank(card) == g.firework(card_color(card)))
-          mv = uid_play<SH>(i);
-      }
-      return mv;
-    }
-
-    case R_TELL_PLAYABLE_CARD_OUTER:                   // :413-451
-    case R_TELL_ANYONE_USEFUL_CARD:                    // :518-519
-      return tell_playable_outer(g);
-
-    case R_TELL_DISPENSABLE: {                         // :454-514, iarg = min_information_tokens
-      if (!(g.info < iarg) || g.info <= 0) return -1;
-      const int minfw = min_firework(g);
-      int mv = -1;
-#pragma unroll
-      for (int k = P - 1; k >= 1; --k)
-#pragma unroll
-        for (int i = H - 1; i >= 0; --i) {
-          const uint32_t w = g.hand[k][i];
-          if (!slot_valid(w)) continue;
-          const int card = slot_card(w), c = card_color(card), r = card_rank(card);
-          const bool ch = slot_chint(w), rh = slot_rhint(w);
-          const int f = g.firework(c);
-          if (!ch && f == 5) mv = uid_color<SH>(k, c);
-          else if (!rh && r < minfw) mv = uid_rank<SH>(k, r);
-          else if (r < f && !ch && rh) mv = uid_color<SH>(k, c);
-          else if (r < f && ch && !rh) mv = uid_rank<SH>(k, r);
+        break;
+      case R_LEGAL_RANDOM:                               // :598-604 (intended semantics)
+        if (a < 0) {
+          unsigned long long m = legal_mask(g);
+          const int n = __popcll(m);
+          if (n > 0) {
+            int j = rand_below(rule_rand(seed, game_id, step, 2), n);
+            while (j-- > 0) m &= m - 1;
+            r = __ffsll((long long)m) - 1;
+          }
         }
-      return mv;
+        break;
+      case R_DISCARD_RANDOMLY:                           // :607-614 (intended semantics)
+        if (a < 0 && g.info < 8 && n0 > 0)
+          r = uid_discard<SH>(rand_below(rule_rand(seed, game_id, step, 3), n0));
+        break;
+      case R_TELL_MOST_INFORMATION:                      // :539-562 always None (:562)
+      default:
+        break;
     }
-
-    case R_PLAY_PROBABLY_SAFE:                         // :617-635
-    case R_HAIL_MARY: {                                // :653-655 = play_probably_safe(0.0) when the deck is
-      const bool hm = rule == R_HAIL_MARY;             // empty and a life can be spared; ONE inlined copy
-      if (hm && !(SH::DECK - g.deck_pos == 0 && g.life > 1)) return -1;
-      return play_probably_safe(g, hm ? 0.0 : farg, hm ? false : iarg != 0, rs, hm ? -1 : slot);
-    }
-
-    case R_LEGAL_RANDOM: {                             // :598-604 (intended semantics)
-      unsigned long long m = legal_mask(g);
-      const int n = __popcll(m);
-      if (n == 0) return -1;
-      int j = rand_below(rule_rand(seed, game_id, step, 2), n);
-      while (j-- > 0) m &= m - 1;
-      return __ffsll((long long)m) - 1;
-    }
-
-    case R_DISCARD_RANDOMLY: {                         // :607-614 (intended semantics)
-      const int n = g.hand_n(0);
-      if (!(g.info < 8) || n == 0) return -1;
-      return uid_discard<SH>(rand_below(rule_rand(seed, game_id, step, 3), n));
-    }
-
-    case R_TELL_MOST_INFORMATION:                      // :539-562 always None (:562)
-    default:
-      return -1;
+    if (a < 0 && r >= 0) { a = r; h = k; }
   }
+  *hit = h;
+  return a < 0 ? 0 : a;
 }
 
-// RulebasedAgent.get_move  rule_based.py:13-25.  *hit = index of the rule that fired
-// (rs.n = the legal_random fallback, stored by the host as entry [n]).
 template <class SH, bool EXT = false>
 __device__ __forceinline__ int rules_act(const Game<SH>& g, const RuleSet& rs,
                                          unsigned long long game_id, unsigned long long step,
                                          int* hit) {
-  int a = -1, h = rs.n;
-#pragma unroll 1
-  for (int k = 0; k <= rs.n; ++k) {
-    if (a < 0) {
-      const int r = run_rule<SH, EXT>(g, rs, k, game_id, step);
-      if (r >= 0) { a = r; h = k; }
-    }
-  }
-  *hit = h;
-  return a < 0 ? 0 : a;
+  Cores co;
+  rule_cores(g, rs.used, co);
+  return rules_resolve<SH, EXT>(g, co, rs, game_id, step, hit);
 }
 
 }  // namespace hbg

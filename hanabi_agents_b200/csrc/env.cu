@@ -25,6 +25,7 @@ struct hb_env {
 
 namespace {
 
+static_assert(hbg::kRuleBlock == 64, "rule tables are sized for 64-thread CTAs");
 constexpr int kThreads = 64;   // games per CTA: 65,536 games -> 1024 CTAs = 6.9 per SM (148 SMs)
 
 __device__ __forceinline__ long long game_index() {
@@ -140,13 +141,15 @@ __global__ void __launch_bounds__(kThreads)
 rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned long long step,
                  int32_t* __restrict__ action, int32_t* __restrict__ rule_hit,
                  unsigned long long* __restrict__ hist) {
+  __shared__ unsigned long long sthr[kThrSlots * kThrRows];
+  stage_thresholds(rs, sthr);
   const long long game = game_index();
   if (game >= rt.n_games) return;
   Game<SH> g;
   load_game(g, state, game);
   int a = 0, hit = -1;
   if (g.step_type != LAST)
-    a = rules_act<SH, EXT>(g, rs, (unsigned long long)(rt.game_id_base + game), step, &hit);
+    a = rules_act<SH, EXT>(g, rs, sthr, (unsigned long long)(rt.game_id_base + game), step, &hit);
   action[game] = a;
   if (rule_hit != nullptr) rule_hit[game] = hit;
   if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
@@ -165,6 +168,8 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
+  __shared__ unsigned long long sthr[kThrSlots * kThrRows];
+  stage_thresholds(rs, sthr);
   const long long game = game_index();
   if (game >= rt.n_games) return;
   const unsigned long long game_id = (unsigned long long)(rt.game_id_base + game);
@@ -198,7 +203,7 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
     if (t == n_steps) break;
 
     int a = 0, hit = -1;
-    if (g.step_type != LAST) a = rules_resolve<SH, EXT>(g, co, rs, game_id, step0 + t, &hit);
+    if (g.step_type != LAST) a = rules_resolve<SH, EXT>(g, co, rs, sthr, game_id, step0 + t, &hit);
     const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, next_card, lm, illegal);
     const long long arow = (long long)t * rt.n_games + game;
     if (action != nullptr) action[arow] = a;
@@ -378,22 +383,64 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
   rs.id[n] = R_LEGAL_RANDOM;   // Ruleset.legal_random fallback (rule_based.py:24)
   rs.farg[n] = 0.0;
   rs.iarg[n] = 0;
-  // comparison tables of the threshold rules: the reference's float64 division, done here once
-  int slots = 0;
+  // comparison tables of the threshold rules (the reference's float64 division, done here once) and
+  // the rows of rules_resolve
+  int slots = 0, td_rows = 0, td_max = -1;
+  rs.lazy = 0;
+  for (int s = 0; s < kThrSlots; ++s) rs.slot_extra[s] = 0;
+  for (int r = 0; r < 16; ++r) rs.key_hi[r] = kKeyAbsent;
+  rs.td_ilt[0] = rs.td_ilt[1] = 0;
+  auto own = [&](int row, int k) { if (rs.key_hi[row] == kKeyAbsent) rs.key_hi[row] = (unsigned int)k << 8; };
   for (int k = 0; k <= n; ++k) {
     rs.tslot[k] = -1;
-    const bool thr_rule = rs.id[k] == R_PLAY_PROBABLY_SAFE || rs.id[k] == R_DISCARD_PROBABLY_USELESS;
-    if (!thr_rule || slots >= kThrSlots) continue;
-    for (int t = 0; t < kThrRows; ++t) {
-      unsigned long long m = 0;
-      for (int p = 0; p < 64 && t > 0; ++p) {
-        volatile double q = (double)p / (double)t;    // rounded to double, no extended precision
-        if (q >= rs.farg[k]) m |= 1ull << p;
+    const int id = rs.id[k];
+    const bool thr_rule = id == R_PLAY_PROBABLY_SAFE || id == R_DISCARD_PROBABLY_USELESS;
+    if (thr_rule && slots < kThrSlots) {
+      for (int t = 0; t < kThrRows; ++t) {
+        unsigned long long m = 0;
+        for (int p = 0; p < 64 && t > 0; ++p) {
+          volatile double q = (double)p / (double)t;    // rounded to double, no extended precision
+          if (q >= rs.farg[k]) m |= 1ull << p;
+        }
+        rs.thr[slots][t] = m;
       }
-      rs.thr[slots][t] = m;
+      rs.tslot[k] = slots++;
     }
-    rs.tslot[k] = slots++;
+    switch (id) {
+      case R_DISCARD_OLDEST_FIRST: own(ROW_DISCARD_OLDEST, k); break;
+      case R_OSAWA_DISCARD: own(ROW_OSAWA, k); break;
+      case R_TELL_UNKNOWN: own(ROW_TELL_UNKNOWN, k); break;
+      case R_PLAY_SAFE_CARD: own(ROW_PLAY_SAFE, k); break;
+      case R_PLAY_IF_CERTAIN: own(ROW_PLAY_CERTAIN, k); break;
+      case R_TELL_PLAYABLE_CARD_OUTER:
+      case R_TELL_ANYONE_USEFUL_CARD: own(ROW_TELL_PLAYABLE, k); break;
+      case R_HAIL_MARY: own(ROW_HAIL_MARY, k); break;
+      case R_TELL_MOST_INFORMATION: break;               // never fires
+      case R_TELL_DISPENSABLE:
+        if (rs.iarg[k] <= td_max) break;                 // an earlier one fires whenever this would
+        if (td_rows < 2) {
+          rs.td_ilt[td_rows] = rs.iarg[k];
+          own(ROW_TELL_DISPENSABLE0 + td_rows, k);
+          ++td_rows;
+        } else {
+          rs.lazy |= 1u << k;
+        }
+        td_max = rs.iarg[k];
+        break;
+      case R_PLAY_PROBABLY_SAFE:
+        if (rs.tslot[k] >= 0 && rs.farg[k] > 0.0) {      // decided by the table alone
+          rs.slot_extra[rs.tslot[k]] = rs.iarg[k] != 0;
+          own(ROW_PPS0 + rs.tslot[k], k);
+        } else {
+          rs.lazy |= 1u << k;
+        }
+        break;
+      default:                                           // random rules, rules dead in the reference
+        rs.lazy |= 1u << k;
+        break;
+    }
   }
+  rs.n_slots = slots;
   return HB_OK;
 }
 

@@ -43,7 +43,26 @@ struct RuleSet {        // entry [n] is the legal_random fallback, filled by the
   // fused self-play kernel (profiles/r01_selfplay_history.md, v4).
   int tslot[kMaxRules + 1];       // -1: divide
   unsigned long long thr[kThrSlots][kThrRows];
+  // How rules_resolve finds the first rule that fires without walking the list: every rule whose
+  // verdict is a plain function of the state owns a ROW; key_hi[row] = (position in the list) << 8, or
+  // kKeyAbsent when the list does not hold it.  Entries of the `lazy` mask (random rules, rules that
+  // are dead in the reference, anything beyond the rows) are evaluated only when a game gets there.
+  unsigned int key_hi[16];
+  int td_ilt[2];                  // tell_dispensable rows: fires when info < td_ilt
+  unsigned int lazy;
+  int n_slots;                    // comparison tables in use
+  int slot_extra[kThrSlots];      // require_extra_lives of the rule that owns the table
 };
+
+enum RuleRow {
+  ROW_DISCARD_OLDEST = 0, ROW_OSAWA = 1, ROW_TELL_UNKNOWN = 2, ROW_PLAY_SAFE = 3, ROW_PLAY_CERTAIN = 4,
+  ROW_TELL_PLAYABLE = 5, ROW_TELL_DISPENSABLE0 = 6, ROW_TELL_DISPENSABLE1 = 7, ROW_HAIL_MARY = 8,
+  ROW_PPS0 = 9, ROW_NUM = ROW_PPS0 + kThrSlots
+};
+static_assert(ROW_NUM <= 16, "RuleSet::key_hi");
+constexpr unsigned int kKeyNone = 0x10000u;      // "no move" sorts after every position
+constexpr unsigned int kKeyAbsent = 0x40000u;
+constexpr int kRuleBlock = 64;    // threads per CTA of every kernel that resolves rule lists
 
 // numerator / denominator >= threshold, exactly as the reference's float64 division decides it
 __device__ __forceinline__ bool ratio_at_least(const RuleSet& rs, int slot, int num, int den,
@@ -200,6 +219,8 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
     o.osawa = first >= 0 ? uid_discard<SH>(first) : (second >= 0 ? uid_discard<SH>(second) : -1);
   }
 
+  // The three "tell" scans pick the FIRST card (seat, then slot order) that satisfies their test;
+  // each keeps the slot word of that card and the move is decoded once, after the scan.
   o.tell_playable = -1;                                // tell_playable_card_outer :413-451
   o.tell_dispensable = -1;                             // tell_dispensable_factory :454-514
   o.tell_unknown = -1;                                 // :285-309 (next player, colour first)
@@ -207,31 +228,42 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
   const bool want_td = used & (1u << R_TELL_DISPENSABLE);
   const bool want_tu = used & (1u << R_TELL_UNKNOWN);
   if (want_tp || want_td || want_tu) {
+    uint32_t tp_w = 0, td_w = 0, tu_w = 0;
+    int tp_k = 1, td_k = 1;
 #pragma unroll
     for (int k = P - 1; k >= 1; --k)                   // reverse order, last write = first match
 #pragma unroll
       for (int i = H - 1; i >= 0; --i) {
         const uint32_t w = g.hand[k][i];
         const uint32_t oh = slot_onehot(w);
-        const int card = slot_card(w), c = card_color(card), r = card_rank(card);
         const bool ch = slot_chint(w), rh = slot_rhint(w);
-        const int by_c = uid_color<SH>(k, c), by_r = uid_rank<SH>(k, r);
-        if (want_tp && (oh & pg) != 0) {
-          if (!rh) o.tell_playable = by_r;
-          else if (!ch) o.tell_playable = by_c;
-        }
-        if (want_td && oh != 0) {
+        if (want_tp && (oh & pg) != 0 && !(ch && rh)) { tp_w = w; tp_k = k; }
+        if (want_td) {
           const bool f5 = (oh & done) != 0, lt = (oh & ltmin) != 0, bl = (oh & g.fw) != 0;
-          if (!ch && f5) o.tell_dispensable = by_c;
-          else if (!rh && lt) o.tell_dispensable = by_r;
-          else if (bl && !ch && rh) o.tell_dispensable = by_c;
-          else if (bl && ch && !rh) o.tell_dispensable = by_r;
+          if ((!ch && f5) || (!rh && lt) || (bl && ch != rh)) { td_w = w; td_k = k; }
         }
-        if (want_tu && k == 1 && oh != 0) {
-          if (!ch) o.tell_unknown = by_c;
-          else if (!rh) o.tell_unknown = by_r;
-        }
+        if (want_tu && k == 1 && oh != 0 && !(ch && rh)) tu_w = w;
       }
+    if (tp_w != 0) {                                   // rank first, then colour
+      const int card = slot_card(tp_w);
+      o.tell_playable = !slot_rhint(tp_w) ? uid_rank<SH>(tp_k, card_rank(card))
+                                          : uid_color<SH>(tp_k, card_color(card));
+    }
+    if (td_w != 0) {
+      const uint32_t oh = slot_onehot(td_w);
+      const int card = slot_card(td_w), c = card_color(card), r = card_rank(card);
+      const bool ch = slot_chint(td_w), rh = slot_rhint(td_w);
+      const bool f5 = (oh & done) != 0, lt = (oh & ltmin) != 0;
+      // :470-510 in order: colour of a finished stack, rank below every stack, then whichever of
+      // colour / rank is still unknown of a card below its stack
+      const bool by_color = (!ch && f5) || (!(!rh && lt) && !ch);
+      o.tell_dispensable = by_color ? uid_color<SH>(td_k, c) : uid_rank<SH>(td_k, r);
+    }
+    if (tu_w != 0) {                                   // colour first, then rank
+      const int card = slot_card(tu_w);
+      o.tell_unknown = !slot_chint(tu_w) ? uid_color<SH>(1, card_color(card))
+                                         : uid_rank<SH>(1, card_rank(card));
+    }
   }
 }
 
@@ -309,104 +341,120 @@ __device__ __noinline__ int run_ext_rule(const Game<SH>& g, int rule, double far
   }
 }
 
-// RulebasedAgent.get_move  rule_based.py:13-25: the first rule of the list that yields a move wins.
-// *hit = index of the rule that fired (rs.n = the legal_random fallback, stored by the host as
-// entry [n]).  The rule ids are warp-uniform (kernel argument), so the switch is a uniform branch.
-template <class SH, bool EXT = false>
-__device__ __forceinline__ int rules_resolve(const Game<SH>& g, const Cores& co, const RuleSet& rs,
-                                             unsigned long long game_id, unsigned long long step,
-                                             int* hit) {
+// A rule that is evaluated only when a game reaches it without a move: the random rules (two 64-bit
+// hashes each), play_probably_safe without a comparison table, and the rules that are dead in the
+// reference.  Returns a move uid or -1.
+template <class SH, bool EXT>
+__device__ __forceinline__ int lazy_rule(const Game<SH>& g, const Cores& co, const RuleSet& rs, int k,
+                                         unsigned long long game_id, unsigned long long step) {
   constexpr int H = SH::H;
   const unsigned long long seed = rs.seed;
+  const int rule = rs.id[k];
   const int n0 = g.hand_n(0);
-  int a = -1, h = rs.n;
-#pragma unroll 1
-  for (int k = 0; k <= rs.n; ++k) {
-    const int rule = rs.id[k];
-    int r = -1;
-    if constexpr (EXT) {
-      if (rule >= R_TELL_ANYONE_USELESS_CARD) {
-        if (a < 0) r = run_ext_rule(g, rule, rs.farg[k], rs, rs.tslot[k], seed, game_id, step);
-        if (a < 0 && r >= 0) { a = r; h = k; }
-        continue;
-      }
-    }
-    switch (rule) {
-      case R_DISCARD_OLDEST_FIRST:                       // ruleset.py:206-216
-        r = g.info < 8 ? uid_discard<SH>(0) : -1;
-        break;
-      case R_OSAWA_DISCARD:
-        r = g.info == 8 ? -1 : co.osawa;
-        break;
-      case R_TELL_UNKNOWN:
-        r = g.info > 0 ? co.tell_unknown : -1;
-        break;
-      case R_PLAY_SAFE_CARD:
-        r = co.play_safe;
-        break;
-      case R_PLAY_IF_CERTAIN:
-        r = co.play_certain;
-        break;
-      case R_TELL_PLAYABLE_CARD_OUTER:                   // :413-451
-      case R_TELL_ANYONE_USEFUL_CARD:                    // :518-519
-        r = g.info > 0 ? co.tell_playable : -1;
-        break;
-      case R_TELL_DISPENSABLE:                           // iarg = min_information_tokens
-        r = (g.info < rs.iarg[k] && g.info > 0) ? co.tell_dispensable : -1;
-        break;
-      case R_PLAY_PROBABLY_SAFE:                         // :617-635; iarg = require_extra_lives
-        if (n0 > 0 && (rs.iarg[k] == 0 || g.life > 1) &&
-            ratio_at_least(rs, rs.tslot[k], co.bp, co.bt, rs.farg[k]))   // :105, :622
-          r = uid_play<SH>(co.best);
-        break;
-      case R_HAIL_MARY:                                  // :653-655 = play_probably_safe(0.0) when the
-        if (n0 > 0 && SH::DECK - g.deck_pos == 0 && g.life > 1)          // deck is empty and a life
-          r = uid_play<SH>(co.best);                                      // can be spared
-        break;
-      case R_TELL_RANDOMLY:                              // :314-347
-        if (a < 0 && g.info > 0 && g.hand_n(1) > 0) {
-          const int idx = rand_below(rule_rand(seed, game_id, step, 0), g.hand_n(1));
-          const int coin = rand_below(rule_rand(seed, game_id, step, 1), 2);
-          uint32_t w = 0;
-#pragma unroll
-          for (int i = 0; i < H; ++i)
-            if (i == idx) w = g.hand[1][i];
-          const int card = slot_card(w);
-          r = coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
-        }
-        break;
-      case R_LEGAL_RANDOM:                               // :598-604 (intended semantics)
-        if (a < 0) {
-          unsigned long long m = legal_mask(g);
-          const int n = __popcll(m);
-          if (n > 0) {
-            int j = rand_below(rule_rand(seed, game_id, step, 2), n);
-            while (j-- > 0) m &= m - 1;
-            r = __ffsll((long long)m) - 1;
-          }
-        }
-        break;
-      case R_DISCARD_RANDOMLY:                           // :607-614 (intended semantics)
-        if (a < 0 && g.info < 8 && n0 > 0)
-          r = uid_discard<SH>(rand_below(rule_rand(seed, game_id, step, 3), n0));
-        break;
-      case R_TELL_MOST_INFORMATION:                      // :539-562 always None (:562)
-      default:
-        break;
-    }
-    if (a < 0 && r >= 0) { a = r; h = k; }
+  if constexpr (EXT) {
+    if (rule >= R_TELL_ANYONE_USELESS_CARD)
+      return run_ext_rule(g, rule, rs.farg[k], rs, rs.tslot[k], seed, game_id, step);
   }
-  *hit = h;
-  return a < 0 ? 0 : a;
+  switch (rule) {
+    case R_TELL_RANDOMLY: {                            // :314-347
+      const int n1 = g.hand_n(1);
+      if (g.info <= 0 || n1 == 0) return -1;
+      const int idx = rand_below(rule_rand(seed, game_id, step, 0), n1);
+      const int coin = rand_below(rule_rand(seed, game_id, step, 1), 2);
+      uint32_t w = 0;
+#pragma unroll
+      for (int i = 0; i < H; ++i)
+        if (i == idx) w = g.hand[1][i];
+      const int card = slot_card(w);
+      return coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
+    }
+    case R_LEGAL_RANDOM: {                             // :598-604 (intended semantics)
+      unsigned long long m = legal_mask(g);
+      const int n = __popcll(m);
+      if (n == 0) return -1;
+      int j = rand_below(rule_rand(seed, game_id, step, 2), n);
+      while (j-- > 0) m &= m - 1;
+      return __ffsll((long long)m) - 1;
+    }
+    case R_DISCARD_RANDOMLY:                           // :607-614 (intended semantics)
+      if (!(g.info < 8) || n0 == 0) return -1;
+      return uid_discard<SH>(rand_below(rule_rand(seed, game_id, step, 3), n0));
+    case R_TELL_DISPENSABLE:                           // a third tell_dispensable of one list
+      return (g.info < rs.iarg[k] && g.info > 0) ? co.tell_dispensable : -1;
+    case R_PLAY_PROBABLY_SAFE:                         // more threshold rules than comparison tables
+      if (n0 > 0 && (rs.iarg[k] == 0 || g.life > 1) &&
+          ratio_at_least(rs, rs.tslot[k], co.bp, co.bt, rs.farg[k]))
+        return uid_play<SH>(co.best);
+      return -1;
+    default:
+      return -1;
+  }
+}
+
+// RulebasedAgent.get_move  rule_based.py:13-25: the first rule of the list that yields a move wins.
+// *hit = index of the rule that fired (rs.n = the legal_random fallback, stored by the host as
+// entry [n]).
+// No walk over the list: every row's verdict becomes the key (position << 8 | move), "no move" keys
+// sort last, and the winner is one chain of 3-input minima.  (A `switch (rule id)` per list entry was
+// 290 instructions per step and 30 % of the stall samples of the self-play kernel, a shared-memory
+// table of verdicts read back per entry still 250: profiles/r01_selfplay_history.md, v5.)
+template <class SH, bool EXT = false>
+__device__ __forceinline__ int rules_resolve(const Game<SH>& g, const Cores& co, const RuleSet& rs,
+                                             const unsigned long long* __restrict__ sthr,
+                                             unsigned long long game_id, unsigned long long step,
+                                             int* hit) {
+  const int n0 = g.hand_n(0);
+  const bool can_tell = g.info > 0, can_discard = g.info < 8;
+  const int play_best = n0 > 0 ? uid_play<SH>(co.best) : -1;
+  // -1 & 0x100ff = "no move"
+#define HB_KEY(row, gate, mv) ((((gate) ? (unsigned int)(mv) : ~0u) & (kKeyNone | 0xffu)) | rs.key_hi[row])
+  unsigned int best = kKeyNone;
+  best = min(best, HB_KEY(ROW_DISCARD_OLDEST, can_discard, 0));                       // ruleset.py:206-216
+  best = min(best, HB_KEY(ROW_OSAWA, g.info != 8, co.osawa));
+  best = min(best, HB_KEY(ROW_TELL_UNKNOWN, can_tell, co.tell_unknown));
+  best = min(best, HB_KEY(ROW_PLAY_SAFE, true, co.play_safe));
+  best = min(best, HB_KEY(ROW_PLAY_CERTAIN, true, co.play_certain));
+  best = min(best, HB_KEY(ROW_TELL_PLAYABLE, can_tell, co.tell_playable));            // :413-451, :518-519
+  best = min(best, HB_KEY(ROW_TELL_DISPENSABLE0, can_tell && g.info < rs.td_ilt[0], co.tell_dispensable));
+  best = min(best, HB_KEY(ROW_TELL_DISPENSABLE1, can_tell && g.info < rs.td_ilt[1], co.tell_dispensable));
+  // hail_mary :653-655 = play_probably_safe(0.0) when the deck is empty and a life can be spared
+  best = min(best, HB_KEY(ROW_HAIL_MARY, SH::DECK - g.deck_pos == 0 && g.life > 1, play_best));
+#pragma unroll 1
+  for (int s = 0; s < rs.n_slots; ++s) {                 // play_probably_safe :617-635 (:105, :622)
+    const int bt = co.bt < kThrRows ? co.bt : 0;         // row 0 of a table is empty
+    const bool ok = (rs.slot_extra[s] == 0 || g.life > 1) && ((sthr[s * kThrRows + bt] >> co.bp) & 1ull);
+    best = min(best, HB_KEY(ROW_PPS0 + s, ok, play_best));
+  }
+#undef HB_KEY
+  // the lazily evaluated entries, in list order: one matters only to a game that gets there
+  for (unsigned int lz = rs.lazy; lz != 0; lz &= lz - 1) {                            // uniform
+    const int k = __ffs((int)lz) - 1;
+    if ((unsigned int)(k << 8) < best) {
+      const int r = lazy_rule<SH, EXT>(g, co, rs, k, game_id, step);
+      if (r >= 0) best = (unsigned int)(k << 8) | (unsigned int)r;
+    }
+  }
+  const bool fired = best < kKeyNone;
+  *hit = fired ? (int)(best >> 8) : rs.n;
+  return fired ? (int)(best & 0xffu) : 0;
+}
+
+// The comparison tables, copied to shared memory by the whole CTA (the row read per game depends on
+// the game: an indexed read of the kernel-argument bank would replay per distinct row).  Every thread
+// of the CTA must call it; ends with a barrier.
+__device__ __forceinline__ void stage_thresholds(const RuleSet& rs, unsigned long long* sthr) {
+  for (int i = threadIdx.x; i < rs.n_slots * kThrRows; i += blockDim.x) sthr[i] = rs.thr[0][i];
+  __syncthreads();
 }
 
 template <class SH, bool EXT = false>
 __device__ __forceinline__ int rules_act(const Game<SH>& g, const RuleSet& rs,
+                                         const unsigned long long* __restrict__ sthr,
                                          unsigned long long game_id, unsigned long long step,
                                          int* hit) {
   Cores co;
   rule_cores(g, rs.used, co);
-  return rules_resolve<SH, EXT>(g, co, rs, game_id, step, hit);
+  return rules_resolve<SH, EXT>(g, co, rs, sthr, game_id, step, hit);
 }
 
 }  // namespace hbg

@@ -64,12 +64,18 @@ constexpr unsigned int kKeyNone = 0x10000u;      // "no move" sorts after every 
 constexpr unsigned int kKeyAbsent = 0x40000u;
 constexpr int kRuleBlock = 64;    // threads per CTA of every kernel that resolves rule lists
 
-// numerator / denominator >= threshold, exactly as the reference's float64 division decides it
+// numerator / denominator >= threshold, exactly as the reference's float64 division decides it.
+// The division is kept out of line: it is reached only by a rule list with more threshold rules than
+// comparison tables, and inlined its ~40 instructions were walked (predicated off) by every game that
+// evaluated a lazy rule.
+__device__ __noinline__ bool ratio_by_division(int num, int den, double threshold) {
+  return (double)num / (double)den >= threshold;
+}
 __device__ __forceinline__ bool ratio_at_least(const RuleSet& rs, int slot, int num, int den,
                                                double threshold) {
   if (threshold <= 0.0) return true;                       // num >= 0, den > 0
   if (slot >= 0 && den < kThrRows && num < 64) return (rs.thr[slot][den] >> num) & 1ull;
-  return (double)num / (double)den >= threshold;
+  return ratio_by_division(num, den, threshold);
 }
 
 __device__ __forceinline__ uint32_t rule_rand(unsigned long long seed, unsigned long long game,

@@ -152,7 +152,13 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
     a = rules_act<SH, EXT>(g, rs, sthr, (unsigned long long)(rt.game_id_base + game), step, &hit);
   action[game] = a;
   if (rule_hit != nullptr) rule_hit[game] = hit;
-  if (hist != nullptr && hit >= 0) atomicAdd(&hist[hit], 1ull);
+  // rule-hit histogram: one global atomic per (warp, rule that fired in it) -- one per game put
+  // 65,536 atomics on ten addresses and made this kernel 27 us (profiles/r01_launches_bench_v5.csv)
+  if (hist != nullptr) {
+    const unsigned int peers = __match_any_sync(__activemask(), hit);
+    if (hit >= 0 && (threadIdx.x & 31) == __ffs((int)peers) - 1)
+      atomicAdd(&hist[hit], (unsigned long long)__popc(peers));
+  }
 }
 
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state

@@ -468,25 +468,19 @@ def run_ours(args):
     # ---- e2e: same workload through the host-buffer API: actions come from pinned host memory
     # each step, observation / legal / reward / step type are read back to the host each step.
     e_steps = min(args.steps, args.e2e_steps)
-    a_host = torch.zeros(n, dtype=torch.int32).pin_memory()
-    blob_host = torch.empty(env.outputs_blob.numel(), dtype=torch.uint8).pin_memory()
-    o_host, l_host, r_host, s_host = env.split_outputs(blob_host)
-    side = torch.cuda.Stream()
-    stepped = torch.cuda.Event()
+    hb = env.host_buffers()                                       # pinned host arrays
+    hb["actions"].copy_(agent.explore(env).cpu())
+    torch.cuda.synchronize()
 
     def e2e_step():
-        main = torch.cuda.current_stream()
-        a_dev = a_host.to(dev, non_blocking=True)                 # H2D: this step's actions
-        env.step(a_dev)
-        stepped.record(main)
-        blob_host.copy_(env.outputs_blob, non_blocking=True)      # D2H: observation + mask + reward + type
-        with torch.cuda.stream(side):                             # meanwhile: the agent's next move ...
-            side.wait_event(stepped)
-            a_host.copy_(agent.explore(env), non_blocking=True)   # ... and its way back to the host
-        main.synchronize()
-        side.synchronize()
+        # observations = env.step(actions); actions = agent.explore(observations), host arrays both ways:
+        # a chunked pipeline over PCIe (include/hanabi_b200.h: hb_env_step_host_async)
+        env.step_host_async(hb["actions"], hb["obs"], hb["legal"], hb["reward"], hb["step_type"],
+                            chunks=args.e2e_chunks)
+        agent.explore_host_async(env, hb["next_actions"])
+        env.host_wait()
+        hb["actions"], hb["next_actions"] = hb["next_actions"], hb["actions"]
 
-    a_host.copy_(agent.explore(env))
     for _ in range(3):
         e2e_step()
     barrier()
@@ -500,7 +494,7 @@ def run_ours(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_val = world * n * e_steps / float(te.item())
     h2d = 4 * n
-    d2h = env.outputs_blob.numel() + 4 * n
+    d2h = n * (4 * env.obs_words + 4 * env.legal_words + 4 + 1) + 4 * n
 
     learner = acting = None
     if not args.no_learner:
@@ -556,8 +550,11 @@ def run_ours(args):
                    "decks": "numpy default_rng(%d) permutations, pool of %d" % (SEED, 4 * n)},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e_steps, "path": "per step: actions H2D from pinned memory, env.step (1 launch), one D2H of the "
-                "step outputs, agent.explore (1 launch, beside the copy) and its actions D2H; host in the loop"},
+                "steps": e_steps, "chunks": args.e2e_chunks,
+                "path": "per step, host in the loop, pinned host arrays both ways: env.step_host_async (per chunk: "
+                "actions H2D, env_step_kernel, D2H of observation rows (%d B) + legal mask + reward + step type) "
+                "| agent.explore_host_async (per chunk: rules_act_kernel + actions D2H on a third stream) | "
+                "env.host_wait" % (4 * env.obs_words)},
         "gpu_launches": launches,
         "roofline": roof,
         "cpu_baseline": cpu,
@@ -580,6 +577,7 @@ def main():
     ap.add_argument("--games", type=int, default=GAMES_PER_GPU)
     ap.add_argument("--fuse", type=int, default=64, help="env steps fused per launch")
     ap.add_argument("--e2e-steps", type=int, default=64)
+    ap.add_argument("--e2e-chunks", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--learner-steps", type=int, default=300)
     ap.add_argument("--act-steps", type=int, default=20)

@@ -61,6 +61,9 @@ SIGNATURES = {
     "hb_env_unpack_obs": (i32, [vp, vp, vp, i64, vp]),
     "hb_env_unpack_legal": (i32, [vp, vp, vp, i64, vp]),
     "hb_env_step_host": (i32, [vp, vp, vp, vp, vp, vp]),
+    "hb_env_step_host_async": (i32, [vp, vp, vp, vp, vp, vp, i32]),
+    "hb_rules_act_host_async": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp]),
+    "hb_env_host_wait": (i32, [vp]),
     # rule-based agents
     "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
     "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),

@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "hanabi_encode.cuh"
 #include "hanabi_rules.cuh"
+#include <algorithm>
 #include <new>
 #include <vector>
 
@@ -21,6 +22,12 @@ struct hb_env {
   // staging for *_host entry points
   void* stage = nullptr;
   size_t stage_bytes = 0;
+  // chunked host pipeline (hb_env_step_host_async / hb_rules_act_host_async / hb_env_host_wait)
+  static constexpr int kMaxChunks = 16;
+  cudaStream_t hs_step = nullptr, hs_out = nullptr, hs_act = nullptr;
+  cudaEvent_t hev_step[kMaxChunks] = {};
+  cudaEvent_t hev_done = nullptr;
+  int h_chunks = 0;
 };
 
 namespace {
@@ -33,12 +40,24 @@ __device__ __forceinline__ long long game_index() {
 }
 
 // Writes the step outputs of one game; returns the legal-move mask of the player to move.
+// `obs_stride` (words) is kObsStride (16-byte row stores) or kObsWords: rows without the alignment
+// padding, for consumers on the far side of PCIe (word stores).
 template <class SH>
 __device__ __forceinline__ unsigned long long emit(const Game<SH>& g, long long row,
                                                    uint32_t* __restrict__ obs,
                                                    uint32_t* __restrict__ legal,
-                                                   uint8_t* __restrict__ step_type) {
-  if (obs != nullptr) encode_obs(g, SH::P - 1, obs + row * SH::kObsStride);
+                                                   uint8_t* __restrict__ step_type,
+                                                   int obs_stride = SH::kObsStride) {
+  if (obs != nullptr) {
+    if (obs_stride == SH::kObsStride) {
+      encode_obs(g, SH::P - 1, obs + row * SH::kObsStride);
+    } else {
+      uint32_t w[SH::kObsStride];
+      encode_row(g, SH::P - 1, w);
+#pragma unroll
+      for (int i = 0; i < SH::kObsWords; ++i) obs[row * obs_stride + i] = w[i];
+    }
+  }
   const unsigned long long m = legal_mask(g);
   if (legal != nullptr) {
     legal[row * SH::kLegalWords] = (uint32_t)m;
@@ -101,9 +120,10 @@ __global__ void __launch_bounds__(kThreads)
 env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__ decks,
                 const int32_t* __restrict__ action, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
-                uint8_t* __restrict__ step_type, unsigned long long* illegal) {
-  const long long game = game_index();
-  if (game >= rt.n_games) return;
+                uint8_t* __restrict__ step_type, unsigned long long* illegal,
+                long long first, long long count, int obs_stride) {
+  const long long game = first + game_index();          // games [first, first + count) of this env
+  if (game >= first + count) return;
   Game<SH> g;
   load_game(g, state, game);
   unsigned long long row = deck_row<SH>(rt, game, g.episode);
@@ -111,7 +131,7 @@ env_step_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   const float r = step_game(g, rt, decks, deck, row, rt.row_step, action[game], peek_card(g, deck),
                             legal_mask(g), illegal);
   if (reward != nullptr) reward[game] = r;
-  emit(g, game, obs, legal, step_type);
+  emit(g, game, obs, legal, step_type, obs_stride);
   store_game(g, state, game);
 }
 
@@ -140,11 +160,11 @@ template <class SH, bool EXT>
 __global__ void __launch_bounds__(kThreads)
 rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned long long step,
                  int32_t* __restrict__ action, int32_t* __restrict__ rule_hit,
-                 unsigned long long* __restrict__ hist) {
+                 unsigned long long* __restrict__ hist, long long first, long long count) {
   __shared__ unsigned long long sthr[kThrSlots * kThrRows];
   stage_thresholds(rs, sthr);
-  const long long game = game_index();
-  if (game >= rt.n_games) return;
+  const long long game = first + game_index();
+  if (game >= first + count) return;
   Game<SH> g;
   load_game(g, state, game);
   int a = 0, hit = -1;
@@ -505,6 +525,12 @@ int hb_env_destroy(hb_env* e) {
   if (e->decks) cudaFree(e->decks);
   if (e->illegal) cudaFree(e->illegal);
   if (e->stage) cudaFree(e->stage);
+  if (e->hs_step) cudaStreamDestroy(e->hs_step);
+  if (e->hs_out) cudaStreamDestroy(e->hs_out);
+  if (e->hs_act) cudaStreamDestroy(e->hs_act);
+  for (int c = 0; c < hb_env::kMaxChunks; ++c)
+    if (e->hev_step[c]) cudaEventDestroy(e->hev_step[c]);
+  if (e->hev_done) cudaEventDestroy(e->hev_done);
   delete e;
   return HB_OK;
 }
@@ -592,7 +618,7 @@ int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d
   hb::DeviceGuard g(e->device);
   HB_DISPATCH(e, (env_step_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, e->decks, d_action, d_obs, d_legal, d_reward, d_step_type,
-                     e->illegal)));
+                     e->illegal, 0, e->rt.n_games, SH::kObsStride)));
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -663,11 +689,11 @@ int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, co
   if (uses_ext_rules(rs)) {
     HB_DISPATCH(e, (rules_act_kernel<SH, true><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                        e->rt, e->state, rs, step, d_action, d_rule_hit,
-                       (unsigned long long*)d_hist)));
+                       (unsigned long long*)d_hist, 0, e->rt.n_games)));
   } else {
     HB_DISPATCH(e, (rules_act_kernel<SH, false><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                        e->rt, e->state, rs, step, d_action, d_rule_hit,
-                       (unsigned long long*)d_hist)));
+                       (unsigned long long*)d_hist, 0, e->rt.n_games)));
   }
   HB_CUDA(cudaGetLastError());
   return HB_OK;
@@ -721,6 +747,145 @@ int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32
   if (h_reward) HB_CUDA(cudaMemcpyAsync(h_reward, d_rew, b_rew, cudaMemcpyDeviceToHost, nullptr));
   if (h_step_type) HB_CUDA(cudaMemcpyAsync(h_step_type, d_st, n, cudaMemcpyDeviceToHost, nullptr));
   HB_CUDA(cudaStreamSynchronize(nullptr));
+  return HB_OK;
+}
+
+
+// ---- chunked host pipeline ---------------------------------------------------------------------
+// The reference's loop is `observations = env.step(actions); actions = agent.explore(observations)`
+// with numpy arrays (run_experiment.py:293-308).  With HOST buffers that loop is bound by PCIe: 93 bytes
+// of outputs per game and step.  The three calls below keep the link busy: the games are cut into
+// chunks; chunk c's actions go up, its step kernel runs, and while its outputs travel down chunk c+1 is
+// already stepping and the agent is choosing chunk c's next move on a third stream.  Observation rows
+// are written without the 16-byte alignment padding (obs_words = ceil(obs_len / 32) words per game).
+// All host pointers should be pinned (cudaHostAlloc / torch pin_memory) -- pageable memory works but the
+// copies then serialise.
+
+namespace {
+struct StagePlan {
+  int32_t* act; uint32_t* obs; uint32_t* leg; float* rew; uint8_t* st; int32_t* act_out;
+};
+int host_pipe_init(hb_env* e, int obs_words, StagePlan* p) {
+  if (!e->hs_step) {
+    HB_CUDA(cudaStreamCreateWithFlags(&e->hs_step, cudaStreamNonBlocking));
+    HB_CUDA(cudaStreamCreateWithFlags(&e->hs_out, cudaStreamNonBlocking));
+    HB_CUDA(cudaStreamCreateWithFlags(&e->hs_act, cudaStreamNonBlocking));
+    for (int c = 0; c < hb_env::kMaxChunks; ++c)
+      HB_CUDA(cudaEventCreateWithFlags(&e->hev_step[c], cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&e->hev_done, cudaEventDisableTiming));
+  }
+  const size_t n = (size_t)e->rt.n_games;
+  auto up = [](size_t b) { return (b + 255) / 256 * 256; };
+  // the four outputs sit back to back (all but the last are whole words), so that host arrays laid
+  // out the same way -- HanabiParallelEnv.host_buffers -- are filled by ONE copy per chunk
+  const size_t b_act = up(n * 4), b_obs = n * obs_words * 4, b_leg = n * e->legal_words * 4,
+               b_rew = n * 4, b_st = up(n);
+  int rc = env_stage(e, 2 * b_act + b_obs + b_leg + b_rew + b_st);
+  if (rc) return rc;
+  char* q = (char*)e->stage;
+  p->act = (int32_t*)q; q += b_act;
+  p->obs = (uint32_t*)q; q += b_obs;
+  p->leg = (uint32_t*)q; q += b_leg;
+  p->rew = (float*)q; q += b_rew;
+  p->st = (uint8_t*)q; q += b_st;
+  p->act_out = (int32_t*)q;
+  return HB_OK;
+}
+inline long long chunk_games(const hb_env* e, int chunks) {
+  const long long per = (e->rt.n_games + chunks - 1) / chunks;
+  return (per + kThreads - 1) / kThreads * kThreads;
+}
+}  // namespace
+
+int hb_env_step_host_async(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
+                           float* h_reward, uint8_t* h_step_type, int chunks) {
+  HB_REQUIRE(e && h_action && chunks >= 1 && chunks <= hb_env::kMaxChunks,
+             "hb_env_step_host_async: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_env_step_host_async: reset the environment first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  const int obs_words = (e->obs_len + 31) / 32;
+  StagePlan p;
+  int rc = host_pipe_init(e, obs_words, &p);
+  if (rc) return rc;
+  // what the previous pipeline pass still reads or writes must be done before the staging is reused
+  HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_done, 0));
+  const long long n = e->rt.n_games, per = chunk_games(e, chunks);
+  int used = 0;
+  for (long long first = 0; first < n; first += per, ++used) {
+    const long long cnt = std::min(per, n - first);
+    const unsigned grid = (unsigned)((cnt + kThreads - 1) / kThreads);
+    HB_CUDA(cudaMemcpyAsync(p.act + first, h_action + first, (size_t)cnt * 4, cudaMemcpyHostToDevice, e->hs_step));
+    HB_DISPATCH(e, (env_step_kernel<SH><<<grid, kThreads, 0, e->hs_step>>>(
+                       e->rt, e->state, e->decks, p.act, h_obs ? p.obs : nullptr, h_legal ? p.leg : nullptr,
+                       h_reward ? p.rew : nullptr, h_step_type ? p.st : nullptr, e->illegal, first, cnt,
+                       obs_words)));
+    HB_CUDA(cudaGetLastError());
+    HB_CUDA(cudaEventRecord(e->hev_step[used], e->hs_step));
+    HB_CUDA(cudaStreamWaitEvent(e->hs_out, e->hev_step[used], 0));
+    const bool whole = cnt == n && h_obs && h_legal && h_reward && h_step_type &&
+                       (char*)h_legal == (char*)h_obs + (size_t)n * obs_words * 4 &&
+                       (char*)h_reward == (char*)h_legal + (size_t)n * e->legal_words * 4 &&
+                       (char*)h_step_type == (char*)h_reward + (size_t)n * 4;
+    if (whole) {     // one chunk into back-to-back host arrays: a single copy (each copy costs ~5 us)
+      HB_CUDA(cudaMemcpyAsync(h_obs, p.obs, (size_t)n * (obs_words * 4 + e->legal_words * 4 + 4 + 1),
+                              cudaMemcpyDeviceToHost, e->hs_out));
+      continue;
+    }
+    if (h_obs)
+      HB_CUDA(cudaMemcpyAsync(h_obs + first * obs_words, p.obs + first * obs_words, (size_t)cnt * obs_words * 4,
+                              cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_legal)
+      HB_CUDA(cudaMemcpyAsync(h_legal + first * e->legal_words, p.leg + first * e->legal_words,
+                              (size_t)cnt * e->legal_words * 4, cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_reward)
+      HB_CUDA(cudaMemcpyAsync(h_reward + first, p.rew + first, (size_t)cnt * 4, cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_step_type)
+      HB_CUDA(cudaMemcpyAsync(h_step_type + first, p.st + first, (size_t)cnt, cudaMemcpyDeviceToHost, e->hs_out));
+  }
+  e->h_chunks = used;
+  return HB_OK;
+}
+
+int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
+                            const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
+                            int32_t* h_action, uint64_t* d_hist) {
+  HB_REQUIRE(e && h_action, "hb_rules_act_host_async: bad arguments");
+  HB_REQUIRE(e->h_chunks >= 1, "hb_rules_act_host_async: call hb_env_step_host_async first");
+  RuleSet rs;
+  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  if (rc) return rc;
+  hb::DeviceGuard g(e->device);
+  StagePlan p;
+  rc = host_pipe_init(e, (e->obs_len + 31) / 32, &p);
+  if (rc) return rc;
+  const bool ext = uses_ext_rules(rs);
+  const long long n = e->rt.n_games, per = chunk_games(e, e->h_chunks);
+  int c = 0;
+  for (long long first = 0; first < n; first += per, ++c) {
+    const long long cnt = std::min(per, n - first);
+    const unsigned grid = (unsigned)((cnt + kThreads - 1) / kThreads);
+    HB_CUDA(cudaStreamWaitEvent(e->hs_act, e->hev_step[c], 0));
+    if (ext) {
+      HB_DISPATCH(e, (rules_act_kernel<SH, true><<<grid, kThreads, 0, e->hs_act>>>(
+                         e->rt, e->state, rs, step, p.act_out, nullptr, (unsigned long long*)d_hist, first, cnt)));
+    } else {
+      HB_DISPATCH(e, (rules_act_kernel<SH, false><<<grid, kThreads, 0, e->hs_act>>>(
+                         e->rt, e->state, rs, step, p.act_out, nullptr, (unsigned long long*)d_hist, first, cnt)));
+    }
+    HB_CUDA(cudaGetLastError());
+    HB_CUDA(cudaMemcpyAsync(h_action + first, p.act_out + first, (size_t)cnt * 4, cudaMemcpyDeviceToHost, e->hs_act));
+  }
+  return HB_OK;
+}
+
+int hb_env_host_wait(hb_env* e) {
+  HB_REQUIRE(e, "hb_env_host_wait: NULL env");
+  if (!e->hs_step) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  HB_CUDA(cudaStreamSynchronize(e->hs_step));
+  HB_CUDA(cudaStreamSynchronize(e->hs_out));
+  HB_CUDA(cudaStreamSynchronize(e->hs_act));
+  HB_CUDA(cudaEventRecord(e->hev_done, e->hs_act));
   return HB_OK;
 }
 

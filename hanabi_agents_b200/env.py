@@ -155,6 +155,41 @@ class HanabiParallelEnv:
                                                step_type.ctypes.data))
         return obs, legal, reward, step_type
 
+    # ---- chunked host pipeline (pinned host buffers; see include/hanabi_b200.h) ----------------
+    @property
+    def obs_words(self):
+        """Words per observation row without the alignment padding: ceil(obs_len / 32)."""
+        return (self.obs_len + 31) // 32
+
+    def host_buffers(self):
+        """Pinned host arrays for `step_host_async`: dict of torch CPU tensors
+        actions int32[N], obs int32[N, obs_words], legal int32[N, legal_words], reward f32[N],
+        step_type u8[N], next_actions int32[N]."""
+        torch = self.torch
+        n = self.n
+        # the four outputs are views of ONE pinned allocation, back to back: with chunks=1 the step's
+        # outputs then come down in a single copy
+        sizes = [n * self.obs_words * 4, n * self.legal_words * 4, n * 4, n]
+        blob = torch.zeros(sum(sizes), dtype=torch.uint8).pin_memory()
+        o = [0, sizes[0], sizes[0] + sizes[1], sizes[0] + sizes[1] + sizes[2]]
+        mk = lambda shape, dt: torch.zeros(shape, dtype=dt).pin_memory()
+        return {"actions": mk((n,), torch.int32),
+                "obs": blob[o[0]:o[1]].view(torch.int32).view(n, self.obs_words),
+                "legal": blob[o[1]:o[2]].view(torch.int32).view(n, self.legal_words),
+                "reward": blob[o[2]:o[3]].view(torch.float32),
+                "step_type": blob[o[3]:],
+                "next_actions": mk((n,), torch.int32), "outputs_blob": blob}
+
+    def step_host_async(self, actions, obs=None, legal=None, reward=None, step_type=None, chunks=1):
+        """`environment.step(actions)` with HOST arrays (torch CPU tensors, pinned for overlap), enqueued
+        as a chunked pipeline; the arrays are valid after `host_wait()`."""
+        p = lambda t: None if t is None else t.data_ptr()
+        _lib.check(_lib.lib().hb_env_step_host_async(self._h, actions.data_ptr(), p(obs), p(legal),
+                                                     p(reward), p(step_type), int(chunks)))
+
+    def host_wait(self):
+        _lib.check(_lib.lib().hb_env_host_wait(self._h))
+
     def observe(self, offset=0, out=None):
         """HanabiObservation of the player `offset` seats after the mover, for every game
         (bit-packed rows + legal masks; `out` = (obs, legal) reuses caller-owned buffers)."""

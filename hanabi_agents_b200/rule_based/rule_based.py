@@ -50,6 +50,16 @@ class RulebasedAgent:
         self._step += 1
         return self._actions
 
+    def explore_host_async(self, env, out):
+        """explore() for a host-side loop: the moves of every game land in `out` (pinned int32[N] torch
+        CPU tensor) chunk by chunk behind `env.step_host_async`; valid after `env.host_wait()`."""
+        self._buffers(env)
+        _lib.check(_lib.lib().hb_rules_act_host_async(
+            env._h, self._ids.ctypes.data, self._farg.ctypes.data, self._iarg.ctypes.data,
+            len(self.rules), self.seed, self._step, out.data_ptr(), self._hist.data_ptr()))
+        self._step += 1
+        return out
+
     def exploit(self, observations):  # rule_based.py:33-34
         return self.explore(observations)
 

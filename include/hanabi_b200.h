@@ -140,6 +140,19 @@ int hb_env_unpack_legal(hb_env* e, const uint32_t* d_legal, int8_t* d_out, int64
 /* Host-buffer step (copies inside, synchronises): the call a numpy binding makes. */
 int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
                      float* h_reward, uint8_t* h_step_type);
+/* The same loop the reference drives with numpy arrays -- observations = env.step(actions);
+ * actions = agent.explore(observations) (hanabi_agents/rainbow/run_experiment.py:293-308) -- as a
+ * chunked pipeline over PCIe: the games are cut into `chunks` (1..16) pieces; piece c's actions go up
+ * and it steps while piece c-1's outputs travel down and the agent picks piece c-1's next move.
+ * hb_env_step_host_async and hb_rules_act_host_async only enqueue; hb_env_host_wait returns when every
+ * host buffer is filled.  Host buffers should be pinned.  h_obs rows are ceil(obs_len / 32) words
+ * (no alignment padding); any output pointer may be NULL. */
+int hb_env_step_host_async(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
+                           float* h_reward, uint8_t* h_step_type, int chunks);
+int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
+                            const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
+                            int32_t* h_action, uint64_t* d_hist);
+int hb_env_host_wait(hb_env* e);
 
 /* ------------------------------------------------------------------------ */
 /* Rule-based agents.  Replaces RulebasedAgent.explore/exploit/get_move        */

@@ -195,7 +195,9 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
   __shared__ unsigned long long sthr[kThrSlots * kThrRows];
-  stage_thresholds(rs, sthr);
+  __shared__ EncTables tabs;
+  stage_enc_tables<SH>(tabs);
+  stage_thresholds(rs, sthr);                                   // ends with the barrier
   const long long game = game_index();
   if (game >= rt.n_games) return;
   const unsigned long long game_id = (unsigned long long)(rt.game_id_base + game);
@@ -213,7 +215,7 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
     const unsigned long long lm = legal_mask(g);
     {
       uint32_t orow_w[SH::kObsStride];
-      encode_row(g, SH::P - 1, orow_w);
+      encode_row(g, SH::P - 1, orow_w, &tabs);
       uint32_t* dst = obs + orow * SH::kObsStride;
 #pragma unroll
       for (int i = 0; i < SH::kObsStride / 4; ++i)

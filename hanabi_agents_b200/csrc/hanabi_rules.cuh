@@ -78,14 +78,26 @@ __device__ __forceinline__ bool ratio_at_least(const RuleSet& rs, int slot, int 
   return ratio_by_division(num, den, threshold);
 }
 
-__device__ __forceinline__ uint32_t rule_rand(unsigned long long seed, unsigned long long game,
-                                              unsigned long long step, uint32_t k) {
+// Counter-based uniform stream keyed (seed, game id, step, draw): a 64-bit key per (seed, game) -- loop
+// invariant in the fused kernel -- then a 32-bit multiply-xorshift hash per (step, draw).  ptxas evaluates
+// every draw of the "lazy" rules ahead of the branches for all games; as 64-bit splitmix hashes those
+// were 143 of 1192 warp-instructions per step (profiles/r01_selfplay_history.md, v6).
+// (The CPU restatement used by the tests defines the same stream.)
+__device__ __forceinline__ unsigned long long rule_key(unsigned long long seed, unsigned long long game) {
   unsigned long long x = seed + 0x9E3779B97F4A7C15ull * (game + 1);
-  x ^= step * 0xBF58476D1CE4E5B9ull + (unsigned long long)(k + 1) * 0x94D049BB133111EBull;
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
   x ^= x >> 27; x *= 0x94D049BB133111EBull;
   x ^= x >> 31;
-  return (uint32_t)(x >> 32);
+  return x;
+}
+__device__ __forceinline__ uint32_t rule_rand(unsigned long long seed, unsigned long long game,
+                                              unsigned long long step, uint32_t k) {
+  const unsigned long long key = rule_key(seed, game);
+  uint32_t h = (uint32_t)key + (uint32_t)step * 0x9E3779B1u + (k + 1) * 0x85EBCA6Bu;
+  h ^= h >> 16; h *= 0x7FEB352Du;
+  h ^= h >> 15; h ^= (uint32_t)(key >> 32); h *= 0x846CA68Bu;
+  h ^= h >> 16;
+  return h;
 }
 __device__ __forceinline__ int rand_below(uint32_t r, int n) {
   return (int)(((unsigned long long)r * (unsigned long long)n) >> 32);

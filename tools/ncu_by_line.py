@@ -64,6 +64,12 @@ def main():
         agg[key][1] += ex
         tot_s += smp
         tot_i += ex
+    dump = os.environ.get("HB_DUMP_LINE")          # "file:line": list that line's SASS with counts
+    if dump:
+        df, dl = dump.split(":")
+        for addr, src, smp, ex in insts:
+            if lines.get(addr - base, ("?", 0)) == (df, int(dl)):
+                print("    %5x  ex %9d  smp %4d  %s" % (addr - base, ex, smp, src))
     print("total samples %d, warp instructions %d, sass instructions %d" % (tot_s, tot_i, len(insts)))
     byfile = collections.defaultdict(lambda: [0, 0])
     for (f, l), (s, e) in agg.items():

@@ -182,13 +182,18 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
   const uint32_t ltmin = below_all_grid(g);
   const uint32_t useful = useful_grid(g);
 
+  // Empty slots are the LAST slots of a hand (cards shift down, the deck refills the end) and every scan
+  // below keeps the lowest matching index, so the tests may ignore whether a slot holds a card: a match
+  // at an index >= the hand size means that no real card matched.
+  const int n0 = g.hand_n(0);
+
   o.play_safe = -1;                                    // :350-380: every plausible identity playable
   if (used & (1u << R_PLAY_SAFE_CARD)) {
+    int idx = H;
 #pragma unroll
-    for (int i = H - 1; i >= 0; --i) {
-      const uint32_t grid = slot_grid(g.hand[0][i]);
-      if (grid != 0 && (grid & ~pg) == 0) o.play_safe = uid_play<SH>(i);
-    }
+    for (int i = H - 1; i >= 0; --i)
+      if ((slot_grid(g.hand[0][i]) & ~pg) == 0) idx = i;
+    if (idx < n0) o.play_safe = uid_play<SH>(idx);
   }
 
   o.play_certain = -1;                                 // :383-409
@@ -220,21 +225,23 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
 
   o.osawa = -1;                                        // :220-280
   if (used & (1u << R_OSAWA_DISCARD)) {
-    const bool last_done = (g.fw >> (5 * (C - 1) + 4)) & 1u;   // fireworks[-1] quirk  :229-230
-    const uint32_t dead = g.fw | ~useful;              // rank < stack, or rank >= max_fireworks
-    int first = -1, second = -1;
+    // Per card: colour hinted -> its stack is finished; NOT hinted -> fireworks[-1] is finished (quirk
+    // :229-230); both hinted -> rank below its stack or at / beyond max_fireworks; rank hinted -> rank
+    // below every stack.  The four hint states pick one of four grids the card's one-hot is tested against.
+    const uint32_t all = ((g.fw >> (5 * (C - 1) + 4)) & 1u) ? SH::kGridAll : 0u;
+    const uint32_t g1 = done, g2 = ltmin | all, g3 = done | ltmin | ((g.fw | ~useful) & SH::kGridAll);
+    int first = H, second = H;
 #pragma unroll
     for (int i = H - 1; i >= 0; --i) {
       const uint32_t w = g.hand[0][i];
-      const uint32_t oh = slot_onehot(w);
-      const bool ch = slot_chint(w), rh = slot_rhint(w);
-      bool a = ch ? (oh & done) != 0 : last_done;
-      if (ch && rh) a = a || (oh & dead) != 0;
-      if (rh) a = a || (oh & ltmin) != 0;
-      if (oh != 0 && a) first = i;
-      if (oh != 0 && (slot_grid(w) & useful) == 0) second = i;   // no plausible identity is still useful
+      const bool ch = (w & (1u << 25)) != 0, rh = (w & (1u << 26)) != 0;
+      const uint32_t sel = rh ? (ch ? g3 : g2) : (ch ? g1 : all);
+      if ((slot_onehot(w) & sel) != 0) first = i;      // an empty slot has no one-hot
+      if ((slot_grid(w) & useful) == 0) second = i;    // no plausible identity is still useful
     }
-    o.osawa = first >= 0 ? uid_discard<SH>(first) : (second >= 0 ? uid_discard<SH>(second) : -1);
+    if (second >= n0) second = H;
+    const int pick = first < H ? first : second;
+    if (pick < H) o.osawa = uid_discard<SH>(pick);
   }
 
   // The three "tell" scans pick the FIRST card (seat, then slot order) that satisfies their test;
@@ -248,19 +255,20 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
   if (want_tp || want_td || want_tu) {
     uint32_t tp_w = 0, td_w = 0, tu_w = 0;
     int tp_k = 1, td_k = 1;
+    // tell_dispensable by hint state: nothing hinted -> finished colour or rank below every stack; colour
+    // hinted -> rank below every stack, or below its own stack; rank hinted -> finished colour, or below its
+    // own stack.  A fully hinted card is told nothing by any of the three rules: its one-hot is dropped.
+    const uint32_t t0 = done | ltmin, t1 = ltmin | g.fw, t2 = done | g.fw;
 #pragma unroll
     for (int k = P - 1; k >= 1; --k)                   // reverse order, last write = first match
 #pragma unroll
       for (int i = H - 1; i >= 0; --i) {
         const uint32_t w = g.hand[k][i];
-        const uint32_t oh = slot_onehot(w);
-        const bool ch = slot_chint(w), rh = slot_rhint(w);
-        if (want_tp && (oh & pg) != 0 && !(ch && rh)) { tp_w = w; tp_k = k; }
-        if (want_td) {
-          const bool f5 = (oh & done) != 0, lt = (oh & ltmin) != 0, bl = (oh & g.fw) != 0;
-          if ((!ch && f5) || (!rh && lt) || (bl && ch != rh)) { td_w = w; td_k = k; }
-        }
-        if (want_tu && k == 1 && oh != 0 && !(ch && rh)) tu_w = w;
+        const bool ch = (w & (1u << 25)) != 0, rh = (w & (1u << 26)) != 0;
+        const uint32_t oh = (ch && rh) ? 0u : slot_onehot(w);
+        if (want_tp && (oh & pg) != 0) { tp_w = w; tp_k = k; }
+        if (want_td && (oh & (ch ? t1 : (rh ? t2 : t0))) != 0) { td_w = w; td_k = k; }
+        if (want_tu && k == 1 && oh != 0) tu_w = w;
       }
     if (tp_w != 0) {                                   // rank first, then colour
       const int card = slot_card(tp_w);

@@ -91,7 +91,8 @@ template <class SH>
 __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint8_t* decks,
                                            const uint8_t*& deck, unsigned long long& row,
                                            unsigned long long row_step, int action, uint32_t next_card,
-                                           unsigned long long lm, unsigned long long* illegal) {
+                                           unsigned long long lm, unsigned long long* illegal,
+                                           const MoveTable* mt = nullptr) {
   if (g.step_type == LAST) {
     ++g.episode;
     row += row_step;
@@ -100,11 +101,14 @@ __device__ __forceinline__ float step_game(Game<SH>& g, const Rt& rt, const uint
     reset_game(g, deck);
     return 0.0f;
   }
-  if (action < 0 || action >= SH::A || !((lm >> action) & 1ull)) {   // lm: legal moves of g
+  bool legal_action;                                               // lm: legal moves of g
+  if constexpr (SH::A <= 32) legal_action = (unsigned)action < (unsigned)SH::A && (((uint32_t)lm >> action) & 1u);
+  else legal_action = (unsigned)action < (unsigned)SH::A && ((lm >> action) & 1ull);
+  if (!legal_action) {
     atomicAdd(illegal, 1ull);   // HLE REQUIREs legality; we count and leave the game as it is
     return 0.0f;
   }
-  const int r = apply_move(g, action, next_card);
+  const int r = apply_move(g, action, next_card, mt);
   g.step_type = g.terminal() ? LAST : MID;
   return (float)r;
 }
@@ -196,17 +200,22 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 unsigned long long* __restrict__ hist, unsigned long long* illegal) {
   __shared__ unsigned long long sthr[kThrSlots * kThrRows];
   __shared__ EncTables tabs;
+  // rule-hit histogram: per-CTA counters in shared memory (one shared-memory atomic per game step on
+  // the load/store pipe; packed 8-bit counters in registers were 20 ALU instructions per step)
+  __shared__ unsigned int shist[kMaxRules + 1];
+  __shared__ MoveTable mtab;
   stage_enc_tables<SH>(tabs);
+  stage_move_table<SH>(mtab);
+  if (threadIdx.x <= kMaxRules) shist[threadIdx.x] = 0;
   stage_thresholds(rs, sthr);                                   // ends with the barrier
   const long long game = game_index();
-  if (game >= rt.n_games) return;
+  const bool live = game < rt.n_games;
   const unsigned long long game_id = (unsigned long long)(rt.game_id_base + game);
+  if (live) {
   Game<SH> g;
   load_game(g, state, game);
   unsigned long long row = deck_row<SH>(rt, game, g.episode);   // one 64-bit modulo per launch
   const uint8_t* deck = decks + row * kDeckPitch;
-  // rule-hit histogram: 8-bit counters packed in two registers (the host keeps n_steps <= 255)
-  unsigned long long cnt_lo = 0, cnt_hi = 0, cnt_fb = 0;
 #pragma unroll 1
   for (int t = 0;; ++t) {
     const long long orow = (long long)(t - 1) * rt.n_games + game;     // outputs of state t
@@ -232,27 +241,17 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
 
     int a = 0, hit = -1;
     if (g.step_type != LAST) a = rules_resolve<SH, EXT>(g, co, rs, sthr, game_id, step0 + t, &hit);
-    const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, next_card, lm, illegal);
+    const float r = step_game(g, rt, decks, deck, row, rt.row_step, a, next_card, lm, illegal, &mtab);
     const long long arow = (long long)t * rt.n_games + game;
     if (action != nullptr) action[arow] = a;
     if (reward != nullptr) reward[arow] = r;
-    if (hit >= 0) {
-      if (hit < 8) cnt_lo += 1ull << (8 * hit);
-      else if (hit < 16) cnt_hi += 1ull << (8 * (hit - 8));
-      else ++cnt_fb;
-    }
+    if (hit >= 0) atomicAdd(&shist[hit], 1u);
   }
   store_game(g, state, game);
-  if (hist != nullptr) {
-#pragma unroll 1
-    for (int k = 0; k <= rs.n; ++k) {
-      unsigned int c = k < 8 ? (unsigned int)(cnt_lo >> (8 * k)) & 255u
-                             : (k < 16 ? (unsigned int)(cnt_hi >> (8 * (k - 8))) & 255u
-                                       : (unsigned int)cnt_fb);
-      c = __reduce_add_sync(__activemask(), c);
-      if ((threadIdx.x & 31) == 0 && c) atomicAdd(&hist[k], (unsigned long long)c);
-    }
   }
+  __syncthreads();
+  if (hist != nullptr && threadIdx.x <= rs.n && shist[threadIdx.x] != 0)
+    atomicAdd(&hist[threadIdx.x], (unsigned long long)shist[threadIdx.x]);
 }
 
 // canonical int32 dump, one thread per game, ABSOLUTE player order (tests; layout = oracle

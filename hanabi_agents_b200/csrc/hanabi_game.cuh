@@ -309,24 +309,53 @@ __device__ __forceinline__ void rotate_once(Game<SH>& g) {
   g.hn = (g.hn >> 3) | ((g.hn & 7u) << (3 * (SH::P - 1)));
 }
 
+// What a move uid means to the transition: lo = cells of the hinted colour / rank | hinted flag
+// (bit 25 colour, bit 26 rank), 0 for a card move; hi = [2:0] hand index (H: not a card move),
+// [3] card move, [4] play, [7:5] target seat.  The fused kernel looks this up in shared memory
+// (one LDS.64 instead of ~20 ALU instructions per game step).
+template <class SH>
+__device__ __forceinline__ unsigned long long decode_move(int uid) {
+  constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R;
+  const bool card_move = uid < 2 * H;
+  const bool is_play = card_move && uid >= H;
+  const int idx = card_move ? (is_play ? uid - H : uid) : H;
+  int u = uid - 2 * H;
+  const bool by_color = u < (P - 1) * C;
+  if (!by_color) u -= (P - 1) * C;
+  const int span = by_color ? C : R;
+  const int k = 1 + u / span, v = u - (k - 1) * span;
+  uint32_t lo = (by_color ? color_cells(v) : rank_cells(v)) | (by_color ? (1u << 25) : (1u << 26));
+  uint32_t hi = (uint32_t)idx | ((uint32_t)k << 5);
+  if (card_move) { lo = 0; hi = (uint32_t)idx | 8u | (is_play ? 16u : 0u); }
+  return (unsigned long long)lo | ((unsigned long long)hi << 32);
+}
+struct MoveTable { unsigned long long e[64]; };
+template <class SH>
+__device__ __forceinline__ void stage_move_table(MoveTable& mt) {   // caller supplies the barrier
+  for (int j = threadIdx.x; j < 64; j += blockDim.x) mt.e[j] = j < SH::A ? decode_move<SH>(j) : 0ull;
+}
+
 // `uid` must be legal.  Returns the reward (score delta).  Ends with the seat rotation.
 // `next_card` = deck[g.deck_pos] (whatever when the deck is empty): the caller loads it ahead of time
 // so that the chance node does not wait for memory.
 // Written without branches: a warp nearly always holds games making every kind of move, so both
 // sides would be walked anyway; as selects they are one basic block the scheduler can interleave.
 template <class SH>
-__device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_card) {
-  constexpr int P = SH::P, H = SH::H, C = SH::C, R = SH::R;
+__device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_card,
+                                          const MoveTable* mt = nullptr) {
+  constexpr int P = SH::P, H = SH::H;
   const int before = __popc(g.fw);                 // the game is running: life >= 1
   const bool deck_empty = g.deck_pos >= SH::DECK;
   if (deck_empty) --g.ttp;                         // evaluated BEFORE the move
   const uint32_t pg = g.playable();
-  const bool card_move = uid < 2 * H;
-  const bool is_play = card_move && uid >= H;
+  const unsigned long long mv = mt != nullptr ? mt->e[uid] : decode_move<SH>(uid);
+  const uint32_t mv_lo = (uint32_t)mv, mv_hi = (uint32_t)(mv >> 32);
+  const bool card_move = (mv_hi & 8u) != 0;
+  const bool is_play = (mv_hi & 16u) != 0;
+  const int idx = (int)(mv_hi & 7u);
   uint32_t last = 1u | ((uint32_t)uid << 1);
 
   // ---- Play / Discard of hand[0][idx] (idx = H: not a card move, nothing shifts)
-  const int idx = card_move ? (is_play ? uid - H : uid) : H;
   uint32_t w = 0;
 #pragma unroll
   for (int i = 0; i < H; ++i)
@@ -361,19 +390,9 @@ __device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_ca
 
   // ---- RevealColor / RevealRank: matching cards keep only the hinted cells and get the hinted
   // flag; the others lose those cells (HanabiHand::RevealColor / RevealRank)
-  int u = uid - 2 * H;
-  const bool by_color = u < (P - 1) * C;
-  if (!by_color) u -= (P - 1) * C;
-  int k = 1, v = u;
-  if constexpr (P > 2) {
-    const int span = by_color ? C : R;
-    k = 1 + u / span;
-    v = u - (k - 1) * span;
-  }
-  uint32_t cells = by_color ? color_cells(v) : rank_cells(v);
-  uint32_t flag = by_color ? (1u << 25) : (1u << 26);
-  if (card_move) { cells = 0; flag = 0; }
-  else --g.info;
+  const uint32_t cells = mv_lo & kGridMask, flag = mv_lo & ~kGridMask;   // 0 for a card move
+  const int k = (int)(mv_hi >> 5);
+  if (!card_move) --g.info;
   uint32_t mask = 0;
 #pragma unroll
   for (int kk = 1; kk < P; ++kk) {

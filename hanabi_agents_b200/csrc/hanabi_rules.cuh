@@ -79,9 +79,11 @@ __device__ __forceinline__ bool ratio_at_least(const RuleSet& rs, int slot, int 
 }
 
 // Counter-based uniform stream keyed (seed, game id, step, draw): a 64-bit key per (seed, game) -- loop
-// invariant in the fused kernel -- then a 32-bit multiply-xorshift hash per (step, draw).  ptxas evaluates
-// every draw of the "lazy" rules ahead of the branches for all games; as 64-bit splitmix hashes those
-// were 143 of 1192 warp-instructions per step (profiles/r01_selfplay_history.md, v6).
+// invariant in the fused kernel -- and ONE 32-bit multiply-xorshift hash per (game, step).  At most one
+// random rule decides a game's move in a step, so only the draws of one rule have to be independent of
+// each other: index draws (0, 2, 3) read the hash from the top, coin draws (1, 4) from bit 15 down.
+// ptxas evaluates the draws of the "lazy" rules ahead of the branches for every game; as five 64-bit
+// splitmix hashes they were 143 of 1192 warp-instructions per step (profiles/r01_selfplay_history.md, v6).
 // (The CPU restatement used by the tests defines the same stream.)
 __device__ __forceinline__ unsigned long long rule_key(unsigned long long seed, unsigned long long game) {
   unsigned long long x = seed + 0x9E3779B97F4A7C15ull * (game + 1);
@@ -93,11 +95,11 @@ __device__ __forceinline__ unsigned long long rule_key(unsigned long long seed, 
 __device__ __forceinline__ uint32_t rule_rand(unsigned long long seed, unsigned long long game,
                                               unsigned long long step, uint32_t k) {
   const unsigned long long key = rule_key(seed, game);
-  uint32_t h = (uint32_t)key + (uint32_t)step * 0x9E3779B1u + (k + 1) * 0x85EBCA6Bu;
+  uint32_t h = (uint32_t)key + (uint32_t)step * 0x9E3779B1u;
   h ^= h >> 16; h *= 0x7FEB352Du;
   h ^= h >> 15; h ^= (uint32_t)(key >> 32); h *= 0x846CA68Bu;
   h ^= h >> 16;
-  return h;
+  return (k == 1 || k == 4) ? h << 16 : h;
 }
 __device__ __forceinline__ int rand_below(uint32_t r, int n) {
   return (int)(((unsigned long long)r * (unsigned long long)n) >> 32);
@@ -258,7 +260,10 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
     // tell_dispensable by hint state: nothing hinted -> finished colour or rank below every stack; colour
     // hinted -> rank below every stack, or below its own stack; rank hinted -> finished colour, or below its
     // own stack.  A fully hinted card is told nothing by any of the three rules: its one-hot is dropped.
-    const uint32_t t0 = done | ltmin, t1 = ltmin | g.fw, t2 = done | g.fw;
+    // (a scan the rule list does not need tests against empty grids: no flag inside the loop)
+    const uint32_t tdm = want_td ? SH::kGridAll : 0u;
+    const uint32_t t0 = (done | ltmin) & tdm, t1 = (ltmin | g.fw) & tdm, t2 = (done | g.fw) & tdm;
+    const uint32_t pg_tp = want_tp ? pg : 0u, all_tu = want_tu ? SH::kGridAll : 0u;
 #pragma unroll
     for (int k = P - 1; k >= 1; --k)                   // reverse order, last write = first match
 #pragma unroll
@@ -266,9 +271,9 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
         const uint32_t w = g.hand[k][i];
         const bool ch = (w & (1u << 25)) != 0, rh = (w & (1u << 26)) != 0;
         const uint32_t oh = (ch && rh) ? 0u : slot_onehot(w);
-        if (want_tp && (oh & pg) != 0) { tp_w = w; tp_k = k; }
-        if (want_td && (oh & (ch ? t1 : (rh ? t2 : t0))) != 0) { td_w = w; td_k = k; }
-        if (want_tu && k == 1 && oh != 0) tu_w = w;
+        if ((oh & pg_tp) != 0) { tp_w = w; tp_k = k; }
+        if ((oh & (ch ? t1 : (rh ? t2 : t0))) != 0) { td_w = w; td_k = k; }
+        if (k == 1 && (oh & all_tu) != 0) tu_w = w;
       }
     if (tp_w != 0) {                                   // rank first, then colour
       const int card = slot_card(tp_w);

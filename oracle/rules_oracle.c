@@ -36,16 +36,18 @@ enum {
 static const int kNumInDeckByRank[5] = {3, 2, 2, 2, 1}; /* ruleset.py:9 */
 
 static uint32_t ro_rand(uint64_t seed, uint64_t game, uint64_t step, uint32_t k) {
-  /* 64-bit key per (seed, game), 32-bit multiply-xorshift hash per (step, draw) */
+  /* 64-bit key per (seed, game), one 32-bit multiply-xorshift hash per (game, step); index draws
+   * (k = 0, 2, 3) read it from the top, coin draws (k = 1, 4) from bit 15 down: at most one random
+   * rule decides a move, so only the draws of one rule need to be independent of each other */
   uint64_t x = seed + 0x9E3779B97F4A7C15ull * (game + 1);
   x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull;
   x ^= x >> 27; x *= 0x94D049BB133111EBull;
   x ^= x >> 31;
-  uint32_t h = (uint32_t)x + (uint32_t)step * 0x9E3779B1u + (k + 1) * 0x85EBCA6Bu;
+  uint32_t h = (uint32_t)x + (uint32_t)step * 0x9E3779B1u;
   h ^= h >> 16; h *= 0x7FEB352Du;
   h ^= h >> 15; h ^= (uint32_t)(x >> 32); h *= 0x846CA68Bu;
   h ^= h >> 16;
-  return h;
+  return (k == 1 || k == 4) ? h << 16 : h;
 }
 static int ro_below(uint32_t r, int n) { return (int)(((uint64_t)r * (uint64_t)n) >> 32); }
 

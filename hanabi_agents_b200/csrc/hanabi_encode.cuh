@@ -67,9 +67,9 @@ __device__ __forceinline__ unsigned long long discard_thermometers(unsigned long
 }
 
 template <class SH, int K, int I, int N>
-__device__ __forceinline__ void put_hand_card(uint32_t (&row)[N], uint32_t w) {
+__device__ __forceinline__ void put_hand_card(uint32_t (&row)[N], uint32_t oh) {
   // EncodeHands: one-hot card index of another player's card
-  put<(K - 1) * SH::H * SH::BPC + I * SH::BPC, SH::BPC>(row, slot_onehot(w));
+  put<(K - 1) * SH::H * SH::BPC + I * SH::BPC, SH::BPC>(row, oh);
 }
 
 // ---- lookup tables in shared memory ------------------------------------------------------------
@@ -150,7 +150,7 @@ __device__ __forceinline__ void put_seat(uint32_t (&row)[N], const Game<SH>& g, 
   if constexpr (K < SH::P) {
 #define HB_CARD(I)                                                        \
     if constexpr (I < SH::H) {                                            \
-      if constexpr (K >= 1) put_hand_card<SH, K, I>(row, g.hand[K][I]);   \
+      if constexpr (K >= 1) put_hand_card<SH, K, I>(row, g.oh[K][I]);     \
       put_knowledge<SH, K, I>(row, g.hand[K][I], tb);                     \
     }
     HB_CARD(0) HB_CARD(1) HB_CARD(2) HB_CARD(3) HB_CARD(4)

@@ -85,6 +85,10 @@ __device__ __forceinline__ int card_rank(int card) { return card - 5 * card_colo
 __device__ __forceinline__ uint32_t color_cells(int c) { return 31u << (5 * c); }
 __device__ __forceinline__ uint32_t rank_cells(int r) { return 0x108421u << r; }
 
+// one-hot grid bit of the card in a slot (0 for an empty slot: the true identity of a card is
+// always among its plausible ones, and an empty slot has an empty grid)
+__device__ __forceinline__ uint32_t slot_onehot(uint32_t w) { return (1u << (w >> 27)) & w & kGridMask; }
+
 template <class SH>
 __device__ __forceinline__ uint32_t fresh_slot(int card) {
   return SH::kGridAll | ((uint32_t)card << 27);   // everything plausible, nothing hinted
@@ -104,6 +108,8 @@ constexpr uint32_t kInst1 = kLow4;
 template <class SH>
 struct Game {
   uint32_t hand[SH::P][SH::H];   // seat-relative card slots
+  uint32_t oh[SH::P][SH::H];     // one-hot grid bit of each slot's card, 0 for an empty slot (derived, not
+                                 // stored: 3 ALU instructions per slot and step when computed on demand)
   uint32_t fw;                   // fireworks thermometer grid: bit 5c+r <=> r < height of stack c
   uint32_t hn;                   // 3 bits per seat
   int info, life, cur, ttp, step_type, deck_pos;
@@ -154,7 +160,10 @@ __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restric
 #pragma unroll
   for (int k = 0; k < SH::P; ++k)
 #pragma unroll
-    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = w[k * SH::H + i];
+    for (int i = 0; i < SH::H; ++i) {
+      g.hand[k][i] = w[k * SH::H + i];
+      g.oh[k][i] = slot_onehot(g.hand[k][i]);
+    }
   const uint32_t a = w[SH::S], b = w[SH::S + 1];
   g.fw = a & kGridMask;
   g.info = (a >> 25) & 15;
@@ -231,6 +240,7 @@ __device__ __forceinline__ void reset_game(Game<SH>& g, const uint8_t* __restric
       const int j = k * SH::H + i;
       const uint32_t card = (q[j >> 2] >> (8 * (j & 3))) & 0xffu;
       g.hand[k][i] = fresh_slot<SH>((int)card);
+      g.oh[k][i] = 1u << card;
     }
   g.fw = 0;
   g.info = SH::MAX_INFO;
@@ -248,16 +258,12 @@ __device__ __forceinline__ void reset_game(Game<SH>& g, const uint8_t* __restric
   g.last = 0;
 }
 
-// one-hot grid bit of the card in a slot (0 for an empty slot: the true identity of a card is
-// always among its plausible ones, and an empty slot has an empty grid)
-__device__ __forceinline__ uint32_t slot_onehot(uint32_t w) { return (1u << (w >> 27)) & w & kGridMask; }
-
 // union of the one-hots of hand k
 template <class SH>
 __device__ __forceinline__ uint32_t hand_union(const Game<SH>& g, int k) {
   uint32_t u = 0;
 #pragma unroll
-  for (int i = 0; i < SH::H; ++i) u |= slot_onehot(g.hand[k][i]);
+  for (int i = 0; i < SH::H; ++i) u |= g.oh[k][i];
   return u;
 }
 
@@ -297,15 +303,15 @@ __device__ __forceinline__ unsigned long long legal_mask(const Game<SH>& g) {
 // ---- transition (A.3): ApplyMove + chance deal + AdvanceToNextPlayer -------------------
 template <class SH>
 __device__ __forceinline__ void rotate_once(Game<SH>& g) {
-  uint32_t first[SH::H];
+  uint32_t first[SH::H], first_oh[SH::H];
 #pragma unroll
-  for (int i = 0; i < SH::H; ++i) first[i] = g.hand[0][i];
+  for (int i = 0; i < SH::H; ++i) { first[i] = g.hand[0][i]; first_oh[i] = g.oh[0][i]; }
 #pragma unroll
   for (int k = 0; k + 1 < SH::P; ++k)
 #pragma unroll
-    for (int i = 0; i < SH::H; ++i) g.hand[k][i] = g.hand[k + 1][i];
+    for (int i = 0; i < SH::H; ++i) { g.hand[k][i] = g.hand[k + 1][i]; g.oh[k][i] = g.oh[k + 1][i]; }
 #pragma unroll
-  for (int i = 0; i < SH::H; ++i) g.hand[SH::P - 1][i] = first[i];
+  for (int i = 0; i < SH::H; ++i) { g.hand[SH::P - 1][i] = first[i]; g.oh[SH::P - 1][i] = first_oh[i]; }
   g.hn = (g.hn >> 3) | ((g.hn & 7u) << (3 * (SH::P - 1)));
 }
 
@@ -382,9 +388,10 @@ __device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_ca
   // at the END of the mover's hand.  While the deck lasts every hand is full, so that is slot H-1.
 #pragma unroll
   for (int i = 0; i < H - 1; ++i)
-    if (i >= idx) g.hand[0][i] = g.hand[0][i + 1];
+    if (i >= idx) { g.hand[0][i] = g.hand[0][i + 1]; g.oh[0][i] = g.oh[0][i + 1]; }
   if (card_move) {
     g.hand[0][H - 1] = deck_empty ? 0u : fresh_slot<SH>((int)next_card);
+    g.oh[0][H - 1] = deck_empty ? 0u : 1u << next_card;
     if (deck_empty) g.hn -= 1u; else ++g.deck_pos;
   }
 
@@ -401,7 +408,7 @@ __device__ __forceinline__ int apply_move(Game<SH>& g, int uid, uint32_t next_ca
 #pragma unroll
     for (int i = 0; i < H; ++i) {
       const uint32_t s = g.hand[kk][i];
-      const bool match = (slot_onehot(s) & kcells) != 0;
+      const bool match = (g.oh[kk][i] & kcells) != 0;
       g.hand[kk][i] = match ? ((s & (kcells | ~kGridMask)) | kflag) : (s & ~kcells);
       if (match) mask |= 1u << i;
     }

@@ -155,7 +155,7 @@ __device__ __forceinline__ void unseen_planes(const Game<SH>& g, uint32_t& l0, u
   for (int k = 1; k < SH::P; ++k)
 #pragma unroll
     for (int i = 0; i < SH::H; ++i) {
-      const uint32_t oh = slot_onehot(g.hand[k][i]);
+      const uint32_t oh = g.oh[k][i];
       v1 ^= v0 & oh;
       v0 ^= oh;
     }
@@ -203,7 +203,7 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
 #pragma unroll
     for (int i = H - 1; i >= 0; --i) {
       const uint32_t w = g.hand[0][i];
-      if ((w & (3u << 25)) == (3u << 25) && (slot_onehot(w) & pg) != 0) o.play_certain = uid_play<SH>(i);
+      if ((w & (3u << 25)) == (3u << 25) && (g.oh[0][i] & pg) != 0) o.play_certain = uid_play<SH>(i);
     }
   }
 
@@ -238,7 +238,7 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
       const uint32_t w = g.hand[0][i];
       const bool ch = (w & (1u << 25)) != 0, rh = (w & (1u << 26)) != 0;
       const uint32_t sel = rh ? (ch ? g3 : g2) : (ch ? g1 : all);
-      if ((slot_onehot(w) & sel) != 0) first = i;      // an empty slot has no one-hot
+      if ((g.oh[0][i] & sel) != 0) first = i;             // an empty slot has no one-hot
       if ((slot_grid(w) & useful) == 0) second = i;    // no plausible identity is still useful
     }
     if (second >= n0) second = H;
@@ -270,7 +270,7 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
       for (int i = H - 1; i >= 0; --i) {
         const uint32_t w = g.hand[k][i];
         const bool ch = (w & (1u << 25)) != 0, rh = (w & (1u << 26)) != 0;
-        const uint32_t oh = (ch && rh) ? 0u : slot_onehot(w);
+        const uint32_t oh = (ch && rh) ? 0u : g.oh[k][i];
         if ((oh & pg_tp) != 0) { tp_w = w; tp_k = k; }
         if ((oh & (ch ? t1 : (rh ? t2 : t0))) != 0) { td_w = w; td_k = k; }
         if (k == 1 && (oh & all_tu) != 0) tu_w = w;

@@ -442,6 +442,8 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
       case R_TELL_PLAYABLE_CARD_OUTER:
       case R_TELL_ANYONE_USEFUL_CARD: own(ROW_TELL_PLAYABLE, k); break;
       case R_HAIL_MARY: own(ROW_HAIL_MARY, k); break;
+      case R_TELL_RANDOMLY: own(ROW_TELL_RANDOMLY, k); break;
+      case R_DISCARD_RANDOMLY: own(ROW_DISCARD_RANDOMLY, k); break;
       case R_TELL_MOST_INFORMATION: break;               // never fires
       case R_TELL_DISPENSABLE:
         if (rs.iarg[k] <= td_max) break;                 // an earlier one fires whenever this would

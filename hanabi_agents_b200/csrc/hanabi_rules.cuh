@@ -57,7 +57,8 @@ struct RuleSet {        // entry [n] is the legal_random fallback, filled by the
 enum RuleRow {
   ROW_DISCARD_OLDEST = 0, ROW_OSAWA = 1, ROW_TELL_UNKNOWN = 2, ROW_PLAY_SAFE = 3, ROW_PLAY_CERTAIN = 4,
   ROW_TELL_PLAYABLE = 5, ROW_TELL_DISPENSABLE0 = 6, ROW_TELL_DISPENSABLE1 = 7, ROW_HAIL_MARY = 8,
-  ROW_PPS0 = 9, ROW_NUM = ROW_PPS0 + kThrSlots
+  ROW_TELL_RANDOMLY = 9, ROW_DISCARD_RANDOMLY = 10,
+  ROW_PPS0 = 11, ROW_NUM = ROW_PPS0 + kThrSlots
 };
 static_assert(ROW_NUM <= 16, "RuleSet::key_hi");
 constexpr unsigned int kKeyNone = 0x10000u;      // "no move" sorts after every position
@@ -387,18 +388,6 @@ __device__ __forceinline__ int lazy_rule(const Game<SH>& g, const Cores& co, con
       return run_ext_rule(g, rule, rs.farg[k], rs, rs.tslot[k], seed, game_id, step);
   }
   switch (rule) {
-    case R_TELL_RANDOMLY: {                            // :314-347
-      const int n1 = g.hand_n(1);
-      if (g.info <= 0 || n1 == 0) return -1;
-      const int idx = rand_below(rule_rand(seed, game_id, step, 0), n1);
-      const int coin = rand_below(rule_rand(seed, game_id, step, 1), 2);
-      uint32_t w = 0;
-#pragma unroll
-      for (int i = 0; i < H; ++i)
-        if (i == idx) w = g.hand[1][i];
-      const int card = slot_card(w);
-      return coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
-    }
     case R_LEGAL_RANDOM: {                             // :598-604 (intended semantics)
       unsigned long long m = legal_mask(g);
       const int n = __popcll(m);
@@ -407,9 +396,6 @@ __device__ __forceinline__ int lazy_rule(const Game<SH>& g, const Cores& co, con
       while (j-- > 0) m &= m - 1;
       return __ffsll((long long)m) - 1;
     }
-    case R_DISCARD_RANDOMLY:                           // :607-614 (intended semantics)
-      if (!(g.info < 8) || n0 == 0) return -1;
-      return uid_discard<SH>(rand_below(rule_rand(seed, game_id, step, 3), n0));
     case R_TELL_DISPENSABLE:                           // a third tell_dispensable of one list
       return (g.info < rs.iarg[k] && g.info > 0) ? co.tell_dispensable : -1;
     case R_PLAY_PROBABLY_SAFE:                         // more threshold rules than comparison tables
@@ -450,6 +436,23 @@ __device__ __forceinline__ int rules_resolve(const Game<SH>& g, const Cores& co,
   best = min(best, HB_KEY(ROW_TELL_DISPENSABLE1, can_tell && g.info < rs.td_ilt[1], co.tell_dispensable));
   // hail_mary :653-655 = play_probably_safe(0.0) when the deck is empty and a life can be spared
   best = min(best, HB_KEY(ROW_HAIL_MARY, SH::DECK - g.deck_pos == 0 && g.life > 1, play_best));
+  // The two cheap random rules are rows as well: with one hash per (game, step) their verdict is a dozen
+  // instructions, while as lazily evaluated entries they were two divergent branches that nearly every
+  // warp took anyway (some game of the 32 gets that far).
+  if (rs.used & ((1u << R_TELL_RANDOMLY) | (1u << R_DISCARD_RANDOMLY))) {             // uniform
+    const int n1 = g.hand_n(1);
+    const int idx = rand_below(rule_rand(rs.seed, game_id, step, 0), n1);             // :318
+    const int coin = rand_below(rule_rand(rs.seed, game_id, step, 1), 2);             // :321
+    uint32_t w = 0;
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i)
+      if (i == idx) w = g.hand[1][i];
+    const int card = slot_card(w);
+    const int tr = coin == 0 ? uid_rank<SH>(1, card_rank(card)) : uid_color<SH>(1, card_color(card));
+    best = min(best, HB_KEY(ROW_TELL_RANDOMLY, can_tell && n1 > 0, tr));              // :314-347
+    const int dr = uid_discard<SH>(rand_below(rule_rand(rs.seed, game_id, step, 3), n0));
+    best = min(best, HB_KEY(ROW_DISCARD_RANDOMLY, can_discard && n0 > 0, dr));        // :607-614
+  }
 #pragma unroll 1
   for (int s = 0; s < rs.n_slots; ++s) {                 // play_probably_safe :617-635 (:105, :622)
     const int bt = co.bt < kThrRows ? co.bt : 0;         // row 0 of a table is empty

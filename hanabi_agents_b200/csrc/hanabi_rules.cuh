@@ -216,14 +216,27 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
   if (used & ((1u << R_PLAY_PROBABLY_SAFE) | (1u << R_HAIL_MARY))) {
     uint32_t l0, l1;
     unseen_planes(g, l0, l1);
+    int p[H], t[H];
 #pragma unroll
     for (int i = 0; i < H; ++i) {
       const uint32_t grid = slot_grid(g.hand[0][i]);
-      const int total = count_planes(grid, l0, l1);
-      const int playable = count_planes(grid & pg, l0, l1);
-      // p_i/t_i > p_b/t_b  <=>  p_i*t_b > p_b*t_i   (t > 0); first maximum wins
-      if (i == 0 || playable * o.bt > o.bp * total) { o.bp = playable; o.bt = total; o.best = i; }
+      t[i] = count_planes(grid, l0, l1);
+      p[i] = count_planes(grid & pg, l0, l1);
     }
+    // first maximum of p_i / t_i (np.argmax) as a tournament: p_j/t_j > p_i/t_i <=> p_j*t_i > p_i*t_j
+    // (t > 0; an empty slot is 0 / 0 and never beats anything).  In a pair the later card wins only if
+    // strictly greater, so ties go to the lowest index at every level.
+    int bi[H];
+#pragma unroll
+    for (int i = 0; i < H; ++i) bi[i] = i;
+#pragma unroll
+    for (int span = 1; span < H; span *= 2)
+#pragma unroll
+      for (int i = 0; i + span < H; i += 2 * span) {
+        const bool later = p[i + span] * t[i] > p[i] * t[i + span];
+        if (later) { p[i] = p[i + span]; t[i] = t[i + span]; bi[i] = bi[i + span]; }
+      }
+    o.bp = p[0]; o.bt = t[0]; o.best = bi[0];
   }
 
   o.osawa = -1;                                        // :220-280
@@ -453,11 +466,17 @@ __device__ __forceinline__ int rules_resolve(const Game<SH>& g, const Cores& co,
     const int dr = uid_discard<SH>(rand_below(rule_rand(rs.seed, game_id, step, 3), n0));
     best = min(best, HB_KEY(ROW_DISCARD_RANDOMLY, can_discard && n0 > 0, dr));        // :607-614
   }
-#pragma unroll 1
-  for (int s = 0; s < rs.n_slots; ++s) {                 // play_probably_safe :617-635 (:105, :622)
+  {                                                      // play_probably_safe :617-635 (:105, :622)
     const int bt = co.bt < kThrRows ? co.bt : 0;         // row 0 of a table is empty
-    const bool ok = (rs.slot_extra[s] == 0 || g.life > 1) && ((sthr[s * kThrRows + bt] >> co.bp) & 1ull);
-    best = min(best, HB_KEY(ROW_PPS0 + s, ok, play_best));
+#define HB_PPS(s)                                                                                      \
+    {                                                                                                  \
+      const bool ok = (rs.slot_extra[s] == 0 || g.life > 1) && ((sthr[(s) * kThrRows + bt] >> co.bp) & 1ull); \
+      best = min(best, HB_KEY(ROW_PPS0 + (s), ok, play_best));                                         \
+    }
+    if (rs.n_slots > 0) HB_PPS(0)                        // uniform; one table is the common case
+#pragma unroll 1
+    for (int s = 1; s < rs.n_slots; ++s) HB_PPS(s)
+#undef HB_PPS
   }
 #undef HB_KEY
   // the lazily evaluated entries, in list order: one matters only to a game that gets there

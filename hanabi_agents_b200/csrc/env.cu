@@ -18,6 +18,9 @@ struct hb_env {
   uint32_t* state = nullptr;
   uint8_t* decks = nullptr;
   unsigned long long* illegal = nullptr;  // device counter
+  // work queue of the fused self-play kernel (SpQueue below): [head, tail] + group[G] + state[G]
+  unsigned long long* spq = nullptr;
+  int spq_groups = 0;
   bool is_reset = false;
   // staging for *_host entry points
   void* stage = nullptr;
@@ -185,6 +188,46 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
   }
 }
 
+// ---- work queue of the fused self-play kernel ---------------------------------------------------
+// 65,536 games are 2048 warps on 592 schedulers: an SM's sub-partitions hold 4 / 4 / 3 / 3 of them, the
+// ones with four set the duration of a launch and the others idle for the last fifth of it
+// (profiles/r01_selfplay_history.md, v6).  Consecutive launches are therefore allowed to OVERLAP
+// (programmatic dependent launch: the next launch's CTAs become resident as soon as slots are free) and
+// the block index no longer names the games: a CTA takes the next group of 64 games from a FIFO ring that
+// the previous launch's CTAs refill as they finish.  A group that finished early (light sub-partition)
+// starts its next 64 steps early, wherever a slot is free, so over a run of launches every group sees
+// the average load instead of some groups always the worst.  Every launch pops each group exactly once
+// (FIFO: pop ticket i of launch k+1 is push ticket i of launch k); results do not depend on the order.
+struct SpQueue {
+  unsigned long long* head;     // next pop ticket
+  unsigned long long* tail;     // next push ticket
+  int* group;                   // [G] ring: group ids
+  int* state;                   // [G] 2r+1: filled in round r, 2r+2: consumed
+  int n_groups;
+};
+
+__global__ void spq_init_kernel(SpQueue q) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i == 0) { *q.head = 0ull; *q.tail = (unsigned long long)q.n_groups; }
+  if (i < q.n_groups) { q.group[i] = i; q.state[i] = 1; }
+}
+
+__device__ __forceinline__ int ld_acquire_gpu(const int* p) {
+  int v;
+  asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu(int* p, int v) {
+  asm volatile("st.release.gpu.global.s32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+// bounded wait (a queue that never fills is a bug: trap instead of hanging the device)
+__device__ __forceinline__ void spq_wait(const int* p, int want) {
+  for (long long spins = 0; ld_acquire_gpu(p) != want; ++spins) {
+    __nanosleep(64);
+    if (spins > (1ll << 24)) __trap();
+  }
+}
+
 // Fused self-play: `n_steps` x {rule-based move, env step, observation} with the game state
 // held in registers; only the per-step outputs touch HBM.  Output row (t, game).
 // Pass t of the loop is {observation of state t -> row t-1, rule bodies on state t} as ONE basic block
@@ -197,9 +240,22 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
                 unsigned long long step0, int n_steps, uint32_t* __restrict__ obs,
                 uint32_t* __restrict__ legal, float* __restrict__ reward,
                 uint8_t* __restrict__ step_type, int32_t* __restrict__ action,
-                unsigned long long* __restrict__ hist, unsigned long long* illegal) {
+                unsigned long long* __restrict__ hist, unsigned long long* illegal, SpQueue q) {
   __shared__ unsigned long long sthr[kThrSlots * kThrRows];
   __shared__ EncTables tabs;
+  __shared__ int s_group;
+  unsigned long long ticket = 0;
+  if (threadIdx.x == 0) ticket = atomicAdd(q.head, 1ull);
+  __syncthreads();
+  // every CTA of this launch has its ticket before the next launch may start taking tickets
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  if (threadIdx.x == 0) {
+    const int slot = (int)(ticket % (unsigned long long)q.n_groups);
+    const int filled = 2 * (int)(ticket / (unsigned long long)q.n_groups) + 1;
+    spq_wait(q.state + slot, filled);
+    s_group = __ldcg(q.group + slot);
+    st_release_gpu(q.state + slot, filled + 1);
+  }
   // rule-hit histogram: per-CTA counters in shared memory (one shared-memory atomic per game step on
   // the load/store pipe; packed 8-bit counters in registers were 20 ALU instructions per step)
   __shared__ unsigned int shist[kMaxRules + 1];
@@ -208,12 +264,13 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   stage_move_table<SH>(mtab);
   if (threadIdx.x <= kMaxRules) shist[threadIdx.x] = 0;
   stage_thresholds(rs, sthr);                                   // ends with the barrier
-  const long long game = game_index();
+  const int group = s_group;
+  const long long game = (long long)group * kThreads + threadIdx.x;
   const bool live = game < rt.n_games;
   const unsigned long long game_id = (unsigned long long)(rt.game_id_base + game);
   if (live) {
   Game<SH> g;
-  load_game(g, state, game);
+  load_game<SH, true>(g, state, game);   // L2 only: the previous launch may still be running on this SM
   unsigned long long row = deck_row<SH>(rt, game, g.episode);   // one 64-bit modulo per launch
   const uint8_t* deck = decks + row * kDeckPitch;
 #pragma unroll 1
@@ -249,9 +306,18 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   }
   store_game(g, state, game);
   }
+  __threadfence();                                              // the group's state, device-wide ...
   __syncthreads();
   if (hist != nullptr && threadIdx.x <= rs.n && shist[threadIdx.x] != 0)
     atomicAdd(&hist[threadIdx.x], (unsigned long long)shist[threadIdx.x]);
+  if (threadIdx.x == 0) {                                       // ... before the group is handed on
+    const unsigned long long t = atomicAdd(q.tail, 1ull);
+    const int slot = (int)(t % (unsigned long long)q.n_groups);
+    const int round = (int)(t / (unsigned long long)q.n_groups);
+    spq_wait(q.state + slot, 2 * round);                        // last round's entry has been taken
+    __stcg(q.group + slot, group);
+    st_release_gpu(q.state + slot, 2 * round + 1);
+  }
 }
 
 // canonical int32 dump, one thread per game, ABSOLUTE player order (tests; layout = oracle
@@ -527,6 +593,7 @@ int hb_env_destroy(hb_env* e) {
   if (e->state) cudaFree(e->state);
   if (e->decks) cudaFree(e->decks);
   if (e->illegal) cudaFree(e->illegal);
+  if (e->spq) cudaFree(e->spq);
   if (e->stage) cudaFree(e->stage);
   if (e->hs_step) cudaStreamDestroy(e->hs_step);
   if (e->hs_out) cudaStreamDestroy(e->hs_out);
@@ -712,15 +779,40 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
-  if (uses_ext_rules(rs)) {
-    HB_DISPATCH(e, (selfplay_kernel<SH, true><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
-                       e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
-                       d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
-  } else {
-    HB_DISPATCH(e, (selfplay_kernel<SH, false><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
-                       e->rt, e->state, e->decks, rs, step0, n_steps, d_obs, d_legal, d_reward,
-                       d_step_type, d_action, (unsigned long long*)d_hist, e->illegal)));
+  const int n_groups = (int)grid_for(e);
+  if (e->spq == nullptr) {
+    HB_CUDA(cudaMalloc(&e->spq, 16 + (size_t)n_groups * 8));
+    e->spq_groups = n_groups;
+    SpQueue q0{e->spq, e->spq + 1, (int*)(e->spq + 2), (int*)(e->spq + 2) + n_groups, n_groups};
+    spq_init_kernel<<<(n_groups + 255) / 256, 256, 0, (cudaStream_t)stream>>>(q0);
+    HB_CUDA(cudaGetLastError());
   }
+  SpQueue q{e->spq, e->spq + 1, (int*)(e->spq + 2), (int*)(e->spq + 2) + n_groups, n_groups};
+  // consecutive self-play launches may overlap (see SpQueue); any other kernel is ordered as usual
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)n_groups);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = (cudaStream_t)stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  unsigned long long* hist = (unsigned long long*)d_hist;
+  const uint8_t* decks = e->decks;
+  const unsigned long long s0 = step0;
+  cudaError_t lerr = cudaSuccess;
+  if (uses_ext_rules(rs)) {
+    HB_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, selfplay_kernel<SH, true>, e->rt, e->state, decks, rs, s0,
+                                              n_steps, d_obs, d_legal, d_reward, d_step_type, d_action, hist,
+                                              e->illegal, q)));
+  } else {
+    HB_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, selfplay_kernel<SH, false>, e->rt, e->state, decks, rs, s0,
+                                              n_steps, d_obs, d_legal, d_reward, d_step_type, d_action, hist,
+                                              e->illegal, q)));
+  }
+  HB_CUDA(lerr);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }

@@ -145,7 +145,7 @@ __device__ __forceinline__ uint32_t even_bits(unsigned long long x) {
 }
 
 // ---- state <-> HBM (16-byte vector accesses; a game is 64 B or 128 B contiguous) ----------
-template <class SH>
+template <class SH, bool L2_ONLY = false>
 __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restrict__ state,
                                           long long game) {
   uint32_t w[SH::kStateWords];
@@ -153,7 +153,7 @@ __device__ __forceinline__ void load_game(Game<SH>& g, const uint32_t* __restric
 #pragma unroll
   for (int i = 0; i < SH::kStateWords / 4; ++i) {
     if (4 * i < SH::S + 6) {
-      const uint4 v = src[i];
+      const uint4 v = L2_ONLY ? __ldcg(src + i) : src[i];
       w[4 * i] = v.x; w[4 * i + 1] = v.y; w[4 * i + 2] = v.z; w[4 * i + 3] = v.w;
     }
   }

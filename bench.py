@@ -241,6 +241,47 @@ def cpu_learner_baseline(seconds):
                       "the reference's JAX learner is not installable here)" % (done, el)}
 
 
+def bench_other_shards(world, rank, args):
+    """The fused self-play kernel on the per-GPU shards of the two multi-GPU configurations of
+    BASELINE.json (informational; the headline stays configs[1]): configs[3] = 1,048,576 Hanabi-Full
+    2p games over 8 GPUs (131,072 per GPU), configs[4] = 262,144 Hanabi-Full 5p games (32,768 per GPU)."""
+    import torch
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.rule_based import RulebasedAgent, predefined_rules
+    out = []
+    for players, n, obs_bytes, state_bytes in ((2, 131072, 84, 64), (5, 32768, 160, 128)):
+        env = HanabiParallelEnv(n, "Hanabi-Full", players, game_id_base=rank * n, n_total=world * n,
+                                n_decks=2 * n, seed=SEED)
+        agent = RulebasedAgent(predefined_rules.piers_rules, seed=SEED)
+        env.reset()
+        T = args.fuse
+        dev = env.device
+        bufs = dict(obs=torch.empty((T, n, env.obs_stride), dtype=torch.int32, device=dev),
+                    legal=torch.empty((T, n, env.legal_words), dtype=torch.int32, device=dev),
+                    reward=torch.empty((T, n), dtype=torch.float32, device=dev),
+                    step_type=torch.empty((T, n), dtype=torch.uint8, device=dev),
+                    action=torch.empty((T, n), dtype=torch.int32, device=dev))
+        for _ in range(4):
+            env.selfplay(agent, T, **bufs)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 40
+        e0.record()
+        for _ in range(reps):
+            env.selfplay(agent, T, **bufs)
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1) / reps
+        per_step = obs_bytes + 4 * env.legal_words + 4 + 1 + 4
+        gbs = n * (T * per_step + 2 * state_bytes) / (ms * 1e-3) / 1e9
+        out.append({"workload": "rule_based(piers) self-play, Hanabi-Full %dp, %d games/GPU" % (players, n),
+                    "ms_per_launch": ms, "env_steps_per_s_per_gpu": n * T / (ms * 1e-3),
+                    "algorithmic_GBps": gbs, "illegal_moves": env.illegal_count()})
+        del env, bufs
+        torch.cuda.empty_cache()
+    return out
+
+
 def bench_session(n, world, rank, args):
     """DQN self-play through HanabiParallelSession at the Rainbow configuration
     of BASELINE configs[3]: two learning agents take turns over n games of this GPU; a training
@@ -500,6 +541,7 @@ def run_ours(args):
     if not args.no_learner:
         learner, acting = bench_learner(env, obs, legal, reward, stype, action, T, world, args)
     session = None if args.no_session else bench_session(n, world, rank, args)
+    other = None if args.no_session else bench_other_shards(world, rank, args)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -547,7 +589,9 @@ def run_ours(args):
         "config": {"workload": WORKLOAD, "games_per_gpu": n, "fused_steps_per_launch": T,
                    "l2": "outputs of one launch (%.0f MB) exceed the 126 MB L2; no flush needed"
                          % (T * n * (env.obs_stride * 4 + env.legal_words * 4 + 9) / 1e6),
-                   "decks": "numpy default_rng(%d) permutations, pool of %d" % (SEED, 4 * n)},
+                   "decks": "numpy default_rng(%d) permutations, pool of %d" % (SEED, 4 * n),
+                   "launch_overlap": "consecutive self-play launches of one stream overlap (programmatic dependent "
+                                     "launch + per-group FIFO hand-over); roofline.launch_ms = timed region / launches"},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "steps": e_steps, "chunks": args.e2e_chunks,
@@ -562,6 +606,7 @@ def run_ours(args):
         "acting": acting,
         "sum_tree": tree,
         "session": session,
+        "other_shards": other,
     }
     print(json.dumps(out))
     if world > 1:

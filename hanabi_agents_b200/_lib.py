@@ -107,6 +107,7 @@ SIGNATURES = {
     "hb_rb_set_insert_priority": (i32, [vp, f32]),
     "hb_net_grads_rainbow": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, vp, vp, vp]),
     "hb_net_adam_tf": (i32, [vp, f32, f32, f32, f32, f32, vp]),
+    "hb_net_loss_event": (vp, [vp]),
     "hb_learner_loss": (vp, [vp]),
     "hb_learner_mean_loss": (vp, [vp]),
     "hb_learner_indices": (vp, [vp]),

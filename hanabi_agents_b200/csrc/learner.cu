@@ -15,8 +15,8 @@ struct hb_learner {
   hb_qnet* net = nullptr;
   hb_replay* rb = nullptr;
   int B = 0, stride = 0, prioritized = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev_in = nullptr, ev_out = nullptr;
+  cudaStream_t stream = nullptr, prio = nullptr;   // prio: priority update beside the backward pass
+  cudaEvent_t ev_in = nullptr, ev_out = nullptr, ev_prio = nullptr;
   // staging (pinned) and device inputs
   static constexpr int kSlots = 4;
   float* h_keys = nullptr;       // [kSlots][B] ring of pinned staging rows
@@ -49,15 +49,20 @@ int phase_a(hb_learner* L, float beta, float discount, int mask_terminal, cudaSt
     if ((rc = hb_rb_sample(L->rb, L->d_keys, L->B, L->d_idx, nullptr, L->d_p32, s))) return rc;
   }
   if ((rc = hb_rb_gather(L->rb, L->d_idx, L->B, L->o1, L->act, L->rew, L->o2, nullptr, L->term, s))) return rc;
-  return hb_net_grads(L->net, L->o1, L->act, L->rew, L->o2, L->term, L->prioritized ? L->d_p32 : nullptr,
-                      nullptr, L->B, beta, discount, mask_terminal, L->loss, L->mean, s);
+  rc = hb_net_grads(L->net, L->o1, L->act, L->rew, L->o2, L->term, L->prioritized ? L->d_p32 : nullptr,
+                    nullptr, L->B, beta, discount, mask_terminal, L->loss, L->mean, s);
+  if (rc || !L->prioritized) return rc;
+  // update_priorities (rlax_rainbow.py:331-334) needs only the per-sample losses: it runs on its own stream
+  // beside the backward GEMMs instead of after Adam (same values: nothing between the two reads the tree)
+  HB_CUDA(cudaStreamWaitEvent(L->prio, (cudaEvent_t)hb_net_loss_event(L->net), 0));
+  rc = hb_rb_update_priorities(L->rb, L->d_idx, L->loss, L->B, L->prio);
+  HB_CUDA(cudaEventRecord(L->ev_prio, L->prio));
+  HB_CUDA(cudaStreamWaitEvent(s, L->ev_prio, 0));
+  return rc;
 }
 
 int phase_b(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale, cudaStream_t s) {
-  int rc = hb_net_adam(L->net, lr, b1, b2, eps, grad_scale, s);
-  if (rc) return rc;
-  if (L->prioritized) rc = hb_rb_update_priorities(L->rb, L->d_idx, L->loss, L->B, s);
-  return rc;
+  return hb_net_adam(L->net, lr, b1, b2, eps, grad_scale, s);
 }
 
 template <class F>
@@ -98,6 +103,8 @@ int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_lea
   cudaError_t e = cudaStreamCreateWithFlags(&L->stream, cudaStreamNonBlocking);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_in, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_out, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->prio, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_prio, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaMallocHost(&L->h_keys, hb_learner::kSlots * B * 4);
   if (e == cudaSuccess) e = cudaMallocHost(&L->h_idx, hb_learner::kSlots * B * 8);
   for (int i = 0; i < hb_learner::kSlots && e == cudaSuccess; ++i)
@@ -135,6 +142,8 @@ int hb_learner_destroy(hb_learner* L) {
     if (ev) cudaEventDestroy(ev);
   if (L->ev_in) cudaEventDestroy(L->ev_in);
   if (L->ev_out) cudaEventDestroy(L->ev_out);
+  if (L->ev_prio) cudaEventDestroy(L->ev_prio);
+  if (L->prio) cudaStreamDestroy(L->prio);
   if (L->stream) cudaStreamDestroy(L->stream);
   delete L;
   return HB_OK;

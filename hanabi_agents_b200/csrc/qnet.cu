@@ -67,7 +67,7 @@ struct hb_qnet {
   int lb = 0, lbp = 0;
   uint32_t* xb = nullptr;              // [2B, obs_stride] packed rows: obs_tm1 then obs_t
   cudaStream_t side = nullptr;         // second stream: target forward / weight gradients run beside
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_dz[kMaxLayers] = {nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_loss = nullptr, ev_dz[kMaxLayers] = {nullptr};
   __half* x = nullptr;                 // [2B, K0]
   __half* xt = nullptr;                // [K0, Bp]
   __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
@@ -528,6 +528,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
     HB_CUDA(cudaStreamCreateWithFlags(&q->side, cudaStreamNonBlocking));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_fork, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_loss, cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
   }
   if ((rc = dev_alloc(&q->xt, (size_t)K0 * Bp))) return rc;
@@ -774,6 +775,7 @@ int hb_net_destroy(hb_qnet* q) {
     cudaStreamDestroy(q->side);
     cudaEventDestroy(q->ev_fork);
     cudaEventDestroy(q->ev_join);
+    if (q->ev_loss) cudaEventDestroy(q->ev_loss);
     for (int l = 0; l < kMaxLayers; ++l) cudaEventDestroy(q->ev_dz[l]);
   }
   dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
@@ -934,6 +936,8 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                           float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
                           const uint32_t* d_legal_t);
 
+void* hb_net_loss_event(hb_qnet* q) { return q ? (void*)q->ev_loss : nullptr; }
+
 int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,
@@ -1022,6 +1026,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   HB_CUDA(cudaGetLastError());
   if (d_loss_out) HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
   if (d_mean_loss) HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
+  HB_CUDA(cudaEventRecord(q->ev_loss, s));   // the per-sample losses are complete (hb_net_loss_event)
   // 5. backward: the dZ chain (critical path) on the main stream, the weight / bias gradients of
   //    every layer on the side stream as soon as that layer's dZ exists
   const float invB = 1.0f / (float)B;

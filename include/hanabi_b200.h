@@ -296,6 +296,11 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,
                  float* d_loss_out, float* d_mean_loss, void* stream);
+/* cudaEvent_t recorded on the caller's stream by the last hb_net_grads / hb_net_grads_rainbow call at the
+ * point where the per-sample losses (d_loss_out) are complete: work that needs nothing but the losses --
+ * PriorityBuffer.update_priorities, hanabi_agents/rlax_dqn/rlax_rainbow.py:331-334 -- can wait on it and
+ * run beside the backward pass. */
+void* hb_net_loss_event(hb_qnet* q);
 /* The same with the TF-Rainbow target of rainbow/rainbow_agent.py:183-236 (the `rainbow/` package's
  * learner): next action = argmax over the LEGAL next moves (d_legal_t, packed) of the
  * TARGET network's q; gamma^n masked by d_term_t (:191-197); d_weights = the caller's importance weights
@@ -326,10 +331,11 @@ float* hb_learner_loss(hb_learner* L);
 float* hb_learner_mean_loss(hb_learner* L);
 int64_t* hb_learner_indices(hb_learner* L);
 /* Phase A: sample_batch (priority_buffer.py:36-46; h_keys = the B stratified keys, float32 as
- * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss).  HOST arrays. */
+ * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss); update_priorities(indices, |loss|)
+ * (rlax_rainbow.py:331-334) runs beside the backward pass as soon as the losses exist.  HOST arrays. */
 int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                      int mask_terminal, void* stream);
-/* Phase B: optix.adam on grad_scale * bucket, then update_priorities(indices, |loss|). */
+/* Phase B: optix.adam on grad_scale * bucket. */
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
                      void* stream);
 

@@ -632,12 +632,31 @@ def main():
     ap.add_argument("--no-session", action="store_true")
     ap.add_argument("--session-ticks", type=int, default=100)
     args = ap.parse_args()
-    if args.impl == "reference":
-        if args.steps > 2048:
-            args.steps = 2048    # bounded sample: ~23 ms per 65,536-game step on 8 host cores
-        run_reference(args)
-    else:
-        run_ours(args)
+    # Only the JSON line may reach stdout: libraries print there too (NCCL announces its version on
+    # stdout when NCCL_DEBUG is set), so file descriptor 1 points at stderr while the benchmark runs.
+    sys.stdout.flush()
+    real_stdout = os.dup(1)
+    os.dup2(2, 1)
+    import io
+    captured = io.StringIO()
+    py_stdout, sys.stdout = sys.stdout, captured
+    try:
+        if args.impl == "reference":
+            if args.steps > 2048:
+                args.steps = 2048    # bounded sample: ~23 ms per 65,536-game step on 8 host cores
+            run_reference(args)
+        else:
+            run_ours(args)
+    finally:
+        sys.stdout = py_stdout
+        sys.stdout.flush()
+        os.dup2(real_stdout, 1)
+        os.close(real_stdout)
+    lines = [ln for ln in captured.getvalue().splitlines() if ln.strip()]
+    for ln in lines[:-1]:
+        sys.stderr.write(ln + "\n")
+    if lines:
+        print(lines[-1], flush=True)
 
 
 if __name__ == "__main__":

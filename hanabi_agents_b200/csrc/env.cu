@@ -21,6 +21,12 @@ struct hb_env {
   // work queue of the fused self-play kernel (SpQueue below): [head, tail] + group[G] + state[G]
   unsigned long long* spq = nullptr;
   int spq_groups = 0;
+  // A self-play launch may overlap the previous kernel of its stream only when that kernel is this env's
+  // previous self-play launch (it hands the games over through the ring; anything else would have to be
+  // waited for with griddepcontrol.wait to see its memory).  Every other entry point clears the flag.
+  bool spq_chain = false;
+  void* spq_chain_stream = nullptr;
+  const void* spq_chain_hist = nullptr;
   bool is_reset = false;
   // staging for *_host entry points
   void* stage = nullptr;
@@ -622,6 +628,7 @@ int64_t hb_env_info(const hb_env* e, int what) {
 }
 
 int hb_env_set_shard(hb_env* e, int64_t game_id_base, int64_t n_total) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && game_id_base >= 0 && n_total >= game_id_base + e->rt.n_games,
              "hb_env_set_shard: bad shard [%lld, +%lld) of %lld", (long long)game_id_base,
              e ? (long long)e->rt.n_games : 0ll, (long long)n_total);
@@ -632,6 +639,7 @@ int hb_env_set_shard(hb_env* e, int64_t game_id_base, int64_t n_total) {
 }
 
 int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && d_decks && n_decks >= 1, "hb_env_set_decks: bad arguments");
   hb::DeviceGuard g(e->device);
   if (e->decks) { HB_CUDA(cudaStreamSynchronize((cudaStream_t)stream)); cudaFree(e->decks); e->decks = nullptr; }
@@ -647,6 +655,7 @@ int hb_env_set_decks(hb_env* e, const uint8_t* d_decks, int64_t n_decks, void* s
 }
 
 int hb_env_set_decks_host(hb_env* e, const uint8_t* h_decks, int64_t n_decks) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && h_decks && n_decks >= 1, "hb_env_set_decks_host: bad arguments");
   // every deck must be a permutation of the card multiset (HLE deals from exactly that multiset)
   const int bpc = e->C * e->R;
@@ -671,6 +680,7 @@ int hb_env_set_decks_host(hb_env* e, const uint8_t* h_decks, int64_t n_decks) {
 }
 
 int hb_env_reset(hb_env* e, uint32_t* d_obs, uint32_t* d_legal, uint8_t* d_step_type, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e, "hb_env_reset: NULL env");
   if (!e->decks) { hb::set_error("hb_env_reset: call hb_env_set_decks first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
@@ -683,6 +693,7 @@ int hb_env_reset(hb_env* e, uint32_t* d_obs, uint32_t* d_legal, uint8_t* d_step_
 
 int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d_legal,
                 float* d_reward, uint8_t* d_step_type, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && d_action, "hb_env_step: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_env_step: reset the environment first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
@@ -694,6 +705,7 @@ int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d
 }
 
 int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && offset >= 0 && offset < e->P, "hb_env_observe: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_env_observe: reset the environment first"); return HB_ERR_STATE; }
   hb::DeviceGuard g(e->device);
@@ -704,6 +716,7 @@ int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, vo
 }
 
 int hb_env_illegal_count(hb_env* e, int64_t* out, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && out, "hb_env_illegal_count: bad arguments");
   hb::DeviceGuard g(e->device);
   unsigned long long v = 0;
@@ -714,6 +727,7 @@ int hb_env_illegal_count(hb_env* e, int64_t* out, void* stream) {
 }
 
 int hb_env_dump(hb_env* e, int32_t* d_out, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && d_out, "hb_env_dump: bad arguments");
   hb::DeviceGuard g(e->device);
   const int len = (int)hb_env_info(e, 7);
@@ -750,6 +764,7 @@ int hb_env_unpack_legal(hb_env* e, const uint32_t* d_legal, int8_t* d_out, int64
 int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, const int32_t* rule_iarg,
                  int n_rules, uint64_t seed, uint64_t step, int32_t* d_action, int32_t* d_rule_hit,
                  uint64_t* d_hist, void* stream) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && d_action, "hb_rules_act: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_rules_act: reset the environment first"); return HB_ERR_STATE; }
   RuleSet rs;
@@ -789,9 +804,10 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   }
   SpQueue q{e->spq, e->spq + 1, (int*)(e->spq + 2), (int*)(e->spq + 2) + n_groups, n_groups};
   // consecutive self-play launches may overlap (see SpQueue); any other kernel is ordered as usual
+  const bool chained = e->spq_chain && e->spq_chain_stream == stream && e->spq_chain_hist == (const void*)d_hist;
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  attr[0].val.programmaticStreamSerializationAllowed = chained ? 1 : 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3((unsigned)n_groups);
   cfg.blockDim = dim3(kThreads);
@@ -813,6 +829,9 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                                               e->illegal, q)));
   }
   HB_CUDA(lerr);
+  e->spq_chain = true;
+  e->spq_chain_stream = stream;
+  e->spq_chain_hist = (const void*)d_hist;
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -820,6 +839,7 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
 // Host-buffer step: what a binding with numpy arguments calls (copies inside).
 int hb_env_step_host(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
                      float* h_reward, uint8_t* h_step_type) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && h_action, "hb_env_step_host: bad arguments");
   hb::DeviceGuard g(e->device);
   const size_t n = (size_t)e->rt.n_games;
@@ -894,6 +914,7 @@ inline long long chunk_games(const hb_env* e, int chunks) {
 
 int hb_env_step_host_async(hb_env* e, const int32_t* h_action, uint32_t* h_obs, uint32_t* h_legal,
                            float* h_reward, uint8_t* h_step_type, int chunks) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && h_action && chunks >= 1 && chunks <= hb_env::kMaxChunks,
              "hb_env_step_host_async: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_env_step_host_async: reset the environment first"); return HB_ERR_STATE; }
@@ -944,6 +965,7 @@ int hb_env_step_host_async(hb_env* e, const int32_t* h_action, uint32_t* h_obs, 
 int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                             const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
                             int32_t* h_action, uint64_t* d_hist) {
+  if (e) e->spq_chain = false;
   HB_REQUIRE(e && h_action, "hb_rules_act_host_async: bad arguments");
   HB_REQUIRE(e->h_chunks >= 1, "hb_rules_act_host_async: call hb_env_step_host_async first");
   RuleSet rs;

@@ -222,6 +222,46 @@ def test_fused_selfplay_equals_stepwise():
     np.testing.assert_array_equal(env.dump(), ora.dump())
 
 
+@pytest.mark.parametrize("name,players,n", [("Hanabi-Full", 2, 5000), ("Hanabi-Full", 5, 700),
+                                            ("Hanabi-Small", 2, 64)])
+def test_back_to_back_selfplay_launches_overlap_safely(name, players, n):
+    """Consecutive self-play launches overlap on the device (programmatic dependent launch; game groups
+    are handed from one launch to the next through a FIFO ring): many short launches in a row, with
+    different step counts and separate output buffers, interleaved with stepwise calls, must produce
+    exactly the oracle's games."""
+    import torch
+    env, ora = _pair(name, players, n, 3 * n + 7)
+    agent, orules = _rules("piers")
+    env.reset(); ora.reset()
+    t = 0
+    launches = []
+    for rep in range(3):
+        for T in (1, 7, 2, 33, 5, 1, 16):
+            launches.append((t, T, env.selfplay(agent, T, obs="alloc", legal="alloc", reward="alloc",
+                                                step_type="alloc", action="alloc")))
+            t += T
+        torch.cuda.synchronize()
+        for t0, T, (obs, legal, rew, st, act) in launches:
+            for k in range(T):
+                oa, _ = ora.rules_act(orules, 77, t0 + k)
+                ora.step(oa)
+                np.testing.assert_array_equal(act[k].cpu().numpy(), oa)
+                np.testing.assert_array_equal(rew[k].cpu().numpy(), ora.reward)
+                np.testing.assert_array_equal(st[k].cpu().numpy(), ora.step_type)
+            np.testing.assert_array_equal(env.unpack_obs(obs[T - 1]).cpu().numpy().astype(np.uint8), ora.obs)
+        launches = []
+        np.testing.assert_array_equal(env.dump(), ora.dump())
+        # a stepwise move between two runs of fused launches (ordinary stream order)
+        a = agent.explore(env)
+        oa, _ = ora.rules_act(orules, 77, t)
+        np.testing.assert_array_equal(a.cpu().numpy(), oa)
+        env.step(a); ora.step(oa)
+        t += 1
+        agent._step = t
+    if name == "Hanabi-Full":      # (the rules hard-code 8 information tokens: illegal discards on Hanabi-Small)
+        assert env.illegal_count() == 0
+
+
 def test_sharded_envs_equal_one_env():
     """Two shards (game_id_base) reproduce the games of one big env: no data-path collective."""
     from hanabi_agents_b200.env import HanabiParallelEnv

@@ -21,6 +21,7 @@ struct hb_env {
   // work queue of the fused self-play kernel (SpQueue below): [head, tail] + group[G] + state[G]
   unsigned long long* spq = nullptr;
   int spq_groups = 0;
+  unsigned long long spq_seq = 0;   // self-play launches so far
   // A self-play launch may overlap the previous kernel of its stream only when that kernel is this env's
   // previous self-play launch (it hands the games over through the ring; anything else would have to be
   // waited for with griddepcontrol.wait to see its memory).  Every other entry point clears the flag.
@@ -203,18 +204,23 @@ rules_act_kernel(Rt rt, const uint32_t* __restrict__ state, RuleSet rs, unsigned
 // the previous launch's CTAs refill as they finish.  A group that finished early (light sub-partition)
 // starts its next 64 steps early, wherever a slot is free, so over a run of launches every group sees
 // the average load instead of some groups always the worst.  Every launch pops each group exactly once
-// (FIFO: pop ticket i of launch k+1 is push ticket i of launch k); results do not depend on the order.
+// (FIFO: the i-th CTA of launch k+1 to start takes the i-th group launch k finished; the push index is
+// counted per launch, because a CTA of launch k+1 may well finish before the last CTA of launch k);
+// results do not depend on the order.
+constexpr int kSpqLaunches = 8;   // push counters: launch seq uses counter seq % 8
 struct SpQueue {
-  unsigned long long* head;     // next pop ticket
-  unsigned long long* tail;     // next push ticket
+  unsigned long long* head;     // next pop ticket (launch `seq` takes tickets [seq * G, (seq + 1) * G))
+  unsigned long long* pushes;   // [kSpqLaunches] groups handed on so far by the launches of each residue
   int* group;                   // [G] ring: group ids
-  int* state;                   // [G] 2r+1: filled in round r, 2r+2: consumed
+  int* state;                   // [G] 2r+1: filled for launch r, 2r+2: taken by launch r
   int n_groups;
+  unsigned long long seq;       // number of this launch (self-play launches of this env so far)
 };
 
 __global__ void spq_init_kernel(SpQueue q) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
-  if (i == 0) { *q.head = 0ull; *q.tail = (unsigned long long)q.n_groups; }
+  if (i == 0) *q.head = 0ull;
+  if (i < kSpqLaunches) q.pushes[i] = 0ull;
   if (i < q.n_groups) { q.group[i] = i; q.state[i] = 1; }
 }
 
@@ -317,12 +323,19 @@ selfplay_kernel(Rt rt, uint32_t* __restrict__ state, const uint8_t* __restrict__
   if (hist != nullptr && threadIdx.x <= rs.n && shist[threadIdx.x] != 0)
     atomicAdd(&hist[threadIdx.x], (unsigned long long)shist[threadIdx.x]);
   if (threadIdx.x == 0) {                                       // ... before the group is handed on
-    const unsigned long long t = atomicAdd(q.tail, 1ull);
-    const int slot = (int)(t % (unsigned long long)q.n_groups);
-    const int round = (int)(t / (unsigned long long)q.n_groups);
-    spq_wait(q.state + slot, 2 * round);                        // last round's entry has been taken
+    // i-th group this launch finishes -> slot i, for launch seq + 1.  The counter of residue seq % 8 has
+    // seen (seq / 8) * G pushes once launch seq - 8 is through (it nearly always is: bounded wait).
+    unsigned long long* ctr = q.pushes + (q.seq % kSpqLaunches);
+    const unsigned long long base = (q.seq / kSpqLaunches) * (unsigned long long)q.n_groups;
+    for (long long spins = 0; *(volatile unsigned long long*)ctr < base; ++spins) {
+      __nanosleep(64);
+      if (spins > (1ll << 24)) __trap();
+    }
+    const int slot = (int)(atomicAdd(ctr, 1ull) - base);
+    const int next = (int)(q.seq + 1);
+    spq_wait(q.state + slot, 2 * next);                         // this launch has taken the slot's last entry
     __stcg(q.group + slot, group);
-    st_release_gpu(q.state + slot, 2 * round + 1);
+    st_release_gpu(q.state + slot, 2 * next + 1);
   }
 }
 
@@ -796,13 +809,16 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   hb::DeviceGuard g(e->device);
   const int n_groups = (int)grid_for(e);
   if (e->spq == nullptr) {
-    HB_CUDA(cudaMalloc(&e->spq, 16 + (size_t)n_groups * 8));
+    HB_CUDA(cudaMalloc(&e->spq, 8 * (1 + kSpqLaunches) + (size_t)n_groups * 8));
     e->spq_groups = n_groups;
-    SpQueue q0{e->spq, e->spq + 1, (int*)(e->spq + 2), (int*)(e->spq + 2) + n_groups, n_groups};
+    e->spq_seq = 0;
+    SpQueue q0{e->spq, e->spq + 1, (int*)(e->spq + 1 + kSpqLaunches),
+               (int*)(e->spq + 1 + kSpqLaunches) + n_groups, n_groups, 0ull};
     spq_init_kernel<<<(n_groups + 255) / 256, 256, 0, (cudaStream_t)stream>>>(q0);
     HB_CUDA(cudaGetLastError());
   }
-  SpQueue q{e->spq, e->spq + 1, (int*)(e->spq + 2), (int*)(e->spq + 2) + n_groups, n_groups};
+  SpQueue q{e->spq, e->spq + 1, (int*)(e->spq + 1 + kSpqLaunches),
+            (int*)(e->spq + 1 + kSpqLaunches) + n_groups, n_groups, e->spq_seq};
   // consecutive self-play launches may overlap (see SpQueue); any other kernel is ordered as usual
   const bool chained = e->spq_chain && e->spq_chain_stream == stream && e->spq_chain_hist == (const void*)d_hist;
   cudaLaunchAttribute attr[1];
@@ -829,6 +845,7 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                                               e->illegal, q)));
   }
   HB_CUDA(lerr);
+  ++e->spq_seq;
   e->spq_chain = true;
   e->spq_chain_stream = stream;
   e->spq_chain_hist = (const void*)d_hist;

@@ -262,6 +262,36 @@ def test_back_to_back_selfplay_launches_overlap_safely(name, players, n):
         assert env.illegal_count() == 0
 
 
+def test_overlapping_launches_at_benchmark_size_equal_serialised_launches():
+    """The benchmark's pattern: launches of 64 steps over 65,536 games, back to back (they overlap on the
+    device), every launch into its own buffers -- against the same launches with a device synchronisation
+    after each (no overlap).  Every output bit must agree."""
+    import torch
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    n, T, L = 65536, 64, 5
+    outs = []
+    for serialise in (False, True):
+        env = HanabiParallelEnv(n, "Hanabi-Full", 2, n_decks=2 * n, seed=11)
+        agent, _ = _rules("piers")
+        env.reset()
+        bufs = [env.selfplay(agent, T, obs="alloc", legal="alloc", reward="alloc", step_type="alloc",
+                             action="alloc") for _ in range(1)]
+        torch.cuda.synchronize()
+        for _ in range(L - 1):
+            bufs.append(env.selfplay(agent, T, obs="alloc", legal="alloc", reward="alloc", step_type="alloc",
+                                     action="alloc"))
+            if serialise:
+                torch.cuda.synchronize()
+        torch.cuda.synchronize()
+        outs.append((bufs, env.dump(), env.illegal_count(), agent.histogram))
+    (a, da, ia, ha), (b, db, ib, hb_) = outs
+    np.testing.assert_array_equal(da, db)
+    assert ia == ib == 0 and ha == hb_
+    for x, y in zip(a, b):
+        for u, v in zip(x, y):
+            assert torch.equal(u, v)
+
+
 def test_sharded_envs_equal_one_env():
     """Two shards (game_id_base) reproduce the games of one big env: no data-path collective."""
     from hanabi_agents_b200.env import HanabiParallelEnv
@@ -285,20 +315,26 @@ def test_sharded_envs_equal_one_env():
                                   torch.cat([p.obs_packed for p in parts]).cpu().numpy())
 
 
-def test_full_size_cfg2_properties_and_oracle():
-    """BASELINE cfg 2 size: 65,536 Hanabi-Full 2p games, rule-based self-play."""
-    n, T = 65536, 100
-    env, ora = _pair("Hanabi-Full", 2, n, 4 * 65536, threads=32)
+@pytest.mark.parametrize("players,n,T", [(2, 65536, 100), (2, 131072, 70), (5, 32768, 90)])
+def test_full_size_properties_and_oracle(players, n, T):
+    """BASELINE sizes per GPU: cfg 2 (65,536 Hanabi-Full 2p games), the shard of cfg 4 (1,048,576 games over
+    8 GPUs) and of cfg 5 (262,144 Hanabi-Full 5p games over 8 GPUs), rule-based self-play in launches of
+    at most 64 steps (the launches overlap on the device)."""
+    env, ora = _pair("Hanabi-Full", players, n, 2 * n + 3, threads=32)
     agent, orules = _rules("piers")
     env.reset(); ora.reset()
-    env.selfplay(agent, T)                         # no outputs kept: state only
+    done = 0
+    while done < T:                                # no outputs kept: state only
+        k = min(64, T - done)
+        env.selfplay(agent, k)
+        done += k
     for t in range(T):
         oa, _ = ora.rules_act(orules, 77, t)
         ora.step(oa)
     d = env.dump()
     np.testing.assert_array_equal(d, ora.dump())
     # size-independent invariants (A.6): card conservation, token ranges
-    C, P, H = 5, 2, 5
+    C, P, H = 5, players, 5 if players <= 3 else 4
     hand_n = d[:, 8 + C:8 + C + P].sum(1)
     disc = d[:, 8 + C + P + 5 * P * H:8 + C + P + 5 * P * H + 25].sum(1)
     assert np.all(d[:, 3] + hand_n + disc + d[:, 8:8 + C].sum(1) == 50)

@@ -509,25 +509,32 @@ def run_ours(args):
     # ---- e2e: same workload through the host-buffer API: actions come from pinned host memory
     # each step, observation / legal / reward / step type are read back to the host each step.
     e_steps = min(args.steps, args.e2e_steps)
-    hb = env.host_buffers()                                       # pinned host arrays
-    hb["actions"].copy_(agent.explore(env).cpu())
+    sets = [env.host_buffers(), env.host_buffers()]              # pinned host arrays, two sets
+    acts = [sets[0]["actions"], sets[0]["next_actions"], sets[1]["actions"]]
+    acts[0].copy_(agent.explore(env).cpu())
     torch.cuda.synchronize()
+    e2e_t = [0]
 
     def e2e_step():
-        # observations = env.step(actions); actions = agent.explore(observations), host arrays both ways:
-        # a chunked pipeline over PCIe (include/hanabi_b200.h: hb_env_step_host_async)
-        env.step_host_async(hb["actions"], hb["obs"], hb["legal"], hb["reward"], hb["step_type"],
-                            chunks=args.e2e_chunks)
-        agent.explore_host_async(env, hb["next_actions"])
-        env.host_wait()
-        hb["actions"], hb["next_actions"] = hb["next_actions"], hb["actions"]
+        # observations = env.step(actions); actions = agent.explore(observations), host arrays both ways,
+        # double-buffered (include/hanabi_b200.h: hb_env_step_host_begin): the next step's actions go up
+        # while this step's 6 MB of outputs are still coming down; the host waits for the actions only
+        t = e2e_t[0]
+        cur, nxt, hs = acts[t % 3], acts[(t + 1) % 3], sets[t & 1]
+        env.step_host_begin(cur)
+        agent.explore_host_async(env, nxt)
+        env.step_host_outputs(hs["obs"], hs["legal"], hs["reward"], hs["step_type"])
+        env.host_wait_actions()
+        e2e_t[0] = t + 1
 
     for _ in range(3):
         e2e_step()
+    env.host_wait()
     barrier()
     t0 = time.perf_counter()
     for _ in range(e_steps):
         e2e_step()
+    env.host_wait()                                                # every output of every step is on the host
     barrier()
     e_s = time.perf_counter() - t0
     te = torch.tensor([e_s], device=dev)
@@ -594,11 +601,12 @@ def run_ours(args):
                                      "launch + per-group FIFO hand-over); roofline.launch_ms = timed region / launches"},
         "clocks": clocks.summary(),
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e_steps, "chunks": args.e2e_chunks,
-                "path": "per step, host in the loop, pinned host arrays both ways: env.step_host_async (per chunk: "
-                "actions H2D, env_step_kernel, D2H of observation rows (%d B) + legal mask + reward + step type) "
-                "| agent.explore_host_async (per chunk: rules_act_kernel + actions D2H on a third stream) | "
-                "env.host_wait" % (4 * env.obs_words)},
+                "steps": e_steps,
+                "path": "per step, host in the loop, pinned host arrays both ways, double-buffered: env.step_host_begin "
+                "(actions H2D, env_step_kernel) | agent.explore_host_async (rules_act_kernel + next actions D2H) | "
+                "env.step_host_outputs (D2H of observation rows (%d B) + legal mask + reward + step type in one copy, "
+                "alternating two host sets) | env.host_wait_actions; env.host_wait at the end of the timed region"
+                % (4 * env.obs_words)},
         "gpu_launches": launches,
         "roofline": roof,
         "cpu_baseline": cpu,

@@ -64,6 +64,11 @@ SIGNATURES = {
     "hb_env_step_host_async": (i32, [vp, vp, vp, vp, vp, vp, i32]),
     "hb_rules_act_host_async": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp]),
     "hb_env_host_wait": (i32, [vp]),
+    "hb_env_step_host_begin": (i32, [vp, vp]),
+    "hb_env_step_host_outputs": (i32, [vp, vp, vp, vp, vp]),
+    "hb_env_host_wait_actions": (i32, [vp]),
+    "hb_env_host_wait_outputs": (i32, [vp, i32]),
+    "hb_env_host_slot": (i32, [vp]),
     # rule-based agents
     "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
     "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),

@@ -38,6 +38,11 @@ struct hb_env {
   cudaEvent_t hev_step[kMaxChunks] = {};
   cudaEvent_t hev_done = nullptr;
   int h_chunks = 0;
+  // double-buffered variant (hb_env_step_host_begin / _outputs / hb_env_host_wait_actions): staging slot of
+  // the step in flight, "outputs of slot s are on the host" and "the agent has read the state" events
+  int h_slot = 0;
+  cudaEvent_t hev_out[2] = {nullptr, nullptr};
+  cudaEvent_t hev_rules = nullptr, hev_acts = nullptr;   // hev_acts: the next actions have left for the host
 };
 
 namespace {
@@ -620,6 +625,10 @@ int hb_env_destroy(hb_env* e) {
   for (int c = 0; c < hb_env::kMaxChunks; ++c)
     if (e->hev_step[c]) cudaEventDestroy(e->hev_step[c]);
   if (e->hev_done) cudaEventDestroy(e->hev_done);
+  if (e->hev_out[0]) cudaEventDestroy(e->hev_out[0]);
+  if (e->hev_out[1]) cudaEventDestroy(e->hev_out[1]);
+  if (e->hev_rules) cudaEventDestroy(e->hev_rules);
+  if (e->hev_acts) cudaEventDestroy(e->hev_acts);
   delete e;
   return HB_OK;
 }
@@ -897,7 +906,7 @@ namespace {
 struct StagePlan {
   int32_t* act; uint32_t* obs; uint32_t* leg; float* rew; uint8_t* st; int32_t* act_out;
 };
-int host_pipe_init(hb_env* e, int obs_words, StagePlan* p) {
+int host_pipe_init(hb_env* e, int obs_words, StagePlan* p, int slot = 0) {
   if (!e->hs_step) {
     HB_CUDA(cudaStreamCreateWithFlags(&e->hs_step, cudaStreamNonBlocking));
     HB_CUDA(cudaStreamCreateWithFlags(&e->hs_out, cudaStreamNonBlocking));
@@ -905,6 +914,10 @@ int host_pipe_init(hb_env* e, int obs_words, StagePlan* p) {
     for (int c = 0; c < hb_env::kMaxChunks; ++c)
       HB_CUDA(cudaEventCreateWithFlags(&e->hev_step[c], cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&e->hev_done, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&e->hev_out[0], cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&e->hev_out[1], cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&e->hev_rules, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&e->hev_acts, cudaEventDisableTiming));
   }
   const size_t n = (size_t)e->rt.n_games;
   auto up = [](size_t b) { return (b + 255) / 256 * 256; };
@@ -912,9 +925,10 @@ int host_pipe_init(hb_env* e, int obs_words, StagePlan* p) {
   // out the same way -- HanabiParallelEnv.host_buffers -- are filled by ONE copy per chunk
   const size_t b_act = up(n * 4), b_obs = n * obs_words * 4, b_leg = n * e->legal_words * 4,
                b_rew = n * 4, b_st = up(n);
-  int rc = env_stage(e, 2 * b_act + b_obs + b_leg + b_rew + b_st);
+  const size_t b_all = 2 * b_act + b_obs + b_leg + b_rew + b_st;       // two staging sets
+  int rc = env_stage(e, 2 * b_all);
   if (rc) return rc;
-  char* q = (char*)e->stage;
+  char* q = (char*)e->stage + (size_t)(slot & 1) * b_all;
   p->act = (int32_t*)q; q += b_act;
   p->obs = (uint32_t*)q; q += b_obs;
   p->leg = (uint32_t*)q; q += b_leg;
@@ -938,10 +952,11 @@ int hb_env_step_host_async(hb_env* e, const int32_t* h_action, uint32_t* h_obs, 
   hb::DeviceGuard g(e->device);
   const int obs_words = (e->obs_len + 31) / 32;
   StagePlan p;
-  int rc = host_pipe_init(e, obs_words, &p);
+  int rc = host_pipe_init(e, obs_words, &p, e->h_slot);
   if (rc) return rc;
   // what the previous pipeline pass still reads or writes must be done before the staging is reused
   HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_done, 0));
+  HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_out[e->h_slot], 0));
   const long long n = e->rt.n_games, per = chunk_games(e, chunks);
   int used = 0;
   for (long long first = 0; first < n; first += per, ++used) {
@@ -990,7 +1005,7 @@ int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* ru
   if (rc) return rc;
   hb::DeviceGuard g(e->device);
   StagePlan p;
-  rc = host_pipe_init(e, (e->obs_len + 31) / 32, &p);
+  rc = host_pipe_init(e, (e->obs_len + 31) / 32, &p, e->h_slot);
   if (rc) return rc;
   const bool ext = uses_ext_rules(rs);
   const long long n = e->rt.n_games, per = chunk_games(e, e->h_chunks);
@@ -1007,10 +1022,95 @@ int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* ru
                          e->rt, e->state, rs, step, p.act_out, nullptr, (unsigned long long*)d_hist, first, cnt)));
     }
     HB_CUDA(cudaGetLastError());
+    HB_CUDA(cudaEventRecord(e->hev_rules, e->hs_act));          // the state has been read
     HB_CUDA(cudaMemcpyAsync(h_action + first, p.act_out + first, (size_t)cnt * 4, cudaMemcpyDeviceToHost, e->hs_act));
   }
+  HB_CUDA(cudaEventRecord(e->hev_acts, e->hs_act));
   return HB_OK;
 }
+
+// ---- double-buffered host loop ------------------------------------------------------------------
+// One step of the host-in-the-loop pattern is bound by its 6 MB of outputs crossing PCIe (114 us) plus
+// ~40 us of dependent small work (actions up, step kernel, agent kernel, next actions down).  With two
+// staging sets the next step's small work runs while this step's outputs are still on the wire:
+//   hb_env_step_host_begin(actions)    actions H2D + env_step_kernel into the other staging set
+//   hb_rules_act_host_async(next)      agent kernel + the next actions D2H (small, queued FIRST)
+//   hb_env_step_host_outputs(bufs)     the step's outputs D2H (large), into host buffers the caller alternates
+//   hb_env_host_wait_actions()         returns when `next` is on the host; the outputs may still be in flight
+// hb_env_host_wait_outputs(slot) / hb_env_host_wait() tell when host buffers are complete.
+int hb_env_step_host_begin(hb_env* e, const int32_t* h_action) {
+  if (e) e->spq_chain = false;
+  HB_REQUIRE(e && h_action, "hb_env_step_host_begin: bad arguments");
+  if (!e->is_reset) { hb::set_error("hb_env_step_host_begin: reset the environment first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  const int obs_words = (e->obs_len + 31) / 32;
+  e->h_slot ^= 1;
+  StagePlan p;
+  int rc = host_pipe_init(e, obs_words, &p, e->h_slot);
+  if (rc) return rc;
+  // this staging set was last used two steps ago: its outputs must have left, and the agent of the previous
+  // step must have read the state this step changes
+  HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_out[e->h_slot], 0));
+  HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_rules, 0));
+  HB_CUDA(cudaStreamWaitEvent(e->hs_step, e->hev_done, 0));
+  const long long n = e->rt.n_games;
+  HB_CUDA(cudaMemcpyAsync(p.act, h_action, (size_t)n * 4, cudaMemcpyHostToDevice, e->hs_step));
+  HB_DISPATCH(e, (env_step_kernel<SH><<<grid_for(e), kThreads, 0, e->hs_step>>>(
+                     e->rt, e->state, e->decks, p.act, p.obs, p.leg, p.rew, p.st, e->illegal, 0, n, obs_words)));
+  HB_CUDA(cudaGetLastError());
+  HB_CUDA(cudaEventRecord(e->hev_step[0], e->hs_step));
+  e->h_chunks = 1;
+  return HB_OK;
+}
+
+int hb_env_step_host_outputs(hb_env* e, uint32_t* h_obs, uint32_t* h_legal, float* h_reward,
+                             uint8_t* h_step_type) {
+  HB_REQUIRE(e && e->h_chunks == 1, "hb_env_step_host_outputs: call hb_env_step_host_begin first");
+  hb::DeviceGuard g(e->device);
+  const int obs_words = (e->obs_len + 31) / 32;
+  StagePlan p;
+  int rc = host_pipe_init(e, obs_words, &p, e->h_slot);
+  if (rc) return rc;
+  const size_t n = (size_t)e->rt.n_games;
+  HB_CUDA(cudaStreamWaitEvent(e->hs_out, e->hev_step[0], 0));
+  // The large copy is ready before the agent's small one (it needs only the step kernel) and would take
+  // the copy engine first: the host would then get its next actions only after 6 MB had crossed.  Behind
+  // the actions it costs the loop nothing, and the next step's work overlaps it.
+  HB_CUDA(cudaStreamWaitEvent(e->hs_out, e->hev_acts, 0));
+  const bool whole = h_obs && h_legal && h_reward && h_step_type &&
+                     (char*)h_legal == (char*)h_obs + n * obs_words * 4 &&
+                     (char*)h_reward == (char*)h_legal + n * e->legal_words * 4 &&
+                     (char*)h_step_type == (char*)h_reward + n * 4;
+  if (whole) {
+    HB_CUDA(cudaMemcpyAsync(h_obs, p.obs, n * (obs_words * 4 + e->legal_words * 4 + 4 + 1),
+                            cudaMemcpyDeviceToHost, e->hs_out));
+  } else {
+    if (h_obs) HB_CUDA(cudaMemcpyAsync(h_obs, p.obs, n * obs_words * 4, cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_legal) HB_CUDA(cudaMemcpyAsync(h_legal, p.leg, n * e->legal_words * 4, cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_reward) HB_CUDA(cudaMemcpyAsync(h_reward, p.rew, n * 4, cudaMemcpyDeviceToHost, e->hs_out));
+    if (h_step_type) HB_CUDA(cudaMemcpyAsync(h_step_type, p.st, n, cudaMemcpyDeviceToHost, e->hs_out));
+  }
+  HB_CUDA(cudaEventRecord(e->hev_out[e->h_slot], e->hs_out));
+  return HB_OK;
+}
+
+int hb_env_host_wait_actions(hb_env* e) {
+  HB_REQUIRE(e, "hb_env_host_wait_actions: NULL env");
+  if (!e->hs_act) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  HB_CUDA(cudaStreamSynchronize(e->hs_act));
+  return HB_OK;
+}
+
+int hb_env_host_wait_outputs(hb_env* e, int slot) {
+  HB_REQUIRE(e && (slot == 0 || slot == 1), "hb_env_host_wait_outputs: bad arguments");
+  if (!e->hs_out) return HB_OK;
+  hb::DeviceGuard g(e->device);
+  HB_CUDA(cudaEventSynchronize(e->hev_out[slot]));
+  return HB_OK;
+}
+
+int hb_env_host_slot(const hb_env* e) { return e ? e->h_slot : -1; }
 
 int hb_env_host_wait(hb_env* e) {
   HB_REQUIRE(e, "hb_env_host_wait: NULL env");

@@ -190,6 +190,25 @@ class HanabiParallelEnv:
     def host_wait(self):
         _lib.check(_lib.lib().hb_env_host_wait(self._h))
 
+    # ---- the same loop double-buffered (include/hanabi_b200.h: hb_env_step_host_begin) ----------
+    def step_host_begin(self, actions):
+        """First half of `environment.step(actions)` with host arrays: actions up + the step kernel."""
+        _lib.check(_lib.lib().hb_env_step_host_begin(self._h, actions.data_ptr()))
+
+    def step_host_outputs(self, obs=None, legal=None, reward=None, step_type=None):
+        """Second half: the step's outputs start their way to the host arrays (alternate two sets);
+        complete after `host_wait_outputs(slot)` / `host_wait()`.  Returns the staging slot."""
+        p = lambda t: None if t is None else t.data_ptr()
+        _lib.check(_lib.lib().hb_env_step_host_outputs(self._h, p(obs), p(legal), p(reward), p(step_type)))
+        return int(_lib.lib().hb_env_host_slot(self._h))
+
+    def host_wait_actions(self):
+        """Returns when the agent's next actions (explore_host_async) are on the host."""
+        _lib.check(_lib.lib().hb_env_host_wait_actions(self._h))
+
+    def host_wait_outputs(self, slot):
+        _lib.check(_lib.lib().hb_env_host_wait_outputs(self._h, int(slot)))
+
     def observe(self, offset=0, out=None):
         """HanabiObservation of the player `offset` seats after the mover, for every game
         (bit-packed rows + legal masks; `out` = (obs, legal) reuses caller-owned buffers)."""

@@ -153,6 +153,19 @@ int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* ru
                             const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
                             int32_t* h_action, uint64_t* d_hist);
 int hb_env_host_wait(hb_env* e);
+/* The same loop double-buffered: the next step's small dependent work (actions up, step kernel, agent
+ * kernel, next actions down) runs while this step's outputs are still crossing PCIe.  Per step:
+ *   hb_env_step_host_begin(actions)  ->  hb_rules_act_host_async(next actions)  ->
+ *   hb_env_step_host_outputs(host buffers; the caller alternates two sets)  ->  hb_env_host_wait_actions()
+ * hb_env_host_wait_actions returns when the next actions are on the host (the outputs may still be in
+ * flight); hb_env_host_wait_outputs(slot) when the outputs of staging slot `slot` (hb_env_host_slot: the
+ * slot of the step begun last) are; hb_env_host_wait when everything is. */
+int hb_env_step_host_begin(hb_env* e, const int32_t* h_action);
+int hb_env_step_host_outputs(hb_env* e, uint32_t* h_obs, uint32_t* h_legal, float* h_reward,
+                             uint8_t* h_step_type);
+int hb_env_host_wait_actions(hb_env* e);
+int hb_env_host_wait_outputs(hb_env* e, int slot);
+int hb_env_host_slot(const hb_env* e);
 
 /* ------------------------------------------------------------------------ */
 /* Rule-based agents.  Replaces RulebasedAgent.explore/exploit/get_move        */

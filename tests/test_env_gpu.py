@@ -136,6 +136,46 @@ def test_host_pipeline_matches_device_path(name, players, chunks):
     assert ag.histogram == ag2.histogram
 
 
+@pytest.mark.parametrize("name,players,n", [("Hanabi-Full", 2, 20000), ("Hanabi-Full", 5, 1000)])
+def test_double_buffered_host_loop_matches_oracle(name, players, n):
+    """step_host_begin / explore_host_async / step_host_outputs / host_wait_actions: the next step is begun
+    while the previous step's outputs may still be on the wire; two sets of host arrays alternate.  Every
+    step's outputs, checked one step late (after host_wait_outputs of their slot), must be the oracle's."""
+    from hanabi_agents_b200.rule_based import RulebasedAgent, predefined_rules
+    env, ora = _pair(name, players, n, n + 77)
+    ag = RulebasedAgent(predefined_rules.piers_rules, seed=9)
+    _, orules = _rules("piers")
+    env.reset(); ora.reset()
+    sets = [env.host_buffers(), env.host_buffers()]
+    acts = [sets[0]["actions"], sets[0]["next_actions"], sets[1]["actions"]]   # three rotating action arrays
+    acts[0].copy_(ag.explore(env).cpu())
+    expected = {}
+    pending = None                                   # (slot, host set, step) of the step before
+    for t in range(40):
+        cur, nxt = acts[t % 3], acts[(t + 1) % 3]
+        env.step_host_begin(cur)
+        ag.explore_host_async(env, nxt)
+        hs = sets[t & 1]
+        slot = env.step_host_outputs(hs["obs"], hs["legal"], hs["reward"], hs["step_type"])
+        env.host_wait_actions()
+        # the oracle plays the same move and must come up with the same next move
+        ora.step(cur.numpy())
+        expected[t] = (ora.obs.copy(), ora.legal.copy(), ora.reward.copy(), ora.step_type.copy())
+        oa, _ = ora.rules_act(orules, 9, t + 1)
+        np.testing.assert_array_equal(nxt.numpy(), oa)
+        if pending is not None:
+            pslot, ph, pt = pending
+            env.host_wait_outputs(pslot)
+            eo, el, er, es = expected.pop(pt)
+            bits = np.unpackbits(ph["obs"].numpy().view(np.uint8), axis=1, bitorder="little")[:, :env.obs_len]
+            np.testing.assert_array_equal(bits, eo)
+            np.testing.assert_array_equal(ph["reward"].numpy(), er)
+            np.testing.assert_array_equal(ph["step_type"].numpy(), es)
+        pending = (slot, hs, t)
+    env.host_wait()
+    np.testing.assert_array_equal(env.dump(), ora.dump())
+
+
 def _rules(preset):
     from hanabi_agents_b200.rule_based import RulebasedAgent, predefined_rules
     from oracle.hanabi import PRESETS

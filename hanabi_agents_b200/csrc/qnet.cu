@@ -67,7 +67,7 @@ struct hb_qnet {
   int lb = 0, lbp = 0;
   uint32_t* xb = nullptr;              // [2B, obs_stride] packed rows: obs_tm1 then obs_t
   cudaStream_t side = nullptr;         // second stream: target forward / weight gradients run beside
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_loss = nullptr, ev_dz[kMaxLayers] = {nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_loss = nullptr, ev_wt = nullptr, ev_dz[kMaxLayers] = {nullptr};
   __half* x = nullptr;                 // [2B, K0]
   __half* xt = nullptr;                // [K0, Bp]
   __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
@@ -386,12 +386,13 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds
                                     float grad_scale, int do_update, float lr, float b1, float b2,
                                     float eps, const int* __restrict__ step_ptr, __half* __restrict__ w16,
                                     __half* __restrict__ /*w16t*/, float* __restrict__ beff, int tf_style) {
-  // bias corrections from the device-side step counter (so that the launch can sit in a CUDA graph)
-  float bc1 = 1.f, bc2 = 1.f;
+  // bias corrections of this step, computed once by adam_tick_kernel from the device-side step counter (so
+  // that the launch can sit in a CUDA graph): [1] 1 - b1^t, [2] 1 - b2^t, [3] [4] their reciprocals,
+  // [5] lr sqrt(1 - b2^t) / (1 - b1^t).  (Two powf and 24 IEEE divisions per thread were most of this kernel.)
+  float r1 = 1.f, r2 = 1.f, lr_tf = 0.f;
   if (do_update) {
-    const float t = (float)*step_ptr;
-    bc1 = 1.0f - powf(b1, t);
-    bc2 = 1.0f - powf(b2, t);
+    const float* sc = reinterpret_cast<const float*>(step_ptr);
+    r1 = sc[3]; r2 = sc[4]; lr_tf = sc[5];
   }
   // four consecutive parameters per thread (every block boundary is a multiple of 8 elements)
   const long long n4 = n_eff >> 2;
@@ -431,9 +432,9 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds
           if (tf_style) {
             // tf.train.AdamOptimizer (rainbow_agent.py:228-230): lr_t = lr sqrt(1-b2^t)/(1-b1^t),
             // theta -= lr_t m / (sqrt(v) + eps) -- eps is NOT bias corrected
-            p[j] = p[j] - (lr * sqrtf(bc2) / bc1) * m[j] / (sqrtf(v[j]) + eps);
+            p[j] = p[j] - lr_tf * m[j] / (sqrtf(v[j]) + eps);
           } else {
-            const float mhat = m[j] / bc1, vhat = v[j] / bc2;
+            const float mhat = m[j] * r1, vhat = v[j] * r2;
             p[j] = p[j] - lr * mhat / (sqrtf(vhat) + eps);
           }
         }
@@ -483,7 +484,15 @@ __global__ void transpose16_kernel(LayerTable tab, const __half* __restrict__ w1
   }
 }
 
-__global__ void adam_tick_kernel(int* step) { *step += 1; }
+// step counter and this step's bias corrections: step[0] = t, then as floats [1] 1 - b1^t, [2] 1 - b2^t,
+// [3] [4] their reciprocals, [5] lr sqrt(1 - b2^t) / (1 - b1^t)  (tf.train.AdamOptimizer's lr_t)
+__global__ void adam_tick_kernel(int* step, float b1, float b2, float lr) {
+  const int t = *step + 1;
+  *step = t;
+  float* sc = reinterpret_cast<float*>(step);
+  const float bc1 = 1.0f - powf(b1, (float)t), bc2 = 1.0f - powf(b2, (float)t);
+  sc[1] = bc1; sc[2] = bc2; sc[3] = 1.0f / bc1; sc[4] = 1.0f / bc2; sc[5] = lr * sqrtf(bc2) / bc1;
+}
 __global__ void fill_kernel(float* p, float v, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -529,6 +538,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_fork, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_loss, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_wt, cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
   }
   if ((rc = dev_alloc(&q->xt, (size_t)K0 * Bp))) return rc;
@@ -626,12 +636,21 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
   return HB_OK;
 }
 
+int launch_transposes(hb_qnet* net, cudaStream_t s) {
+  int tiles = 0;
+  for (int l = 0; l < net->n_layers; ++l)
+    tiles += ((net->tab.l[l].N + 31) / 32) * ((net->tab.l[l].K + 31) / 32);
+  transpose16_kernel<<<tiles, 256, 0, s>>>(net->tab, net->w16, net->w16t);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
 int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
              cudaStream_t s, int tf_style = 0) {
   int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
   if (do_update) {
     net->adam_step += 1;                       // host mirror (hb_net_info); the kernels use the device copy
-    adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr);
+    adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr, b1, b2, lr);
     HB_CUDA(cudaGetLastError());
   }
   const long long n4 = net->n_eff / 4;
@@ -645,12 +664,7 @@ int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float ep
                                                   net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
                                                   lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   HB_CUDA(cudaGetLastError());
-  int tiles = 0;
-  for (int l = 0; l < net->n_layers; ++l)
-    tiles += ((net->tab.l[l].N + 31) / 32) * ((net->tab.l[l].K + 31) / 32);
-  transpose16_kernel<<<tiles, 256, 0, s>>>(net->tab, net->w16, net->w16t);
-  HB_CUDA(cudaGetLastError());
-  return HB_OK;
+  return HB_OK;                 // w16t is refreshed by the next hb_net_grads (launch_transposes)
 }
 
 // maps (layer, kind, element of the reference-layout tensor) <-> flat effective index
@@ -758,7 +772,7 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   if (!rc) rc = dev_alloc(&q->t16, (size_t)q->n_w);
   if (!rc) rc = dev_alloc(&q->beff, (size_t)q->n_b);
   if (!rc) rc = dev_alloc(&q->tbeff, (size_t)q->n_b);
-  if (!rc) rc = dev_alloc(&q->scalars, 4);
+  if (!rc) rc = dev_alloc(&q->scalars, 12);      // [0] mean loss [1] max weight [2] Adam step [3..7] its corrections
   if (rc) { hb_net_destroy(q); return rc; }
   *out = q;
   return HB_OK;
@@ -776,6 +790,7 @@ int hb_net_destroy(hb_qnet* q) {
     cudaEventDestroy(q->ev_fork);
     cudaEventDestroy(q->ev_join);
     if (q->ev_loss) cudaEventDestroy(q->ev_loss);
+    if (q->ev_wt) cudaEventDestroy(q->ev_wt);
     for (int l = 0; l < kMaxLayers; ++l) cudaEventDestroy(q->ev_dz[l]);
   }
   dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
@@ -1004,6 +1019,11 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   }
   HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, q->side));
   HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  // transposed effective weights for the dZ chain of the backward pass: refreshed on the side stream while
+  // the main stream computes the loss, instead of behind Adam where they were 8 us of every update's
+  // critical path (ev_wt: waited for before the first dZ GEMM)
+  if ((rc = launch_transposes(q, q->side))) return rc;
+  HB_CUDA(cudaEventRecord(q->ev_wt, q->side));
   // 2. online network on both observation sets (main stream)
   if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
                     fused ? q->xb : nullptr))) return rc;
@@ -1030,6 +1050,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   // 5. backward: the dZ chain (critical path) on the main stream, the weight / bias gradients of
   //    every layer on the side stream as soon as that layer's dZ exists
   const float invB = 1.0f / (float)B;
+  HB_CUDA(cudaStreamWaitEvent(s, q->ev_wt, 0));
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];
     HB_CUDA(cudaEventRecord(q->ev_dz[l], s));              // dz[l] / dzt[l] are complete here

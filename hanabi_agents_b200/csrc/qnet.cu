@@ -67,7 +67,9 @@ struct hb_qnet {
   int lb = 0, lbp = 0;
   uint32_t* xb = nullptr;              // [2B, obs_stride] packed rows: obs_tm1 then obs_t
   cudaStream_t side = nullptr;         // second stream: target forward / weight gradients run beside
-  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_loss = nullptr, ev_wt = nullptr, ev_dz[kMaxLayers] = {nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_loss = nullptr, ev_wt = nullptr,
+              ev_dz[kMaxLayers] = {nullptr};
+  cudaStream_t side2 = nullptr;        // small kernels beside the GEMMs of `side`
   __half* x = nullptr;                 // [2B, K0]
   __half* xt = nullptr;                // [K0, Bp]
   __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
@@ -535,6 +537,8 @@ int ensure_learner_ws(hb_qnet* q, int B) {
   if ((rc = dev_alloc(&q->xb, (size_t)2 * B * q->obs_stride))) return rc;
   if (q->side == nullptr) {
     HB_CUDA(cudaStreamCreateWithFlags(&q->side, cudaStreamNonBlocking));
+    HB_CUDA(cudaStreamCreateWithFlags(&q->side2, cudaStreamNonBlocking));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_join2, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_fork, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_loss, cudaEventDisableTiming));
@@ -787,6 +791,8 @@ int hb_net_destroy(hb_qnet* q) {
   dev_free(q->scalars);
   if (q->side) {
     cudaStreamDestroy(q->side);
+    if (q->side2) cudaStreamDestroy(q->side2);
+    if (q->ev_join2) cudaEventDestroy(q->ev_join2);
     cudaEventDestroy(q->ev_fork);
     cudaEventDestroy(q->ev_join);
     if (q->ev_loss) cudaEventDestroy(q->ev_loss);
@@ -1002,33 +1008,37 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
                     q->n_atoms > 1 ? (tf_variant ? q->q_tg : nullptr) : q->tlogits, ldq, q->side,
                     fused ? q->xb + (size_t)B * row_words : nullptr))) return rc;
+  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  // a second side stream for the small kernels, so that the target network's GEMMs are all `side` runs
+  HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fork, 0));
   {
     const long long tot = (long long)K0 * ((B + 7) / 8);
-    unpack_t_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, q->side>>>(q->xb, q->obs_stride, B, q->xt, Bp);
+    unpack_t_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, q->side2>>>(q->xb, q->obs_stride, B, q->xt, Bp);
     HB_CUDA(cudaGetLastError());
   }
   // importance weights
   if (d_prios) {
-    is_weights_kernel<<<1, 256, 0, q->side>>>(d_prios, B, beta, q->w_is);
+    is_weights_kernel<<<1, 256, 0, q->side2>>>(d_prios, B, beta, q->w_is);
     HB_CUDA(cudaGetLastError());
   } else if (d_weights) {
-    HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, q->side));
+    HB_CUDA(cudaMemcpyAsync(q->w_is, d_weights, (size_t)B * 4, cudaMemcpyDeviceToDevice, q->side2));
   } else {
-    fill_kernel<<<(B + 255) / 256, 256, 0, q->side>>>(q->w_is, 1.f, B);
+    fill_kernel<<<(B + 255) / 256, 256, 0, q->side2>>>(q->w_is, 1.f, B);
     HB_CUDA(cudaGetLastError());
   }
-  HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, q->side));
-  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
-  // transposed effective weights for the dZ chain of the backward pass: refreshed on the side stream while
-  // the main stream computes the loss, instead of behind Adam where they were 8 us of every update's
-  // critical path (ev_wt: waited for before the first dZ GEMM)
-  if ((rc = launch_transposes(q, q->side))) return rc;
-  HB_CUDA(cudaEventRecord(q->ev_wt, q->side));
+  HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, q->side2));
+  HB_CUDA(cudaEventRecord(q->ev_join2, q->side2));
+  // transposed effective weights for the dZ chain of the backward pass: refreshed beside the forward
+  // passes instead of behind Adam where they were 8 us of every update's critical path (ev_wt: waited for
+  // before the first dZ GEMM)
+  if ((rc = launch_transposes(q, q->side2))) return rc;
+  HB_CUDA(cudaEventRecord(q->ev_wt, q->side2));
   // 2. online network on both observation sets (main stream)
   if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
                     fused ? q->xb : nullptr))) return rc;
   HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, s));
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join2, 0));
   // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
   if (q->n_atoms > 1) {
     c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, tf_variant ? q->q_tg : q->q_on + (size_t)B * ldq, ldq,
@@ -1063,7 +1073,8 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
     if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, q->side))) return rc;
-    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, q->side>>>(q->dzt[l], Bp, L.N, B, invB,
+    HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_dz[l], 0));
+    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, q->side2>>>(q->dzt[l], Bp, L.N, B, invB,
                                                         q->grad + L.eoff + (long long)L.N * L.K);
     HB_CUDA(cudaGetLastError());
     if (l > 0) {
@@ -1081,6 +1092,8 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   }
   HB_CUDA(cudaEventRecord(q->ev_join, q->side));
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  HB_CUDA(cudaEventRecord(q->ev_join2, q->side2));
+  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join2, 0));
   return HB_OK;
 }
 

@@ -55,3 +55,7 @@ def tick_and_learn():
 dev, wall = timed(tick_and_learn, ticks)
 print(f"train tick + {upd} update(s) per agent        : {dev:.3f} ms device, {wall:.3f} ms wall -> {n / dev * 1e3:.3e} env-steps/s")
 print("stats", ses.stats(), "illegal", env.illegal_count(), "replay", a0.experience.size, a1.experience.size)
+from hanabi_agents_b200 import _lib  # noqa: E402
+for a in (a0, a1):
+    print("graph captures", int(_lib.lib().hb_learner_info(a._learner, 1)), "eager steps",
+          int(_lib.lib().hb_learner_info(a._learner, 2)), "train_step", a.train_step)

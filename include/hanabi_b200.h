@@ -344,11 +344,12 @@ float* hb_learner_loss(hb_learner* L);
 float* hb_learner_mean_loss(hb_learner* L);
 int64_t* hb_learner_indices(hb_learner* L);
 /* Phase A: sample_batch (priority_buffer.py:36-46; h_keys = the B stratified keys, float32 as
- * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss); update_priorities(indices, |loss|)
- * (rlax_rainbow.py:331-334) runs beside the backward pass as soon as the losses exist.  HOST arrays. */
+ * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss).  HOST arrays.  With HB_LEARNER_PRIO_OVERLAP=1 in
+ * the environment update_priorities(indices, |loss|) (rlax_rainbow.py:331-334) already runs here, beside
+ * the backward pass, instead of in phase B. */
 int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                      int mask_terminal, void* stream);
-/* Phase B: optix.adam on grad_scale * bucket. */
+/* Phase B: optix.adam on grad_scale * bucket, then update_priorities(indices, |loss|). */
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
                      void* stream);
 

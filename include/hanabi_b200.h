@@ -185,7 +185,10 @@ int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                  const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step,
                  int32_t* d_action, int32_t* d_rule_hit, uint64_t* d_hist, void* stream);
 /* Fused self-play: n_steps x {rules act, env step, observe} in one launch with the game state
- * in registers.  Outputs are [n_steps, n_games, ...]; any may be NULL. */
+ * in registers.  Outputs are [n_steps, n_games, ...]; any may be NULL.  Calls that follow each other
+ * directly on one stream overlap on the device (the next launch takes over groups of games as this one
+ * finishes them: programmatic dependent launch + a FIFO ring of group ids); the results do not depend on
+ * it, and any other call or kernel of the stream is ordered as usual. */
 int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                     const int32_t* rule_iarg, int n_rules, uint64_t seed, uint64_t step0,
                     int n_steps, uint32_t* d_obs, uint32_t* d_legal, float* d_reward,

@@ -36,14 +36,14 @@ struct hb_learner {
   // graphs + the scalar arguments they were captured with
   cudaGraphExec_t gA = nullptr, gB = nullptr;
   float kA[3] = {0, 0, 0};       // beta, discount, mask_terminal
+  const void* kA_ptr[3] = {nullptr, nullptr, nullptr};   // the net's staging the graph was captured with
   float kB[5] = {0, 0, 0, 0, 0}; // lr, b1, b2, eps, grad_scale
   int warm = 0;                  // eager steps run (the first one allocates workspaces)
   int recaptures = 0;
   int use_graph = 1;
-  // update_priorities beside the backward pass (HB_LEARNER_PRIO_OVERLAP=1) or after Adam (default): alone the
-  // learner gains 7 % from the overlap (133 vs 143 us per update), but between the replay inserts of a
-  // self-play session a tick with two updates went from 0.70 to 0.87 ms, so it is opt-in
-  int prio_overlap = 0;
+  // update_priorities beside the backward pass (default) or after Adam (HB_LEARNER_PRIO_OVERLAP=0): alone the
+  // learner gains 7 % from the overlap, a self-play session tick with two updates 4 % (0.68 vs 0.70 ms)
+  int prio_overlap = 1;
 };
 
 namespace {
@@ -70,6 +70,27 @@ int phase_b(hb_learner* L, float lr, float b1, float b2, float eps, float grad_s
   int rc = hb_net_adam(L->net, lr, b1, b2, eps, grad_scale, s);
   if (!rc && L->prioritized && !L->prio_overlap) rc = hb_rb_update_priorities(L->rb, L->d_idx, L->loss, L->B, s);
   return rc;
+}
+
+// The packed rows are gathered straight into the network's staging and the losses are read where the
+// network leaves them (hb_net_learner_buffers): four device-to-device copies less on the critical path of
+// every update.  Should the network ever reallocate them, both graphs are captured again.
+int borrow_net_buffers(hb_learner* L) {
+  uint32_t* st = nullptr;
+  float *lo = nullptr, *me = nullptr;
+  int rc = hb_net_learner_buffers(L->net, L->B, &st, &lo, &me);
+  if (rc) return rc;
+  const void* now[3] = {st, lo, me};
+  if (memcmp(now, L->kA_ptr, sizeof(now)) != 0) {
+    if (L->gA) { cudaGraphExecDestroy(L->gA); L->gA = nullptr; }
+    if (L->gB) { cudaGraphExecDestroy(L->gB); L->gB = nullptr; }
+    memcpy(L->kA_ptr, now, sizeof(now));
+  }
+  L->o1 = st;
+  L->o2 = st + (size_t)L->B * L->stride;
+  L->loss = lo;
+  L->mean = me;
+  return HB_OK;
 }
 
 template <class F>
@@ -120,17 +141,14 @@ int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_lea
   if (e == cudaSuccess) e = cudaMalloc(&L->d_keys, B * 4);
   if (e == cudaSuccess) e = cudaMalloc(&L->d_idx, B * 8);
   if (e == cudaSuccess) e = cudaMalloc(&L->d_p32, B * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&L->o1, B * L->stride * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&L->o2, B * L->stride * 4);
   if (e == cudaSuccess) e = cudaMalloc(&L->act, B * 4);
   if (e == cudaSuccess) e = cudaMalloc(&L->rew, B * 4);
   if (e == cudaSuccess) e = cudaMalloc(&L->term, B);
-  if (e == cudaSuccess) e = cudaMalloc(&L->loss, B * 4);
-  if (e == cudaSuccess) e = cudaMalloc(&L->mean, 4);
   if (e != cudaSuccess) {
     hb_learner_destroy(L);
     return hb::cuda_fail(e, "hb_learner_create alloc", __FILE__, __LINE__);
   }
+  if (int rc = borrow_net_buffers(L)) { hb_learner_destroy(L); return rc; }
   *out = L;
   return HB_OK;
 }
@@ -143,7 +161,7 @@ int hb_learner_destroy(hb_learner* L) {
   if (L->gB) cudaGraphExecDestroy(L->gB);
   if (L->h_keys) cudaFreeHost(L->h_keys);
   if (L->h_idx) cudaFreeHost(L->h_idx);
-  void* dv[] = {L->d_keys, L->d_idx, L->d_p32, L->o1, L->o2, L->act, L->rew, L->term, L->loss, L->mean};
+  void* dv[] = {L->d_keys, L->d_idx, L->d_p32, L->act, L->rew, L->term};   // o1 / o2 / loss / mean are the net's
   for (void* p : dv)
     if (p) cudaFree(p);
   for (cudaEvent_t ev : L->slot_done)
@@ -185,6 +203,7 @@ int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, f
              "hb_learner_grads: %s", L->prioritized ? "keys required" : "indices required");
   hb::DeviceGuard g(L->device);
   cudaStream_t cs = (cudaStream_t)stream;
+  if (int brc = borrow_net_buffers(L)) return brc;
   // this step's keys / indices: pinned ring slot -> device (outside the graph: the source moves)
   const int slot = L->slot;
   L->slot = (L->slot + 1) % hb_learner::kSlots;

@@ -957,6 +957,17 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                           float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
                           const uint32_t* d_legal_t);
 
+int hb_net_learner_buffers(hb_qnet* q, int B, uint32_t** obs_staging, float** loss, float** mean_loss) {
+  HB_REQUIRE(q && B >= 1, "hb_net_learner_buffers: bad arguments");
+  hb::DeviceGuard g(q->device);
+  int rc = ensure_learner_ws(q, B);
+  if (rc) return rc;
+  if (obs_staging) *obs_staging = q->xb;
+  if (loss) *loss = q->loss_b;
+  if (mean_loss) *mean_loss = q->scalars;
+  return HB_OK;
+}
+
 void* hb_net_loss_event(hb_qnet* q) { return q ? (void*)q->ev_loss : nullptr; }
 
 int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
@@ -996,9 +1007,13 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   const int ldq = q->n_atoms > 1 ? q->A : LL.N;
   // 1. packed rows side by side: [0, B) = obs_tm1, [B, 2B) = obs_t
   const size_t row_words = (size_t)q->obs_stride;
-  HB_CUDA(cudaMemcpyAsync(q->xb, d_obs_tm1, (size_t)B * row_words * 4, cudaMemcpyDeviceToDevice, s));
-  HB_CUDA(cudaMemcpyAsync(q->xb + (size_t)B * row_words, d_obs_t, (size_t)B * row_words * 4,
-                          cudaMemcpyDeviceToDevice, s));
+  // (a caller that gathered its rows straight into hb_net_obs_staging saves the two copies: each is a
+  // node of a few microseconds on the critical path of the captured update)
+  if (d_obs_tm1 != q->xb)
+    HB_CUDA(cudaMemcpyAsync(q->xb, d_obs_tm1, (size_t)B * row_words * 4, cudaMemcpyDeviceToDevice, s));
+  if (d_obs_t != q->xb + (size_t)B * row_words)
+    HB_CUDA(cudaMemcpyAsync(q->xb + (size_t)B * row_words, d_obs_t, (size_t)B * row_words * 4,
+                            cudaMemcpyDeviceToDevice, s));
   const bool fused = nl > 1;                 // layer 0 expands the bits inside the GEMM
   if (!fused && (rc = launch_unpack(q->xb, q->obs_stride, 2 * B, q->x, K0, nullptr, 0, 0, s))) return rc;
   // fork: the side stream runs the target network, the transposed observations and the importance
@@ -1054,8 +1069,10 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   HB_CUDA(cudaGetLastError());
   mean_loss_kernel<<<1, 256, 0, s>>>(q->loss_b, q->w_is, B, q->n_atoms > 1 ? 0 : 1, q->scalars);
   HB_CUDA(cudaGetLastError());
-  if (d_loss_out) HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
-  if (d_mean_loss) HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
+  if (d_loss_out && d_loss_out != q->loss_b)
+    HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
+  if (d_mean_loss && d_mean_loss != q->scalars)
+    HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
   HB_CUDA(cudaEventRecord(q->ev_loss, s));   // the per-sample losses are complete (hb_net_loss_event)
   // 5. backward: the dZ chain (critical path) on the main stream, the weight / bias gradients of
   //    every layer on the side stream as soon as that layer's dZ exists

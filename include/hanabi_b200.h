@@ -316,6 +316,11 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
  * point where the per-sample losses (d_loss_out) are complete: work that needs nothing but the losses --
  * PriorityBuffer.update_priorities, hanabi_agents/rlax_dqn/rlax_rainbow.py:331-334 -- can wait on it and
  * run beside the backward pass. */
+/* The network's own staging for a batch of B: packed observation rows [2B, obs_stride] (obs_tm1 rows, then
+ * obs_t rows from row B on), per-sample loss [B], mean loss [1].  hb_net_grads called with exactly these
+ * pointers (d_obs_tm1 = staging, d_obs_t = staging + B * obs_stride, d_loss_out, d_mean_loss) skips its
+ * device-to-device copies.  The pointers stay valid until a call with a larger B. */
+int hb_net_learner_buffers(hb_qnet* q, int B, uint32_t** obs_staging, float** loss, float** mean_loss);
 void* hb_net_loss_event(hb_qnet* q);
 /* The same with the TF-Rainbow target of rainbow/rainbow_agent.py:183-236 (the `rainbow/` package's
  * learner): next action = argmax over the LEGAL next moves (d_legal_t, packed) of the
@@ -347,12 +352,12 @@ float* hb_learner_loss(hb_learner* L);
 float* hb_learner_mean_loss(hb_learner* L);
 int64_t* hb_learner_indices(hb_learner* L);
 /* Phase A: sample_batch (priority_buffer.py:36-46; h_keys = the B stratified keys, float32 as
- * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss).  HOST arrays.  With HB_LEARNER_PRIO_OVERLAP=1 in
- * the environment update_priorities(indices, |loss|) (rlax_rainbow.py:331-334) already runs here, beside
- * the backward pass, instead of in phase B. */
+ * pybind narrows them) or uniform rows (h_idx) -> __getitem__ -> jax.grad(loss); update_priorities(indices, |loss|)
+ * (rlax_rainbow.py:331-334) runs here as well, beside the backward pass, as soon as the losses exist
+ * (HB_LEARNER_PRIO_OVERLAP=0 in the environment: in phase B, after Adam).  HOST arrays. */
 int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                      int mask_terminal, void* stream);
-/* Phase B: optix.adam on grad_scale * bucket, then update_priorities(indices, |loss|). */
+/* Phase B: optix.adam on grad_scale * bucket. */
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
                      void* stream);
 

@@ -4,7 +4,7 @@
 Workload (BASELINE.json configs[1]): rule-based (piers) self-play, Hanabi-Full 2 players,
 65,536 parallel games PER GPU, every env step = rule agent move + HanabiState transition +
 chance deal + canonical observation (bit-packed) + legal-move mask + reward + step type.
-One bench "step" = one env step of every game.
+One bench "step" = one fused launch = --fuse (64) env steps of every game, for both arms.
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
   torchrun ... bench.py --gpus N ...     (one rank per GPU, games sharded, no data collective)
@@ -180,6 +180,8 @@ def bench_learner(env, obs, legal, reward, stype, action, T, world, args):
                "algorithmic_tflops": 5 * flop_fwd * 256 * world * k / (ms * 1e-3) / 1e12,
                "allreduce_bytes": agent.network.n_grad * 4 if world > 1 else 0,
                "loss": float(agent.last_loss)}
+    if world > 1:
+        learner.update(allreduce_selfcheck(agent, world, env.device))
     # acting: explore() over the n games of this GPU, packed rows resident
     o, l = obs[T - 1], legal[T - 1]
     for _ in range(3):
@@ -208,6 +210,74 @@ def bench_learner(env, obs, legal, reward, stype, action, T, world, args):
                            "peak_source": "measured sustained cuBLAS bf16 (MEASURED_PEAKS.json)",
                            "traffic": None}}
     return learner, acting
+
+
+def allreduce_selfcheck(agent, world, device):
+    """Which collective the learner's update() ran, and proof that it sums: the NVLink kernel
+    (csrc/comm.cu) and torch.distributed.all_reduce (NCCL) on copies of ONE rank-dependent bucket
+    of the gradient's size.  bit-equal at world 2 (one addition per element, same on both); for more
+    ranks the two may add in different orders: every element must agree within 1 ulp of the sum of the
+    absolute values, and the NVLink result must be identical on every rank (fixed reduction order)."""
+    import torch
+    import torch.distributed as dist
+    rank = dist.get_rank()
+    impl = getattr(agent, "allreduce_impl", None)
+    out = {"allreduce_impl": impl, "allreduce_fallback_reason": getattr(agent, "allreduce_fallback_reason", None)}
+    n = agent.network.grad_bucket.numel()
+    g = torch.Generator(device=device)
+    g.manual_seed(1234 + rank)
+    src = torch.randn(n, generator=g, device=device, dtype=torch.float32)
+    ref = src.clone()
+    dist.all_reduce(ref)
+    mag = src.abs()
+    dist.all_reduce(mag)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn, reps=20):
+        for _ in range(3):
+            fn()
+        dist.barrier()
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps * 1e3], device=device)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    scratch = src.clone()
+    out["nccl_allreduce_us"] = timed(lambda: dist.all_reduce(scratch))
+    if impl == "nvlink":
+        comm = agent._comm
+        bucket = agent.network.grad_bucket
+        keep = bucket.clone()
+        bucket.copy_(src)
+        comm()
+        got = bucket.clone()
+        # identical on every rank?
+        lo, hi = got.clone(), got.clone()
+        dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+        same_everywhere = bool(torch.equal(lo, hi))
+        if world == 2:
+            ok = bool(torch.equal(got, ref))
+            how = "bit-equal to NCCL"
+        else:
+            ulp = torch.finfo(torch.float32).eps * mag
+            ok = bool(((got - ref).abs() <= ulp).all().item())
+            how = "within 1 ulp of sum|x| of NCCL's result"
+        out["allreduce_check"] = "ok" if (ok and same_everywhere) else "FAILED"
+        out["allreduce_check_detail"] = "%s: %s; identical on every rank: %s; max |diff| %.3g" % (
+            how, ok, same_everywhere, float((got - ref).abs().max().item()))
+        out["allreduce_us"] = timed(lambda: comm())
+        bucket.copy_(keep)
+    else:
+        out["allreduce_check"] = "nccl (library collective; nothing of ours to check)"
+        out["allreduce_us"] = out["nccl_allreduce_us"]
+    out["allreduce_payload_bytes"] = n * 4
+    return out
 
 
 def cpu_learner_baseline(seconds):
@@ -403,8 +473,10 @@ def bench_sum_tree(args):
                                  "note": "sampling only: ordered updates of one tree are one dependent chain"}
     # CPU: the reference's own pybind module, one thread (parity mode) -- bounded sample
     try:
-        sys.path.insert(0, os.path.join(ROOT, "oracle", "_ref"))
-        import sum_tree as ref_mod
+        from oracle import ref_pybind_module
+        ref_mod = ref_pybind_module()
+        if ref_mod is None:
+            raise RuntimeError("oracle/_ref/sum_tree*.so was not built")
         t0 = time.perf_counter()
         rt = ref_mod.SumTreef(cap)
         for c0 in range(0, cap, 65536):
@@ -432,15 +504,23 @@ def run_reference(args):
     if rank != 0:
         return
     threads = os.cpu_count() or 1
-    val, done, el = cpu_port_throughput(GAMES_PER_GPU, None, threads, steps_cap=args.steps,
-                                        warm=args.warmup)
-    sample = "%d env steps of all %d games (rule agent + step + int8 [N,658] encoding), %d threads" % (
-        done, GAMES_PER_GPU, threads)
+    # same step as our arm: one bench step = args.fuse env steps of each of the 65,536 games; the
+    # sample is bounded to 4096 env steps per game (a few tens of seconds on 8-16 host threads)
+    env_steps = min(args.steps * args.fuse, 4096)
+    warm = min(args.warmup * args.fuse, 256)
+    val, done, el = cpu_port_throughput(GAMES_PER_GPU, None, threads, steps_cap=env_steps, warm=warm)
+    bench_steps = done / float(args.fuse)
+    sample = ("%d env steps of all %d games = %.1f bench steps of %d env steps (rule agent + step + int8 "
+              "[N,658] encoding), %d threads" % (done, GAMES_PER_GPU, bench_steps, args.fuse, threads))
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / done,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / bench_steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
-        "data": "synthetic", "config": {"workload": WORKLOAD, "host": "cpu"},
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "host": "cpu", "games_per_gpu": GAMES_PER_GPU,
+                   "fused_steps_per_launch": args.fuse,
+                   "step": "one bench step = %d env steps of each of the %d games" % (args.fuse, GAMES_PER_GPU),
+                   "env_steps_timed_per_game": done},
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample,
                          "note": "reference engine is third-party HLE (absent); oracle/ restatement timed"},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -475,40 +555,73 @@ def run_ours(args):
     stype = torch.empty((T, n), dtype=torch.uint8, device=dev)
     action = torch.empty((T, n), dtype=torch.int32, device=dev)
 
-    def launch(k):
-        env.selfplay(agent, k, obs=obs[:k], legal=legal[:k], reward=reward[:k],
-                     step_type=stype[:k], action=action[:k])
+    def launch():
+        env.selfplay(agent, T, obs=obs, legal=legal, reward=reward, step_type=stype, action=action)
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    chunks = [T] * (args.steps // T) + ([args.steps % T] if args.steps % T else [])
-    for _ in range(max(3, (args.warmup + T - 1) // T)):
-        launch(T)
-    barrier()
+    # One bench step = ONE fused launch = T env steps of every game (config.fused_steps_per_launch).
+    # The launches of the timed region are queued behind a stream gate (hb_gate_*: a one-thread kernel
+    # polling a host flag) before the first event is recorded, so the region holds device time only:
+    # at --steps 20 the host's launch latency used to be more than half of it.
+    from hanabi_agents_b200._lib import StreamGate
+    gate = StreamGate(local)
+    launches = args.steps
+    queued = min(launches, 96)           # the launch queue holds ~1000 entries; 96 x 0.17 ms is ample lead
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clocks:
         barrier()
         clocks.mark_start()
+        # warm-up: W launches, and at least ~0.3 s of the same kernel so that the clocks the sampler
+        # sees (20 ms period) are the clocks of the timed region
+        t_w = time.perf_counter()
+        done_w = 0
+        while done_w < max(3, args.warmup) or time.perf_counter() - t_w < 0.3:
+            launch()
+            done_w += 1
+            if done_w % 64 == 0:
+                torch.cuda.synchronize()
+        barrier()
+        if not args.no_gate:
+            gate.close()
         ev0.record()
-        for k in chunks:
-            launch(k)
+        for _ in range(queued):
+            launch()
+        gate.open()
+        for _ in range(launches - queued):
+            launch()
         ev1.record()
         barrier()
         clocks.mark_end()
     ms = ev0.elapsed_time(ev1)
-    t = torch.tensor([ms], device=dev)
+    # an isolated launch (nothing before or after it on the device): what ncu's serialised
+    # gpu__time_duration measures; consecutive launches of the timed region overlap (PDL hand-over)
+    iso = []
+    eva, evb = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    for _ in range(5):
+        torch.cuda.synchronize()
+        if not args.no_gate:
+            gate.close()
+        eva.record()
+        launch()
+        evb.record()
+        gate.open()
+        torch.cuda.synchronize()
+        iso.append(eva.elapsed_time(evb))
+    iso_ms = sorted(iso)[len(iso) // 2]
+    t = torch.tensor([ms, iso_ms], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    launches = len(chunks)
-    value = world * n * args.steps / (ms * 1e-3)
+    ms, iso_ms = float(t[0].item()), float(t[1].item())
+    env_steps = launches * T
+    value = world * n * env_steps / (ms * 1e-3)
 
     # ---- e2e: same workload through the host-buffer API: actions come from pinned host memory
     # each step, observation / legal / reward / step type are read back to the host each step.
-    e_steps = min(args.steps, args.e2e_steps)
+    e_steps = min(env_steps, args.e2e_steps)
     sets = [env.host_buffers(), env.host_buffers()]              # pinned host arrays, two sets
     acts = [sets[0]["actions"], sets[0]["next_actions"], sets[1]["actions"]]
     acts[0].copy_(agent.explore(env).cpu())
@@ -567,21 +680,51 @@ def run_ours(args):
     # per launch, i.e. 128/T per step.
     per_step = 84 + 4 + 4 + 1 + 4
     bytes_per_launch = n * (T * per_step + 2 * env.state_words * 4)
-    launch_ms = ms / (args.steps / T)
+    launch_ms = ms / launches                      # the launches actually timed
     achieved = bytes_per_launch / (launch_ms * 1e-3) / 1e9
-    traffic = None
+    prof = {}
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         try:
-            traffic = json.load(open(tp)).get("selfplay_kernel")
+            prof = json.load(open(tp)).get("selfplay_kernel") or {}
+            if not isinstance(prof, dict):
+                prof = {"dram_bytes_per_launch": prof}
         except Exception:
-            traffic = None
+            prof = {}
+    same_shape = prof.get("games") == n and prof.get("fused_steps") == T
     roof = {"bound": "hbm", "kernel": "selfplay_kernel", "achieved": achieved, "peak": peak,
             "peak_source": which + " copy bandwidth (MEASURED_PEAKS.json)", "unit": "GB/s",
             "frac": achieved / peak, "peak_nominal": 8000.0, "frac_nominal": achieved / 8000.0,
-            "traffic": traffic,
+            # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch from an ncu --set full capture
+            # of this kernel at this shape (profiles/traffic.json names the capture); null otherwise
+            "traffic": prof.get("dram_bytes_per_launch") if same_shape else None,
+            "traffic_source": prof.get("source") if same_shape else None,
             "algorithmic_bytes_per_launch": bytes_per_launch,
-            "launch_ms": launch_ms}
+            "launches_timed": launches, "launch_ms": launch_ms,
+            "isolated_launch_ms": iso_ms,
+            "isolated_achieved": bytes_per_launch / (iso_ms * 1e-3) / 1e9,
+            "isolated_frac": bytes_per_launch / (iso_ms * 1e-3) / 1e9 / peak,
+            "note": "launch_ms = timed region / launches (consecutive launches overlap on the device); "
+                    "isolated_* = one launch alone between two events, which is what ncu's serialised "
+                    "gpu__time_duration sees"}
+    # The kernel's binding resource is not HBM but the ALU pipe (LOP3 / SHF / ISETP / SEL: one warp
+    # instruction per TWO cycles per SM sub-partition).  alu_issue = ALU-pipe warp instructions of one
+    # launch (ncu sm__inst_executed_pipe_alu.sum of the capture named in profiles/traffic.json) / live
+    # launch time, against 148 SMs x 4 sub-partitions x 0.5 / cycle at the SM clock sampled in the run.
+    roof_alu = None
+    if same_shape and prof.get("alu_warp_inst_per_launch"):
+        clk = (clocks.summary().get("sm_mhz") or 1965.0) * 1e6
+        n_sm = torch.cuda.get_device_properties(local).multi_processor_count
+        alu_peak = n_sm * 4 * 0.5 * clk / 1e9
+        alu = float(prof["alu_warp_inst_per_launch"]) / (launch_ms * 1e-3) / 1e9
+        roof_alu = {"bound": "alu_issue", "kernel": "selfplay_kernel", "achieved": alu, "peak": alu_peak,
+                    "unit": "G warp-inst/s", "frac": alu / alu_peak,
+                    "alu_warp_inst_per_launch": prof["alu_warp_inst_per_launch"],
+                    "alu_warp_inst_per_warp_step": float(prof["alu_warp_inst_per_launch"]) / (n / 32 * T),
+                    "isolated_frac": float(prof["alu_warp_inst_per_launch"]) / (iso_ms * 1e-3) / 1e9 / alu_peak,
+                    "source": prof.get("source"),
+                    "peak_note": "%d SMs x 4 sub-partitions x 1 ALU warp-instruction / 2 cycles x %.0f MHz"
+                                 % (n_sm, clk / 1e6)}
 
     cores = os.cpu_count() or 1
     cval, cdone, cel = cpu_port_throughput(n, args.cpu_seconds, cores)
@@ -591,17 +734,25 @@ def run_ours(args):
            "note": "reference engine is third-party HLE (absent here); oracle/ restatement timed"}
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
+        "warmup": args.warmup, "ms_per_step": ms / launches, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u32-bitfield", "data": "synthetic",
         "config": {"workload": WORKLOAD, "games_per_gpu": n, "fused_steps_per_launch": T,
+                   "step": "one bench step = one fused launch = %d env steps of each of the %d games per GPU "
+                           "(%d env-steps per GPU); the reference arm's step is the same %d env steps per game"
+                           % (T, n, T * n, T),
+                   "env_steps_timed_per_game": env_steps,
+                   "timing": "CUDA events on the launching stream; the first %d launches are queued behind a "
+                             "stream gate before the first event, so no host launch latency is inside" % queued,
+                   "warmup_launches": done_w,
                    "l2": "outputs of one launch (%.0f MB) exceed the 126 MB L2; no flush needed"
                          % (T * n * (env.obs_stride * 4 + env.legal_words * 4 + 9) / 1e6),
                    "decks": "numpy default_rng(%d) permutations, pool of %d" % (SEED, 4 * n),
                    "launch_overlap": "consecutive self-play launches of one stream overlap (programmatic dependent "
                                      "launch + per-group FIFO hand-over); roofline.launch_ms = timed region / launches"},
         "clocks": clocks.summary(),
-        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "steps": e_steps,
+        "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d * T, "d2h_bytes_per_step": d2h * T,
+                "h2d_bytes_per_env_step": h2d, "d2h_bytes_per_env_step": d2h,
+                "env_steps_timed": e_steps, "ms_per_env_step": 1e3 * float(te.item()) / e_steps,
                 "path": "per step, host in the loop, pinned host arrays both ways, double-buffered: env.step_host_begin "
                 "(actions H2D, env_step_kernel) | agent.explore_host_async (rules_act_kernel + next actions D2H) | "
                 "env.step_host_outputs (D2H of observation rows (%d B) + legal mask + reward + step type in one copy, "
@@ -609,6 +760,7 @@ def run_ours(args):
                 % (4 * env.obs_words)},
         "gpu_launches": launches,
         "roofline": roof,
+        "roofline_alu": roof_alu,
         "cpu_baseline": cpu,
         "learner": learner,
         "acting": acting,
@@ -624,12 +776,13 @@ def run_ours(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=65536)
-    ap.add_argument("--warmup", type=int, default=128)
+    ap.add_argument("--steps", type=int, default=1024,
+                    help="bench steps; one step = one fused launch of --fuse env steps of every game")
+    ap.add_argument("--warmup", type=int, default=16)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--games", type=int, default=GAMES_PER_GPU)
     ap.add_argument("--fuse", type=int, default=64, help="env steps fused per launch")
-    ap.add_argument("--e2e-steps", type=int, default=64)
+    ap.add_argument("--e2e-steps", type=int, default=512, help="env steps of the host-in-the-loop leg")
     ap.add_argument("--e2e-chunks", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--learner-steps", type=int, default=300)
@@ -638,6 +791,9 @@ def main():
     ap.add_argument("--no-learner", action="store_true")
     ap.add_argument("--no-tree", action="store_true")
     ap.add_argument("--no-session", action="store_true")
+    ap.add_argument("--no-gate", action="store_true",
+                    help="do not hold the stream behind a gate (for runs under ncu, which executes every launch "
+                         "synchronously: a gate kernel would wait for a host that is blocked in its launch)")
     ap.add_argument("--session-ticks", type=int, default=100)
     args = ap.parse_args()
     # Only the JSON line may reach stdout: libraries print there too (NCCL announces its version on
@@ -650,8 +806,6 @@ def main():
     py_stdout, sys.stdout = sys.stdout, captured
     try:
         if args.impl == "reference":
-            if args.steps > 2048:
-                args.steps = 2048    # bounded sample: ~23 ms per 65,536-game step on 8 host cores
             run_reference(args)
         else:
             run_ours(args)

@@ -28,6 +28,10 @@ SIGNATURES = {
     "hb_last_error": (C.c_char_p, []),
     "hb_version": (i32, []),
     "hb_build_arch": (C.c_char_p, []),
+    "hb_gate_create": (i32, [i32, C.POINTER(vp)]),
+    "hb_gate_destroy": (i32, [vp]),
+    "hb_gate_close": (i32, [vp, vp]),
+    "hb_gate_open": (i32, [vp]),
     # sum tree
     "hb_st_create": (i32, [i64, i32, C.POINTER(vp)]),
     "hb_st_destroy": (i32, [vp]),
@@ -126,6 +130,7 @@ SIGNATURES = {
     "hb_comm_open": (i32, [vp, vp]),
     "hb_comm_allreduce": (i32, [vp, vp]),
     "hb_comm_info": (i32, [vp, i32]),
+    "hb_comm_status": (i32, [vp]),
     # self-play session
     "hb_session_create": (i32, [i32, i64, i32, C.POINTER(vp)]),
     "hb_session_destroy": (i32, [vp]),
@@ -179,6 +184,30 @@ def current_stream_ptr():
     """cudaStream_t of torch's current stream (torch is used for hand-off only)."""
     import torch
     return torch.cuda.current_stream().cuda_stream
+
+
+class StreamGate:
+    """Holds a CUDA stream until `open()` (include/hanabi_b200.h: hb_gate_*): queue the launches of a
+    timed region behind it and the region no longer contains the host's launch latency."""
+
+    def __init__(self, device_index):
+        self._h = vp()
+        check(lib().hb_gate_create(int(device_index), C.byref(self._h)))
+
+    def close(self, stream_ptr=None):
+        check(lib().hb_gate_close(self._h, current_stream_ptr() if stream_ptr is None else stream_ptr))
+
+    def open(self):
+        check(lib().hb_gate_open(self._h))
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and h.value:
+            try:
+                lib().hb_gate_destroy(h)
+            except Exception:
+                pass
+            self._h = None
 
 
 class DevView:

@@ -14,7 +14,11 @@
 // 5-23 MB of this path the three flag barriers (a few microseconds each) are the rest of the cost.
 // Barriers are per CTA: CTA b of rank r raises flag[peer][b][r] on every peer and waits for its own
 // row -- only CTAs with the same index on different GPUs wait for each other, so no co-residency of a
-// whole grid is assumed.  Waits are bounded: a peer that never arrives becomes a trap, not a hang.
+// whole grid is assumed.  A wait for a late peer does NOT trap (a rank that is seconds late -- an
+// evaluation on rank 0, a graph recapture, a first-use allocation -- is normal, and a trap would poison
+// the CUDA context of every rank): it polls for up to ~2 minutes, then raises a flag in host-mapped
+// memory (hb_comm_status) and leaves the barrier so that the host can raise an error instead of
+// hanging the device.  Ranks must call hb_comm_allreduce in lockstep, as with any collective.
 #include "common.cuh"
 #include <new>
 #include <string.h>
@@ -34,6 +38,8 @@ struct hb_comm {
   uint32_t* peer_flags[kMaxWorld] = {nullptr};
   bool opened = false;
   uint32_t epoch = 0;
+  int* h_timeout = nullptr;           // pinned + mapped: set by a barrier that gave up waiting
+  int* d_timeout = nullptr;
 };
 
 namespace {
@@ -44,6 +50,7 @@ struct CommArgs {
   int rank, world;
   long long n4;                       // float4 elements
   uint32_t epoch;
+  int* timeout;                       // host-mapped flag
 };
 
 // peer data: system-scope loads that never come from this SM's L1
@@ -88,8 +95,15 @@ __device__ __forceinline__ void gpu_barrier(const CommArgs& a, int stage) {
       else st_flag_relaxed(a.flags[peer] + slot + a.rank, a.epoch);
       const uint32_t* mine = a.flags[a.rank] + slot + peer;
       const long long t0 = clock64();
+      unsigned spins = 0;
       while ((int32_t)(ld_flag_relaxed(mine) - a.epoch) < 0) {
-        if (clock64() - t0 > 8000000000ll) __trap();      // ~4 s: a rank is missing
+        // every 2^16 polls: has the bound (~2 min at 1.9 GHz) passed, or has another CTA given up?
+        // (the status word is host memory: one PCIe read, so it is not part of the hot poll)
+        if ((++spins & 0xffffu) == 0 &&
+            (clock64() - t0 > 240000000000ll || *(volatile int*)a.timeout != 0)) {
+          *(volatile int*)a.timeout = 1;                    // the host reports it (hb_comm_status)
+          break;
+        }
       }
       asm volatile("fence.acq_rel.sys;" ::: "memory");
     }
@@ -169,6 +183,14 @@ int hb_comm_create(int rank, int world, int device, float* d_bucket, int64_t n, 
   cudaError_t e = cudaMalloc(&c->flags, fbytes < ((size_t)2 << 20) ? ((size_t)2 << 20) : fbytes);
   if (e == cudaSuccess) e = cudaMemset(c->flags, 0, fbytes);
   if (e != cudaSuccess) { delete c; return hb::cuda_fail(e, "hb_comm_create alloc", __FILE__, __LINE__); }
+  if (cudaHostAlloc((void**)&c->h_timeout, 64, cudaHostAllocMapped) != cudaSuccess ||
+      cudaHostGetDevicePointer((void**)&c->d_timeout, c->h_timeout, 0) != cudaSuccess) {
+    cudaFree(c->flags);
+    delete c;
+    hb::set_error("hb_comm_create: cannot allocate the mapped status word");
+    return HB_ERR_CUDA;
+  }
+  *c->h_timeout = 0;
   c->peer_buf[rank] = d_bucket;
   c->peer_flags[rank] = c->flags;
   *out = c;
@@ -215,6 +237,7 @@ int hb_comm_destroy(hb_comm* c) {
       if (c->peer_flags[j]) cudaIpcCloseMemHandle(c->peer_flags[j]);
     }
   if (c->flags) cudaFree(c->flags);
+  if (c->h_timeout) cudaFreeHost(c->h_timeout);
   delete c;
   return HB_OK;
 }
@@ -230,6 +253,11 @@ int hb_comm_allreduce(hb_comm* c, void* stream) {
   for (int j = 0; j < kMaxWorld; ++j) { a.buf[j] = c->peer_buf[j]; a.flags[j] = c->peer_flags[j]; }
   a.rank = c->rank; a.world = c->world; a.n4 = c->n / 4;
   a.epoch = ++c->epoch;
+  a.timeout = c->d_timeout;
+  if (*(volatile int*)c->h_timeout != 0) {
+    hb::set_error("hb_comm_allreduce: an earlier all-reduce gave up waiting for a peer (ranks out of lockstep)");
+    return HB_ERR_STATE;
+  }
   cudaStream_t st = (cudaStream_t)stream;
   switch (c->world) {
     case 2: allreduce_two_shot_kernel<2><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
@@ -241,6 +269,16 @@ int hb_comm_allreduce(hb_comm* c, void* stream) {
     default: allreduce_two_shot_kernel<8><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
   }
   HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+/* HB_OK, or HB_ERR_STATE when a barrier of an earlier all-reduce timed out waiting for a peer. */
+int hb_comm_status(const hb_comm* c) {
+  HB_REQUIRE(c != nullptr, "hb_comm_status: NULL communicator");
+  if (c->h_timeout && *(volatile int*)c->h_timeout != 0) {
+    hb::set_error("all-reduce: a peer did not arrive within the wait bound (ranks out of lockstep)");
+    return HB_ERR_STATE;
+  }
   return HB_OK;
 }
 

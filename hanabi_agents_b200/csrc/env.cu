@@ -5,6 +5,7 @@
 #include "hanabi_encode.cuh"
 #include "hanabi_rules.cuh"
 #include <algorithm>
+#include <cstring>
 #include <new>
 #include <vector>
 
@@ -43,6 +44,22 @@ struct hb_env {
   int h_slot = 0;
   cudaEvent_t hev_out[2] = {nullptr, nullptr};
   cudaEvent_t hev_rules = nullptr, hev_acts = nullptr;   // hev_acts: the next actions have left for the host
+  // Rule lists seen so far, with their comparison tables already built: an agent passes the same
+  // (ids, fargs, iargs, seed) on every call, and the tables (52 x 64 float64 divisions per threshold
+  // rule) cost more host time than a 20-step launch takes on the device.
+  struct RuleKey {
+    int n = -1;
+    unsigned long long seed = 0;
+    int32_t ids[hbg::kMaxRules] = {};
+    int32_t iarg[hbg::kMaxRules] = {};
+    double farg[hbg::kMaxRules] = {};
+  };
+  static constexpr int kRuleCache = 8;
+  RuleKey rule_key[kRuleCache];
+  hbg::RuleSet rule_set[kRuleCache];
+  bool rule_ext[kRuleCache] = {};
+  int rule_cached = 0, rule_next = 0;
+  unsigned long long rule_fills = 0;    // hb_env_info(e, 9): tables built so far
 };
 
 namespace {
@@ -563,6 +580,42 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
   return HB_OK;
 }
 
+// The RuleSet of a rule list, built on first sight and kept with the env (hb_env::rule_set).
+int cached_ruleset(hb_env* e, const int32_t* ids, const double* farg, const int32_t* iarg, int n,
+                   unsigned long long seed, const RuleSet** out, bool* ext) {
+  HB_REQUIRE(n >= 0 && n <= kMaxRules, "rule list too long (%d > %d)", n, kMaxRules);
+  HB_REQUIRE(n == 0 || ids != nullptr, "rule ids are NULL");
+  hb_env::RuleKey key;
+  key.n = n;
+  key.seed = seed;
+  for (int k = 0; k < n; ++k) {
+    key.ids[k] = ids[k];
+    key.iarg[k] = iarg ? iarg[k] : 0;
+    key.farg[k] = farg ? farg[k] : 0.0;
+  }
+  for (int c = 0; c < e->rule_cached; ++c) {
+    const hb_env::RuleKey& k = e->rule_key[c];
+    if (k.n == n && k.seed == seed && memcmp(k.ids, key.ids, sizeof(key.ids)) == 0 &&
+        memcmp(k.iarg, key.iarg, sizeof(key.iarg)) == 0 && memcmp(k.farg, key.farg, sizeof(key.farg)) == 0) {
+      *out = &e->rule_set[c];
+      *ext = e->rule_ext[c];
+      return HB_OK;
+    }
+  }
+  const int slot = e->rule_next;
+  e->rule_key[slot].n = -1;                                  // not a hit while half built
+  int rc = fill_ruleset(e->rule_set[slot], ids, farg, iarg, n, seed);
+  if (rc) return rc;
+  e->rule_key[slot] = key;
+  e->rule_ext[slot] = uses_ext_rules(e->rule_set[slot]);
+  e->rule_next = (slot + 1) % hb_env::kRuleCache;
+  if (e->rule_cached < hb_env::kRuleCache) ++e->rule_cached;
+  ++e->rule_fills;
+  *out = &e->rule_set[slot];
+  *ext = e->rule_ext[slot];
+  return HB_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -645,6 +698,7 @@ int64_t hb_env_info(const hb_env* e, int what) {
     case 6: return e->rt.n_games;
     case 7: return 8 + e->C + e->P + 5 * e->P * e->H + e->C * e->R + 12;  // dump length
     case 8: return e->P;
+    case 9: return (int64_t)e->rule_fills;
     default: return -1;
   }
 }
@@ -789,11 +843,13 @@ int hb_rules_act(hb_env* e, const int32_t* rule_ids, const double* rule_farg, co
   if (e) e->spq_chain = false;
   HB_REQUIRE(e && d_action, "hb_rules_act: bad arguments");
   if (!e->is_reset) { hb::set_error("hb_rules_act: reset the environment first"); return HB_ERR_STATE; }
-  RuleSet rs;
-  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  const RuleSet* rsp = nullptr;
+  bool ext = false;
+  int rc = cached_ruleset(e, rule_ids, rule_farg, rule_iarg, n_rules, seed, &rsp, &ext);
   if (rc) return rc;
+  const RuleSet& rs = *rsp;
   hb::DeviceGuard g(e->device);
-  if (uses_ext_rules(rs)) {
+  if (ext) {
     HB_DISPATCH(e, (rules_act_kernel<SH, true><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                        e->rt, e->state, rs, step, d_action, d_rule_hit,
                        (unsigned long long*)d_hist, 0, e->rt.n_games)));
@@ -812,9 +868,11 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
                     int32_t* d_action, uint64_t* d_hist, void* stream) {
   HB_REQUIRE(e && n_steps >= 1 && n_steps <= 255, "hb_env_selfplay: n_steps must be 1..255");
   if (!e->is_reset) { hb::set_error("hb_env_selfplay: reset the environment first"); return HB_ERR_STATE; }
-  RuleSet rs;
-  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  const RuleSet* rsp = nullptr;
+  bool ext = false;
+  int rc = cached_ruleset(e, rule_ids, rule_farg, rule_iarg, n_rules, seed, &rsp, &ext);
   if (rc) return rc;
+  const RuleSet& rs = *rsp;
   hb::DeviceGuard g(e->device);
   const int n_groups = (int)grid_for(e);
   if (e->spq == nullptr) {
@@ -844,7 +902,7 @@ int hb_env_selfplay(hb_env* e, const int32_t* rule_ids, const double* rule_farg,
   const uint8_t* decks = e->decks;
   const unsigned long long s0 = step0;
   cudaError_t lerr = cudaSuccess;
-  if (uses_ext_rules(rs)) {
+  if (ext) {
     HB_DISPATCH(e, (lerr = cudaLaunchKernelEx(&cfg, selfplay_kernel<SH, true>, e->rt, e->state, decks, rs, s0,
                                               n_steps, d_obs, d_legal, d_reward, d_step_type, d_action, hist,
                                               e->illegal, q)));
@@ -1000,14 +1058,15 @@ int hb_rules_act_host_async(hb_env* e, const int32_t* rule_ids, const double* ru
   if (e) e->spq_chain = false;
   HB_REQUIRE(e && h_action, "hb_rules_act_host_async: bad arguments");
   HB_REQUIRE(e->h_chunks >= 1, "hb_rules_act_host_async: call hb_env_step_host_async first");
-  RuleSet rs;
-  int rc = fill_ruleset(rs, rule_ids, rule_farg, rule_iarg, n_rules, seed);
+  const RuleSet* rsp = nullptr;
+  bool ext = false;
+  int rc = cached_ruleset(e, rule_ids, rule_farg, rule_iarg, n_rules, seed, &rsp, &ext);
   if (rc) return rc;
+  const RuleSet& rs = *rsp;
   hb::DeviceGuard g(e->device);
   StagePlan p;
   rc = host_pipe_init(e, (e->obs_len + 31) / 32, &p, e->h_slot);
   if (rc) return rc;
-  const bool ext = uses_ext_rules(rs);
   const long long n = e->rt.n_games, per = chunk_games(e, e->h_chunks);
   int c = 0;
   for (long long first = 0; first < n; first += per, ++c) {

@@ -37,6 +37,7 @@ struct hb_learner {
   cudaGraphExec_t gA = nullptr, gB = nullptr;
   float kA[3] = {0, 0, 0};       // beta, discount, mask_terminal
   const void* kA_ptr[3] = {nullptr, nullptr, nullptr};   // the net's staging the graph was captured with
+  int64_t rb_gen = -1;           // generation of the replay shard's scratch the graphs were captured with
   float kB[5] = {0, 0, 0, 0, 0}; // lr, b1, b2, eps, grad_scale
   int warm = 0;                  // eager steps run (the first one allocates workspaces)
   int recaptures = 0;
@@ -81,7 +82,11 @@ int borrow_net_buffers(hb_learner* L) {
   int rc = hb_net_learner_buffers(L->net, L->B, &st, &lo, &me);
   if (rc) return rc;
   const void* now[3] = {st, lo, me};
-  if (memcmp(now, L->kA_ptr, sizeof(now)) != 0) {
+  // the replay scratch (sampled values / new priorities) is baked into both graphs as well: a call with a
+  // larger n than the batch (sample_batch(512), a long update_priorities) moves it (hb_rb_info 6)
+  const int64_t gen = hb_rb_info(L->rb, 6);
+  if (memcmp(now, L->kA_ptr, sizeof(now)) != 0 || gen != L->rb_gen) {
+    L->rb_gen = gen;
     if (L->gA) { cudaGraphExecDestroy(L->gA); L->gA = nullptr; }
     if (L->gB) { cudaGraphExecDestroy(L->gB); L->gB = nullptr; }
     memcpy(L->kA_ptr, now, sizeof(now));

@@ -37,6 +37,11 @@ struct hb_replay {
   int32_t* h_total = nullptr;         // pinned host copy
   float* vals = nullptr;              // scratch for priorities / sampled values
   int64_t vals_n = 0;
+  // A learner's captured graphs hold `vals`: a larger request allocates a NEW buffer, the old ones
+  // stay alive until hb_rb_destroy, and vals_gen tells the learner to capture again (hb_rb_info 6).
+  int64_t vals_gen = 0;
+  float* vals_retired[16] = {nullptr};
+  int n_retired = 0;
 };
 
 namespace {
@@ -277,12 +282,20 @@ unsigned blocks_for(int64_t total, int threads) {
 
 int ensure_vals(hb_replay* rb, int64_t n, cudaStream_t s) {
   if (rb->vals_n >= n) return HB_OK;
-  HB_CUDA(cudaStreamSynchronize(s));
-  if (rb->vals) cudaFree(rb->vals);
-  rb->vals = nullptr;
-  rb->vals_n = 0;
-  HB_CUDA(cudaMalloc(&rb->vals, sizeof(float) * (n + 1)));
-  rb->vals_n = n;
+  (void)s;
+  // sizes double, so at most a handful of buffers are ever retired; none is freed while graphs
+  // captured with it may still be replayed
+  int64_t want = rb->vals_n > 0 ? rb->vals_n : 256;
+  while (want < n) want *= 2;
+  float* fresh = nullptr;
+  HB_CUDA(cudaMalloc(&fresh, sizeof(float) * (want + 1)));
+  if (rb->vals) {
+    if (rb->n_retired < 16) rb->vals_retired[rb->n_retired++] = rb->vals;
+    else { cudaDeviceSynchronize(); cudaFree(rb->vals); }
+  }
+  rb->vals = fresh;
+  rb->vals_n = want;
+  ++rb->vals_gen;
   return HB_OK;
 }
 
@@ -384,6 +397,7 @@ int hb_rb_destroy(hb_replay* rb) {
   if (rb->prio_range) cudaFree(rb->prio_range);
   if (rb->block_sum) cudaFree(rb->block_sum);
   if (rb->vals) cudaFree(rb->vals);
+  for (int i = 0; i < rb->n_retired; ++i) cudaFree(rb->vals_retired[i]);
   if (rb->tree) hb_st_destroy(rb->tree);
   delete rb;
   return HB_OK;
@@ -398,6 +412,7 @@ int64_t hb_rb_info(const hb_replay* rb, int what) {
     case 3: return rb->stride;
     case 4: return rb->legal_words;
     case 5: return rb->prioritized;
+    case 6: return rb->vals_gen;
     default: return -1;
   }
 }

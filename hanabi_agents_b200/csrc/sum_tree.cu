@@ -716,11 +716,17 @@ int hb_st_check(hb_sumtree* t, void* stream) {
 }
 
 // ---- host-buffer forms (the pybind surface) --------------------------------
+// Synchronous calls, as the reference's are (it holds the GIL for the whole call).  They run on the legacy
+// default stream, which does not order against non-blocking streams (the learner's, a caller's own):
+// every form therefore starts with a device-wide synchronisation, so whatever was enqueued on ANY stream
+// before the call -- an overlapped priority update, say -- is complete before the heap is touched, and
+// returns only when its own work is done.
 int hb_st_update_host(hb_sumtree* t, const int64_t* h_idx, const float* h_val, int64_t n) {
   HB_REQUIRE(t && n >= 0, "hb_st_update_host: bad arguments");
   if (n == 0) return HB_OK;
   HB_REQUIRE(h_idx && h_val, "hb_st_update_host: NULL buffer");
   hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaDeviceSynchronize());
   int rc = ensure_stage(t, (size_t)n * 12);
   if (rc) return rc;
   int64_t* d_idx = (int64_t*)t->stage;
@@ -737,6 +743,7 @@ int hb_st_get_indices_host(hb_sumtree* t, const float* h_q, int64_t* h_out, int6
   if (n == 0) return HB_OK;
   HB_REQUIRE(h_q && h_out, "hb_st_get_indices_host: NULL buffer");
   hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaDeviceSynchronize());
   int rc = ensure_stage(t, (size_t)n * 12);
   if (rc) return rc;
   int64_t* d_out = (int64_t*)t->stage;
@@ -753,6 +760,7 @@ int hb_st_get_values_host(hb_sumtree* t, const int64_t* h_idx, float* h_out, int
   if (n == 0) return HB_OK;
   HB_REQUIRE(h_idx && h_out, "hb_st_get_values_host: NULL buffer");
   hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaDeviceSynchronize());
   int rc = ensure_stage(t, (size_t)n * 12);
   if (rc) return rc;
   int64_t* d_idx = (int64_t*)t->stage;
@@ -767,6 +775,7 @@ int hb_st_get_values_host(hb_sumtree* t, const int64_t* h_idx, float* h_out, int
 int hb_st_total_host(hb_sumtree* t, float* h_out) {
   HB_REQUIRE(t && h_out, "hb_st_total_host: bad arguments");
   hb::DeviceGuard g(t->device);
+  HB_CUDA(cudaDeviceSynchronize());
   HB_CUDA(cudaMemcpy(h_out, t->heap + 1, sizeof(float), cudaMemcpyDeviceToHost));
   return HB_OK;
 }

@@ -12,7 +12,11 @@ tensor for CUDA input.
 
 Data parallel: when torch.distributed is initialised, every rank owns its games and its replay
 shard; `update()` all-reduces the flat gradient bucket once (the only collective) and scales by
-1/world inside the fused Adam, so parameters stay identical on every rank.
+1/world inside the fused Adam, so parameters stay identical on every rank.  Ranks must call
+`update()` in lockstep (one collective per call).  Divergence from a single-process run at the same
+global batch: every rank stratifies over ITS shard's tree and divides its
+importance weights by ITS batch maximum (rlax_rainbow.py:188-189 on the local batch); the global
+batch is the union of the per-rank batches, not one stratified draw over one tree.
 """
 import os
 import pickle
@@ -133,12 +137,18 @@ class DQNAgent:
         HB_ALLREDUCE=nccl."""
         if getattr(self, "_comm", None) is None:
             self._comm = False
+            self.allreduce_impl = "nccl"
             if os.environ.get("HB_ALLREDUCE", "nvlink") != "nccl":
                 try:
                     from ..dist import NvlinkAllReduce
                     self._comm = NvlinkAllReduce(self.network.grad_bucket, self.process_group)
-                except Exception:      # noqa: BLE001 -- every rank takes the same branch (dist.py)
+                    self.allreduce_impl = "nvlink"
+                except RuntimeError as e:   # peers cannot be mapped: every rank takes this branch (dist.py)
+                    import warnings
                     self._comm = False
+                    self.allreduce_fallback_reason = repr(e)
+                    warnings.warn("hanabi_agents_b200: NVLink all-reduce unavailable, using "
+                                  "torch.distributed.all_reduce instead: %r" % (e,), RuntimeWarning)
         if self._comm:
             self._comm()
         else:
@@ -160,8 +170,9 @@ class DQNAgent:
             keys = np.ascontiguousarray(PriorityBuffer.stratified_keys(B, uniforms), dtype=np.float32)
             kp, ip = keys.ctypes.data, None
         else:                                        # uniform sample, prios = ones  (:315-318)
-            idx = np.ascontiguousarray(
-                np.random.choice(np.arange(0, exp.capacity, dtype=np.int64)[:exp.size], size=B), dtype=np.int64)
+            # np.random.choice(np.arange(capacity)[:size], B) draws randint(0, size, B) from the global RNG:
+            # the same stream without building a capacity-sized array every step
+            idx = np.ascontiguousarray(np.random.randint(0, exp.size, size=B), dtype=np.int64)
             kp, ip = None, idx.ctypes.data
         _lib.check(L.hb_learner_grads(self._learner, kp, ip, float(self.params.beta_is(self.train_step)),
                                       float(self.params.discount), 0, stream))

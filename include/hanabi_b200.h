@@ -35,6 +35,16 @@ const char* hb_last_error(void);
 int hb_version(void);
 const char* hb_build_arch(void);
 
+/* Stream gate (measurement plumbing; replaces nothing in the reference): hb_gate_close enqueues a
+ * one-thread kernel that holds `stream` until hb_gate_open is called from the host, so that a
+ * benchmark can queue its launches first and time them without the host's launch latency
+ * (bench.py).  The wait is bounded (~20 s); the kernel then ends by itself. */
+typedef struct hb_gate hb_gate;
+int hb_gate_create(int device, hb_gate** out);
+int hb_gate_destroy(hb_gate* g);
+int hb_gate_close(hb_gate* g, void* stream);
+int hb_gate_open(hb_gate* g);
+
 /* ------------------------------------------------------------------------ */
 /* Sum tree  (replaces sum_tree/sum_tree/include/sum_tree.h:22-130 and the   */
 /* pybind module sum_tree/sum_tree/src/sum_tree_py.cc:7-27)                  */
@@ -110,7 +120,8 @@ int hb_env_create(int players, int colors, int ranks, int hand_size, int max_inf
                   int64_t n_games, int device, hb_env** out);
 int hb_env_destroy(hb_env* e);
 /* what: 0 obs_len(bits) 1 obs_stride(words) 2 num_moves 3 legal_words 4 deck_size
- *       5 state_words 6 n_games 7 dump_len 8 players */
+ *       5 state_words 6 n_games 7 dump_len 8 players
+ *       9 rule lists whose comparison tables were built so far (they are cached per env) */
 int64_t hb_env_info(const hb_env* e, int what);
 /* This device holds games [game_id_base, game_id_base+n_games) of an n_total-game job
  * (deck selection and the rule agents' random stream use the global game id). */
@@ -208,7 +219,8 @@ typedef struct hb_replay hb_replay;
 int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capacity, int prioritized,
                  float alpha, int device, hb_replay** out);
 int hb_rb_destroy(hb_replay* rb);
-/* what: 0 capacity, 1 size, 2 oldest_entry, 3 obs_stride, 4 legal_words, 5 prioritized */
+/* what: 0 capacity, 1 size, 2 oldest_entry, 3 obs_stride, 4 legal_words, 5 prioritized,
+ *       6 generation of the sampling scratch (changes when a larger n reallocates it) */
 int64_t hb_rb_info(const hb_replay* rb, int what);
 /* The shard's sum tree (owned by the shard; NULL when not prioritized). */
 hb_sumtree* hb_rb_tree(hb_replay* rb);
@@ -409,9 +421,12 @@ int hb_comm_destroy(hb_comm* c);
 int hb_comm_export(hb_comm* c, void* h_out128);
 /* ... and maps every peer from the gathered world x 128 bytes. */
 int hb_comm_open(hb_comm* c, const void* h_all);
-/* Stream-ordered all-reduce; every rank calls it once per step.  The sum runs over the ranks in
- * fixed order, so every rank ends with the same bits. */
+/* Stream-ordered all-reduce; every rank calls it once per step, in lockstep (as with any
+ * collective).  The sum runs over the ranks in fixed order, so every rank ends with the same bits.
+ * A rank that waits for a late peer keeps polling (minutes, never a trap); should the bound pass, the
+ * kernel ends, hb_comm_status and later hb_comm_allreduce calls return HB_ERR_STATE. */
 int hb_comm_allreduce(hb_comm* c, void* stream);
+int hb_comm_status(const hb_comm* c);
 /* what: 0 rank, 1 world, 2 peers mapped, 3 calls so far */
 int hb_comm_info(const hb_comm* c, int what);
 

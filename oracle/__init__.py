@@ -48,6 +48,25 @@ def oracle_lib():
     return _oracle
 
 
+def ref_pybind_module():
+    """The reference's own pybind module (sum_tree_py.cc, unmodified, built into oracle/_ref by
+    oracle/build.py), loaded from its file WITHOUT touching sys.modules['sum_tree'] -- that top-level
+    name belongs to the drop-in shim at the repository root.  None if it was never built."""
+    import glob
+    import importlib.util
+    mods = glob.glob(os.path.join(HERE, "_ref", "sum_tree*.so"))
+    if not mods:
+        from . import build
+        build.build_ref()
+        mods = glob.glob(os.path.join(HERE, "_ref", "sum_tree*.so"))
+    if not mods:
+        return None
+    spec = importlib.util.spec_from_file_location("sum_tree", mods[0])
+    m = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(m)
+    return m
+
+
 def ref_lib(omp=False):
     """The reference header compiled into oracle/_ref (None if it was never built)."""
     path = REF_OMP_LIB if omp else REF_SEQ_LIB

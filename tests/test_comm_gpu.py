@@ -1,5 +1,5 @@
 """GPU: the NVLink all-reduce of the gradient bucket (csrc/comm.cu).  On one GPU: the C-ABI life cycle
-(create / export / world-1 no-op / argument checks).  With two or more GPUs: tools/test_comm.py under
+(create / export / world-1 no-op / argument checks).  With two or more GPUs: tools/comm_check.py under
 torchrun -- bit-equality with NCCL at world size 2, identical bits on every rank, DQNAgent.update with
 either collective."""
 import ctypes as C
@@ -47,6 +47,6 @@ def test_comm_two_gpus_against_nccl():
     if torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs on one node")
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
-           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tools", "test_comm.py")]
+           "--master-addr", "127.0.0.1", "--master-port", "29541", os.path.join(ROOT, "tools", "comm_check.py")]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=300, cwd=ROOT)
     assert r.returncode == 0 and "comm ok" in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]

@@ -131,3 +131,18 @@ def test_uniform_sample_uses_numpy_global_rng():
     np.random.seed(3)
     idx = np.random.choice(np.arange(64)[:20], size=8)
     np.testing.assert_array_equal(tr.observation_tm1, buf[idx].observation_tm1)
+
+
+def test_priority_buffer_against_the_reference_run():
+    """The CUDA shard through the numpy API against fixtures recorded from the reference's OWN
+    priority_buffer.py + sum tree (tests/golden/make_priority_golden.py): leaves, total, max / min
+    priority, cursor, sampled indices and probabilities, ring contents after every operation,
+    including wrap-around and duplicate indices in one update."""
+    from hanabi_agents_b200.rlax_dqn import PriorityBuffer
+    from test_replay_oracle import PGOLD as G, replay_priority_fixture
+    cap, tree_cap = int(G["cap"]), int(G["tree_cap"])
+    buf = PriorityBuffer(int(G["L"]), int(G["A"]), 1, cap, float(G["alpha"]))
+    assert buf.sum_tree.get_capacity() == tree_cap
+    replay_priority_fixture(
+        buf, lambda b: np.array(b.sum_tree.get_values(list(range(tree_cap))), np.float32),
+        lambda b, B, u: b.sample_batch(B, u), _all_rows)

@@ -78,3 +78,53 @@ def test_priority_pow_is_within_one_ulp_of_numpy_float32():
     assert theirs.dtype == np.float32
     ulp = np.spacing(ours)
     assert np.all(np.abs(ours.astype(np.float64) - theirs.astype(np.float64)) <= ulp)
+
+
+# ---- PriorityBuffer pinned on the REFERENCE ITSELF --------------------------------------------
+# tests/golden/priority_ref.npz was recorded by running /root/reference/hanabi_agents/rlax_dqn/
+# priority_buffer.py:13-52 on the reference's own pybind sum tree (tests/golden/make_priority_golden.py).
+PGOLD = np.load(os.path.join(os.path.dirname(__file__), "golden", "priority_ref.npz"))
+
+
+def replay_priority_fixture(buf, leaves_of, sample, state_of):
+    """Drives `buf` (oracle or CUDA shard) through the recorded operation sequence and checks every
+    recorded quantity bit for bit.  leaves_of(buf) -> float32[tree_cap]; sample(buf, B, uniforms) ->
+    (indices, prios f64, 6 arrays); state_of(buf) -> dict of the six ring arrays."""
+    G = PGOLD
+    tree_cap = int(G["tree_cap"])
+    for k, op in enumerate(G["ops"]):
+        if op == "add":
+            buf.add_transitions(G["a%d_o1" % k], G["a%d_a" % k], G["a%d_r" % k], G["a%d_o2" % k],
+                                G["a%d_lm" % k], G["a%d_t" % k])
+        elif op == "sample":
+            B = int(G["p%d_B" % k])
+            np.random.seed(int(G["p%d_seed" % k]))              # the draw priority_buffer.py:40 made
+            u = np.random.uniform(size=(B,), high=1. / B)
+            idx, prios, tr = sample(buf, B, u)
+            assert list(idx) == G["p%d_idx" % k].tolist(), "op %d sampled indices" % k
+            np.testing.assert_array_equal(np.asarray(prios, np.float64), G["p%d_prios" % k], err_msg="op %d prios" % k)
+            for name, got in zip(("observation_tm1", "action_tm1", "reward_t", "observation_t",
+                                  "legal_moves_t", "terminal_t"), tr):
+                np.testing.assert_array_equal(got, G["p%d_%s" % (k, name)], err_msg="op %d %s" % (k, name))
+        else:
+            buf.update_priorities(G["u%d_idx" % k], G["u%d_td" % k])
+        leaves = leaves_of(buf)
+        assert leaves.shape == (tree_cap,)
+        np.testing.assert_array_equal(leaves, G["s%d_leaves" % k], err_msg="op %d (%s) leaves" % (k, op))
+        assert np.float32(buf.sum_tree.get_total_val()) == G["s%d_total" % k], "op %d total" % k
+        assert np.float32(buf.max_priority) == np.float32(G["s%d_max" % k]), "op %d max_priority" % k
+        assert np.float32(buf.min_priority) == np.float32(G["s%d_min" % k]), "op %d min_priority" % k
+        assert (buf.size, buf.oldest_entry) == (int(G["s%d_size" % k]), int(G["s%d_oldest" % k])), k
+        for name, arr in state_of(buf).items():
+            np.testing.assert_array_equal(arr, G["s%d_%s" % (k, name)], err_msg="op %d ring %s" % (k, name))
+
+
+def test_priority_buffer_against_the_reference_run():
+    G = PGOLD
+    cap, tree_cap = int(G["cap"]), int(G["tree_cap"])
+    buf = OraclePriorityBuffer(int(G["L"]), int(G["A"]), 1, cap, float(G["alpha"]))
+    assert buf.sum_tree.get_capacity() == tree_cap
+    assert list(G["ops"]).count("sample") >= 5 and list(G["ops"]).count("update") >= 5
+    replay_priority_fixture(
+        buf, lambda b: np.array(b.sum_tree.get_values(list(range(tree_cap))), np.float32),
+        lambda b, B, u: b.sample_batch(B, u), _state)

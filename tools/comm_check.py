@@ -1,7 +1,7 @@
 """2+ GPUs (torchrun): the NVLink all-reduce kernel (csrc/comm.cu) against NCCL on the same data,
 then DQNAgent.update with either collective -- parameters must stay bit-identical across ranks, and for
 world size 2 (a + b is commutative) identical between the two collectives.
-  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/test_comm.py"""
+  python -m torch.distributed.run --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29533 tools/comm_check.py"""
 import os
 import sys
 import time

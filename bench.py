@@ -450,6 +450,39 @@ def bench_sum_tree(args):
            "us_per_iter": 1e3 * ms / iters,
            "algorithmic_GBps": 70656 * iters / (ms * 1e-3) / 1e9,
            "note": "latency-bound: 22 dependent levels; 2 launches per iteration"}
+    # The loop above is paced by the HOST (two Python / ctypes calls per iteration cost more than the two
+    # kernels): the same iterations captured once into a CUDA graph and replayed give the device-side
+    # figure -- what a caller inside a captured update (the learner) sees.
+    try:
+        per = min(iters, 256)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            for i in range(3):
+                it(i)
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for i in range(per):
+                    it(i)
+            for _ in range(2):
+                g.replay()
+            side.synchronize()
+            reps = max(1, iters // per)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(side)
+            for _ in range(reps):
+                g.replay()
+            e1.record(side)
+            side.synchronize()
+        gms = e0.elapsed_time(e1)
+        out["graph_replay"] = {"iters": reps * per, "us_per_iter": 1e3 * gms / (reps * per),
+                               "iters_per_s": reps * per / (gms * 1e-3),
+                               "algorithmic_GBps": 70656 * reps * per / (gms * 1e-3) / 1e9,
+                               "note": "%d iterations (sample + update each) captured into one CUDA graph, replayed %d "
+                                       "times: no host pacing" % (per, reps)}
+        torch.cuda.current_stream().wait_stream(side)
+    except Exception as e:  # noqa: BLE001
+        out["graph_replay"] = {"unavailable": repr(e)[:200]}
     # throughput variant (SURVEY 8d cfg 3): 1,024 independent batches of 256 keys in flight in ONE
     # sample launch (descent + leaf gather + total: 4*22 + 4 = 92 algorithmic bytes per key)
     nb = 1024

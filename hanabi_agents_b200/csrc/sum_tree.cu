@@ -20,6 +20,7 @@
 // This file is compiled with -fmad=false: no multiply-add contraction may
 // change the reference's rounding.
 #include "common.cuh"
+#include "sum_tree_dev.cuh"
 #include <math.h>
 #include <new>
 
@@ -38,45 +39,39 @@ struct hb_sumtree {
 
 namespace {
 
-constexpr int kTopLevels = 11;                // levels 0..10 staged in smem
-constexpr int kTopNodes = 1 << kTopLevels;    // heap[1 .. 2047]
+using hbst::kTopNodes;
+using hbst::ld_cg;
+using hbst::st_cg;
 constexpr int kDescendThreads = 256;
+constexpr int64_t kLatencyKeys = 16384;       // up to this many keys per launch: the latency-optimised descent
 constexpr int kPass = 1024;                   // batch elements per update pass
 
-__device__ __forceinline__ float ld_cg(const float* p) { return __ldcg(p); }
-__device__ __forceinline__ void st_cg(float* p, float v) { __stcg(p, v); }
-
 // ---- stratified prefix-sum descent (ST-2) + leaf gather (ST-3) -------------
-template <bool kWithValues>
+// hbst::descend: the top 11 levels from shared memory, then four levels per L2 round trip
+// (sum_tree_dev.cuh); the leaf value comes out of the last fetched block, so ST-3 costs no load.
+// kLatency: few keys (a learner batch): four levels per round trip through shared-memory scratch;
+// otherwise (thousands of keys in flight) the plain one-level-per-load walk, which keeps more warps resident.
+template <bool kWithValues, bool kLatency>
 __global__ void __launch_bounds__(kDescendThreads)
 st_descend_kernel(const float* __restrict__ heap, int depth, int64_t cap,
                   const float* __restrict__ q_in, int64_t* __restrict__ idx_out,
                   float* __restrict__ val_out, float* __restrict__ total_out, int64_t n) {
   __shared__ float top[kTopNodes];
-  const int staged = (int)min((int64_t)kTopNodes, 2 * cap);  // heap entries [0, staged)
-  for (int i = threadIdx.x; i < staged; i += kDescendThreads) top[i] = ld_cg(heap + i);
-  __syncthreads();
-
+  __shared__ float4 scratch[kLatency ? 8 * kDescendThreads : 1];
   const int64_t k = (int64_t)blockIdx.x * kDescendThreads + threadIdx.x;
+  const float quant = k < n ? q_in[k] : 0.f;      // in flight while the top levels are staged
+  const int staged = hbst::stage_top(heap, cap, top);
   const float root = top[1];
   if (kWithValues && total_out != nullptr && k == 0) *total_out = root;
   if (k >= n) return;
-
-  float q = q_in[k] * root;  // getIndex: quantile * root_->value   sum_tree.h:47
-  int64_t node = 1;
-  for (int l = 0; l < depth; ++l) {
-    const int64_t left = node << 1;
-    const float lv = left < staged ? top[left] : ld_cg(heap + left);
-    if (q < lv) {             // sum_tree.h:99
-      node = left;
-    } else {                  // sum_tree.h:104
-      q = q - lv;
-      node = left + 1;
-    }
-  }
-  const int64_t leaf = node - cap;
-  idx_out[k] = leaf;
-  if (kWithValues) val_out[k] = node < staged ? top[node] : ld_cg(heap + node);
+  const float q = __fmul_rn(quant, root);         // getIndex: quantile * root_->value   sum_tree.h:47
+  float leaf_value;
+  const int64_t node = kLatency
+      ? hbst::descend(heap, top, staged, depth, q, &leaf_value, reinterpret_cast<float*>(scratch + threadIdx.x),
+                      kDescendThreads)
+      : hbst::descend_throughput(heap, top, staged, depth, q, &leaf_value);
+  idx_out[k] = node - cap;
+  if (kWithValues) val_out[k] = leaf_value;
 }
 
 __global__ void st_gather_kernel(const float* __restrict__ heap, int64_t cap,
@@ -138,25 +133,46 @@ st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
           }
         }
         __syncthreads();
+        // (level, element) items, eight per thread at a time: first the loads of every run head among
+        // them (independent of one another -- a node is the head of exactly one run -- so the L2 round
+        // trips overlap instead of queueing behind each other's stores), then the ordered adds.
         const int items = depth * pass_n;
-        for (int it = threadIdx.x; it < items; it += blockDim.x) {
-          const int l = it / pass_n, b = it - l * pass_n;      // level l: shift = depth - l
-          const int shift = depth - l;
-          const int64_t node = s_leaf[b] >> shift;
-          if (b == 0 || (s_leaf[b - 1] >> shift) != node) {
-            float sacc = ld_cg(heap + node);
-            int j = b;
+        for (int it0 = threadIdx.x; it0 < items; it0 += 8 * blockDim.x) {
+          float sacc[8];
+          int64_t nodes[8];
+          int shifts[8], firsts[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int it = it0 + u * blockDim.x;
+            nodes[u] = -1;
+            if (it < items) {
+              const int l = it / pass_n, b = it - l * pass_n;    // level l: shift = depth - l
+              const int shift = depth - l;
+              const int64_t node = s_leaf[b] >> shift;
+              if (b == 0 || (s_leaf[b - 1] >> shift) != node) {
+                nodes[u] = node; shifts[u] = shift; firsts[u] = b;
+                sacc[u] = ld_cg(heap + node);
+              }
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            if (nodes[u] < 0) continue;
+            const int64_t node = nodes[u];
+            const int shift = shifts[u];
+            float acc = sacc[u];
+            int j = firsts[u];
             // whole groups of 8 inside the run: the loads are independent, the adds stay ordered
             while (j + 8 <= pass_n && (s_leaf[j + 7] >> shift) == node) {
               float d[8];
 #pragma unroll
-              for (int u = 0; u < 8; ++u) d[u] = s_diff[j + u];
+              for (int v = 0; v < 8; ++v) d[v] = s_diff[j + v];
 #pragma unroll
-              for (int u = 0; u < 8; ++u) sacc = sacc + d[u];
+              for (int v = 0; v < 8; ++v) acc = acc + d[v];
               j += 8;
             }
-            for (; j < pass_n && (s_leaf[j] >> shift) == node; ++j) sacc = sacc + s_diff[j];
-            st_cg(heap + node, sacc);
+            for (; j < pass_n && (s_leaf[j] >> shift) == node; ++j) acc = acc + s_diff[j];
+            st_cg(heap + node, acc);
           }
         }
         __syncthreads();
@@ -660,8 +676,12 @@ int hb_st_get_indices(hb_sumtree* t, const float* d_q, int64_t* d_out, int64_t n
   HB_REQUIRE(d_q && d_out, "hb_st_get_indices: NULL buffer");
   hb::DeviceGuard g(t->device);
   const unsigned blocks = (unsigned)((n + kDescendThreads - 1) / kDescendThreads);
-  st_descend_kernel<false><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
-      t->heap, t->depth, t->cap, d_q, d_out, nullptr, nullptr, n);
+  if (n <= kLatencyKeys)
+    st_descend_kernel<false, true><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+        t->heap, t->depth, t->cap, d_q, d_out, nullptr, nullptr, n);
+  else
+    st_descend_kernel<false, false><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+        t->heap, t->depth, t->cap, d_q, d_out, nullptr, nullptr, n);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -676,8 +696,12 @@ int hb_st_sample(hb_sumtree* t, const float* d_q, int64_t* d_idx_out, float* d_v
   HB_REQUIRE(d_q && d_idx_out && d_val_out, "hb_st_sample: NULL buffer");
   hb::DeviceGuard g(t->device);
   const unsigned blocks = (unsigned)((n + kDescendThreads - 1) / kDescendThreads);
-  st_descend_kernel<true><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
-      t->heap, t->depth, t->cap, d_q, d_idx_out, d_val_out, d_total, n);
+  if (n <= kLatencyKeys)
+    st_descend_kernel<true, true><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+        t->heap, t->depth, t->cap, d_q, d_idx_out, d_val_out, d_total, n);
+  else
+    st_descend_kernel<true, false><<<blocks, kDescendThreads, 0, (cudaStream_t)stream>>>(
+        t->heap, t->depth, t->cap, d_q, d_idx_out, d_val_out, d_total, n);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }

@@ -40,6 +40,7 @@ SIGNATURES = {
     "hb_st_heap": (vp, [vp]),
     "hb_st_update": (i32, [vp, vp, vp, i64, vp]),
     "hb_st_update_range": (i32, [vp, i64, i64, vp, f32, vp]),
+    "hb_st_update_range_noalloc": (i32, [vp, i64, i64, vp, f32, vp]),
     "hb_st_get_indices": (i32, [vp, vp, vp, i64, vp]),
     "hb_st_get_values": (i32, [vp, vp, vp, i64, vp]),
     "hb_st_total": (i32, [vp, vp, vp]),

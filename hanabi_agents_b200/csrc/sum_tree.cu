@@ -670,6 +670,79 @@ static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const f
   return HB_OK;
 }
 
+// ---- allocation-free range update ---------------------------------------------------------------
+// hb_st_update_range keeps its per-element diffs in t->scratch, grown with cudaMalloc on demand.  Callers
+// that must not allocate (stream capture, serving loops, harnesses that forbid cudaMalloc) get the same
+// kernels over a fixed scratch array that lives in the library image: kNoAllocMaxRange floats (256 KB) on
+// every GPU that loads the library, until the process exits.
+constexpr int64_t kNoAllocMaxRange = 65536;
+static __device__ __align__(256) float g_noalloc_range_scratch[kNoAllocMaxRange];
+
+namespace {
+// In host code `g_noalloc_range_scratch` is only a stand-in for the symbol, not a device address: the
+// address is looked up once per device, with that device current, and handed to the kernels.
+int noalloc_scratch_ptr(int device, float** out) {
+  static float* ptr[64] = {nullptr};
+  if (device < 0 || device >= 64) { hb::set_error("hb_st_update_range_noalloc: device %d out of range", device); return HB_ERR_INVALID; }
+  if (ptr[device] == nullptr) {
+    float* p = nullptr;
+    cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_range_scratch);   // the caller made `device` current
+    if (e != cudaSuccess) return hb::cuda_fail(e, "cudaGetSymbolAddress(g_noalloc_range_scratch)", __FILE__, __LINE__);
+    if (p == nullptr) { hb::set_error("hb_st_update_range_noalloc: NULL scratch address"); return HB_ERR_CUDA; }
+    ptr[device] = p;
+  }
+  *out = ptr[device];
+  return HB_OK;
+}
+}  // namespace
+
+int hb_st_update_range_noalloc(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
+                               void* stream) {
+  HB_REQUIRE(t && n >= 0, "hb_st_update_range_noalloc: bad arguments");
+  if (n == 0) return HB_OK;
+  if (n > kNoAllocMaxRange) {
+    hb::set_error("hb_st_update_range_noalloc: %lld elements exceed the fixed scratch of %lld (use hb_st_update_range, "
+                  "or split the range)", (long long)n, (long long)kNoAllocMaxRange);
+    return HB_ERR_INVALID;
+  }
+  if (start < 0 || start + n > t->cap) {
+    hb::set_error("hb_st_update_range_noalloc: [%lld,%lld) outside capacity %lld", (long long)start,
+                  (long long)(start + n), (long long)t->cap);
+    return HB_ERR_INDEX;
+  }
+  hb::DeviceGuard g(t->device);
+  float* scratch = nullptr;
+  int rc = noalloc_scratch_ptr(t->device, &scratch);
+  if (rc) return rc;
+  cudaStream_t s = (cudaStream_t)stream;
+  // The array keeps the previous call's diffs; nothing has to start at zero: st_range_leaf_kernel writes
+  // diff[0 .. n) before any kernel of this call reads it (stream order), and nothing beyond n is read.
+  const int threads = 256;
+  st_range_leaf_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, s>>>(
+      t->heap, t->cap, start, n, d_val, fill, nullptr, scratch);
+  HB_CUDA(cudaGetLastError());
+  if (t->depth > 0) {   // the level split of hb_st_update_range: scan / warp chain / thread per node
+    const int scan_levels = t->depth >= kScanSpanLog2 ? t->depth - kScanSpanLog2 + 1 : 0;
+    const int warp_levels = (t->depth >= 6 ? t->depth - 5 : 0) - scan_levels;
+    if (scan_levels > 0) {
+      dim3 grid((unsigned)((n >> kScanSpanLog2) + 2), (unsigned)scan_levels);
+      st_range_internal_scan_kernel<<<grid, kScanThreads, 0, s>>>(t->heap, t->depth, t->cap, start, n, scratch);
+      HB_CUDA(cudaGetLastError());
+    }
+    if (warp_levels > 0) {
+      dim3 grid((unsigned)((n / 64 + 2 + 3) / 4), (unsigned)warp_levels);
+      st_range_internal_warp_kernel<<<grid, 128, 0, s>>>(t->heap, t->depth, t->cap, start, n, scratch, scan_levels);
+      HB_CUDA(cudaGetLastError());
+    }
+    const int upper = scan_levels + warp_levels;
+    const int th = 128;
+    dim3 grid((unsigned)((n / 2 + 2 + th - 1) / th), (unsigned)(t->depth - upper));
+    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, scratch, upper);
+    HB_CUDA(cudaGetLastError());
+  }
+  return HB_OK;
+}
+
 int hb_st_get_indices(hb_sumtree* t, const float* d_q, int64_t* d_out, int64_t n, void* stream) {
   HB_REQUIRE(t && n >= 0, "hb_st_get_indices: bad arguments");
   if (n == 0) return HB_OK;

@@ -77,6 +77,19 @@ int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_v
  * max_priority on the device: priority_buffer.py:29-31 without a host round trip). */
 int hb_st_update_range_dev(hb_sumtree* t, int64_t start, int64_t n, const float* d_fill,
                            void* stream);
+/* hb_st_update_range without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same kernels and the same bits as hb_st_update_range; the
+ * per-element diffs live in a fixed file-scope __device__ array of HB_ST_NOALLOC_MAX_RANGE floats
+ * (256 KB, held by every GPU that loads the library until the process exits) instead of a buffer grown
+ * with cudaMalloc.  n > HB_ST_NOALLOC_MAX_RANGE is rejected with HB_ERR_INVALID.  The call itself uses
+ * no cudaMalloc / cudaFree / allocating routine; the first call on a device looks the array's address up
+ * (cudaGetSymbolAddress, once per device).  Every call on a device SHARES the array: calls that overlap
+ * on the GPU (different streams, or different trees on different streams) race -- keep them on one
+ * stream or order them with events.  Nothing in the array has to start at zero. */
+#define HB_ST_NOALLOC_MAX_RANGE 65536
+int hb_st_update_range_noalloc(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
+                               void* stream);
 /* getIndices(quantiles)  sum_tree.h:52-59 -> getIndex :46-50 -> getIndex_ :92-105 */
 int hb_st_get_indices(hb_sumtree* t, const float* d_q, int64_t* d_out, int64_t n, void* stream);
 /* getValues(indices)  sum_tree.h:65-72 (.at() bounds check -> sticky error flag) */

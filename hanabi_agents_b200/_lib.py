@@ -90,6 +90,7 @@ SIGNATURES = {
     "hb_rb_check": (i32, [vp, vp]),
     "hb_rb_sample": (i32, [vp, vp, i64, vp, vp, vp, vp]),
     "hb_rb_update_priorities": (i32, [vp, vp, vp, i64, vp]),
+    "hb_rb_sample_gather": (i32, [vp, vp, i32, vp, vp, f32, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, vp]),
     "hb_rb_priority_range": (i32, [vp, C.POINTER(f32), C.POINTER(f32), vp]),
     "hb_pack_bits": (i32, [vp, i32, vp, i32, i64, vp]),
     "hb_unpack_bits": (i32, [vp, i32, i32, vp, i64, vp]),

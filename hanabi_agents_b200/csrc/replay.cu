@@ -13,6 +13,7 @@
 // two-level ballot scan so that their order -- and therefore the ring and sum-tree contents --
 // is the reference's.
 #include "common.cuh"
+#include "sum_tree_dev.cuh"
 #include <new>
 
 struct hb_replay {
@@ -217,6 +218,89 @@ __global__ void prios_kernel(const float* __restrict__ val, const float* __restr
   const double p = ((double)val[i] + 1e-10) / (double)*total;
   if (p64) p64[i] = p;
   if (p32) p32[i] = (float)p;
+}
+
+// The learner's front end in ONE launch (one CTA of 1024 threads, B <= 1024):
+//   keys -> indices      SumTree::getIndices   (priority_buffer.py:41; sum_tree.h:46-59)
+//   prios                (getValues(indices) + 1e-10) / getTotalVal() in float64      (:42)
+//   weights_is           (1 / prios)^beta / max(.) in float32         (rlax_rainbow.py:188-189)
+//   transitions          self[indices]         (priority_buffer.py:46; experience_buffer.py:83-87)
+// It replaces four dependent launches (H2D copy of the keys, descent, prios, gather) and the
+// is_weights kernel of the network on the update's critical path.
+// `keys` and `dyn_in` may be pinned host memory (read in place over PCIe: 1 KB).  dyn_in[0..7] are the
+// step's scalars (beta, discount, ...): copied to dyn_out (device) for the kernels that follow.
+__global__ void __launch_bounds__(1024)
+sample_gather_kernel(hb_replay rb, const float* __restrict__ heap, int depth, int64_t tree_cap,
+                     const float* __restrict__ keys, int B, const float* __restrict__ dyn_in,
+                     float* __restrict__ dyn_out, float beta_value, int64_t* __restrict__ idx_out,
+                     float* __restrict__ prios32, double* __restrict__ prios64, float* __restrict__ w_is,
+                     uint32_t* __restrict__ obs_tm1, int32_t* __restrict__ act, float* __restrict__ rew,
+                     uint32_t* __restrict__ obs_t, uint32_t* __restrict__ lms, uint8_t* __restrict__ term,
+                     int* err) {
+  __shared__ float top[hbst::kTopNodes];
+  __shared__ int64_t s_pos[1024];
+  __shared__ float red[32];
+  extern __shared__ float4 scratch[];                      // [8 chunks][nd threads], nd = B rounded up to 32
+  const int nd = (B + 31) & ~31;
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const int k = threadIdx.x;
+  if (k == 0) *err = 0;                                   // ordered before any `*err = 1` by stage_top's barrier
+  const float quant = k < B ? keys[k] : 0.f;              // in flight while the top levels are staged
+  float beta = beta_value;
+  if (dyn_in != nullptr) {
+    beta = dyn_in[0];
+    if (k < 8) dyn_out[k] = dyn_in[k];
+  }
+  const int staged = hbst::stage_top(heap, tree_cap, top);
+  const float root = top[1];
+  float w = 0.f;
+  if (k < B) {
+    const float q = __fmul_rn(quant, root);               // sum_tree.h:47
+    float value;
+    const int64_t node = hbst::descend(heap, top, staged, depth, q, &value,
+                                       reinterpret_cast<float*>(scratch + k), nd);
+    int64_t pos = node - tree_cap;
+    idx_out[k] = pos;
+    if (pos < 0) pos += rb.cap;                           // numpy negative indexing (never taken here)
+    if (pos < 0 || pos >= rb.cap) { *err = 1; pos = 0; }  // a leaf beyond the ring: caller's IndexError
+    s_pos[k] = pos;
+    const double p = ((double)value + 1e-10) / (double)root;
+    const float p32 = (float)p;
+    if (prios64 != nullptr) prios64[k] = p;
+    if (prios32 != nullptr) prios32[k] = p32;
+    w = powf(1.0f / p32, beta);
+    if (act) act[k] = rb.act[pos];
+    if (rew) rew[k] = rb.rew[pos];
+    if (term) term[k] = rb.term[pos];
+    if (lms)
+      for (int j = 0; j < rb.legal_words; ++j) lms[(int64_t)k * rb.legal_words + j] = rb.lms[pos * rb.legal_words + j];
+  }
+  // max over the batch (weights are positive; lanes past B hold 0)
+  float mx = w;
+  for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  if ((k & 31) == 0) red[k >> 5] = mx;
+  __syncthreads();                                        // also publishes s_pos
+  if (k < 32) {
+    mx = red[k];
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (k == 0) red[0] = mx;
+  }
+  __syncthreads();
+  if (k < B && w_is != nullptr) w_is[k] = w / red[0];
+  // gather: (row, 16-byte chunk) items over the whole CTA, every load independent of the others
+  const int q16 = rb.stride >> 2;
+  const uint4* s1 = reinterpret_cast<const uint4*>(rb.obs_tm1);
+  const uint4* s2 = reinterpret_cast<const uint4*>(rb.obs_t);
+  uint4* d1 = reinterpret_cast<uint4*>(obs_tm1);
+  uint4* d2 = reinterpret_cast<uint4*>(obs_t);
+  const int items = B * q16;
+  for (int it = k; it < items; it += 1024) {
+    const int r = it / q16, c = it - r * q16;
+    const int64_t src = s_pos[r] * q16 + c;
+    if (d1) d1[it] = s1[src];
+    if (d2) d2[it] = s2[src];
+  }
 }
 
 // priorities = (|td| + 1e-10) ** alpha in float32, running max / min  (priority_buffer.py:49-51).
@@ -524,6 +608,42 @@ int hb_rb_sample(hb_replay* rb, const float* d_keys, int64_t n, int64_t* d_idx, 
   if (rc) return rc;
   prios_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(rb->vals, rb->vals + n, n, d_prios64, d_prios32);
   HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int hb_rb_sample_gather(hb_replay* rb, const float* d_keys, int B, const float* d_dyn_in, float* d_dyn_out,
+                        float beta, int64_t* d_idx, float* d_prios32, double* d_prios64, float* d_w_is,
+                        uint32_t* d_obs_tm1, int32_t* d_act, float* d_rew, uint32_t* d_obs_t,
+                        uint32_t* d_lms, uint8_t* d_term, int pdl, void* stream) {
+  HB_REQUIRE(rb && rb->prioritized && d_keys && d_idx && B >= 1 && B <= 1024,
+             "hb_rb_sample_gather: bad arguments (prioritized shard, 1 <= B <= 1024)");
+  HB_REQUIRE((d_dyn_in == nullptr) == (d_dyn_out == nullptr), "hb_rb_sample_gather: dyn_in and dyn_out go together");
+  HB_REQUIRE((((uintptr_t)d_obs_tm1 | (uintptr_t)d_obs_t) & 15) == 0, "hb_rb_sample_gather: rows must be 16-byte aligned");
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(1024);
+  cfg.dynamicSmemBytes = (size_t)((B + 31) & ~31) * hbst::kScratchBytesPerThread;
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  {   // static (top levels, positions) + dynamic (descent scratch) shared memory exceeds 48 KB from B = 256 on
+    static bool configured[64] = {false};
+    if (rb->device < 0 || rb->device >= 64 || !configured[rb->device]) {
+      HB_CUDA(cudaFuncSetAttribute(sample_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 131072));
+      if (rb->device >= 0 && rb->device < 64) configured[rb->device] = true;
+    }
+  }
+  const float* heap = hb_st_heap(rb->tree);
+  const int depth = hb_st_depth(rb->tree);
+  const int64_t tcap = hb_st_capacity(rb->tree);
+  HB_CUDA(cudaLaunchKernelEx(&cfg, sample_gather_kernel, *rb, heap, depth, tcap, d_keys, B, d_dyn_in, d_dyn_out,
+                             beta, d_idx, d_prios32, d_prios64, d_w_is, d_obs_tm1, d_act, d_rew, d_obs_t,
+                             d_lms, d_term, (int*)rb->total));
   return HB_OK;
 }
 

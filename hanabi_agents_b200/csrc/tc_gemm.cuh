@@ -70,7 +70,19 @@ struct EpiParams {
   // ABITS kernels: the A operand is bit-packed rows (bit k of row m at word k>>5, position k&31)
   const uint32_t* a_bits;    // [M, a_stride] words
   int a_stride;
+  // host side only: launch with programmatic stream serialization, i.e. this kernel's prologue
+  // (barrier init, TMEM allocation, tensor-map prefetch) may run while the previous kernel of the
+  // stream is still finishing; every global access sits behind griddepcontrol.wait
+  int pdl;
 };
+
+// Programmatic dependent launch (PDL).  wait: returns once every grid this one depends on has
+// completed and its memory is visible (a no-op for a launch without the attribute).  launch_dependents:
+// the next kernel of the stream may start its own prologue now.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
 
 // ---------------------------------------------------------------- PTX wrappers ----
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
@@ -475,6 +487,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // everything above touched no global memory; the operands may still be in the making
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 0) {
     if (lane == 0) {

@@ -67,8 +67,17 @@ inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   const long long tiles = (long long)((N + BN_ - 1) / BN_) * ((M + BM - 1) / BM);
   const int sms = sm_count();
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
-  gemm_f16_kernel<EPI, BN_, ABITS><<<grid, kThreads, smem_bytes_for(BN_), stream>>>(ta, tb, tout, K, ep);
-  HB_CUDA(cudaGetLastError());
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = ep.pdl ? 1 : 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem_bytes_for(BN_);
+  cfg.stream = stream;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  HB_CUDA(cudaLaunchKernelEx(&cfg, gemm_f16_kernel<EPI, BN_, ABITS>, ta, tb, tout, K, ep));
   return HB_OK;
 }
 

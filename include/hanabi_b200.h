@@ -260,6 +260,17 @@ int hb_rb_check(hb_replay* rb, void* stream);
  * jitted learner sees).  Keys are explicit so that "identical uniforms" is well defined. */
 int hb_rb_sample(hb_replay* rb, const float* d_keys, int64_t n, int64_t* d_idx, double* d_prios64,
                  float* d_prios32, void* stream);
+/* sample_batch + the learner's importance weights in ONE launch (B <= 1024): indices = get_indices(keys)
+ * (priority_buffer.py:41), prios = (get_values + 1e-10) / get_total_val in float64 (:42; d_prios32 = the
+ * float32 narrowing), weights_is = (1 / prios32)^beta / max (rlax_rainbow.py:188-189) and self[indices]
+ * (:46) gathered into the caller's buffers (any output but d_idx may be NULL).  d_keys may be pinned host
+ * memory (read in place).  d_dyn_in (optional, 8 floats, may be pinned host memory): [0] replaces `beta`,
+ * all 8 are copied to d_dyn_out (device) for the kernels that follow.  pdl != 0: programmatic dependent
+ * launch behind the previous kernel of the stream.  hb_rb_check reports a leaf outside the ring. */
+int hb_rb_sample_gather(hb_replay* rb, const float* d_keys, int B, const float* d_dyn_in, float* d_dyn_out,
+                        float beta, int64_t* d_idx, float* d_prios32, double* d_prios64, float* d_w_is,
+                        uint32_t* d_obs_tm1, int32_t* d_act, float* d_rew, uint32_t* d_obs_t,
+                        uint32_t* d_lms, uint8_t* d_term, int pdl, void* stream);
 /* update_priorities (priority_buffer.py:48-52): p = (|td| + 1e-10) ** alpha in float32 (power
  * evaluated in double and rounded once), running max / min, ordered sum-tree scatter. */
 int hb_rb_update_priorities(hb_replay* rb, const int64_t* d_idx, const float* d_td_abs, int64_t n,

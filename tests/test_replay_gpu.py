@@ -146,3 +146,41 @@ def test_priority_buffer_against_the_reference_run():
     replay_priority_fixture(
         buf, lambda b: np.array(b.sum_tree.get_values(list(range(tree_cap))), np.float32),
         lambda b, B, u: b.sample_batch(B, u), _all_rows)
+
+
+@pytest.mark.parametrize("B,cap", [(256, 5000), (32, 300), (1000, 70000)])
+def test_fused_sample_gather_matches_the_separate_calls(B, cap):
+    """hb_rb_sample_gather (one launch: descent + probabilities + importance weights + row gather, the
+    learner's front end) against hb_rb_sample + hb_rb_gather and the float32 statements of
+    rlax_rainbow.py:188-189 on their output: indices / probabilities / rows bit-exact, weights to 1 ulp
+    (powf on the device vs numpy)."""
+    import torch
+    from hanabi_agents_b200 import _lib
+    from hanabi_agents_b200.rlax_dqn import PriorityBuffer
+    L, A = 658, 20
+    rng = np.random.default_rng(B)
+    buf = PriorityBuffer(L, A, 1, cap)
+    for _ in range(3):
+        buf.add_transitions(*_rand_tr(rng, cap // 3, L, A))
+        idx0, _, _ = buf.sample_batch(64, rng.uniform(0, 1 / 64, 64))
+        buf.update_priorities(idx0, np.abs(rng.standard_normal(64)).astype(np.float32) * 2)
+    u = rng.uniform(0, 1.0 / B, B)
+    idx, p64, p32, (o1, a, r, o2, lm, t) = buf.sample_device(B, u)
+    keys = torch.as_tensor(PriorityBuffer.stratified_keys(B, u).astype(np.float32), device="cuda")
+    dyn_in = torch.tensor([0.4, 0.99, 1e-3, 0.9, 0.999, 3e-5, 1.0, 0.0], device="cuda")
+    dyn_out = torch.zeros(8, device="cuda")
+    e = lambda shape, dt: torch.zeros(shape, dtype=dt, device="cuda")  # noqa: E731
+    f_idx, f_p32, f_p64, f_w = e(B, torch.int64), e(B, torch.float32), e(B, torch.float64), e(B, torch.float32)
+    f_o1, f_o2 = e((B, buf.obs_stride), torch.int32), e((B, buf.obs_stride), torch.int32)
+    f_a, f_r, f_lm, f_t = e(B, torch.int32), e(B, torch.float32), e((B, buf.legal_words), torch.int32), e(B, torch.uint8)
+    _lib.check(_lib.lib().hb_rb_sample_gather(
+        buf._h, keys.data_ptr(), B, dyn_in.data_ptr(), dyn_out.data_ptr(), 0.0, f_idx.data_ptr(), f_p32.data_ptr(),
+        f_p64.data_ptr(), f_w.data_ptr(), f_o1.data_ptr(), f_a.data_ptr(), f_r.data_ptr(), f_o2.data_ptr(),
+        f_lm.data_ptr(), f_t.data_ptr(), 0, _lib.current_stream_ptr()))
+    _lib.check(_lib.lib().hb_rb_check(buf._h, _lib.current_stream_ptr()))
+    for got, want in ((f_idx, idx), (f_p64, p64), (f_p32, p32), (f_o1, o1), (f_o2, o2), (f_a, a), (f_r, r),
+                      (f_lm, lm), (f_t, t), (dyn_out, dyn_in)):
+        assert torch.equal(got, want)
+    w = np.power(np.float32(1.0) / p32.cpu().numpy(), np.float32(0.4)).astype(np.float32)
+    w = w / w.max()
+    np.testing.assert_allclose(f_w.cpu().numpy(), w, rtol=3e-7, atol=0)

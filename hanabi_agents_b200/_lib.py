@@ -110,6 +110,9 @@ SIGNATURES = {
     "hb_net_forward": (i32, [vp, vp, i64, i32, vp, vp, vp]),
     "hb_net_grads": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp]),
     "hb_net_adam": (i32, [vp, f32, f32, f32, f32, f32, vp]),
+    "hb_net_grads_ex": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp, vp]),
+    "hb_net_is_weights": (vp, [vp, i32]),
+    "hb_net_adam_dyn": (i32, [vp, vp, vp]),
     # fused learner step
     "hb_learner_create": (i32, [vp, vp, i32, i32, C.POINTER(vp)]),
     "hb_learner_destroy": (i32, [vp]),

@@ -70,6 +70,10 @@ struct hb_qnet {
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_loss = nullptr, ev_wt = nullptr,
               ev_dz[kMaxLayers] = {nullptr};
   cudaStream_t side2 = nullptr;        // small kernels beside the GEMMs of `side`
+  // one stream per layer for {dW_l GEMM -> Adam_l}: layer l's update starts as soon as dZ_l exists and
+  // runs beside the rest of the backward pass (single-process learner, hb_net_grads_ex adam_per_layer)
+  cudaStream_t lstream[kMaxLayers] = {nullptr};
+  cudaEvent_t ev_bias[kMaxLayers] = {nullptr}, ev_layer[kMaxLayers] = {nullptr}, ev_tick = nullptr;
   __half* x = nullptr;                 // [2B, K0]
   __half* xt = nullptr;                // [K0, Bp]
   __half* h[kMaxLayers] = {nullptr};   // hidden activations, online [2B, N]
@@ -245,8 +249,11 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
                                 const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
                                 const uint8_t* __restrict__ term_t, int mask_terminal,
                                 const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
-                                float gamma, __half* __restrict__ dz, __half* __restrict__ dzt,
-                                int ld_dzt, float* __restrict__ loss_b) {
+                                float gamma, const float* __restrict__ dyn, __half* __restrict__ dz,
+                                __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b) {
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
   const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (b >= B) return;
@@ -329,8 +336,12 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
 __global__ void dqn_loss_kernel(const float* __restrict__ q_on, int ldq, const float* __restrict__ q_t,
                                 const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
                                 const uint8_t* __restrict__ term_t, const float* __restrict__ w_is,
-                                int B, int A, float gamma, __half* __restrict__ dz, int ld_dz,
+                                int B, int A, float gamma, const float* __restrict__ dyn,
+                                __half* __restrict__ dz, int ld_dz,
                                 __half* __restrict__ dzt, int ld_dzt, float* __restrict__ td_out) {
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  if (dyn != nullptr) gamma = dyn[1];
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= B) return;
   const float* qs = q_on + (long long)(B + b) * ldq;     // online(obs_t)
@@ -381,8 +392,10 @@ __global__ void bias_grad_kernel(const __half* __restrict__ zt, int ld, int N, i
 // Fused Adam (optix.adam: m, v, bias correction, theta -= lr * mhat / (sqrt(vhat) + eps)) over the
 // flat effective-parameter space + refresh of the fp16 effective weights in both layouts.
 // do_update == 0: refresh only (after parameters were loaded).
+// [i4_begin, i4_end): the range of 4-element groups to update (everything, or one layer).
 template <int KINDS>
-__global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds*/, float* __restrict__ master,
+__global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, long long i4_begin, long long i4_end,
+                                    float* __restrict__ master,
                                     const float* __restrict__ eps_noise, float* __restrict__ am,
                                     float* __restrict__ av, const float* __restrict__ grad,
                                     float grad_scale, int do_update, float lr, float b1, float b2,
@@ -393,12 +406,14 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, int /*kinds
   // [5] lr sqrt(1 - b2^t) / (1 - b1^t).  (Two powf and 24 IEEE divisions per thread were most of this kernel.)
   float r1 = 1.f, r2 = 1.f, lr_tf = 0.f;
   if (do_update) {
+    // the step's hyper-parameters as the tick kernel left them ([6..10]: they may have come from the
+    // learner's staging slot rather than from this launch's arguments, which a replayed graph freezes)
     const float* sc = reinterpret_cast<const float*>(step_ptr);
     r1 = sc[3]; r2 = sc[4]; lr_tf = sc[5];
+    lr = sc[6]; b1 = sc[7]; b2 = sc[8]; eps = sc[9]; grad_scale = sc[10];
   }
   // four consecutive parameters per thread (every block boundary is a multiple of 8 elements)
-  const long long n4 = n_eff >> 2;
-  for (long long i4 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < n4;
+  for (long long i4 = i4_begin + (long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < i4_end;
        i4 += (long long)gridDim.x * blockDim.x) {
     const long long i = i4 << 2;
     int l = 0;
@@ -488,12 +503,18 @@ __global__ void transpose16_kernel(LayerTable tab, const __half* __restrict__ w1
 
 // step counter and this step's bias corrections: step[0] = t, then as floats [1] 1 - b1^t, [2] 1 - b2^t,
 // [3] [4] their reciprocals, [5] lr sqrt(1 - b2^t) / (1 - b1^t)  (tf.train.AdamOptimizer's lr_t)
-__global__ void adam_tick_kernel(int* step, float b1, float b2, float lr) {
+// [6..10] lr, b1, b2, eps, grad_scale of this step.  dyn (optional; device or pinned host memory):
+// [2] lr [3] b1 [4] b2 [5] eps [6] grad_scale replace the by-value arguments -- a replayed CUDA graph
+// freezes its kernel arguments, the learner's schedules (learning rate, ...) must not force a re-capture.
+__global__ void adam_tick_kernel(int* step, float b1, float b2, float lr, float eps, float grad_scale,
+                                 const float* __restrict__ dyn) {
+  if (dyn != nullptr) { lr = dyn[2]; b1 = dyn[3]; b2 = dyn[4]; eps = dyn[5]; grad_scale = dyn[6]; }
   const int t = *step + 1;
   *step = t;
   float* sc = reinterpret_cast<float*>(step);
   const float bc1 = 1.0f - powf(b1, (float)t), bc2 = 1.0f - powf(b2, (float)t);
   sc[1] = bc1; sc[2] = bc2; sc[3] = 1.0f / bc1; sc[4] = 1.0f / bc2; sc[5] = lr * sqrtf(bc2) / bc1;
+  sc[6] = lr; sc[7] = b1; sc[8] = b2; sc[9] = eps; sc[10] = grad_scale;
 }
 __global__ void fill_kernel(float* p, float v, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -544,6 +565,12 @@ int ensure_learner_ws(hb_qnet* q, int B) {
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_loss, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_wt, cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
+    for (int l = 0; l < kMaxLayers; ++l) {
+      HB_CUDA(cudaStreamCreateWithFlags(&q->lstream[l], cudaStreamNonBlocking));
+      HB_CUDA(cudaEventCreateWithFlags(&q->ev_bias[l], cudaEventDisableTiming));
+      HB_CUDA(cudaEventCreateWithFlags(&q->ev_layer[l], cudaEventDisableTiming));
+    }
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_tick, cudaEventDisableTiming));
   }
   if ((rc = dev_alloc(&q->xt, (size_t)K0 * Bp))) return rc;
   for (int l = 0; l < nl; ++l) {
@@ -598,7 +625,7 @@ int launch_unpack(const uint32_t* packed, int stride, long long rows, __half* ou
 // q (and logits when given).
 int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0, long long rows,
             __half* const* hbuf, __half* const* hbuf_t, int ld_t, float* logits, float* q_out, int ldq,
-            cudaStream_t s, const uint32_t* x_bits = nullptr) {
+            cudaStream_t s, const uint32_t* x_bits = nullptr, int pdl = 0) {
   const __half* in = x0;
   int ld_in = net->tab.l[0].K;
   const int nl = net->n_layers;
@@ -607,6 +634,7 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
     tc::EpiParams ep{};
     ep.alpha = 1.f;
     ep.bias = bias + g.boff;
+    ep.pdl = pdl;
     int rc;
     if (l < nl - 1) {
       ep.relu = 1;
@@ -649,26 +677,40 @@ int launch_transposes(hb_qnet* net, cudaStream_t s) {
   return HB_OK;
 }
 
-int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
-             cudaStream_t s, int tf_style = 0) {
+int adam_tick(hb_qnet* net, float lr, float b1, float b2, float eps, float grad_scale, const float* dyn,
+              cudaStream_t s) {
   int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
-  if (do_update) {
-    net->adam_step += 1;                       // host mirror (hb_net_info); the kernels use the device copy
-    adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr, b1, b2, lr);
-    HB_CUDA(cudaGetLastError());
-  }
-  const long long n4 = net->n_eff / 4;
+  net->adam_step += 1;                       // host mirror (hb_net_info); the kernels use the device copy
+  adam_tick_kernel<<<1, 1, 0, s>>>(step_ptr, b1, b2, lr, eps, grad_scale, dyn);
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+// optix.adam / refresh over the 4-element groups [i4_begin, i4_end) of the flat parameter space
+int adam_range(hb_qnet* net, int do_update, long long i4_begin, long long i4_end, cudaStream_t s, int tf_style) {
+  int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
+  const long long n4 = i4_end - i4_begin;
+  if (n4 <= 0) return HB_OK;
   const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
   if (net->kinds == 3)
-    adam_refresh_kernel<3><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 3, net->master, net->eps,
-                                                  net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff, tf_style);
+    adam_refresh_kernel<3><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
+                                                  net->adam_m, net->adam_v, net->grad, 1.f, do_update,
+                                                  0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   else
-    adam_refresh_kernel<1><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, 1, net->master, net->eps,
-                                                  net->adam_m, net->adam_v, net->grad, grad_scale, do_update,
-                                                  lr, b1, b2, eps, step_ptr, net->w16, net->w16t, net->beff, tf_style);
+    adam_refresh_kernel<1><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
+                                                  net->adam_m, net->adam_v, net->grad, 1.f, do_update,
+                                                  0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   HB_CUDA(cudaGetLastError());
-  return HB_OK;                 // w16t is refreshed by the next hb_net_grads (launch_transposes)
+  return HB_OK;
+}
+
+int run_adam(hb_qnet* net, int do_update, float lr, float b1, float b2, float eps, float grad_scale,
+             cudaStream_t s, int tf_style = 0, const float* dyn = nullptr) {
+  if (do_update) {
+    int rc = adam_tick(net, lr, b1, b2, eps, grad_scale, dyn, s);
+    if (rc) return rc;
+  }
+  return adam_range(net, do_update, 0, net->n_eff / 4, s, tf_style);   // w16t: refreshed by the next hb_net_grads
 }
 
 // maps (layer, kind, element of the reference-layout tensor) <-> flat effective index
@@ -776,7 +818,7 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   if (!rc) rc = dev_alloc(&q->t16, (size_t)q->n_w);
   if (!rc) rc = dev_alloc(&q->beff, (size_t)q->n_b);
   if (!rc) rc = dev_alloc(&q->tbeff, (size_t)q->n_b);
-  if (!rc) rc = dev_alloc(&q->scalars, 12);      // [0] mean loss [1] max weight [2] Adam step [3..7] its corrections
+  if (!rc) rc = dev_alloc(&q->scalars, 32);      // [0] mean loss [1] max weight [2] Adam step [3..7] its corrections
   if (rc) { hb_net_destroy(q); return rc; }
   *out = q;
   return HB_OK;
@@ -798,6 +840,12 @@ int hb_net_destroy(hb_qnet* q) {
     if (q->ev_loss) cudaEventDestroy(q->ev_loss);
     if (q->ev_wt) cudaEventDestroy(q->ev_wt);
     for (int l = 0; l < kMaxLayers; ++l) cudaEventDestroy(q->ev_dz[l]);
+    for (int l = 0; l < kMaxLayers; ++l) {
+      if (q->lstream[l]) cudaStreamDestroy(q->lstream[l]);
+      if (q->ev_bias[l]) cudaEventDestroy(q->ev_bias[l]);
+      if (q->ev_layer[l]) cudaEventDestroy(q->ev_layer[l]);
+    }
+    if (q->ev_tick) cudaEventDestroy(q->ev_tick);
   }
   dev_free(q->act_x); dev_free(q->act_h[0]); dev_free(q->act_h[1]); dev_free(q->act_q);
   free_learner_ws(q);
@@ -955,7 +1003,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                           const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                           const float* d_weights, int B, float beta, float discount, int mask_terminal,
                           float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
-                          const uint32_t* d_legal_t);
+                          const uint32_t* d_legal_t, const hb_net_step_opts* opts = nullptr);
 
 int hb_net_learner_buffers(hb_qnet* q, int B, uint32_t** obs_staging, float** loss, float** mean_loss) {
   HB_REQUIRE(q && B >= 1, "hb_net_learner_buffers: bad arguments");
@@ -978,6 +1026,24 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
                         mask_terminal, d_loss_out, d_mean_loss, stream, 0, nullptr);
 }
 
+/* The learner's form of hb_net_grads (hb_net_step_opts in the header): importance weights already on the
+ * device, the step's scalars read from device memory, kernels chained with programmatic dependent launch,
+ * and optionally optix.adam applied layer by layer beside the backward pass. */
+int hb_net_grads_ex(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                    const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                    const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                    float* d_loss_out, float* d_mean_loss, const hb_net_step_opts* opts, void* stream) {
+  return net_grads_impl(q, d_obs_tm1, d_a_tm1, d_r_t, d_obs_t, d_term_t, d_prios, d_weights, B, beta, discount,
+                        mask_terminal, d_loss_out, d_mean_loss, stream, 0, nullptr, opts);
+}
+
+float* hb_net_is_weights(hb_qnet* q, int B) {
+  if (!q || B < 1) return nullptr;
+  hb::DeviceGuard g(q->device);
+  if (ensure_learner_ws(q, B)) return nullptr;
+  return q->w_is;
+}
+
 /* TF-Rainbow target (rainbow/rainbow_agent.py:183-236): the greedy next action comes from the TARGET
  * network's q = sum(p z) over the LEGAL next moves, gamma is masked by the terminal flag, importance
  * weights are given (1/sqrt(priority), normalised by the caller's max).  Same kernels otherwise. */
@@ -995,7 +1061,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                           const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                           const float* d_weights, int B, float beta, float discount, int mask_terminal,
                           float* d_loss_out, float* d_mean_loss, void* stream, int tf_variant,
-                          const uint32_t* d_legal_t) {
+                          const uint32_t* d_legal_t, const hb_net_step_opts* opts) {
   HB_REQUIRE(q && d_obs_tm1 && d_a_tm1 && d_r_t && d_obs_t && B >= 1, "hb_net_grads: bad arguments");
   HB_REQUIRE(!(d_prios && d_weights), "hb_net_grads: give prios or weights, not both");
   hb::DeviceGuard g(q->device);
@@ -1005,6 +1071,9 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   const int nl = q->n_layers, K0 = q->tab.l[0].K, Bp = q->lbp;
   const LayerGeo& LL = q->tab.l[nl - 1];
   const int ldq = q->n_atoms > 1 ? q->A : LL.N;
+  const int pdl = opts ? opts->pdl : 0;
+  const float* dyn = opts ? opts->d_dyn : nullptr;
+  const bool per_layer = opts && opts->adam_per_layer;
   // 1. packed rows side by side: [0, B) = obs_tm1, [B, 2B) = obs_t
   const size_t row_words = (size_t)q->obs_stride;
   // (a caller that gathered its rows straight into hb_net_obs_staging saves the two copies: each is a
@@ -1022,17 +1091,16 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_fork, 0));
   if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
                     q->n_atoms > 1 ? (tf_variant ? q->q_tg : nullptr) : q->tlogits, ldq, q->side,
-                    fused ? q->xb + (size_t)B * row_words : nullptr))) return rc;
+                    fused ? q->xb + (size_t)B * row_words : nullptr, pdl))) return rc;
   HB_CUDA(cudaEventRecord(q->ev_join, q->side));
   // a second side stream for the small kernels, so that the target network's GEMMs are all `side` runs
   HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fork, 0));
-  {
-    const long long tot = (long long)K0 * ((B + 7) / 8);
-    unpack_t_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, q->side2>>>(q->xb, q->obs_stride, B, q->xt, Bp);
-    HB_CUDA(cudaGetLastError());
-  }
-  // importance weights
-  if (d_prios) {
+  // importance weights (a caller that computed them with the sample -- hb_rb_sample_gather into
+  // hb_net_is_weights -- passes opts->d_w_is == that buffer: nothing to do)
+  if (opts && opts->d_w_is) {
+    if (opts->d_w_is != q->w_is)
+      HB_CUDA(cudaMemcpyAsync(q->w_is, opts->d_w_is, (size_t)B * 4, cudaMemcpyDeviceToDevice, q->side2));
+  } else if (d_prios) {
     is_weights_kernel<<<1, 256, 0, q->side2>>>(d_prios, B, beta, q->w_is);
     HB_CUDA(cudaGetLastError());
   } else if (d_weights) {
@@ -1041,47 +1109,80 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     fill_kernel<<<(B + 255) / 256, 256, 0, q->side2>>>(q->w_is, 1.f, B);
     HB_CUDA(cudaGetLastError());
   }
+  // dL/dlogits is written for the action taken only: the rest of both layouts is cleared here, beside
+  // the forward passes (the [B, N] one used to sit on the main stream between the head and the loss)
   HB_CUDA(cudaMemsetAsync(q->dzt[nl - 1], 0, (size_t)LL.N * Bp * 2, q->side2));
+  HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, q->side2));
   HB_CUDA(cudaEventRecord(q->ev_join2, q->side2));
+  {
+    const long long tot = (long long)K0 * ((B + 7) / 8);
+    unpack_t_kernel<<<(unsigned)((tot + 255) / 256), 256, 0, q->side2>>>(q->xb, q->obs_stride, B, q->xt, Bp);
+    HB_CUDA(cudaGetLastError());
+  }
   // transposed effective weights for the dZ chain of the backward pass: refreshed beside the forward
   // passes instead of behind Adam where they were 8 us of every update's critical path (ev_wt: waited for
   // before the first dZ GEMM)
   if ((rc = launch_transposes(q, q->side2))) return rc;
+  if (per_layer) {   // this step's Adam bias corrections and hyper-parameters, once, before any layer's update
+    if ((rc = adam_tick(q, opts->lr, opts->b1, opts->b2, opts->eps, opts->grad_scale, dyn, q->side2))) return rc;
+    HB_CUDA(cudaEventRecord(q->ev_tick, q->side2));
+  }
   HB_CUDA(cudaEventRecord(q->ev_wt, q->side2));
   // 2. online network on both observation sets (main stream)
   if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
-                    fused ? q->xb : nullptr))) return rc;
-  HB_CUDA(cudaMemsetAsync(q->dz[nl - 1], 0, (size_t)B * LL.N * 2, s));
+                    fused ? q->xb : nullptr, pdl))) return rc;
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join2, 0));
   // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
-  if (q->n_atoms > 1) {
-    c51_loss_kernel<<<(B + 3) / 4, 128, 0, s>>>(q->logits, tf_variant ? q->q_tg : q->q_on + (size_t)B * ldq, ldq,
-                                               tf_variant ? d_legal_t : nullptr, (q->A + 31) / 32, q->tlogits,
-                                               LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, q->w_is,
-                                               B, q->A, q->n_atoms, q->vmax, discount, q->dz[nl - 1],
-                                               q->dzt[nl - 1], Bp, q->loss_b);
-  } else {
-    dqn_loss_kernel<<<(B + 127) / 128, 128, 0, s>>>(q->q_on, ldq, q->tlogits, d_a_tm1, d_r_t, d_term_t,
-                                                   q->w_is, B, q->A, discount, q->dz[nl - 1], LL.N,
-                                                   q->dzt[nl - 1], Bp, q->loss_b);
+  {
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+    cudaLaunchConfig_t cfg = {};
+    cfg.stream = s;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    if (q->n_atoms > 1) {
+      cfg.gridDim = dim3((B + 3) / 4);
+      cfg.blockDim = dim3(128);
+      const float* q_sel = tf_variant ? q->q_tg : q->q_on + (size_t)B * ldq;
+      const uint32_t* legal_t = tf_variant ? d_legal_t : nullptr;
+      const float* logits = q->logits;
+      const float* tlogits = q->tlogits;
+      const float* w_is = q->w_is;
+      HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel, logits, q_sel, ldq, legal_t, (q->A + 31) / 32, tlogits,
+                                 LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A, q->n_atoms,
+                                 q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp, q->loss_b));
+    } else {
+      cfg.gridDim = dim3((B + 127) / 128);
+      cfg.blockDim = dim3(128);
+      const float* q_on = q->q_on;
+      const float* q_t = q->tlogits;
+      const float* w_is = q->w_is;
+      HB_CUDA(cudaLaunchKernelEx(&cfg, dqn_loss_kernel, q_on, ldq, q_t, d_a_tm1, d_r_t, d_term_t, w_is, B, q->A,
+                                 discount, dyn, q->dz[nl - 1], LL.N, q->dzt[nl - 1], Bp, q->loss_b));
+    }
   }
-  HB_CUDA(cudaGetLastError());
-  mean_loss_kernel<<<1, 256, 0, s>>>(q->loss_b, q->w_is, B, q->n_atoms > 1 ? 0 : 1, q->scalars);
+  HB_CUDA(cudaEventRecord(q->ev_loss, s));   // the per-sample losses are complete (hb_net_loss_event)
+  // mean(loss * w) is only reported: beside the backward pass, not in front of it
+  HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_loss, 0));
+  mean_loss_kernel<<<1, 256, 0, q->side2>>>(q->loss_b, q->w_is, B, q->n_atoms > 1 ? 0 : 1, q->scalars);
   HB_CUDA(cudaGetLastError());
   if (d_loss_out && d_loss_out != q->loss_b)
-    HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, s));
+    HB_CUDA(cudaMemcpyAsync(d_loss_out, q->loss_b, (size_t)B * 4, cudaMemcpyDeviceToDevice, q->side2));
   if (d_mean_loss && d_mean_loss != q->scalars)
-    HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, s));
-  HB_CUDA(cudaEventRecord(q->ev_loss, s));   // the per-sample losses are complete (hb_net_loss_event)
-  // 5. backward: the dZ chain (critical path) on the main stream, the weight / bias gradients of
-  //    every layer on the side stream as soon as that layer's dZ exists
+    HB_CUDA(cudaMemcpyAsync(d_mean_loss, q->scalars, 4, cudaMemcpyDeviceToDevice, q->side2));
+  // 5. backward: the dZ chain (critical path) on the main stream with programmatic dependent launch;
+  //    every layer's weight gradient on that layer's own stream as soon as its dZ exists, the bias
+  //    gradients on side2, and (adam_per_layer) that layer's optix.adam right behind its gradient, so
+  //    that only the first layer's update is left when the chain ends
   const float invB = 1.0f / (float)B;
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_wt, 0));
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];
+    cudaStream_t ls = q->lstream[l];
     HB_CUDA(cudaEventRecord(q->ev_dz[l], s));              // dz[l] / dzt[l] are complete here
-    HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_dz[l], 0));
+    HB_CUDA(cudaStreamWaitEvent(ls, q->ev_dz[l], 0));
     // dW_l [N, K] = dZ_l^T . X_l  : A = dzt[l] [N, B], B = (layer input)^T [K, B]
     const __half* in_t = l == 0 ? q->xt : q->ht[l - 1];
     const int ld_in_t = l == 0 ? Bp : 2 * Bp;
@@ -1089,11 +1190,19 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.alpha = invB;
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
-    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, q->side))) return rc;
+    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
     HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_dz[l], 0));
     bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, q->side2>>>(q->dzt[l], Bp, L.N, B, invB,
                                                         q->grad + L.eoff + (long long)L.N * L.K);
     HB_CUDA(cudaGetLastError());
+    if (per_layer) {
+      HB_CUDA(cudaEventRecord(q->ev_bias[l], q->side2));
+      HB_CUDA(cudaStreamWaitEvent(ls, q->ev_bias[l], 0));
+      HB_CUDA(cudaStreamWaitEvent(ls, q->ev_tick, 0));
+      const long long e0 = L.eoff, e1 = l + 1 < nl ? q->tab.l[l + 1].eoff : q->n_eff;
+      if ((rc = adam_range(q, 1, e0 / 4, e1 / 4, ls, 0))) return rc;
+    }
+    HB_CUDA(cudaEventRecord(q->ev_layer[l], ls));
     if (l > 0) {
       // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
       tc::EpiParams eb{};
@@ -1104,11 +1213,11 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       eb.ld_out = L.K;
       eb.out16_t = q->dzt[l - 1];
       eb.ld_out_t = Bp;
+      eb.pdl = pdl;
       if ((rc = tc::gemm<tc::EPI_F16>(q->dz[l], L.N, q->w16t + L.woff, L.N, B, L.K, L.N, eb, s))) return rc;
     }
   }
-  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
-  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  for (int l = 0; l < nl; ++l) HB_CUDA(cudaStreamWaitEvent(s, q->ev_layer[l], 0));
   HB_CUDA(cudaEventRecord(q->ev_join2, q->side2));
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join2, 0));
   return HB_OK;
@@ -1126,6 +1235,12 @@ int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_
   HB_REQUIRE(q, "hb_net_adam: NULL net");
   hb::DeviceGuard g(q->device);
   return run_adam(q, 1, lr, b1, b2, eps, grad_scale, (cudaStream_t)stream);
+}
+
+int hb_net_adam_dyn(hb_qnet* q, const float* d_dyn, void* stream) {
+  HB_REQUIRE(q && d_dyn, "hb_net_adam_dyn: bad arguments");
+  hb::DeviceGuard g(q->device);
+  return run_adam(q, 1, 0.f, 0.f, 0.f, 0.f, 1.f, (cudaStream_t)stream, 0, d_dyn);
 }
 
 /* Q-values / logits of n packed observations (tests, evaluation): d_q [n, num_actions] unmasked;

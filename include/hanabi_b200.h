@@ -348,6 +348,32 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,
                  float* d_loss_out, float* d_mean_loss, void* stream);
+/* The learner's form of hb_net_grads.  What a captured, replayed update needs on top of it:
+ *   d_w_is         importance weights already on the device (hb_rb_sample_gather computed them with the
+ *                  sample; hb_net_is_weights(q, B) is the network's own buffer: pass it to skip a copy)
+ *   d_dyn          the step's scalars in DEVICE memory -- [0] beta [1] discount [2] lr [3] b1 [4] b2
+ *                  [5] eps [6] grad_scale -- read by the kernels instead of the by-value arguments, which
+ *                  a replayed CUDA graph freezes (beta_is / learning_rate are schedules, params.py:5-20)
+ *   pdl            chain the kernels of the critical path with programmatic dependent launch
+ *   adam_per_layer apply optix.adam (rlax_rainbow.py:215-216) to every layer as soon as its gradient is
+ *                  complete, beside the rest of the backward pass (single-process learner: no all-reduce
+ *                  between gradient and update); lr, b1, b2, eps, grad_scale as in hb_net_adam */
+typedef struct hb_net_step_opts {
+  const float* d_w_is;
+  const float* d_dyn;
+  int pdl;
+  int adam_per_layer;
+  float lr, b1, b2, eps, grad_scale;
+} hb_net_step_opts;
+int hb_net_grads_ex(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
+                    const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
+                    const float* d_weights, int B, float beta, float discount, int mask_terminal,
+                    float* d_loss_out, float* d_mean_loss, const hb_net_step_opts* opts, void* stream);
+/* The network's importance-weight buffer for a batch of B (valid until a call with a larger B). */
+float* hb_net_is_weights(hb_qnet* q, int B);
+/* hb_net_adam with the hyper-parameters read from d_dyn ([2] lr [3] b1 [4] b2 [5] eps [6] grad_scale;
+ * device or pinned host memory) at execution time. */
+int hb_net_adam_dyn(hb_qnet* q, const float* d_dyn, void* stream);
 /* cudaEvent_t recorded on the caller's stream by the last hb_net_grads / hb_net_grads_rainbow call at the
  * point where the per-sample losses (d_loss_out) are complete: work that needs nothing but the losses --
  * PriorityBuffer.update_priorities, hanabi_agents/rlax_dqn/rlax_rainbow.py:331-334 -- can wait on it and

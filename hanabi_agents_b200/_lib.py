@@ -128,6 +128,7 @@ SIGNATURES = {
     "hb_learner_indices": (vp, [vp]),
     "hb_learner_grads": (i32, [vp, vp, vp, f32, f32, i32, vp]),
     "hb_learner_apply": (i32, [vp, f32, f32, f32, f32, f32, vp]),
+    "hb_learner_step": (i32, [vp, vp, vp, f32, f32, i32, f32, f32, f32, f32, vp]),
     # NVLink all-reduce of the gradient bucket
     "hb_comm_create": (i32, [i32, i32, i32, vp, i64, C.POINTER(vp)]),
     "hb_comm_destroy": (i32, [vp]),

@@ -174,13 +174,17 @@ class DQNAgent:
             # the same stream without building a capacity-sized array every step
             idx = np.ascontiguousarray(np.random.randint(0, exp.size, size=B), dtype=np.int64)
             kp, ip = None, idx.ctypes.data
-        _lib.check(L.hb_learner_grads(self._learner, kp, ip, float(self.params.beta_is(self.train_step)),
-                                      float(self.params.discount), 0, stream))
         world, _ = self._world()
-        if world > 1:
+        beta = float(self.params.beta_is(self.train_step))
+        lr = self.params.learning_rate
+        lr = float(lr(self.train_step)) if callable(lr) else float(lr)
+        if world == 1:      # one call, one graph: Adam runs layer by layer beside the backward pass
+            _lib.check(L.hb_learner_step(self._learner, kp, ip, beta, float(self.params.discount), 0,
+                                         lr, 0.9, 0.999, self.adam_eps, stream))
+        else:
+            _lib.check(L.hb_learner_grads(self._learner, kp, ip, beta, float(self.params.discount), 0, stream))
             self._allreduce_grads()
-        _lib.check(L.hb_learner_apply(self._learner, float(self.params.learning_rate), 0.9, 0.999,
-                                      self.adam_eps, 1.0 / world, stream))
+            _lib.check(L.hb_learner_apply(self._learner, lr, 0.9, 0.999, self.adam_eps, 1.0 / world, stream))
         if self.train_step % self.params.target_update_period == 0:   # :336-337
             self.network.sync_target()
         self.train_step += 1

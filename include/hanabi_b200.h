@@ -400,8 +400,11 @@ int hb_net_adam_tf(hb_qnet* q, float lr, float b1, float b2, float eps, float gr
 int hb_net_adam(hb_qnet* q, float lr, float b1, float b2, float eps, float grad_scale, void* stream);
 
 /* ------------------------------------------------------------------------ */
-/* One learner step = DQNAgent.update (rlax_rainbow.py:310-339) in two C calls   */
-/* around the caller's gradient all-reduce; each phase is a replayed CUDA graph. */
+/* One learner step = DQNAgent.update (rlax_rainbow.py:310-339): one C call for   */
+/* a single process (hb_learner_step), or two around the caller's gradient       */
+/* all-reduce (hb_learner_grads / hb_learner_apply); replayed CUDA graphs.  The   */
+/* scalars that are schedules in the reference (beta_is, learning_rate) are read  */
+/* from staging memory at run time: changing them does not capture a new graph.   */
 /* ------------------------------------------------------------------------ */
 typedef struct hb_learner hb_learner;
 int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_learner** out);
@@ -420,6 +423,10 @@ int64_t* hb_learner_indices(hb_learner* L);
 int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                      int mask_terminal, void* stream);
 /* Phase B: optix.adam on grad_scale * bucket. */
+/* Both phases in ONE call and one graph, for a single process (no all-reduce between gradient and
+ * update): optix.adam is applied layer by layer beside the backward pass. */
+int hb_learner_step(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
+                    int mask_terminal, float lr, float b1, float b2, float eps, void* stream);
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
                      void* stream);
 

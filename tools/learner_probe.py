@@ -59,7 +59,15 @@ def phase_a():
     _lib.check(L.hb_learner_grads(agent._learner, keys.ctypes.data, None, 0.5, 0.99, 0, stream))
 def phase_b():
     _lib.check(L.hb_learner_apply(agent._learner, 1e-4, 0.9, 0.999, agent.adam_eps, 1.0, stream))
-for name, fn in (("phase A (sample..grads, priorities)", phase_a), ("phase B (adam)", phase_b)):
+def both():
+    phase_a()
+    phase_b()
+def fused():
+    _lib.check(L.hb_learner_step(agent._learner, keys.ctypes.data, None, 0.5, 0.99, 0, 1e-4, 0.9, 0.999,
+                                 agent.adam_eps, stream))
+for name, fn in (("phase A (sample..grads, priorities)", phase_a), ("phase B (adam)", phase_b),
+                 ("phase A + phase B (data-parallel path, no all-reduce)", both),
+                 ("hb_learner_step (one graph, per-layer Adam)", fused)):
     for _ in range(5):
         fn()
     torch.cuda.synchronize()

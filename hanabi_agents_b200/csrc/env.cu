@@ -511,6 +511,7 @@ int fill_ruleset(RuleSet& rs, const int32_t* ids, const double* farg, const int3
     HB_REQUIRE(ids[k] >= 0 && ids[k] < R_NUM_RULES, "unknown rule id %d", ids[k]);
     rs.id[k] = ids[k];
     rs.used |= 1u << ids[k];
+    if (ids[k] == R_OSAWA_DISCARD && iarg && iarg[k] != 0) rs.used |= kOsawaIntended;   // applies to the whole list
     rs.farg[k] = farg ? farg[k] : 0.0;
     rs.iarg[k] = iarg ? iarg[k] : 0;
   }

@@ -28,6 +28,9 @@ enum RuleId {
 };
 
 constexpr int kMaxRules = 16;
+// bit of RuleSet::used (rule ids end at 16): osawa_discard with its iarg != 0, i.e. the INTENDED reading of
+// ruleset.py:229-230 (colour test only on colour-hinted cards) instead of the fireworks[-1] quirk
+constexpr unsigned int kOsawaIntended = 1u << 31;
 constexpr int kThrSlots = 4;      // rules with a probability threshold that get a comparison table
 constexpr int kThrRows = 52;      // denominators 0..51 (a deck holds 50 cards)
 struct RuleSet {        // entry [n] is the legal_random fallback, filled by the host
@@ -244,7 +247,8 @@ __device__ __forceinline__ void rule_cores(const Game<SH>& g, const unsigned int
     // Per card: colour hinted -> its stack is finished; NOT hinted -> fireworks[-1] is finished (quirk
     // :229-230); both hinted -> rank below its stack or at / beyond max_fireworks; rank hinted -> rank
     // below every stack.  The four hint states pick one of four grids the card's one-hot is tested against.
-    const uint32_t all = ((g.fw >> (5 * (C - 1) + 4)) & 1u) ? SH::kGridAll : 0u;
+    // (kOsawaIntended in `used`: the intended reading of :229, un-hinted colours are skipped -> `all` = 0)
+    const uint32_t all = (!(used & kOsawaIntended) && ((g.fw >> (5 * (C - 1) + 4)) & 1u)) ? SH::kGridAll : 0u;
     const uint32_t g1 = done, g2 = ltmin | all, g3 = done | ltmin | ((g.fw | ~useful) & SH::kGridAll);
     int first = H, second = H;
 #pragma unroll

@@ -29,12 +29,17 @@ def truncated_normal(rng, shape, stddev):
 def init_params(obs_len, hidden, num_actions, n_atoms, noisy=True, seed=1234):
     """Initial parameters and the trace-time noise constants, reference layout.
 
-    The reference draws them from jax's threefry stream (rlax_rainbow.py:250-251,
-    noisy_mlp.py:110-140), which cannot be reproduced without jax: the distributions are the
-    reference's (truncated normal with stddev 1/sqrt(fan_in) for w, w_mu, w_sigma; zero biases;
-    standard normal noise), the stream is numpy's default_rng(seed)."""
+    The NOISE is the reference's own: NoisyMLP always seeds jax.random.PRNGKey(1234), whatever
+    params.seed is, and draws the constants while it is traced (noisy_mlp.py:127,140,79,87); jax_prng
+    restates that threefry stream, so a pickle written by the reference's save_weights evaluates to
+    the reference's network after restore_weights.  The initial WEIGHTS come from haiku's initialisers
+    on another jax stream (rlax_rainbow.py:250-251): their distributions are the reference's
+    (truncated normal with stddev 1/sqrt(fan_in) for w, w_mu, w_sigma; zero biases), their stream is
+    numpy's default_rng(seed)."""
+    from .jax_prng import noisy_mlp_noise
     rng = np.random.default_rng(seed)
     sizes = [obs_len] + list(hidden) + [num_actions * n_atoms]
+    noise = noisy_mlp_noise(sizes) if noisy else None
     layers = []
     for i in range(len(sizes) - 1):
         fi, fo = sizes[i], sizes[i + 1]
@@ -45,8 +50,7 @@ def init_params(obs_len, hidden, num_actions, n_atoms, noisy=True, seed=1234):
             p["w_sigma"] = truncated_normal(rng, (fi, fo), sd)
             p["b_mu"] = np.zeros(fo, np.float32)
             p["b_sigma"] = np.zeros(fo, np.float32)
-            p["eps_w"] = rng.standard_normal((fi, fo)).astype(np.float32)
-            p["eps_b"] = rng.standard_normal(fo).astype(np.float32)
+            p["eps_w"], p["eps_b"] = noise[i]
         layers.append(p)
     return layers
 

@@ -37,6 +37,17 @@ class Ruleset:
     tell_most_information = Rule(13, "tell_most_information")       # :539 (always None, :562)
 
     @staticmethod
+    def osawa_discard_factory(unknown_color="quirk"):
+        """osawa_discard with the reading of ruleset.py:229-230 made explicit.  "quirk" (what
+        `Ruleset.osawa_discard` is): `card.color is not None` holds for the kUnknownColor enum too, so an
+        un-hinted card tests `fireworks[-1]`, the last colour's stack.  "intended": un-hinted colours are
+        skipped.  The binding that decides which one the reference really executes is not available
+        (SURVEY RB-3); a rule list uses one reading for all its osawa_discard entries."""
+        if unknown_color not in ("quirk", "intended"):
+            raise ValueError("unknown_color must be 'quirk' or 'intended'")
+        return Rule(1, "osawa_discard", iarg=int(unknown_color == "intended"))
+
+    @staticmethod
     def tell_dispensable_factory(min_information_tokens=8):         # :454
         return Rule(7, "tell_dispensable", iarg=min_information_tokens)
 

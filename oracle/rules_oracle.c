@@ -182,8 +182,14 @@ static int run_rule(const view* v, int rule, double farg, int iarg) {
       const int minfw = min_fireworks(v);
       for (int i = 0; i < s->hand_n[me]; ++i) {
         const int ch = s->color_hint[me][i], rh = s->rank_hint[me][i];
-        const int cidx = ch >= 0 ? ch : C - 1; /* fireworks[-1] quirk, :229-230 */
-        if (s->fireworks[cidx] == 5) return mk(v, HO_DISCARD, i, -1, -1, -1);
+        /* :229-230 `if card.color is not None: if fireworks[card.color] == 5`.  iarg == 0 (default): the
+         * quirk reading -- an un-hinted colour is kUnknownColor = -1, never None, so the test runs on
+         * fireworks[-1], the LAST colour's stack.  iarg != 0: the intended reading, un-hinted colours are
+         * skipped (what the comment two lines above it in the reference, `color = card['color']`, did). */
+        if (ch >= 0 || iarg == 0) {
+          const int cidx = ch >= 0 ? ch : C - 1;
+          if (s->fireworks[cidx] == 5) return mk(v, HO_DISCARD, i, -1, -1, -1);
+        }
         if (ch >= 0 && rh >= 0)
           if (rh < s->fireworks[ch] || rh >= mf[ch]) return mk(v, HO_DISCARD, i, -1, -1, -1);
         if (rh >= 0)

@@ -109,7 +109,11 @@ def test_agent_numpy_compat_and_weights_roundtrip(tmp_path):
     other = DQNAgent(env.observation_spec(), env.action_spec(), params._replace(seed=99))
     assert not torch.equal(other.network.forward(env.obs_packed), agent.network.forward(env.obs_packed))
     other.restore_weights(str(on), str(tg))
-    # the trace-time noise constants are not part of the reference's pickles: copy them explicitly
+    # the trace-time noise constants are not part of the reference's pickles; every network regenerates the
+    # reference's own (jax PRNGKey(1234) threefry stream, rlax_dqn/jax_prng.py), whatever params.seed is:
+    # the restored network evaluates to the saved one without anything else being copied
+    assert torch.equal(other.network.forward(env.obs_packed), agent.network.forward(env.obs_packed))
+    # (setting the noise explicitly stays possible)
     noise = [{k: v for k, v in l.items() if k.startswith("eps")} for l in agent.network.get_params(with_noise=True)]
     other.network.set_params(noise, sync_target=True)
     assert torch.equal(other.network.forward(env.obs_packed), agent.network.forward(env.obs_packed))

@@ -380,3 +380,44 @@ def test_full_size_properties_and_oracle(players, n, T):
     assert np.all(d[:, 3] + hand_n + disc + d[:, 8:8 + C].sum(1) == 50)
     assert np.all((d[:, 1] >= 0) & (d[:, 1] <= 8)) and np.all((d[:, 2] >= 0) & (d[:, 2] <= 3))
     assert env.illegal_count() == 0
+
+
+@pytest.mark.parametrize("name,players", [("Hanabi-Full", 2), ("Hanabi-Full", 5)])
+def test_osawa_discard_intended_flag(name, players):
+    """Ruleset.osawa_discard_factory('intended') (SURVEY RB-3: the reading of ruleset.py:229-230 as a
+    documented switch) against the oracle's iarg = 1, stepwise and fused; and it really differs from the
+    quirk reading on the same games (a finished LAST colour makes the quirk discard un-hinted cards)."""
+    from hanabi_agents_b200.rule_based import RulebasedAgent, Ruleset
+    from oracle import hanabi as oh
+    with pytest.raises(ValueError):
+        Ruleset.osawa_discard_factory("other")
+    assert Ruleset.osawa_discard_factory("quirk").iarg == Ruleset.osawa_discard.iarg == 0
+    rules = [Ruleset.play_safe_card, Ruleset.osawa_discard_factory("intended"), Ruleset.tell_playable_card_outer,
+             Ruleset.tell_unknown, Ruleset.discard_oldest_first]
+    orules = [(oh.R_PLAY_SAFE_CARD, 0, 0), (oh.R_OSAWA_DISCARD, 0, 1), (oh.R_TELL_PLAYABLE_CARD_OUTER, 0, 0),
+              (oh.R_TELL_UNKNOWN, 0, 0), (oh.R_DISCARD_OLDEST_FIRST, 0, 0)]
+    n = 512
+    env, ora = _pair(name, players, n, 4242)
+    agent = RulebasedAgent(rules, seed=5)
+    env.reset(); ora.reset()
+    differs = 0
+    for step in range(260):
+        a = agent.explore(env.observations())
+        oa, _ = ora.rules_act(orules, 5, step)
+        np.testing.assert_array_equal(a.cpu().numpy(), oa)
+        quirk, _ = ora.rules_act([(r, f, 0) for r, f, _ in orules], 5, step)
+        differs += int((quirk != oa).sum())
+        obs, legal, rew, st = env.step(a)
+        ora.step(oa)
+        _check(env, ora, obs, legal, rew, st)
+    assert env.illegal_count() == 0
+    assert differs > 0, "the two readings never disagreed: the flag is not exercised"
+    env2, ora2 = _pair(name, players, n, 4242)
+    agent2 = RulebasedAgent(rules, seed=5)
+    env2.reset(); ora2.reset()
+    T = 100
+    _, _, _, _, act = env2.selfplay(agent2, T, obs=None, legal=None, reward=None, step_type=None, action="alloc")
+    for t in range(T):
+        oa, _ = ora2.rules_act(orules, 5, t)
+        np.testing.assert_array_equal(act[t].cpu().numpy(), oa, err_msg="fused step %d" % t)
+        ora2.step(oa)

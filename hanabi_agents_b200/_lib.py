@@ -61,6 +61,8 @@ SIGNATURES = {
     "hb_env_reset": (i32, [vp, vp, vp, vp, vp]),
     "hb_env_step": (i32, [vp, vp, vp, vp, vp, vp, vp]),
     "hb_env_observe": (i32, [vp, i32, vp, vp, vp]),
+    "hb_env_obs_len_as": (i64, [vp, i32]),
+    "hb_env_observe_as": (i32, [vp, i32, i32, vp, i32, vp]),
     "hb_env_illegal_count": (i32, [vp, C.POINTER(i64), vp]),
     "hb_env_dump": (i32, [vp, vp, vp]),
     "hb_env_unpack_obs": (i32, [vp, vp, vp, i64, vp]),

@@ -191,6 +191,58 @@ env_observe_kernel(Rt rt, const uint32_t* __restrict__ state, int offset,
   }
 }
 
+// The other HLE observation types from the same state (HanabiGame::AgentObservationType; only
+// kCardKnowledge is used by the reference's environments, run_experiment.py:114-128):
+//   0 kMinimal  the canonical row without its last section, the card knowledge;
+//   2 kSeer     the observer's own cards are encoded too, as the FIRST block of the hands section
+//               (EncodeHands with show_own_cards): the canonical row moves up by H * BPC bits and the
+//               one-hots of seat 0's slots fill the gap.
+// Rows are assembled in registers; `stride` (words) comes from the host (16-byte multiples).
+template <class SH>
+__global__ void __launch_bounds__(kThreads)
+env_observe_as_kernel(Rt rt, const uint32_t* __restrict__ state, int offset, int obs_type,
+                      uint32_t* __restrict__ obs, int stride) {
+  const long long game = game_index();
+  if (game >= rt.n_games) return;
+  Game<SH> g;
+  load_game(g, state, game);
+  rotate_seats(g, offset);
+  uint32_t row[SH::kObsStride];
+  encode_row(g, SH::P - 1 - offset, row);
+  uint32_t* dst = obs + game * stride;
+  if (obs_type == 2) {
+    constexpr int kShift = SH::H * SH::BPC;                     // bits the canonical row moves up by
+    constexpr int kWords = (SH::kObsLen + kShift + 31) / 32;
+    constexpr int ws = kShift / 32, bs = kShift % 32;
+    uint32_t out[kWords];
+#pragma unroll
+    for (int j = 0; j < kWords; ++j) {
+      uint32_t v = 0;
+      if (j - ws >= 0 && j - ws < SH::kObsStride) v = row[j - ws] << bs;
+      if (bs != 0 && j - ws - 1 >= 0 && j - ws - 1 < SH::kObsStride) v |= row[j - ws - 1] >> (32 - bs);
+      out[j] = v;
+    }
+#pragma unroll
+    for (int i = 0; i < SH::H; ++i) {                           // own cards: slot i at bit i * BPC
+      const unsigned long long oh = (unsigned long long)(g.oh[0][i] & SH::kGridAll) << ((i * SH::BPC) % 32);
+      constexpr int dummy = 0; (void)dummy;
+      const int w0 = (i * SH::BPC) / 32;
+      out[w0] |= (uint32_t)oh;
+      if (w0 + 1 < kWords) out[w0 + 1] |= (uint32_t)(oh >> 32);
+    }
+    for (int j = 0; j < stride; ++j) dst[j] = j < kWords ? out[j] : 0u;
+  } else {
+    const int bits = obs_type == 0 ? SH::kOffKnow : SH::kObsLen;
+    for (int j = 0; j < stride; ++j) {
+      uint32_t v = j < SH::kObsStride ? row[j] : 0u;
+      const int lo = 32 * j;
+      if (lo >= bits) v = 0u;
+      else if (lo + 32 > bits) v &= (1u << (bits - lo)) - 1u;
+      dst[j] = v;
+    }
+  }
+}
+
 // RulebasedAgent.explore over the whole batch (rule_based.py:27-31)
 template <class SH, bool EXT>
 __global__ void __launch_bounds__(kThreads)
@@ -788,6 +840,29 @@ int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, vo
   hb::DeviceGuard g(e->device);
   HB_DISPATCH(e, (env_observe_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
                      e->rt, e->state, offset, d_obs, d_legal)));
+  HB_CUDA(cudaGetLastError());
+  return HB_OK;
+}
+
+int64_t hb_env_obs_len_as(const hb_env* e, int obs_type) {
+  if (!e || obs_type < 0 || obs_type > 2) return -1;
+  const int bpc = e->C * e->R;
+  if (obs_type == 0) return e->obs_len - e->P * e->H * (bpc + e->C + e->R);
+  if (obs_type == 2) return e->obs_len + e->H * bpc;
+  return e->obs_len;
+}
+
+int hb_env_observe_as(hb_env* e, int obs_type, int offset, uint32_t* d_obs, int stride_words, void* stream) {
+  if (e) e->spq_chain = false;
+  HB_REQUIRE(e && d_obs && offset >= 0 && offset < e->P && obs_type >= 0 && obs_type <= 2,
+             "hb_env_observe_as: bad arguments (obs_type 0 minimal, 1 card knowledge, 2 seer)");
+  HB_REQUIRE((int64_t)stride_words * 32 >= hb_env_obs_len_as(e, obs_type),
+             "hb_env_observe_as: rows of %d words are shorter than %lld bits", stride_words,
+             (long long)hb_env_obs_len_as(e, obs_type));
+  if (!e->is_reset) { hb::set_error("hb_env_observe_as: reset the environment first"); return HB_ERR_STATE; }
+  hb::DeviceGuard g(e->device);
+  HB_DISPATCH(e, (env_observe_as_kernel<SH><<<grid_for(e), kThreads, 0, (cudaStream_t)stream>>>(
+                     e->rt, e->state, offset, obs_type, d_obs, stride_words)));
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }

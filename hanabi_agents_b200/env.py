@@ -222,6 +222,26 @@ class HanabiParallelEnv:
                                              self._s()))
         return obs, legal
 
+    OBSERVATION_TYPES = {"minimal": 0, "card_knowledge": 1, "seer": 2}
+
+    def observe_as(self, observation_type, offset=0, unpack=False):
+        """The observation of the player `offset` seats after the mover in another of HLE's observation
+        types ("minimal": no card-knowledge section; "seer": own cards visible; "card_knowledge": what
+        `observe` / `step` give).  Returns (rows, length in bits): bit-packed int32 [N, stride] CUDA rows, or
+        int8 0/1 [N, length] with unpack=True."""
+        torch = self.torch
+        t = self.OBSERVATION_TYPES[observation_type] if isinstance(observation_type, str) else int(observation_type)
+        L = _lib.lib()
+        bits = int(L.hb_env_obs_len_as(self._h, t))
+        stride = ((bits + 31) // 32 + 3) // 4 * 4
+        rows = torch.empty((self.n, stride), dtype=torch.int32, device=self.device)
+        _lib.check(L.hb_env_observe_as(self._h, t, int(offset), rows.data_ptr(), stride, self._s()))
+        if not unpack:
+            return rows, bits
+        out = torch.empty((self.n, bits), dtype=torch.int8, device=self.device)
+        _lib.check(L.hb_unpack_bits(rows.data_ptr(), stride, bits, out.data_ptr(), self.n, self._s()))
+        return out, bits
+
     def unpack_obs(self, packed=None):
         torch = self.torch
         packed = self.obs_packed if packed is None else packed

@@ -153,6 +153,13 @@ int hb_env_step(hb_env* e, const int32_t* d_action, uint32_t* d_obs, uint32_t* d
                 float* d_reward, uint8_t* d_step_type, void* stream);
 /* HanabiObservation of player (current + offset) mod players, without stepping. */
 int hb_env_observe(hb_env* e, int offset, uint32_t* d_obs, uint32_t* d_legal, void* stream);
+/* The observation of player (current + offset) in another of HLE's observation types
+ * (HanabiGame::AgentObservationType, chosen by `observation_type` in HLE's game config; the reference's
+ * environments all use 1, run_experiment.py:114-128): 0 kMinimal = the canonical vector without the card
+ * knowledge section, 1 kCardKnowledge = hb_env_observe, 2 kSeer = own cards encoded as the first block of
+ * the hands section.  Rows are bit-packed, stride_words 32-bit words each (>= hb_env_obs_len_as bits). */
+int64_t hb_env_obs_len_as(const hb_env* e, int obs_type);
+int hb_env_observe_as(hb_env* e, int obs_type, int offset, uint32_t* d_obs, int stride_words, void* stream);
 /* Number of illegal actions seen so far (HLE aborts on them; here the game is left as is). */
 int hb_env_illegal_count(hb_env* e, int64_t* out, void* stream);
 /* Canonical int32 state dump [n_games, dump_len] (tests compare it with the oracle's). */

@@ -58,6 +58,9 @@ def _lib():
         L.ho_env_step.restype = i64
         L.ho_env_step.argtypes = [vp, vp, vp, vp, vp, vp]
         L.ho_env_observe.argtypes = [vp, i32, vp, vp]
+        L.ho_env_observe_typed.argtypes = [vp, i32, i32, vp]
+        L.ho_obs_len_typed.restype = i32
+        L.ho_obs_len_typed.argtypes = [vp, i32]
         L.ho_state_dump_len.restype = i32
         L.ho_state_dump_len.argtypes = [vp]
         L.ho_env_dump.argtypes = [vp, vp]
@@ -122,6 +125,13 @@ class HanabiOracleEnv:
         legal = np.zeros_like(self.legal)
         self.L.ho_env_observe(self.h, offset, obs.ctypes.data, legal.ctypes.data)
         return obs, legal
+
+    def observe_typed(self, obs_type, offset=0):
+        """HLE observation types: 0 kMinimal, 1 kCardKnowledge, 2 kSeer -> uint8 [N, length of that type]."""
+        n = int(self.L.ho_obs_len_typed(self.L.ho_env_game(self.h), obs_type))
+        obs = np.zeros((self.n, n), np.uint8)
+        self.L.ho_env_observe_typed(self.h, offset, obs_type, obs.ctypes.data)
+        return obs
 
     def dump(self):
         n = self.L.ho_state_dump_len(self.L.ho_env_game(self.h))

@@ -373,6 +373,42 @@ void ho_encode(const ho_game* g, const ho_state* s, int observer, uint8_t* out) 
   }
 }
 
+/* The other two HLE observation types (HanabiGame::AgentObservationType: kMinimal = 0, kCardKnowledge = 1,
+ * kSeer = 2; hanabi_game.h / canonical_encoders.cc, [RECALL]: HLE is not on the box).
+ *   kMinimal        the card-knowledge section is not encoded (Encode skips EncodeCardKnowledge and
+ *                   Shape() leaves its length out);
+ *   kCardKnowledge  ho_encode (what every environment of the reference uses, run_experiment.py:114-128);
+ *   kSeer           the observer also sees its own cards: EncodeHands runs over every player, offset 0
+ *                   first (show_own_cards), so the hands section grows by hand_size * bits_per_card.
+ * The hands section is written out here; sections 2-5 are ho_encode's, moved to their new offset. */
+int ho_obs_len_typed(const ho_game* g, int obs_type) {
+  if (obs_type == 0) return g->obs_len - g->knowledge_len;
+  if (obs_type == 2) return g->obs_len + g->hand_size * g->bits_per_card;
+  return g->obs_len;
+}
+
+void ho_encode_typed(const ho_game* g, const ho_state* s, int observer, int obs_type, uint8_t* out) {
+  const int P = g->players, H = g->hand_size, bpc = g->bits_per_card;
+  const int len = ho_obs_len_typed(g, obs_type);
+  uint8_t full[HO_MAX_OBS];
+  ho_encode(g, s, observer, full);            /* sections 2..5 are shared; only their offset moves */
+  memset(out, 0, (size_t)len);
+  int off = 0;
+  /* 1. hands: offset 0 (own cards) first when the observer is a seer */
+  for (int k = obs_type == 2 ? 0 : 1; k < P; ++k) {
+    const int pl = (observer + k) % P;
+    for (int i = 0; i < s->hand_n[pl]; ++i) out[off + i * bpc + s->hand_card[pl][i]] = 1;
+    off += H * bpc;
+  }
+  for (int k = 0; k < P; ++k)
+    if (s->hand_n[(observer + k) % P] < H) out[off + k] = 1;
+  off += P;
+  /* 2-4. board, discards, last action; 5. card knowledge unless minimal */
+  const int rest_from = g->hands_len;
+  const int rest_len = (obs_type == 0 ? g->obs_len - g->knowledge_len : g->obs_len) - rest_from;
+  memcpy(out + off, full + rest_from, (size_t)rest_len);
+}
+
 /* --------------------------------------------------------- batched env ---- */
 struct ho_env {
   ho_game game;
@@ -491,6 +527,15 @@ void ho_env_observe(ho_env* e, int offset, uint8_t* obs, uint8_t* legal) {
     const int pl = (s->cur_player + offset) % e->game.players;
     if (obs) ho_encode(&e->game, s, pl, obs + g * e->game.obs_len);
     if (legal) ho_legal_mask(&e->game, s, pl, legal + g * e->game.num_moves);
+  }
+}
+
+void ho_env_observe_typed(ho_env* e, int offset, int obs_type, uint8_t* obs) {
+  const int len = ho_obs_len_typed(&e->game, obs_type);
+#pragma omp parallel for num_threads(e->threads) schedule(static)
+  for (int64_t g = 0; g < e->n; ++g) {
+    const ho_state* s = &e->st[g];
+    ho_encode_typed(&e->game, s, (s->cur_player + offset) % e->game.players, obs_type, obs + g * len);
   }
 }
 

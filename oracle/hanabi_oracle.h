@@ -26,6 +26,7 @@
 #define HO_MAXR 5
 #define HO_MAXDECK 50
 #define HO_MAXCARDS (HO_MAXC * HO_MAXR)
+#define HO_MAX_OBS 2048            /* longest observation: 1280 (Full 5p) + 100 (seer) */
 
 /* move types, HLE HanabiMove::Type order */
 enum { HO_INVALID = 0, HO_PLAY = 1, HO_DISCARD = 2, HO_REVEAL_COLOR = 3, HO_REVEAL_RANK = 4, HO_DEAL = 5 };
@@ -100,6 +101,10 @@ int ho_env_reset(ho_env* e, uint8_t* obs, uint8_t* legal, uint8_t* step_type);
 int64_t ho_env_step(ho_env* e, const int32_t* actions, uint8_t* obs, uint8_t* legal, float* reward,
                     uint8_t* step_type);
 void ho_env_observe(ho_env* e, int offset, uint8_t* obs, uint8_t* legal);
+/* observation types of HLE: 0 kMinimal, 1 kCardKnowledge (= ho_encode), 2 kSeer */
+int ho_obs_len_typed(const ho_game* g, int obs_type);
+void ho_encode_typed(const ho_game* g, const ho_state* s, int observer, int obs_type, uint8_t* out);
+void ho_env_observe_typed(ho_env* e, int offset, int obs_type, uint8_t* obs /*[n, ho_obs_len_typed]*/);
 /* canonical int32 dump of one game's state (layout documented in hanabi_oracle.c) */
 int ho_state_dump_len(const ho_game* g);
 void ho_env_dump(ho_env* e, int32_t* out /*[n_games, dump_len]*/);

@@ -421,3 +421,31 @@ def test_osawa_discard_intended_flag(name, players):
         oa, _ = ora2.rules_act(orules, 5, t)
         np.testing.assert_array_equal(act[t].cpu().numpy(), oa, err_msg="fused step %d" % t)
         ora2.step(oa)
+
+
+@pytest.mark.parametrize("name,players", CONFIGS)
+def test_minimal_and_seer_observation_types(name, players):
+    """hb_env_observe_as (HLE's kMinimal / kSeer observation types) against the oracle's
+    ho_encode_typed, every bit, every seat offset, along random legal play-outs."""
+    import torch
+    n = 256
+    env, ora = _pair(name, players, n, 4 * n)
+    env.reset(); ora.reset()
+    rng = np.random.default_rng(7)
+    for step in range(70):
+        for t, tname in ((0, "minimal"), (1, "card_knowledge"), (2, "seer")):
+            for offset in range(players):
+                got, bits = env.observe_as(tname, offset, unpack=True)
+                want = ora.observe_typed(t, offset)
+                assert bits == want.shape[1]
+                np.testing.assert_array_equal(got.cpu().numpy().astype(np.uint8), want,
+                                              err_msg="%s offset %d step %d" % (tname, offset, step))
+        packed, bits = env.observe_as("seer")
+        assert packed.shape[1] % 4 == 0 and packed.shape[1] * 32 >= bits
+        legal = ora.legal
+        acts = np.array([rng.choice(np.nonzero(legal[g])[0]) for g in range(n)], np.int32)
+        env.step(torch.as_tensor(acts, device="cuda"))
+        ora.step(acts)
+    with pytest.raises(ValueError):
+        from hanabi_agents_b200 import _lib
+        _lib.check(_lib.lib().hb_env_observe_as(env._h, 3, 0, packed.data_ptr(), packed.shape[1], None))

@@ -386,3 +386,39 @@ def test_intended_semantics_of_the_dead_rules(name, players):
         env.step(a)
         assert env.illegal == 0
     assert all(f > 20 for f in fired), fired
+
+
+@pytest.mark.parametrize("name,players", [("Hanabi-Full", 2), ("Hanabi-Full", 5), ("Hanabi-Small", 2)])
+def test_minimal_and_seer_observation_types(name, players):
+    """HLE's other observation types (oracle/hanabi_oracle.c ho_encode_typed): kMinimal drops the card
+    knowledge section, kSeer prepends the observer's own cards to the hands section.  Checked against the
+    canonical vector and the state dump on random play-outs, from both seats' points of view."""
+    p = game_params(name, players)
+    n = 64
+    env = HanabiOracleEnv(n, threads=2, **p)
+    env.set_decks(make_decks(p["colors"], p["ranks"], 4 * n, 3))
+    env.reset()
+    H, bpc, P = p["hand_size"], p["colors"] * p["ranks"], players
+    know = P * H * (bpc + p["colors"] + p["ranks"])
+    rng = np.random.default_rng(1)
+    if (name, players) == ("Hanabi-Full", 2):
+        assert env.observe_typed(0).shape[1] == 658 - 350 and env.observe_typed(2).shape[1] == 658 + 125
+    for step in range(60):
+        for offset in (0, players - 1):
+            canon, _ = env.observe(offset)
+            mini, card, seer = env.observe_typed(0, offset), env.observe_typed(1, offset), env.observe_typed(2, offset)
+            np.testing.assert_array_equal(card, canon)
+            np.testing.assert_array_equal(mini, canon[:, :canon.shape[1] - know])
+            np.testing.assert_array_equal(seer[:, H * bpc:], canon)         # everything else moves up
+            d = env.dump()
+            cur = d[:, 0]
+            hands = d[:, 8 + p["colors"] + P:8 + p["colors"] + P + 5 * P * H].reshape(n, P, H, 5)
+            own = hands[np.arange(n), (cur + offset) % P, :, 0]             # card index or -1, oldest first
+            want = np.zeros((n, H, bpc), np.uint8)
+            for i in range(H):
+                ok = own[:, i] >= 0
+                want[np.nonzero(ok)[0], i, own[ok, i]] = 1
+            np.testing.assert_array_equal(seer[:, :H * bpc], want.reshape(n, -1))
+        legal = env.legal
+        acts = np.array([rng.choice(np.nonzero(legal[g])[0]) for g in range(n)], np.int32)
+        env.step(acts)

@@ -249,7 +249,7 @@ def allreduce_selfcheck(agent, world, device):
 
     scratch = src.clone()
     out["nccl_allreduce_us"] = timed(lambda: dist.all_reduce(scratch))
-    if impl == "nvlink":
+    if getattr(agent, "_comm", None):
         comm = agent._comm
         bucket = agent.network.grad_bucket
         keep = bucket.clone()

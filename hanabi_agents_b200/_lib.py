@@ -131,6 +131,7 @@ SIGNATURES = {
     "hb_learner_grads": (i32, [vp, vp, vp, f32, f32, i32, vp]),
     "hb_learner_apply": (i32, [vp, f32, f32, f32, f32, f32, vp]),
     "hb_learner_step": (i32, [vp, vp, vp, f32, f32, i32, f32, f32, f32, f32, vp]),
+    "hb_learner_set_comm": (i32, [vp, vp, i32]),
     # NVLink all-reduce of the gradient bucket
     "hb_comm_create": (i32, [i32, i32, i32, vp, i64, C.POINTER(vp)]),
     "hb_comm_destroy": (i32, [vp]),
@@ -139,6 +140,7 @@ SIGNATURES = {
     "hb_comm_allreduce": (i32, [vp, vp]),
     "hb_comm_info": (i32, [vp, i32]),
     "hb_comm_status": (i32, [vp]),
+    "hb_comm_allreduce_range": (i32, [vp, i32, i64, i64, vp]),
     # self-play session
     "hb_session_create": (i32, [i32, i64, i32, C.POINTER(vp)]),
     "hb_session_destroy": (i32, [vp]),

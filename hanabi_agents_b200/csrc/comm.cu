@@ -25,15 +25,22 @@
 
 namespace {
 constexpr int kMaxWorld = 8;
-constexpr int kCommBlocks = 144;      // CTAs per rank (same on every rank; < 148 SMs, all resident)
+constexpr int kCommBlocks = 144;      // most CTAs per rank (same on every rank; < 148 SMs, all resident)
 constexpr int kCommThreads = 512;
+// Independent CHANNELS: all-reduces of different channels may be in flight at the same time (the learner
+// reduces every layer's gradient on that layer's stream, beside the backward pass); calls of one channel
+// must be stream-ordered on every rank and made in the same order on all ranks.  Each channel has its own
+// barrier flags and its own epoch counter IN DEVICE MEMORY (bumped by the kernel itself), so a call can sit
+// in a replayed CUDA graph: nothing that changes from call to call is a kernel argument.
+constexpr int kChannels = 8;
 }  // namespace
 
 struct hb_comm {
   int device = 0, rank = 0, world = 1;
   float* own = nullptr;               // this rank's bucket (not owned)
   int64_t n = 0;
-  uint32_t* flags = nullptr;          // [3 barriers][kCommBlocks][kMaxWorld] epoch counters (owned, exported)
+  uint32_t* flags = nullptr;          // [kChannels][3 barriers][kCommBlocks][kMaxWorld] epoch counters (owned, exported)
+  uint32_t* epochs = nullptr;         // [kChannels] {calls completed, CTAs done} pairs (device, local)
   float* peer_buf[kMaxWorld] = {nullptr};
   uint32_t* peer_flags[kMaxWorld] = {nullptr};
   bool opened = false;
@@ -48,8 +55,9 @@ struct CommArgs {
   float* buf[kMaxWorld];
   uint32_t* flags[kMaxWorld];
   int rank, world;
-  long long n4;                       // float4 elements
-  uint32_t epoch;
+  long long off4, n4;                 // range of the bucket, in float4 elements
+  int channel;
+  uint32_t* epoch;                    // this channel's {calls completed, CTAs done}
   int* timeout;                       // host-mapped flag
 };
 
@@ -85,18 +93,18 @@ __device__ __forceinline__ uint32_t ld_flag_relaxed(const uint32_t* p) {
 // signal is a relaxed store (stage 0: the bucket was written by earlier kernels of this stream).
 // The poll is a relaxed system-scope load; one acquire fence follows the successful poll.
 template <bool PUBLISH>
-__device__ __forceinline__ void gpu_barrier(const CommArgs& a, int stage) {
+__device__ __forceinline__ void gpu_barrier(const CommArgs& a, int stage, uint32_t epoch) {
   __syncthreads();
   if (threadIdx.x < a.world) {
     const int peer = threadIdx.x;
-    const size_t slot = ((size_t)stage * kCommBlocks + blockIdx.x) * kMaxWorld;
+    const size_t slot = (((size_t)a.channel * 3 + stage) * kCommBlocks + blockIdx.x) * kMaxWorld;
     if (peer != a.rank) {
-      if (PUBLISH) st_flag(a.flags[peer] + slot + a.rank, a.epoch);
-      else st_flag_relaxed(a.flags[peer] + slot + a.rank, a.epoch);
+      if (PUBLISH) st_flag(a.flags[peer] + slot + a.rank, epoch);
+      else st_flag_relaxed(a.flags[peer] + slot + a.rank, epoch);
       const uint32_t* mine = a.flags[a.rank] + slot + peer;
       const long long t0 = clock64();
       unsigned spins = 0;
-      while ((int32_t)(ld_flag_relaxed(mine) - a.epoch) < 0) {
+      while ((int32_t)(ld_flag_relaxed(mine) - epoch) < 0) {
         // every 2^16 polls: has the bound (~2 min at 1.9 GHz) passed, or has another CTA given up?
         // (the status word is host memory: one PCIe read, so it is not part of the hot poll)
         if ((++spins & 0xffffu) == 0 &&
@@ -116,11 +124,15 @@ __global__ void __launch_bounds__(kCommThreads)
 allreduce_two_shot_kernel(CommArgs a) {
   const int r = a.rank;
   const long long per = (a.n4 + W - 1) / W;               // slice length in float4
-  gpu_barrier<false>(a, 0);
+  // this call's number on its channel: one more than the calls completed (the counter moves only when the
+  // last CTA of a call leaves, and calls of a channel are stream-ordered)
+  const uint32_t epoch = *(volatile uint32_t*)a.epoch + 1u;
+  gpu_barrier<false>(a, 0, epoch);
   constexpr int U = W <= 2 ? 8 : (W <= 4 ? 4 : 2);         // independent peer loads in flight per thread
-  const long long stride = (long long)kCommBlocks * kCommThreads;
+  const long long stride = (long long)gridDim.x * kCommThreads;
+  const long long end4 = a.off4 + a.n4;
   {
-    const long long lo = per * r, hi = lo + per < a.n4 ? lo + per : a.n4;
+    const long long lo = a.off4 + per * r, hi = lo + per < end4 ? lo + per : end4;
     for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += U * stride) {
       float4 v[U][W];
 #pragma unroll
@@ -142,10 +154,10 @@ allreduce_two_shot_kernel(CommArgs a) {
       }
     }
   }
-  gpu_barrier<true>(a, 1);
+  gpu_barrier<true>(a, 1, epoch);
   for (int jj = 1; jj < W; ++jj) {
     const int j = (r + jj) % W;                            // spread the peers over the links
-    const long long lo = per * j, hi = lo + per < a.n4 ? lo + per : a.n4;
+    const long long lo = a.off4 + per * j, hi = lo + per < end4 ? lo + per : end4;
     const float4* src = reinterpret_cast<const float4*>(a.buf[j]);
     float4* dst = reinterpret_cast<float4*>(a.buf[r]);
     for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += 2 * U * stride) {
@@ -158,7 +170,16 @@ allreduce_two_shot_kernel(CommArgs a) {
         if (i0 + u * stride < hi) dst[i0 + u * stride] = v[u];
     }
   }
-  gpu_barrier<false>(a, 2);
+  gpu_barrier<false>(a, 2, epoch);
+  // the last CTA to leave completes the call: CTAs-done back to 0, calls-completed + 1
+  if (threadIdx.x == 0) {
+    __threadfence();
+    if (atomicAdd(a.epoch + 1, 1u) == gridDim.x - 1) {
+      a.epoch[1] = 0u;
+      __threadfence();
+      *(volatile uint32_t*)a.epoch = epoch;
+    }
+  }
 }
 
 }  // namespace
@@ -178,10 +199,12 @@ int hb_comm_create(int rank, int world, int device, float* d_bucket, int64_t n, 
   hb_comm* c = new (std::nothrow) hb_comm();
   HB_REQUIRE(c != nullptr, "hb_comm_create: out of host memory");
   c->device = device; c->rank = rank; c->world = world; c->own = d_bucket; c->n = n;
-  const size_t fbytes = (size_t)3 * kCommBlocks * kMaxWorld * sizeof(uint32_t);
+  const size_t fbytes = (size_t)kChannels * 3 * kCommBlocks * kMaxWorld * sizeof(uint32_t);
   // own 2 MB block: the IPC handle then maps exactly this allocation on the peers
   cudaError_t e = cudaMalloc(&c->flags, fbytes < ((size_t)2 << 20) ? ((size_t)2 << 20) : fbytes);
   if (e == cudaSuccess) e = cudaMemset(c->flags, 0, fbytes);
+  if (e == cudaSuccess) e = cudaMalloc(&c->epochs, kChannels * 2 * sizeof(uint32_t));
+  if (e == cudaSuccess) e = cudaMemset(c->epochs, 0, kChannels * 2 * sizeof(uint32_t));
   if (e != cudaSuccess) { delete c; return hb::cuda_fail(e, "hb_comm_create alloc", __FILE__, __LINE__); }
   if (cudaHostAlloc((void**)&c->h_timeout, 64, cudaHostAllocMapped) != cudaSuccess ||
       cudaHostGetDevicePointer((void**)&c->d_timeout, c->h_timeout, 0) != cudaSuccess) {
@@ -237,39 +260,58 @@ int hb_comm_destroy(hb_comm* c) {
       if (c->peer_flags[j]) cudaIpcCloseMemHandle(c->peer_flags[j]);
     }
   if (c->flags) cudaFree(c->flags);
+  if (c->epochs) cudaFree(c->epochs);
   if (c->h_timeout) cudaFreeHost(c->h_timeout);
   delete c;
   return HB_OK;
 }
 
-/* In-place sum of the bucket over all ranks; every rank must call it the same number of times.
- * Stream ordered; the result is identical on every rank (fixed summation order). */
-int hb_comm_allreduce(hb_comm* c, void* stream) {
+/* In-place sum of bucket[offset, offset + n) over all ranks on `channel` (0..7).  Calls of one channel must
+ * be stream-ordered on every rank and come in the same order on all ranks; different channels are
+ * independent and may overlap.  Stream ordered, capturable into a CUDA graph (no per-call state in the
+ * arguments); the result is identical on every rank (fixed summation order). */
+int hb_comm_allreduce_range(hb_comm* c, int channel, int64_t offset, int64_t n, void* stream) {
   HB_REQUIRE(c != nullptr, "hb_comm_allreduce: NULL communicator");
+  HB_REQUIRE(channel >= 0 && channel < kChannels, "hb_comm_allreduce: channel %d (0..%d)", channel, kChannels - 1);
+  HB_REQUIRE(offset >= 0 && n > 0 && offset + n <= c->n && offset % 4 == 0 && n % 4 == 0,
+             "hb_comm_allreduce: range [%lld, +%lld) of a %lld-element bucket must be 16-byte aligned",
+             (long long)offset, (long long)n, (long long)c->n);
   if (c->world == 1) return HB_OK;
   if (!c->opened) { hb::set_error("hb_comm_allreduce: peers are not mapped (hb_comm_open)"); return HB_ERR_STATE; }
   hb::DeviceGuard g(c->device);
   CommArgs a;
   for (int j = 0; j < kMaxWorld; ++j) { a.buf[j] = c->peer_buf[j]; a.flags[j] = c->peer_flags[j]; }
-  a.rank = c->rank; a.world = c->world; a.n4 = c->n / 4;
-  a.epoch = ++c->epoch;
+  a.rank = c->rank; a.world = c->world; a.off4 = offset / 4; a.n4 = n / 4;
+  a.channel = channel;
+  a.epoch = c->epochs + 2 * channel;
   a.timeout = c->d_timeout;
+  ++c->epoch;
   if (*(volatile int*)c->h_timeout != 0) {
     hb::set_error("hb_comm_allreduce: an earlier all-reduce gave up waiting for a peer (ranks out of lockstep)");
     return HB_ERR_STATE;
   }
+  // CTAs: enough for ~4 float4 per thread of this rank's slice, the same number on every rank
+  const long long per = (a.n4 + c->world - 1) / c->world;
+  long long want = (per + 4 * kCommThreads - 1) / (4 * kCommThreads);
+  const unsigned blocks = (unsigned)(want < 16 ? 16 : (want > kCommBlocks ? kCommBlocks : want));
   cudaStream_t st = (cudaStream_t)stream;
   switch (c->world) {
-    case 2: allreduce_two_shot_kernel<2><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    case 3: allreduce_two_shot_kernel<3><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    case 4: allreduce_two_shot_kernel<4><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    case 5: allreduce_two_shot_kernel<5><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    case 6: allreduce_two_shot_kernel<6><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    case 7: allreduce_two_shot_kernel<7><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
-    default: allreduce_two_shot_kernel<8><<<kCommBlocks, kCommThreads, 0, st>>>(a); break;
+    case 2: allreduce_two_shot_kernel<2><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 3: allreduce_two_shot_kernel<3><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 4: allreduce_two_shot_kernel<4><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 5: allreduce_two_shot_kernel<5><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 6: allreduce_two_shot_kernel<6><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 7: allreduce_two_shot_kernel<7><<<blocks, kCommThreads, 0, st>>>(a); break;
+    default: allreduce_two_shot_kernel<8><<<blocks, kCommThreads, 0, st>>>(a); break;
   }
   HB_CUDA(cudaGetLastError());
   return HB_OK;
+}
+
+/* The whole bucket, on the last channel (the learner's per-layer calls use channels 0 .. layers - 1). */
+int hb_comm_allreduce(hb_comm* c, void* stream) {
+  HB_REQUIRE(c != nullptr, "hb_comm_allreduce: NULL communicator");
+  return hb_comm_allreduce_range(c, kChannels - 1, 0, c->n, stream);
 }
 
 /* HB_OK, or HB_ERR_STATE when a barrier of an earlier all-reduce timed out waiting for a peer. */

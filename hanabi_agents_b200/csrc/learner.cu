@@ -62,6 +62,8 @@ struct hb_learner {
   // update_priorities beside the backward pass (default) or after Adam (HB_LEARNER_PRIO_OVERLAP=0)
   int prio_overlap = 1;
   int pdl = 1;                   // HB_LEARNER_PDL=0: no programmatic dependent launch
+  hb_comm* comm = nullptr;       // data parallel: per-layer all-reduce inside hb_learner_step
+  int world = 1;
 };
 
 namespace {
@@ -94,6 +96,7 @@ int phase_a(hb_learner* L, int slot, float beta, float discount, int mask_termin
   opts.pdl = L->pdl;
   opts.adam_per_layer = fused_adam ? 1 : 0;
   opts.lr = lr; opts.b1 = b1; opts.b2 = b2; opts.eps = eps; opts.grad_scale = grad_scale;
+  opts.comm = fused_adam ? L->comm : nullptr;
   rc = hb_net_grads_ex(L->net, L->o1, L->act, L->rew, L->o2, L->term, nullptr, nullptr, L->B, beta, discount,
                        mask_terminal, L->loss, L->mean, &opts, s);
   if (rc || !L->prioritized) return rc;
@@ -315,7 +318,18 @@ int64_t* hb_learner_indices(hb_learner* L) { return L ? L->d_idx : nullptr; }
  * update_priorities.  Ordered after everything already enqueued on `stream`; `stream` waits for it. */
 int hb_learner_step(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                     int mask_terminal, float lr, float b1, float b2, float eps, void* stream) {
-  return run_phase_a(L, h_keys, h_idx, beta, discount, mask_terminal, true, lr, b1, b2, eps, 1.0f, stream);
+  const float scale = L && L->comm ? 1.0f / (float)L->world : 1.0f;
+  return run_phase_a(L, h_keys, h_idx, beta, discount, mask_terminal, true, lr, b1, b2, eps, scale, stream);
+}
+
+int hb_learner_set_comm(hb_learner* L, hb_comm* comm, int world) {
+  HB_REQUIRE(L && world >= 1, "hb_learner_set_comm: bad arguments");
+  hb::DeviceGuard g(L->device);
+  HB_CUDA(cudaDeviceSynchronize());
+  drop_graphs(L);                 // the communicator is part of what the graphs captured
+  L->comm = world > 1 ? comm : nullptr;
+  L->world = world;
+  return HB_OK;
 }
 
 /* Phase A: sample (h_keys: B stratified keys as float32, prioritized shards; h_idx: B row indices,

@@ -1200,6 +1200,9 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       HB_CUDA(cudaStreamWaitEvent(ls, q->ev_bias[l], 0));
       HB_CUDA(cudaStreamWaitEvent(ls, q->ev_tick, 0));
       const long long e0 = L.eoff, e1 = l + 1 < nl ? q->tab.l[l + 1].eoff : q->n_eff;
+      // data parallel: this layer's slice of the bucket is summed over the ranks on the layer's own
+      // channel while the dZ chain and the other layers' gradients are still being computed
+      if (opts->comm != nullptr && (rc = hb_comm_allreduce_range(opts->comm, l, e0, e1 - e0, ls))) return rc;
       if ((rc = adam_range(q, 1, e0 / 4, e1 / 4, ls, 0))) return rc;
     }
     HB_CUDA(cudaEventRecord(q->ev_layer[l], ls));

@@ -131,10 +131,14 @@ class DQNAgent:
                 pass
             self._learner = None
 
-    def _allreduce_grads(self):
-        """The one collective of the job: sum of the flat gradient bucket over the ranks.  One kernel over
-        NVLink peer memory (dist.NvlinkAllReduce) when the peers can be mapped, NCCL otherwise or when
-        HB_ALLREDUCE=nccl."""
+    _fused_dp = False
+
+    def _setup_allreduce(self):
+        """The one collective of the job: sum of the flat gradient bucket over the ranks.  Kernels over
+        NVLink peer memory (dist.NvlinkAllReduce) when the peers can be mapped -- then fused into the
+        update, one all-reduce per layer beside the backward pass (HB_ALLREDUCE=nvlink, the default;
+        HB_ALLREDUCE=nvlink-unfused keeps one whole-bucket all-reduce between two graphs) -- NCCL
+        otherwise or when HB_ALLREDUCE=nccl."""
         if getattr(self, "_comm", None) is None:
             self._comm = False
             self.allreduce_impl = "nccl"
@@ -143,12 +147,22 @@ class DQNAgent:
                     from ..dist import NvlinkAllReduce
                     self._comm = NvlinkAllReduce(self.network.grad_bucket, self.process_group)
                     self.allreduce_impl = "nvlink"
+                    if os.environ.get("HB_ALLREDUCE", "nvlink") == "nvlink":
+                        from .. import _lib
+                        world, _ = self._world()
+                        _lib.check(_lib.lib().hb_learner_set_comm(self._learner, self._comm._h, world))
+                        self._fused_dp = True
+                        self.allreduce_impl = "nvlink, per layer inside the update"
                 except RuntimeError as e:   # peers cannot be mapped: every rank takes this branch (dist.py)
                     import warnings
                     self._comm = False
                     self.allreduce_fallback_reason = repr(e)
                     warnings.warn("hanabi_agents_b200: NVLink all-reduce unavailable, using "
                                   "torch.distributed.all_reduce instead: %r" % (e,), RuntimeWarning)
+
+    def _allreduce_grads(self):
+        if getattr(self, "_comm", None) is None:
+            self._setup_allreduce()
         if self._comm:
             self._comm()
         else:
@@ -178,7 +192,11 @@ class DQNAgent:
         beta = float(self.params.beta_is(self.train_step))
         lr = self.params.learning_rate
         lr = float(lr(self.train_step)) if callable(lr) else float(lr)
-        if world == 1:      # one call, one graph: Adam runs layer by layer beside the backward pass
+        if world > 1 and getattr(self, "_comm", None) is None:
+            self._setup_allreduce()
+        if world == 1 or self._fused_dp:
+            # one call, one graph: Adam runs layer by layer beside the backward pass; data parallel: each
+            # layer's gradient is all-reduced over NVLink on its own channel in between (csrc/comm.cu)
             _lib.check(L.hb_learner_step(self._learner, kp, ip, beta, float(self.params.discount), 0,
                                          lr, 0.9, 0.999, self.adam_eps, stream))
         else:

@@ -365,12 +365,17 @@ int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, 
  *   adam_per_layer apply optix.adam (rlax_rainbow.py:215-216) to every layer as soon as its gradient is
  *                  complete, beside the rest of the backward pass (single-process learner: no all-reduce
  *                  between gradient and update); lr, b1, b2, eps, grad_scale as in hb_net_adam */
+struct hb_comm;
 typedef struct hb_net_step_opts {
   const float* d_w_is;
   const float* d_dyn;
   int pdl;
   int adam_per_layer;
   float lr, b1, b2, eps, grad_scale;
+  /* data parallel (with adam_per_layer): every layer's slice of the gradient bucket is all-reduced over
+   * this communicator (hb_comm_allreduce_range, channel = layer) between its gradient and its Adam
+   * update, beside the rest of the backward pass; grad_scale = 1 / world.  NULL: single process. */
+  struct hb_comm* comm;
 } hb_net_step_opts;
 int hb_net_grads_ex(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
                     const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
@@ -430,8 +435,11 @@ int64_t* hb_learner_indices(hb_learner* L);
 int hb_learner_grads(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                      int mask_terminal, void* stream);
 /* Phase B: optix.adam on grad_scale * bucket. */
-/* Both phases in ONE call and one graph, for a single process (no all-reduce between gradient and
- * update): optix.adam is applied layer by layer beside the backward pass. */
+/* Both phases in ONE call and one graph: optix.adam is applied layer by layer beside the backward pass.
+ * With a communicator attached (hb_learner_set_comm; the learner's one exchange step) every
+ * layer's gradient is all-reduced over NVLink on its own channel between its GEMM and its Adam update,
+ * overlapping the rest of the backward pass, and scaled by 1 / world.  Ranks call it in lockstep. */
+int hb_learner_set_comm(hb_learner* L, struct hb_comm* comm, int world);
 int hb_learner_step(hb_learner* L, const float* h_keys, const int64_t* h_idx, float beta, float discount,
                     int mask_terminal, float lr, float b1, float b2, float eps, void* stream);
 int hb_learner_apply(hb_learner* L, float lr, float b1, float b2, float eps, float grad_scale,
@@ -491,6 +499,12 @@ int hb_comm_open(hb_comm* c, const void* h_all);
  * kernel ends, hb_comm_status and later hb_comm_allreduce calls return HB_ERR_STATE. */
 int hb_comm_allreduce(hb_comm* c, void* stream);
 int hb_comm_status(const hb_comm* c);
+/* The same on bucket[offset, offset + n) (multiples of 4 elements) over `channel` 0..7.  Calls of one channel
+ * must be stream-ordered on a rank and made in the same order on every rank; different channels have their
+ * own barrier flags and may overlap -- the learner reduces every layer's gradient on that layer's stream
+ * beside the backward pass.  Nothing that changes from call to call is a kernel argument (the call counter
+ * lives in device memory), so the call can be captured into a CUDA graph and replayed. */
+int hb_comm_allreduce_range(hb_comm* c, int channel, int64_t offset, int64_t n, void* stream);
 /* what: 0 rank, 1 world, 2 peers mapped, 3 calls so far */
 int hb_comm_info(const hb_comm* c, int what);
 

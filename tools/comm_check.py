@@ -44,6 +44,40 @@ for it in range(40):
     assert int(lo) == int(hi), (rank, it)
 
 
+# ranges on independent channels, in flight together on two streams, captured into ONE graph and replayed:
+# every replay must give the sum again (nothing of a call is frozen into the graph but pointers)
+from hanabi_agents_b200 import _lib  # noqa: E402
+L = _lib.lib()
+n_all = bucket.numel()
+cut = (n_all // 2) // 4 * 4
+s1, s2 = torch.cuda.Stream(), torch.cuda.Stream()
+graph = torch.cuda.CUDAGraph()
+x = torch.randn(n_all, device=dev, generator=g)
+bucket.copy_(x)
+torch.cuda.synchronize()
+with torch.cuda.graph(graph):
+    cur = torch.cuda.current_stream()
+    s1.wait_stream(cur)
+    s2.wait_stream(cur)
+    _lib.check(L.hb_comm_allreduce_range(comm._h, 0, 0, cut, s1.cuda_stream))
+    _lib.check(L.hb_comm_allreduce_range(comm._h, 1, cut, n_all - cut, s2.cuda_stream))
+    cur.wait_stream(s1)
+    cur.wait_stream(s2)
+for it in range(5):
+    x = torch.randn(n_all, device=dev, generator=g) * (1.0 + it)
+    bucket.copy_(x)
+    ref = x.clone()
+    dist.all_reduce(ref)
+    graph.replay()
+    torch.cuda.synchronize()
+    if world == 2:
+        assert torch.equal(bucket, ref), ("graph replay", rank, it, float((bucket - ref).abs().max()))
+    else:
+        assert torch.allclose(bucket, ref, rtol=1e-5, atol=1e-5 * (1 + it)), ("graph replay", rank, it)
+if rank == 0:
+    print("two channels on two streams, captured and replayed 5 times: ok")
+
+
 def timed(fn, reps=200):
     for _ in range(10):
         fn()
@@ -94,7 +128,7 @@ for step in range(6):
     a_nv.update(uniforms=u)
     a_nc.update(uniforms=u)
 torch.cuda.synchronize()
-assert a_nv._comm and not a_nc._comm
+assert a_nv._comm and a_nv._fused_dp and not a_nc._comm
 for pa, pb in zip(a_nv.network.get_params(), a_nc.network.get_params()):
     for k in pa:
         if world == 2:
@@ -111,7 +145,8 @@ assert torch.equal(lo, hi)
 B = 256
 params = RlaxRainbowParams(train_batch_size=B, layers=[512, 512], experience_buffer_size=2 ** 15, seed=1)
 res = {}
-for name, force in (("nvlink", False), ("nccl", True)):
+for name, force in (("nvlink", False), ("nvlink-unfused", False), ("nccl", True)):
+    os.environ["HB_ALLREDUCE"] = name if name != "nccl" else "nvlink"
     ag = DQNAgent(ObservationSpec((1024, 658)), ActionSpec(20), params)
     if force:
         ag._comm = False
@@ -122,7 +157,9 @@ for name, force in (("nvlink", False), ("nccl", True)):
                                   (rng.random((n, 20)) < 0.6).astype(np.int8), np.zeros(n, np.uint8))
     res[name] = timed(lambda: ag.update(), reps=200)
 if rank == 0:
-    print("learner update, batch %d per GPU, %d GPUs: nvlink %.1f us (%.0f updates/s), nccl %.1f us (%.0f updates/s)" % (
-        B, world, res["nvlink"] * 1e3, 1e3 / res["nvlink"], res["nccl"] * 1e3, 1e3 / res["nccl"]))
+    print("learner update, batch %d per GPU, %d GPUs: nvlink per layer inside the update %.1f us (%.0f updates/s), "
+          "nvlink whole bucket between two graphs %.1f us (%.0f updates/s), nccl %.1f us (%.0f updates/s)" % (
+              B, world, res["nvlink"] * 1e3, 1e3 / res["nvlink"], res["nvlink-unfused"] * 1e3,
+              1e3 / res["nvlink-unfused"], res["nccl"] * 1e3, 1e3 / res["nccl"]))
     print("comm ok")
 dist.destroy_process_group()

@@ -689,6 +689,37 @@ def run_ours(args):
     e2e_val = world * n * e_steps / float(te.item())
     h2d = 4 * n
     d2h = n * (4 * env.obs_words + 4 * env.legal_words + 4 + 1) + 4 * n
+    # The ceiling of this leg: the same bytes per env step, nothing else -- every rank copies d2h bytes from
+    # the device into its pinned host buffer and h2d bytes back, back to back on one stream, all ranks at the
+    # same time (they share the host's memory system and PCIe root complexes).  e2e / ceiling says how much of
+    # what the host side allows the pipelined loop reaches; a ceiling that does not scale with the ranks is
+    # the host's, not the kernels'.
+    blob_d = torch.empty(d2h, dtype=torch.uint8, device=dev)
+    blob_h = torch.empty(d2h, dtype=torch.uint8).pin_memory()
+    act_d = torch.empty(h2d, dtype=torch.uint8, device=dev)
+    act_h = torch.empty(h2d, dtype=torch.uint8).pin_memory()
+    for _ in range(5):
+        blob_h.copy_(blob_d, non_blocking=True)
+        act_d.copy_(act_h, non_blocking=True)
+    barrier()
+    reps_c = 200
+    t0 = time.perf_counter()
+    for _ in range(reps_c):
+        blob_h.copy_(blob_d, non_blocking=True)
+        act_d.copy_(act_h, non_blocking=True)
+    torch.cuda.synchronize()
+    c_s = time.perf_counter() - t0
+    barrier()
+    tc = torch.tensor([c_s], device=dev)
+    if world > 1:
+        dist.all_reduce(tc, op=dist.ReduceOp.MAX)
+    ceiling_val = world * n * reps_c / float(tc.item())
+    ceiling_gbs = world * (d2h + h2d) * reps_c / float(tc.item()) / 1e9
+    cpu_aff = None
+    try:
+        cpu_aff = len(os.sched_getaffinity(0))
+    except Exception:
+        pass
 
     learner = acting = None
     if not args.no_learner:
@@ -786,6 +817,10 @@ def run_ours(args):
         "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": h2d * T, "d2h_bytes_per_step": d2h * T,
                 "h2d_bytes_per_env_step": h2d, "d2h_bytes_per_env_step": d2h,
                 "env_steps_timed": e_steps, "ms_per_env_step": 1e3 * float(te.item()) / e_steps,
+                "ceiling": {"value": ceiling_val, "unit": UNIT, "frac": e2e_val / ceiling_val,
+                            "copy_GBps_all_ranks": ceiling_gbs, "host_cpus_per_rank": cpu_aff,
+                            "how": "the same D2H + H2D bytes per env step copied back to back into pinned host "
+                                   "memory by every rank at once, nothing else running (max over ranks)"},
                 "path": "per step, host in the loop, pinned host arrays both ways, double-buffered: env.step_host_begin "
                 "(actions H2D, env_step_kernel) | agent.explore_host_async (rules_act_kernel + next actions D2H) | "
                 "env.step_host_outputs (D2H of observation rows (%d B) + legal mask + reward + step type in one copy, "

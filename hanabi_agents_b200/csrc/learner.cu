@@ -29,13 +29,13 @@ struct hb_learner {
   cudaStream_t stream = nullptr, prio = nullptr;   // prio: priority update beside the backward pass
   cudaEvent_t ev_in = nullptr, ev_out = nullptr, ev_prio = nullptr;
   // staging (pinned): per slot [B keys | 8 scalars]; scalars = beta, discount, lr, b1, b2, eps, grad_scale
-  static constexpr int kSlots = 4;
+  static constexpr int kSlots = 2;   // each slot has its own captured graph; the host runs at most 2 steps ahead
   static constexpr int kDyn = 8;
   float* h_in = nullptr;         // [kSlots][B + kDyn]
   int64_t* h_idx = nullptr;      // [kSlots][B] (uniform replay)
   float* h_dynB = nullptr;       // [kSlots][kDyn] scalars of phase B (data-parallel path)
-  cudaEvent_t slot_done[kSlots] = {nullptr, nullptr, nullptr, nullptr};
-  cudaEvent_t slotB_done[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+  cudaEvent_t slot_done[kSlots] = {nullptr, nullptr};
+  cudaEvent_t slotB_done[kSlots] = {nullptr, nullptr};
   int slot = 0, slotB = 0;
   const float* d_in = nullptr;   // h_in as the device addresses it
   int64_t* d_idx = nullptr;
@@ -50,11 +50,11 @@ struct hb_learner {
   float* mean = nullptr;         // [1]
   float* w_is = nullptr;         // the network's importance-weight buffer
   // graphs: per staging slot; what they were captured with
-  cudaGraphExec_t gStep[kSlots] = {nullptr, nullptr, nullptr, nullptr};
-  cudaGraphExec_t gA[kSlots] = {nullptr, nullptr, nullptr, nullptr};
+  cudaGraphExec_t gStep[kSlots] = {nullptr, nullptr};
+  cudaGraphExec_t gA[kSlots] = {nullptr, nullptr};
   cudaGraphExec_t gB = nullptr;
   int kA_mask = -1;              // mask_terminal the graphs were captured with
-  const void* kA_ptr[4] = {nullptr, nullptr, nullptr, nullptr};   // the net's staging the graphs hold
+  const void* kA_ptr[4] = {nullptr, nullptr};   // the net's staging the graphs hold
   int64_t rb_gen = -1;           // generation of the replay shard's scratch the graphs were captured with
   int warm = 0;                  // eager steps run (the first one allocates workspaces)
   int recaptures = 0;

@@ -2,23 +2,27 @@
 // gradient bucket across the GPUs of one node ("ncclAllReduce(sum, fp32) of the flat
 // gradient bucket once per update, fixed algorithm for run-to-run determinism").
 //
-// One process per GPU.  Every rank exports its bucket and a small flag array with CUDA IPC and maps
-// its peers'; the kernel is a two-shot all-reduce with plain peer loads / stores over NVLink:
-//   barrier      every rank's bucket is complete (stream order) and visible
-//   shot 1       rank r sums slice r of ALL buckets, ranks in fixed order 0..W-1 (every rank computes
-//                the same bits), and writes the result over slice r of its own bucket
-//   barrier
-//   shot 2       rank r copies the reduced slice j from rank j's bucket, for every j != r
-//   barrier      nobody still reads a bucket that its owner is about to overwrite
-// 2 (W-1)/W of the bucket crosses NVLink per rank instead of the (W-1) of a one-shot scheme; at the
-// 5-23 MB of this path the three flag barriers (a few microseconds each) are the rest of the cost.
-// Barriers are per CTA: CTA b of rank r raises flag[peer][b][r] on every peer and waits for its own
-// row -- only CTAs with the same index on different GPUs wait for each other, so no co-residency of a
-// whole grid is assumed.  A wait for a late peer does NOT trap (a rank that is seconds late -- an
-// evaluation on rank 0, a graph recapture, a first-use allocation -- is normal, and a trap would poison
-// the CUDA context of every rank): it polls for up to ~2 minutes, then raises a flag in host-mapped
-// memory (hb_comm_status) and leaves the barrier so that the host can raise an error instead of
-// hanging the device.  Ranks must call hb_comm_allreduce in lockstep, as with any collective.
+// One process per GPU.  Every rank exports its bucket and one more allocation (barrier flags + a staging
+// area as large as the bucket) with CUDA IPC and maps its peers'.  The kernel is a two-shot all-reduce made of
+// PUSHES -- remote stores over NVLink, which are one-way, where the first version pulled with remote loads,
+// each a round trip:
+//   shot 1       rank r stores slice j of its bucket into slot r of rank j's staging area, for every j != r,
+//                then raises flag[j][r] (release)
+//   reduce       rank r waits for the W-1 flags, sums slice r -- its own bucket and the W-1 staged copies --
+//                in fixed rank order 0..W-1 (every element is summed ONCE, by its owner: all ranks end up with
+//                the same bits), and
+//   shot 2       stores the result into slice r of EVERY rank's bucket, then raises flag2[j][r]
+//   done         rank r waits for the W-1 flag2's: its bucket holds every reduced slice.
+// Two one-way hops instead of three barriers of round trips, and no trailing barrier: nobody ever READS a
+// peer's bucket, so a rank may overwrite its bucket as soon as its own call is through; a peer can only push
+// into my staging area for call e+1 after it finished call e, which needed my flag2, which I raise after my
+// reduction has read the staging area.  2 (W-1)/W of the bucket leaves each rank per call.
+// Flags are per CTA: CTA b of every rank handles the same elements, so only CTAs with the same index on
+// different GPUs wait for each other and no co-residency of a whole grid is assumed.  A wait for a late peer
+// does NOT trap (a rank that is seconds late -- an evaluation on rank 0, a graph recapture, a first-use
+// allocation -- is normal, and a trap would poison the CUDA context of every rank): it polls for up to ~2
+// minutes, then raises a flag in host-mapped memory (hb_comm_status) and leaves so that the host can raise an
+// error instead of hanging the device.  Ranks must call hb_comm_allreduce in lockstep, as with any collective.
 #include "common.cuh"
 #include <new>
 #include <string.h>
@@ -33,6 +37,7 @@ constexpr int kCommThreads = 512;
 // barrier flags and its own epoch counter IN DEVICE MEMORY (bumped by the kernel itself), so a call can sit
 // in a replayed CUDA graph: nothing that changes from call to call is a kernel argument.
 constexpr int kChannels = 8;
+constexpr size_t kStageOffset = (size_t)1 << 20;   // flags (110 KB) and the staging area share one allocation
 }  // namespace
 
 struct hb_comm {
@@ -42,7 +47,7 @@ struct hb_comm {
   uint32_t* flags = nullptr;          // [kChannels][3 barriers][kCommBlocks][kMaxWorld] epoch counters (owned, exported)
   uint32_t* epochs = nullptr;         // [kChannels] {calls completed, CTAs done} pairs (device, local)
   float* peer_buf[kMaxWorld] = {nullptr};
-  uint32_t* peer_flags[kMaxWorld] = {nullptr};
+  uint32_t* peer_flags[kMaxWorld] = {nullptr};   // staging of rank j = (float*)((char*)peer_flags[j] + kStageOffset)
   bool opened = false;
   uint32_t epoch = 0;
   int* h_timeout = nullptr;           // pinned + mapped: set by a barrier that gave up waiting
@@ -56,6 +61,7 @@ struct CommArgs {
   uint32_t* flags[kMaxWorld];
   int rank, world;
   long long off4, n4;                 // range of the bucket, in float4 elements
+  long long chan4;                    // float4 elements of staging per channel (bucket + slack)
   int channel;
   uint32_t* epoch;                    // this channel's {calls completed, CTAs done}
   int* timeout;                       // host-mapped flag
@@ -88,89 +94,91 @@ __device__ __forceinline__ uint32_t ld_flag_relaxed(const uint32_t* p) {
   return v;
 }
 
-// CTA-level barrier across the GPUs (stage 0..2).  Thread i < world signals peer i and waits for it.
-// PUBLISH: this CTA wrote data the peers will read after the barrier (release store); otherwise the
-// signal is a relaxed store (stage 0: the bucket was written by earlier kernels of this stream).
-// The poll is a relaxed system-scope load; one acquire fence follows the successful poll.
-template <bool PUBLISH>
-__device__ __forceinline__ void gpu_barrier(const CommArgs& a, int stage, uint32_t epoch) {
-  __syncthreads();
-  if (threadIdx.x < a.world) {
-    const int peer = threadIdx.x;
-    const size_t slot = (((size_t)a.channel * 3 + stage) * kCommBlocks + blockIdx.x) * kMaxWorld;
-    if (peer != a.rank) {
-      if (PUBLISH) st_flag(a.flags[peer] + slot + a.rank, epoch);
-      else st_flag_relaxed(a.flags[peer] + slot + a.rank, epoch);
-      const uint32_t* mine = a.flags[a.rank] + slot + peer;
-      const long long t0 = clock64();
-      unsigned spins = 0;
-      while ((int32_t)(ld_flag_relaxed(mine) - epoch) < 0) {
-        // every 2^16 polls: has the bound (~2 min at 1.9 GHz) passed, or has another CTA given up?
-        // (the status word is host memory: one PCIe read, so it is not part of the hot poll)
-        if ((++spins & 0xffffu) == 0 &&
-            (clock64() - t0 > 240000000000ll || *(volatile int*)a.timeout != 0)) {
-          *(volatile int*)a.timeout = 1;                    // the host reports it (hb_comm_status)
-          break;
-        }
-      }
-      asm volatile("fence.acq_rel.sys;" ::: "memory");
+// Wait until peer `peer`'s flag of (stage, this CTA) has reached `epoch` (bounded, see the header).
+__device__ __forceinline__ void wait_flag(const CommArgs& a, int stage, int peer, uint32_t epoch) {
+  const size_t slot = (((size_t)a.channel * 3 + stage) * kCommBlocks + blockIdx.x) * kMaxWorld;
+  const uint32_t* mine = a.flags[a.rank] + slot + peer;
+  const long long t0 = clock64();
+  unsigned spins = 0;
+  while ((int32_t)(ld_flag_relaxed(mine) - epoch) < 0) {
+    // every 2^16 polls: has the bound (~2 min at 1.9 GHz) passed, or has another CTA given up?
+    // (the status word is host memory: one PCIe read, so it is not part of the hot poll)
+    if ((++spins & 0xffffu) == 0 &&
+        (clock64() - t0 > 240000000000ll || *(volatile int*)a.timeout != 0)) {
+      *(volatile int*)a.timeout = 1;                    // the host reports it (hb_comm_status)
+      break;
     }
   }
-  __syncthreads();
+}
+__device__ __forceinline__ void raise_flag(const CommArgs& a, int stage, int peer, uint32_t epoch) {
+  const size_t slot = (((size_t)a.channel * 3 + stage) * kCommBlocks + blockIdx.x) * kMaxWorld;
+  st_flag(a.flags[peer] + slot + a.rank, epoch);        // release: the CTA's stores before the barrier first
+}
+// every channel has a staging area of its own (calls of different channels overlap in time and the slots of
+// a range reach up to W - 1 elements past its end)
+__device__ __forceinline__ float4* stage_of(const CommArgs& a, int j) {
+  return reinterpret_cast<float4*>(reinterpret_cast<char*>(a.flags[j]) + kStageOffset) + a.channel * a.chan4;
 }
 
 template <int W>
 __global__ void __launch_bounds__(kCommThreads)
-allreduce_two_shot_kernel(CommArgs a) {
+allreduce_push_kernel(CommArgs a) {
   const int r = a.rank;
   const long long per = (a.n4 + W - 1) / W;               // slice length in float4
   // this call's number on its channel: one more than the calls completed (the counter moves only when the
   // last CTA of a call leaves, and calls of a channel are stream-ordered)
   const uint32_t epoch = *(volatile uint32_t*)a.epoch + 1u;
-  gpu_barrier<false>(a, 0, epoch);
-  constexpr int U = W <= 2 ? 8 : (W <= 4 ? 4 : 2);         // independent peer loads in flight per thread
   const long long stride = (long long)gridDim.x * kCommThreads;
+  const long long t = (long long)blockIdx.x * kCommThreads + threadIdx.x;
   const long long end4 = a.off4 + a.n4;
-  {
-    const long long lo = a.off4 + per * r, hi = lo + per < end4 ? lo + per : end4;
-    for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += U * stride) {
-      float4 v[U][W];
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-#pragma unroll
-        for (int j = 0; j < W; ++j)
-          if (i < hi) v[u][j] = ld_peer(reinterpret_cast<const float4*>(a.buf[j]) + i);
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const long long i = i0 + u * stride;
-        if (i < hi) {
-          float4 s = v[u][0];
-#pragma unroll
-          for (int j = 1; j < W; ++j) { s.x += v[u][j].x; s.y += v[u][j].y; s.z += v[u][j].z; s.w += v[u][j].w; }
-          reinterpret_cast<float4*>(a.buf[r])[i] = s;
-        }
-      }
-    }
-  }
-  gpu_barrier<true>(a, 1, epoch);
+  const float4* own = reinterpret_cast<const float4*>(a.buf[r]);
+  // ---- shot 1: my copy of slice j -> slot r of rank j's staging area (element k of the slice at
+  // off4 + r * per + k; W * per <= n4 + W, the staging area has that slack)
+#pragma unroll 1
   for (int jj = 1; jj < W; ++jj) {
     const int j = (r + jj) % W;                            // spread the peers over the links
-    const long long lo = a.off4 + per * j, hi = lo + per < end4 ? lo + per : end4;
-    const float4* src = reinterpret_cast<const float4*>(a.buf[j]);
-    float4* dst = reinterpret_cast<float4*>(a.buf[r]);
-    for (long long i0 = lo + (long long)blockIdx.x * kCommThreads + threadIdx.x; i0 < hi; i0 += 2 * U * stride) {
-      float4 v[2 * U];
+    const long long lo = a.off4 + per * j;
+    const long long len = lo + per < end4 ? per : (end4 > lo ? end4 - lo : 0);
+    float4* dst = stage_of(a, j) + a.off4 + per * r;
+    for (long long k = t; k < len; k += 4 * stride) {
+      float4 v[4];
 #pragma unroll
-      for (int u = 0; u < 2 * U; ++u)
-        if (i0 + u * stride < hi) v[u] = ld_peer(src + i0 + u * stride);
+      for (int u = 0; u < 4; ++u)
+        if (k + u * stride < len) v[u] = own[lo + k + u * stride];
 #pragma unroll
-      for (int u = 0; u < 2 * U; ++u)
-        if (i0 + u * stride < hi) dst[i0 + u * stride] = v[u];
+      for (int u = 0; u < 4; ++u)
+        if (k + u * stride < len) dst[k + u * stride] = v[u];
     }
   }
-  gpu_barrier<false>(a, 2, epoch);
+  __syncthreads();
+  if (threadIdx.x < W && threadIdx.x != r) raise_flag(a, 0, threadIdx.x, epoch);
+  // ---- reduce slice r in rank order, store it into every rank's bucket
+  if (threadIdx.x < W && threadIdx.x != r) wait_flag(a, 0, threadIdx.x, epoch);
+  if (threadIdx.x < W) asm volatile("fence.acq_rel.sys;" ::: "memory");
+  __syncthreads();
+  {
+    const long long lo = a.off4 + per * r;
+    const long long len = lo + per < end4 ? per : (end4 > lo ? end4 - lo : 0);
+    const float4* st = stage_of(a, r) + a.off4;
+    for (long long k = t; k < len; k += stride) {
+      float4 s;
+#pragma unroll
+      for (int p = 0; p < W; ++p) {
+        // staged copies were written by remote stores: read them past the L1 (ld.volatile)
+        const float4 v = p == r ? own[lo + k] : ld_peer(st + per * p + k);
+        if (p == 0) s = v;
+        else { s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w; }
+      }
+#pragma unroll
+      for (int j = 0; j < W; ++j) reinterpret_cast<float4*>(a.buf[j])[lo + k] = s;
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < W && threadIdx.x != r) raise_flag(a, 1, threadIdx.x, epoch);
+  // ---- done when every other owner's slice has landed in my bucket
+  if (threadIdx.x < W && threadIdx.x != r) wait_flag(a, 1, threadIdx.x, epoch);
+  if (threadIdx.x < W) asm volatile("fence.acq_rel.sys;" ::: "memory");
+  __syncthreads();
   // the last CTA to leave completes the call: CTAs-done back to 0, calls-completed + 1
   if (threadIdx.x == 0) {
     __threadfence();
@@ -200,8 +208,11 @@ int hb_comm_create(int rank, int world, int device, float* d_bucket, int64_t n, 
   HB_REQUIRE(c != nullptr, "hb_comm_create: out of host memory");
   c->device = device; c->rank = rank; c->world = world; c->own = d_bucket; c->n = n;
   const size_t fbytes = (size_t)kChannels * 3 * kCommBlocks * kMaxWorld * sizeof(uint32_t);
-  // own 2 MB block: the IPC handle then maps exactly this allocation on the peers
-  cudaError_t e = cudaMalloc(&c->flags, fbytes < ((size_t)2 << 20) ? ((size_t)2 << 20) : fbytes);
+  static_assert((size_t)kChannels * 3 * kCommBlocks * kMaxWorld * sizeof(uint32_t) <= kStageOffset, "flags overlap the staging area");
+  // one block of its own: the IPC handle then maps exactly this allocation on the peers.  Flags first, the
+  // staging area (the bucket's size + slack for the rounded-up slices) from kStageOffset on.
+  const size_t total = kStageOffset + (size_t)kChannels * ((size_t)n + 16 * kMaxWorld) * sizeof(float);
+  cudaError_t e = cudaMalloc(&c->flags, total < ((size_t)2 << 20) ? ((size_t)2 << 20) : total);
   if (e == cudaSuccess) e = cudaMemset(c->flags, 0, fbytes);
   if (e == cudaSuccess) e = cudaMalloc(&c->epochs, kChannels * 2 * sizeof(uint32_t));
   if (e == cudaSuccess) e = cudaMemset(c->epochs, 0, kChannels * 2 * sizeof(uint32_t));
@@ -282,6 +293,7 @@ int hb_comm_allreduce_range(hb_comm* c, int channel, int64_t offset, int64_t n, 
   CommArgs a;
   for (int j = 0; j < kMaxWorld; ++j) { a.buf[j] = c->peer_buf[j]; a.flags[j] = c->peer_flags[j]; }
   a.rank = c->rank; a.world = c->world; a.off4 = offset / 4; a.n4 = n / 4;
+  a.chan4 = (c->n + 16 * kMaxWorld) / 4;
   a.channel = channel;
   a.epoch = c->epochs + 2 * channel;
   a.timeout = c->d_timeout;
@@ -296,13 +308,13 @@ int hb_comm_allreduce_range(hb_comm* c, int channel, int64_t offset, int64_t n, 
   const unsigned blocks = (unsigned)(want < 16 ? 16 : (want > kCommBlocks ? kCommBlocks : want));
   cudaStream_t st = (cudaStream_t)stream;
   switch (c->world) {
-    case 2: allreduce_two_shot_kernel<2><<<blocks, kCommThreads, 0, st>>>(a); break;
-    case 3: allreduce_two_shot_kernel<3><<<blocks, kCommThreads, 0, st>>>(a); break;
-    case 4: allreduce_two_shot_kernel<4><<<blocks, kCommThreads, 0, st>>>(a); break;
-    case 5: allreduce_two_shot_kernel<5><<<blocks, kCommThreads, 0, st>>>(a); break;
-    case 6: allreduce_two_shot_kernel<6><<<blocks, kCommThreads, 0, st>>>(a); break;
-    case 7: allreduce_two_shot_kernel<7><<<blocks, kCommThreads, 0, st>>>(a); break;
-    default: allreduce_two_shot_kernel<8><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 2: allreduce_push_kernel<2><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 3: allreduce_push_kernel<3><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 4: allreduce_push_kernel<4><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 5: allreduce_push_kernel<5><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 6: allreduce_push_kernel<6><<<blocks, kCommThreads, 0, st>>>(a); break;
+    case 7: allreduce_push_kernel<7><<<blocks, kCommThreads, 0, st>>>(a); break;
+    default: allreduce_push_kernel<8><<<blocks, kCommThreads, 0, st>>>(a); break;
   }
   HB_CUDA(cudaGetLastError());
   return HB_OK;

@@ -265,42 +265,74 @@ sample_gather_kernel(hb_replay rb, const float* __restrict__ heap, int depth, in
     if (pos < 0) pos += rb.cap;                           // numpy negative indexing (never taken here)
     if (pos < 0 || pos >= rb.cap) { *err = 1; pos = 0; }  // a leaf beyond the ring: caller's IndexError
     s_pos[k] = pos;
+    // the row's scalars: loads issued before the arithmetic below (they miss to HBM; the shard is far
+    // larger than L2), stored after it
+    const int32_t r_act = act ? rb.act[pos] : 0;
+    const float r_rew = rew ? rb.rew[pos] : 0.f;
+    const uint8_t r_term = term ? rb.term[pos] : (uint8_t)0;
+    uint32_t r_lms[2] = {0u, 0u};
+    if (lms)
+      for (int j = 0; j < rb.legal_words; ++j) r_lms[j] = rb.lms[pos * rb.legal_words + j];
     const double p = ((double)value + 1e-10) / (double)root;
     const float p32 = (float)p;
     if (prios64 != nullptr) prios64[k] = p;
     if (prios32 != nullptr) prios32[k] = p32;
     w = powf(1.0f / p32, beta);
-    if (act) act[k] = rb.act[pos];
-    if (rew) rew[k] = rb.rew[pos];
-    if (term) term[k] = rb.term[pos];
+    if (act) act[k] = r_act;
+    if (rew) rew[k] = r_rew;
+    if (term) term[k] = r_term;
     if (lms)
-      for (int j = 0; j < rb.legal_words; ++j) lms[(int64_t)k * rb.legal_words + j] = rb.lms[pos * rb.legal_words + j];
+      for (int j = 0; j < rb.legal_words; ++j) lms[(int64_t)k * rb.legal_words + j] = r_lms[j];
   }
   // max over the batch (weights are positive; lanes past B hold 0)
   float mx = w;
   for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
   if ((k & 31) == 0) red[k >> 5] = mx;
   __syncthreads();                                        // also publishes s_pos
-  if (k < 32) {
-    mx = red[k];
-    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (k == 0) red[0] = mx;
-  }
-  __syncthreads();
-  if (k < B && w_is != nullptr) w_is[k] = w / red[0];
-  // gather: (row, 16-byte chunk) items over the whole CTA, every load independent of the others
+  // gather: (row, 16-byte chunk) items over the whole CTA.  Up to four items per thread and observation
+  // array, ALL their loads (HBM misses) issued before the first store and before the weight normalisation.
   const int q16 = rb.stride >> 2;
   const uint4* s1 = reinterpret_cast<const uint4*>(rb.obs_tm1);
   const uint4* s2 = reinterpret_cast<const uint4*>(rb.obs_t);
   uint4* d1 = reinterpret_cast<uint4*>(obs_tm1);
   uint4* d2 = reinterpret_cast<uint4*>(obs_t);
   const int items = B * q16;
-  for (int it = k; it < items; it += 1024) {
-    const int r = it / q16, c = it - r * q16;
-    const int64_t src = s_pos[r] * q16 + c;
-    if (d1) d1[it] = s1[src];
-    if (d2) d2[it] = s2[src];
+  uint4 v1[4], v2[4];
+  auto load4 = [&](int it0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int it = it0 + u * 1024;
+      if (it < items) {
+        const int r = it / q16, c = it - r * q16;
+        const int64_t src = s_pos[r] * q16 + c;
+        if (d1) v1[u] = s1[src];
+        if (d2) v2[u] = s2[src];
+      }
+    }
+  };
+  auto store4 = [&](int it0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int it = it0 + u * 1024;
+      if (it < items) {
+        if (d1) d1[it] = v1[u];
+        if (d2) d2[it] = v2[u];
+      }
+    }
+  };
+  load4(k);
+  if (k < 32) {                                            // warp 0, all lanes: the block maximum while the loads fly
+    mx = red[k];
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    if (k == 0) red[0] = mx;
   }
+  store4(k);
+  for (int it0 = k + 4 * 1024; it0 < items; it0 += 4 * 1024) {
+    load4(it0);
+    store4(it0);
+  }
+  __syncthreads();
+  if (k < B && w_is != nullptr) w_is[k] = w / red[0];
 }
 
 // priorities = (|td| + 1e-10) ** alpha in float32, running max / min  (priority_buffer.py:49-51).

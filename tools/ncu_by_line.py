@@ -34,16 +34,21 @@ def main():
     base = insts[0][0]
     tmp = tempfile.mkdtemp()
     subprocess.run(["cuobjdump", "-xelf", "all", os.path.abspath(lib)], cwd=tmp, capture_output=True)
-    lines = {}
+    # every .text section whose name holds the substring (one per template instance); the one with
+    # as many instructions as the report's kernel is the instance that was profiled
+    cands = []
     for f in os.listdir(tmp):
         if not f.endswith(".cubin"):
             continue
         dis = subprocess.run(["nvdisasm", "-g", "-c", os.path.join(tmp, f)], capture_output=True,
                              text=True).stdout.splitlines()
-        inside, cur = False, ("?", 0)
+        inside, cur, sec = False, ("?", 0), None
         for ln in dis:
             if ln.startswith("//---") and ".text." in ln:
-                inside = kern in ln and not lines
+                inside = kern in ln
+                if inside:
+                    sec = {}
+                    cands.append(sec)
                 continue
             if not inside:
                 continue
@@ -53,9 +58,11 @@ def main():
                 continue
             m = re.match(r"\s*/\*([0-9a-f]+)\*/\s+(\S.*);", ln)
             if m:
-                lines[int(m.group(1), 16)] = cur
-        if lines:
-            break
+                sec[int(m.group(1), 16)] = cur
+    exact = [c for c in cands if len(c) == len(insts)]
+    lines = exact[0] if exact else (min(cands, key=lambda c: abs(len(c) - len(insts))) if cands else {})
+    if not exact:
+        print("warning: no section with exactly %d instructions (%s)" % (len(insts), [len(c) for c in cands]))
     agg = collections.defaultdict(lambda: [0, 0])
     tot_s = tot_i = 0
     for addr, _src, smp, ex in insts:

@@ -244,10 +244,14 @@ int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_lea
   if (const char* v = getenv("HB_LEARNER_PDL")) L->pdl = atoi(v) != 0;
   const size_t B = (size_t)batch;
   const int S = hb_learner::kSlots, D = hb_learner::kDyn;
-  cudaError_t e = cudaStreamCreateWithFlags(&L->stream, cudaStreamNonBlocking);
+  // the update's main chain runs at the highest priority, the priority write-back at the lowest (qnet.cu:
+  // "Priorities")
+  int prio_lo = 0, prio_hi = 0;
+  cudaError_t e = cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&L->stream, cudaStreamNonBlocking, prio_hi);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_in, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_out, cudaEventDisableTiming);
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->prio, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&L->prio, cudaStreamNonBlocking, prio_lo);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_prio, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaHostAlloc((void**)&L->h_in, S * (B + D) * 4, cudaHostAllocMapped | cudaHostAllocPortable);
   if (e == cudaSuccess) e = cudaHostGetDevicePointer((void**)&L->d_in, L->h_in, 0);

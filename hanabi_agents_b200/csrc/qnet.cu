@@ -239,33 +239,48 @@ __global__ void is_weights_kernel(const float* __restrict__ prios, int B, float 
   for (int i = threadIdx.x; i < B; i += blockDim.x) w[i] = w[i] / mx;
 }
 
-// One warp per sample.  rlax.categorical_double_q_learning (rlax_rainbow.py:172-184):
+// The head layer's backward product folded into the C51 loss (see c51_loss_kernel<true>).
+struct HeadBackward {
+  const __half* w;          // head's effective weights [N, K]
+  int K;                    // width of the previous layer (multiple of 8)
+  const __half* gate;       // previous layer's activations [B.., K] (ReLU backward)
+  __half* dz_prev;          // [B, K]
+  __half* dzt_prev;         // [K, ld_dzt]
+};
+constexpr int kHeadBwSmemMax = 112 * 1024;     // rows of one action (n_atoms x K halves) staged per sample
+
+// One warp, one sample.  rlax.categorical_double_q_learning (rlax_rainbow.py:172-184):
 //   a* = argmax_a q_sel;  p = softmax(target_logits[a*]);  target_z = r + gamma * z;
 //   m = categorical_l2_project(target_z, p, z);  loss = -sum_i m_i log_softmax(logits_tm1[a])_i
-// Writes loss_b and dL/dlogits * B / w-normalisation folded later:  dz[b, a*64+i] = w_b (p_i S - m_i).
-__global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const float* __restrict__ q_sel,
-                                int ldq, const uint32_t* __restrict__ legal_t, int legal_words,
-                                const float* __restrict__ tlogits, int ldl,
-                                const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
-                                const uint8_t* __restrict__ term_t, int mask_terminal,
-                                const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
-                                float gamma, const float* __restrict__ dyn, __half* __restrict__ dz,
-                                __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b) {
-  tc::pdl_launch_dependents();
-  tc::pdl_wait();
-  if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
-  const int b = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  const int lane = threadIdx.x & 31;
-  if (b >= B) return;
+// Writes loss_b and dL/dlogits * B / w-normalisation folded later:  dz[b, a*64+i] = w_b (p_i S - m_i);
+// returns the lane's two values (atoms lane and lane + 32) as the fp16 numbers that were stored.
+__device__ __forceinline__ void c51_row(int b, int lane, const float* __restrict__ logits_tm1,
+                                        const float* __restrict__ q_sel, int ldq,
+                                        const uint32_t* __restrict__ legal_t, int legal_words,
+                                        const float* __restrict__ tlogits, int ldl, int a,
+                                        const float* __restrict__ r_t, const uint8_t* __restrict__ term_t,
+                                        int mask_terminal, const float* __restrict__ w_is, int A, int n_atoms,
+                                        float vmax, float gamma, __half* __restrict__ dz,
+                                        __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b,
+                                        __half& h0, __half& h1) {
   const unsigned full = 0xffffffffu;
+  const float vmin = -vmax, dzv = 2.0f * vmax / (float)(n_atoms - 1);
+  const int i0 = lane, i1 = lane + 32;
+  // everything that does not depend on a* is requested first (these loads used to sit behind the
+  // argmax -> target logits -> projection chain, one L2 round trip each)
+  const float* ol = logits_tm1 + (long long)b * ldl + a * 64;
+  const float l0 = i0 < n_atoms ? ol[i0] : -INFINITY, l1 = i1 < n_atoms ? ol[i1] : -INFINITY;
+  const float r = r_t[b];
+  const float w = w_is[b];
+  const bool terminal = mask_terminal && term_t != nullptr && term_t[b];
   // a* = first maximum of q_sel[b, :]  (jnp.argmax)
   float best = -INFINITY;
   int besta = 0x7fffffff;
-  for (int a = lane; a < A; a += 32) {
-    float v = q_sel[(long long)b * ldq + a];
+  for (int aa = lane; aa < A; aa += 32) {
+    float v = q_sel[(long long)b * ldq + aa];
     // TF-Rainbow: argmax(next_qt + next_legal_actions), illegal = -inf  (rainbow_agent.py:203-204)
-    if (legal_t != nullptr && !((legal_t[(long long)b * legal_words + (a >> 5)] >> (a & 31)) & 1u)) v = -INFINITY;
-    if (v > best) { best = v; besta = a; }
+    if (legal_t != nullptr && !((legal_t[(long long)b * legal_words + (aa >> 5)] >> (aa & 31)) & 1u)) v = -INFINITY;
+    if (v > best) { best = v; besta = aa; }
   }
   for (int o = 16; o; o >>= 1) {
     const float ov = __shfl_xor_sync(full, best, o);
@@ -273,8 +288,6 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
     if (ov > best || (ov == best && oa < besta)) { best = ov; besta = oa; }
   }
   const int astar = besta == 0x7fffffff ? 0 : besta;
-  const float vmin = -vmax, dzv = 2.0f * vmax / (float)(n_atoms - 1);
-  const int i0 = lane, i1 = lane + 32;
   // target distribution p_j
   const float* tl = tlogits + (long long)b * ldl + astar * 64;
   const float t0 = i0 < n_atoms ? tl[i0] : -INFINITY, t1 = i1 < n_atoms ? tl[i1] : -INFINITY;
@@ -285,8 +298,7 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
   for (int o = 16; o; o >>= 1) den += __shfl_xor_sync(full, den, o);
   const float p0 = e0 / den, p1 = e1 / den;
   // projection onto the fixed support: m_i = sum_j clip(1 - |clip(tz_j) - z_i| / dz, 0, 1) p_j
-  const float r = r_t[b];
-  const float g = (mask_terminal && term_t != nullptr && term_t[b]) ? 0.f : gamma;
+  const float g = terminal ? 0.f : gamma;
   const float zi0 = vmin + dzv * (float)i0, zi1 = vmin + dzv * (float)i1;
   float m0 = 0.f, m1 = 0.f;
   const float inv_dz = 1.0f / dzv;
@@ -302,9 +314,6 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
   if (i0 >= n_atoms) m0 = 0.f;
   if (i1 >= n_atoms) m1 = 0.f;
   // log-softmax of the online logits of the action taken
-  const int a = a_tm1[b];
-  const float* ol = logits_tm1 + (long long)b * ldl + a * 64;
-  const float l0 = i0 < n_atoms ? ol[i0] : -INFINITY, l1 = i1 < n_atoms ? ol[i1] : -INFINITY;
   float lmx = fmaxf(l0, l1);
   for (int o = 16; o; o >>= 1) lmx = fmaxf(lmx, __shfl_xor_sync(full, lmx, o));
   const float f0 = i0 < n_atoms ? expf(l0 - lmx) : 0.f, f1 = i1 < n_atoms ? expf(l1 - lmx) : 0.f;
@@ -318,16 +327,101 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
     S += __shfl_xor_sync(full, S, o);
   }
   if (lane == 0) loss_b[b] = -part;
-  const float w = w_is[b];
   const float d0 = w * (f0 / lden * S - m0), d1 = w * (f1 / lden * S - m1);
+  h0 = __float2half_rn(i0 < n_atoms ? d0 : 0.f);
+  h1 = __float2half_rn(i1 < n_atoms ? d1 : 0.f);
   const long long col = (long long)a * 64;
   if (i0 < n_atoms) {
-    dz[(long long)b * ldl + col + i0] = __float2half_rn(d0);
-    dzt[(col + i0) * ld_dzt + b] = __float2half_rn(d0);
+    dz[(long long)b * ldl + col + i0] = h0;
+    dzt[(col + i0) * ld_dzt + b] = h0;
   }
   if (i1 < n_atoms) {
-    dz[(long long)b * ldl + col + i1] = __float2half_rn(d1);
-    dzt[(col + i1) * ld_dzt + b] = __float2half_rn(d1);
+    dz[(long long)b * ldl + col + i1] = h1;
+    dzt[(col + i1) * ld_dzt + b] = h1;
+  }
+}
+
+// HEAD_BW == false: one warp per sample (grid = ceil(B / warps per CTA)).
+// HEAD_BW == true: one CTA per sample that also computes the previous layer's dZ row.  dL/dlogits of a
+// sample is n_atoms values of ONE action, so that row is n_atoms consecutive rows of the head's effective
+// weights [N, K] combined -- not a dense [B, N] x [N, K] product (that GEMM was 15 us of every update's
+// critical path: 20 k-blocks for 51 non-zero columns per row).  The rows depend only on the action taken:
+// one bulk copy (cp.async.bulk, 51 KB) brings them to shared memory while warp 0 computes the loss.
+// The fp16-rounded dL/dlogits are used, as the GEMM would read them; fp32 accumulation.
+template <bool HEAD_BW>
+__global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const float* __restrict__ q_sel,
+                                int ldq, const uint32_t* __restrict__ legal_t, int legal_words,
+                                const float* __restrict__ tlogits, int ldl,
+                                const int32_t* __restrict__ a_tm1, const float* __restrict__ r_t,
+                                const uint8_t* __restrict__ term_t, int mask_terminal,
+                                const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
+                                float gamma, const float* __restrict__ dyn, __half* __restrict__ dz,
+                                __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b,
+                                HeadBackward hb) {
+  extern __shared__ __align__(128) unsigned char hb_smem[];
+  tc::pdl_launch_dependents();
+  tc::pdl_wait();
+  if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = HEAD_BW ? (int)blockIdx.x : (int)(blockIdx.x * (blockDim.x >> 5)) + warp;
+  if (b >= B) return;
+  const int a = a_tm1[b];
+  __half h0, h1;
+  if constexpr (!HEAD_BW) {
+    c51_row(b, lane, logits_tm1, q_sel, ldq, legal_t, legal_words, tlogits, ldl, a, r_t, term_t, mask_terminal,
+            w_is, A, n_atoms, vmax, gamma, dz, dzt, ld_dzt, loss_b, h0, h1);
+  } else {
+    const uint32_t bytes = (uint32_t)n_atoms * (uint32_t)hb.K * 2u;
+    const __half* wsm = reinterpret_cast<const __half*>(hb_smem);
+    float* gsm = reinterpret_cast<float*>(hb_smem + ((bytes + 127u) & ~127u));
+    uint64_t* bar = reinterpret_cast<uint64_t*>(gsm + 64);
+    if (threadIdx.x == 32) {                     // warp 1: warp 0 goes straight to the loss
+      tc::mbar_init(bar, 1);
+      tc::fence_barrier_init();
+      tc::mbar_expect_tx(bar, bytes);
+      const __half* src = hb.w + (size_t)a * 64 * hb.K;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(tc::smem_u32(hb_smem)), "l"(src), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+    }
+    if (warp == 0) {
+      c51_row(b, lane, logits_tm1, q_sel, ldq, legal_t, legal_words, tlogits, ldl, a, r_t, term_t, mask_terminal,
+              w_is, A, n_atoms, vmax, gamma, dz, dzt, ld_dzt, loss_b, h0, h1);
+      gsm[lane] = __half2float(h0);
+      gsm[lane + 32] = __half2float(h1);
+    }
+    __syncthreads();
+    tc::mbar_wait(bar, 0);
+    for (int k4 = threadIdx.x; k4 < (hb.K >> 2); k4 += blockDim.x) {
+      float acc[4] = {0.f, 0.f, 0.f, 0.f};
+      const __half* col = wsm + 4 * k4;
+#pragma unroll 4
+      for (int i = 0; i < n_atoms; ++i) {
+        const uint2 v = *reinterpret_cast<const uint2*>(col + (size_t)i * hb.K);
+        const float gi = gsm[i];
+        const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+        const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+        acc[0] = fmaf(gi, f0.x, acc[0]);
+        acc[1] = fmaf(gi, f0.y, acc[1]);
+        acc[2] = fmaf(gi, f1.x, acc[2]);
+        acc[3] = fmaf(gi, f1.y, acc[3]);
+      }
+      const uint2 gv = *reinterpret_cast<const uint2*>(hb.gate + (size_t)b * hb.K + 4 * k4);   // ReLU backward
+      const float2 g0 = __half22float2(*reinterpret_cast<const __half2*>(&gv.x));
+      const float2 g1 = __half22float2(*reinterpret_cast<const __half2*>(&gv.y));
+      if (!(g0.x > 0.f)) acc[0] = 0.f;
+      if (!(g0.y > 0.f)) acc[1] = 0.f;
+      if (!(g1.x > 0.f)) acc[2] = 0.f;
+      if (!(g1.y > 0.f)) acc[3] = 0.f;
+      const __half2 o0 = __floats2half2_rn(acc[0], acc[1]), o1 = __floats2half2_rn(acc[2], acc[3]);
+      uint2 o;
+      o.x = *reinterpret_cast<const uint32_t*>(&o0);
+      o.y = *reinterpret_cast<const uint32_t*>(&o1);
+      *reinterpret_cast<uint2*>(hb.dz_prev + (size_t)b * hb.K + 4 * k4) = o;
+      hb.dzt_prev[(size_t)(4 * k4) * ld_dzt + b] = __low2half(o0);
+      hb.dzt_prev[(size_t)(4 * k4 + 1) * ld_dzt + b] = __high2half(o0);
+      hb.dzt_prev[(size_t)(4 * k4 + 2) * ld_dzt + b] = __low2half(o1);
+      hb.dzt_prev[(size_t)(4 * k4 + 3) * ld_dzt + b] = __high2half(o1);
+    }
   }
 }
 
@@ -380,6 +474,7 @@ __global__ void mean_loss_kernel(const float* __restrict__ loss_b, const float* 
 // gb[n] = alpha * sum_b zt[n, b]   (one warp per output unit, fixed order)
 __global__ void bias_grad_kernel(const __half* __restrict__ zt, int ld, int N, int B, float alpha,
                                  float* __restrict__ gb) {
+  tc::pdl_wait();              // launched programmatically behind the dZ GEMM (first layer): resident early
   const int n = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   const int lane = threadIdx.x & 31;
   if (n >= N) return;
@@ -557,8 +652,15 @@ int ensure_learner_ws(hb_qnet* q, int B) {
   if ((rc = dev_alloc(&q->x, (size_t)2 * B * K0))) return rc;
   if ((rc = dev_alloc(&q->xb, (size_t)2 * B * q->obs_stride))) return rc;
   if (q->side == nullptr) {
-    HB_CUDA(cudaStreamCreateWithFlags(&q->side, cudaStreamNonBlocking));
-    HB_CUDA(cudaStreamCreateWithFlags(&q->side2, cudaStreamNonBlocking));
+    // Priorities: the target network's forward pass (side) and the first layer's gradient + update
+    // (lstream[0]) are on the critical path of an update; the other layers' optix.adam kernels are
+    // bandwidth-bound grids of hundreds of CTAs that would otherwise hold the SMs' registers while a
+    // critical-path GEMM waits to be placed (seen in the CUPTI timeline: 13 us).  Captured kernel nodes
+    // keep their stream's priority.
+    int prio_lo = 0, prio_hi = 0;
+    HB_CUDA(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+    HB_CUDA(cudaStreamCreateWithPriority(&q->side, cudaStreamNonBlocking, prio_hi));
+    HB_CUDA(cudaStreamCreateWithPriority(&q->side2, cudaStreamNonBlocking, prio_lo));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join2, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_fork, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
@@ -566,7 +668,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_wt, cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) {
-      HB_CUDA(cudaStreamCreateWithFlags(&q->lstream[l], cudaStreamNonBlocking));
+      HB_CUDA(cudaStreamCreateWithPriority(&q->lstream[l], cudaStreamNonBlocking, l == 0 ? prio_hi : prio_lo));
       HB_CUDA(cudaEventCreateWithFlags(&q->ev_bias[l], cudaEventDisableTiming));
       HB_CUDA(cudaEventCreateWithFlags(&q->ev_layer[l], cudaEventDisableTiming));
     }
@@ -687,19 +789,35 @@ int adam_tick(hb_qnet* net, float lr, float b1, float b2, float eps, float grad_
 }
 
 // optix.adam / refresh over the 4-element groups [i4_begin, i4_end) of the flat parameter space
-int adam_range(hb_qnet* net, int do_update, long long i4_begin, long long i4_end, cudaStream_t s, int tf_style) {
+// ctas_per_sm > 0: a layer's update beside the backward pass is held to that many CTAs per SM (by asking
+// for a matching share of the shared memory it never touches).  Left alone, the bandwidth-bound grid fills
+// every SM's register file for its whole 10-15 us and a critical-path kernel that becomes ready in the
+// meantime (the first layer's bias gradient, a gradient GEMM) waits for CTAs to retire whatever its priority.
+int adam_range(hb_qnet* net, int do_update, long long i4_begin, long long i4_end, cudaStream_t s, int tf_style,
+               int ctas_per_sm = 0) {
   int* step_ptr = reinterpret_cast<int*>(net->scalars + 2);
   const long long n4 = i4_end - i4_begin;
   if (n4 <= 0) return HB_OK;
   const unsigned blocks = (unsigned)((n4 + 255) / 256 < 148 * 16 ? (n4 + 255) / 256 : 148 * 16);
+  size_t smem = 0;
+  if (ctas_per_sm > 0) {
+    smem = (size_t)(227 * 1024) / ctas_per_sm - 2048;
+    static bool configured[64] = {false};
+    const int dev = net->device;
+    if (dev < 0 || dev >= 64 || !configured[dev]) {
+      HB_CUDA(cudaFuncSetAttribute(adam_refresh_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      HB_CUDA(cudaFuncSetAttribute(adam_refresh_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024));
+      if (dev >= 0 && dev < 64) configured[dev] = true;
+    }
+  }
   if (net->kinds == 3)
-    adam_refresh_kernel<3><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
-                                                  net->adam_m, net->adam_v, net->grad, 1.f, do_update,
-                                                  0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
+    adam_refresh_kernel<3><<<blocks, 256, smem, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
+                                                     net->adam_m, net->adam_v, net->grad, 1.f, do_update,
+                                                     0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   else
-    adam_refresh_kernel<1><<<blocks, 256, 0, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
-                                                  net->adam_m, net->adam_v, net->grad, 1.f, do_update,
-                                                  0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
+    adam_refresh_kernel<1><<<blocks, 256, smem, s>>>(net->tab, net->n_eff, i4_begin, i4_end, net->master, net->eps,
+                                                     net->adam_m, net->adam_v, net->grad, 1.f, do_update,
+                                                     0.f, 0.f, 0.f, 0.f, step_ptr, net->w16, net->w16t, net->beff, tf_style);
   HB_CUDA(cudaGetLastError());
   return HB_OK;
 }
@@ -1074,6 +1192,13 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   const int pdl = opts ? opts->pdl : 0;
   const float* dyn = opts ? opts->d_dyn : nullptr;
   const bool per_layer = opts && opts->adam_per_layer;
+  // C51: the head's backward product is part of the loss kernel (HB_DENSE_HEAD_BW=1: the dense GEMM)
+  static const bool l_main = !(getenv("HB_DW0_OWN_STREAM") && atoi(getenv("HB_DW0_OWN_STREAM")) != 0);
+  static const int adam_ctas = getenv("HB_ADAM_CTAS_PER_SM") ? atoi(getenv("HB_ADAM_CTAS_PER_SM")) : 0;
+  static const bool bias0_main = getenv("HB_BIAS0_MAIN") && atoi(getenv("HB_BIAS0_MAIN")) != 0;
+  static const bool dense_head_bw = getenv("HB_DENSE_HEAD_BW") && atoi(getenv("HB_DENSE_HEAD_BW")) != 0;
+  const bool head_bw = q->n_atoms > 1 && q->n_atoms <= 64 && nl >= 2 && LL.K % 8 == 0 &&
+                       (size_t)q->n_atoms * LL.K * 2 <= (size_t)kHeadBwSmemMax && !dense_head_bw;
   // 1. packed rows side by side: [0, B) = obs_tm1, [B, 2B) = obs_t
   const size_t row_words = (size_t)q->obs_stride;
   // (a caller that gathered its rows straight into hb_net_obs_staging saves the two copies: each is a
@@ -1150,9 +1275,32 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       const float* logits = q->logits;
       const float* tlogits = q->tlogits;
       const float* w_is = q->w_is;
-      HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel, logits, q_sel, ldq, legal_t, (q->A + 31) / 32, tlogits,
-                                 LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A, q->n_atoms,
-                                 q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp, q->loss_b));
+      HeadBackward hbw{};
+      const float* qs = q_sel;
+      if (head_bw) {
+        hbw.w = q->w16 + LL.woff;
+        hbw.K = LL.K;
+        hbw.gate = q->h[nl - 2];
+        hbw.dz_prev = q->dz[nl - 2];
+        hbw.dzt_prev = q->dzt[nl - 2];
+        cfg.gridDim = dim3(B);                   // one CTA per sample
+        cfg.dynamicSmemBytes = (((size_t)q->n_atoms * LL.K * 2 + 127) & ~(size_t)127) + 64 * 4 + 16;
+        static bool attr_set[64] = {};
+        if (!attr_set[q->device & 63]) {
+          HB_CUDA(cudaFuncSetAttribute(c51_loss_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                       kHeadBwSmemMax + 1024));
+          attr_set[q->device & 63] = true;
+        }
+        HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<true>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
+                                   tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
+                                   q->n_atoms, q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp,
+                                   q->loss_b, hbw));
+      } else {
+        HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<false>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
+                                   tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
+                                   q->n_atoms, q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp,
+                                   q->loss_b, hbw));
+      }
     } else {
       cfg.gridDim = dim3((B + 127) / 128);
       cfg.blockDim = dim3(128);
@@ -1180,9 +1328,13 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_wt, 0));
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];
-    cudaStream_t ls = q->lstream[l];
+    // the first layer's gradient and update are the tail of the critical path: they stay on the main
+    // stream (nothing else is left for it), right behind the last dZ GEMM with a programmatic launch --
+    // handed to another stream the gradient GEMM started 4 to 10 us after its input was complete
+    const bool on_main = l == 0 && per_layer && l_main;
+    cudaStream_t ls = on_main ? s : q->lstream[l];
     HB_CUDA(cudaEventRecord(q->ev_dz[l], s));              // dz[l] / dzt[l] are complete here
-    HB_CUDA(cudaStreamWaitEvent(ls, q->ev_dz[l], 0));
+    if (!on_main) HB_CUDA(cudaStreamWaitEvent(ls, q->ev_dz[l], 0));
     // dW_l [N, K] = dZ_l^T . X_l  : A = dzt[l] [N, B], B = (layer input)^T [K, B]
     const __half* in_t = l == 0 ? q->xt : q->ht[l - 1];
     const int ld_in_t = l == 0 ? Bp : 2 * Bp;
@@ -1190,23 +1342,40 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.alpha = invB;
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
+    ep.pdl = on_main ? pdl : 0;
     if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
-    HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_dz[l], 0));
-    bias_grad_kernel<<<(L.N + 7) / 8, 256, 0, q->side2>>>(q->dzt[l], Bp, L.N, B, invB,
-                                                        q->grad + L.eoff + (long long)L.N * L.K);
-    HB_CUDA(cudaGetLastError());
+    // (the first layer's bias gradient on the high-priority side stream, idle since the target network's
+    // forward pass: on side2 it queued behind the other layers' Adam CTAs and held the last update up)
+    cudaStream_t bs = on_main ? (bias0_main ? s : q->side) : q->side2;
+    if (bs != s) HB_CUDA(cudaStreamWaitEvent(bs, q->ev_dz[l], 0));
+    {
+      // programmatic launch for the first layer: its CTAs are placed while the SMs still have room and
+      // wait inside the kernel, instead of queueing behind the other layers' Adam CTAs when dZ is ready
+      cudaLaunchAttribute battr[1];
+      battr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      battr[0].val.programmaticStreamSerializationAllowed = (on_main && pdl) ? 1 : 0;
+      cudaLaunchConfig_t bcfg = {};
+      bcfg.gridDim = dim3((L.N + 7) / 8);
+      bcfg.blockDim = dim3(256);
+      bcfg.stream = bs;
+      bcfg.attrs = battr;
+      bcfg.numAttrs = 1;
+      const __half* zt = q->dzt[l];
+      HB_CUDA(cudaLaunchKernelEx(&bcfg, bias_grad_kernel, zt, Bp, L.N, B, invB,
+                                 q->grad + L.eoff + (long long)L.N * L.K));
+    }
     if (per_layer) {
-      HB_CUDA(cudaEventRecord(q->ev_bias[l], q->side2));
+      HB_CUDA(cudaEventRecord(q->ev_bias[l], bs));
       HB_CUDA(cudaStreamWaitEvent(ls, q->ev_bias[l], 0));
       HB_CUDA(cudaStreamWaitEvent(ls, q->ev_tick, 0));
       const long long e0 = L.eoff, e1 = l + 1 < nl ? q->tab.l[l + 1].eoff : q->n_eff;
       // data parallel: this layer's slice of the bucket is summed over the ranks on the layer's own
       // channel while the dZ chain and the other layers' gradients are still being computed
       if (opts->comm != nullptr && (rc = hb_comm_allreduce_range(opts->comm, l, e0, e1 - e0, ls))) return rc;
-      if ((rc = adam_range(q, 1, e0 / 4, e1 / 4, ls, 0))) return rc;
+      if ((rc = adam_range(q, 1, e0 / 4, e1 / 4, ls, 0, on_main ? 0 : adam_ctas))) return rc;
     }
     HB_CUDA(cudaEventRecord(q->ev_layer[l], ls));
-    if (l > 0) {
+    if (l > 0 && !(l == nl - 1 && head_bw)) {
       // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
       tc::EpiParams eb{};
       eb.alpha = 1.f;

@@ -13,6 +13,7 @@
 // Masters, Adam moments and gradients are fp32; the GEMM operands are the fp16 roundings of the
 // effective weights ([N, K] and its transpose) and fp16 activations, accumulated in fp32.
 #include "tc_host.cuh"
+#include "tc_chain.cuh"
 #include <math.h>
 #include <new>
 #include <vector>
@@ -68,6 +69,7 @@ struct hb_qnet {
   uint32_t* xb = nullptr;              // [2B, obs_stride] packed rows: obs_tm1 then obs_t
   cudaStream_t side = nullptr;         // second stream: target forward / weight gradients run beside
   cudaEvent_t ev_fork = nullptr, ev_join = nullptr, ev_join2 = nullptr, ev_loss = nullptr, ev_wt = nullptr,
+              ev_fwd = nullptr,
               ev_dz[kMaxLayers] = {nullptr};
   cudaStream_t side2 = nullptr;        // small kernels beside the GEMMs of `side`
   // one stream per layer for {dW_l GEMM -> Adam_l}: layer l's update starts as soon as dZ_l exists and
@@ -88,6 +90,7 @@ struct hb_qnet {
   float* w_is = nullptr;               // [B]
   float* loss_b = nullptr;             // [B] per-sample loss / td
   float* scalars = nullptr;            // [4]: mean loss, max weight, ...
+  unsigned int* chain = nullptr;       // tc_chain.cuh: [0..1] launch state, [2..] row-block counters
 };
 
 namespace {
@@ -570,6 +573,24 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, long long i
   }
 }
 
+// out[c, r] = in[r, c] for r < rows, c < cols (activations for the weight-gradient GEMMs): 32 x 32 tiles
+// through shared memory, grid (ceil(cols / 32), ceil(rows / 32)), 256 threads
+__global__ void transpose_act_kernel(const __half* __restrict__ in, int ld_in, int rows, int cols,
+                                     __half* __restrict__ out, int ld_out) {
+  __shared__ __half tile[32][33];
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int i = ty; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + tx;
+    tile[i][tx] = (r < rows && c < cols) ? in[(size_t)r * ld_in + c] : __float2half(0.f);
+  }
+  __syncthreads();
+  for (int i = ty; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + tx;
+    if (r < rows && c < cols) out[(size_t)c * ld_out + r] = tile[tx][i];
+  }
+}
+
 // w16t[k, n] = w16[n, k] for every layer: 32 x 32 tiles through shared memory so that both the
 // reads and the writes are coalesced (the v1 Adam kernel scattered 2-byte stores: 38 us per step).
 __global__ void transpose16_kernel(LayerTable tab, const __half* __restrict__ w16, __half* __restrict__ w16t) {
@@ -666,6 +687,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_join, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_loss, cudaEventDisableTiming));
     HB_CUDA(cudaEventCreateWithFlags(&q->ev_wt, cudaEventDisableTiming));
+    HB_CUDA(cudaEventCreateWithFlags(&q->ev_fwd, cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) HB_CUDA(cudaEventCreateWithFlags(&q->ev_dz[l], cudaEventDisableTiming));
     for (int l = 0; l < kMaxLayers; ++l) {
       HB_CUDA(cudaStreamCreateWithPriority(&q->lstream[l], cudaStreamNonBlocking, l == 0 ? prio_hi : prio_lo));
@@ -767,6 +789,172 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
     }
     if (rc) return rc;
   }
+  return HB_OK;
+}
+
+// The learner's two forward passes (online network on 2B rows, target network on B rows) as one launch
+// of tc::mlp_chain_kernel.  Same operands and epilogues as forward() gives each layer.  Returns
+// HB_OK with *done = 0 when the shapes do not qualify (the caller then runs forward() twice).
+int forward_chain(hb_qnet* q, int B, const int32_t* d_a_tm1, int tf_variant, int ldq, cudaStream_t s, int pdl,
+                  int* done) {
+  *done = 0;
+  const int nl = q->n_layers;
+  static const bool off = getenv("HB_FWD_CHAIN") && atoi(getenv("HB_FWD_CHAIN")) == 0;
+  if (off || nl < 2 || 2 * nl > tc::kChainMaxJobs) return HB_OK;
+  tc::ChainParams P{};
+  // Tile widths.  The target network's head writes every logit (the loss picks the action once the online
+  // network's argmax is known): 64 KB per 128-wide tile at the ~45 GB/s one SM stores, so its tiles are 64
+  // wide when all tiles of the launch still fit on the device.
+  int bn_of[kMaxLayers][2];
+  {
+    static const bool narrow_off = getenv("HB_CHAIN_NARROW") && atoi(getenv("HB_CHAIN_NARROW")) == 0;
+    long long total = 0;
+    const long long tm_on = (2 * B + tc::BM - 1) / tc::BM, tm_tg = (B + tc::BM - 1) / tc::BM;
+    for (int l = 0; l < nl; ++l) {
+      bn_of[l][0] = bn_of[l][1] = 128;
+      total += (tm_on + tm_tg) * ((q->tab.l[l].N + 127) / 128);
+    }
+    const int NH = q->tab.l[nl - 1].N;
+    if (!narrow_off && q->n_atoms > 1 && total + tm_tg * ((NH + 63) / 64 - (NH + 127) / 128) <= tc::sm_count())
+      bn_of[nl - 1][1] = 64;
+  }
+  int tiles = 0, flags = 0;
+  const size_t row_words = (size_t)q->obs_stride;
+  for (int l = 0; l < nl; ++l) {
+    const LayerGeo& g = q->tab.l[l];
+    for (int net = 0; net < 2; ++net) {
+      const int rows = net == 0 ? 2 * B : B;
+      const __half* wts = net == 0 ? q->w16 : q->t16;
+      const float* bias = net == 0 ? q->beff : q->tbeff;
+      __half* const* hbuf = net == 0 ? q->h : q->th;
+      tc::ChainJob& J = P.job[2 * l + net];
+      tc::EpiParams& ep = J.ep;
+      ep = tc::EpiParams{};
+      ep.M = rows;
+      ep.N = g.N;
+      ep.alpha = 1.f;
+      ep.bias = bias + g.boff;
+      J.K = g.K;
+      J.bn = bn_of[l][net];
+      J.tiles_n = (g.N + J.bn - 1) / J.bn;
+      const int tiles_m = (rows + tc::BM - 1) / tc::BM;
+      J.tile_base = tiles;
+      tiles += tiles_m * J.tiles_n;
+      J.flag_base = 2 + flags;
+      flags += tiles_m;
+      J.dep = l == 0 ? -1 : 2 * (l - 1) + net;
+      J.dep_arrivals = l == 0 ? 0 : P.job[J.dep].tiles_n * (P.job[J.dep].bn == 64 ? tc::kEpiWarps / 2 : tc::kEpiWarps);
+      J.has_consumer = l < nl - 1;
+      int rc;
+      if ((rc = tc::make_tmap(&J.tb, wts + g.woff, g.N, g.K, g.K, J.bn))) return rc;
+      if (l == 0) {
+        J.abits = 1;
+        J.ta = J.tb;
+        ep.a_bits = q->xb + (net == 0 ? 0 : (size_t)B * row_words);
+        ep.a_stride = q->obs_stride;
+        if (q->obs_stride % 2 != 0 || g.K > 32 * q->obs_stride) return HB_OK;
+      } else {
+        const int Kin = q->tab.l[l - 1].N;
+        if ((rc = tc::make_tmap(&J.ta, hbuf[l - 1], rows, g.K, Kin, tc::BM))) return rc;
+      }
+      J.tout = J.tb;
+      if (l < nl - 1) {
+        J.epi = tc::EPI_F16;
+        ep.relu = 1;
+        ep.out16 = hbuf[l];
+        ep.ld_out = g.N;
+        // (no transposed copy here: the weight-gradient GEMMs want it much later, the caller makes it
+        // beside the loss -- in the epilogue it was 1.5-2 us of every hidden layer)
+        if ((rc = tc::out_map<tc::EPI_F16>(&J.tout, J.tb, ep))) return rc;
+      } else if (q->n_atoms > 1) {
+        J.epi = tc::EPI_C51;
+        ep.out32 = net == 0 ? q->logits : q->tlogits;
+        ep.ld_out = g.N;
+        ep.q = net == 0 ? q->q_on : (tf_variant ? q->q_tg : nullptr);
+        ep.ld_q = ldq;
+        ep.n_atoms = q->n_atoms;
+        ep.z0 = -q->vmax;
+        ep.dz = 2.f * q->vmax / (float)(q->n_atoms - 1);
+        ep.q_scale = 1.0f / (float)q->n_atoms;
+        if (net == 0 && !tf_variant) {       // online head: logits of the action taken, q of the next state
+          J.sel_action = d_a_tm1;
+          J.sel_rows = B;
+        }
+      } else {
+        J.epi = tc::EPI_F32;
+        ep.out32 = net == 0 ? q->q_on : q->tlogits;
+        ep.ld_out = ldq;
+      }
+    }
+  }
+  if (tiles > tc::sm_count() || 2 + flags > 128) return HB_OK;
+  P.n_jobs = 2 * nl;
+  P.total = tiles;
+  P.state = q->chain;
+  P.flags = q->chain;                      // flag_base already counts from the start of the buffer
+  static bool configured[64] = {false};
+  const int dev = q->device;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    HB_CUDA(cudaFuncSetAttribute(tc::mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::smem_bytes_for(tc::kChainBN)));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)tiles);
+  cfg.blockDim = dim3(tc::kThreads);
+  cfg.dynamicSmemBytes = tc::smem_bytes_for(tc::kChainBN);
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  // HB_CHAIN_TRACE=1 (debugging, eager launches only): per-job phase times of the launch on stderr
+  static const bool trace = getenv("HB_CHAIN_TRACE") && atoi(getenv("HB_CHAIN_TRACE")) != 0;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (trace) cudaStreamIsCapturing(s, &cap);
+  static unsigned long long* d_trace = nullptr;
+  if (trace && cap == cudaStreamCaptureStatusNone) {
+    if (d_trace == nullptr) HB_CUDA(cudaMalloc(&d_trace, 256 * 16 * 8));
+    HB_CUDA(cudaMemsetAsync(d_trace, 0, 256 * 16 * 8, s));
+    P.trace = d_trace;
+  }
+  HB_CUDA(cudaLaunchKernelEx(&cfg, tc::mlp_chain_kernel, P));
+  if (P.trace != nullptr) {
+    std::vector<unsigned long long> h(256 * 16);
+    HB_CUDA(cudaStreamSynchronize(s));
+    HB_CUDA(cudaMemcpy(h.data(), d_trace, 256 * 16 * 8, cudaMemcpyDeviceToHost));
+    unsigned long long t0 = ~0ull;
+    for (int c = 0; c < tiles; ++c) if (h[c * 16] && h[c * 16] < t0) t0 = h[c * 16];
+    for (int jn = 0; jn < P.n_jobs; ++jn) {
+      const int c0 = P.job[jn].tile_base, c1 = jn + 1 < P.n_jobs ? P.job[jn + 1].tile_base : tiles;
+      double mx[6] = {0, 0, 0, 0, 0, 0}, mn[6] = {1e30, 1e30, 1e30, 1e30, 1e30, 1e30};
+      for (int c = c0; c < c1; ++c)
+        for (int k = 0; k < 6; ++k) {
+          const double v = ((double)h[c * 16 + k] - (double)t0) * 1e-3;
+          if (v > mx[k]) mx[k] = v;
+          if (v < mn[k]) mn[k] = v;
+        }
+      {
+        const int c = c0;   // SM clock: cycles between two stamps of one CTA over the same span in ns
+        fprintf(stderr, "  [cta %d: %.0f cycles in %.0f ns between 'acc' and 'stores done']\n", c,
+                (double)(h[c * 16 + 7] - h[c * 16 + 6]), (double)(h[c * 16 + 5] - h[c * 16 + 3]));
+        if (h[c * 16 + 8] && P.job[jn].abits)
+          fprintf(stderr, "  [expand kb 0 cycles: wait slot %lld | expand+sts %lld | proxy fence %lld | arrive %lld]\n",
+                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
+                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]));
+        else if (h[c * 16 + 8])
+          fprintf(stderr, "  [c51 epilogue cycles: tmem %lld | bias+add %lld | stage %lld | row stores %lld | q %lld]\n",
+                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
+                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]),
+                  (long long)(h[c * 16 + 13] - h[c * 16 + 12]));
+      }
+      fprintf(stderr, "chain job %d (%d tiles): start %.1f-%.1f | rows ready %.1f-%.1f | mma issued %.1f-%.1f | "
+              "acc %.1f-%.1f | stores issued %.1f-%.1f | stores done %.1f-%.1f us\n", jn, c1 - c0, mn[0], mx[0],
+              mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mn[4], mx[4], mn[5], mx[5]);
+    }
+  }
+  *done = 1;
   return HB_OK;
 }
 
@@ -936,6 +1124,7 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   if (!rc) rc = dev_alloc(&q->t16, (size_t)q->n_w);
   if (!rc) rc = dev_alloc(&q->beff, (size_t)q->n_b);
   if (!rc) rc = dev_alloc(&q->tbeff, (size_t)q->n_b);
+  if (!rc) rc = dev_alloc(&q->chain, 128);
   if (!rc) rc = dev_alloc(&q->scalars, 32);      // [0] mean loss [1] max weight [2] Adam step [3..7] its corrections
   if (rc) { hb_net_destroy(q); return rc; }
   *out = q;
@@ -949,6 +1138,7 @@ int hb_net_destroy(hb_qnet* q) {
   dev_free(q->master); dev_free(q->tmaster); dev_free(q->eps); dev_free(q->adam_m); dev_free(q->adam_v); dev_free(q->grad);
   dev_free(q->w16); dev_free(q->w16t); dev_free(q->t16); dev_free(q->beff); dev_free(q->tbeff);
   dev_free(q->scalars);
+  dev_free(q->chain);
   if (q->side) {
     cudaStreamDestroy(q->side);
     if (q->side2) cudaStreamDestroy(q->side2);
@@ -957,6 +1147,7 @@ int hb_net_destroy(hb_qnet* q) {
     cudaEventDestroy(q->ev_join);
     if (q->ev_loss) cudaEventDestroy(q->ev_loss);
     if (q->ev_wt) cudaEventDestroy(q->ev_wt);
+    if (q->ev_fwd) cudaEventDestroy(q->ev_fwd);
     for (int l = 0; l < kMaxLayers; ++l) cudaEventDestroy(q->ev_dz[l]);
     for (int l = 0; l < kMaxLayers; ++l) {
       if (q->lstream[l]) cudaStreamDestroy(q->lstream[l]);
@@ -1213,11 +1404,17 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   // fork: the side stream runs the target network, the transposed observations and the importance
   // weights while the main stream runs the online network (both join before the loss)
   HB_CUDA(cudaEventRecord(q->ev_fork, s));
-  HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_fork, 0));
-  if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
-                    q->n_atoms > 1 ? (tf_variant ? q->q_tg : nullptr) : q->tlogits, ldq, q->side,
-                    fused ? q->xb + (size_t)B * row_words : nullptr, pdl))) return rc;
-  HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  // both networks, every layer, one launch (tc_chain.cuh) when every tile fits on the device at once ...
+  int chained = 0;
+  if (fused && (rc = forward_chain(q, B, d_a_tm1, tf_variant, ldq, s, pdl, &chained))) return rc;
+  if (chained) HB_CUDA(cudaEventRecord(q->ev_fwd, s));
+  if (!chained) {   // ... else the target network layer by layer on the side stream
+    HB_CUDA(cudaStreamWaitEvent(q->side, q->ev_fork, 0));
+    if ((rc = forward(q, q->t16, q->tbeff, q->x + (size_t)B * K0, B, q->th, nullptr, 0, q->tlogits,
+                      q->n_atoms > 1 ? (tf_variant ? q->q_tg : nullptr) : q->tlogits, ldq, q->side,
+                      fused ? q->xb + (size_t)B * row_words : nullptr, pdl))) return rc;
+    HB_CUDA(cudaEventRecord(q->ev_join, q->side));
+  }
   // a second side stream for the small kernels, so that the target network's GEMMs are all `side` runs
   HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fork, 0));
   // importance weights (a caller that computed them with the sample -- hb_rb_sample_gather into
@@ -1252,11 +1449,24 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     if ((rc = adam_tick(q, opts->lr, opts->b1, opts->b2, opts->eps, opts->grad_scale, dyn, q->side2))) return rc;
     HB_CUDA(cudaEventRecord(q->ev_tick, q->side2));
   }
+  if (chained) {
+    // transposed hidden activations of the sampled rows (B operand of the weight-gradient GEMMs), beside
+    // the loss; ev_wt orders them before every gradient GEMM
+    HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fwd, 0));
+    for (int l = 0; l + 1 < nl; ++l) {
+      const int N = q->tab.l[l].N;
+      transpose_act_kernel<<<dim3((N + 31) / 32, (B + 31) / 32), 256, 0, q->side2>>>(q->h[l], N, B, N, q->ht[l],
+                                                                                    2 * Bp);
+      HB_CUDA(cudaGetLastError());
+    }
+  }
   HB_CUDA(cudaEventRecord(q->ev_wt, q->side2));
   // 2. online network on both observation sets (main stream)
-  if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
-                    fused ? q->xb : nullptr, pdl))) return rc;
-  HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  if (!chained) {
+    if ((rc = forward(q, q->w16, q->beff, q->x, 2 * B, q->h, q->ht, 2 * Bp, q->logits, q->q_on, ldq, s,
+                      fused ? q->xb : nullptr, pdl))) return rc;
+    HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
+  }
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_join2, 0));
   // 4. loss and dL/dlogits (scaled by B; 1/B is folded into the dW / db epilogues)
   {

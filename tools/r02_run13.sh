@@ -1,5 +1,3 @@
-for b in 0 1; do for c in 8 32; do
-echo "== HB_BIAS0_MAIN=$b CUDA_DEVICE_MAX_CONNECTIONS=$c"
-CUDA_DEVICE_MAX_CONNECTIONS=$c HB_BIAS0_MAIN=$b timeout 300 python tools/learner_probe.py 2>&1 | grep -E "device events|hb_learner_step"
-done; done
-HB_BIAS0_MAIN=1 timeout 300 python tools/learner_trace.py 2>&1 | tail -14
+HB_CHAIN_TRACE=1 timeout 600 python -m pytest tests/test_qnet_gpu.py -m gpu -x -q -s -k "learner_step_parity" 2>&1 | grep -E "chain job|expand|c51|passed|failed" | head -12
+timeout 600 python -m pytest tests/test_qnet_gpu.py tests/test_rainbow_gpu.py tests/test_agent_gpu.py -m gpu -x -q 2>&1 | tail -3
+timeout 300 python tools/learner_probe.py 2>&1 | grep -E "device events|hb_learner_step"

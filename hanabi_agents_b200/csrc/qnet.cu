@@ -360,15 +360,32 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
                                 const float* __restrict__ w_is, int B, int A, int n_atoms, float vmax,
                                 float gamma, const float* __restrict__ dyn, __half* __restrict__ dz,
                                 __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b,
-                                HeadBackward hb) {
+                                HeadBackward hb, int early) {
   extern __shared__ __align__(128) unsigned char hb_smem[];
   tc::pdl_launch_dependents();
-  tc::pdl_wait();
-  if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int b = HEAD_BW ? (int)blockIdx.x : (int)(blockIdx.x * (blockDim.x >> 5)) + warp;
+  // early != 0: the launch in front of this one released its dependents only after ITS dependencies were
+  // complete (tc_chain.cuh), so the sampled actions are visible here, in front of the wait, and the weight
+  // rows (written by the previous update) can be on their way while the forward pass still runs
+  int a = 0;
+  if (HEAD_BW && early && b < B) {
+    a = a_tm1[b];
+    if (threadIdx.x == 32) {
+      const uint32_t bytes = (uint32_t)n_atoms * (uint32_t)hb.K * 2u;
+      uint64_t* bar = reinterpret_cast<uint64_t*>(hb_smem + ((bytes + 127u) & ~127u) + 64 * 4);
+      tc::mbar_init(bar, 1);
+      tc::fence_barrier_init();
+      tc::mbar_expect_tx(bar, bytes);
+      const __half* src = hb.w + (size_t)a * 64 * hb.K;
+      asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                   :: "r"(tc::smem_u32(hb_smem)), "l"(src), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
+    }
+  }
+  tc::pdl_wait();
+  if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
   if (b >= B) return;
-  const int a = a_tm1[b];
+  if (!(HEAD_BW && early)) a = a_tm1[b];
   __half h0, h1;
   if constexpr (!HEAD_BW) {
     c51_row(b, lane, logits_tm1, q_sel, ldq, legal_t, legal_words, tlogits, ldl, a, r_t, term_t, mask_terminal,
@@ -378,7 +395,7 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
     const __half* wsm = reinterpret_cast<const __half*>(hb_smem);
     float* gsm = reinterpret_cast<float*>(hb_smem + ((bytes + 127u) & ~127u));
     uint64_t* bar = reinterpret_cast<uint64_t*>(gsm + 64);
-    if (threadIdx.x == 32) {                     // warp 1: warp 0 goes straight to the loss
+    if (threadIdx.x == 32 && !early) {           // warp 1: warp 0 goes straight to the loss
       tc::mbar_init(bar, 1);
       tc::fence_barrier_init();
       tc::mbar_expect_tx(bar, bytes);
@@ -1504,12 +1521,12 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
         HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<true>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
                                    tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
                                    q->n_atoms, q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp,
-                                   q->loss_b, hbw));
+                                   q->loss_b, hbw, (chained && pdl) ? 1 : 0));
       } else {
         HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<false>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
                                    tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
                                    q->n_atoms, q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp,
-                                   q->loss_b, hbw));
+                                   q->loss_b, hbw, 0));
       }
     } else {
       cfg.gridDim = dim3((B + 127) / 128);

@@ -186,19 +186,25 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  pdl_launch_dependents();
+  // The weights do not depend on the launch in front of this one (they were written by the previous
+  // update): the first ring-full of B tiles is requested before the wait, while the sample kernel runs.
+  const int pre = num_kb < kSt ? num_kb : kSt;
+  if (warp == 0 && lane == 0) {
+    for (int kb = 0; kb < pre; ++kb) {
+      uint8_t* b_dst = smem + kb * kStB + BM * BK * 2;
+      mbar_expect_tx(&full_bar[kb], abits ? (uint32_t)job.bn * BK * 2 : stage_bytes);
+      tma_load_2d(b_dst, &job.tb, &full_bar[kb], kb * BK, n0);
+    }
+  }
+  // dependents are released only once this grid's own dependencies are complete: what the kernel in front
+  // of this one wrote (the sampled actions, rewards, weights) is then visible to the next kernel's
+  // prologue too, which starts its own loads there (c51_loss_kernel)
   pdl_wait();
+  pdl_launch_dependents();
 
   if (warp == 0) {
     if (lane == 0) {
       HB_CHAIN_STAMP(0);                                    // dependencies of the launch are complete
-      // weights first: they do not depend on the previous layer
-      const int pre = job.dep >= 0 ? (num_kb < kSt ? num_kb : kSt) : 0;
-      for (int kb = 0; kb < pre; ++kb) {
-        uint8_t* b_dst = smem + kb * kStB + BM * BK * 2;
-        mbar_expect_tx(&full_bar[kb], stage_bytes);
-        tma_load_2d(b_dst, &job.tb, &full_bar[kb], kb * BK, n0);
-      }
       if (job.dep >= 0) {
         const unsigned int launches = *reinterpret_cast<volatile const unsigned int*>(p.state);
         const unsigned int target = (launches + 1u) * (unsigned int)job.dep_arrivals;
@@ -210,8 +216,9 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
         fence_proxy_async_all();                           // the rows were written by other CTAs; read by TMA
       }
       HB_CHAIN_STAMP(1);                                    // input rows complete
-      for (int kb = 0; kb < pre; ++kb)
-        tma_load_2d(smem + kb * kStB, &job.ta, &full_bar[kb], kb * BK, m0);
+      if (!abits)
+        for (int kb = 0; kb < pre; ++kb)
+          tma_load_2d(smem + kb * kStB, &job.ta, &full_bar[kb], kb * BK, m0);
       for (int kb = pre; kb < num_kb; ++kb) {
         const int s = kb % kSt;
         const uint32_t ph = (kb / kSt) & 1;
@@ -276,6 +283,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
 #pragma unroll
         for (int rr = 0; rr < 2; ++rr) {
           const int r = pr + 64 * rr;
+          // (a 256-entry table of chunks in shared memory was tried instead of the arithmetic: twice as slow)
 #pragma unroll
           for (int c = 0; c < 8; ++c) {
             const uint32_t byte = ((c < 4 ? w[rr].x : w[rr].y) >> (8 * (c & 3))) & 0xffu;

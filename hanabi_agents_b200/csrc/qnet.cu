@@ -50,7 +50,7 @@ struct hb_qnet {
   float* master = nullptr;             // [kinds][n_eff]
   float* tmaster = nullptr;            // masters of the target snapshot (save_weights)
   float* eps = nullptr;                // [n_eff] noise constants (noisy)
-  float* adam_m = nullptr;             // [kinds][n_eff]
+  float* adam_m = nullptr;             // [kinds == 3 ? 2 : 1][n_eff]: kinds 0 and 1 share their moments
   float* adam_v = nullptr;
   float* grad = nullptr;               // [n_eff] flat gradient bucket
   __half* w16 = nullptr;               // online effective weights [N, K] per layer
@@ -249,6 +249,7 @@ struct HeadBackward {
   const __half* gate;       // previous layer's activations [B.., K] (ReLU backward)
   __half* dz_prev;          // [B, K]
   __half* dzt_prev;         // [K, ld_dzt]
+  unsigned long long* trace;  // debugging (HB_LOSS_TRACE): 8 globaltimer stamps per sample, or nullptr
 };
 constexpr int kHeadBwSmemMax = 112 * 1024;     // rows of one action (n_atoms x K halves) staged per sample
 
@@ -344,6 +345,117 @@ __device__ __forceinline__ void c51_row(int b, int lane, const float* __restrict
   }
 }
 
+// The same row program spread over the four warps of a CTA (HEAD_BW): as one warp it was a 7.5 us chain of
+// dependent loads, shuffle reductions and a 51-step projection loop (profiles/r02_loss_trace_*.txt).
+//   warp 0: argmax -> target logits -> softmax p          warp 1: log-softmax of the online logits
+//   all:    a quarter of the projection's 51 terms each   warp 0: the sums, loss and dL/dlogits
+// The arithmetic and the order of every sum over atoms are c51_row's, except that m_i is accumulated in
+// four partial sums (j = 0..12, 13..25, 26..38, 39..50) added in that order.
+struct C51Shared {
+  float p[64], soft[64], logp[64], pm[4][64];
+};
+__device__ __forceinline__ void c51_row_cta(C51Shared& sh, int b, int warp, int lane,
+                                            const float* __restrict__ logits_tm1,
+                                            const float* __restrict__ q_sel, int ldq,
+                                            const uint32_t* __restrict__ legal_t, int legal_words,
+                                            const float* __restrict__ tlogits, int ldl, int a,
+                                            const float* __restrict__ r_t, const uint8_t* __restrict__ term_t,
+                                            int mask_terminal, const float* __restrict__ w_is, int A, int n_atoms,
+                                            float vmax, float gamma, __half* __restrict__ dz,
+                                            __half* __restrict__ dzt, int ld_dzt, float* __restrict__ loss_b,
+                                            float* __restrict__ gsm) {
+  const unsigned full = 0xffffffffu;
+  const float vmin = -vmax, dzv = 2.0f * vmax / (float)(n_atoms - 1);
+  const int i0 = lane, i1 = lane + 32;
+  const float r = r_t[b];
+  const bool terminal = mask_terminal && term_t != nullptr && term_t[b];
+  if (warp == 0) {
+    float best = -INFINITY;
+    int besta = 0x7fffffff;
+    for (int aa = lane; aa < A; aa += 32) {
+      float v = q_sel[(long long)b * ldq + aa];
+      if (legal_t != nullptr && !((legal_t[(long long)b * legal_words + (aa >> 5)] >> (aa & 31)) & 1u)) v = -INFINITY;
+      if (v > best) { best = v; besta = aa; }
+    }
+    for (int o = 16; o; o >>= 1) {
+      const float ov = __shfl_xor_sync(full, best, o);
+      const int oa = __shfl_xor_sync(full, besta, o);
+      if (ov > best || (ov == best && oa < besta)) { best = ov; besta = oa; }
+    }
+    const int astar = besta == 0x7fffffff ? 0 : besta;
+    const float* tl = tlogits + (long long)b * ldl + astar * 64;
+    const float t0 = i0 < n_atoms ? tl[i0] : -INFINITY, t1 = i1 < n_atoms ? tl[i1] : -INFINITY;
+    float mx = fmaxf(t0, t1);
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(full, mx, o));
+    const float e0 = i0 < n_atoms ? expf(t0 - mx) : 0.f, e1 = i1 < n_atoms ? expf(t1 - mx) : 0.f;
+    float den = e0 + e1;
+    for (int o = 16; o; o >>= 1) den += __shfl_xor_sync(full, den, o);
+    sh.p[i0] = e0 / den;
+    sh.p[i1] = e1 / den;
+  } else if (warp == 1) {
+    const float* ol = logits_tm1 + (long long)b * ldl + a * 64;
+    const float l0 = i0 < n_atoms ? ol[i0] : -INFINITY, l1 = i1 < n_atoms ? ol[i1] : -INFINITY;
+    float lmx = fmaxf(l0, l1);
+    for (int o = 16; o; o >>= 1) lmx = fmaxf(lmx, __shfl_xor_sync(full, lmx, o));
+    const float f0 = i0 < n_atoms ? expf(l0 - lmx) : 0.f, f1 = i1 < n_atoms ? expf(l1 - lmx) : 0.f;
+    float lden = f0 + f1;
+    for (int o = 16; o; o >>= 1) lden += __shfl_xor_sync(full, lden, o);
+    const float lse = lmx + logf(lden);
+    sh.soft[i0] = f0 / lden;
+    sh.soft[i1] = f1 / lden;
+    sh.logp[i0] = i0 < n_atoms ? l0 - lse : 0.f;
+    sh.logp[i1] = i1 < n_atoms ? l1 - lse : 0.f;
+  }
+  __syncthreads();
+  {
+    // projection onto the fixed support: m_i = sum_j clip(1 - |clip(tz_j) - z_i| / dz, 0, 1) p_j
+    const float g = terminal ? 0.f : gamma;
+    const float zi0 = vmin + dzv * (float)i0, zi1 = vmin + dzv * (float)i1;
+    const float inv_dz = 1.0f / dzv;
+    const int q4 = (n_atoms + 3) >> 2;
+    const int j0 = warp * q4, j1 = (j0 + q4 < n_atoms) ? j0 + q4 : n_atoms;
+    float m0 = 0.f, m1 = 0.f;
+#pragma unroll 4
+    for (int j = j0; j < j1; ++j) {
+      const float pj = sh.p[j];
+      float tz = r + g * (vmin + dzv * (float)j);
+      tz = fminf(fmaxf(tz, vmin), vmax);
+      m0 += fminf(fmaxf(1.0f - fabsf(tz - zi0) * inv_dz, 0.f), 1.f) * pj;
+      m1 += fminf(fmaxf(1.0f - fabsf(tz - zi1) * inv_dz, 0.f), 1.f) * pj;
+    }
+    sh.pm[warp][i0] = m0;
+    sh.pm[warp][i1] = m1;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    float m0 = ((sh.pm[0][i0] + sh.pm[1][i0]) + sh.pm[2][i0]) + sh.pm[3][i0];
+    float m1 = ((sh.pm[0][i1] + sh.pm[1][i1]) + sh.pm[2][i1]) + sh.pm[3][i1];
+    if (i0 >= n_atoms) m0 = 0.f;
+    if (i1 >= n_atoms) m1 = 0.f;
+    float part = m0 * sh.logp[i0] + m1 * sh.logp[i1];
+    float S = m0 + m1;
+    for (int o = 16; o; o >>= 1) {
+      part += __shfl_xor_sync(full, part, o);
+      S += __shfl_xor_sync(full, S, o);
+    }
+    if (lane == 0) loss_b[b] = -part;
+    const float w = w_is[b];
+    const float d0 = w * (sh.soft[i0] * S - m0), d1 = w * (sh.soft[i1] * S - m1);
+    const __half h0 = __float2half_rn(i0 < n_atoms ? d0 : 0.f), h1 = __float2half_rn(i1 < n_atoms ? d1 : 0.f);
+    const long long col = (long long)a * 64;
+    if (i0 < n_atoms) {
+      dz[(long long)b * ldl + col + i0] = h0;
+      dzt[(col + i0) * ld_dzt + b] = h0;
+    }
+    if (i1 < n_atoms) {
+      dz[(long long)b * ldl + col + i1] = h1;
+      dzt[(col + i1) * ld_dzt + b] = h1;
+    }
+    gsm[i0] = __half2float(h0);
+    gsm[i1] = __half2float(h1);
+  }
+}
+
 // HEAD_BW == false: one warp per sample (grid = ceil(B / warps per CTA)).
 // HEAD_BW == true: one CTA per sample that also computes the previous layer's dZ row.  dL/dlogits of a
 // sample is n_atoms values of ONE action, so that row is n_atoms consecutive rows of the head's effective
@@ -382,7 +494,10 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
                    :: "r"(tc::smem_u32(hb_smem)), "l"(src), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
     }
   }
+#define HB_LOSS_STAMP(k) do { if (HEAD_BW && hb.trace != nullptr && (threadIdx.x & 31) == 0) \
+    hb.trace[(size_t)blockIdx.x * 8 + (k)] = tc::globaltimer_ns(); } while (0)
   tc::pdl_wait();
+  if (threadIdx.x == 0) HB_LOSS_STAMP(0);
   if (dyn != nullptr) gamma = dyn[1];            // the step's discount, staged by the sample kernel
   if (b >= B) return;
   if (!(HEAD_BW && early)) a = a_tm1[b];
@@ -403,14 +518,13 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
       asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                    :: "r"(tc::smem_u32(hb_smem)), "l"(src), "r"(bytes), "r"(tc::smem_u32(bar)) : "memory");
     }
-    if (warp == 0) {
-      c51_row(b, lane, logits_tm1, q_sel, ldq, legal_t, legal_words, tlogits, ldl, a, r_t, term_t, mask_terminal,
-              w_is, A, n_atoms, vmax, gamma, dz, dzt, ld_dzt, loss_b, h0, h1);
-      gsm[lane] = __half2float(h0);
-      gsm[lane + 32] = __half2float(h1);
-    }
+    __shared__ C51Shared c51sh;
+    c51_row_cta(c51sh, b, warp, lane, logits_tm1, q_sel, ldq, legal_t, legal_words, tlogits, ldl, a, r_t, term_t,
+                mask_terminal, w_is, A, n_atoms, vmax, gamma, dz, dzt, ld_dzt, loss_b, gsm);
+    if (warp == 0) HB_LOSS_STAMP(1);
     __syncthreads();
     tc::mbar_wait(bar, 0);
+    if (threadIdx.x == 0) HB_LOSS_STAMP(2);
     for (int k4 = threadIdx.x; k4 < (hb.K >> 2); k4 += blockDim.x) {
       float acc[4] = {0.f, 0.f, 0.f, 0.f};
       const __half* col = wsm + 4 * k4;
@@ -442,6 +556,8 @@ __global__ void c51_loss_kernel(const float* __restrict__ logits_tm1, const floa
       hb.dzt_prev[(size_t)(4 * k4 + 2) * ld_dzt + b] = __low2half(o1);
       hb.dzt_prev[(size_t)(4 * k4 + 3) * ld_dzt + b] = __high2half(o1);
     }
+    if (threadIdx.x == 0) HB_LOSS_STAMP(3);
+#undef HB_LOSS_STAMP
   }
 }
 
@@ -547,36 +663,56 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, long long i
       const float4 t = *reinterpret_cast<const float4*>(grad + i);
       gr4[0] = t.x; gr4[1] = t.y; gr4[2] = t.z; gr4[3] = t.w;
     }
-    float eff[4] = {0.f, 0.f, 0.f, 0.f};
+    // NoisyLinear's plain weight and its w_mu (kinds 0 and 1) enter the output as a sum (noisy_mlp.py:62,80):
+    // their gradients are the same number, and from optix.adam's zero state so are their moments and their
+    // steps.  One moment pair serves both (state slot 0; w_sigma's is slot 1): 16 of the 82 bytes this
+    // kernel moved per parameter.
+    constexpr int STATES = KINDS == 3 ? 2 : 1;
+    float p[KINDS][4];
 #pragma unroll
     for (int k = 0; k < KINDS; ++k) {
-      float4 pv = *reinterpret_cast<const float4*>(master + k * n_eff + i);
-      float p[4] = {pv.x, pv.y, pv.z, pv.w};
-      if (do_update) {
-        const float4 mv = *reinterpret_cast<const float4*>(am + k * n_eff + i);
-        const float4 vv = *reinterpret_cast<const float4*>(av + k * n_eff + i);
+      const float4 pv = *reinterpret_cast<const float4*>(master + k * n_eff + i);
+      p[k][0] = pv.x; p[k][1] = pv.y; p[k][2] = pv.z; p[k][3] = pv.w;
+    }
+    if (do_update) {
+#pragma unroll
+      for (int st = 0; st < STATES; ++st) {
+        const float4 mv = *reinterpret_cast<const float4*>(am + st * n_eff + i);
+        const float4 vv = *reinterpret_cast<const float4*>(av + st * n_eff + i);
         float m[4] = {mv.x, mv.y, mv.z, mv.w}, v[4] = {vv.x, vv.y, vv.z, vv.w};
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float gr = gr4[j] * grad_scale * (k == 2 ? noise[j] : 1.0f);
+          const float gr = gr4[j] * grad_scale * (st == 1 ? noise[j] : 1.0f);
           m[j] = b1 * m[j] + (1.0f - b1) * gr;
           v[j] = b2 * v[j] + (1.0f - b2) * gr * gr;
+          float step;
           if (tf_style) {
             // tf.train.AdamOptimizer (rainbow_agent.py:228-230): lr_t = lr sqrt(1-b2^t)/(1-b1^t),
             // theta -= lr_t m / (sqrt(v) + eps) -- eps is NOT bias corrected
-            p[j] = p[j] - lr_tf * m[j] / (sqrtf(v[j]) + eps);
+            step = lr_tf * m[j] / (sqrtf(v[j]) + eps);
           } else {
             const float mhat = m[j] * r1, vhat = v[j] * r2;
-            p[j] = p[j] - lr * mhat / (sqrtf(vhat) + eps);
+            step = lr * mhat / (sqrtf(vhat) + eps);
+          }
+          if (st == 0) {
+            p[0][j] = p[0][j] - step;
+            if (KINDS == 3) p[1][j] = p[1][j] - step;
+          } else {
+            p[KINDS - 1][j] = p[KINDS - 1][j] - step;
           }
         }
-        *reinterpret_cast<float4*>(am + k * n_eff + i) = make_float4(m[0], m[1], m[2], m[3]);
-        *reinterpret_cast<float4*>(av + k * n_eff + i) = make_float4(v[0], v[1], v[2], v[3]);
-        *reinterpret_cast<float4*>(master + k * n_eff + i) = make_float4(p[0], p[1], p[2], p[3]);
+        *reinterpret_cast<float4*>(am + st * n_eff + i) = make_float4(m[0], m[1], m[2], m[3]);
+        *reinterpret_cast<float4*>(av + st * n_eff + i) = make_float4(v[0], v[1], v[2], v[3]);
       }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) eff[j] += (k == 2) ? p[j] * noise[j] : p[j];
+      for (int k = 0; k < KINDS; ++k)
+        *reinterpret_cast<float4*>(master + k * n_eff + i) = make_float4(p[k][0], p[k][1], p[k][2], p[k][3]);
     }
+    float eff[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int k = 0; k < KINDS; ++k)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) eff[j] += (k == 2) ? p[k][j] * noise[j] : p[k][j];
     if (loc < (long long)g.N * g.K) {   // transposes: transpose16_kernel (coalesced)
       const __half2 h0 = __floats2half2_rn(eff[0], eff[1]), h1 = __floats2half2_rn(eff[2], eff[3]);
       uint2 o;
@@ -1133,8 +1269,8 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   if (!rc) rc = dev_alloc(&q->master, (size_t)q->kinds * q->n_eff);
   if (!rc) rc = dev_alloc(&q->tmaster, (size_t)q->kinds * q->n_eff);
   if (!rc && noisy) rc = dev_alloc(&q->eps, (size_t)q->n_eff);
-  if (!rc) rc = dev_alloc(&q->adam_m, (size_t)q->kinds * q->n_eff);
-  if (!rc) rc = dev_alloc(&q->adam_v, (size_t)q->kinds * q->n_eff);
+  if (!rc) rc = dev_alloc(&q->adam_m, (size_t)(q->kinds == 3 ? 2 : 1) * q->n_eff);
+  if (!rc) rc = dev_alloc(&q->adam_v, (size_t)(q->kinds == 3 ? 2 : 1) * q->n_eff);
   if (!rc) rc = dev_alloc(&q->grad, (size_t)q->n_eff);
   if (!rc) rc = dev_alloc(&q->w16, (size_t)q->n_w);
   if (!rc) rc = dev_alloc(&q->w16t, (size_t)q->n_w);
@@ -1518,10 +1654,35 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                                        kHeadBwSmemMax + 1024));
           attr_set[q->device & 63] = true;
         }
+        static const bool ltrace = getenv("HB_LOSS_TRACE") && atoi(getenv("HB_LOSS_TRACE")) != 0;
+        static unsigned long long* d_ltrace = nullptr;
+        cudaStreamCaptureStatus lcap = cudaStreamCaptureStatusNone;
+        if (ltrace) cudaStreamIsCapturing(s, &lcap);
+        if (ltrace && lcap == cudaStreamCaptureStatusNone) {
+          if (d_ltrace == nullptr) HB_CUDA(cudaMalloc(&d_ltrace, 4096 * 8 * 8));
+          HB_CUDA(cudaMemsetAsync(d_ltrace, 0, 4096 * 8 * 8, s));
+          if (B <= 4096) hbw.trace = d_ltrace;
+        }
         HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<true>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
                                    tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
                                    q->n_atoms, q->vmax, discount, dyn, q->dz[nl - 1], q->dzt[nl - 1], Bp,
                                    q->loss_b, hbw, (chained && pdl) ? 1 : 0));
+        if (hbw.trace != nullptr) {
+          std::vector<unsigned long long> h((size_t)B * 8);
+          HB_CUDA(cudaStreamSynchronize(s));
+          HB_CUDA(cudaMemcpy(h.data(), d_ltrace, (size_t)B * 8 * 8, cudaMemcpyDeviceToHost));
+          unsigned long long t0 = ~0ull;
+          for (int c = 0; c < B; ++c) if (h[c * 8] && h[c * 8] < t0) t0 = h[c * 8];
+          double mx[4] = {0, 0, 0, 0}, mn[4] = {1e30, 1e30, 1e30, 1e30};
+          for (int c = 0; c < B; ++c)
+            for (int k = 0; k < 4; ++k) {
+              const double v = ((double)h[c * 8 + k] - (double)t0) * 1e-3;
+              if (v > mx[k]) mx[k] = v;
+              if (v < mn[k]) mn[k] = v;
+            }
+          fprintf(stderr, "c51 loss (%d samples): wait over %.1f-%.1f | row done %.1f-%.1f | weights in %.1f-%.1f | "
+                  "dZ row stored %.1f-%.1f us\n", B, mn[0], mx[0], mn[1], mx[1], mn[2], mx[2], mn[3], mx[3]);
+        }
       } else {
         HB_CUDA(cudaLaunchKernelEx(&cfg, c51_loss_kernel<false>, logits, qs, ldq, legal_t, (q->A + 31) / 32,
                                    tlogits, LL.N, d_a_tm1, d_r_t, d_term_t, mask_terminal, w_is, B, q->A,
@@ -1570,6 +1731,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
     ep.pdl = on_main ? pdl : 0;
+    ep.b_early = ep.pdl;           // the transposed layer input was complete before the dZ GEMM could start
     if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
     // (the first layer's bias gradient on the high-priority side stream, idle since the target network's
     // forward pass: on side2 it queued behind the other layers' Adam CTAs and held the last update up)
@@ -1613,6 +1775,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       eb.out16_t = q->dzt[l - 1];
       eb.ld_out_t = Bp;
       eb.pdl = pdl;
+      eb.b_early = pdl;            // the transposed weights (ev_wt) are a full dependency of this launch
       if ((rc = tc::gemm<tc::EPI_F16>(q->dz[l], L.N, q->w16t + L.woff, L.N, B, L.K, L.N, eb, s))) return rc;
     }
   }

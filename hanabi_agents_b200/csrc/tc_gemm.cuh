@@ -74,6 +74,9 @@ struct EpiParams {
   // (barrier init, TMEM allocation, tensor-map prefetch) may run while the previous kernel of the
   // stream is still finishing; every global access sits behind griddepcontrol.wait
   int pdl;
+  // the B operand does not depend on the kernel this launch waits for (it was complete before that kernel
+  // could start): the first ring-full of B tiles is requested in front of griddepcontrol.wait
+  int b_early;
 };
 
 // Programmatic dependent launch (PDL).  wait: returns once every grid this one depends on has
@@ -489,6 +492,14 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
   // everything above touched no global memory; the operands may still be in the making
   pdl_launch_dependents();
+  const int early = (ep.b_early && (int)blockIdx.x < total) ? (num_kb < kSt ? num_kb : kSt) : 0;
+  if (warp == 0 && lane == 0) {
+    const int n0 = ((int)blockIdx.x % tiles_n) * BN_;
+    for (int kb = 0; kb < early; ++kb) {             // first tile's first k-blocks: B now, A behind the wait
+      mbar_expect_tx(&full_bar[kb], ABITS ? BN_ * BK * 2 : kStB);
+      tma_load_2d(smem + kb * kStB + BM * BK * 2, &tmap_b, &full_bar[kb], kb * BK, n0);
+    }
+  }
   pdl_wait();
 
   if (warp == 0) {
@@ -499,9 +510,13 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         for (int kb = 0; kb < num_kb; ++kb, ++it) {
           const int s = it % kSt;
           const uint32_t ph = (it / kSt) & 1;
-          mbar_wait(&empty_bar[s], ph ^ 1);          // slot free (first pass: returns at once)
           uint8_t* a_dst = smem + s * kStB;
           uint8_t* b_dst = a_dst + BM * BK * 2;
+          if (it < early) {                          // B is on its way already
+            if (!ABITS) tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
+            continue;
+          }
+          mbar_wait(&empty_bar[s], ph ^ 1);          // slot free (first pass: returns at once)
           if (ABITS) {
             mbar_expect_tx(&full_bar[s], BN_ * BK * 2);
           } else {

@@ -1,3 +1,3 @@
-HB_CHAIN_TRACE=1 timeout 600 python -m pytest tests/test_qnet_gpu.py -m gpu -x -q -s -k "learner_step_parity" 2>&1 | grep -E "chain job|expand|passed|failed" | head -9 | cut -c1-220
 timeout 600 python -m pytest tests/test_qnet_gpu.py tests/test_rainbow_gpu.py tests/test_agent_gpu.py tests/test_session_gpu.py -m gpu -x -q 2>&1 | tail -3
-timeout 300 python tools/learner_probe.py 2>&1 | grep -E "device events|hb_learner_step"
+timeout 300 python tools/learner_probe.py 2>&1 | grep -E "device events|hb_learner_step|phase"
+timeout 300 python tools/learner_trace.py 2>&1 | tail -24

@@ -1540,6 +1540,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   static const bool l_main = !(getenv("HB_DW0_OWN_STREAM") && atoi(getenv("HB_DW0_OWN_STREAM")) != 0);
   static const int adam_ctas = getenv("HB_ADAM_CTAS_PER_SM") ? atoi(getenv("HB_ADAM_CTAS_PER_SM")) : 0;
   static const bool bias0_main = getenv("HB_BIAS0_MAIN") && atoi(getenv("HB_BIAS0_MAIN")) != 0;
+  static const bool dz0_plain = getenv("HB_DZ0_PLAIN") && atoi(getenv("HB_DZ0_PLAIN")) != 0;
   static const bool dense_head_bw = getenv("HB_DENSE_HEAD_BW") && atoi(getenv("HB_DENSE_HEAD_BW")) != 0;
   const bool head_bw = q->n_atoms > 1 && q->n_atoms <= 64 && nl >= 2 && LL.K % 8 == 0 &&
                        (size_t)q->n_atoms * LL.K * 2 <= (size_t)kHeadBwSmemMax && !dense_head_bw;
@@ -1764,7 +1765,21 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       if ((rc = adam_range(q, 1, e0 / 4, e1 / 4, ls, 0, on_main ? 0 : adam_ctas))) return rc;
     }
     HB_CUDA(cudaEventRecord(q->ev_layer[l], ls));
-    if (l > 0 && !(l == nl - 1 && head_bw)) {
+    if (l == 1 && !(l == nl - 1 && head_bw) && per_layer && l_main && !dz0_plain) {
+      // The last product of the chain, dZ_0, is only ever read transposed (first layer's weight and bias
+      // gradients): computed as dZ_0^T [K, B] = W_1^T [K, N] . dZ_1^T, operands swapped, it leaves through
+      // the tile's bulk tensor store instead of 2-byte scattered stores (2 us of the critical path).
+      // The ReLU gate is read transposed too: ht[0] [K, 2Bp] (complete before ev_wt).
+      tc::EpiParams eb{};
+      eb.alpha = 1.f;
+      eb.gate = q->ht[0];
+      eb.ld_gate = 2 * Bp;
+      eb.out16 = q->dzt[0];
+      eb.ld_out = Bp;
+      eb.pdl = pdl;
+      eb.a_early = pdl;            // the transposed weights (ev_wt) are a full dependency of this launch
+      if ((rc = tc::gemm<tc::EPI_F16>(q->w16t + L.woff, L.N, q->dz[1], L.N, L.K, B, L.N, eb, s))) return rc;
+    } else if (l > 0 && !(l == nl - 1 && head_bw)) {
       // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
       tc::EpiParams eb{};
       eb.alpha = 1.f;

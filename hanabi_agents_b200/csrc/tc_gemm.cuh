@@ -77,6 +77,7 @@ struct EpiParams {
   // the B operand does not depend on the kernel this launch waits for (it was complete before that kernel
   // could start): the first ring-full of B tiles is requested in front of griddepcontrol.wait
   int b_early;
+  int a_early;               // the same for the A operand (not both)
 };
 
 // Programmatic dependent launch (PDL).  wait: returns once every grid this one depends on has
@@ -492,12 +493,14 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
   const uint32_t tmem_base = *tmem_slot;
   // everything above touched no global memory; the operands may still be in the making
   pdl_launch_dependents();
-  const int early = (ep.b_early && (int)blockIdx.x < total) ? (num_kb < kSt ? num_kb : kSt) : 0;
+  const bool a_first = !ABITS && ep.a_early && !ep.b_early;
+  const int early = ((ep.b_early || a_first) && (int)blockIdx.x < total) ? (num_kb < kSt ? num_kb : kSt) : 0;
   if (warp == 0 && lane == 0) {
-    const int n0 = ((int)blockIdx.x % tiles_n) * BN_;
-    for (int kb = 0; kb < early; ++kb) {             // first tile's first k-blocks: B now, A behind the wait
-      mbar_expect_tx(&full_bar[kb], ABITS ? BN_ * BK * 2 : kStB);
-      tma_load_2d(smem + kb * kStB + BM * BK * 2, &tmap_b, &full_bar[kb], kb * BK, n0);
+    const int m0 = ((int)blockIdx.x / tiles_n) * BM, n0 = ((int)blockIdx.x % tiles_n) * BN_;
+    for (int kb = 0; kb < early; ++kb) {             // first tile's first k-blocks: one operand now,
+      mbar_expect_tx(&full_bar[kb], ABITS ? BN_ * BK * 2 : kStB);   // the other behind the wait
+      if (a_first) tma_load_2d(smem + kb * kStB, &tmap_a, &full_bar[kb], kb * BK, m0);
+      else tma_load_2d(smem + kb * kStB + BM * BK * 2, &tmap_b, &full_bar[kb], kb * BK, n0);
     }
   }
   pdl_wait();
@@ -512,8 +515,9 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
           const uint32_t ph = (it / kSt) & 1;
           uint8_t* a_dst = smem + s * kStB;
           uint8_t* b_dst = a_dst + BM * BK * 2;
-          if (it < early) {                          // B is on its way already
-            if (!ABITS) tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
+          if (it < early) {                          // one operand is on its way already
+            if (a_first) tma_load_2d(b_dst, &tmap_b, &full_bar[s], kb * BK, n0);
+            else if (!ABITS) tma_load_2d(a_dst, &tmap_a, &full_bar[s], kb * BK, m0);
             continue;
           }
           mbar_wait(&empty_bar[s], ph ^ 1);          // slot free (first pass: returns at once)

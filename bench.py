@@ -407,8 +407,7 @@ def bench_session(n, world, rank, args):
 
     def learn_tick():
         ses.step(train=True)
-        for a in agents:
-            a.update()
+        ses.update_learners()        # one update per agent (side by side in a single-process job)
 
     k = args.session_ticks
     ev = timed(lambda: ses.step(train=False), k)

@@ -88,6 +88,8 @@ SIGNATURES = {
     "hb_rb_add": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
     "hb_rb_store_first": (i32, [vp, vp, vp, vp, i64, vp]),
     "hb_rb_add_masked": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), vp]),
+    "hb_rb_add_masked_begin": (i32, [vp, vp, i64, vp]),
+    "hb_rb_add_masked_finish": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), vp]),
     "hb_rb_gather": (i32, [vp, vp, i64, vp, vp, vp, vp, vp, vp, vp]),
     "hb_rb_check": (i32, [vp, vp]),
     "hb_rb_sample": (i32, [vp, vp, i64, vp, vp, vp, vp]),
@@ -108,6 +110,7 @@ SIGNATURES = {
     "hb_net_get_target_param": (i32, [vp, i32, i32, vp, i64]),
     "hb_net_refresh": (i32, [vp, vp]),
     "hb_net_sync_target": (i32, [vp, vp]),
+    "hb_net_set_act_reserve": (i32, [vp, i32]),
     "hb_net_act": (i32, [vp, vp, vp, i32, i64, i32, f32, vp, u64, u64, i64, i32, vp, vp, vp]),
     "hb_net_forward": (i32, [vp, vp, i64, i32, vp, vp, vp]),
     "hb_net_grads": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, f32, i32, vp, vp, vp]),
@@ -190,9 +193,20 @@ def check(rc):
     raise HanabiB200Error("hanabi_b200 error %d: %s" % (rc, msg))
 
 
+_raw_stream = None
+
+
 def current_stream_ptr():
-    """cudaStream_t of torch's current stream (torch is used for hand-off only)."""
+    """cudaStream_t of torch's current stream (torch is used for hand-off only).  Through torch's raw
+    accessor when it has one: `torch.cuda.current_stream()` builds a Stream object and resolves the
+    device by name every time, ~5 us a call and ten calls per session tick."""
+    global _raw_stream
     import torch
+    if _raw_stream is None:
+        fn = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+        _raw_stream = fn if fn is not None else False
+    if _raw_stream:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 

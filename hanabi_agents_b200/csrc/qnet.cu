@@ -90,6 +90,7 @@ struct hb_qnet {
   float* w_is = nullptr;               // [B]
   float* loss_b = nullptr;             // [B] per-sample loss / td
   float* scalars = nullptr;            // [4]: mean loss, max weight, ...
+  int act_reserve_sms = 0;             // hb_net_set_act_reserve
   unsigned int* chain = nullptr;       // tc_chain.cuh: [0..1] launch state, [2..] row-block counters
 };
 
@@ -902,7 +903,7 @@ int launch_unpack(const uint32_t* packed, int stride, long long rows, __half* ou
 // q (and logits when given).
 int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0, long long rows,
             __half* const* hbuf, __half* const* hbuf_t, int ld_t, float* logits, float* q_out, int ldq,
-            cudaStream_t s, const uint32_t* x_bits = nullptr, int pdl = 0) {
+            cudaStream_t s, const uint32_t* x_bits = nullptr, int pdl = 0, int max_ctas = 0) {
   const __half* in = x0;
   int ld_in = net->tab.l[0].K;
   const int nl = net->n_layers;
@@ -912,6 +913,7 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
     ep.alpha = 1.f;
     ep.bias = bias + g.boff;
     ep.pdl = pdl;
+    ep.max_ctas = max_ctas;
     int rc;
     if (l < nl - 1) {
       ep.relu = 1;
@@ -1414,6 +1416,15 @@ int hb_net_sync_target(hb_qnet* q, void* stream) {
   return HB_OK;
 }
 
+/* The acting pass's persistent GEMMs leave `sms` SMs unoccupied (0: none), for work a caller overlaps with
+ * them on another stream: their CTAs take a whole SM's registers and shared memory, so nothing else runs
+ * beside them otherwise. */
+int hb_net_set_act_reserve(hb_qnet* q, int sms) {
+  HB_REQUIRE(q && sms >= 0 && sms < tc::sm_count(), "hb_net_set_act_reserve: bad arguments");
+  q->act_reserve_sms = sms;
+  return HB_OK;
+}
+
 /* DQNAgent.explore / exploit (rlax_rainbow.py:277-290) for n rows of bit-packed observations and
  * legal-move masks.  greedy != 0: eval_policy.  d_uniform: one U[0,1) (explore: U[0,0.999)) draw per
  * row, or NULL for the built-in counter-based stream keyed (seed, counter, row0 + row).
@@ -1441,7 +1452,8 @@ int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int l
     __half* hb[kMaxLayers];
     for (int l = 0; l < kMaxLayers; ++l) hb[l] = q->act_h[l & 1];
     rc = forward(q, use_target ? q->t16 : q->w16, use_target ? q->tbeff : q->beff, q->act_x, rows, hb,
-                 nullptr, 0, nullptr, q->act_q, ldq, s, fused ? d_obs + r0 * q->obs_stride : nullptr);
+                 nullptr, 0, nullptr, q->act_q, ldq, s, fused ? d_obs + r0 * q->obs_stride : nullptr, 0,
+                 q->act_reserve_sms > 0 ? tc::sm_count() - q->act_reserve_sms : 0);
     if (rc) return rc;
     policy_kernel<<<(unsigned)((rows + 127) / 128), 128, 0, s>>>(
         q->act_q, ldq, d_legal + r0 * legal_words, legal_words, q->A, rows, greedy, epsilon,

@@ -565,13 +565,13 @@ int hb_rb_store_first(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs
   return HB_OK;
 }
 
-int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
-                     const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
-                     int64_t* n_added, void* stream) {
-  HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
-             "hb_rb_add_masked: bad arguments");
-  HB_REQUIRE((((uintptr_t)d_last_obs | (uintptr_t)d_obs) & 15) == 0, "hb_rb_add_masked: rows must be 16-byte aligned");
-  if (n_added) *n_added = 0;
+/* hb_rb_add_masked in two halves, so that a caller with several shards (the self-play session: one per
+ * learning seat) can start every shard's row count before it waits for the first one.
+ * begin: counts the rows that will be appended (step types -> per-block counts -> scan) and starts the copy
+ * of the total to the host.  finish (same arguments, same stream): waits for that total -- the ring cursor
+ * lives on the host, as in the reference -- and appends. */
+int hb_rb_add_masked_begin(hb_replay* rb, const uint8_t* d_step_type, int64_t n, void* stream) {
+  HB_REQUIRE(rb && d_step_type && n >= 0, "hb_rb_add_masked_begin: bad arguments");
   if (n == 0) return HB_OK;
   hb::DeviceGuard g(rb->device);
   cudaStream_t s = (cudaStream_t)stream;
@@ -589,6 +589,21 @@ int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
   mask_scan_kernel<<<1, kScanBlock, 0, s>>>(rb->block_sum, (int)n_blocks, rb->total);
   HB_CUDA(cudaGetLastError());
   HB_CUDA(cudaMemcpyAsync(rb->h_total, rb->total, 4, cudaMemcpyDeviceToHost, s));
+  return HB_OK;
+}
+
+int hb_rb_add_masked_finish(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                            const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                            int64_t* n_added, void* stream) {
+  HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
+             "hb_rb_add_masked: bad arguments");
+  HB_REQUIRE((((uintptr_t)d_last_obs | (uintptr_t)d_obs) & 15) == 0, "hb_rb_add_masked: rows must be 16-byte aligned");
+  if (n_added) *n_added = 0;
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n_blocks = (n + kScanBlock - 1) / kScanBlock;
+  HB_REQUIRE(rb->scan_n >= n_blocks, "hb_rb_add_masked_finish: no matching hb_rb_add_masked_begin");
   HB_CUDA(cudaStreamSynchronize(s));       // the ring cursor lives on the host, as in the reference
   const int64_t cnt = *rb->h_total;
   if (n_added) *n_added = cnt;
@@ -602,6 +617,17 @@ int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
   HB_CUDA(cudaGetLastError());
   advance(rb, cnt);
   return HB_OK;
+}
+
+int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                     const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                     int64_t* n_added, void* stream) {
+  HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
+             "hb_rb_add_masked: bad arguments");
+  if (n_added) *n_added = 0;
+  int rc = hb_rb_add_masked_begin(rb, d_step_type, n, stream);
+  if (rc) return rc;
+  return hb_rb_add_masked_finish(rb, d_last_obs, d_obs, d_lms, d_act, d_rew, d_step_type, n, n_added, stream);
 }
 
 int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,

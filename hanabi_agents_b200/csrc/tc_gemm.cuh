@@ -78,6 +78,7 @@ struct EpiParams {
   // could start): the first ring-full of B tiles is requested in front of griddepcontrol.wait
   int b_early;
   int a_early;               // the same for the A operand (not both)
+  int max_ctas;              // host side only: upper bound of the persistent grid (0: one CTA per SM)
 };
 
 // Programmatic dependent launch (PDL).  wait: returns once every grid this one depends on has

@@ -65,7 +65,8 @@ inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
     if (dev >= 0 && dev < 64) configured[dev] = true;
   }
   const long long tiles = (long long)((N + BN_ - 1) / BN_) * ((M + BM - 1) / BM);
-  const int sms = sm_count();
+  int sms = sm_count();
+  if (ep.max_ctas > 0 && ep.max_ctas < sms) sms = ep.max_ctas;
   const unsigned grid = (unsigned)(tiles < sms ? tiles : sms);
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

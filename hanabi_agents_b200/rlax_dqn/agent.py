@@ -108,6 +108,19 @@ class DQNAgent:
                                           self._dev(rewards, torch.float32),
                                           self._dev(step_types, torch.uint8))
 
+    def add_experience_begin(self, observations, step_types):
+        """add_experience in two halves (the session starts every seat's row count before it waits for the
+        first): begin on the current stream, add_experience_finish with the same arguments on the same one."""
+        obs, _, _ = self._pack_pair(observations)
+        self.experience.add_masked_begin(self._dev(step_types, self.torch.uint8), obs.shape[0])
+
+    def add_experience_finish(self, observations, actions, rewards, step_types):
+        torch = self.torch
+        obs, legal, _ = self._pack_pair(observations)
+        return self.experience.add_masked_finish(self.last_obs, obs, legal, self._dev(actions, torch.int32),
+                                                 self._dev(rewards, torch.float32),
+                                                 self._dev(step_types, torch.uint8))
+
     def _make_learner(self):
         import ctypes as C
         from .. import _lib

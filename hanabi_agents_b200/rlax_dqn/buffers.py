@@ -130,6 +130,18 @@ class ExperienceBuffer:
             rewards.data_ptr(), step_types.data_ptr(), obs.shape[0], C.byref(n_added), self._s()))
         return int(n_added.value)
 
+    def add_masked_begin(self, step_types, n):
+        """First half of add_masked (hb_rb_add_masked_begin): the row count is on its way to the host."""
+        _lib.check(_lib.lib().hb_rb_add_masked_begin(self._h, step_types.data_ptr(), int(n), self._s()))
+
+    def add_masked_finish(self, last_obs, obs, legal, actions, rewards, step_types):
+        """Second half, on the stream of the first: waits for the count and appends."""
+        n_added = C.c_int64()
+        _lib.check(_lib.lib().hb_rb_add_masked_finish(
+            self._h, last_obs.data_ptr(), obs.data_ptr(), legal.data_ptr(), actions.data_ptr(),
+            rewards.data_ptr(), step_types.data_ptr(), obs.shape[0], C.byref(n_added), self._s()))
+        return int(n_added.value)
+
     def store_first(self, last_obs, obs, step_types):
         _lib.check(_lib.lib().hb_rb_store_first(self._h, last_obs.data_ptr(), obs.data_ptr(),
                                                 step_types.data_ptr(), obs.shape[0], self._s()))

@@ -17,6 +17,7 @@ own point of view, its last action and the reward since -- what `agent.end_episo
 reward_since_last_action)` (:335) delivers in the reference.
 """
 import ctypes as C
+import os
 
 import numpy as np
 
@@ -63,6 +64,16 @@ class HanabiParallelSession:
         self.tick = 0
         self.is_reset = False
         self._side_obs = None
+        # Training ticks: the replay inserts of a tick (both seats' masked appends, their sum-tree range
+        # updates, two host round trips for the row counts) do not feed the move that is chosen in it, so
+        # they run on a second stream beside the acting pass (HB_SESSION_OVERLAP=0: one after the other, the
+        # reference's order of calls).  The acting GEMMs are persistent CTAs that take whole SMs: they leave
+        # HB_SESSION_RESERVE_SMS (default 32 of the 148) of them to the inserts, for that call only.
+        self._overlap = os.environ.get("HB_SESSION_OVERLAP", "1") != "0"
+        self._ins_stream = None
+        self._ins_event = None
+        self._seat_streams = []
+        self._reserve = int(os.environ.get("HB_SESSION_RESERVE_SMS", "32"))
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -89,8 +100,11 @@ class HanabiParallelSession:
         if offset == 0:
             return env.observations_packed()
         if self._side_obs is None:
-            self._side_obs = (self.torch.empty_like(env.obs_packed), self.torch.empty_like(env.legal_packed))
-        return (env, env.observe(offset, out=self._side_obs))
+            self._side_obs = {}
+        if offset not in self._side_obs:     # one pair per offset: the seats' inserts may run side by side
+            self._side_obs[offset] = (self.torch.empty_like(env.obs_packed),
+                                      self.torch.empty_like(env.legal_packed))
+        return (env, env.observe(offset, out=self._side_obs[offset]))
 
     # -- control ----------------------------------------------------------------------------
     def reset(self, clear_stats=True):
@@ -109,7 +123,8 @@ class HanabiParallelSession:
         agent = self.agents[k]
         _lib.check(L.hb_session_begin_turn(self._h, k, env.step_type.data_ptr(), self._s()))
         obs = self._obs_for(agent)
-        if train:
+
+        def inserts():
             if agent.requires_vectorized_observation():
                 self._bind(k)
                 agent.add_experience_first(obs, self.step_types[k])
@@ -123,6 +138,52 @@ class HanabiParallelSession:
                 other.add_experience(self._obs_for(other, (j - k) % self.P), self.last_action[j],
                                      self.reward_since_last_action[j], self.step_types[j])
             self._bind(k)
+
+        if train and self._overlap and self._learners:
+            torch = self.torch
+            main = torch.cuda.current_stream(env.device)
+            if self._ins_stream is None:
+                self._ins_stream = torch.cuda.Stream(device=env.device)
+                self._ins_event = torch.cuda.Event()
+            self._ins_event.record(main)             # observations and per-seat accounting are in place
+            self._bind(k)
+            net = getattr(getattr(agent, "network", None), "_h", None)
+            if net is not None:
+                _lib.check(L.hb_net_set_act_reserve(net, self._reserve))
+            actions = agent.explore(obs)             # enqueued first: the inserts' host waits run under it
+            if net is not None:
+                _lib.check(L.hb_net_set_act_reserve(net, 0))
+            seats = [j for j in [k] + [j for j in range(self.P) if j != k]
+                     if self.agents[j].requires_vectorized_observation()]
+            split = (len(set(id(self.agents[j]) for j in seats)) == len(seats) and
+                     all(hasattr(self.agents[j], "add_experience_begin") for j in seats))
+            if not split:                            # a shared agent / another agent type: one after the other
+                with torch.cuda.stream(self._ins_stream):
+                    self._ins_stream.wait_event(self._ins_event)
+                    inserts()
+                main.wait_stream(self._ins_stream)   # the env step overwrites what the inserts read
+            else:
+                # one stream per seat; every seat's row count is started before the host waits for the first
+                while len(self._seat_streams) < self.P:
+                    self._seat_streams.append(torch.cuda.Stream(device=env.device))
+                seat_obs = {}
+                for j in seats:
+                    with torch.cuda.stream(self._seat_streams[j]):
+                        self._seat_streams[j].wait_event(self._ins_event)
+                        if j == k:
+                            agent.add_experience_first(obs, self.step_types[k])
+                            seat_obs[j] = obs
+                        else:
+                            seat_obs[j] = self._obs_for(self.agents[j], (j - k) % self.P)
+                        self.agents[j].add_experience_begin(seat_obs[j], self.step_types[j])
+                for j in seats:
+                    with torch.cuda.stream(self._seat_streams[j]):
+                        self.agents[j].add_experience_finish(seat_obs[j], self.last_action[j],
+                                                             self.reward_since_last_action[j], self.step_types[j])
+                for j in seats:
+                    main.wait_stream(self._seat_streams[j])
+        elif train:
+            inserts()
             actions = agent.explore(obs)
         else:
             actions = agent.exploit(obs)
@@ -154,6 +215,32 @@ class HanabiParallelSession:
         self.episodes_done.zero_()
         _lib.dev_tensor(_lib.lib().hb_session_buffer(self._h, 9, 0), 4, "<f8", self, self.env.device).zero_()
 
+    def update_learners(self):
+        """One learner update of every learning agent (run_experiment.py:323-327 loops over the agents).
+        The agents share nothing (own network, own replay shard), and one update is a chain of small
+        kernels that leaves most of the device idle: in a single-process job they run side by side, each
+        from its own stream.  Data-parallel jobs keep them in line (one collective order for all ranks)."""
+        ls = self._learners
+        side = self._overlap and len(ls) > 1 and all(
+            getattr(a, "_world", None) is not None and a._world()[0] == 1 for a in ls)
+        if not side:
+            for a in ls:
+                a.update()
+            return
+        torch = self.torch
+        main = torch.cuda.current_stream(self.env.device)
+        if self._ins_event is None:
+            self._ins_event = torch.cuda.Event()
+        while len(self._seat_streams) < len(ls):
+            self._seat_streams.append(torch.cuda.Stream(device=self.env.device))
+        self._ins_event.record(main)
+        for i, a in enumerate(ls):
+            with torch.cuda.stream(self._seat_streams[i]):
+                self._seat_streams[i].wait_event(self._ins_event)
+                a.update()
+        for i in range(len(ls)):
+            main.wait_stream(self._seat_streams[i])
+
     def train(self, n_iter, n_sim_steps, n_train_steps, n_warmup=0):
         """n_iter x {n_sim_steps ticks of acting + recording, n_train_steps learner updates of
         every learning agent}; the first n_warmup ticks only fill the replay shards."""
@@ -163,8 +250,7 @@ class HanabiParallelSession:
         for _ in range(int(n_iter)):
             self.run(n_sim_steps, train=True)
             for _ in range(int(n_train_steps)):
-                for a in self._learners:
-                    a.update()
+                self.update_learners()
         return self.stats()
 
     def run_eval(self, check_every=16, max_ticks=4096):

@@ -258,6 +258,13 @@ int hb_rb_store_first(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs
 int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
                      const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
                      int64_t* n_added, void* stream);
+/* The same in two halves (begin: count the rows and start the copy of the total to the host; finish: wait
+ * for it and append), so that a caller with several shards starts every count before waiting for the
+ * first.  Same stream for both halves of a shard; finish takes hb_rb_add_masked's arguments. */
+int hb_rb_add_masked_begin(hb_replay* rb, const uint8_t* d_step_type, int64_t n, void* stream);
+int hb_rb_add_masked_finish(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                            const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                            int64_t* n_added, void* stream);
 /* __getitem__(indices) (experience_buffer.py:83-87); any output may be NULL. */
 int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,
                  float* d_rew, uint32_t* d_obs_t, uint32_t* d_lms, uint8_t* d_term, void* stream);
@@ -339,6 +346,10 @@ int hb_net_sync_target(hb_qnet* q, void* stream);
  * eval_policy :125-150) on n bit-packed observation rows + legal masks.  d_uniform: one draw per row
  * (explore: U[0, 0.999)), or NULL = counter-based stream keyed (seed, counter, row0 + row).
  * d_q (optional) [n, num_actions]: q-values with illegal moves at -inf. */
+/* Scheduling knob, no counterpart in the reference: the acting pass's persistent GEMMs (hb_net_act) leave
+ * `sms` SMs unoccupied for work the caller overlaps on another stream (the self-play session's replay
+ * inserts); 0 restores one CTA per SM. */
+int hb_net_set_act_reserve(hb_qnet* q, int sms);
 int hb_net_act(hb_qnet* q, const uint32_t* d_obs, const uint32_t* d_legal, int legal_words, int64_t n,
                int greedy, float epsilon, const float* d_uniform, uint64_t seed, uint64_t counter,
                int64_t row0, int use_target, int32_t* d_action, float* d_q, void* stream);

@@ -105,8 +105,13 @@ def test_masked_append_matches_add_experience():
                                 legal[nf], (st[nf] == 2).reshape(-1, 1))
             last_obs[nf] = obs[nf]
         last_obs[first] = obs[first]
-        # device
-        n_added = dev.add_masked(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
+        # device: in one call, or in the two halves the session uses (hb_rb_add_masked_begin / _finish)
+        if it % 2 == 0:
+            n_added = dev.add_masked(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
+        else:
+            d_st = to_dev(st)
+            dev.add_masked_begin(d_st, N)
+            n_added = dev.add_masked_finish(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), d_st)
         dev.store_first(d_last, d_obs, to_dev(st))
         assert n_added == int(nf.sum())
         assert (dev.size, dev.oldest_entry) == (ora.size, ora.oldest_entry)

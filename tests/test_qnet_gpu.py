@@ -194,3 +194,22 @@ def test_adam_multi_step_against_oracle():
         for gp, rp in zip(net.get_params(), ora.params):
             for k in rp:
                 np.testing.assert_allclose(gp[k], rp[k].numpy(), rtol=1e-5, atol=2e-7)
+
+
+def test_learner_step_parity_on_the_per_layer_paths():
+    """The learner step has switches that restore the round-1 launch structure (one GEMM launch per layer
+    instead of mlp_chain_kernel, the dense head backward GEMM instead of the product inside the C51 loss,
+    the last dZ product untransposed): the same parity tests must hold there.  The switches are read once
+    per process, hence the child process."""
+    import os
+    import subprocess
+    import sys
+    if os.environ.get("HB_FWD_CHAIN") == "0":
+        pytest.skip("already inside the child")
+    env = dict(os.environ, HB_FWD_CHAIN="0", HB_DENSE_HEAD_BW="1", HB_DZ0_PLAIN="1")
+    r = subprocess.run([sys.executable, "-m", "pytest", os.path.abspath(__file__), "-q", "-x", "-m", "gpu",
+                        "-k", "test_learner_step_parity and not per_layer_paths", "-p", "no:cacheprovider"],
+                       env=env, capture_output=True, text=True, timeout=600,
+                       cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert " passed" in r.stdout

@@ -1,1 +1,1 @@
-timeout 600 python tools/session_trace.py eval 2>&1 | grep -v Warn | tail -6
+timeout 900 python -m pytest tests/test_qnet_gpu.py -m gpu -x -q 2>&1 | tail -3

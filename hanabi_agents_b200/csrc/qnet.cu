@@ -92,6 +92,7 @@ struct hb_qnet {
   float* scalars = nullptr;            // [4]: mean loss, max weight, ...
   int act_reserve_sms = 0;             // hb_net_set_act_reserve
   unsigned int* chain = nullptr;       // tc_chain.cuh: [0..1] launch state, [2..] row-block counters
+  int chain_B = 0;                     // batch the counters were last used with
 };
 
 namespace {
@@ -1043,6 +1044,13 @@ int forward_chain(hb_qnet* q, int B, const int32_t* d_a_tm1, int tf_variant, int
     }
   }
   if (tiles > tc::sm_count() || 2 + flags > 128) return HB_OK;
+  // The row-block counters only ever grow, by the same amount per launch -- as long as every launch has the
+  // same row blocks.  Another batch size starts them over (stream ordered; a captured update never gets here
+  // with a new batch without being captured again).
+  if (q->chain_B != B) {
+    HB_CUDA(cudaMemsetAsync(q->chain, 0, 128 * sizeof(unsigned int), s));
+    q->chain_B = B;
+  }
   P.n_jobs = 2 * nl;
   P.total = tiles;
   P.state = q->chain;

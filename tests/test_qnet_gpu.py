@@ -196,6 +196,23 @@ def test_adam_multi_step_against_oracle():
                 np.testing.assert_allclose(gp[k], rp[k].numpy(), rtol=1e-5, atol=2e-7)
 
 
+def test_learner_step_with_changing_batch_sizes():
+    """One network, batches of 256, 40 and 256 rows again: the forward chain's row-block counters
+    (csrc/tc_chain.cuh) are per batch geometry; losses must match the oracle each time."""
+    import torch
+    obs_len, hidden, A, n_atoms = CONFIGS[0][:4]
+    net, ora, stride = _setup(obs_len, hidden, A, n_atoms, True, seed=7)
+    rng = np.random.default_rng(9)
+    t = lambda v: torch.tensor(v)  # noqa: E731
+    for B in (256, 40, 256, 40):
+        (x1, x2, a, r, term, prios), dev = _batch(rng, B, obs_len, stride, A)
+        mean_ref, per_ref, _ = ora.grads(t(x1), t(a), t(r), t(x2), t(term), prios=t(prios), beta=0.4, discount=0.99)
+        loss, mean = net.grads(dev[0], dev[1], dev[2], dev[3], dev[4], prios=dev[5], beta=0.4, discount=0.99)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(loss.cpu(), per_ref, rtol=1e-3, atol=1e-3 * float(per_ref.abs().max()))
+        assert abs(float(mean) - mean_ref) <= 1e-3 * abs(mean_ref) + 1e-6
+
+
 def test_learner_step_parity_on_the_per_layer_paths():
     """The learner step has switches that restore the round-1 launch structure (one GEMM launch per layer
     instead of mlp_chain_kernel, the dense head backward GEMM instead of the product inside the C51 loss,

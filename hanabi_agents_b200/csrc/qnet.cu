@@ -1098,8 +1098,7 @@ int forward_chain(hb_qnet* q, int B, const int32_t* d_a_tm1, int tf_variant, int
           if (v > mx[k]) mx[k] = v;
           if (v < mn[k]) mn[k] = v;
         }
-      {
-        const int c = c0;   // SM clock: cycles between two stamps of one CTA over the same span in ns
+      for (int c = c0; c < c1; c += (c1 - c0 > 20 ? 20 : c1 - c0)) {   // first CTA (and every 20th) of the job
         fprintf(stderr, "  [cta %d: %.0f cycles in %.0f ns between 'acc' and 'stores done']\n", c,
                 (double)(h[c * 16 + 7] - h[c * 16 + 6]), (double)(h[c * 16 + 5] - h[c * 16 + 3]));
         if (h[c * 16 + 8] && P.job[jn].abits)
@@ -1112,6 +1111,12 @@ int forward_chain(hb_qnet* q, int B, const int32_t* d_a_tm1, int tf_variant, int
                   (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]),
                   (long long)(h[c * 16 + 13] - h[c * 16 + 12]));
       }
+      if (atoi(getenv("HB_CHAIN_TRACE")) > 1)
+        for (int c = c0; c < c1; ++c)
+          fprintf(stderr, "    cta %d (m-block %d, n-tile %d): rows ready %.1f acc %.1f stores issued %.1f done %.1f\n", c,
+                  (c - c0) / P.job[jn].tiles_n, (c - c0) % P.job[jn].tiles_n, ((double)h[c * 16 + 1] - (double)t0) * 1e-3,
+                  ((double)h[c * 16 + 3] - (double)t0) * 1e-3, ((double)h[c * 16 + 4] - (double)t0) * 1e-3,
+                  ((double)h[c * 16 + 5] - (double)t0) * 1e-3);
       fprintf(stderr, "chain job %d (%d tiles): start %.1f-%.1f | rows ready %.1f-%.1f | mma issued %.1f-%.1f | "
               "acc %.1f-%.1f | stores issued %.1f-%.1f | stores done %.1f-%.1f us\n", jn, c1 - c0, mn[0], mx[0],
               mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mn[4], mx[4], mn[5], mx[5]);

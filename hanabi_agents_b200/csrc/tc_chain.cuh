@@ -68,8 +68,10 @@ __device__ __forceinline__ void fence_proxy_async_all() { asm volatile("fence.pr
 // (32 lines per instruction, 16 instructions per action: 6-7 us of the head's tiles).  Staged as a swizzled
 // [32 rows][64 floats] block per warp, a row goes out as one 256-byte store instruction.
 // `stage`: 8 KB of the operand ring (free once the accumulator is complete).
+// x[64] arrives holding the bias values and my_act the row's action (or -1): both are loaded before the
+// accumulator is complete -- behind it they were two L2 round trips in every head tile's epilogue.
 __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, int n0, int ew, int half, int lane,
-                                                    const EpiParams& ep, uint8_t* stage,
+                                                    const EpiParams& ep, uint8_t* stage, float (&x)[64], int my_act,
                                                     const int* sel_action, int sel_rows, unsigned long long* tr) {
 #define HB_EPI_STAMP(k) do { if (tr != nullptr) tr[k] = (unsigned long long)clock64(); } while (0)
   HB_EPI_STAMP(8);
@@ -82,8 +84,6 @@ __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, 
   tmem_ld32(lane_addr + half * 64, v0);
   tmem_ld32(lane_addr + half * 64 + 32, v1);
   HB_EPI_STAMP(9);
-  float x[64];
-  load_bias<64>(ep.bias, nb, ep.N, x);
 #pragma unroll
   for (int j = 0; j < 32; ++j) {
     x[j] += ep.alpha * __uint_as_float(v0[j]);
@@ -91,7 +91,6 @@ __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, 
   }
   HB_EPI_STAMP(10);
   // rows whose logits somebody reads (all of them without sel_action)
-  const int my_act = (sel_action != nullptr && m < sel_rows) ? sel_action[m] : -1;
   const bool mine = sel_action == nullptr || my_act == (nb >> 6);
   const unsigned want = __ballot_sync(0xffffffffu, mine && row_ok);
   if (ep.out32 != nullptr && want != 0u) {
@@ -103,11 +102,11 @@ __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, 
     HB_EPI_STAMP(11);
     const int rows = ep.M - (m0 + ew * 32);
 #pragma unroll 4
-    for (int r = 0; r < 32; ++r) {
+    for (int i = 0; i < 16; ++i) {                   // two rows per instruction, 16 bytes per lane
+      const int r = 2 * i + (lane >> 4), c4 = lane & 15;
       if (r < rows && ((want >> r) & 1u)) {
-        const float2 o = *reinterpret_cast<const float2*>(stage + r * 256 + (((lane >> 1) ^ (r & 15)) << 4) +
-                                                          (lane & 1) * 8);
-        *reinterpret_cast<float2*>(ep.out32 + (size_t)(m0 + ew * 32 + r) * ep.ld_out + nb + 2 * lane) = o;
+        const float4 o = *reinterpret_cast<const float4*>(stage + r * 256 + ((c4 ^ (r & 15)) << 4));
+        *reinterpret_cast<float4*>(ep.out32 + (size_t)(m0 + ew * 32 + r) * ep.ld_out + nb + 4 * c4) = o;
       }
     }
   }
@@ -121,21 +120,8 @@ __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, 
       for (int j = 0; j < 32; ++j)
         if (j >= ep.n_atoms) x[j] = -INFINITY;
     }
-    float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-    for (int j = 0; j < 64; ++j) m4[j & 3] = fmaxf(m4[j & 3], x[j]);
-    const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-    const float kLog2e = 1.4426950408889634f;
-    const float mxs = mx * kLog2e;
-    float d4[4] = {0.f, 0.f, 0.f, 0.f}, n4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-    for (int j = 0; j < 64; ++j) {
-      const float e = exp2f(fmaf(x[j], kLog2e, -mxs));
-      d4[j & 3] += e;
-      n4[j & 3] = fmaf(e, ep.z0 + (float)j * ep.dz, n4[j & 3]);
-    }
-    const float den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
-    const float num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
+    float den, num;
+    softmax_mean64(x, ep.n_atoms, ep.z0, ep.dz, den, num);
     ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
   }
   HB_EPI_STAMP(13);
@@ -326,6 +312,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
     }
     const bool drains = job.bn == BN_ || half == 0;       // a 64-wide tile is the first half's alone
     if (drains) {
+    float xb[64];
+    int my_act = -1;
+    if (job.epi == EPI_C51) {
+      load_bias<64>(ep.bias, n0 + half * 64, ep.N, xb);
+      const int m = m0 + ew * 32 + lane;
+      if (job.sel_action != nullptr && m < job.sel_rows && m < ep.M) my_act = job.sel_action[m];
+    }
     mbar_wait(&acc_full[0], 0);
     tc_fence_after();
     if (warp == 4 && lane == 0) HB_CHAIN_STAMP(3);         // accumulator complete
@@ -334,8 +327,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
     if (job.epi == EPI_F16)
       epilogue_tile<EPI_F16, BN_>(tmem_base, 0u, m0, n0, ew, half, lane, ep, &job.tout, stage);
     else if (job.epi == EPI_C51)
-      epilogue_c51_staged(tmem_base, m0, n0, ew, half, lane, ep, smem + (warp - 4) * 8192, job.sel_action,
-                          job.sel_rows,
+      epilogue_c51_staged(tmem_base, m0, n0, ew, half, lane, ep, smem + (warp - 4) * 8192, xb, my_act,
+                          job.sel_action, job.sel_rows,
                           (p.trace != nullptr && warp == 4 && lane == 0) ? p.trace + blockIdx.x * 16 : nullptr);
     else
       epilogue_tile<EPI_F32, BN_>(tmem_base, 0u, m0, n0, ew, half, lane, ep, &job.tout, stage);

@@ -247,6 +247,40 @@ __device__ __forceinline__ void load_bias(const float* __restrict__ bias, int nb
   }
 }
 
+// den = sum_j exp(x_j - max), num = sum_j exp(x_j - max) z_j over the 64 columns of one action (pad columns
+// hold -inf).  ex2.approx.ftz instead of exp2f: the arguments are <= 0, a result that flushes to zero adds
+// nothing to sums that hold at least one 1.0, and exp2f's range handling was four instructions around every
+// MUFU -- with the masks and the 64-column loops 4200 cycles of a head tile's epilogue.  The common case
+// n_atoms <= 52 walks 52 columns.
+__device__ __forceinline__ float ex2_approx(float v) {
+  float r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
+  return r;
+}
+template <int W>
+__device__ __forceinline__ void softmax_mean_w(const float (&x)[64], float z0, float dz, float& den, float& num) {
+  float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+  for (int j = 0; j < W; ++j) m4[j & 3] = fmaxf(m4[j & 3], x[j]);
+  const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
+  const float kLog2e = 1.4426950408889634f;
+  const float mxs = mx * kLog2e;
+  float d4[4] = {0.f, 0.f, 0.f, 0.f}, n4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+  for (int j = 0; j < W; ++j) {
+    const float e = ex2_approx(fmaf(x[j], kLog2e, -mxs));
+    d4[j & 3] += e;
+    n4[j & 3] = fmaf(e, z0 + (float)j * dz, n4[j & 3]);
+  }
+  den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
+  num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
+}
+__device__ __forceinline__ void softmax_mean64(const float (&x)[64], int n_atoms, float z0, float dz, float& den,
+                                               float& num) {
+  if (n_atoms <= 52) softmax_mean_w<52>(x, z0, dz, den, num);
+  else softmax_mean_w<64>(x, z0, dz, den, num);
+}
+
 // ---------------------------------------------------------------------- epilogue ----
 // One epilogue warp: rows m0 + ew*32 + lane of the tile whose accumulator starts at TMEM column
 // `acc_col` (thread = TMEM lane = D row, 32 fp32 columns per tcgen05.ld).
@@ -290,21 +324,8 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_c
           for (int j = 0; j < 32; ++j)
             if (j >= ep.n_atoms) x[j] = -INFINITY;
         }
-        float m4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-        for (int j = 0; j < 64; ++j) m4[j & 3] = fmaxf(m4[j & 3], x[j]);
-        const float mx = fmaxf(fmaxf(m4[0], m4[1]), fmaxf(m4[2], m4[3]));
-        const float kLog2e = 1.4426950408889634f;
-        const float mxs = mx * kLog2e;
-        float d4[4] = {0.f, 0.f, 0.f, 0.f}, n4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-        for (int j = 0; j < 64; ++j) {
-          const float e = exp2f(fmaf(x[j], kLog2e, -mxs));
-          d4[j & 3] += e;
-          n4[j & 3] = fmaf(e, ep.z0 + (float)j * ep.dz, n4[j & 3]);
-        }
-        const float den = (d4[0] + d4[1]) + (d4[2] + d4[3]);
-        const float num = (n4[0] + n4[1]) + (n4[2] + n4[3]);
+        float den, num;
+        softmax_mean64(x, ep.n_atoms, ep.z0, ep.dz, den, num);
         ep.q[(size_t)m * ep.ld_q + (nb >> 6)] = ep.q_scale * num / den;
       }
     }

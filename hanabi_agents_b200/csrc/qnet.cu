@@ -93,6 +93,9 @@ struct hb_qnet {
   int act_reserve_sms = 0;             // hb_net_set_act_reserve
   unsigned int* chain = nullptr;       // tc_chain.cuh: [0..1] launch state, [2..] row-block counters
   int chain_B = 0;                     // batch the counters were last used with
+  unsigned int* chain2 = nullptr;      // the same for the backward tail (dZ_0^T -> dW_0)
+  int chain2_B = 0;
+  float* bias_part = nullptr;          // [ceil(B / 64)][N_0] row sums of dZ_0^T (EpiParams::row_part)
 };
 
 namespace {
@@ -813,6 +816,7 @@ void free_learner_ws(hb_qnet* q) {
   }
   dev_free(q->logits); dev_free(q->q_on); dev_free(q->q_tg); dev_free(q->tlogits); dev_free(q->w_is);
   dev_free(q->loss_b);
+  dev_free(q->bias_part);
   q->lb = q->lbp = 0;
 }
 
@@ -868,6 +872,7 @@ int ensure_learner_ws(hb_qnet* q, int B) {
   if ((rc = dev_alloc(&q->q_tg, (size_t)B * NL))) return rc;
   if ((rc = dev_alloc(&q->w_is, (size_t)B))) return rc;
   if ((rc = dev_alloc(&q->loss_b, (size_t)B))) return rc;
+  if ((rc = dev_alloc(&q->bias_part, (size_t)((B + 63) / 64) * q->tab.l[0].N))) return rc;
   q->lb = B;
   q->lbp = Bp;
   return HB_OK;
@@ -944,6 +949,80 @@ int forward(hb_qnet* net, const __half* wts, const float* bias, const __half* x0
       rc = tc::gemm<tc::EPI_F32>(in, ld_in, wts + g.woff, g.K, (int)rows, g.N, g.K, ep, s);
     }
     if (rc) return rc;
+  }
+  return HB_OK;
+}
+
+// Launch of tc::mlp_chain_kernel (+ HB_CHAIN_TRACE: per-job phase times of an eager launch on stderr).
+int launch_chain(hb_qnet* q, tc::ChainParams& P, int tiles, cudaStream_t s, int pdl, const char* tag) {
+  static const int compact = getenv("HB_CHAIN_COMPACT") ? atoi(getenv("HB_CHAIN_COMPACT")) : 1;
+  P.compact = compact;
+  static bool configured[64] = {false};
+  const int dev = q->device;
+  if (dev < 0 || dev >= 64 || !configured[dev]) {
+    HB_CUDA(cudaFuncSetAttribute(tc::mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 tc::smem_bytes_for(tc::kChainBN)));
+    if (dev >= 0 && dev < 64) configured[dev] = true;
+  }
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)tiles);
+  cfg.blockDim = dim3(tc::kThreads);
+  cfg.dynamicSmemBytes = tc::smem_bytes_for(tc::kChainBN);
+  cfg.stream = s;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  // HB_CHAIN_TRACE=1 (debugging, eager launches only): per-job phase times of the launch on stderr
+  static const bool trace = getenv("HB_CHAIN_TRACE") && atoi(getenv("HB_CHAIN_TRACE")) != 0;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (trace) cudaStreamIsCapturing(s, &cap);
+  static unsigned long long* d_trace = nullptr;
+  if (trace && cap == cudaStreamCaptureStatusNone) {
+    if (d_trace == nullptr) HB_CUDA(cudaMalloc(&d_trace, 256 * 16 * 8));
+    HB_CUDA(cudaMemsetAsync(d_trace, 0, 256 * 16 * 8, s));
+    P.trace = d_trace;
+  }
+  HB_CUDA(cudaLaunchKernelEx(&cfg, tc::mlp_chain_kernel, P));
+  if (P.trace != nullptr) {
+    std::vector<unsigned long long> h(256 * 16);
+    HB_CUDA(cudaStreamSynchronize(s));
+    HB_CUDA(cudaMemcpy(h.data(), d_trace, 256 * 16 * 8, cudaMemcpyDeviceToHost));
+    unsigned long long t0 = ~0ull;
+    for (int c = 0; c < tiles; ++c) if (h[c * 16] && h[c * 16] < t0) t0 = h[c * 16];
+    for (int jn = 0; jn < P.n_jobs; ++jn) {
+      const int c0 = P.job[jn].tile_base, c1 = jn + 1 < P.n_jobs ? P.job[jn + 1].tile_base : tiles;
+      double mx[6] = {0, 0, 0, 0, 0, 0}, mn[6] = {1e30, 1e30, 1e30, 1e30, 1e30, 1e30};
+      for (int c = c0; c < c1; ++c)
+        for (int k = 0; k < 6; ++k) {
+          const double v = ((double)h[c * 16 + k] - (double)t0) * 1e-3;
+          if (v > mx[k]) mx[k] = v;
+          if (v < mn[k]) mn[k] = v;
+        }
+      for (int c = c0; c < c1; c += (c1 - c0 > 20 ? 20 : c1 - c0)) {   // first CTA (and every 20th) of the job
+        fprintf(stderr, "  [cta %d: %.0f cycles in %.0f ns between 'acc' and 'stores done']\n", c,
+                (double)(h[c * 16 + 7] - h[c * 16 + 6]), (double)(h[c * 16 + 5] - h[c * 16 + 3]));
+        if (h[c * 16 + 8] && P.job[jn].abits)
+          fprintf(stderr, "  [expand kb 0 cycles: wait slot %lld | expand+sts %lld | proxy fence %lld | arrive %lld]\n",
+                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
+                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]));
+        else if (h[c * 16 + 8])
+          fprintf(stderr, "  [c51 epilogue cycles: tmem %lld | bias+add %lld | stage %lld | row stores %lld | q %lld]\n",
+                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
+                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]),
+                  (long long)(h[c * 16 + 13] - h[c * 16 + 12]));
+      }
+      if (atoi(getenv("HB_CHAIN_TRACE")) > 1)
+        for (int c = c0; c < c1; ++c)
+          fprintf(stderr, "    cta %d (m-block %d, n-tile %d): rows ready %.1f acc %.1f stores issued %.1f done %.1f\n", c,
+                  (c - c0) / P.job[jn].tiles_n, (c - c0) % P.job[jn].tiles_n, ((double)h[c * 16 + 1] - (double)t0) * 1e-3,
+                  ((double)h[c * 16 + 3] - (double)t0) * 1e-3, ((double)h[c * 16 + 4] - (double)t0) * 1e-3,
+                  ((double)h[c * 16 + 5] - (double)t0) * 1e-3);
+      fprintf(stderr, "%s job %d (%d tiles): start %.1f-%.1f | rows ready %.1f-%.1f | mma issued %.1f-%.1f | "
+              "acc %.1f-%.1f | stores issued %.1f-%.1f | stores done %.1f-%.1f us\n", tag, jn, c1 - c0, mn[0], mx[0],
+              mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mn[4], mx[4], mn[5], mx[5]);
+    }
   }
   return HB_OK;
 }
@@ -1055,73 +1134,88 @@ int forward_chain(hb_qnet* q, int B, const int32_t* d_a_tm1, int tf_variant, int
   P.total = tiles;
   P.state = q->chain;
   P.flags = q->chain;                      // flag_base already counts from the start of the buffer
-  static bool configured[64] = {false};
-  const int dev = q->device;
-  if (dev < 0 || dev >= 64 || !configured[dev]) {
-    HB_CUDA(cudaFuncSetAttribute(tc::mlp_chain_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 tc::smem_bytes_for(tc::kChainBN)));
-    if (dev >= 0 && dev < 64) configured[dev] = true;
+  int rc0;
+  if ((rc0 = launch_chain(q, P, tiles, s, pdl, "chain"))) return rc0;
+  *done = 1;
+  return HB_OK;
+}
+
+// The tail of the backward pass as one launch of tc::mlp_chain_kernel: dZ_0^T [N_0, B] = W_1^T . dZ_1^T (ReLU
+// gate read transposed, row sums left for the bias gradient) and, released row block by row block,
+// dW_0 [N_0, K_0] = dZ_0^T . X^T / B, whose tiles of column block 0 finish db_0.  Replaces two GEMM launches
+// and bias_grad_kernel on the critical path.  *done = 0: shapes do not qualify, nothing was launched.
+int backward_tail_chain(hb_qnet* q, int B, int Bp, cudaStream_t s, int pdl, int* done) {
+  *done = 0;
+  static const bool off = getenv("HB_BWD_CHAIN") && atoi(getenv("HB_BWD_CHAIN")) == 0;
+  if (off || q->n_layers < 2) return HB_OK;
+  const LayerGeo& L0 = q->tab.l[0];
+  const LayerGeo& L1 = q->tab.l[1];
+  tc::ChainParams P{};
+  int rc;
+  tc::ChainJob& Z = P.job[0];
+  Z.ep = tc::EpiParams{};
+  Z.ep.M = L1.K;                       // = N_0
+  Z.ep.N = B;
+  Z.ep.alpha = 1.f;
+  Z.ep.gate = q->ht[0];
+  Z.ep.ld_gate = 2 * Bp;
+  Z.ep.out16 = q->dzt[0];
+  Z.ep.ld_out = Bp;
+  Z.ep.row_part = q->bias_part;
+  Z.ep.ld_part = L0.N;
+  Z.K = L1.N;
+  Z.epi = tc::EPI_F16;
+  // 64-wide tiles for both jobs: one SM stores ~20 B / clock, and the epilogues (32 KB of fp16 + the gate per
+  // dZ tile, 64 KB of fp32 per dW tile at 128 columns) were 4 us each of a 16 us launch
+  static const int bn_env = getenv("HB_BWD_CHAIN_BN") ? atoi(getenv("HB_BWD_CHAIN_BN")) : 64;
+  const int bn = bn_env == 128 ? 128 : 64;
+  Z.bn = bn;
+  Z.tiles_n = (B + bn - 1) / bn;
+  Z.tile_base = 0;
+  Z.dep = -1;
+  Z.flag_base = 2;
+  Z.has_consumer = 1;
+  Z.b_late = 1;
+  if ((rc = tc::make_tmap(&Z.ta, q->w16t + L1.woff, L1.K, L1.N, L1.N, tc::BM))) return rc;
+  if ((rc = tc::make_tmap(&Z.tb, q->dz[1], B, L1.N, L1.N, bn))) return rc;
+  if ((rc = tc::out_map<tc::EPI_F16>(&Z.tout, Z.tb, Z.ep))) return rc;
+  if (!Z.ep.tma_out) return HB_OK;     // the row sums are made on the tensor-store path only
+  const int tiles_m = (L1.K + tc::BM - 1) / tc::BM;
+  tc::ChainJob& W = P.job[1];
+  W.ep = tc::EpiParams{};
+  W.ep.M = L0.N;
+  W.ep.N = L0.K;
+  W.ep.alpha = 1.0f / (float)B;
+  W.ep.out32 = q->grad + L0.eoff;
+  W.ep.ld_out = L0.K;
+  W.K = B;
+  W.epi = tc::EPI_F32;
+  W.bn = bn;
+  W.tiles_n = (L0.K + bn - 1) / bn;
+  W.tile_base = tiles_m * Z.tiles_n;
+  W.dep = 0;
+  W.dep_arrivals = Z.tiles_n * (bn == 64 ? tc::kEpiWarps / 2 : tc::kEpiWarps);
+  W.flag_base = 2 + tiles_m;
+  W.has_consumer = 0;
+  W.bias_in = q->bias_part;
+  W.bias_parts = (B + 63) / 64;
+  W.bias_ld = L0.N;
+  W.bias_out = q->grad + L0.eoff + (long long)L0.N * L0.K;
+  W.bias_alpha = 1.0f / (float)B;
+  if ((rc = tc::make_tmap(&W.ta, q->dzt[0], L0.N, B, Bp, tc::BM))) return rc;
+  if ((rc = tc::make_tmap(&W.tb, q->xt, L0.K, B, Bp, bn))) return rc;
+  W.tout = W.tb;
+  const int tiles = W.tile_base + tiles_m * W.tiles_n;
+  if (tiles > tc::sm_count() || 2 + 2 * tiles_m > 128) return HB_OK;
+  if (q->chain2_B != B) {
+    HB_CUDA(cudaMemsetAsync(q->chain2, 0, 128 * sizeof(unsigned int), s));
+    q->chain2_B = B;
   }
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = pdl ? 1 : 0;
-  cudaLaunchConfig_t cfg = {};
-  cfg.gridDim = dim3((unsigned)tiles);
-  cfg.blockDim = dim3(tc::kThreads);
-  cfg.dynamicSmemBytes = tc::smem_bytes_for(tc::kChainBN);
-  cfg.stream = s;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  // HB_CHAIN_TRACE=1 (debugging, eager launches only): per-job phase times of the launch on stderr
-  static const bool trace = getenv("HB_CHAIN_TRACE") && atoi(getenv("HB_CHAIN_TRACE")) != 0;
-  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
-  if (trace) cudaStreamIsCapturing(s, &cap);
-  static unsigned long long* d_trace = nullptr;
-  if (trace && cap == cudaStreamCaptureStatusNone) {
-    if (d_trace == nullptr) HB_CUDA(cudaMalloc(&d_trace, 256 * 16 * 8));
-    HB_CUDA(cudaMemsetAsync(d_trace, 0, 256 * 16 * 8, s));
-    P.trace = d_trace;
-  }
-  HB_CUDA(cudaLaunchKernelEx(&cfg, tc::mlp_chain_kernel, P));
-  if (P.trace != nullptr) {
-    std::vector<unsigned long long> h(256 * 16);
-    HB_CUDA(cudaStreamSynchronize(s));
-    HB_CUDA(cudaMemcpy(h.data(), d_trace, 256 * 16 * 8, cudaMemcpyDeviceToHost));
-    unsigned long long t0 = ~0ull;
-    for (int c = 0; c < tiles; ++c) if (h[c * 16] && h[c * 16] < t0) t0 = h[c * 16];
-    for (int jn = 0; jn < P.n_jobs; ++jn) {
-      const int c0 = P.job[jn].tile_base, c1 = jn + 1 < P.n_jobs ? P.job[jn + 1].tile_base : tiles;
-      double mx[6] = {0, 0, 0, 0, 0, 0}, mn[6] = {1e30, 1e30, 1e30, 1e30, 1e30, 1e30};
-      for (int c = c0; c < c1; ++c)
-        for (int k = 0; k < 6; ++k) {
-          const double v = ((double)h[c * 16 + k] - (double)t0) * 1e-3;
-          if (v > mx[k]) mx[k] = v;
-          if (v < mn[k]) mn[k] = v;
-        }
-      for (int c = c0; c < c1; c += (c1 - c0 > 20 ? 20 : c1 - c0)) {   // first CTA (and every 20th) of the job
-        fprintf(stderr, "  [cta %d: %.0f cycles in %.0f ns between 'acc' and 'stores done']\n", c,
-                (double)(h[c * 16 + 7] - h[c * 16 + 6]), (double)(h[c * 16 + 5] - h[c * 16 + 3]));
-        if (h[c * 16 + 8] && P.job[jn].abits)
-          fprintf(stderr, "  [expand kb 0 cycles: wait slot %lld | expand+sts %lld | proxy fence %lld | arrive %lld]\n",
-                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
-                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]));
-        else if (h[c * 16 + 8])
-          fprintf(stderr, "  [c51 epilogue cycles: tmem %lld | bias+add %lld | stage %lld | row stores %lld | q %lld]\n",
-                  (long long)(h[c * 16 + 9] - h[c * 16 + 8]), (long long)(h[c * 16 + 10] - h[c * 16 + 9]),
-                  (long long)(h[c * 16 + 11] - h[c * 16 + 10]), (long long)(h[c * 16 + 12] - h[c * 16 + 11]),
-                  (long long)(h[c * 16 + 13] - h[c * 16 + 12]));
-      }
-      if (atoi(getenv("HB_CHAIN_TRACE")) > 1)
-        for (int c = c0; c < c1; ++c)
-          fprintf(stderr, "    cta %d (m-block %d, n-tile %d): rows ready %.1f acc %.1f stores issued %.1f done %.1f\n", c,
-                  (c - c0) / P.job[jn].tiles_n, (c - c0) % P.job[jn].tiles_n, ((double)h[c * 16 + 1] - (double)t0) * 1e-3,
-                  ((double)h[c * 16 + 3] - (double)t0) * 1e-3, ((double)h[c * 16 + 4] - (double)t0) * 1e-3,
-                  ((double)h[c * 16 + 5] - (double)t0) * 1e-3);
-      fprintf(stderr, "chain job %d (%d tiles): start %.1f-%.1f | rows ready %.1f-%.1f | mma issued %.1f-%.1f | "
-              "acc %.1f-%.1f | stores issued %.1f-%.1f | stores done %.1f-%.1f us\n", jn, c1 - c0, mn[0], mx[0],
-              mn[1], mx[1], mn[2], mx[2], mn[3], mx[3], mn[4], mx[4], mn[5], mx[5]);
-    }
-  }
+  P.n_jobs = 2;
+  P.total = tiles;
+  P.state = q->chain2;
+  P.flags = q->chain2;
+  if ((rc = launch_chain(q, P, tiles, s, pdl, "bwd chain"))) return rc;
   *done = 1;
   return HB_OK;
 }
@@ -1293,6 +1387,7 @@ int hb_net_create(int obs_len, int obs_stride_words, const int32_t* hidden, int 
   if (!rc) rc = dev_alloc(&q->beff, (size_t)q->n_b);
   if (!rc) rc = dev_alloc(&q->tbeff, (size_t)q->n_b);
   if (!rc) rc = dev_alloc(&q->chain, 128);
+  if (!rc) rc = dev_alloc(&q->chain2, 128);
   if (!rc) rc = dev_alloc(&q->scalars, 32);      // [0] mean loss [1] max weight [2] Adam step [3..7] its corrections
   if (rc) { hb_net_destroy(q); return rc; }
   *out = q;
@@ -1307,6 +1402,7 @@ int hb_net_destroy(hb_qnet* q) {
   dev_free(q->w16); dev_free(q->w16t); dev_free(q->t16); dev_free(q->beff); dev_free(q->tbeff);
   dev_free(q->scalars);
   dev_free(q->chain);
+  dev_free(q->chain2);
   if (q->side) {
     cudaStreamDestroy(q->side);
     if (q->side2) cudaStreamDestroy(q->side2);
@@ -1740,6 +1836,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   //    that only the first layer's update is left when the chain ends
   const float invB = 1.0f / (float)B;
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_wt, 0));
+  bool tail_chained = false;          // dZ_0^T, dW_0 and db_0 came out of one launch (backward_tail_chain)
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];
     // the first layer's gradient and update are the tail of the critical path: they stay on the main
@@ -1758,12 +1855,13 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.ld_out = L.K;
     ep.pdl = on_main ? pdl : 0;
     ep.b_early = ep.pdl;           // the transposed layer input was complete before the dZ GEMM could start
-    if ((rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
+    const bool have_grads = l == 0 && tail_chained;
+    if (!have_grads && (rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
     // (the first layer's bias gradient on the high-priority side stream, idle since the target network's
     // forward pass: on side2 it queued behind the other layers' Adam CTAs and held the last update up)
     cudaStream_t bs = on_main ? (bias0_main ? s : q->side) : q->side2;
-    if (bs != s) HB_CUDA(cudaStreamWaitEvent(bs, q->ev_dz[l], 0));
-    {
+    if (bs != s && !have_grads) HB_CUDA(cudaStreamWaitEvent(bs, q->ev_dz[l], 0));
+    if (!have_grads) {
       // programmatic launch for the first layer: its CTAs are placed while the SMs still have room and
       // wait inside the kernel, instead of queueing behind the other layers' Adam CTAs when dZ is ready
       cudaLaunchAttribute battr[1];
@@ -1780,8 +1878,10 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
                                  q->grad + L.eoff + (long long)L.N * L.K));
     }
     if (per_layer) {
-      HB_CUDA(cudaEventRecord(q->ev_bias[l], bs));
-      HB_CUDA(cudaStreamWaitEvent(ls, q->ev_bias[l], 0));
+      if (!have_grads) {
+        HB_CUDA(cudaEventRecord(q->ev_bias[l], bs));
+        HB_CUDA(cudaStreamWaitEvent(ls, q->ev_bias[l], 0));
+      }
       HB_CUDA(cudaStreamWaitEvent(ls, q->ev_tick, 0));
       const long long e0 = L.eoff, e1 = l + 1 < nl ? q->tab.l[l + 1].eoff : q->n_eff;
       // data parallel: this layer's slice of the bucket is summed over the ranks on the layer's own
@@ -1795,15 +1895,22 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       // gradients): computed as dZ_0^T [K, B] = W_1^T [K, N] . dZ_1^T, operands swapped, it leaves through
       // the tile's bulk tensor store instead of 2-byte scattered stores (2 us of the critical path).
       // The ReLU gate is read transposed too: ht[0] [K, 2Bp] (complete before ev_wt).
-      tc::EpiParams eb{};
-      eb.alpha = 1.f;
-      eb.gate = q->ht[0];
-      eb.ld_gate = 2 * Bp;
-      eb.out16 = q->dzt[0];
-      eb.ld_out = Bp;
-      eb.pdl = pdl;
-      eb.a_early = pdl;            // the transposed weights (ev_wt) are a full dependency of this launch
-      if ((rc = tc::gemm<tc::EPI_F16>(q->w16t + L.woff, L.N, q->dz[1], L.N, L.K, B, L.N, eb, s))) return rc;
+      // ... and, when every tile of it and of the first layer's weight gradient fits on the device at once,
+      // the two are one launch that also finishes the bias gradient (backward_tail_chain)
+      int tail = 0;
+      if ((rc = backward_tail_chain(q, B, Bp, s, pdl, &tail))) return rc;
+      tail_chained = tail != 0;
+      if (!tail_chained) {
+        tc::EpiParams eb{};
+        eb.alpha = 1.f;
+        eb.gate = q->ht[0];
+        eb.ld_gate = 2 * Bp;
+        eb.out16 = q->dzt[0];
+        eb.ld_out = Bp;
+        eb.pdl = pdl;
+        eb.a_early = pdl;          // the transposed weights (ev_wt) are a full dependency of this launch
+        if ((rc = tc::gemm<tc::EPI_F16>(q->w16t + L.woff, L.N, q->dz[1], L.N, L.K, B, L.N, eb, s))) return rc;
+      }
     } else if (l > 0 && !(l == nl - 1 && head_bw)) {
       // dZ_{l-1} [B, K] = (dZ_l . W_l) * relu'(H_{l-1}) : A = dz[l] [B, N], B = W^T [K, N]
       tc::EpiParams eb{};

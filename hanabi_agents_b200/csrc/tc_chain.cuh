@@ -37,6 +37,15 @@ struct ChainJob {
   // sel_rows rows (the loss), expected values only for the rows behind them (the double-Q argmax)
   const int* sel_action;      // [sel_rows] or nullptr: store everything
   int sel_rows;
+  // Backward tail (dZ_0^T -> dW_0): the B operand of the first job is what the launch waits for, its A
+  // operand (weights) is not
+  int b_late;                 // request A ahead of the wait and B behind it (default: the other way round)
+  // The consumer job's tiles of column block 0 also finish the bias gradient from the row sums the
+  // producer's epilogue left (EpiParams::row_part): bias_out[m] = bias_alpha * sum_p bias_in[p * ld + m]
+  const float* bias_in;
+  int bias_parts, bias_ld;
+  float* bias_out;
+  float bias_alpha;
 };
 
 struct ChainParams {
@@ -44,6 +53,8 @@ struct ChainParams {
   unsigned int* flags;        // monotonic arrival counters (never reset)
   unsigned int* state;        // [0] launches completed, [1] CTAs of the current launch that are done
   unsigned long long* trace;  // debugging (HB_CHAIN_TRACE): 8 globaltimer stamps per CTA, or nullptr
+  int compact;                // HB_CHAIN_COMPACT: 0 tc_gemm.cuh's unrolled epilogues, 1 (default) fp32 tiles through
+                              // epilogue_f32_staged, 2 fp16 tiles through epilogue_f16_compact as well
   ChainJob job[kChainMaxJobs];
 };
 
@@ -128,6 +139,129 @@ __device__ __forceinline__ void epilogue_c51_staged(uint32_t tmem_base, int m0, 
 #undef HB_EPI_STAMP
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+        "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// out32[m, n] = alpha * acc (+ bias) leaving through shared memory: as with the head's logits, a thread owns a
+// row, so direct stores put every lane of an instruction in a different row (the first layer's weight
+// gradient: 64 KB per tile, 4.6 us of epilogue).  Same staging as epilogue_c51_staged.
+__device__ __forceinline__ void epilogue_f32_staged(uint32_t tmem_base, int m0, int n0, int ew, int half, int lane,
+                                                    const EpiParams& ep, uint8_t* stage,
+                                                    unsigned long long* tr = nullptr) {
+#define HB_EPI_STAMP(k) do { if (tr != nullptr) tr[k] = (unsigned long long)clock64(); } while (0)
+  HB_EPI_STAMP(8);
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+  const int nb = n0 + half * 64;
+  if (nb >= ep.N) return;                            // warp-uniform
+  HB_EPI_STAMP(9);
+  // sixteen columns at a time in a loop that is NOT unrolled: a CTA of this kernel runs its epilogue once, so
+  // every instruction of it is an instruction-cache miss; as 64 unrolled columns the accumulator took 3100
+  // cycles to reach shared memory
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[16];
+    tmem_ld16(lane_addr + half * 64 + c * 16, v);
+    float x[16];
+    load_bias<16>(ep.bias, nb + c * 16, ep.N, x);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] += ep.alpha * __uint_as_float(v[j]);
+#pragma unroll
+    for (int j4 = 0; j4 < 4; ++j4)
+      *reinterpret_cast<float4*>(stage + lane * 256 + (((4 * c + j4) ^ (lane & 15)) << 4)) =
+          make_float4(x[4 * j4], x[4 * j4 + 1], x[4 * j4 + 2], x[4 * j4 + 3]);
+  }
+  __syncwarp();
+  HB_EPI_STAMP(10);
+  HB_EPI_STAMP(11);
+  const int rows = ep.M - (m0 + ew * 32);
+#pragma unroll 4
+  for (int i = 0; i < 16; ++i) {                     // two rows per instruction, 16 bytes per lane
+    const int r = 2 * i + (lane >> 4), c4 = lane & 15;
+    if (r < rows && nb + 4 * c4 < ep.N) {
+      const float4 o = *reinterpret_cast<const float4*>(stage + r * 256 + ((c4 ^ (r & 15)) << 4));
+      *reinterpret_cast<float4*>(ep.out32 + (size_t)(m0 + ew * 32 + r) * ep.ld_out + nb + 4 * c4) = o;
+    }
+  }
+  HB_EPI_STAMP(12);
+  HB_EPI_STAMP(13);
+#undef HB_EPI_STAMP
+}
+
+// fp16 epilogue (bias, ReLU or ReLU gate, optional row sums) through the tile's tensor store, sixteen columns
+// per iteration of a loop that is not unrolled (see epilogue_f32_staged: code size is what these one-shot
+// epilogues pay for).  The warp's 32 x 64 block goes to `stage` as the 128-byte-swizzled box of the output
+// map.  Requires ep.tma_out; no transposed copy.
+__device__ __forceinline__ void epilogue_f16_compact(uint32_t tmem_base, int m0, int n0, int ew, int half, int lane,
+                                                     const EpiParams& ep, const CUtensorMap* tmap_out,
+                                                     uint8_t* stage) {
+  const uint32_t lane_addr = tmem_base + ((uint32_t)(ew * 32) << 16);
+  const int m = m0 + ew * 32 + lane;
+  const bool row_ok = m < ep.M;
+  const int nb = n0 + half * 64;
+  if (nb >= ep.N) return;                            // warp-uniform
+  float rs = 0.f;
+#pragma unroll 1
+  for (int c = 0; c < 4; ++c) {
+    uint32_t v[16];
+    tmem_ld16(lane_addr + half * 64 + c * 16, v);
+    const int n16 = nb + c * 16;
+    float x[16];
+    load_bias<16>(ep.bias, n16, ep.N, x);
+#pragma unroll
+    for (int j = 0; j < 16; ++j) x[j] += ep.alpha * __uint_as_float(v[j]);
+    if (ep.relu) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) x[j] = fmaxf(x[j], 0.f);
+    }
+    if (ep.gate != nullptr && row_ok) {
+      const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + n16);
+#pragma unroll
+      for (int j4 = 0; j4 < 2; ++j4) {
+        if (n16 + 8 * j4 < ep.N) {
+          const uint4 gv = __ldg(g + j4);
+          const __half2* gh = reinterpret_cast<const __half2*>(&gv);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float2 f = __half22float2(gh[j]);
+            if (!(f.x > 0.f)) x[8 * j4 + 2 * j] = 0.f;
+            if (!(f.y > 0.f)) x[8 * j4 + 2 * j + 1] = 0.f;
+          }
+        }
+      }
+    }
+    uint32_t pk[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
+      pk[j] = *reinterpret_cast<const uint32_t*>(&h2);
+      if (ep.row_part != nullptr) {
+        const float2 f = __half22float2(h2);
+        if (n16 + 2 * j < ep.N) rs += f.x;
+        if (n16 + 2 * j + 1 < ep.N) rs += f.y;
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < 2; ++k)                      // 16-byte chunk 2c + k of row `lane`, swizzled
+      *reinterpret_cast<uint4*>(stage + lane * 128 + (((2 * c + k) ^ (lane & 7)) << 4)) =
+          make_uint4(pk[4 * k], pk[4 * k + 1], pk[4 * k + 2], pk[4 * k + 3]);
+  }
+  if (ep.row_part != nullptr && row_ok) ep.row_part[(size_t)(nb >> 6) * ep.ld_part + m] = rs;
+  fence_proxy_async();
+  __syncwarp();
+  if (lane == 0) {
+    tma_store_2d(tmap_out, stage, nb, m0 + ew * 32);
+    tma_store_commit();
+  }
+}
+
 __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_constant__ ChainParams p) {
   constexpr int BN_ = kChainBN;
   constexpr int kSt = stages_for(BN_);
@@ -179,7 +313,8 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
     for (int kb = 0; kb < pre; ++kb) {
       uint8_t* b_dst = smem + kb * kStB + BM * BK * 2;
       mbar_expect_tx(&full_bar[kb], abits ? (uint32_t)job.bn * BK * 2 : stage_bytes);
-      tma_load_2d(b_dst, &job.tb, &full_bar[kb], kb * BK, n0);
+      if (job.b_late) tma_load_2d(smem + kb * kStB, &job.ta, &full_bar[kb], kb * BK, m0);
+      else tma_load_2d(b_dst, &job.tb, &full_bar[kb], kb * BK, n0);
     }
   }
   // dependents are released only once this grid's own dependencies are complete: what the kernel in front
@@ -202,9 +337,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
         fence_proxy_async_all();                           // the rows were written by other CTAs; read by TMA
       }
       HB_CHAIN_STAMP(1);                                    // input rows complete
-      if (!abits)
+      if (job.b_late) {
+        for (int kb = 0; kb < pre; ++kb)
+          tma_load_2d(smem + kb * kStB + BM * BK * 2, &job.tb, &full_bar[kb], kb * BK, n0);
+      } else if (!abits) {
         for (int kb = 0; kb < pre; ++kb)
           tma_load_2d(smem + kb * kStB, &job.ta, &full_bar[kb], kb * BK, m0);
+      }
       for (int kb = pre; kb < num_kb; ++kb) {
         const int s = kb % kSt;
         const uint32_t ph = (kb / kSt) & 1;
@@ -312,6 +451,19 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
     }
     const bool drains = job.bn == BN_ || half == 0;       // a 64-wide tile is the first half's alone
     if (drains) {
+    if (job.epi == EPI_F16 && ep.gate != nullptr) {
+      // the ReLU gate of this thread's row pulled into L1 while the MMAs run (the epilogue's __ldg then hits)
+      const int m = m0 + ew * 32 + lane, nb = n0 + half * 64;
+      if (m < ep.M) {
+        const uint4* g = reinterpret_cast<const uint4*>(ep.gate + (size_t)m * ep.ld_gate + nb);
+#pragma unroll
+        for (int j4 = 0; j4 < 8; ++j4)
+          if (nb + 8 * j4 < ep.N) {
+            const uint4 gv = __ldg(g + j4);
+            asm volatile("" ::"r"(gv.x), "r"(gv.y), "r"(gv.z), "r"(gv.w));
+          }
+      }
+    }
     float xb[64];
     int my_act = -1;
     if (job.epi == EPI_C51) {
@@ -324,14 +476,29 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
     if (warp == 4 && lane == 0) HB_CHAIN_STAMP(3);         // accumulator complete
     if (warp == 4 && lane == 0 && p.trace != nullptr) p.trace[blockIdx.x * 16 + 6] = (unsigned long long)clock64();
     uint8_t* stage = out_stage + (warp - 4) * kOutStage;
-    if (job.epi == EPI_F16)
+    if (job.epi == EPI_F16 && ep.tma_out && ep.out16_t == nullptr && p.compact >= 2)
+      epilogue_f16_compact(tmem_base, m0, n0, ew, half, lane, ep, &job.tout, stage);
+    else if (job.epi == EPI_F16)
       epilogue_tile<EPI_F16, BN_>(tmem_base, 0u, m0, n0, ew, half, lane, ep, &job.tout, stage);
     else if (job.epi == EPI_C51)
       epilogue_c51_staged(tmem_base, m0, n0, ew, half, lane, ep, smem + (warp - 4) * 8192, xb, my_act,
                           job.sel_action, job.sel_rows,
                           (p.trace != nullptr && warp == 4 && lane == 0) ? p.trace + blockIdx.x * 16 : nullptr);
+    else if (ep.beta == 0.f && (ep.ld_out & 3) == 0 && (ep.N & 3) == 0 && p.compact >= 1)
+      epilogue_f32_staged(tmem_base, m0, n0, ew, half, lane, ep, smem + (warp - 4) * 8192,
+                          (p.trace != nullptr && warp == 4 && lane == 0) ? p.trace + blockIdx.x * 16 : nullptr);
     else
       epilogue_tile<EPI_F32, BN_>(tmem_base, 0u, m0, n0, ew, half, lane, ep, &job.tout, stage);
+    if (job.bias_out != nullptr && n0 == 0 && half == 0) {
+      // (what the producer's epilogue warps wrote is visible: the TMA thread acquired their counter before
+      // the loads whose arrival, through the MMAs, released this warp)
+      const int m = m0 + ew * 32 + lane;
+      if (m < ep.M) {
+        float sum = 0.f;
+        for (int q = 0; q < job.bias_parts; ++q) sum += job.bias_in[(size_t)q * job.bias_ld + m];
+        job.bias_out[m] = job.bias_alpha * sum;
+      }
+    }
     if (warp == 4 && lane == 0) HB_CHAIN_STAMP(4);         // epilogue stores issued
     if (job.epi == EPI_F16 && ep.tma_out && lane == 0) tma_store_wait_all();
     if (warp == 4 && lane == 0) HB_CHAIN_STAMP(5);         // stores complete

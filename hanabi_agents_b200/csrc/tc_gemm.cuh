@@ -79,6 +79,10 @@ struct EpiParams {
   int b_early;
   int a_early;               // the same for the A operand (not both)
   int max_ctas;              // host side only: upper bound of the persistent grid (0: one CTA per SM)
+  // EPI_F16 through the tensor store only: row_part[(n >> 6) * ld_part + m] = sum of the 64 stored (fp16
+  // rounded) values of row m in columns n .. n + 63, in column order -- the pieces of a bias gradient
+  float* row_part;
+  int ld_part;
 };
 
 // Programmatic dependent launch (PDL).  wait: returns once every grid this one depends on has
@@ -374,6 +378,16 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_c
       for (int j = 0; j < 32; ++j) {
         const __half2 h2 = __floats2half2_rn(x[2 * j], x[2 * j + 1]);
         p[j] = *reinterpret_cast<const uint32_t*>(&h2);
+      }
+      if (ep.row_part != nullptr && row_ok) {
+        float rs = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&p[j]));
+          if (nb + 2 * j < ep.N) rs += f.x;
+          if (nb + 2 * j + 1 < ep.N) rs += f.y;
+        }
+        ep.row_part[(size_t)(nb >> 6) * ep.ld_part + m] = rs;
       }
       if (lane == 0) tma_store_wait_read();        // the previous block has left the buffer
       __syncwarp();

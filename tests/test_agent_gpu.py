@@ -157,3 +157,52 @@ def test_graph_replay_equals_eager_updates():
         for k in a:
             np.testing.assert_array_equal(a[k], b[k])
     np.testing.assert_array_equal(h0, h1)
+
+
+def test_learner_update_gradients_and_step_against_the_oracle():
+    """DQNAgent.update on the 658-512-512 network through hb_learner_step (the path with the chained forward
+    pass, the head's backward product inside the loss, the chained backward tail and per-layer Adam): the
+    gradients left in the bucket and the first optix.adam step against oracle/learner.py on the very batch
+    the agent samples.  Tolerances as in test_qnet_gpu.py::test_learner_step_parity."""
+    import torch
+    from hanabi_agents_b200.env import HanabiParallelEnv
+    from hanabi_agents_b200.rlax_dqn import DQNAgent, RlaxRainbowParams
+    N, B = 512, 64
+    params = RlaxRainbowParams(train_batch_size=B, layers=[512, 512], experience_buffer_size=8192, seed=5)
+    env = HanabiParallelEnv(N, "Hanabi-Full", 2, seed=9)
+    agent = DQNAgent(env.observation_spec(), env.action_spec(), params)
+    env.reset()
+    obs = env.observations_packed()
+    agent.add_experience_first(obs, env.step_type)
+    for _ in range(6):
+        a = agent.explore(obs)
+        env.step(a)
+        obs = env.observations_packed()
+        agent.add_experience(obs, a, env.reward, env.step_type)
+        agent.add_experience_first(obs, env.step_type)
+    rng = np.random.default_rng(3)
+    u = rng.uniform(0, 1.0 / B, B)
+    idx, _, p32, (o1, ac, r, o2, _lm, term) = agent.experience.sample_device(B, u)
+    ora = _oracle_from(agent.network, params.n_atoms, True, env.num_moves)
+    x1 = agent.experience.unpack_obs(o1).cpu()
+    x2 = agent.experience.unpack_obs(o2).cpu()
+    beta = float(params.beta_is(agent.train_step))
+    lr = params.learning_rate
+    lr = float(lr(agent.train_step)) if callable(lr) else float(lr)
+    ref_mean, _, g_ref = ora.grads(x1, ac.cpu(), r.cpu(), x2, term.cpu(), prios=p32.cpu(), beta=beta,
+                                   discount=float(params.discount))
+    mean = agent.update(uniforms=u)
+    torch.cuda.synchronize()
+    assert abs(float(mean) - ref_mean) <= 1e-3 * abs(ref_mean) + 1e-6
+    got = agent.network.get_params(grads=True)
+    assert len(got) == 3
+    for l, (gg, gr) in enumerate(zip(got, g_ref)):
+        for k_dev, k_ref in (("dw", "w"), ("db", "b")):
+            ref = gr[k_ref].numpy()
+            err = gg[k_dev] - ref
+            assert np.linalg.norm(err) <= 1e-2 * np.linalg.norm(ref) + 1e-12, (l, k_dev)
+            assert np.abs(err).max() <= 1e-1 * max(np.abs(ref).max(), 1e-12), (l, k_dev)
+    ora.adam(g_ref, lr=lr, eps=agent.adam_eps)
+    for l, (gp, rp) in enumerate(zip(agent.network.get_params(), ora.params)):
+        for k in rp:
+            assert np.abs(gp[k] - rp[k].numpy()).max() <= 0.35 * lr, (l, k)

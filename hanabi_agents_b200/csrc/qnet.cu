@@ -1176,6 +1176,13 @@ int backward_tail_chain(hb_qnet* q, int B, int Bp, cudaStream_t s, int pdl, int*
   Z.flag_base = 2;
   Z.has_consumer = 1;
   Z.b_late = 1;
+  // Both operands that could be requested ahead of a job's wait (W_1^T, X^T) are written by THIS update's side
+  // stream.  They are complete before this launch can start only if that dependency is an ordinary (full)
+  // graph edge; the timelines say it is (the launch always starts when the side stream's last kernel ends),
+  // the documentation does not promise it for a launch with the programmatic attribute -- and requesting
+  // them early bought nothing measurable (72.0 vs 72.1 us).  HB_BWD_CHAIN_EARLY=1 requests them early.
+  static const bool early = getenv("HB_BWD_CHAIN_EARLY") && atoi(getenv("HB_BWD_CHAIN_EARLY")) != 0;
+  Z.no_early = early ? 0 : 1;
   if ((rc = tc::make_tmap(&Z.ta, q->w16t + L1.woff, L1.K, L1.N, L1.N, tc::BM))) return rc;
   if ((rc = tc::make_tmap(&Z.tb, q->dz[1], B, L1.N, L1.N, bn))) return rc;
   if ((rc = tc::out_map<tc::EPI_F16>(&Z.tout, Z.tb, Z.ep))) return rc;
@@ -1197,6 +1204,7 @@ int backward_tail_chain(hb_qnet* q, int B, int Bp, cudaStream_t s, int pdl, int*
   W.dep_arrivals = Z.tiles_n * (bn == 64 ? tc::kEpiWarps / 2 : tc::kEpiWarps);
   W.flag_base = 2 + tiles_m;
   W.has_consumer = 0;
+  W.no_early = Z.no_early;
   W.bias_in = q->bias_part;
   W.bias_parts = (B + 63) / 64;
   W.bias_ld = L0.N;
@@ -1854,7 +1862,6 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     ep.out32 = q->grad + L.eoff;
     ep.ld_out = L.K;
     ep.pdl = on_main ? pdl : 0;
-    ep.b_early = ep.pdl;           // the transposed layer input was complete before the dZ GEMM could start
     const bool have_grads = l == 0 && tail_chained;
     if (!have_grads && (rc = tc::gemm<tc::EPI_F32>(q->dzt[l], Bp, in_t, ld_in_t, L.N, L.K, B, ep, ls))) return rc;
     // (the first layer's bias gradient on the high-priority side stream, idle since the target network's
@@ -1908,7 +1915,6 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
         eb.out16 = q->dzt[0];
         eb.ld_out = Bp;
         eb.pdl = pdl;
-        eb.a_early = pdl;          // the transposed weights (ev_wt) are a full dependency of this launch
         if ((rc = tc::gemm<tc::EPI_F16>(q->w16t + L.woff, L.N, q->dz[1], L.N, L.K, B, L.N, eb, s))) return rc;
       }
     } else if (l > 0 && !(l == nl - 1 && head_bw)) {
@@ -1922,7 +1928,6 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
       eb.out16_t = q->dzt[l - 1];
       eb.ld_out_t = Bp;
       eb.pdl = pdl;
-      eb.b_early = pdl;            // the transposed weights (ev_wt) are a full dependency of this launch
       if ((rc = tc::gemm<tc::EPI_F16>(q->dz[l], L.N, q->w16t + L.woff, L.N, B, L.K, L.N, eb, s))) return rc;
     }
   }

@@ -40,6 +40,8 @@ struct ChainJob {
   // Backward tail (dZ_0^T -> dW_0): the B operand of the first job is what the launch waits for, its A
   // operand (weights) is not
   int b_late;                 // request A ahead of the wait and B behind it (default: the other way round)
+  int no_early;               // nothing ahead of the wait: the operand requested first comes from this launch's
+                              // own dependencies as well
   // The consumer job's tiles of column block 0 also finish the bias gradient from the row sums the
   // producer's epilogue left (EpiParams::row_part): bias_out[m] = bias_alpha * sum_p bias_in[p * ld + m]
   const float* bias_in;
@@ -309,7 +311,7 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
   // The weights do not depend on the launch in front of this one (they were written by the previous
   // update): the first ring-full of B tiles is requested before the wait, while the sample kernel runs.
   const int pre = num_kb < kSt ? num_kb : kSt;
-  if (warp == 0 && lane == 0) {
+  if (warp == 0 && lane == 0 && !job.no_early) {
     for (int kb = 0; kb < pre; ++kb) {
       uint8_t* b_dst = smem + kb * kStB + BM * BK * 2;
       mbar_expect_tx(&full_bar[kb], abits ? (uint32_t)job.bn * BK * 2 : stage_bytes);
@@ -326,6 +328,13 @@ __global__ void __launch_bounds__(kThreads, 1) mlp_chain_kernel(const __grid_con
   if (warp == 0) {
     if (lane == 0) {
       HB_CHAIN_STAMP(0);                                    // dependencies of the launch are complete
+      if (job.no_early) {
+        for (int kb = 0; kb < pre; ++kb) {
+          mbar_expect_tx(&full_bar[kb], abits ? (uint32_t)job.bn * BK * 2 : stage_bytes);
+          if (job.b_late) tma_load_2d(smem + kb * kStB, &job.ta, &full_bar[kb], kb * BK, m0);
+          else tma_load_2d(smem + kb * kStB + BM * BK * 2, &job.tb, &full_bar[kb], kb * BK, n0);
+        }
+      }
       if (job.dep >= 0) {
         const unsigned int launches = *reinterpret_cast<volatile const unsigned int*>(p.state);
         const unsigned int target = (launches + 1u) * (unsigned int)job.dep_arrivals;

@@ -75,7 +75,9 @@ struct EpiParams {
   // stream is still finishing; every global access sits behind griddepcontrol.wait
   int pdl;
   // the B operand does not depend on the kernel this launch waits for (it was complete before that kernel
-  // could start): the first ring-full of B tiles is requested in front of griddepcontrol.wait
+  // could start): the first ring-full of B tiles is requested in front of griddepcontrol.wait.  Only for
+  // operands written before the launch's whole dependency chain began (weights of a previous update); the
+  // learner does not use it (no measurable gain).
   int b_early;
   int a_early;               // the same for the A operand (not both)
   int max_ctas;              // host side only: upper bound of the persistent grid (0: one CTA per SM)

@@ -150,9 +150,11 @@ class HanabiParallelSession:
             net = getattr(getattr(agent, "network", None), "_h", None)
             if net is not None:
                 _lib.check(L.hb_net_set_act_reserve(net, self._reserve))
-            actions = agent.explore(obs)             # enqueued first: the inserts' host waits run under it
-            if net is not None:
-                _lib.check(L.hb_net_set_act_reserve(net, 0))
+            try:
+                actions = agent.explore(obs)         # enqueued first: the inserts' host waits run under it
+            finally:
+                if net is not None:
+                    _lib.check(L.hb_net_set_act_reserve(net, 0))
             seats = [j for j in [k] + [j for j in range(self.P) if j != k]
                      if self.agents[j].requires_vectorized_observation()]
             split = (len(set(id(self.agents[j]) for j in seats)) == len(seats) and

@@ -80,6 +80,7 @@ SIGNATURES = {
     "hb_rules_act": (i32, [vp, vp, vp, vp, i32, u64, u64, vp, vp, vp, vp]),
     "hb_env_selfplay": (i32, [vp, vp, vp, vp, i32, u64, u64, i32, vp, vp, vp, vp, vp, vp, vp]),
     "hb_st_update_range_dev": (i32, [vp, i64, i64, vp, vp]),
+    "hb_st_update_range_indirect": (i32, [vp, vp, i64, vp, vp]),
     # replay shard
     "hb_rb_create": (i32, [i32, i32, i32, i64, i32, f32, i32, C.POINTER(vp)]),
     "hb_rb_destroy": (i32, [vp]),
@@ -89,6 +90,7 @@ SIGNATURES = {
     "hb_rb_store_first": (i32, [vp, vp, vp, vp, i64, vp]),
     "hb_rb_add_masked": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), vp]),
     "hb_rb_add_masked_begin": (i32, [vp, vp, i64, vp]),
+    "hb_rb_add_masked_async": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, vp]),
     "hb_rb_add_masked_finish": (i32, [vp, vp, vp, vp, vp, vp, vp, i64, C.POINTER(i64), vp]),
     "hb_rb_gather": (i32, [vp, vp, i64, vp, vp, vp, vp, vp, vp, vp]),
     "hb_rb_check": (i32, [vp, vp]),

@@ -43,6 +43,19 @@ struct hb_replay {
   int64_t vals_gen = 0;
   float* vals_retired[16] = {nullptr};
   int n_retired = 0;
+  // Device-side ring cursor (hb_rb_add_masked_async): d_cur = {oldest, size, write base of the current
+  // append, its row count, range 0 {start, n}, range 1 {start, n}}.  While cur_on_device the host fields
+  // `oldest` / `size` are stale; pull_cursor() brings them back (one stream synchronisation).
+  int64_t* d_cur = nullptr;
+  int64_t* h_cur = nullptr;           // pinned
+  bool cur_on_device = false;
+  cudaStream_t cur_stream = nullptr;
+  // a copy of the cursor follows every asynchronous append to the host WITHOUT being waited for; when the
+  // previous append's copy has arrived by the time of the next one, the host knows where that one starts
+  // and skips the launches of the wrapped-around range when it cannot wrap
+  int64_t* h_peek = nullptr;          // pinned: {oldest, size} after the last asynchronous append
+  cudaEvent_t ev_peek = nullptr;
+  bool peek_valid = false;            // a copy is in flight or has arrived, and nothing was appended since
 };
 
 namespace {
@@ -100,9 +113,10 @@ __global__ void __launch_bounds__(kScanBlock)
 masked_append_kernel(hb_replay rb, uint32_t* __restrict__ last_obs, const uint32_t* __restrict__ obs,
                      const uint32_t* __restrict__ lms, const int32_t* __restrict__ act,
                      const float* __restrict__ rew, const uint8_t* __restrict__ step_type, int64_t n,
-                     const int32_t* __restrict__ block_off) {
+                     const int32_t* __restrict__ block_off, const int64_t* __restrict__ d_cur = nullptr) {
   __shared__ int warp_off[32];
   __shared__ int64_t dst_row[kScanBlock];          // ring position of each selected row, -1 otherwise
+  const int64_t write_base = d_cur != nullptr ? d_cur[2] : rb.oldest;   // device-side cursor (async form)
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int64_t row0 = (int64_t)blockIdx.x * kScanBlock;
   const int64_t i = row0 + threadIdx.x;
@@ -123,7 +137,7 @@ masked_append_kernel(hb_replay rb, uint32_t* __restrict__ last_obs, const uint32
   __syncthreads();
   int64_t pos = -1;
   if (sel) {
-    pos = rb.oldest + block_off[blockIdx.x] + warp_off[warp] + __popc(b & ((1u << lane) - 1));
+    pos = write_base + block_off[blockIdx.x] + warp_off[warp] + __popc(b & ((1u << lane) - 1));
     if (pos >= rb.cap) pos -= rb.cap;                       // ring wrap (experience_buffer.py:62-81)
     for (int w = 0; w < rb.legal_words; ++w) rb.lms[pos * rb.legal_words + w] = lms[i * rb.legal_words + w];
     rb.act[pos] = act[i];
@@ -427,6 +441,47 @@ void advance(hb_replay* rb, int64_t n) {
   }
 }
 
+// The same bookkeeping on the device (one thread): cur = {oldest, size, write base, count, range 0, range 1}.
+// The ranges are the sum-tree leaves of the rows about to be written, [oldest, cap) then [0, tail).
+__global__ void cursor_kernel(int64_t* __restrict__ cur, const int32_t* __restrict__ total, int64_t cap) {
+  const int64_t n = *total;
+  int64_t oldest = cur[0], size = cur[1];
+  cur[2] = oldest;
+  cur[3] = n;
+  const int64_t first = oldest + n <= cap ? n : cap - oldest;
+  cur[4] = oldest; cur[5] = first;
+  cur[6] = 0;      cur[7] = n - first;
+  if (n > 0) {                                   // advance(), word for word
+    if (oldest + n <= cap) {
+      if (oldest + n == cap) size = cap;
+      oldest = (oldest + n) % cap;
+      if (oldest > size) size = oldest;
+    } else {
+      oldest = oldest + n - cap;
+      size = cap;
+    }
+  }
+  cur[0] = oldest;
+  cur[1] = size;
+}
+__global__ void cursor_set_kernel(int64_t* __restrict__ cur, int64_t oldest, int64_t size) {
+  cur[0] = oldest;
+  cur[1] = size;
+}
+
+// host fields <- device cursor (after asynchronous appends); every host-side use of oldest / size starts here
+int pull_cursor(hb_replay* rb) {
+  if (!rb->cur_on_device) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  HB_CUDA(cudaMemcpyAsync(rb->h_cur, rb->d_cur, 16, cudaMemcpyDeviceToHost, rb->cur_stream));
+  HB_CUDA(cudaStreamSynchronize(rb->cur_stream));
+  rb->oldest = rb->h_cur[0];
+  rb->size = rb->h_cur[1];
+  rb->cur_on_device = false;
+  rb->peek_valid = false;
+  return HB_OK;
+}
+
 // PriorityBuffer.add_transitions: leaves of the rows about to be written take max_priority, in the
 // order of get_update_indices (experience_buffer.py:21-24): [oldest, cap) then [0, tail).
 int insert_priorities(hb_replay* rb, int64_t n, cudaStream_t s) {
@@ -474,6 +529,11 @@ int hb_rb_create(int obs_len, int obs_stride_words, int num_moves, int64_t capac
   if (e == cudaSuccess) e = cudaMalloc(&rb->term, c);
   if (e == cudaSuccess) e = cudaMalloc(&rb->total, 4);
   if (e == cudaSuccess) e = cudaMallocHost(&rb->h_total, 4);
+  if (e == cudaSuccess) e = cudaMalloc(&rb->d_cur, 8 * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaMemset(rb->d_cur, 0, 8 * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaMallocHost(&rb->h_cur, 2 * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaMallocHost(&rb->h_peek, 2 * sizeof(int64_t));
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&rb->ev_peek, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaMalloc(&rb->prio_range, 12);
   if (e == cudaSuccess) {
     // np.empty in the reference; zero here so that unwritten rows are defined
@@ -510,6 +570,10 @@ int hb_rb_destroy(hb_replay* rb) {
   if (rb->term) cudaFree(rb->term);
   if (rb->total) cudaFree(rb->total);
   if (rb->h_total) cudaFreeHost(rb->h_total);
+  if (rb->d_cur) cudaFree(rb->d_cur);
+  if (rb->h_cur) cudaFreeHost(rb->h_cur);
+  if (rb->h_peek) cudaFreeHost(rb->h_peek);
+  if (rb->ev_peek) cudaEventDestroy(rb->ev_peek);
   if (rb->prio_range) cudaFree(rb->prio_range);
   if (rb->block_sum) cudaFree(rb->block_sum);
   if (rb->vals) cudaFree(rb->vals);
@@ -521,6 +585,7 @@ int hb_rb_destroy(hb_replay* rb) {
 
 int64_t hb_rb_info(const hb_replay* rb, int what) {
   if (!rb) return -1;
+  if ((what == 1 || what == 2) && pull_cursor(const_cast<hb_replay*>(rb))) return -1;
   switch (what) {
     case 0: return rb->cap;
     case 1: return rb->size;
@@ -544,7 +609,9 @@ int hb_rb_add(hb_replay* rb, const uint32_t* d_obs_tm1, const int32_t* d_act, co
   HB_REQUIRE(n <= rb->cap, "hb_rb_add: %lld rows exceed the capacity %lld", (long long)n, (long long)rb->cap);
   hb::DeviceGuard g(rb->device);
   cudaStream_t s = (cudaStream_t)stream;
-  int rc = insert_priorities(rb, n, s);
+  int rc = pull_cursor(rb);
+  if (rc) return rc;
+  rc = insert_priorities(rb, n, s);
   if (rc) return rc;
   append_kernel<<<(unsigned)((n + 7) / 8), 256, 0, s>>>(*rb, d_obs_tm1, d_act, d_rew, d_obs_t, d_lms,
                                                        d_term, n);
@@ -605,6 +672,10 @@ int hb_rb_add_masked_finish(hb_replay* rb, uint32_t* d_last_obs, const uint32_t*
   const int64_t n_blocks = (n + kScanBlock - 1) / kScanBlock;
   HB_REQUIRE(rb->scan_n >= n_blocks, "hb_rb_add_masked_finish: no matching hb_rb_add_masked_begin");
   HB_CUDA(cudaStreamSynchronize(s));       // the ring cursor lives on the host, as in the reference
+  {
+    const int prc = pull_cursor(rb);       // ... unless asynchronous appends moved it to the device
+    if (prc) return prc;
+  }
   const int64_t cnt = *rb->h_total;
   if (n_added) *n_added = cnt;
   if (cnt == 0) return HB_OK;
@@ -628,6 +699,71 @@ int hb_rb_add_masked(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs,
   int rc = hb_rb_add_masked_begin(rb, d_step_type, n, stream);
   if (rc) return rc;
   return hb_rb_add_masked_finish(rb, d_last_obs, d_obs, d_lms, d_act, d_rew, d_step_type, n, n_added, stream);
+}
+
+/* hb_rb_add_masked without the host in the loop: the number of appended rows never travels to the host.  The
+ * ring cursor moves to device memory (cursor_kernel), the sum-tree leaves of the new rows are set through
+ * hb_st_update_range_indirect, the append reads its write position from the device.  The host's view of
+ * size / oldest_entry (hb_rb_info, hb_rb_add, hb_rb_add_masked) is refreshed on demand, with one stream
+ * synchronisation.  Same results as hb_rb_add_masked, bit for bit (tests/test_replay_gpu.py). */
+int hb_rb_add_masked_async(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                           const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                           void* stream) {
+  HB_REQUIRE(rb && d_last_obs && d_obs && d_lms && d_act && d_rew && d_step_type && n >= 0,
+             "hb_rb_add_masked_async: bad arguments");
+  HB_REQUIRE((((uintptr_t)d_last_obs | (uintptr_t)d_obs) & 15) == 0,
+             "hb_rb_add_masked_async: rows must be 16-byte aligned");
+  HB_REQUIRE(n <= rb->cap, "hb_rb_add_masked_async: %lld rows exceed the capacity %lld", (long long)n,
+             (long long)rb->cap);
+  if (n == 0) return HB_OK;
+  hb::DeviceGuard g(rb->device);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int64_t n_blocks = (n + kScanBlock - 1) / kScanBlock;
+  if (rb->scan_n < n_blocks) {
+    HB_CUDA(cudaStreamSynchronize(s));
+    if (rb->block_sum) cudaFree(rb->block_sum);
+    rb->block_sum = nullptr;
+    rb->scan_n = 0;
+    HB_CUDA(cudaMalloc(&rb->block_sum, sizeof(int32_t) * n_blocks));
+    rb->scan_n = n_blocks;
+  }
+  // can the rows of this call wrap around the end of the ring?  Known when the host's cursor is current, or
+  // when the copy that followed the previous asynchronous append has arrived; assumed otherwise.
+  bool may_wrap = true;
+  if (!rb->cur_on_device) may_wrap = rb->oldest + n > rb->cap;
+  else if (rb->peek_valid && cudaEventQuery(rb->ev_peek) == cudaSuccess) may_wrap = rb->h_peek[0] + n > rb->cap;
+  else (void)cudaGetLastError();             // cudaErrorNotReady is not an error
+  if (!rb->cur_on_device) {                  // the host's cursor is the current one: hand it over
+    cursor_set_kernel<<<1, 1, 0, s>>>(rb->d_cur, rb->oldest, rb->size);
+    HB_CUDA(cudaGetLastError());
+    rb->cur_on_device = true;
+  } else if (rb->cur_stream != s) {
+    // appends of one shard are ordered by the caller; a change of stream is ordered here
+    HB_CUDA(cudaStreamSynchronize(rb->cur_stream));
+  }
+  rb->cur_stream = s;
+  mask_count_kernel<<<(unsigned)n_blocks, kScanBlock, 0, s>>>(d_step_type, n, rb->block_sum);
+  HB_CUDA(cudaGetLastError());
+  mask_scan_kernel<<<1, kScanBlock, 0, s>>>(rb->block_sum, (int)n_blocks, rb->total);
+  HB_CUDA(cudaGetLastError());
+  cursor_kernel<<<1, 1, 0, s>>>(rb->d_cur, rb->total, rb->cap);
+  HB_CUDA(cudaGetLastError());
+  if (rb->prioritized) {
+    const float* fill = rb->fixed_insert ? rb->prio_range + 2 : rb->prio_range;
+    int rc = hb_st_update_range_indirect(rb->tree, rb->d_cur + 4, n, fill, s);
+    if (rc) return rc;
+    if (may_wrap) {                          // [0, tail): four launches that do nothing when there is no tail
+      rc = hb_st_update_range_indirect(rb->tree, rb->d_cur + 6, n, fill, s);
+      if (rc) return rc;
+    }
+  }
+  masked_append_kernel<<<(unsigned)n_blocks, kScanBlock, 0, s>>>(*rb, d_last_obs, d_obs, d_lms, d_act,
+                                                                d_rew, d_step_type, n, rb->block_sum, rb->d_cur);
+  HB_CUDA(cudaGetLastError());
+  HB_CUDA(cudaMemcpyAsync(rb->h_peek, rb->d_cur, 16, cudaMemcpyDeviceToHost, s));   // not waited for
+  HB_CUDA(cudaEventRecord(rb->ev_peek, s));
+  rb->peek_valid = true;
+  return HB_OK;
 }
 
 int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,

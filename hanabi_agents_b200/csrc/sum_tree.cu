@@ -236,7 +236,9 @@ st_update_kernel(float* __restrict__ heap, int depth, int64_t cap,
 // ---- ordered update of a contiguous ascending leaf range (PB-3 inserts) ----
 __global__ void st_range_leaf_kernel(float* __restrict__ heap, int64_t cap, int64_t start,
                                      int64_t n, const float* __restrict__ val, float fill,
-                                     const float* __restrict__ fill_dev, float* __restrict__ diff) {
+                                     const float* __restrict__ fill_dev, float* __restrict__ diff,
+                                     const int64_t* __restrict__ rng = nullptr) {
+  if (rng != nullptr) { start = rng[0]; n = rng[1]; }    // bounds from device memory (hb_st_update_range_indirect)
   const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
   float* leaf = heap + cap + start + k;
@@ -251,7 +253,9 @@ __global__ void st_range_leaf_kernel(float* __restrict__ heap, int64_t cap, int6
 // diffs of its covered leaves in ascending (= batch) order.
 __global__ void st_range_internal_kernel(float* __restrict__ heap, int depth, int64_t cap,
                                          int64_t start, int64_t n,
-                                         const float* __restrict__ diff, int level0) {
+                                         const float* __restrict__ diff, int level0,
+                                         const int64_t* __restrict__ rng = nullptr) {
+  if (rng != nullptr) { start = rng[0]; n = rng[1]; if (n <= 0) return; }
   const int l = blockIdx.y + level0;
   const int shift = depth - l;
   const int64_t first = (cap + start) >> shift;
@@ -284,7 +288,9 @@ __global__ void st_range_internal_kernel(float* __restrict__ heap, int depth, in
 // of load latency (a 65,536-row insert: 1.0 ms -> ~0.2 ms).  blockIdx.y = level (0 = root).
 __global__ void st_range_internal_warp_kernel(float* __restrict__ heap, int depth, int64_t cap,
                                               int64_t start, int64_t n,
-                                              const float* __restrict__ diff, int level0) {
+                                              const float* __restrict__ diff, int level0,
+                                              const int64_t* __restrict__ rng = nullptr) {
+  if (rng != nullptr) { start = rng[0]; n = rng[1]; if (n <= 0) return; }
   const int l = blockIdx.y + level0;
   const int shift = depth - l;
   const int lane = threadIdx.x & 31;
@@ -384,7 +390,9 @@ __device__ __forceinline__ float warp_chain(float s, const float* __restrict__ d
 
 __global__ void __launch_bounds__(kScanThreads)
 st_range_internal_scan_kernel(float* __restrict__ heap, int depth, int64_t cap, int64_t start,
-                              int64_t n, const float* __restrict__ diff) {
+                              int64_t n, const float* __restrict__ diff,
+                              const int64_t* __restrict__ rng = nullptr) {
+  if (rng != nullptr) { start = rng[0]; n = rng[1]; if (n <= 0) return; }
   const int l = blockIdx.y;
   const int shift = depth - l;
   const int64_t first = (cap + start) >> shift;
@@ -605,7 +613,7 @@ int hb_st_update(hb_sumtree* t, const int64_t* d_idx, const float* d_val, int64_
 }
 
 static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const float* d_val,
-                                float fill, const float* d_fill, void* stream);
+                                float fill, const float* d_fill, void* stream, const int64_t* d_rng = nullptr);
 
 int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_val, float fill,
                        void* stream) {
@@ -618,11 +626,23 @@ int hb_st_update_range_dev(hb_sumtree* t, int64_t start, int64_t n, const float*
   return st_update_range_impl(t, start, n, nullptr, 0.f, d_fill, stream);
 }
 
+// d_rng != nullptr: the range is {start, n} in DEVICE memory (n <= the argument n, which then only sizes the
+// grids and the scratch; inside the capacity by the caller's construction).
+/* hb_st_update_range_dev with the range itself in device memory: d_rng = {start, n}, n <= n_max (n_max sizes
+ * the launches; n = 0 is a no-op on the device).  For callers whose range is produced by a kernel (the replay
+ * shard's device-side ring cursor): no host round trip between that kernel and the update. */
+int hb_st_update_range_indirect(hb_sumtree* t, const int64_t* d_rng, int64_t n_max, const float* d_fill,
+                                void* stream) {
+  HB_REQUIRE(d_rng != nullptr && d_fill != nullptr && n_max >= 0, "hb_st_update_range_indirect: bad arguments");
+  HB_REQUIRE(t && n_max <= t->cap, "hb_st_update_range_indirect: n_max beyond the capacity");
+  return st_update_range_impl(t, 0, n_max, nullptr, 0.f, d_fill, stream, d_rng);
+}
+
 static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const float* d_val,
-                                float fill, const float* d_fill, void* stream) {
+                                float fill, const float* d_fill, void* stream, const int64_t* d_rng) {
   HB_REQUIRE(t && n >= 0, "hb_st_update_range: bad arguments");
   if (n == 0) return HB_OK;
-  if (start < 0 || start + n > t->cap) {
+  if (d_rng == nullptr && (start < 0 || start + n > t->cap)) {
     hb::set_error("hb_st_update_range: [%lld,%lld) outside capacity %lld", (long long)start,
                   (long long)(start + n), (long long)t->cap);
     return HB_ERR_INDEX;
@@ -639,7 +659,7 @@ static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const f
   }
   const int threads = 256;
   st_range_leaf_kernel<<<(unsigned)((n + threads - 1) / threads), threads, 0, s>>>(
-      t->heap, t->cap, start, n, d_val, fill, d_fill, t->scratch);
+      t->heap, t->cap, start, n, d_val, fill, d_fill, t->scratch, d_rng);
   HB_CUDA(cudaGetLastError());
   if (t->depth > 0) {
     // levels whose nodes cover >= 2048 leaves: CTA per node, ordered sum as a scan;
@@ -650,21 +670,21 @@ static int st_update_range_impl(hb_sumtree* t, int64_t start, int64_t n, const f
       const int64_t widest = (n >> kScanSpanLog2) + 2;
       dim3 grid((unsigned)widest, (unsigned)scan_levels);
       st_range_internal_scan_kernel<<<grid, kScanThreads, 0, s>>>(t->heap, t->depth, t->cap, start, n,
-                                                                   t->scratch);
+                                                                   t->scratch, d_rng);
       HB_CUDA(cudaGetLastError());
     }
     if (warp_levels > 0) {
       const int64_t widest = n / 64 + 2;
       dim3 grid((unsigned)((widest + 3) / 4), (unsigned)warp_levels);
       st_range_internal_warp_kernel<<<grid, 128, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch,
-                                                         scan_levels);
+                                                         scan_levels, d_rng);
       HB_CUDA(cudaGetLastError());
     }
     const int upper = scan_levels + warp_levels;
     const int64_t widest = n / 2 + 2;  // nodes covered at the deepest internal level
     const int th = 128;
     dim3 grid((unsigned)((widest + th - 1) / th), (unsigned)(t->depth - upper));
-    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch, upper);
+    st_range_internal_kernel<<<grid, th, 0, s>>>(t->heap, t->depth, t->cap, start, n, t->scratch, upper, d_rng);
     HB_CUDA(cudaGetLastError());
   }
   return HB_OK;

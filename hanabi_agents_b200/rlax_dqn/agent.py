@@ -108,6 +108,13 @@ class DQNAgent:
                                           self._dev(rewards, torch.float32),
                                           self._dev(step_types, torch.uint8))
 
+    def add_experience_async(self, observations, actions, rewards, step_types):
+        """add_experience without the count coming back to the host (no synchronisation); returns None."""
+        torch = self.torch
+        obs, legal, _ = self._pack_pair(observations)
+        self.experience.add_masked_async(self.last_obs, obs, legal, self._dev(actions, torch.int32),
+                                         self._dev(rewards, torch.float32), self._dev(step_types, torch.uint8))
+
     def add_experience_begin(self, observations, step_types):
         """add_experience in two halves (the session starts every seat's row count before it waits for the
         first): begin on the current stream, add_experience_finish with the same arguments on the same one."""

@@ -142,6 +142,13 @@ class ExperienceBuffer:
             rewards.data_ptr(), step_types.data_ptr(), obs.shape[0], C.byref(n_added), self._s()))
         return int(n_added.value)
 
+    def add_masked_async(self, last_obs, obs, legal, actions, rewards, step_types):
+        """add_masked without a host round trip (hb_rb_add_masked_async): nothing is returned; `size` and
+        `oldest_entry` catch up when they are next read."""
+        _lib.check(_lib.lib().hb_rb_add_masked_async(
+            self._h, last_obs.data_ptr(), obs.data_ptr(), legal.data_ptr(), actions.data_ptr(),
+            rewards.data_ptr(), step_types.data_ptr(), obs.shape[0], self._s()))
+
     def store_first(self, last_obs, obs, step_types):
         _lib.check(_lib.lib().hb_rb_store_first(self._h, last_obs.data_ptr(), obs.data_ptr(),
                                                 step_types.data_ptr(), obs.shape[0], self._s()))

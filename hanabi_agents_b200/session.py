@@ -74,6 +74,8 @@ class HanabiParallelSession:
         self._ins_event = None
         self._seat_streams = []
         self._reserve = int(os.environ.get("HB_SESSION_RESERVE_SMS", "32"))
+        # HB_SESSION_ASYNC_INSERT=0: the inserts report their row counts to the host (two waits per tick)
+        self._async_inserts = os.environ.get("HB_SESSION_ASYNC_INSERT", "1") != "0"
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -169,6 +171,7 @@ class HanabiParallelSession:
                 while len(self._seat_streams) < self.P:
                     self._seat_streams.append(torch.cuda.Stream(device=env.device))
                 seat_obs = {}
+                nosync = self._async_inserts and all(hasattr(self.agents[j], "add_experience_async") for j in seats)
                 for j in seats:
                     with torch.cuda.stream(self._seat_streams[j]):
                         self._seat_streams[j].wait_event(self._ins_event)
@@ -177,11 +180,18 @@ class HanabiParallelSession:
                             seat_obs[j] = obs
                         else:
                             seat_obs[j] = self._obs_for(self.agents[j], (j - k) % self.P)
-                        self.agents[j].add_experience_begin(seat_obs[j], self.step_types[j])
-                for j in seats:
-                    with torch.cuda.stream(self._seat_streams[j]):
-                        self.agents[j].add_experience_finish(seat_obs[j], self.last_action[j],
-                                                             self.reward_since_last_action[j], self.step_types[j])
+                        if nosync:   # ring cursor on the device: the tick has no host wait at all
+                            self.agents[j].add_experience_async(seat_obs[j], self.last_action[j],
+                                                                self.reward_since_last_action[j],
+                                                                self.step_types[j])
+                        else:
+                            self.agents[j].add_experience_begin(seat_obs[j], self.step_types[j])
+                if not nosync:
+                    for j in seats:
+                        with torch.cuda.stream(self._seat_streams[j]):
+                            self.agents[j].add_experience_finish(seat_obs[j], self.last_action[j],
+                                                                 self.reward_since_last_action[j],
+                                                                 self.step_types[j])
                 for j in seats:
                     main.wait_stream(self._seat_streams[j])
         elif train:

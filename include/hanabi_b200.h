@@ -77,6 +77,11 @@ int hb_st_update_range(hb_sumtree* t, int64_t start, int64_t n, const float* d_v
  * max_priority on the device: priority_buffer.py:29-31 without a host round trip). */
 int hb_st_update_range_dev(hb_sumtree* t, int64_t start, int64_t n, const float* d_fill,
                            void* stream);
+/* The same with the range itself in device memory, d_rng = {start, n} with n <= n_max (n_max sizes the
+ * launches; n = 0: nothing changes).  No counterpart in the reference (its tree is host code); used by
+ * hb_rb_add_masked_async, whose ring cursor lives on the device. */
+int hb_st_update_range_indirect(hb_sumtree* t, const int64_t* d_rng, int64_t n_max, const float* d_fill,
+                                void* stream);
 /* hb_st_update_range without any allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
  * serving loops, harnesses that forbid it).  Same kernels and the same bits as hb_st_update_range; the
@@ -265,6 +270,14 @@ int hb_rb_add_masked_begin(hb_replay* rb, const uint8_t* d_step_type, int64_t n,
 int hb_rb_add_masked_finish(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
                             const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
                             int64_t* n_added, void* stream);
+/* hb_rb_add_masked with nothing coming back to the host: the ring cursor moves to device memory, the count
+ * of appended rows is never read by the host, no call in it synchronises.  The host-side view of size /
+ * oldest_entry (hb_rb_info 1, 2; hb_rb_add; hb_rb_add_masked) is refreshed on demand.  Bit-identical shard
+ * and tree.  No counterpart in the reference (its buffer is host code): what the self-play session uses for
+ * its per-tick inserts. */
+int hb_rb_add_masked_async(hb_replay* rb, uint32_t* d_last_obs, const uint32_t* d_obs, const uint32_t* d_lms,
+                           const int32_t* d_act, const float* d_rew, const uint8_t* d_step_type, int64_t n,
+                           void* stream);
 /* __getitem__(indices) (experience_buffer.py:83-87); any output may be NULL. */
 int hb_rb_gather(hb_replay* rb, const int64_t* d_idx, int64_t n, uint32_t* d_obs_tm1, int32_t* d_act,
                  float* d_rew, uint32_t* d_obs_t, uint32_t* d_lms, uint8_t* d_term, void* stream);

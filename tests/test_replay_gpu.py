@@ -89,7 +89,7 @@ def test_masked_append_matches_add_experience():
     last_obs = np.zeros((N, L), np.int8)
     d_last = torch.zeros((N, dev.obs_stride), dtype=torch.int32, device="cuda")
     to_dev = lambda a: torch.as_tensor(a, device="cuda")  # noqa: E731
-    for it in range(6):
+    for it in range(9):
         obs = (rng.random((N, L)) < .2).astype(np.int8)
         legal = (rng.random((N, A)) < .5).astype(np.int8)
         act = rng.integers(0, A, N).astype(np.int32)
@@ -105,18 +105,45 @@ def test_masked_append_matches_add_experience():
                                 legal[nf], (st[nf] == 2).reshape(-1, 1))
             last_obs[nf] = obs[nf]
         last_obs[first] = obs[first]
-        # device: in one call, or in the two halves the session uses (hb_rb_add_masked_begin / _finish)
-        if it % 2 == 0:
+        # device: in one call, in the two halves (hb_rb_add_masked_begin / _finish), or without the host in
+        # the loop (hb_rb_add_masked_async: the ring cursor lives on the device until somebody asks)
+        if it % 3 == 0:
             n_added = dev.add_masked(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
-        else:
+        elif it % 3 == 1:
             d_st = to_dev(st)
             dev.add_masked_begin(d_st, N)
             n_added = dev.add_masked_finish(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), d_st)
+        else:
+            dev.add_masked_async(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
+            n_added = int(nf.sum())          # (nothing is returned; size / oldest_entry are checked below)
         dev.store_first(d_last, d_obs, to_dev(st))
         assert n_added == int(nf.sum())
         assert (dev.size, dev.oldest_entry) == (ora.size, ora.oldest_entry)
         np.testing.assert_array_equal(dev.unpack_obs(d_last).cpu().numpy(), last_obs)
         np.testing.assert_array_equal(dev.sum_tree.heap()[1:], ora.sum_tree.heap()[1:])
+    # a run of asynchronous appends with nothing read back in between (the device-side cursor carries the
+    # ring position from one to the next, around the end of the ring as well; with and without the copy of
+    # the cursor having reached the host before the next call)
+    for it in range(7):
+        obs = (rng.random((N, L)) < .2).astype(np.int8)
+        legal = (rng.random((N, A)) < .5).astype(np.int8)
+        act = rng.integers(0, A, N).astype(np.int32)
+        rew = rng.integers(-2, 2, N).astype(np.float32)
+        st = rng.choice([0, 0, 0, 1, 2], N).astype(np.uint8)
+        d_obs = to_dev(pack_bits(obs, dev.obs_stride).view(np.int32))
+        d_leg = to_dev(pack_bits(legal, dev.legal_words).view(np.int32))
+        first, nf = st == 0, st != 0
+        ora.add_transitions(last_obs[nf], act[nf].reshape(-1, 1), rew[nf].reshape(-1, 1), obs[nf], legal[nf],
+                            (st[nf] == 2).reshape(-1, 1))
+        last_obs[nf] = obs[nf]
+        last_obs[first] = obs[first]
+        dev.add_masked_async(d_last, d_obs, d_leg, to_dev(act), to_dev(rew), to_dev(st))
+        dev.store_first(d_last, d_obs, to_dev(st))
+        if it % 2:
+            torch.cuda.synchronize()
+    assert (dev.size, dev.oldest_entry) == (ora.size, ora.oldest_entry)
+    np.testing.assert_array_equal(dev.unpack_obs(d_last).cpu().numpy(), last_obs)
+    np.testing.assert_array_equal(dev.sum_tree.heap()[1:], ora.sum_tree.heap()[1:])
     got = _all_rows(dev)
     np.testing.assert_array_equal(got["obs_tm1"], ora._obs_tm1_buf)
     np.testing.assert_array_equal(got["obs_t"], ora._obs_t_buf)

@@ -196,6 +196,24 @@ def check(rc):
 
 
 _raw_stream = None
+_stream_override = []
+
+
+class use_stream:
+    """`with _lib.use_stream(ptr):` -- the library's launches inside go to that cudaStream_t instead of torch's
+    current stream.  What `torch.cuda.stream(s)` does for this library's calls at a twentieth of the cost (that
+    context manager was 30 us of a 250 us session tick); torch's own allocations and kernels are NOT moved."""
+
+    def __init__(self, stream_ptr):
+        self.ptr = int(stream_ptr)
+
+    def __enter__(self):
+        _stream_override.append(self.ptr)
+        return self
+
+    def __exit__(self, *exc):
+        _stream_override.pop()
+        return False
 
 
 def current_stream_ptr():
@@ -203,6 +221,8 @@ def current_stream_ptr():
     accessor when it has one: `torch.cuda.current_stream()` builds a Stream object and resolves the
     device by name every time, ~5 us a call and ten calls per session tick."""
     global _raw_stream
+    if _stream_override:
+        return _stream_override[-1]
     import torch
     if _raw_stream is None:
         fn = getattr(torch._C, "_cuda_getCurrentRawStream", None)

@@ -68,12 +68,12 @@ class HanabiParallelSession:
         # updates, two host round trips for the row counts) do not feed the move that is chosen in it, so
         # they run on a second stream beside the acting pass (HB_SESSION_OVERLAP=0: one after the other, the
         # reference's order of calls).  The acting GEMMs are persistent CTAs that take whole SMs: they leave
-        # HB_SESSION_RESERVE_SMS (default 32 of the 148) of them to the inserts, for that call only.
+        # HB_SESSION_RESERVE_SMS (default 16 of the 148) of them to the inserts, for that call only.
         self._overlap = os.environ.get("HB_SESSION_OVERLAP", "1") != "0"
         self._ins_stream = None
         self._ins_event = None
         self._seat_streams = []
-        self._reserve = int(os.environ.get("HB_SESSION_RESERVE_SMS", "32"))
+        self._reserve = int(os.environ.get("HB_SESSION_RESERVE_SMS", "16"))
         # HB_SESSION_ASYNC_INSERT=0: the inserts report their row counts to the host (two waits per tick)
         self._async_inserts = os.environ.get("HB_SESSION_ASYNC_INSERT", "1") != "0"
 
@@ -170,10 +170,17 @@ class HanabiParallelSession:
                 # one stream per seat; every seat's row count is started before the host waits for the first
                 while len(self._seat_streams) < self.P:
                     self._seat_streams.append(torch.cuda.Stream(device=env.device))
+                # the environment's packed device rows need no torch work on the way in: the library's launches
+                # are pointed at the seat's stream directly (torch.cuda.stream(...) costs 15 us a time)
+                packed = obs[1] is not None and getattr(obs[1][0], "is_cuda", False) and obs[1][0].dtype == torch.int32
+
+                def on(j):
+                    st = self._seat_streams[j]
+                    return _lib.use_stream(st.cuda_stream) if packed else torch.cuda.stream(st)
                 seat_obs = {}
                 nosync = self._async_inserts and all(hasattr(self.agents[j], "add_experience_async") for j in seats)
                 for j in seats:
-                    with torch.cuda.stream(self._seat_streams[j]):
+                    with on(j):
                         self._seat_streams[j].wait_event(self._ins_event)
                         if j == k:
                             agent.add_experience_first(obs, self.step_types[k])
@@ -188,7 +195,7 @@ class HanabiParallelSession:
                             self.agents[j].add_experience_begin(seat_obs[j], self.step_types[j])
                 if not nosync:
                     for j in seats:
-                        with torch.cuda.stream(self._seat_streams[j]):
+                        with on(j):
                             self.agents[j].add_experience_finish(seat_obs[j], self.last_action[j],
                                                                  self.reward_since_last_action[j],
                                                                  self.step_types[j])

@@ -254,7 +254,7 @@ class HanabiParallelSession:
             self._seat_streams.append(torch.cuda.Stream(device=self.env.device))
         self._ins_event.record(main)
         for i, a in enumerate(ls):
-            with torch.cuda.stream(self._seat_streams[i]):
+            with _lib.use_stream(self._seat_streams[i].cuda_stream):   # update() launches through the library only
                 self._seat_streams[i].wait_event(self._ins_event)
                 a.update()
         for i in range(len(ls)):

@@ -1,1 +1,3 @@
-for r in 8 16 24 32 48; do echo "reserve $r"; HB_SESSION_RESERVE_SMS=$r timeout 600 python tools/session_trace.py train 2>&1 | grep -E "tick:"; done
+timeout 900 python -m pytest tests/test_session_gpu.py tests/test_agent_gpu.py -m gpu -x -q 2>&1 | tail -3
+timeout 600 python tools/session_trace.py learn 2>&1 | grep -E "tick:"
+timeout 600 python tools/session_trace.py train 2>&1 | grep -E "tick:"

@@ -487,8 +487,13 @@ __device__ __forceinline__ void epilogue_tile(uint32_t tmem_base, uint32_t acc_c
 // CTAs working at the same time share A tiles through L2).  The TMEM accumulator is double
 // buffered: the MMA warp fills buffer (i & 1) of its i-th tile while the epilogue warps drain the
 // other one.
+// ABITS kernels carry more warps behind the epilogue's: further pairs of expanding warps, each taking every
+// kAbitsPairs-th k-block.
+constexpr int kAbitsPairs = 2;   // pairs of expanding warps in an ABITS kernel (warps 2-3, then 12-13, 14-15)
+__host__ __device__ constexpr int threads_for(bool abits) { return abits ? kThreads + 64 * (kAbitsPairs - 1) : kThreads; }
+
 template <int EPI, int BN_, bool ABITS>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(threads_for(ABITS), 1)
 gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b,
                 const __grid_constant__ CUtensorMap tmap_out, int K, EpiParams ep) {
   constexpr int kSt = stages_for(BN_);
@@ -596,16 +601,21 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         umma_commit(&acc_full[buf]);                 // accumulator complete
       }
     }
-  } else if (ABITS && (warp == 2 || warp == 3)) {
+  } else if (ABITS && (warp == 2 || warp == 3 || warp >= 12)) {
     // A operand straight from the bit-packed observation rows: thread p owns rows p and p + 64 of
     // the tile, keeps their packed words in registers and expands 8 bits -> 8 fp16 (one 16-byte
     // chunk) at a time into the 128-byte-swizzled layout the MMA descriptor expects
     // (chunk c of row r at r*128 + ((c ^ (r & 7)) << 4)).
-    const int p = (warp - 2) * 32 + lane;
+    // Two pairs of warps, each expanding every other k-block of the ring: one k-block costs a pair a serial
+    // chain (load the packed words, wait for the slot, expand, proxy fence, arrive) of ~0.8 us whatever is
+    // done to shorten its parts, against 0.27 us of MMA at BN = 256.
+    const int pair = warp >= 12 ? 1 + ((warp - 12) >> 1) : 0;
+    const int p = (warp >= 12 ? (warp - 12) & 1 : warp - 2) * 32 + lane;
     int it = 0;
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
       const int m0 = (t / tiles_n) * BM;
       for (int kb = 0; kb < num_kb; ++kb, ++it) {
+        if (it % kAbitsPairs != pair) continue;
         const int s = it % kSt;
         const uint32_t ph = (it / kSt) & 1;
         uint2 w[2];
@@ -638,7 +648,7 @@ gemm_f16_kernel(const __grid_constant__ CUtensorMap tmap_a, const __grid_constan
         if (lane == 0) mbar_arrive(&full_bar[s]);
       }
     }
-  } else if (warp >= 4) {
+  } else if (warp >= 4 && warp < 12) {
     const int ew = warp & 3;                         // the TMEM lane quarter this warp may read
     const int half = (warp - 4) >> 2;                // which half of the tile's columns it drains
     int i = 0;

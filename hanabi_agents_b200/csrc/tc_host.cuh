@@ -73,7 +73,7 @@ inline int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUten
   attr[0].val.programmaticStreamSerializationAllowed = ep.pdl ? 1 : 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(grid);
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(threads_for(ABITS));
   cfg.dynamicSmemBytes = smem_bytes_for(BN_);
   cfg.stream = stream;
   cfg.attrs = attr;

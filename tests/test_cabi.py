@@ -53,3 +53,22 @@ def test_product_never_imports_oracle():
                 if re.search(r"^\s*(from|import)\s+oracle\b|oracle/|liboracle", src, flags=re.M):
                     bad.append(os.path.join(dirpath, f))
     assert not bad, bad
+
+
+def test_stream_override_nests_and_restores():
+    """_lib.use_stream points the library's launches at a given cudaStream_t without touching torch's
+    current stream (what the session uses for its per-seat insert streams); host logic only."""
+    from hanabi_agents_b200 import _lib
+    assert _lib._stream_override == []
+    with _lib.use_stream(0x1000):
+        assert _lib.current_stream_ptr() == 0x1000
+        with _lib.use_stream(0x2000):
+            assert _lib.current_stream_ptr() == 0x2000
+        assert _lib.current_stream_ptr() == 0x1000
+        try:
+            with _lib.use_stream(0x3000):
+                raise RuntimeError("boom")
+        except RuntimeError:
+            pass
+        assert _lib.current_stream_ptr() == 0x1000
+    assert _lib._stream_override == []

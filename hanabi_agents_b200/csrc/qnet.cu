@@ -733,10 +733,20 @@ __global__ void adam_refresh_kernel(LayerTable tab, long long n_eff, long long i
 
 // out[c, r] = in[r, c] for r < rows, c < cols (activations for the weight-gradient GEMMs): 32 x 32 tiles
 // through shared memory, grid (ceil(cols / 32), ceil(rows / 32)), 256 threads
-__global__ void transpose_act_kernel(const __half* __restrict__ in, int ld_in, int rows, int cols,
-                                     __half* __restrict__ out, int ld_out) {
+// (all hidden layers in one launch: blockIdx.z = layer -- as one launch per layer the second one ended 2 us
+// after the loss and the backward tail waited for it)
+struct TransposeActs {
+  const __half* in[kMaxLayers];
+  __half* out[kMaxLayers];
+  int cols[kMaxLayers];
+};
+__global__ void transpose_act_kernel(TransposeActs ta, int rows, int ld_out) {
   __shared__ __half tile[32][33];
+  const __half* __restrict__ in = ta.in[blockIdx.z];
+  __half* __restrict__ out = ta.out[blockIdx.z];
+  const int cols = ta.cols[blockIdx.z], ld_in = cols;
   const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  if (c0 >= cols) return;
   const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
   for (int i = ty; i < 32; i += 8) {
     const int r = r0 + i, c = c0 + tx;
@@ -1736,11 +1746,25 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     // transposed hidden activations of the sampled rows (B operand of the weight-gradient GEMMs), beside
     // the loss; ev_wt orders them before every gradient GEMM
     HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fwd, 0));
+    TransposeActs ta{};
+    int widest = 0;
     for (int l = 0; l + 1 < nl; ++l) {
-      const int N = q->tab.l[l].N;
-      transpose_act_kernel<<<dim3((N + 31) / 32, (B + 31) / 32), 256, 0, q->side2>>>(q->h[l], N, B, N, q->ht[l],
-                                                                                    2 * Bp);
+      ta.in[l] = q->h[l];
+      ta.out[l] = q->ht[l];
+      ta.cols[l] = q->tab.l[l].N;
+      widest = ta.cols[l] > widest ? ta.cols[l] : widest;
+    }
+    static const bool per_layer_t = getenv("HB_MERGED_TRANSPOSE") && atoi(getenv("HB_MERGED_TRANSPOSE")) == 0;
+    if (!per_layer_t) {
+      transpose_act_kernel<<<dim3((widest + 31) / 32, (B + 31) / 32, nl - 1), 256, 0, q->side2>>>(ta, B, 2 * Bp);
       HB_CUDA(cudaGetLastError());
+    } else {
+      for (int l = 0; l + 1 < nl; ++l) {
+        TransposeActs one{};
+        one.in[0] = ta.in[l]; one.out[0] = ta.out[l]; one.cols[0] = ta.cols[l];
+        transpose_act_kernel<<<dim3((ta.cols[l] + 31) / 32, (B + 31) / 32, 1), 256, 0, q->side2>>>(one, B, 2 * Bp);
+        HB_CUDA(cudaGetLastError());
+      }
     }
   }
   HB_CUDA(cudaEventRecord(q->ev_wt, q->side2));

@@ -1680,6 +1680,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   static const int adam_ctas = getenv("HB_ADAM_CTAS_PER_SM") ? atoi(getenv("HB_ADAM_CTAS_PER_SM")) : 0;
   static const bool bias0_main = getenv("HB_BIAS0_MAIN") && atoi(getenv("HB_BIAS0_MAIN")) != 0;
   static const bool dz0_plain = getenv("HB_DZ0_PLAIN") && atoi(getenv("HB_DZ0_PLAIN")) != 0;
+  static const bool act_t_side = !(getenv("HB_ACT_T_SIDE") && atoi(getenv("HB_ACT_T_SIDE")) == 0);
   static const bool dense_head_bw = getenv("HB_DENSE_HEAD_BW") && atoi(getenv("HB_DENSE_HEAD_BW")) != 0;
   const bool head_bw = q->n_atoms > 1 && q->n_atoms <= 64 && nl >= 2 && LL.K % 8 == 0 &&
                        (size_t)q->n_atoms * LL.K * 2 <= (size_t)kHeadBwSmemMax && !dense_head_bw;
@@ -1744,8 +1745,11 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   }
   if (chained) {
     // transposed hidden activations of the sampled rows (B operand of the weight-gradient GEMMs), beside
-    // the loss; ev_wt orders them before every gradient GEMM
-    HB_CUDA(cudaStreamWaitEvent(q->side2, q->ev_fwd, 0));
+    // the loss, on the high-priority side stream (idle when the forward passes are chained): behind the
+    // weight transposes on side2 they started 5 us after the forward pass had ended and the backward tail
+    // waited for them.  ev_join orders them before the backward pass.
+    cudaStream_t ts = act_t_side ? q->side : q->side2;
+    HB_CUDA(cudaStreamWaitEvent(ts, q->ev_fwd, 0));
     TransposeActs ta{};
     int widest = 0;
     for (int l = 0; l + 1 < nl; ++l) {
@@ -1756,17 +1760,18 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
     }
     static const bool per_layer_t = getenv("HB_MERGED_TRANSPOSE") && atoi(getenv("HB_MERGED_TRANSPOSE")) == 0;
     if (!per_layer_t) {
-      transpose_act_kernel<<<dim3((widest + 31) / 32, (B + 31) / 32, nl - 1), 256, 0, q->side2>>>(ta, B, 2 * Bp);
+      transpose_act_kernel<<<dim3((widest + 31) / 32, (B + 31) / 32, nl - 1), 256, 0, ts>>>(ta, B, 2 * Bp);
       HB_CUDA(cudaGetLastError());
     } else {
       for (int l = 0; l + 1 < nl; ++l) {
         TransposeActs one{};
         one.in[0] = ta.in[l]; one.out[0] = ta.out[l]; one.cols[0] = ta.cols[l];
-        transpose_act_kernel<<<dim3((ta.cols[l] + 31) / 32, (B + 31) / 32, 1), 256, 0, q->side2>>>(one, B, 2 * Bp);
+        transpose_act_kernel<<<dim3((ta.cols[l] + 31) / 32, (B + 31) / 32, 1), 256, 0, ts>>>(one, B, 2 * Bp);
         HB_CUDA(cudaGetLastError());
       }
     }
   }
+  if (chained && act_t_side) HB_CUDA(cudaEventRecord(q->ev_join, q->side));
   HB_CUDA(cudaEventRecord(q->ev_wt, q->side2));
   // 2. online network on both observation sets (main stream)
   if (!chained) {
@@ -1868,6 +1873,7 @@ static int net_grads_impl(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* 
   //    that only the first layer's update is left when the chain ends
   const float invB = 1.0f / (float)B;
   HB_CUDA(cudaStreamWaitEvent(s, q->ev_wt, 0));
+  if (chained && act_t_side) HB_CUDA(cudaStreamWaitEvent(s, q->ev_join, 0));
   bool tail_chained = false;          // dZ_0^T, dW_0 and db_0 came out of one launch (backward_tail_chain)
   for (int l = nl - 1; l >= 0; --l) {
     const LayerGeo& L = q->tab.l[l];

@@ -18,6 +18,7 @@
 // Built only on the public entry points of the other translation units (hb_rb_*, hb_net_*).
 #include "common.cuh"
 #include <new>
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -65,6 +66,8 @@ struct hb_learner {
   hb_comm* comm = nullptr;       // data parallel: per-layer all-reduce inside hb_learner_step
   int world = 1;
 };
+
+extern "C" const void* hb_net_kernel_handle(int which);   // qnet.cu
 
 namespace {
 
@@ -147,6 +150,39 @@ int borrow_net_buffers(hb_learner* L, int mask_terminal) {
   return HB_OK;
 }
 
+// HB_GRAPH_DOT: the types of the edges into the update's two PDL kernels on stderr.  (Measured: stream
+// capture makes EVERY incoming edge of a launch with the programmatic attribute programmatic -- type 1, port
+// 1 -- the cross-stream ones included; the backward chain still starts 2 us after the loss has ended, every SM
+// holding loss CTAs of 52 KB beside which a 213 KB chain CTA does not fit.)
+int inspect_edges(cudaGraph_t g) {
+  if (getenv("HB_GRAPH_DOT") == nullptr) return HB_OK;
+  size_t n = 0;
+  HB_CUDA(cudaGraphGetEdges_v2(g, nullptr, nullptr, nullptr, &n));
+  if (n == 0) return HB_OK;
+  cudaGraphNode_t* from = new cudaGraphNode_t[n];
+  cudaGraphNode_t* to = new cudaGraphNode_t[n];
+  cudaGraphEdgeData* data = new cudaGraphEdgeData[n];
+  const cudaError_t e = cudaGraphGetEdges_v2(g, from, to, data, &n);
+  auto name_of = [](cudaGraphNode_t node) -> const char* {
+    cudaGraphNodeType t;
+    if (cudaGraphNodeGetType(node, &t) != cudaSuccess || t != cudaGraphNodeTypeKernel) return "other";
+    cudaKernelNodeParams kp;
+    if (cudaGraphKernelNodeGetParams(node, &kp) != cudaSuccess) { cudaGetLastError(); return "kernel"; }
+    if (kp.func == hb_net_kernel_handle(0)) return "chain";
+    if (kp.func == hb_net_kernel_handle(1) || kp.func == hb_net_kernel_handle(2)) return "loss";
+    return "kernel";
+  };
+  for (size_t i = 0; i < n && e == cudaSuccess; ++i) {
+    const char* nt = name_of(to[i]);
+    if (nt[0] == 'c' || nt[0] == 'l')
+      fprintf(stderr, "[graph] edge -> %s from %s: type %d from_port %d\n", nt, name_of(from[i]),
+              (int)data[i].type, (int)data[i].from_port);
+  }
+  delete[] from; delete[] to; delete[] data;
+  if (e != cudaSuccess) return hb::cuda_fail(e, "inspect_edges", __FILE__, __LINE__);
+  return HB_OK;
+}
+
 template <class F>
 int capture(hb_learner* L, cudaGraphExec_t* exec, F body) {
   if (*exec) { cudaGraphExecDestroy(*exec); *exec = nullptr; }
@@ -156,6 +192,14 @@ int capture(hb_learner* L, cudaGraphExec_t* exec, F body) {
   const cudaError_t e = cudaStreamEndCapture(L->stream, &g);
   if (rc != HB_OK) { if (g) cudaGraphDestroy(g); return rc; }
   if (e != cudaSuccess) return hb::cuda_fail(e, "cudaStreamEndCapture", __FILE__, __LINE__);
+  // HB_GRAPH_DOT=<path>: the captured update (nodes, edges and their types) as a dot file
+  if (const char* dot = getenv("HB_GRAPH_DOT")) {
+    static int n_dots = 0;
+    char path[512];
+    snprintf(path, sizeof(path), "%s.%d", dot, n_dots++);
+    cudaGraphDebugDotPrint(g, path, cudaGraphDebugDotFlagsKernelNodeAttributes);
+  }
+  if (int prc = inspect_edges(g)) { cudaGraphDestroy(g); return prc; }
   const cudaError_t e2 = cudaGraphInstantiate(exec, g, 0);
   cudaGraphDestroy(g);
   if (e2 != cudaSuccess) return hb::cuda_fail(e2, "cudaGraphInstantiate", __FILE__, __LINE__);

@@ -1619,6 +1619,17 @@ int hb_net_learner_buffers(hb_qnet* q, int B, uint32_t** obs_staging, float** lo
 
 void* hb_net_loss_event(hb_qnet* q) { return q ? (void*)q->ev_loss : nullptr; }
 
+// (internal, learner.cu) the host-side handles of the update's two PDL kernels: 0 = tc::mlp_chain_kernel,
+// 1 = c51_loss_kernel<true>, 2 = c51_loss_kernel<false>
+const void* hb_net_kernel_handle(int which) {
+  switch (which) {
+    case 0: return (const void*)tc::mlp_chain_kernel;
+    case 1: return (const void*)c51_loss_kernel<true>;
+    case 2: return (const void*)c51_loss_kernel<false>;
+    default: return nullptr;
+  }
+}
+
 int hb_net_grads(hb_qnet* q, const uint32_t* d_obs_tm1, const int32_t* d_a_tm1, const float* d_r_t,
                  const uint32_t* d_obs_t, const uint8_t* d_term_t, const float* d_prios,
                  const float* d_weights, int B, float beta, float discount, int mask_terminal,

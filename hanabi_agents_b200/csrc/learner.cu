@@ -39,6 +39,12 @@ struct hb_learner {
   cudaEvent_t slotB_done[kSlots] = {nullptr, nullptr};
   int slot = 0, slotB = 0;
   const float* d_in = nullptr;   // h_in as the device addresses it
+  // the slot is copied to device memory on `copy` when it is staged (the host runs ahead of the device)
+  // instead of being read over PCIe by the sample kernel: -0.6 us per update (HB_LEARNER_KEYS_H2D=0: in place)
+  int keys_h2d = 1;
+  float* d_keys = nullptr;       // [kSlots][B + kDyn]
+  cudaStream_t copy = nullptr;
+  cudaEvent_t ev_keys = nullptr;
   int64_t* d_idx = nullptr;
   float* d_p32 = nullptr;
   float* d_dyn = nullptr;        // [kDyn] this step's scalars on the device
@@ -84,7 +90,8 @@ void drop_graphs(hb_learner* L) {
 int phase_a(hb_learner* L, int slot, float beta, float discount, int mask_terminal, bool fused_adam,
             float lr, float b1, float b2, float eps, float grad_scale, cudaStream_t s) {
   int rc;
-  const float* h_keys = L->d_in + (size_t)slot * (L->B + hb_learner::kDyn);   // pinned host, read in place
+  const float* h_keys = (L->keys_h2d ? L->d_keys : L->d_in) + (size_t)slot * (L->B + hb_learner::kDyn);
+  // (pinned host memory read in place, or its device copy)
   if (L->prioritized) {
     rc = hb_rb_sample_gather(L->rb, h_keys, L->B, h_keys + L->B, L->d_dyn, beta, L->d_idx, L->d_p32, nullptr,
                              L->w_is, L->o1, L->act, L->rew, L->o2, nullptr, L->term, 0, s);
@@ -219,6 +226,12 @@ int stage_inputs(hb_learner* L, const float* h_keys, const int64_t* h_idx, const
   memcpy(in + L->B, dyn, sizeof(float) * hb_learner::kDyn);
   if (L->prioritized) {
     memcpy(in, h_keys, (size_t)L->B * 4);                // read in place by the sample kernel
+    if (L->keys_h2d) {
+      const size_t words = (size_t)L->B + hb_learner::kDyn;
+      HB_CUDA(cudaMemcpyAsync(L->d_keys + (size_t)slot * words, in, words * 4, cudaMemcpyHostToDevice, L->copy));
+      HB_CUDA(cudaEventRecord(L->ev_keys, L->copy));
+      HB_CUDA(cudaStreamWaitEvent(L->stream, L->ev_keys, 0));
+    }
   } else {
     int64_t* hi = L->h_idx + (size_t)slot * L->B;
     memcpy(hi, h_idx, (size_t)L->B * 8);
@@ -286,6 +299,7 @@ int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_lea
   }
   if (const char* v = getenv("HB_LEARNER_PRIO_OVERLAP")) L->prio_overlap = atoi(v) != 0;
   if (const char* v = getenv("HB_LEARNER_PDL")) L->pdl = atoi(v) != 0;
+  if (const char* v = getenv("HB_LEARNER_KEYS_H2D")) L->keys_h2d = atoi(v) != 0;
   const size_t B = (size_t)batch;
   const int S = hb_learner::kSlots, D = hb_learner::kDyn;
   // the update's main chain runs at the highest priority, the priority write-back at the lowest (qnet.cu:
@@ -305,6 +319,9 @@ int hb_learner_create(hb_qnet* net, hb_replay* rb, int batch, int device, hb_lea
     e = cudaEventCreateWithFlags(&L->slot_done[i], cudaEventDisableTiming);
   for (int i = 0; i < S && e == cudaSuccess; ++i)
     e = cudaEventCreateWithFlags(&L->slotB_done[i], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaMalloc(&L->d_keys, S * (B + D) * 4);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&L->copy, cudaStreamNonBlocking);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&L->ev_keys, cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaMalloc(&L->d_idx, B * 8);
   if (e == cudaSuccess) e = cudaMalloc(&L->d_p32, B * 4);
   if (e == cudaSuccess) e = cudaMalloc(&L->d_dyn, D * 4);
@@ -339,6 +356,9 @@ int hb_learner_destroy(hb_learner* L) {
   if (L->ev_in) cudaEventDestroy(L->ev_in);
   if (L->ev_out) cudaEventDestroy(L->ev_out);
   if (L->ev_prio) cudaEventDestroy(L->ev_prio);
+  if (L->ev_keys) cudaEventDestroy(L->ev_keys);
+  if (L->copy) cudaStreamDestroy(L->copy);
+  if (L->d_keys) cudaFree(L->d_keys);
   if (L->prio) cudaStreamDestroy(L->prio);
   if (L->stream) cudaStreamDestroy(L->stream);
   delete L;

@@ -129,6 +129,7 @@ SIGNATURES = {
     "hb_net_grads_rainbow": (i32, [vp, vp, vp, vp, vp, vp, vp, vp, i32, f32, vp, vp, vp]),
     "hb_net_adam_tf": (i32, [vp, f32, f32, f32, f32, f32, vp]),
     "hb_net_loss_event": (vp, [vp]),
+    "hb_net_kernel_handle": (vp, [i32]),
     "hb_net_learner_buffers": (i32, [vp, i32, vp, vp, vp]),
     "hb_learner_loss": (vp, [vp]),
     "hb_learner_mean_loss": (vp, [vp]),

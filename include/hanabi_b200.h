@@ -420,6 +420,10 @@ int hb_net_adam_dyn(hb_qnet* q, const float* d_dyn, void* stream);
  * device-to-device copies.  The pointers stay valid until a call with a larger B. */
 int hb_net_learner_buffers(hb_qnet* q, int B, uint32_t** obs_staging, float** loss, float** mean_loss);
 void* hb_net_loss_event(hb_qnet* q);
+/* Diagnostics: the host-side handle (what cudaGraphKernelNodeGetParams reports as `func`) of the update's
+ * programmatically launched kernels -- 0 = the chained-GEMM kernel, 1 / 2 = the C51 loss with / without the
+ * head's backward product; NULL otherwise.  Used by the learner's HB_GRAPH_DOT dump to name graph nodes. */
+const void* hb_net_kernel_handle(int which);
 /* The same with the TF-Rainbow target of rainbow/rainbow_agent.py:183-236 (the `rainbow/` package's
  * learner): next action = argmax over the LEGAL next moves (d_legal_t, packed) of the
  * TARGET network's q; gamma^n masked by d_term_t (:191-197); d_weights = the caller's importance weights
